@@ -1,0 +1,309 @@
+// TEST INFRASTRUCTURE ONLY — C ABI over the UNMODIFIED reference classes
+// (compiled from /root/reference/src by oracle/build_ref.py into oracle/_ref/).
+// Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline /
+// --impl reference legs may load it.  It mirrors what
+// core_interface::Index::_dense_search does (src/core/interface/index.cc:581-652):
+// reformer->transform(query) -> searcher->search_impl(query, qmeta, count, ctx)
+// -> metric->normalize(score); and how tests build indexes
+// (tests/core/algorithm/flat/flat_searcher_test.cpp:29-78).
+#include <unistd.h>
+#include <atomic>
+#include <cstdio>
+#include <cstring>
+#include <memory>
+#include <string>
+#include <thread>
+#include <vector>
+#include <zvec/core/framework/index_builder.h>
+#include <zvec/core/framework/index_converter.h>
+#include <zvec/core/framework/index_factory.h>
+#include <zvec/core/framework/index_holder.h>
+#include <zvec/core/framework/index_meta.h>
+#include <zvec/core/framework/index_metric.h>
+#include <zvec/core/framework/index_reformer.h>
+#include <zvec/core/framework/index_searcher.h>
+
+using namespace zvec::core;
+using zvec::ailego::Params;
+
+namespace {
+
+// Zero-copy holder over caller memory: row i = base + i*elem, key = i.
+class RawHolder : public IndexHolder {
+ public:
+  RawHolder(const void *p, size_t n, IndexMeta::DataType t, size_t dim, size_t elem)
+      : p_((const char *)p), n_(n), t_(t), dim_(dim), elem_(elem) {}
+  size_t count() const override { return n_; }
+  size_t dimension() const override { return dim_; }
+  IndexMeta::DataType data_type() const override { return t_; }
+  size_t element_size() const override { return elem_; }
+  bool multipass() const override { return true; }
+  struct It : public IndexHolder::Iterator {
+    const RawHolder *h; size_t i{0};
+    explicit It(const RawHolder *hh) : h(hh) {}
+    const void *data() const override { return h->p_ + i * h->elem_; }
+    bool is_valid() const override { return i < h->n_; }
+    uint64_t key() const override { return i; }
+    void next() override { ++i; }
+  };
+  Iterator::Pointer create_iterator() override {
+    return Iterator::Pointer(new It(this));
+  }
+ private:
+  const char *p_; size_t n_; IndexMeta::DataType t_; size_t dim_, elem_;
+};
+
+struct RefIndex {
+  IndexMeta in_meta;            // what the caller's rows / queries look like
+  IndexMeta meta;               // what is stored (after converter)
+  IndexConverter::Pointer converter;
+  IndexReformer::Pointer reformer;
+  IndexMetric::Pointer metric;
+  IndexSearcher::Pointer searcher;
+  std::string path;
+  std::string stored;           // converted rows, row-major, n * meta.element_size()
+  size_t n{0};
+  ~RefIndex() {
+    if (searcher) { searcher->unload(); searcher->cleanup(); }
+    if (!path.empty()) ::unlink(path.c_str());
+  }
+};
+
+thread_local std::string g_err;
+int fail(int code, const std::string &m) { g_err = m; return code < 0 ? code : -1; }
+
+void parse_params(const char *kv, Params *p) {
+  // "key=value;key=value" ; value typed by shape: int, float, bool, else string
+  if (!kv) return;
+  std::string s(kv);
+  size_t pos = 0;
+  while (pos < s.size()) {
+    size_t e = s.find(';', pos);
+    if (e == std::string::npos) e = s.size();
+    std::string item = s.substr(pos, e - pos);
+    pos = e + 1;
+    size_t eq = item.find('=');
+    if (eq == std::string::npos) continue;
+    std::string k = item.substr(0, eq), v = item.substr(eq + 1);
+    char *end = nullptr;
+    long long iv = strtoll(v.c_str(), &end, 10);
+    if (end && *end == 0 && !v.empty()) { p->set(k, (int64_t)iv); continue; }
+    double dv = strtod(v.c_str(), &end);
+    if (end && *end == 0 && !v.empty()) { p->set(k, (float)dv); continue; }
+    if (v == "true" || v == "false") { p->set(k, v == "true"); continue; }
+    p->set(k, v);
+  }
+}
+
+}  // namespace
+
+extern "C" {
+
+const char *zref_last_error(void) { return g_err.c_str(); }
+
+// kind: "Flat" | "IVF".  dtype: IndexMeta::DataType of the CALLER's rows.
+// converter: "" or a registered converter name (e.g. Int8StreamingConverter,
+// HalfFloatConverter, CosineNormalizeConverter).  column_major: 0 row / 1 column.
+// build_params / search_params: "k=v;k=v".
+void *zref_index_create(const char *kind, const void *rows, uint64_t n, uint32_t dim,
+                        int dtype, const char *metric, const char *converter,
+                        int column_major, const char *build_params,
+                        const char *search_params) {
+  auto ix = std::make_unique<RefIndex>();
+  auto dt = (IndexMeta::DataType)dtype;
+  ix->in_meta.set_meta(dt, dim);
+  ix->in_meta.set_metric(metric, 0, Params());
+  ix->meta = ix->in_meta;
+  ix->n = n;
+  IndexHolder::Pointer holder =
+      std::make_shared<RawHolder>(rows, n, dt, dim, ix->in_meta.element_size());
+  if (converter && *converter) {
+    ix->converter = IndexFactory::CreateConverter(converter);
+    if (!ix->converter) { fail(-1, "no converter"); return nullptr; }
+    if (ix->converter->init(ix->in_meta, Params()) != 0) { fail(-1, "converter init"); return nullptr; }
+    if (IndexConverter::TrainAndTransform(ix->converter, holder) != 0) { fail(-1, "converter run"); return nullptr; }
+    holder = ix->converter->result();
+    ix->meta = ix->converter->meta();
+    if (!ix->meta.reformer_name().empty()) {
+      ix->reformer = IndexFactory::CreateReformer(ix->meta.reformer_name());
+      if (!ix->reformer || ix->reformer->init(ix->meta.reformer_params()) != 0) { fail(-1, "reformer"); return nullptr; }
+    }
+  }
+  ix->meta.set_major_order(column_major ? IndexMeta::MO_COLUMN : IndexMeta::MO_ROW);
+  // keep the stored bytes (what a device store must ingest)
+  {
+    size_t es = ix->meta.element_size();
+    ix->stored.resize(n * es);
+    auto it = holder->create_iterator();
+    size_t i = 0;
+    for (; it->is_valid() && i < n; it->next(), ++i)
+      std::memcpy(&ix->stored[i * es], it->data(), es);
+  }
+  ix->metric = IndexFactory::CreateMetric(ix->meta.metric_name());
+  if (!ix->metric || ix->metric->init(ix->meta, ix->meta.metric_params()) != 0) { fail(-1, "metric"); return nullptr; }
+
+  std::string k(kind);
+  static std::atomic<int> seq{0};
+  char buf[256];
+  snprintf(buf, sizeof buf, "/tmp/zref_%d_%d.index", (int)getpid(), seq++);
+  ix->path = buf;
+  auto builder = IndexFactory::CreateBuilder(k + "Builder");
+  auto dumper = IndexFactory::CreateDumper("FileDumper");
+  if (!builder || !dumper) { fail(-1, "no builder"); return nullptr; }
+  Params bp; parse_params(build_params, &bp);
+  int r = builder->init(ix->meta, bp);
+  if (r != 0) { fail(r, "builder init"); return nullptr; }
+  if (dumper->create(ix->path) != 0) { fail(-1, "dumper create"); return nullptr; }
+  r = IndexBuilder::TrainBuildAndDump(builder, holder, dumper);
+  if (r != 0) { fail(r, "build"); return nullptr; }
+  dumper->close();
+  ix->searcher = IndexFactory::CreateSearcher(k + "Searcher");
+  auto storage = IndexFactory::CreateStorage("MMapFileReadStorage");
+  Params sp; parse_params(search_params, &sp);
+  if (!ix->searcher || !storage) { fail(-1, "no searcher"); return nullptr; }
+  if (ix->searcher->init(sp) != 0) { fail(-1, "searcher init"); return nullptr; }
+  if (storage->open(ix->path, false) != 0) { fail(-1, "storage open"); return nullptr; }
+  r = ix->searcher->load(storage, IndexMetric::Pointer());
+  if (r != 0) { fail(r, "searcher load"); return nullptr; }
+  return ix.release();
+}
+
+void zref_index_destroy(void *h) { delete (RefIndex *)h; }
+
+// Stored (post-converter) layout: dtype, dimension, element bytes, metric name.
+int zref_index_info(void *h, int *dtype, uint32_t *dim, uint32_t *elem, uint64_t *n,
+                    char *metric_name, uint32_t cap) {
+  auto ix = (RefIndex *)h;
+  *dtype = (int)ix->meta.data_type();
+  *dim = ix->meta.dimension();
+  *elem = ix->meta.element_size();
+  *n = ix->n;
+  if (metric_name && cap) snprintf(metric_name, cap, "%s", ix->meta.metric_name().c_str());
+  return 0;
+}
+
+// Copy the stored rows (row-major, n*elem bytes) out.
+int zref_index_stored(void *h, void *out, uint64_t cap) {
+  auto ix = (RefIndex *)h;
+  if (cap < ix->stored.size()) return fail(-31, "cap");
+  std::memcpy(out, ix->stored.data(), ix->stored.size());
+  return 0;
+}
+
+// Transform caller-format queries to the stored format (reformer->transform);
+// identity copy when there is no reformer.  Returns bytes per query or <0.
+int zref_index_transform_queries(void *h, const void *queries, uint32_t count,
+                                 void *out, uint64_t cap) {
+  auto ix = (RefIndex *)h;
+  IndexQueryMeta qm(ix->in_meta.data_type(), ix->in_meta.dimension());
+  size_t qes = ix->in_meta.element_size();
+  size_t oes = ix->meta.element_size();
+  if (cap < (uint64_t)count * oes) return fail(-31, "cap");
+  for (uint32_t i = 0; i < count; ++i) {
+    const char *q = (const char *)queries + i * qes;
+    if (ix->reformer) {
+      std::string o; IndexQueryMeta om;
+      int r = ix->reformer->transform(q, qm, &o, &om);
+      if (r != 0) return fail(r, "transform");
+      if (o.size() != oes) return fail(-1, "transform size");
+      std::memcpy((char *)out + i * oes, o.data(), oes);
+    } else {
+      std::memcpy((char *)out + i * oes, q, oes);
+    }
+  }
+  return (int)oes;
+}
+
+// Search `count` caller-format queries, `batch` at a time through
+// search_impl(q, qmeta, batch, ctx) on `threads` threads (own context each).
+// out_keys/out_scores are count*topk (padded with key=~0, score=NaN);
+// out_index = row index inside the index.  normalize!=0 applies
+// metric->normalize like index.cc:624-628.
+int zref_index_search(void *h, const void *queries, uint32_t count, uint32_t topk,
+                      uint32_t batch, uint32_t threads, int normalize,
+                      uint64_t *out_keys, float *out_scores, uint32_t *out_index,
+                      uint32_t *out_counts) {
+  auto ix = (RefIndex *)h;
+  size_t oes = ix->meta.element_size();
+  std::string tq((size_t)count * oes, '\0');
+  int r = zref_index_transform_queries(h, queries, count, &tq[0], tq.size());
+  if (r < 0) return r;
+  IndexQueryMeta qm(ix->meta.data_type(), ix->meta.dimension());
+  if (batch == 0) batch = 1;
+  if (threads == 0) threads = 1;
+  uint32_t nb = (count + batch - 1) / batch;
+  std::atomic<uint32_t> next{0};
+  std::atomic<int> err{0};
+  auto work = [&]() {
+    auto ctx = ix->searcher->create_context();
+    ctx->set_topk(topk);
+    for (;;) {
+      uint32_t b = next.fetch_add(1);
+      if (b >= nb) break;
+      uint32_t q0 = b * batch, qn = std::min(batch, count - q0);
+      int rc = (qn == 1) ? ix->searcher->search_impl(&tq[(size_t)q0 * oes], qm, ctx)
+                         : ix->searcher->search_impl(&tq[(size_t)q0 * oes], qm, qn, ctx);
+      if (rc != 0) { err = rc; break; }
+      for (uint32_t i = 0; i < qn; ++i) {
+        const auto &res = ctx->result(i);
+        size_t o = (size_t)(q0 + i) * topk;
+        uint32_t c = (uint32_t)std::min<size_t>(res.size(), topk);
+        if (out_counts) out_counts[q0 + i] = c;
+        for (uint32_t j = 0; j < topk; ++j) {
+          if (j < c) {
+            float s = res[j].score();
+            if (normalize && ix->metric->support_normalize()) ix->metric->normalize(&s);
+            out_keys[o + j] = res[j].key(); out_scores[o + j] = s;
+            if (out_index) out_index[o + j] = res[j].index();
+          } else {
+            out_keys[o + j] = ~0ull; out_scores[o + j] = __builtin_nanf("");
+            if (out_index) out_index[o + j] = ~0u;
+          }
+        }
+      }
+    }
+  };
+  if (threads == 1) work();
+  else {
+    std::vector<std::thread> ts;
+    for (uint32_t t = 0; t < threads; ++t) ts.emplace_back(work);
+    for (auto &t : ts) t.join();
+  }
+  return err.load();
+}
+
+// Raw 1x1 distance of the index's metric (IndexMetric::distance()) between
+// stored-format rows m[i] and ONE stored-format query: out[i], i<n.
+int zref_index_distances(void *h, const void *m, uint64_t n, const void *q, float *out) {
+  auto ix = (RefIndex *)h;
+  auto f = ix->metric->distance();
+  if (!f) return fail(-12, "no distance");
+  size_t es = ix->meta.element_size();
+  for (uint64_t i = 0; i < n; ++i)
+    f((const char *)m + i * es, q, ix->meta.dimension(), out + i);
+  return 0;
+}
+
+// Stand-alone metric distance: metric name + dtype + dimension (stored dim,
+// tail included) [+ origin metric for QuantizedInteger].
+int zref_metric_distances(const char *metric, const char *origin_metric, int dtype,
+                          uint32_t dim, const void *m, uint64_t n, const void *q,
+                          float *out) {
+  IndexMeta meta;
+  meta.set_meta((IndexMeta::DataType)dtype, dim);
+  Params mp;
+  if (origin_metric && *origin_metric)
+    mp.set("proxima.quantized_integer.metric.origin_metric_name", std::string(origin_metric));
+  meta.set_metric(metric, 0, mp);
+  auto mt = IndexFactory::CreateMetric(metric);
+  if (!mt) return fail(-12, "no metric");
+  int r = mt->init(meta, mp);
+  if (r != 0) return fail(r, "metric init");
+  auto f = mt->distance();
+  if (!f) return fail(-12, "no distance");
+  size_t es = meta.element_size();
+  for (uint64_t i = 0; i < n; ++i) f((const char *)m + i * es, q, dim, out + i);
+  return 0;
+}
+
+}  // extern "C"
