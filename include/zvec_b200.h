@@ -1,0 +1,165 @@
+/* zvec_b200.h — C ABI of the B200-native exhaustive-scan path (distance + fused top-k)
+ * that replaces zvec's Flat / IVF posting-list scan.  Plain pointers and sizes only.
+ *
+ * Score convention = the reference's INTERNAL one: smaller is better;
+ * inner product is returned as -x.q, cosine as 1 - x^.q^; IndexMetric::normalize()
+ * (src/core/metric/inner_product_metric.cc:377-379) is applied by the caller, exactly
+ * as src/core/interface/index.cc:624-628 does after search_impl().
+ *
+ * Every call returns 0 or a NEGATIVE code with the reference's IndexError values
+ * (src/core/framework/index_error.cc:19-70).  There is no CPU fallback: without a
+ * CUDA device every compute entry point returns ZVB200_ERR_RUNTIME.
+ */
+#ifndef ZVEC_B200_H_
+#define ZVEC_B200_H_
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define ZVB200_OK 0
+#define ZVB200_ERR_RUNTIME (-1)           /* IndexError_Runtime (CUDA / NCCL failure) */
+#define ZVB200_ERR_UNSUPPORTED (-12)      /* IndexError_Unsupported */
+#define ZVB200_ERR_NOMEMORY (-19)         /* IndexError_NoMemory */
+#define ZVB200_ERR_NOREADY (-21)          /* IndexError_NoReady (store not sealed) */
+#define ZVB200_ERR_MISMATCH (-24)         /* IndexError_Mismatch */
+#define ZVB200_ERR_INVALID_ARGUMENT (-31) /* IndexError_InvalidArgument */
+
+/* IndexMeta::DataType values (src/include/zvec/core/framework/index_meta.h:31-40). */
+#define ZVB200_DT_FP16 1
+#define ZVB200_DT_FP32 2
+#define ZVB200_DT_INT8 4
+
+/* Metric = reference metric name (+ origin metric for "QuantizedInteger").
+ *  L2SQ    "SquaredEuclidean"  src/core/metric/euclidean_metric.cc:743-906
+ *  L2      "Euclidean"         euclidean_metric.cc:910-1027
+ *  IP      "InnerProduct"      inner_product_metric.cc:256-434        (score = -x.q)
+ *  COSINE  "Cosine"            cosine_metric.cc:141-230; rows carry a trailing fp32 norm
+ *                              slot (dim+1 fp32 / dim+2 fp16) that is not read
+ *  QI8_*   "QuantizedInteger"  quantized_integer_metric.cc:30-318 with origin metric
+ *                              SquaredEuclidean / InnerProduct / Cosine; rows = d int8
+ *                              codes + 16 B tail (+4 B norm for cosine)
+ *                              (quantized_integer_metric_matrix.h:36-60,94-112,167-174)
+ */
+#define ZVB200_METRIC_L2SQ 0
+#define ZVB200_METRIC_L2 1
+#define ZVB200_METRIC_IP 2
+#define ZVB200_METRIC_COSINE 3
+#define ZVB200_METRIC_QI8_L2SQ 4
+#define ZVB200_METRIC_QI8_IP 5
+#define ZVB200_METRIC_QI8_COSINE 6
+
+#define ZVB200_INVALID_INDEX 0xffffffffu
+#define ZVB200_INVALID_KEY 0xffffffffffffffffull /* kInvalidKey, index_helper / flat_streamer_entity.cc:269 */
+#define ZVB200_MAX_TOPK 1024u
+
+typedef struct zvb200_store zvb200_store; /* device-resident vector store on ONE GPU */
+typedef struct zvb200_ctx zvb200_ctx;     /* per-thread search context (IndexContext) */
+
+const char *zvb200_version(void);
+/* Message of the last failing call on this thread. */
+const char *zvb200_last_error(void);
+/* Number of CUDA devices visible (0 when there is none / no driver). */
+int zvb200_device_count(void);
+/* Kernels launched by this library in this process so far (bench.py's gpu_launches). */
+uint64_t zvb200_kernel_launches(void);
+
+/* ---- store: replaces FlatSearcher::load / FlatStreamerEntity storage reads
+ * (src/core/algorithm/flat/flat_searcher.cc:118-152, flat_streamer_entity.cc:900-991).
+ * `dim` is the reference's STORED dimension (IndexMeta::dimension(), tails included);
+ * one element is IndexMeta::element_size() bytes: dim*4 (fp32), dim*2 (fp16), dim (int8).
+ */
+int zvb200_store_create(int device, int dtype, int metric, uint32_t dim, zvb200_store **out);
+int zvb200_store_destroy(zvb200_store *s);
+/* Pre-size the device arrays for `rows` rows (optional; append grows geometrically). */
+int zvb200_store_reserve(zvb200_store *s, uint64_t rows);
+/* Append n rows in the reference's row-major element layout from HOST memory.
+ * keys may be NULL (key = row index).  A key of ZVB200_INVALID_KEY marks a hole that the
+ * scan skips (flat_streamer_entity.cc:269). */
+int zvb200_store_append(zvb200_store *s, const void *rows, uint64_t n, const uint64_t *keys);
+/* Same, rows already in DEVICE memory of the store's GPU (synthetic data, ingest kernels). */
+int zvb200_store_append_device(zvb200_store *s, const void *rows_dev, uint64_t n);
+/* Publish appended rows to searches (computes |x|^2 for the batched L2 path). */
+int zvb200_store_seal(zvb200_store *s);
+uint64_t zvb200_store_count(const zvb200_store *s);
+/* Mark a row deleted / undeleted (FlatStreamerEntity DeletionMap, flat_index_format.h:106-126). */
+int zvb200_store_set_deleted(zvb200_store *s, uint64_t row, int deleted);
+/* Copy one stored row back in the reference layout (IndexSearcher::get_vector). */
+int zvb200_store_get_vector(const zvb200_store *s, uint64_t row, void *out, size_t cap);
+/* Bytes of HBM one full scan must read (the roofline's algorithmic bytes). */
+uint64_t zvb200_store_scan_bytes(const zvb200_store *s);
+
+/* ---- context: replaces FlatSearcherContext / FlatStreamerContext
+ * (flat_searcher_context.h:187-196, index_context.h:57-260): owns a CUDA stream, pinned
+ * staging and device scratch.  One per calling thread. */
+int zvb200_ctx_create(zvb200_store *s, zvb200_ctx **out);
+int zvb200_ctx_destroy(zvb200_ctx *c);
+
+/* ---- search: replaces FlatSearcher::search_impl(query, qmeta, count, ctx)
+ * (flat_searcher.cc:186-211) + heap/sort/topk_to_result (index_document.h:250-261,
+ * heap.h:103-115,173-175, flat_streamer_context.h:104-128).
+ *  queries  : q consecutive elements in the STORED layout (post-reformer), HOST memory
+ *  k        : 1..ZVB200_MAX_TOPK
+ *  threshold: IndexContext::threshold() in internal score units; FLT_MAX = none.
+ *             Rows with score > threshold (and NaN scores) are not returned.
+ *  filter   : NULL, or a HOST bitmap of store_count bits, bit i set = drop row i
+ *             (IndexFilter returning true; evaluated by the host adaptor).
+ *  outputs  : q*k each, sorted ascending by (score, row index); unused slots hold
+ *             key = ZVB200_INVALID_KEY, index = ZVB200_INVALID_INDEX, score = NaN.
+ *             out_keys / out_index / out_counts may be NULL.
+ * Tie-break (documented difference): among equal scores the LOWER row index
+ * wins; the reference's choice at the k-th score is heap-order dependent.
+ */
+int zvb200_search(zvb200_ctx *c, const void *queries, uint32_t q, uint32_t k, float threshold,
+                  const uint32_t *filter, uint64_t *out_keys, float *out_scores,
+                  uint32_t *out_index, uint32_t *out_counts);
+
+/* Same with DEVICE-resident queries / filter / outputs, asynchronous on the context's
+ * stream; out_scores_dev and out_index_dev are q*k.  zvb200_ctx_sync() waits. */
+int zvb200_search_device(zvb200_ctx *c, const void *queries_dev, uint32_t q, uint32_t k,
+                         float threshold, const uint32_t *filter_dev, float *out_scores_dev,
+                         uint32_t *out_index_dev);
+int zvb200_ctx_sync(zvb200_ctx *c);
+/* The context's cudaStream_t (as void*) so callers can record events on it. */
+void *zvb200_ctx_stream(zvb200_ctx *c);
+/* Force a scan kernel: 0 auto, 1 GEMV scan (CUDA cores), 2 tiled CUDA-core, 3 tcgen05. */
+int zvb200_ctx_set_kernel(zvb200_ctx *c, int which);
+/* Name of the scan kernel the last search on this context used. */
+const char *zvb200_ctx_last_kernel(const zvb200_ctx *c);
+
+/* ---- distance functions: replaces ailego XxxDistanceMatrix<T,1,1>::Compute as handed out
+ * by IndexMetric::distance() (src/core/metric/euclidean_metric.cc:785-851): out[j*n+i] =
+ * dist(m[i], q[j]).  HOST pointers; computed on `device`. */
+int zvb200_distance_matrix(int device, int metric, int dtype, uint32_t dim, const void *m,
+                           uint64_t n, const void *q, uint32_t nq, float *out);
+
+/* ---- multi-GPU shard merge: replaces the concat + std::sort + truncate of
+ * CombinedVectorColumnIndexer::Search (src/db/index/column/vector_column/
+ * combined_vector_column_indexer.cc:167-222).  `lists` G sorted per-shard results laid
+ * out [g][q][k] (DEVICE memory, e.g. the NCCL all-gather output); index values are
+ * shard-local and are offset by shard_base[g].  Output q*k sorted by (score, global row). */
+int zvb200_merge_topk_device(zvb200_ctx *c, const float *scores_dev, const uint32_t *index_dev,
+                             uint32_t g, const uint64_t *shard_base, uint32_t q, uint32_t k,
+                             float *out_scores_dev, uint64_t *out_rows_dev);
+
+/* ---- IVF: replaces IVFSearcher::search_impl (src/core/algorithm/ivf/ivf_searcher.cc:
+ * 183-250): coarse search over centroids (IVFCentroidIndex::search, ivf_centroid_index.cc:
+ * 273-295) + IVFEntity::search per list (ivf_entity.cc:662-716) under the scan budget of
+ * IVFSearcherContext::update (ivf_searcher_context.h:61-79).
+ * The store must hold the rows grouped by list: rows [list_offsets[l], list_offsets[l+1])
+ * belong to list l.  centroids: nlist elements of the store's dtype/metric layout, HOST. */
+int zvb200_ivf_attach(zvb200_store *s, const void *centroids, uint32_t nlist,
+                      const uint64_t *list_offsets);
+/* nprobe = max(1, round(nlist*scan_ratio)); max_scan_count = max(bf_threshold,
+ * ceil(N*scan_ratio)): lists are visited in coarse order while the rows scanned so far
+ * are < max_scan_count. */
+int zvb200_ivf_search(zvb200_ctx *c, const void *queries, uint32_t q, uint32_t k,
+                      uint32_t nprobe, uint64_t max_scan_count, uint64_t *out_keys,
+                      float *out_scores, uint32_t *out_index, uint32_t *out_counts);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* ZVEC_B200_H_ */

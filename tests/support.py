@@ -1,0 +1,275 @@
+"""Test-only helpers: oracle loaders (oracle/ is the CHECKER, never the product path),
+seeded data generators and the parity comparison with the documented tie rule."""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+ORACLE_DIR = os.path.join(ROOT, "oracle")
+
+DT_FP16, DT_FP32, DT_INT8 = 1, 2, 4
+M_L2SQ, M_L2, M_IP, M_COSINE, M_QI8_L2SQ, M_QI8_IP, M_QI8_COSINE = range(7)
+
+
+def P(a):
+    return a.ctypes.data_as(C.c_void_p) if a is not None else None
+
+
+_oracle = None
+
+
+def oracle():
+    """The scalar CPU restatement (oracle/zvec_oracle.cc), built on demand with g++."""
+    global _oracle
+    if _oracle is None:
+        so = os.path.join(ORACLE_DIR, "libzvec_oracle.so")
+        src = os.path.join(ORACLE_DIR, "zvec_oracle.cc")
+        if not os.path.exists(so) or os.path.getmtime(so) < os.path.getmtime(src):
+            subprocess.check_call(["make", "-C", ORACLE_DIR, "libzvec_oracle.so"], stdout=subprocess.DEVNULL)
+        L = C.CDLL(so)
+        L.zo_distance.restype = C.c_float
+        L.zo_distance.argtypes = [C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_uint32]
+        L.zo_normalize_score.restype = C.c_float
+        L.zo_normalize_score.argtypes = [C.c_int, C.c_float]
+        L.zo_distances.argtypes = [C.c_int, C.c_int, C.c_void_p, C.c_uint64, C.c_uint32, C.c_uint32,
+                                   C.c_void_p, C.c_void_p]
+        L.zo_flat_search.argtypes = [C.c_int, C.c_int, C.c_void_p, C.c_uint64, C.c_uint32, C.c_uint32,
+                                     C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_float,
+                                     C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+        L.zo_quantize_record_int8.argtypes = [C.c_void_p, C.c_uint32, C.c_int, C.c_void_p]
+        L.zo_cosine_normalize_fp32.argtypes = [C.c_void_p, C.c_uint32, C.c_void_p]
+        L.zo_fp32_to_fp16.argtypes = [C.c_void_p, C.c_uint64, C.c_void_p]
+        L.zo_fp16_to_fp32.argtypes = [C.c_void_p, C.c_uint64, C.c_void_p]
+        _oracle = L
+    return _oracle
+
+
+def cpu_has(flag):
+    try:
+        with open("/proc/cpuinfo") as f:
+            for line in f:
+                if line.startswith("flags"):
+                    return flag in line.split()
+    except OSError:
+        pass
+    return False
+
+
+_ref = False
+
+
+def ref():
+    """The reference itself (oracle/_ref, compiled from /root/reference by oracle/build_ref.py);
+    None when the prebuilt library is absent or the host CPU cannot run it."""
+    global _ref
+    if _ref is False:
+        _ref = None
+        cands = []
+        if cpu_has("avx512f") and cpu_has("avx512bw") and cpu_has("avx512vl") and cpu_has("avx512dq"):
+            cands.append("libzvec_ref_skylake-avx512.so")
+        if cpu_has("avx2") and cpu_has("fma"):
+            cands.append("libzvec_ref_haswell.so")
+        for c in cands:
+            p = os.path.join(ORACLE_DIR, "_ref", c)
+            if os.path.exists(p):
+                L = C.CDLL(p)
+                L.zref_index_create.restype = C.c_void_p
+                L.zref_index_create.argtypes = [C.c_char_p, C.c_void_p, C.c_uint64, C.c_uint32, C.c_int,
+                                                C.c_char_p, C.c_char_p, C.c_int, C.c_char_p, C.c_char_p]
+                L.zref_last_error.restype = C.c_char_p
+                L.zref_index_destroy.argtypes = [C.c_void_p]
+                L.zref_index_info.argtypes = [C.c_void_p] + [C.c_void_p] * 5 + [C.c_uint32]
+                L.zref_index_stored.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64]
+                L.zref_index_transform_queries.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p, C.c_uint64]
+                L.zref_index_search.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32,
+                                                C.c_uint32, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+                L.zref_index_distances.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p]
+                L.zref_metric_distances.argtypes = [C.c_char_p, C.c_char_p, C.c_int, C.c_uint32, C.c_void_p,
+                                                    C.c_uint64, C.c_void_p, C.c_void_p]
+                L._name = c
+                _ref = L
+                break
+    return _ref
+
+
+class RefIndex:
+    """A Flat/IVF index built and searched by the reference's own classes."""
+
+    def __init__(self, rows_fp32_or_native, dtype, dim, metric, converter="", kind="Flat", column_major=False,
+                 build_params="", search_params=""):
+        L = ref()
+        self.L = L
+        self.rows = np.ascontiguousarray(rows_fp32_or_native)
+        esz = {DT_FP32: 4, DT_FP16: 2, DT_INT8: 1}[dtype]
+        n = self.rows.nbytes // (dim * esz)
+        self.h = L.zref_index_create(kind.encode(), P(self.rows), n, dim, dtype, metric.encode(),
+                                     converter.encode(), int(column_major), build_params.encode(),
+                                     search_params.encode())
+        if not self.h:
+            raise RuntimeError("reference index build failed: %s" % L.zref_last_error().decode())
+        dt, dm, el, nn = C.c_int(), C.c_uint32(), C.c_uint32(), C.c_uint64()
+        name = C.create_string_buffer(64)
+        L.zref_index_info(self.h, C.byref(dt), C.byref(dm), C.byref(el), C.byref(nn), name, 64)
+        self.dtype, self.dim, self.elem, self.n = dt.value, dm.value, el.value, nn.value
+        self.metric_name = name.value.decode()
+        self.in_elem = dim * esz
+
+    def stored(self):
+        out = np.zeros((self.n, self.elem), np.uint8)
+        assert self.L.zref_index_stored(self.h, P(out), out.nbytes) == 0
+        return out
+
+    def transform_queries(self, queries):
+        queries = np.ascontiguousarray(queries)
+        q = queries.nbytes // self.in_elem
+        out = np.zeros((q, self.elem), np.uint8)
+        r = self.L.zref_index_transform_queries(self.h, P(queries), q, P(out), out.nbytes)
+        assert r == self.elem, r
+        return out
+
+    def search(self, queries, k, batch=1, threads=1, normalize=False):
+        queries = np.ascontiguousarray(queries)
+        q = queries.nbytes // self.in_elem
+        keys = np.zeros((q, k), np.uint64)
+        scores = np.zeros((q, k), np.float32)
+        index = np.zeros((q, k), np.uint32)
+        counts = np.zeros(q, np.uint32)
+        r = self.L.zref_index_search(self.h, P(queries), q, k, batch, threads, int(normalize), P(keys),
+                                     P(scores), P(index), P(counts))
+        assert r == 0, r
+        return keys, scores, index, counts
+
+    def distances(self, stored_rows, stored_query):
+        stored_rows = np.ascontiguousarray(stored_rows)
+        n = stored_rows.nbytes // self.elem
+        out = np.zeros(n, np.float32)
+        assert self.L.zref_index_distances(self.h, P(stored_rows), n, P(np.ascontiguousarray(stored_query)), P(out)) == 0
+        return out
+
+    def close(self):
+        if self.h:
+            self.L.zref_index_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+# ---------------------------------------------------------------------------------------
+# oracle-side helpers
+# ---------------------------------------------------------------------------------------
+def oracle_flat_search(metric, dtype, stored_rows, dim, queries, k, threshold=None, keys=None, drop=None):
+    O = oracle()
+    stored_rows = np.ascontiguousarray(stored_rows)
+    queries = np.ascontiguousarray(queries)
+    elem = dim * {DT_FP32: 4, DT_FP16: 2, DT_INT8: 1}[dtype]
+    n = stored_rows.nbytes // elem
+    q = queries.nbytes // elem
+    okeys = np.zeros((q, k), np.uint64)
+    oscores = np.zeros((q, k), np.float32)
+    oindex = np.zeros((q, k), np.uint32)
+    ocounts = np.zeros(q, np.uint32)
+    th = float(np.finfo(np.float32).max) if threshold is None else threshold
+    kk = None if keys is None else np.ascontiguousarray(keys, dtype=np.uint64)
+    dd = None if drop is None else np.ascontiguousarray(drop, dtype=np.uint8)
+    O.zo_flat_search(metric, dtype, P(stored_rows), n, dim, elem, P(kk), P(dd), P(queries), q, k, th,
+                     P(okeys), P(oscores), P(oindex), P(ocounts))
+    return okeys, oscores, oindex, ocounts
+
+
+def oracle_distances(metric, dtype, stored_rows, dim, query):
+    O = oracle()
+    stored_rows = np.ascontiguousarray(stored_rows)
+    elem = dim * {DT_FP32: 4, DT_FP16: 2, DT_INT8: 1}[dtype]
+    n = stored_rows.nbytes // elem
+    out = np.zeros(n, np.float32)
+    O.zo_distances(metric, dtype, P(stored_rows), n, dim, elem, P(np.ascontiguousarray(query)), P(out))
+    return out
+
+
+def quantize_int8(rows_fp32, is_euclidean=True):
+    """Int8StreamingConverter / IntegerStreamingReformer layout via the oracle restatement."""
+    O = oracle()
+    rows = np.ascontiguousarray(rows_fp32, dtype=np.float32)
+    n, d = rows.shape
+    out = np.zeros((n, d + 16), np.uint8)
+    for i in range(n):
+        O.zo_quantize_record_int8(C.c_void_p(rows[i].ctypes.data), d, int(is_euclidean), C.c_void_p(out[i].ctypes.data))
+    return out
+
+
+def cosine_normalize_fp32(rows_fp32):
+    O = oracle()
+    rows = np.ascontiguousarray(rows_fp32, dtype=np.float32)
+    n, d = rows.shape
+    out = np.zeros((n, d + 1), np.float32)
+    for i in range(n):
+        O.zo_cosine_normalize_fp32(C.c_void_p(rows[i].ctypes.data), d, C.c_void_p(out[i].ctypes.data))
+    return out
+
+
+# ---------------------------------------------------------------------------------------
+# parity rule (DESIGN.md "tie-break")
+# ---------------------------------------------------------------------------------------
+def check_topk_parity(got_index, got_scores, exp_index, exp_scores, all_dist=None, exact=False, rtol=1e-4,
+                      what=""):
+    """Compare one query's result lists.
+
+    exact=True (integer paths): score sequences must be bit-identical; indices must match as
+    SETS inside every run of equal scores, except the run that touches position k-1, whose
+    members must only come from rows having exactly that score (checked with all_dist).
+    exact=False (fp32/fp16): scores within rtol; index order may differ only inside groups of
+    adjacent results whose scores are within rtol of each other (near-ties), and boundary rows
+    must have a true distance within rtol of the k-th score.
+    """
+    got_index = np.asarray(got_index); exp_index = np.asarray(exp_index)
+    got_scores = np.asarray(got_scores, np.float32); exp_scores = np.asarray(exp_scores, np.float32)
+    valid_e = exp_index != 0xFFFFFFFF
+    valid_g = got_index != 0xFFFFFFFF
+    assert valid_e.sum() == valid_g.sum(), "%s: result count %d != %d" % (what, valid_g.sum(), valid_e.sum())
+    n = int(valid_e.sum())
+    if n == 0:
+        return
+    gs, es, gi, ei = got_scores[:n], exp_scores[:n], got_index[:n], exp_index[:n]
+    assert np.all(np.diff(gs) >= 0), "%s: scores not ascending" % what
+    if exact:
+        assert np.array_equal(gs.view(np.uint32), es.view(np.uint32)), \
+            "%s: scores differ bitwise\n got %s\n exp %s" % (what, gs, es)
+        last = es[n - 1]
+        for s in np.unique(es):
+            a = set(gi[gs == s].tolist()); b = set(ei[es == s].tolist())
+            if s == last:
+                if all_dist is not None:
+                    cand = set(np.nonzero(all_dist == s)[0].tolist())
+                    assert a <= cand, "%s: boundary ids %s not at the k-th score" % (what, a - cand)
+                else:
+                    assert len(a) == len(b)
+            else:
+                assert a == b, "%s: ids differ at score %r: %s vs %s" % (what, s, a, b)
+        # inside a run of equal scores our order is by row index (documented tie-break)
+        for s in np.unique(gs):
+            run = gi[gs == s]
+            assert np.all(np.diff(run.astype(np.int64)) > 0), "%s: tie-break not by row index" % what
+        return
+    denom = np.maximum(np.abs(es), 1e-30)
+    assert np.all(np.abs(gs - es) <= rtol * np.maximum(denom, 1e-6) + 1e-7), \
+        "%s: scores beyond rtol\n got %s\n exp %s" % (what, gs, es)
+    if np.array_equal(gi, ei):
+        return
+    # differences allowed only among near-ties
+    tol = rtol * max(abs(float(es[n - 1])), 1e-6) + 1e-7
+    for pos in range(n):
+        if gi[pos] == ei[pos]:
+            continue
+        # the row we returned must be (near-)tied with the expected score at this position
+        if all_dist is not None:
+            assert abs(float(all_dist[gi[pos]]) - float(es[pos])) <= 2 * tol, \
+                "%s: pos %d id %d (true %r) vs expected id %d (%r): not a near-tie" % (
+                    what, pos, gi[pos], all_dist[gi[pos]], ei[pos], es[pos])
+        else:
+            assert abs(float(gs[pos]) - float(es[pos])) <= 2 * tol

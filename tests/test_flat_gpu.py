@@ -1,0 +1,199 @@
+"""GPU parity tests: the CUDA scan (through the C ABI) against the oracle on the same seeded
+inputs, and against the reference's own results where oracle/_ref is present."""
+import numpy as np
+import pytest
+
+import support as S
+import zvec_b200 as z
+
+pytestmark = pytest.mark.gpu
+
+ESZ = {S.DT_FP32: 4, S.DT_FP16: 2, S.DT_INT8: 1}
+
+
+def make_stored(kind, n, d, seed):
+    """-> (metric id, dtype, stored dim, stored rows bytes [n, elem], stored queries fn)"""
+    rng = np.random.default_rng(seed)
+    x = rng.standard_normal((n, d)).astype(np.float32)
+
+    def conv(a):
+        if kind in ("fp32_l2", "fp32_ip", "fp32_l2sqrt"):
+            return a.astype(np.float32).view(np.uint8).reshape(len(a), -1)
+        if kind in ("fp16_l2", "fp16_ip"):
+            return a.astype(np.float16).view(np.uint8).reshape(len(a), -1)
+        if kind == "fp32_cos":
+            return S.cosine_normalize_fp32(a).view(np.uint8).reshape(len(a), -1)
+        if kind == "fp16_cos":
+            c = S.cosine_normalize_fp32(a)
+            h = c[:, :-1].astype(np.float16).view(np.uint8).reshape(len(a), -1)
+            return np.concatenate([h, c[:, -1:].copy().view(np.uint8).reshape(len(a), 4)], axis=1)
+        if kind in ("i8_l2", "i8_ip"):
+            return np.clip(np.round(a * 40), -127, 127).astype(np.int8).view(np.uint8).reshape(len(a), -1)
+        if kind == "qi8_l2":
+            return S.quantize_int8(a, True)
+        if kind == "qi8_ip":
+            return S.quantize_int8(a, False)
+        if kind == "qi8_cos":
+            c = S.cosine_normalize_fp32(a)
+            qz = S.quantize_int8(c[:, :-1], False)
+            return np.concatenate([qz, c[:, -1:].copy().view(np.uint8).reshape(len(a), 4)], axis=1)
+        raise KeyError(kind)
+
+    table = {
+        "fp32_l2": (S.M_L2SQ, S.DT_FP32, d), "fp32_l2sqrt": (S.M_L2, S.DT_FP32, d), "fp32_ip": (S.M_IP, S.DT_FP32, d),
+        "fp16_l2": (S.M_L2SQ, S.DT_FP16, d), "fp16_ip": (S.M_IP, S.DT_FP16, d),
+        "fp32_cos": (S.M_COSINE, S.DT_FP32, d + 1), "fp16_cos": (S.M_COSINE, S.DT_FP16, d + 2),
+        "i8_l2": (S.M_L2SQ, S.DT_INT8, d), "i8_ip": (S.M_IP, S.DT_INT8, d),
+        "qi8_l2": (S.M_QI8_L2SQ, S.DT_INT8, d + 16), "qi8_ip": (S.M_QI8_IP, S.DT_INT8, d + 16),
+        "qi8_cos": (S.M_QI8_COSINE, S.DT_INT8, d + 20),
+    }
+    metric, dt, sdim = table[kind]
+    return metric, dt, sdim, np.ascontiguousarray(conv(x)), conv
+
+
+KINDS = ["fp32_l2", "fp32_l2sqrt", "fp32_ip", "fp16_l2", "fp16_ip", "fp32_cos", "fp16_cos", "i8_l2", "i8_ip",
+         "qi8_l2", "qi8_ip", "qi8_cos"]
+
+
+def run_case(kind, n, d, q, k, seed, kernel=0, drop=None, keys=None, threshold=None, filt=None):
+    metric, dt, sdim, stored, conv = make_stored(kind, n, d, seed)
+    rng = np.random.default_rng(seed + 1000)
+    queries = np.ascontiguousarray(conv(rng.standard_normal((q, d)).astype(np.float32)))
+    st = z.Store(dt, metric, sdim)
+    half = n // 2
+    st.append(stored[:half], None if keys is None else keys[:half])   # two appends: growth path
+    st.append(stored[half:], None if keys is None else keys[half:])
+    st.seal()
+    if drop is not None:
+        for r in np.nonzero(drop)[0]:
+            st.set_deleted(int(r), True)
+    ctx = z.Context(st)
+    ctx.set_kernel(kernel)
+    fb = None
+    odrop = None if drop is None else drop.astype(np.uint8).copy()
+    if filt is not None:
+        fb = np.zeros((n + 31) // 32, np.uint32)
+        for r in np.nonzero(filt)[0]:
+            fb[r >> 5] |= np.uint32(1 << (r & 31))
+        odrop = filt.astype(np.uint8) if odrop is None else (odrop | filt.astype(np.uint8))
+    th = float(np.finfo(np.float32).max) if threshold is None else threshold
+    gk, gs, gi, gc = ctx.search(queries, k, threshold=th, filter_bitmap=fb)
+    ek, es, ei, ec = S.oracle_flat_search(metric, dt, stored, sdim, queries, k, threshold=threshold, keys=keys,
+                                          drop=odrop)
+    exact = dt == S.DT_INT8
+    for i in range(q):
+        alld = S.oracle_distances(metric, dt, stored, sdim, queries[i])
+        S.check_topk_parity(gi[i], gs[i], ei[i], es[i], all_dist=alld, exact=exact,
+                            what="%s n=%d d=%d q%d k=%d [%s]" % (kind, n, d, i, k, ctx.last_kernel()))
+        assert gc[i] == ec[i]
+        nv = int(gc[i])
+        exp_keys = gi[i][:nv].astype(np.uint64) if keys is None else np.asarray(keys, np.uint64)[gi[i][:nv]]
+        assert np.array_equal(gk[i][:nv], exp_keys)
+        assert (gk[i][nv:] == np.uint64(0xFFFFFFFFFFFFFFFF)).all() and np.isnan(gs[i][nv:]).all()
+    name = ctx.last_kernel()
+    ctx.close(); st.close()
+    return name
+
+
+@pytest.mark.parametrize("kind", KINDS)
+def test_batch1_parity_all_metrics(kind):
+    assert run_case(kind, 5000, 96, 1, 10, seed=11) == "scan_gemv"
+
+
+@pytest.mark.parametrize("kind", KINDS)
+def test_small_batch_parity(kind):
+    run_case(kind, 3000, 64, 7, 10, seed=12)
+
+
+@pytest.mark.parametrize("d", [1, 3, 4, 7, 17, 33, 100, 128, 257, 768, 1536])
+@pytest.mark.parametrize("kind", ["fp32_l2", "fp16_ip", "qi8_l2"])
+def test_ragged_dimensions(kind, d):
+    run_case(kind, 1500, d, 2, 5, seed=13 + d)
+
+
+@pytest.mark.parametrize("k", [1, 2, 31, 32, 33, 100, 257, 1024])
+def test_topk_sizes(k):
+    run_case("fp32_l2", 4000, 32, 2, k, seed=14)
+    run_case("i8_l2", 4000, 32, 1, k, seed=15)   # heavy ties
+
+
+def test_k_larger_than_n_and_tiny_stores():
+    run_case("fp32_l2", 2, 8, 1, 10, seed=16)
+    run_case("fp32_ip", 37, 8, 3, 100, seed=17)
+    run_case("qi8_l2", 33, 8, 1, 64, seed=18)
+
+
+def test_deleted_rows_keys_and_holes():
+    n = 3000
+    rng = np.random.default_rng(3)
+    drop = rng.random(n) < 0.3
+    keys = (np.arange(n, dtype=np.uint64) * 7 + 5)
+    holes = rng.random(n) < 0.1
+    keys[holes] = np.uint64(0xFFFFFFFFFFFFFFFF)      # kInvalidKey holes are skipped by the scan
+    run_case("fp32_l2", n, 24, 3, 10, seed=19, drop=drop, keys=keys)
+
+
+def test_filter_bitmap_and_threshold():
+    n = 4000
+    rng = np.random.default_rng(4)
+    filt = rng.random(n) < 0.5
+    run_case("fp16_ip", n, 40, 2, 20, seed=20, filt=filt)
+    run_case("fp32_l2", n, 16, 2, 50, seed=21, threshold=12.0)     # RNN radius: fewer than k results
+    run_case("fp32_l2", n, 16, 1, 10, seed=22, filt=np.ones(n, bool))  # everything filtered
+
+
+def test_exact_duplicates_tie_break_by_row():
+    # 64 identical rows: every score ties; we must return rows 0..k-1 in order
+    st = z.Store(S.DT_FP32, S.M_L2SQ, 8)
+    st.append(np.ones((64, 8), np.float32)); st.seal()
+    ctx = z.Context(st)
+    _, sc, ix, cnt = ctx.search(np.zeros((1, 8), np.float32), 10)
+    assert list(ix[0]) == list(range(10)) and (sc[0] == 8.0).all() and cnt[0] == 10
+
+
+@pytest.mark.skipif(S.ref() is None, reason="oracle/_ref not available on this host")
+@pytest.mark.parametrize("conv,metric,origin", [
+    ("", "SquaredEuclidean", None), ("HalfFloatConverter", "InnerProduct", None),
+    ("CosineNormalizeConverter", "Cosine", None), ("Int8StreamingConverter", "SquaredEuclidean", "SquaredEuclidean"),
+    ("Int8StreamingConverter", "InnerProduct", "InnerProduct"),
+])
+def test_against_reference_itself(conv, metric, origin):
+    """Same inputs through the reference's FlatSearcher (oracle/_ref) and through the GPU path,
+    fed with the reference's own stored bytes and reformer-transformed queries."""
+    rng = np.random.default_rng(77)
+    n, d, q, k = 20000, 96, 8, 10
+    x = rng.uniform(-1, 1, (n, d)).astype(np.float32)
+    qs = rng.uniform(-1, 1, (q, d)).astype(np.float32)
+    ri = S.RefIndex(x, S.DT_FP32, d, metric, conv)
+    stored, tq = ri.stored(), ri.transform_queries(qs)
+    mid = z.metric_from_names(ri.metric_name, origin)
+    st = z.Store(ri.dtype, mid, ri.dim)
+    st.append(stored); st.seal()
+    ctx = z.Context(st)
+    _, gs, gi, _ = ctx.search(tq, k)
+    _, rs, rix, _ = ri.search(qs, k)
+    for i in range(q):
+        alld = S.oracle_distances(mid, ri.dtype, stored, ri.dim, tq[i])
+        S.check_topk_parity(gi[i], gs[i], rix[i], rs[i], all_dist=alld, exact=ri.dtype == S.DT_INT8,
+                            what="vs reference %s/%s q%d" % (conv, metric, i))
+    ri.close()
+
+
+def test_distance_matrix_contract():
+    for kind in ("fp32_l2", "fp16_ip", "qi8_l2", "i8_l2", "fp32_cos"):
+        metric, dt, sdim, stored, conv = make_stored(kind, 257, 50, 5)
+        queries = np.ascontiguousarray(conv(np.random.default_rng(6).standard_normal((3, 50)).astype(np.float32)))
+        got = z.distance_matrix(metric, dt, sdim, stored, queries)
+        for j in range(3):
+            exp = S.oracle_distances(metric, dt, stored, sdim, queries[j])
+            if dt == S.DT_INT8:
+                assert np.array_equal(got[j].view(np.uint32), exp.view(np.uint32)), kind
+            else:
+                assert np.allclose(got[j], exp, rtol=1e-5, atol=1e-6), kind
+
+
+def test_get_vector_round_trip():
+    metric, dt, sdim, stored, _ = make_stored("qi8_l2", 100, 24, 9)
+    st = z.Store(dt, metric, sdim); st.append(stored); st.seal()
+    for r in (0, 57, 99):
+        assert np.array_equal(st.get_vector(r), stored[r])

@@ -1,0 +1,229 @@
+"""ctypes binding over include/zvec_b200.h (no torch types cross this boundary)."""
+import ctypes as C
+import os
+
+import numpy as np
+
+DT_FP16, DT_FP32, DT_INT8 = 1, 2, 4
+(METRIC_L2SQ, METRIC_L2, METRIC_IP, METRIC_COSINE,
+ METRIC_QI8_L2SQ, METRIC_QI8_IP, METRIC_QI8_COSINE) = range(7)
+INVALID_INDEX = 0xFFFFFFFF
+INVALID_KEY = 0xFFFFFFFFFFFFFFFF
+FLT_MAX = float(np.finfo(np.float32).max)
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+
+
+def lib_path():
+    return os.path.join(_HERE, "lib", "libzvec_b200.so")
+
+
+class ZvecB200Error(RuntimeError):
+    def __init__(self, code, msg):
+        super().__init__("zvec_b200 error %d: %s" % (code, msg))
+        self.code = code
+
+
+_lib = None
+
+_SIGS = {
+    "zvb200_version": (C.c_char_p, []),
+    "zvb200_last_error": (C.c_char_p, []),
+    "zvb200_device_count": (C.c_int, []),
+    "zvb200_kernel_launches": (C.c_uint64, []),
+    "zvb200_store_create": (C.c_int, [C.c_int, C.c_int, C.c_int, C.c_uint32, C.POINTER(C.c_void_p)]),
+    "zvb200_store_destroy": (C.c_int, [C.c_void_p]),
+    "zvb200_store_reserve": (C.c_int, [C.c_void_p, C.c_uint64]),
+    "zvb200_store_append": (C.c_int, [C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p]),
+    "zvb200_store_append_device": (C.c_int, [C.c_void_p, C.c_void_p, C.c_uint64]),
+    "zvb200_store_seal": (C.c_int, [C.c_void_p]),
+    "zvb200_store_count": (C.c_uint64, [C.c_void_p]),
+    "zvb200_store_set_deleted": (C.c_int, [C.c_void_p, C.c_uint64, C.c_int]),
+    "zvb200_store_get_vector": (C.c_int, [C.c_void_p, C.c_uint64, C.c_void_p, C.c_size_t]),
+    "zvb200_store_scan_bytes": (C.c_uint64, [C.c_void_p]),
+    "zvb200_ctx_create": (C.c_int, [C.c_void_p, C.POINTER(C.c_void_p)]),
+    "zvb200_ctx_destroy": (C.c_int, [C.c_void_p]),
+    "zvb200_search": (C.c_int, [C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_float, C.c_void_p,
+                                C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "zvb200_search_device": (C.c_int, [C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_float,
+                                       C.c_void_p, C.c_void_p, C.c_void_p]),
+    "zvb200_ctx_sync": (C.c_int, [C.c_void_p]),
+    "zvb200_ctx_stream": (C.c_void_p, [C.c_void_p]),
+    "zvb200_ctx_set_kernel": (C.c_int, [C.c_void_p, C.c_int]),
+    "zvb200_ctx_last_kernel": (C.c_char_p, [C.c_void_p]),
+    "zvb200_distance_matrix": (C.c_int, [C.c_int, C.c_int, C.c_int, C.c_uint32, C.c_void_p, C.c_uint64,
+                                         C.c_void_p, C.c_uint32, C.c_void_p]),
+    "zvb200_merge_topk_device": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p,
+                                           C.c_uint32, C.c_uint32, C.c_void_p, C.c_void_p]),
+    "zvb200_ivf_attach": (C.c_int, [C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p]),
+    "zvb200_ivf_search": (C.c_int, [C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint64,
+                                    C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
+}
+
+
+def exported_symbols():
+    return sorted(_SIGS)
+
+
+def lib():
+    """Load libzvec_b200.so; fail loudly when it has not been built."""
+    global _lib
+    if _lib is None:
+        p = lib_path()
+        if not os.path.exists(p):
+            raise ZvecB200Error(-1, "CUDA library %s is missing: run __graft_entry__.build() "
+                                    "(make -C zvec_b200/csrc); there is no CPU fallback" % p)
+        L = C.CDLL(p)
+        for name, (res, args) in _SIGS.items():
+            f = getattr(L, name)
+            f.restype = res
+            f.argtypes = args
+        _lib = L
+    return _lib
+
+
+def _check(rc):
+    if rc != 0:
+        raise ZvecB200Error(rc, lib().zvb200_last_error().decode())
+
+
+def _ptr(a):
+    if a is None:
+        return None
+    if isinstance(a, int):
+        return C.c_void_p(a)
+    return a.ctypes.data_as(C.c_void_p)
+
+
+def metric_from_names(metric, origin=None):
+    """Reference metric name (+ origin metric of QuantizedInteger) -> ZVB200_METRIC_*."""
+    plain = {"SquaredEuclidean": METRIC_L2SQ, "Euclidean": METRIC_L2, "InnerProduct": METRIC_IP,
+             "Cosine": METRIC_COSINE}
+    if metric == "QuantizedInteger":
+        return {"SquaredEuclidean": METRIC_QI8_L2SQ, "InnerProduct": METRIC_QI8_IP,
+                "Cosine": METRIC_QI8_COSINE}[origin]
+    return plain[metric]
+
+
+class Store:
+    """Device-resident vector store on one GPU (zvb200_store_*)."""
+
+    def __init__(self, dtype, metric, dim, device=0):
+        h = C.c_void_p()
+        _check(lib().zvb200_store_create(device, dtype, metric, dim, C.byref(h)))
+        self.h, self.dtype, self.metric, self.dim, self.device = h, dtype, metric, dim, device
+        esz = {DT_FP32: 4, DT_FP16: 2, DT_INT8: 1}[dtype]
+        self.elem_bytes = dim * esz
+
+    def reserve(self, rows):
+        _check(lib().zvb200_store_reserve(self.h, rows))
+
+    def append(self, rows, keys=None):
+        rows = np.ascontiguousarray(rows)
+        n = rows.nbytes // self.elem_bytes
+        assert n * self.elem_bytes == rows.nbytes, "rows are not whole elements"
+        if keys is not None:
+            keys = np.ascontiguousarray(keys, dtype=np.uint64)
+            assert keys.size == n
+        _check(lib().zvb200_store_append(self.h, _ptr(rows), n, _ptr(keys)))
+
+    def append_device(self, dev_ptr, n):
+        _check(lib().zvb200_store_append_device(self.h, C.c_void_p(dev_ptr), n))
+
+    def seal(self):
+        _check(lib().zvb200_store_seal(self.h))
+
+    def count(self):
+        return lib().zvb200_store_count(self.h)
+
+    def scan_bytes(self):
+        return lib().zvb200_store_scan_bytes(self.h)
+
+    def set_deleted(self, row, deleted=True):
+        _check(lib().zvb200_store_set_deleted(self.h, row, int(deleted)))
+
+    def get_vector(self, row):
+        out = np.zeros(self.elem_bytes, np.uint8)
+        _check(lib().zvb200_store_get_vector(self.h, row, _ptr(out), out.nbytes))
+        return out
+
+    def close(self):
+        if self.h:
+            lib().zvb200_store_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+class Context:
+    """Per-thread search context (zvb200_ctx_*)."""
+
+    def __init__(self, store):
+        h = C.c_void_p()
+        _check(lib().zvb200_ctx_create(store.h, C.byref(h)))
+        self.h, self.store = h, store
+
+    def set_kernel(self, which):
+        _check(lib().zvb200_ctx_set_kernel(self.h, which))
+
+    def last_kernel(self):
+        return lib().zvb200_ctx_last_kernel(self.h).decode()
+
+    def stream(self):
+        return lib().zvb200_ctx_stream(self.h)
+
+    def sync(self):
+        _check(lib().zvb200_ctx_sync(self.h))
+
+    def search(self, queries, k, threshold=FLT_MAX, filter_bitmap=None):
+        """Host queries (stored layout) -> (keys u64, scores f32, index u32, counts u32)."""
+        queries = np.ascontiguousarray(queries)
+        q = queries.nbytes // self.store.elem_bytes
+        assert q * self.store.elem_bytes == queries.nbytes
+        keys = np.empty((q, k), np.uint64)
+        scores = np.empty((q, k), np.float32)
+        index = np.empty((q, k), np.uint32)
+        counts = np.empty(q, np.uint32)
+        if filter_bitmap is not None:
+            filter_bitmap = np.ascontiguousarray(filter_bitmap, dtype=np.uint32)
+        _check(lib().zvb200_search(self.h, _ptr(queries), q, k, threshold, _ptr(filter_bitmap),
+                                   _ptr(keys), _ptr(scores), _ptr(index), _ptr(counts)))
+        return keys, scores, index, counts
+
+    def search_device(self, q_ptr, q, k, out_scores_ptr, out_index_ptr, threshold=FLT_MAX, filter_ptr=None):
+        _check(lib().zvb200_search_device(self.h, C.c_void_p(q_ptr), q, k, threshold,
+                                          C.c_void_p(filter_ptr) if filter_ptr else None,
+                                          C.c_void_p(out_scores_ptr), C.c_void_p(out_index_ptr)))
+
+    def merge_topk_device(self, scores_ptr, index_ptr, g, shard_base, q, k, out_scores_ptr, out_rows_ptr):
+        sb = np.ascontiguousarray(shard_base, dtype=np.uint64)
+        _check(lib().zvb200_merge_topk_device(self.h, C.c_void_p(scores_ptr), C.c_void_p(index_ptr), g,
+                                              _ptr(sb), q, k, C.c_void_p(out_scores_ptr),
+                                              C.c_void_p(out_rows_ptr)))
+
+    def close(self):
+        if self.h:
+            lib().zvb200_ctx_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+def distance_matrix(metric, dtype, dim, rows, queries, device=0):
+    """out[j, i] = dist(rows[i], queries[j]) — the ailego <T,1,1>::Compute contract."""
+    rows = np.ascontiguousarray(rows)
+    queries = np.ascontiguousarray(queries)
+    esz = {DT_FP32: 4, DT_FP16: 2, DT_INT8: 1}[dtype]
+    n = rows.nbytes // (dim * esz)
+    nq = queries.nbytes // (dim * esz)
+    out = np.empty((nq, n), np.float32)
+    _check(lib().zvb200_distance_matrix(device, metric, dtype, dim, _ptr(rows), n, _ptr(queries), nq, _ptr(out)))
+    return out

@@ -1,0 +1,562 @@
+// C ABI of libzvec_b200.so (include/zvec_b200.h): device-resident vector store, search
+// contexts and the search / merge / distance entry points.  No CPU fallback: every
+// compute path launches the CUDA kernels in this directory or fails.
+#include <float.h>
+
+#include <algorithm>
+#include <atomic>
+#include <cstdio>
+#include <cstring>
+
+#include "internal.h"
+
+using namespace zvb;
+
+namespace zvb {
+static std::atomic<uint64_t> g_launches{0};
+void count_launch(int n) { g_launches.fetch_add((uint64_t)n, std::memory_order_relaxed); }
+}  // namespace zvb
+
+static thread_local std::string g_err;
+
+static int set_err(int code, const char *what, const char *detail = "") {
+  g_err = std::string(what) + (detail && *detail ? ": " : "") + (detail ? detail : "");
+  return code;
+}
+static int cuda_fail(cudaError_t e, const char *what) {
+  cudaGetLastError();  // clear sticky-less error state
+  return set_err(e == cudaErrorMemoryAllocation ? ZVB200_ERR_NOMEMORY : ZVB200_ERR_RUNTIME, what,
+                 cudaGetErrorString(e));
+}
+#define CU(x)                                        \
+  do {                                               \
+    cudaError_t _e = (x);                            \
+    if (_e != cudaSuccess) return cuda_fail(_e, #x); \
+  } while (0)
+
+struct zvb200_store {
+  int device = 0, dtype = 0, metric = 0, sm_count = 148;
+  uint32_t dim = 0, elem_bytes = 0, d = 0, vec_bytes = 0, row_stride = 0, chunks = 0, tail_off = 0;
+  bool has_tail = false, sealed = false;
+  uint8_t *rows = nullptr;
+  float4 *tails = nullptr;
+  float *norms = nullptr;
+  uint32_t *drop = nullptr;       // device bitmap (allocated lazily)
+  uint64_t drop_words = 0;
+  uint64_t n = 0, cap = 0, normed = 0;
+  std::vector<uint64_t> keys;     // empty = identity
+  std::vector<uint32_t> drop_host;
+  bool has_drop = false, drop_dirty = false;
+  cudaStream_t stream = nullptr;
+  uint8_t *staging = nullptr;     // device staging for host appends
+  size_t staging_bytes = 0;
+  // IVF
+  zvb200_store *centroids = nullptr;
+  std::vector<uint64_t> list_offsets;
+  std::mutex mu;
+
+  RowsView view() const {
+    RowsView v;
+    v.rows = rows; v.n = n; v.row_stride = row_stride; v.chunks = chunks; v.d = d;
+    v.dtype = dtype; v.metric = metric; v.tails = tails; v.norms = norms;
+    v.drop = has_drop ? drop : nullptr;
+    return v;
+  }
+};
+
+struct DevBuf {
+  void *p = nullptr;
+  size_t cap = 0;
+  cudaError_t ensure(size_t bytes) {
+    if (bytes <= cap) return cudaSuccess;
+    if (p) cudaFree(p);
+    p = nullptr; cap = 0;
+    size_t want = std::max(bytes, (size_t)4096);
+    cudaError_t e = cudaMalloc(&p, want);
+    if (e == cudaSuccess) cap = want;
+    return e;
+  }
+  void release() { if (p) cudaFree(p); p = nullptr; cap = 0; }
+};
+struct HostBuf {
+  void *p = nullptr;
+  size_t cap = 0;
+  cudaError_t ensure(size_t bytes) {
+    if (bytes <= cap) return cudaSuccess;
+    if (p) cudaFreeHost(p);
+    p = nullptr; cap = 0;
+    size_t want = std::max(bytes, (size_t)4096);
+    cudaError_t e = cudaMallocHost(&p, want);
+    if (e == cudaSuccess) cap = want;
+    return e;
+  }
+  void release() { if (p) cudaFreeHost(p); p = nullptr; cap = 0; }
+};
+
+struct zvb200_ctx {
+  zvb200_store *s = nullptr;
+  cudaStream_t stream = nullptr;
+  DevBuf qin, qf32, qraw, qtails, qnorms, part, out_scores, out_index, filter, misc;
+  HostBuf h_q, h_scores, h_index;
+  int force_kernel = 0;
+  const char *last_kernel = "none";
+};
+
+static int layout_for(int dtype, int metric, uint32_t dim, zvb200_store *s) {
+  s->has_tail = false;
+  uint32_t esz;
+  switch (dtype) {
+    case ZVB200_DT_FP32: esz = 4; break;
+    case ZVB200_DT_FP16: esz = 2; break;
+    case ZVB200_DT_INT8: esz = 1; break;
+    default: return set_err(ZVB200_ERR_UNSUPPORTED, "unsupported data type");
+  }
+  if (metric < ZVB200_METRIC_L2SQ || metric > ZVB200_METRIC_QI8_COSINE)
+    return set_err(ZVB200_ERR_UNSUPPORTED, "unsupported metric");
+  uint32_t strip = 0;
+  if (metric_is_qi8(metric)) {
+    // QuantizedIntegerMetric::init accepts DT_INT8 / DT_INT4 only (quantized_integer_metric.cc:33-38)
+    if (dtype != ZVB200_DT_INT8) return set_err(ZVB200_ERR_UNSUPPORTED, "QuantizedInteger needs int8");
+    strip = metric == ZVB200_METRIC_QI8_COSINE ? 20 : 16;
+    s->has_tail = true;
+  } else if (metric == ZVB200_METRIC_COSINE) {
+    // CosineMetric: fp32 / fp16 only (cosine_metric.cc:150-160); trailing fp32 norm slot
+    if (dtype == ZVB200_DT_INT8) return set_err(ZVB200_ERR_UNSUPPORTED, "Cosine needs fp32/fp16");
+    strip = 4 / esz;
+  }
+  if (dim <= strip) return set_err(ZVB200_ERR_INVALID_ARGUMENT, "dimension too small");
+  s->dtype = dtype; s->metric = metric; s->dim = dim;
+  s->elem_bytes = dim * esz;
+  s->d = dim - strip;
+  s->vec_bytes = s->d * esz;
+  s->row_stride = (s->vec_bytes + 15u) & ~15u;
+  s->chunks = s->row_stride / 16;
+  s->tail_off = s->vec_bytes;
+  return 0;
+}
+
+static int store_grow(zvb200_store *s, uint64_t want) {
+  if (want <= s->cap) return 0;
+  uint64_t ncap = std::max<uint64_t>(want, s->cap + s->cap / 2);
+  ncap = std::max<uint64_t>(ncap, 1024);
+  uint8_t *nr = nullptr;
+  CU(cudaMalloc((void **)&nr, ncap * s->row_stride));
+  if (s->n) CU(cudaMemcpyAsync(nr, s->rows, s->n * s->row_stride, cudaMemcpyDeviceToDevice, s->stream));
+  float4 *nt = nullptr;
+  if (s->has_tail) {
+    CU(cudaMalloc((void **)&nt, ncap * sizeof(float4)));
+    if (s->n) CU(cudaMemcpyAsync(nt, s->tails, s->n * sizeof(float4), cudaMemcpyDeviceToDevice, s->stream));
+  }
+  CU(cudaStreamSynchronize(s->stream));
+  if (s->rows) cudaFree(s->rows);
+  if (s->tails) cudaFree(s->tails);
+  if (s->norms) { cudaFree(s->norms); s->norms = nullptr; s->normed = 0; }
+  s->rows = nr; s->tails = nt; s->cap = ncap;
+  return 0;
+}
+
+extern "C" {
+
+const char *zvb200_version(void) { return "zvec_b200 0.1 (sm_100a)"; }
+const char *zvb200_last_error(void) { return g_err.c_str(); }
+uint64_t zvb200_kernel_launches(void) { return g_launches.load(); }
+
+int zvb200_device_count(void) {
+  int n = 0;
+  if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }
+  return n;
+}
+
+int zvb200_store_create(int device, int dtype, int metric, uint32_t dim, zvb200_store **out) {
+  if (!out) return set_err(ZVB200_ERR_INVALID_ARGUMENT, "null out");
+  *out = nullptr;
+  auto s = new zvb200_store();
+  int r = layout_for(dtype, metric, dim, s);
+  if (r != 0) { delete s; return r; }
+  int ndev = zvb200_device_count();
+  if (ndev == 0) { delete s; return set_err(ZVB200_ERR_RUNTIME, "no CUDA device (there is no CPU fallback)"); }
+  if (device < 0 || device >= ndev) { delete s; return set_err(ZVB200_ERR_INVALID_ARGUMENT, "bad device"); }
+  s->device = device;
+  cudaError_t e = cudaSetDevice(device);
+  if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking);
+  if (e == cudaSuccess) e = cudaDeviceGetAttribute(&s->sm_count, cudaDevAttrMultiProcessorCount, device);
+  if (e != cudaSuccess) { delete s; return cuda_fail(e, "store_create"); }
+  *out = s;
+  return 0;
+}
+
+int zvb200_store_destroy(zvb200_store *s) {
+  if (!s) return 0;
+  cudaSetDevice(s->device);
+  if (s->centroids) zvb200_store_destroy(s->centroids);
+  if (s->rows) cudaFree(s->rows);
+  if (s->tails) cudaFree(s->tails);
+  if (s->norms) cudaFree(s->norms);
+  if (s->drop) cudaFree(s->drop);
+  if (s->staging) cudaFree(s->staging);
+  if (s->stream) cudaStreamDestroy(s->stream);
+  delete s;
+  return 0;
+}
+
+int zvb200_store_reserve(zvb200_store *s, uint64_t rows) {
+  if (!s) return set_err(ZVB200_ERR_INVALID_ARGUMENT, "null store");
+  std::lock_guard<std::mutex> g(s->mu);
+  CU(cudaSetDevice(s->device));
+  if (rows <= s->cap) return 0;
+  uint64_t keep = s->cap;
+  s->cap = 0;  // force exact size
+  int r = store_grow(s, rows);
+  if (r != 0) s->cap = keep;
+  return r;
+}
+
+static int append_common(zvb200_store *s, const uint8_t *src_dev, uint64_t n) {
+  CU(launch_repack_rows(src_dev, s->elem_bytes, n, s->rows + s->n * s->row_stride, s->row_stride,
+                        s->vec_bytes, s->has_tail ? s->tails + s->n : nullptr, s->tail_off, s->stream));
+  return 0;
+}
+
+int zvb200_store_append(zvb200_store *s, const void *rows, uint64_t n, const uint64_t *keys) {
+  if (!s || (!rows && n)) return set_err(ZVB200_ERR_INVALID_ARGUMENT, "null argument");
+  std::lock_guard<std::mutex> g(s->mu);
+  if (s->n + n >= 0xffffffffull) return set_err(ZVB200_ERR_INVALID_ARGUMENT, "store holds < 2^32-1 rows");
+  CU(cudaSetDevice(s->device));
+  int r = store_grow(s, s->n + n);
+  if (r != 0) return r;
+  const size_t chunk_rows = std::max<size_t>(1, ((size_t)64 << 20) / s->elem_bytes);
+  if (!s->staging) {
+    s->staging_bytes = chunk_rows * s->elem_bytes;
+    CU(cudaMalloc((void **)&s->staging, s->staging_bytes));
+  }
+  const uint64_t n0 = s->n;
+  for (uint64_t off = 0; off < n; off += chunk_rows) {
+    const uint64_t m = std::min<uint64_t>(chunk_rows, n - off);
+    CU(cudaMemcpyAsync(s->staging, (const uint8_t *)rows + off * s->elem_bytes, m * s->elem_bytes,
+                       cudaMemcpyHostToDevice, s->stream));
+    r = append_common(s, s->staging, m);
+    if (r != 0) return r;
+    CU(cudaStreamSynchronize(s->stream));
+    s->n += m;
+  }
+  // keys / holes
+  if (keys || !s->keys.empty()) {
+    if (s->keys.empty()) { s->keys.resize(n0); for (uint64_t i = 0; i < n0; ++i) s->keys[i] = i; }
+    s->keys.resize(n0 + n);
+    for (uint64_t i = 0; i < n; ++i) {
+      const uint64_t kv = keys ? keys[i] : n0 + i;
+      s->keys[n0 + i] = kv;
+      if (kv == ZVB200_INVALID_KEY) {
+        s->drop_host.resize((s->n + 31) / 32, 0u);
+        s->drop_host[(n0 + i) >> 5] |= 1u << ((n0 + i) & 31);
+        s->has_drop = true; s->drop_dirty = true;
+      }
+    }
+  }
+  s->sealed = false;
+  return 0;
+}
+
+int zvb200_store_append_device(zvb200_store *s, const void *rows_dev, uint64_t n) {
+  if (!s || (!rows_dev && n)) return set_err(ZVB200_ERR_INVALID_ARGUMENT, "null argument");
+  std::lock_guard<std::mutex> g(s->mu);
+  if (s->n + n >= 0xffffffffull) return set_err(ZVB200_ERR_INVALID_ARGUMENT, "store holds < 2^32-1 rows");
+  CU(cudaSetDevice(s->device));
+  int r = store_grow(s, s->n + n);
+  if (r != 0) return r;
+  r = append_common(s, (const uint8_t *)rows_dev, n);
+  if (r != 0) return r;
+  CU(cudaStreamSynchronize(s->stream));
+  if (!s->keys.empty()) { uint64_t n0 = s->n; s->keys.resize(n0 + n); for (uint64_t i = 0; i < n; ++i) s->keys[n0 + i] = n0 + i; }
+  s->n += n;
+  s->sealed = false;
+  return 0;
+}
+
+static int sync_drop(zvb200_store *s) {
+  if (!s->has_drop || !s->drop_dirty) return 0;
+  const uint64_t words = (s->n + 31) / 32;
+  s->drop_host.resize(words, 0u);
+  if (words > s->drop_words) {
+    if (s->drop) cudaFree(s->drop);
+    s->drop = nullptr;
+    CU(cudaMalloc((void **)&s->drop, std::max<uint64_t>(words, 64) * 4));
+    s->drop_words = std::max<uint64_t>(words, 64);
+  }
+  CU(cudaMemcpyAsync(s->drop, s->drop_host.data(), words * 4, cudaMemcpyHostToDevice, s->stream));
+  CU(cudaStreamSynchronize(s->stream));
+  s->drop_dirty = false;
+  return 0;
+}
+
+int zvb200_store_seal(zvb200_store *s) {
+  if (!s) return set_err(ZVB200_ERR_INVALID_ARGUMENT, "null store");
+  std::lock_guard<std::mutex> g(s->mu);
+  CU(cudaSetDevice(s->device));
+  int r = sync_drop(s);
+  if (r != 0) return r;
+  if (s->dtype != ZVB200_DT_INT8 && s->n > 0) {
+    if (!s->norms) { CU(cudaMalloc((void **)&s->norms, s->cap * sizeof(float))); s->normed = 0; }
+    if (s->normed < s->n) {
+      RowsView v = s->view();
+      CU(launch_row_norms(v, s->normed, s->n, s->norms, s->stream));
+      CU(cudaStreamSynchronize(s->stream));
+      s->normed = s->n;
+    }
+  }
+  s->sealed = true;
+  return 0;
+}
+
+uint64_t zvb200_store_count(const zvb200_store *s) { return s ? s->n : 0; }
+
+uint64_t zvb200_store_scan_bytes(const zvb200_store *s) {
+  if (!s) return 0;
+  return s->n * ((uint64_t)s->vec_bytes + (s->has_tail ? 16 : 0));
+}
+
+int zvb200_store_set_deleted(zvb200_store *s, uint64_t row, int deleted) {
+  if (!s || row >= s->n) return set_err(ZVB200_ERR_INVALID_ARGUMENT, "bad row");
+  std::lock_guard<std::mutex> g(s->mu);
+  s->drop_host.resize((s->n + 31) / 32, 0u);
+  if (deleted) s->drop_host[row >> 5] |= 1u << (row & 31);
+  else s->drop_host[row >> 5] &= ~(1u << (row & 31));
+  s->has_drop = true; s->drop_dirty = true;
+  CU(cudaSetDevice(s->device));
+  return sync_drop(s);
+}
+
+int zvb200_store_get_vector(const zvb200_store *s, uint64_t row, void *out, size_t cap) {
+  if (!s || !out || row >= s->n) return set_err(ZVB200_ERR_INVALID_ARGUMENT, "bad argument");
+  if (cap < s->elem_bytes) return set_err(ZVB200_ERR_INVALID_ARGUMENT, "buffer too small");
+  CU(cudaSetDevice(s->device));
+  memset(out, 0, s->elem_bytes);
+  CU(cudaMemcpy(out, s->rows + row * s->row_stride, s->vec_bytes, cudaMemcpyDeviceToHost));
+  if (s->has_tail)
+    CU(cudaMemcpy((uint8_t *)out + s->tail_off, s->tails + row, 16, cudaMemcpyDeviceToHost));
+  return 0;
+}
+
+int zvb200_ctx_create(zvb200_store *s, zvb200_ctx **out) {
+  if (!s || !out) return set_err(ZVB200_ERR_INVALID_ARGUMENT, "null argument");
+  CU(cudaSetDevice(s->device));
+  auto c = new zvb200_ctx();
+  c->s = s;
+  cudaError_t e = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking);
+  if (e != cudaSuccess) { delete c; return cuda_fail(e, "ctx_create"); }
+  *out = c;
+  return 0;
+}
+
+int zvb200_ctx_destroy(zvb200_ctx *c) {
+  if (!c) return 0;
+  cudaSetDevice(c->s->device);
+  cudaStreamSynchronize(c->stream);
+  DevBuf *d[] = {&c->qin, &c->qf32, &c->qraw, &c->qtails, &c->qnorms, &c->part, &c->out_scores,
+                 &c->out_index, &c->filter, &c->misc};
+  for (auto b : d) b->release();
+  c->h_q.release(); c->h_scores.release(); c->h_index.release();
+  cudaStreamDestroy(c->stream);
+  delete c;
+  return 0;
+}
+
+int zvb200_ctx_sync(zvb200_ctx *c) {
+  if (!c) return set_err(ZVB200_ERR_INVALID_ARGUMENT, "null ctx");
+  CU(cudaStreamSynchronize(c->stream));
+  return 0;
+}
+void *zvb200_ctx_stream(zvb200_ctx *c) { return c ? (void *)c->stream : nullptr; }
+int zvb200_ctx_set_kernel(zvb200_ctx *c, int which) {
+  if (!c || which < 0 || which > 3) return set_err(ZVB200_ERR_INVALID_ARGUMENT, "bad kernel id");
+  c->force_kernel = which;
+  return 0;
+}
+const char *zvb200_ctx_last_kernel(const zvb200_ctx *c) { return c ? c->last_kernel : "none"; }
+
+}  // extern "C"
+
+// ======================================================================================
+// search
+// ======================================================================================
+
+// Prepare queries and run scan + final merge for queries already on the device.
+static int search_core(zvb200_ctx *c, const void *queries_dev, uint32_t q, uint32_t k,
+                       float threshold, const uint32_t *filter_dev, float *out_scores_dev,
+                       uint32_t *out_index_dev, uint64_t row_begin, uint64_t row_end) {
+  zvb200_store *s = c->s;
+  RowsView rv = s->view();
+  const uint32_t esz = s->dtype == ZVB200_DT_FP32 ? 4 : s->dtype == ZVB200_DT_FP16 ? 2 : 1;
+  const size_t qf32_bytes = s->dtype == ZVB200_DT_INT8 ? 0 : (size_t)q * (s->chunks * 16 / esz) * 4;
+  const size_t qraw_bytes = s->dtype == ZVB200_DT_FP32 ? 0 : (size_t)q * s->row_stride;
+  CU(c->qf32.ensure(qf32_bytes));
+  CU(c->qraw.ensure(qraw_bytes));
+  CU(c->qtails.ensure((size_t)q * sizeof(float4)));
+  CU(c->qnorms.ensure((size_t)q * sizeof(float)));
+  CU(launch_prep_queries(rv, queries_dev, q, s->elem_bytes, (float *)c->qf32.p, (uint8_t *)c->qraw.p,
+                         (float4 *)c->qtails.p, (float *)c->qnorms.p, c->stream));
+  QueryView qv;
+  qv.qf32 = (const float *)c->qf32.p; qv.qraw = (const uint8_t *)c->qraw.p;
+  qv.qtails = (const float4 *)c->qtails.p; qv.qnorms = (const float *)c->qnorms.p;
+  SearchParams sp;
+  sp.k = k; sp.threshold = threshold; sp.filter = filter_dev;
+
+  int which = c->force_kernel;
+  if (which == 0) which = (q <= 4 || !scan_tile_supports(k)) ? 1 : 2;
+  if (which == 3) return set_err(ZVB200_ERR_UNSUPPORTED, "tcgen05 scan not built yet");
+  if (which == 2 && !scan_tile_supports(k)) which = 1;
+  const size_t maxparts = which == 1 ? scan_gemv_max_parts(s->sm_count) : scan_tile_max_parts(s->sm_count);
+  // bound the partial-list scratch to 256 MiB: process the queries in groups
+  const size_t per_query = maxparts * (size_t)k * sizeof(u64);
+  uint32_t group = (uint32_t)std::max<size_t>(1, ((size_t)256 << 20) / per_query);
+  if (group >= 64) group &= ~63u; else if (group >= 4) group &= ~3u;
+  group = std::min(group, q);
+  CU(c->part.ensure((size_t)group * per_query));
+  for (uint32_t q0 = 0; q0 < q; q0 += group) {
+    const uint32_t qn = std::min(group, q - q0);
+    QueryView g = qv;
+    g.q = qn;
+    if (g.qf32) g.qf32 += (size_t)q0 * (s->chunks * 16 / esz);
+    if (g.qraw) g.qraw += (size_t)q0 * s->row_stride;
+    g.qtails += q0; g.qnorms += q0;
+    uint32_t nparts = 0;
+    if (which == 1) {
+      CU(launch_scan_gemv(rv, g, sp, row_begin, row_end, (u64 *)c->part.p, &nparts, s->sm_count, c->stream));
+      c->last_kernel = "scan_gemv";
+    } else {
+      CU(launch_scan_tile(rv, g, sp, row_begin, row_end, (u64 *)c->part.p, &nparts, s->sm_count, c->stream));
+      c->last_kernel = "scan_tile";
+    }
+    CU(launch_merge_parts((const u64 *)c->part.p, nparts, qn, k, out_scores_dev + (size_t)q0 * k,
+                          out_index_dev + (size_t)q0 * k, c->stream));
+  }
+  return 0;
+}
+
+static int check_search_args(zvb200_ctx *c, const void *queries, uint32_t q, uint32_t k) {
+  if (!c || (!queries && q)) return set_err(ZVB200_ERR_INVALID_ARGUMENT, "null argument");
+  if (k == 0 || k > ZVB200_MAX_TOPK) return set_err(ZVB200_ERR_INVALID_ARGUMENT, "topk must be 1..1024");
+  if (!c->s->sealed) return set_err(ZVB200_ERR_NOREADY, "store not sealed");
+  return 0;
+}
+
+extern "C" {
+
+int zvb200_search_device(zvb200_ctx *c, const void *queries_dev, uint32_t q, uint32_t k,
+                         float threshold, const uint32_t *filter_dev, float *out_scores_dev,
+                         uint32_t *out_index_dev) {
+  int r = check_search_args(c, queries_dev, q, k);
+  if (r != 0) return r;
+  if (q == 0) return 0;
+  CU(cudaSetDevice(c->s->device));
+  return search_core(c, queries_dev, q, k, threshold, filter_dev, out_scores_dev, out_index_dev, 0, c->s->n);
+}
+
+int zvb200_search(zvb200_ctx *c, const void *queries, uint32_t q, uint32_t k, float threshold,
+                  const uint32_t *filter, uint64_t *out_keys, float *out_scores,
+                  uint32_t *out_index, uint32_t *out_counts) {
+  int r = check_search_args(c, queries, q, k);
+  if (r != 0) return r;
+  if (!out_scores) return set_err(ZVB200_ERR_INVALID_ARGUMENT, "null out_scores");
+  if (q == 0) return 0;
+  zvb200_store *s = c->s;
+  CU(cudaSetDevice(s->device));
+  const size_t qbytes = (size_t)q * s->elem_bytes, nres = (size_t)q * k;
+  CU(c->h_q.ensure(qbytes));
+  CU(c->qin.ensure(qbytes));
+  CU(c->out_scores.ensure(nres * 4));
+  CU(c->out_index.ensure(nres * 4));
+  CU(c->h_scores.ensure(nres * 4));
+  CU(c->h_index.ensure(nres * 4));
+  memcpy(c->h_q.p, queries, qbytes);
+  CU(cudaMemcpyAsync(c->qin.p, c->h_q.p, qbytes, cudaMemcpyHostToDevice, c->stream));
+  const uint32_t *fdev = nullptr;
+  if (filter) {
+    const size_t fb = ((s->n + 31) / 32) * 4;
+    CU(c->filter.ensure(fb));
+    CU(cudaMemcpyAsync(c->filter.p, filter, fb, cudaMemcpyHostToDevice, c->stream));
+    fdev = (const uint32_t *)c->filter.p;
+  }
+  r = search_core(c, c->qin.p, q, k, threshold, fdev, (float *)c->out_scores.p,
+                  (uint32_t *)c->out_index.p, 0, s->n);
+  if (r != 0) return r;
+  CU(cudaMemcpyAsync(c->h_scores.p, c->out_scores.p, nres * 4, cudaMemcpyDeviceToHost, c->stream));
+  CU(cudaMemcpyAsync(c->h_index.p, c->out_index.p, nres * 4, cudaMemcpyDeviceToHost, c->stream));
+  CU(cudaStreamSynchronize(c->stream));
+  const float *hs = (const float *)c->h_scores.p;
+  const uint32_t *hi = (const uint32_t *)c->h_index.p;
+  memcpy(out_scores, hs, nres * 4);
+  if (out_index) memcpy(out_index, hi, nres * 4);
+  for (uint32_t i = 0; i < q; ++i) {
+    uint32_t cnt = 0;
+    for (uint32_t j = 0; j < k; ++j) {
+      const uint32_t ix = hi[(size_t)i * k + j];
+      if (ix != ZVB200_INVALID_INDEX) ++cnt;
+      if (out_keys)
+        out_keys[(size_t)i * k + j] = ix == ZVB200_INVALID_INDEX ? ZVB200_INVALID_KEY
+                                      : (s->keys.empty() ? (uint64_t)ix : s->keys[ix]);
+    }
+    if (out_counts) out_counts[i] = cnt;
+  }
+  return 0;
+}
+
+int zvb200_merge_topk_device(zvb200_ctx *c, const float *scores_dev, const uint32_t *index_dev,
+                             uint32_t g, const uint64_t *shard_base, uint32_t q, uint32_t k,
+                             float *out_scores_dev, uint64_t *out_rows_dev) {
+  if (!c || !scores_dev || !index_dev || !shard_base || g == 0 || k == 0)
+    return set_err(ZVB200_ERR_INVALID_ARGUMENT, "bad argument");
+  CU(cudaSetDevice(c->s->device));
+  CU(c->misc.ensure((size_t)g * 8));
+  CU(cudaMemcpyAsync(c->misc.p, shard_base, (size_t)g * 8, cudaMemcpyHostToDevice, c->stream));
+  CU(launch_merge_shards(scores_dev, index_dev, g, (const uint64_t *)c->misc.p, q, k, out_scores_dev,
+                         out_rows_dev, c->stream));
+  return 0;
+}
+
+int zvb200_distance_matrix(int device, int metric, int dtype, uint32_t dim, const void *m,
+                           uint64_t n, const void *q, uint32_t nq, float *out) {
+  if (!m || !q || !out) return set_err(ZVB200_ERR_INVALID_ARGUMENT, "null argument");
+  zvb200_store *s = nullptr;
+  int r = zvb200_store_create(device, dtype, metric, dim, &s);
+  if (r != 0) return r;
+  zvb200_ctx *c = nullptr;
+  r = zvb200_store_append(s, m, n, nullptr);
+  if (r == 0) r = zvb200_ctx_create(s, &c);
+  if (r == 0 && n && nq) {
+    auto body = [&]() -> int {
+      const uint32_t esz = dtype == ZVB200_DT_FP32 ? 4 : dtype == ZVB200_DT_FP16 ? 2 : 1;
+      CU(c->qin.ensure((size_t)nq * s->elem_bytes));
+      CU(c->qf32.ensure((size_t)nq * (s->chunks * 16 / esz) * 4));
+      CU(c->qraw.ensure((size_t)nq * s->row_stride));
+      CU(c->qtails.ensure((size_t)nq * sizeof(float4)));
+      CU(c->qnorms.ensure((size_t)nq * 4));
+      CU(c->misc.ensure((size_t)nq * n * 4));
+      CU(cudaMemcpyAsync(c->qin.p, q, (size_t)nq * s->elem_bytes, cudaMemcpyHostToDevice, c->stream));
+      RowsView rv = s->view();
+      CU(launch_prep_queries(rv, c->qin.p, nq, s->elem_bytes, (float *)c->qf32.p, (uint8_t *)c->qraw.p,
+                             (float4 *)c->qtails.p, (float *)c->qnorms.p, c->stream));
+      QueryView qv;
+      qv.qf32 = (const float *)c->qf32.p; qv.qraw = (const uint8_t *)c->qraw.p;
+      qv.qtails = (const float4 *)c->qtails.p; qv.qnorms = (const float *)c->qnorms.p; qv.q = nq;
+      CU(launch_distance_matrix(rv, qv, (float *)c->misc.p, c->stream));
+      CU(cudaMemcpyAsync(out, c->misc.p, (size_t)nq * n * 4, cudaMemcpyDeviceToHost, c->stream));
+      CU(cudaStreamSynchronize(c->stream));
+      return 0;
+    };
+    r = body();
+  }
+  if (c) zvb200_ctx_destroy(c);
+  zvb200_store_destroy(s);
+  return r;
+}
+
+int zvb200_ivf_attach(zvb200_store *, const void *, uint32_t, const uint64_t *) {
+  return set_err(ZVB200_ERR_UNSUPPORTED, "ivf not built yet");
+}
+int zvb200_ivf_search(zvb200_ctx *, const void *, uint32_t, uint32_t, uint32_t, uint64_t, uint64_t *,
+                      float *, uint32_t *, uint32_t *) {
+  return set_err(ZVB200_ERR_UNSUPPORTED, "ivf not built yet");
+}
+
+}  // extern "C"

@@ -1,0 +1,339 @@
+// Small kernels around the scan: query preparation, row repacking on ingest, the final
+// per-query merge of partial lists (K5a) and the multi-GPU shard merge (K5b).
+#include <math_constants.h>
+
+#include "internal.h"
+#include "topk.cuh"
+
+namespace zvb {
+
+namespace {
+
+// ---- queries: stored layout -> compute layout ---------------------------------------
+// fp32 / fp16: strip the cosine norm slot, widen to fp32, zero-pad to whole 16-B chunks;
+// int8: codes zero-padded to row_stride, QuantizedInteger tail split off
+// (tail = 4 floats right after the d codes, record_quantizer.h:72-80).
+__global__ void prep_queries_kernel(RowsView rv, const uint8_t *qin, uint32_t elem_bytes,
+                                    float *qf32, uint8_t *qraw, float4 *qtails, float *qnorms) {
+  const uint32_t qi = blockIdx.x;
+  const uint8_t *src = qin + (size_t)qi * elem_bytes;
+  const uint32_t d = rv.d;
+  __shared__ float red[32];
+  float nrm = 0.f;
+  if (rv.dtype == ZVB200_DT_INT8) {
+    for (uint32_t i = threadIdx.x; i < rv.row_stride; i += blockDim.x)
+      qraw[(size_t)qi * rv.row_stride + i] = i < d ? src[i] : 0;
+    if (metric_is_qi8(rv.metric) && threadIdx.x < 4) {
+      float v;
+      memcpy(&v, src + d + threadIdx.x * 4, 4);
+      reinterpret_cast<float *>(qtails + qi)[threadIdx.x] = v;
+    }
+  } else {
+    const uint32_t esz = rv.dtype == ZVB200_DT_FP32 ? 4 : 2;
+    const uint32_t padded = rv.chunks * 16 / esz;
+    for (uint32_t i = threadIdx.x; i < padded; i += blockDim.x) {
+      float v = 0.f;
+      if (i < d) {
+        if (esz == 4) memcpy(&v, src + (size_t)i * 4, 4);
+        else { __half h; memcpy(&h, src + (size_t)i * 2, 2); v = __half2float(h); }
+      }
+      qf32[(size_t)qi * padded + i] = v;
+      nrm = fmaf(v, v, nrm);
+      if (esz == 2 && qraw) {
+        uint16_t hv = 0;
+        if (i < d) memcpy(&hv, src + (size_t)i * 2, 2);
+        reinterpret_cast<uint16_t *>(qraw + (size_t)qi * rv.row_stride)[i] = hv;
+      }
+    }
+  }
+  // |q|^2
+  for (int o = 16; o > 0; o >>= 1) nrm += __shfl_xor_sync(0xffffffffu, nrm, o);
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = nrm;
+  __syncthreads();
+  if (threadIdx.x == 0 && qnorms) {
+    float s = 0.f;
+    for (int w = 0; w < (int)(blockDim.x >> 5); ++w) s += red[w];
+    qnorms[qi] = s;
+  }
+}
+
+// ---- ingest: reference element layout -> store layout --------------------------------
+__global__ void repack_rows_kernel(const uint8_t *src, uint32_t elem_bytes, uint64_t n,
+                                   uint8_t *dst, uint32_t row_stride, uint32_t vec_bytes,
+                                   float4 *tails, uint32_t tail_off) {
+  const uint32_t cpr = row_stride / 16;
+  const uint64_t total = n * cpr;
+  for (uint64_t t = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; t < total;
+       t += (uint64_t)gridDim.x * blockDim.x) {
+    const uint64_t r = t / cpr;
+    const uint32_t c = (uint32_t)(t % cpr);
+    const uint8_t *s = src + r * elem_bytes + (size_t)c * 16;
+    uint4 v = make_uint4(0, 0, 0, 0);
+    const uint32_t off = c * 16;
+    if (off + 16 <= vec_bytes && (elem_bytes & 15) == 0) {
+      v = *reinterpret_cast<const uint4 *>(s);
+    } else {
+      uint8_t *b = reinterpret_cast<uint8_t *>(&v);
+      for (int i = 0; i < 16; ++i)
+        if (off + i < vec_bytes) b[i] = s[i];
+    }
+    *reinterpret_cast<uint4 *>(dst + r * row_stride + (size_t)c * 16) = v;
+    if (tails && c == 0) {
+      float4 tv;
+      memcpy(&tv, src + r * elem_bytes + tail_off, 16);
+      tails[r] = tv;
+    }
+  }
+}
+
+// |x|^2 per stored row (fp32 / fp16), one warp per row
+__global__ void row_norms_kernel(RowsView rv, uint64_t row_begin, uint64_t row_end, float *norms) {
+  const uint64_t r = row_begin + ((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) / 32;
+  if (r >= row_end) return;
+  const int lane = threadIdx.x & 31;
+  const uint8_t *p = rv.rows + r * rv.row_stride;
+  float s = 0.f;
+  for (uint32_t c = lane; c < rv.chunks; c += 32) {
+    const uint4 v = *reinterpret_cast<const uint4 *>(p + (size_t)c * 16);
+    if (rv.dtype == ZVB200_DT_FP32) {
+      const float x0 = __uint_as_float(v.x), x1 = __uint_as_float(v.y), x2 = __uint_as_float(v.z),
+                  x3 = __uint_as_float(v.w);
+      s = fmaf(x0, x0, s); s = fmaf(x1, x1, s); s = fmaf(x2, x2, s); s = fmaf(x3, x3, s);
+    } else {
+      const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const float2 f = __half22float2(*reinterpret_cast<const __half2 *>(&w[i]));
+        s = fmaf(f.x, f.x, s); s = fmaf(f.y, f.y, s);
+      }
+    }
+  }
+  for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+  if (lane == 0) norms[r] = s;
+}
+
+// ---- K5a: part[q][nparts][k] -> final q*k ---------------------------------------------
+constexpr int kMergeWarps = 8;
+
+__global__ void __launch_bounds__(kMergeWarps * 32) merge_parts_kernel(
+    const u64 *part, uint32_t nparts, uint32_t k, float *out_scores, uint32_t *out_index) {
+  extern __shared__ __align__(16) uint8_t smem[];
+  const int lane = lane_id(), warp = threadIdx.x >> 5;
+  const uint32_t qi = blockIdx.x;
+  const size_t total = (size_t)nparts * k;
+  const u64 *src = part + (size_t)qi * total;
+  int2 *meta = reinterpret_cast<int2 *>(smem);
+  u64 *tkbase = reinterpret_cast<u64 *>(smem + sizeof(int2) * kMergeWarps);
+  const size_t tk_u64 = (size_t)2 * k + 32;
+  WarpTopk tk;
+  u64 *b = tkbase + (size_t)warp * tk_u64;
+  tk.init(b, b + k, b + 2 * k, (int)k, kMaxKey);
+  for (size_t i0 = (size_t)warp * 32; i0 < total; i0 += (size_t)kMergeWarps * 32) {
+    const size_t i = i0 + lane;
+    const u64 e = i < total ? src[i] : kMaxKey;
+    tk.push(e < tk.tau, e, kMaxKey);
+  }
+  tk.finish(kMaxKey);
+  if (lane == 0) meta[warp] = make_int2((int)(tk.list - tkbase), tk.cnt);
+  __syncthreads();
+  if (warp != 0) return;
+  for (int w = 1; w < kMergeWarps; ++w) {
+    const int2 m = meta[w];
+    const u64 *s = tkbase + m.x;
+    for (int i0 = 0; i0 < m.y; i0 += 32) {
+      const int i = i0 + lane;
+      const u64 e = i < m.y ? s[i] : kMaxKey;
+      tk.push(i < m.y && e < tk.tau, e, kMaxKey);
+    }
+  }
+  tk.finish(kMaxKey);
+  for (uint32_t i = lane; i < k; i += 32) {
+    const bool ok = (int)i < tk.cnt;
+    const u64 e = ok ? tk.list[i] : kMaxKey;
+    out_scores[(size_t)qi * k + i] = ok ? unorder_f32((uint32_t)(e >> 32)) : CUDART_NAN_F;
+    out_index[(size_t)qi * k + i] = ok ? (uint32_t)e : ZVB200_INVALID_INDEX;
+  }
+}
+
+// ---- K5b: G sorted shard lists -> one list by (score, global row) ---------------------
+// Replaces concat + std::sort + resize(topk) of CombinedVectorColumnIndexer::Search
+// (combined_vector_column_indexer.cc:167-222).  Rank-based: candidate (g,i) lands at
+// i + sum_{g'<g} #{s' <= s} + sum_{g'>g} #{s' < s}; shards are contiguous row ranges in
+// shard order, so (score, g, i) order == (score, global row) order.
+__device__ __forceinline__ uint32_t ord_or_max(float s) {
+  return (s != s) ? 0xffffffffu : order_f32(s);
+}
+
+__global__ void merge_shards_kernel(const float *scores, const uint32_t *index, uint32_t g,
+                                    const uint64_t *shard_base, uint32_t q, uint32_t k,
+                                    float *out_scores, uint64_t *out_rows) {
+  const uint32_t qi = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (qi >= q) return;
+  const int lane = threadIdx.x & 31;
+  for (uint32_t i = lane; i < k; i += 32) {
+    out_scores[(size_t)qi * k + i] = CUDART_NAN_F;
+    out_rows[(size_t)qi * k + i] = ZVB200_INVALID_KEY;
+  }
+  __syncwarp();
+  const size_t gstride = (size_t)q * k;
+  for (uint32_t c = lane; c < g * k; c += 32) {
+    const uint32_t gi = c / k, i = c % k;
+    const float s = scores[gi * gstride + (size_t)qi * k + i];
+    const uint32_t idx = index[gi * gstride + (size_t)qi * k + i];
+    if (idx == ZVB200_INVALID_INDEX || s != s) continue;
+    const uint32_t so = order_f32(s);
+    uint32_t rank = i;
+    for (uint32_t g2 = 0; g2 < g; ++g2) {
+      if (g2 == gi) continue;
+      const float *l2 = scores + g2 * gstride + (size_t)qi * k;
+      uint32_t lo = 0, hi = k;
+      while (lo < hi) {
+        const uint32_t mid = (lo + hi) >> 1;
+        const uint32_t mo = ord_or_max(l2[mid]);
+        const bool before = g2 < gi ? (mo <= so) : (mo < so);
+        if (before) lo = mid + 1; else hi = mid;
+      }
+      rank += lo;
+    }
+    if (rank < k) {
+      out_scores[(size_t)qi * k + rank] = s;
+      out_rows[(size_t)qi * k + rank] = shard_base[gi] + idx;
+    }
+  }
+}
+
+// ---- distance matrix: out[j*n + i] = dist(row i, query j) ----------------------------
+// The ailego <T,1,1>::Compute contract (IndexMetric::distance(), euclidean_metric.cc:785-851)
+// one warp per row, queries looped.
+__global__ void distance_matrix_kernel(RowsView rv, QueryView qv, float *out) {
+  const uint64_t r = ((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) / 32;
+  if (r >= rv.n) return;
+  const int lane = threadIdx.x & 31;
+  const uint8_t *p = rv.rows + r * rv.row_stride;
+  const bool l2 = metric_is_l2(rv.metric);
+  for (uint32_t j = 0; j < qv.q; ++j) {
+    float fs = 0.f;
+    int ab = 0, aa = 0, qq = 0;
+    for (uint32_t c = lane; c < rv.chunks; c += 32) {
+      const uint4 v = *reinterpret_cast<const uint4 *>(p + (size_t)c * 16);
+      const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+      if (rv.dtype == ZVB200_DT_INT8) {
+        const uint4 qv4 = *reinterpret_cast<const uint4 *>(qv.qraw + (size_t)j * rv.row_stride + (size_t)c * 16);
+        const uint32_t qw[4] = {qv4.x, qv4.y, qv4.z, qv4.w};
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          ab = __dp4a((int)w[i], (int)qw[i], ab);
+          aa = __dp4a((int)w[i], (int)w[i], aa);
+          qq = __dp4a((int)qw[i], (int)qw[i], qq);
+        }
+      } else if (rv.dtype == ZVB200_DT_FP32) {
+        const float *qp = qv.qf32 + (size_t)j * rv.chunks * 4 + (size_t)c * 4;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          const float x = __uint_as_float(w[i]);
+          if (l2) { const float d = x - qp[i]; fs = fmaf(d, d, fs); } else fs = fmaf(x, qp[i], fs);
+        }
+      } else {
+        const float *qp = qv.qf32 + (size_t)j * rv.chunks * 8 + (size_t)c * 8;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          const float2 f = __half22float2(*reinterpret_cast<const __half2 *>(&w[i]));
+          if (l2) {
+            float d = f.x - qp[2 * i]; fs = fmaf(d, d, fs);
+            d = f.y - qp[2 * i + 1]; fs = fmaf(d, d, fs);
+          } else { fs = fmaf(f.x, qp[2 * i], fs); fs = fmaf(f.y, qp[2 * i + 1], fs); }
+        }
+      }
+    }
+    for (int o = 16; o > 0; o >>= 1) {
+      fs += __shfl_xor_sync(0xffffffffu, fs, o);
+      ab += __shfl_xor_sync(0xffffffffu, ab, o);
+      aa += __shfl_xor_sync(0xffffffffu, aa, o);
+      qq += __shfl_xor_sync(0xffffffffu, qq, o);
+    }
+    if (lane == 0) {
+      float s;
+      const int m = rv.metric;
+      if (rv.dtype == ZVB200_DT_INT8) {
+        if (m == ZVB200_METRIC_QI8_L2SQ) s = qi8_l2sq((float)ab, rv.tails[r], qv.qtails[j], (float)rv.d);
+        else if (metric_is_qi8(m)) s = qi8_mip((float)ab, rv.tails[r], qv.qtails[j], (float)rv.d);
+        else if (l2) { s = (float)(aa - 2 * ab + qq); if (m == ZVB200_METRIC_L2) s = sqrtf(s); }
+        else s = -(float)ab;
+      } else {
+        s = m == ZVB200_METRIC_L2SQ ? fs : m == ZVB200_METRIC_L2 ? sqrtf(fs)
+            : m == ZVB200_METRIC_IP ? -fs : 1.0f - fs;
+      }
+      out[(size_t)j * rv.n + r] = s;
+    }
+  }
+}
+
+}  // namespace
+
+cudaError_t launch_prep_queries(const RowsView &rv, const void *queries_dev, uint32_t q,
+                                uint32_t elem_bytes, float *qf32, uint8_t *qraw, float4 *qtails,
+                                float *qnorms, cudaStream_t st) {
+  if (q == 0) return cudaSuccess;
+  prep_queries_kernel<<<q, 128, 0, st>>>(rv, (const uint8_t *)queries_dev, elem_bytes, qf32, qraw,
+                                        qtails, qnorms);
+  count_launch();
+  return cudaGetLastError();
+}
+
+cudaError_t launch_repack_rows(const uint8_t *src, uint32_t elem_bytes, uint64_t n, uint8_t *dst,
+                               uint32_t row_stride, uint32_t vec_bytes, float4 *tails,
+                               uint32_t tail_off, cudaStream_t st) {
+  if (n == 0) return cudaSuccess;
+  const uint64_t total = n * (row_stride / 16);
+  const int grid = (int)std::min<uint64_t>((total + 255) / 256, 148 * 16);
+  repack_rows_kernel<<<grid, 256, 0, st>>>(src, elem_bytes, n, dst, row_stride, vec_bytes, tails, tail_off);
+  count_launch();
+  return cudaGetLastError();
+}
+
+cudaError_t launch_row_norms(const RowsView &rv, uint64_t row_begin, uint64_t row_end,
+                             float *norms, cudaStream_t st) {
+  if (row_end <= row_begin) return cudaSuccess;
+  const uint64_t rows = row_end - row_begin;
+  const uint64_t blocks = (rows + 7) / 8;
+  row_norms_kernel<<<(unsigned)blocks, 256, 0, st>>>(rv, row_begin, row_end, norms);
+  count_launch();
+  return cudaGetLastError();
+}
+
+cudaError_t launch_merge_parts(const u64 *part, uint32_t nparts, uint32_t q, uint32_t k,
+                               float *out_scores, uint32_t *out_index, cudaStream_t st) {
+  if (q == 0) return cudaSuccess;
+  const size_t smem = sizeof(int2) * kMergeWarps + (size_t)kMergeWarps * (2 * (size_t)k + 32) * sizeof(u64);
+  static bool attr_set = false;
+  if (!attr_set) {
+    cudaError_t e = cudaFuncSetAttribute(merge_parts_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+    if (e != cudaSuccess) return e;
+    attr_set = true;
+  }
+  merge_parts_kernel<<<q, kMergeWarps * 32, smem, st>>>(part, nparts, k, out_scores, out_index);
+  count_launch();
+  return cudaGetLastError();
+}
+
+cudaError_t launch_merge_shards(const float *scores, const uint32_t *index, uint32_t g,
+                                const uint64_t *shard_base_dev, uint32_t q, uint32_t k,
+                                float *out_scores, uint64_t *out_rows, cudaStream_t st) {
+  if (q == 0) return cudaSuccess;
+  const int wpb = 4;
+  merge_shards_kernel<<<(q + wpb - 1) / wpb, wpb * 32, 0, st>>>(scores, index, g, shard_base_dev, q,
+                                                               k, out_scores, out_rows);
+  count_launch();
+  return cudaGetLastError();
+}
+
+cudaError_t launch_distance_matrix(const RowsView &rv, const QueryView &qv, float *out,
+                                   cudaStream_t st) {
+  if (rv.n == 0 || qv.q == 0) return cudaSuccess;
+  const uint64_t blocks = (rv.n + 7) / 8;
+  distance_matrix_kernel<<<(unsigned)blocks, 256, 0, st>>>(rv, qv, out);
+  count_launch();
+  return cudaGetLastError();
+}
+
+}  // namespace zvb

@@ -1,0 +1,82 @@
+// Host-side structures shared by the C ABI and the kernel launchers.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include <mutex>
+#include <string>
+#include <vector>
+
+#include "common.cuh"
+
+namespace zvb {
+
+// What a scan kernel needs to know about the rows it streams (device pointers).
+struct RowsView {
+  const uint8_t *rows = nullptr;  // n rows, row_stride bytes apart, 16-B aligned
+  uint64_t n = 0;
+  uint32_t row_stride = 0;  // bytes, multiple of 16
+  uint32_t chunks = 0;      // 16-byte chunks of a row that carry vector data
+  uint32_t d = 0;           // elements that enter the dot product (tails stripped)
+  int dtype = 0, metric = 0;
+  const float4 *tails = nullptr;    // QI8: {a, b, s, s2} per row
+  const float *norms = nullptr;     // |x|^2 per row (tensor-core L2 path)
+  const uint32_t *drop = nullptr;   // bit set = deleted row or kInvalidKey hole
+};
+
+// Queries in "compute layout", produced by prep_queries() on the device.
+struct QueryView {
+  const float *qf32 = nullptr;     // fp32/fp16 stores: q x (chunks*16/esz) floats, zero padded
+  const uint8_t *qraw = nullptr;   // raw codes/halves: q x row_stride bytes, zero padded
+  const float4 *qtails = nullptr;  // QI8 query tails
+  const float *qnorms = nullptr;   // |q|^2
+  uint32_t q = 0;
+};
+
+struct SearchParams {
+  uint32_t k = 0;
+  float threshold = 0.f;
+  const uint32_t *filter = nullptr;  // device bitmap, bit set = drop
+};
+
+// Partial top-k lists: part[query][nparts][k] packed keys, padded with kMaxKey.
+struct PartView {
+  u64 *part = nullptr;
+  uint32_t nparts = 0;
+};
+
+// ---- launchers (each returns a cudaError_t; all asynchronous on `st`) ----
+// K1: GEMV-style streaming scan, CUDA cores, best for q <= 4.
+cudaError_t launch_scan_gemv(const RowsView &rv, const QueryView &qv, const SearchParams &sp,
+                             uint64_t row_begin, uint64_t row_end, u64 *part, uint32_t *nparts,
+                             int sm_count, cudaStream_t st);
+size_t scan_gemv_max_parts(int sm_count);
+// K2c: tiled CUDA-core contraction, exact (x-q)^2 for L2; any q.
+cudaError_t launch_scan_tile(const RowsView &rv, const QueryView &qv, const SearchParams &sp,
+                             uint64_t row_begin, uint64_t row_end, u64 *part, uint32_t *nparts,
+                             int sm_count, cudaStream_t st);
+size_t scan_tile_max_parts(int sm_count);
+bool scan_tile_supports(uint32_t k);
+// queries (stored layout, device) -> compute layout
+cudaError_t launch_prep_queries(const RowsView &rv, const void *queries_dev, uint32_t q,
+                                uint32_t elem_bytes, float *qf32, uint8_t *qraw, float4 *qtails,
+                                float *qnorms, cudaStream_t st);
+// part[q][nparts][k] -> final sorted (score,index) q*k, padded NaN / INVALID
+cudaError_t launch_merge_parts(const u64 *part, uint32_t nparts, uint32_t q, uint32_t k,
+                               float *out_scores, uint32_t *out_index, cudaStream_t st);
+// G sorted shard lists [g][q][k] -> q*k by (score, shard_base[g]+index)
+cudaError_t launch_merge_shards(const float *scores, const uint32_t *index, uint32_t g,
+                                const uint64_t *shard_base_dev, uint32_t q, uint32_t k,
+                                float *out_scores, uint64_t *out_rows, cudaStream_t st);
+// reference element layout (host order) -> store layout
+cudaError_t launch_repack_rows(const uint8_t *src, uint32_t elem_bytes, uint64_t n, uint8_t *dst,
+                               uint32_t row_stride, uint32_t vec_bytes, float4 *tails,
+                               uint32_t tail_off, cudaStream_t st);
+cudaError_t launch_row_norms(const RowsView &rv, uint64_t row_begin, uint64_t row_end,
+                             float *norms, cudaStream_t st);
+cudaError_t launch_distance_matrix(const RowsView &rv, const QueryView &qv, float *out,
+                                   cudaStream_t st);
+
+void count_launch(int n = 1);
+
+}  // namespace zvb

@@ -1,0 +1,327 @@
+// K1 — GEMV-style streaming scan with fused warp top-k (small query batches).
+//
+// Replaces the per-row loop of FlatStreamerEntity::search_block
+// (src/core/algorithm/flat/flat_streamer_entity.cc:256-316) /
+// FlatSearcherContext::search_row_nofilter (flat_searcher_context.h:847-921): for every
+// stored row one ailego XxxDistanceMatrix<T,1,1>::Compute (euclidean_distance_matrix_fp32.cc:287,
+// inner_product_matrix_fp16.cc:167-189, inner_product_matrix_int8.cc:374) and one
+// heap->emplace.  HBM-bound: every stored byte is read exactly once with 128-bit
+// L1-bypassing loads, the queries live in shared memory, nothing but k keys per CTA
+// goes back to HBM.
+#include "internal.h"
+#include "topk.cuh"
+
+namespace zvb {
+
+namespace {
+
+constexpr int kThreads = 256;
+constexpr int kWarps = kThreads / 32;
+constexpr int kU = 8;  // row groups in flight per warp (memory-level parallelism)
+
+struct GemvArgs {
+  RowsView rv;
+  QueryView qv;
+  uint32_t q0;        // first query of this launch
+  uint32_t k;
+  float threshold;
+  const uint32_t *filter;
+  uint64_t row_begin, row_end;
+  u64 *part;          // [q][nparts][k]
+  uint32_t nparts;
+  int lpr_log2;       // lanes per row = 1 << lpr_log2
+};
+
+__device__ __forceinline__ bool bit_set(const uint32_t *bm, uint64_t i) {
+  return (bm[i >> 5] >> (i & 31)) & 1u;
+}
+
+// accumulate one 16-byte chunk of a stored row against the query chunk in smem
+template <int DT, bool L2>
+struct Chunk;
+
+template <bool L2>
+struct Chunk<ZVB200_DT_FP32, L2> {
+  typedef float Acc;
+  static __device__ __forceinline__ void fma(Acc &acc, Acc &, const uint4 &v, const uint8_t *qs, int c) {
+    const float4 q = *reinterpret_cast<const float4 *>(qs + (size_t)c * 16);
+    const float x0 = __uint_as_float(v.x), x1 = __uint_as_float(v.y), x2 = __uint_as_float(v.z),
+                x3 = __uint_as_float(v.w);
+    if (L2) {
+      float d0 = x0 - q.x, d1 = x1 - q.y, d2 = x2 - q.z, d3 = x3 - q.w;
+      acc = fmaf(d0, d0, acc); acc = fmaf(d1, d1, acc); acc = fmaf(d2, d2, acc); acc = fmaf(d3, d3, acc);
+    } else {
+      acc = fmaf(x0, q.x, acc); acc = fmaf(x1, q.y, acc); acc = fmaf(x2, q.z, acc); acc = fmaf(x3, q.w, acc);
+    }
+  }
+  static __host__ __device__ size_t qbytes(uint32_t chunks) { return (size_t)chunks * 16; }
+};
+
+template <bool L2>
+struct Chunk<ZVB200_DT_FP16, L2> {
+  typedef float Acc;
+  // query kept as fp32 in smem (32 B per 16-B chunk of halves): widen once, like the
+  // reference's F16C path (inner_product_matrix_fp16.cc:144-189), accumulate in fp32.
+  static __device__ __forceinline__ void fma(Acc &acc, Acc &, const uint4 &v, const uint8_t *qs, int c) {
+    const float4 qa = *reinterpret_cast<const float4 *>(qs + (size_t)c * 32);
+    const float4 qb = *reinterpret_cast<const float4 *>(qs + (size_t)c * 32 + 16);
+    const float2 a = __half22float2(*reinterpret_cast<const __half2 *>(&v.x));
+    const float2 b = __half22float2(*reinterpret_cast<const __half2 *>(&v.y));
+    const float2 e = __half22float2(*reinterpret_cast<const __half2 *>(&v.z));
+    const float2 f = __half22float2(*reinterpret_cast<const __half2 *>(&v.w));
+    if (L2) {
+      float d;
+      d = a.x - qa.x; acc = fmaf(d, d, acc); d = a.y - qa.y; acc = fmaf(d, d, acc);
+      d = b.x - qa.z; acc = fmaf(d, d, acc); d = b.y - qa.w; acc = fmaf(d, d, acc);
+      d = e.x - qb.x; acc = fmaf(d, d, acc); d = e.y - qb.y; acc = fmaf(d, d, acc);
+      d = f.x - qb.z; acc = fmaf(d, d, acc); d = f.y - qb.w; acc = fmaf(d, d, acc);
+    } else {
+      acc = fmaf(a.x, qa.x, acc); acc = fmaf(a.y, qa.y, acc); acc = fmaf(b.x, qa.z, acc);
+      acc = fmaf(b.y, qa.w, acc); acc = fmaf(e.x, qb.x, acc); acc = fmaf(e.y, qb.y, acc);
+      acc = fmaf(f.x, qb.z, acc); acc = fmaf(f.y, qb.w, acc);
+    }
+  }
+  static __host__ __device__ size_t qbytes(uint32_t chunks) { return (size_t)chunks * 32; }
+};
+
+template <bool L2>
+struct Chunk<ZVB200_DT_INT8, L2> {
+  typedef int Acc;
+  // exact int32 accumulation as euclidean_distance_matrix_int8.cc:33-120 /
+  // inner_product_matrix_int8.cc:319-368; L2 = aa - 2ab + qq with aa gathered here.
+  static __device__ __forceinline__ void fma(Acc &ab, Acc &aa, const uint4 &v, const uint8_t *qs, int c) {
+    const uint4 q = *reinterpret_cast<const uint4 *>(qs + (size_t)c * 16);
+    ab = __dp4a((int)v.x, (int)q.x, ab); ab = __dp4a((int)v.y, (int)q.y, ab);
+    ab = __dp4a((int)v.z, (int)q.z, ab); ab = __dp4a((int)v.w, (int)q.w, ab);
+    if (L2) {
+      aa = __dp4a((int)v.x, (int)v.x, aa); aa = __dp4a((int)v.y, (int)v.y, aa);
+      aa = __dp4a((int)v.z, (int)v.z, aa); aa = __dp4a((int)v.w, (int)v.w, aa);
+    }
+  }
+  static __host__ __device__ size_t qbytes(uint32_t chunks) { return (size_t)chunks * 16; }
+};
+
+template <int DT, bool L2, int QB>
+__global__ void __launch_bounds__(kThreads, QB == 1 ? 2 : 1) scan_gemv_kernel(const GemvArgs a) {
+  typedef Chunk<DT, L2> CK;
+  typedef typename CK::Acc Acc;
+  extern __shared__ __align__(16) uint8_t smem[];
+  const int lane = lane_id(), warp = threadIdx.x >> 5;
+  const uint32_t C = a.rv.chunks;
+  const size_t qbytes = CK::qbytes(C);
+  const int nq = min((uint32_t)QB, a.qv.q - a.q0);  // live queries of this launch
+  const int k = a.k;
+
+  // ---- smem: QB queries | int qq[QB] | meta[kWarps*QB] | top-k storage ----
+  uint8_t *qs = smem;
+  int *qq = reinterpret_cast<int *>(smem + (size_t)QB * qbytes);
+  int2 *meta = reinterpret_cast<int2 *>(qq + QB + (QB & 1));  // {list offset in u64s, cnt}
+  u64 *tkbase = reinterpret_cast<u64 *>(meta + kWarps * QB);
+  const size_t tk_u64 = (size_t)2 * k + 32;
+
+  // load queries (compute layout) into smem
+  for (int j = 0; j < QB; ++j) {
+    const bool live = j < nq;
+    const uint8_t *src = (DT == ZVB200_DT_INT8)
+                             ? a.qv.qraw + (size_t)(a.q0 + j) * a.rv.row_stride
+                             : reinterpret_cast<const uint8_t *>(a.qv.qf32) + (size_t)(a.q0 + j) * qbytes;
+    for (size_t o = (size_t)threadIdx.x * 16; o < qbytes; o += (size_t)kThreads * 16) {
+      uint4 v = make_uint4(0, 0, 0, 0);
+      if (live) v = *reinterpret_cast<const uint4 *>(src + o);
+      *reinterpret_cast<uint4 *>(qs + (size_t)j * qbytes + o) = v;
+    }
+  }
+  __syncthreads();
+  if (DT == ZVB200_DT_INT8 && L2 && threadIdx.x < QB) {  // qq = sum q^2 (plain int8 L2)
+    int s = 0;
+    const int8_t *p = reinterpret_cast<const int8_t *>(qs + (size_t)threadIdx.x * qbytes);
+    for (size_t i = 0; i < qbytes; ++i) s += (int)p[i] * (int)p[i];
+    qq[threadIdx.x] = s;
+  }
+  __syncthreads();
+
+  WarpTopk tk[QB];
+#pragma unroll
+  for (int j = 0; j < QB; ++j) {
+    u64 *b = tkbase + (size_t)(warp * QB + j) * tk_u64;
+    tk[j].init(b, b + k, b + 2 * k, k, kMaxKey);
+  }
+
+  const int lpr = 1 << a.lpr_log2, R = 32 >> a.lpr_log2;
+  const int l = lane & (lpr - 1), sub = lane >> a.lpr_log2;
+  const uint64_t rows_per_warp_step = (uint64_t)kU * R;
+  const uint64_t rows_per_tile = rows_per_warp_step * kWarps;
+  const uint64_t nrows = a.row_end - a.row_begin;
+  const uint64_t ntiles = (nrows + rows_per_tile - 1) / rows_per_tile;
+  const int metric = a.rv.metric;
+  const float dq = (float)a.rv.d;
+
+  float4 qt[QB];
+  if (metric_is_qi8(metric)) {
+#pragma unroll
+    for (int j = 0; j < QB; ++j) qt[j] = j < nq ? a.qv.qtails[a.q0 + j] : make_float4(0, 0, 0, 0);
+  }
+
+  for (uint64_t t = blockIdx.x; t < ntiles; t += gridDim.x) {
+    const uint64_t base = a.row_begin + t * rows_per_tile + (uint64_t)warp * rows_per_warp_step;
+    if (base >= a.row_end) continue;  // warp-uniform
+    Acc acc[kU][QB], aa[kU];
+    const uint8_t *rp[kU];
+#pragma unroll
+    for (int u = 0; u < kU; ++u) {
+      uint64_t r = base + (uint64_t)u * R + sub;
+      if (r >= a.row_end) r = a.row_end - 1;  // clamp: loaded, result discarded
+      rp[u] = a.rv.rows + r * a.rv.row_stride;
+      aa[u] = 0;
+#pragma unroll
+      for (int j = 0; j < QB; ++j) acc[u][j] = 0;
+    }
+    for (uint32_t c = l; c < C; c += lpr) {
+      uint4 v[kU];
+#pragma unroll
+      for (int u = 0; u < kU; ++u) v[u] = ldg_stream(rp[u] + (size_t)c * 16);
+#pragma unroll
+      for (int j = 0; j < QB; ++j) {
+#pragma unroll
+        for (int u = 0; u < kU; ++u) {
+          Acc dummy = 0;
+          CK::fma(acc[u][j], j == 0 ? aa[u] : dummy, v[u], qs + (size_t)j * qbytes, c);
+        }
+      }
+    }
+    // reduce across the lanes of a row
+    for (int o = lpr >> 1; o > 0; o >>= 1) {
+#pragma unroll
+      for (int u = 0; u < kU; ++u) {
+        if (DT == ZVB200_DT_INT8 && L2) aa[u] += __shfl_xor_sync(0xffffffffu, aa[u], o);
+#pragma unroll
+        for (int j = 0; j < QB; ++j) acc[u][j] += __shfl_xor_sync(0xffffffffu, acc[u][j], o);
+      }
+    }
+    // epilogue: score, gate, push
+#pragma unroll
+    for (int u = 0; u < kU; ++u) {
+      const uint64_t r = base + (uint64_t)u * R + sub;
+      bool valid = (l == 0) && r < a.row_end;
+      if (valid && a.rv.drop) valid = !bit_set(a.rv.drop, r);
+      if (valid && a.filter) valid = !bit_set(a.filter, r);
+      float4 mt = make_float4(0, 0, 0, 0);
+      if (metric_is_qi8(metric) && valid) mt = a.rv.tails[r];
+#pragma unroll
+      for (int j = 0; j < QB; ++j) {
+        float s;
+        if (DT == ZVB200_DT_INT8) {
+          if (metric == ZVB200_METRIC_QI8_L2SQ) s = qi8_l2sq((float)acc[u][j], mt, qt[j], dq);
+          else if (metric_is_qi8(metric)) s = qi8_mip((float)acc[u][j], mt, qt[j], dq);
+          else if (L2) {
+            s = (float)((int)aa[u] - 2 * (int)acc[u][j] + qq[j]);
+            if (metric == ZVB200_METRIC_L2) s = sqrtf(s);
+          } else s = -(float)acc[u][j];
+        } else {
+          const float f = (float)acc[u][j];
+          s = metric == ZVB200_METRIC_L2SQ ? f
+              : metric == ZVB200_METRIC_L2 ? sqrtf(f)
+              : metric == ZVB200_METRIC_IP ? -f : 1.0f - f;
+        }
+        const u64 key = pack_key(s, (uint32_t)r);
+        const bool has = valid && j < nq && s <= a.threshold && key < tk[j].tau;
+        tk[j].push(has, key, kMaxKey);
+      }
+    }
+  }
+
+  // ---- merge the warps' lists inside the CTA, one owner warp per query ----
+#pragma unroll
+  for (int j = 0; j < QB; ++j) {
+    tk[j].finish(kMaxKey);
+    if (lane == 0) meta[warp * QB + j] = make_int2((int)(tk[j].list - tkbase), tk[j].cnt);
+  }
+  __syncthreads();
+#pragma unroll
+  for (int j = 0; j < QB; ++j) {
+    if (warp != (j % kWarps) || j >= nq) continue;
+    for (int w = 0; w < kWarps; ++w) {
+      if (w == warp) continue;
+      const int2 m = meta[w * QB + j];
+      const u64 *src = tkbase + m.x;
+      for (int i0 = 0; i0 < m.y; i0 += 32) {
+        const int i = i0 + lane;
+        const u64 e = i < m.y ? src[i] : kMaxKey;
+        tk[j].push(i < m.y && e < tk[j].tau, e, kMaxKey);
+      }
+    }
+    tk[j].finish(kMaxKey);
+    u64 *dst = a.part + ((size_t)(a.q0 + j) * a.nparts + blockIdx.x) * k;
+    for (int i = lane; i < k; i += 32) dst[i] = i < tk[j].cnt ? tk[j].list[i] : kMaxKey;
+  }
+}
+
+template <int DT, bool L2, int QB>
+cudaError_t launch_one(const GemvArgs &a, int grid, size_t smem, cudaStream_t st) {
+  auto kern = scan_gemv_kernel<DT, L2, QB>;
+  cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  if (e != cudaSuccess) return e;
+  kern<<<grid, kThreads, smem, st>>>(a);
+  count_launch();
+  return cudaGetLastError();
+}
+
+template <int DT, bool L2>
+cudaError_t launch_qb(const GemvArgs &a, int qb, int grid, size_t smem, cudaStream_t st) {
+  switch (qb) {
+    case 1: return launch_one<DT, L2, 1>(a, grid, smem, st);
+    case 2: return launch_one<DT, L2, 2>(a, grid, smem, st);
+    default: return launch_one<DT, L2, 4>(a, grid, smem, st);
+  }
+}
+
+size_t gemv_smem(int dtype, uint32_t chunks, int qb, uint32_t k) {
+  size_t qbytes = dtype == ZVB200_DT_FP16 ? (size_t)chunks * 32 : (size_t)chunks * 16;
+  return (size_t)qb * qbytes + sizeof(int) * (qb + (qb & 1)) + sizeof(int2) * kWarps * qb +
+         (size_t)kWarps * qb * (2 * (size_t)k + 32) * sizeof(u64);
+}
+
+}  // namespace
+
+size_t scan_gemv_max_parts(int sm_count) { return (size_t)sm_count * 2; }
+
+cudaError_t launch_scan_gemv(const RowsView &rv, const QueryView &qv, const SearchParams &sp,
+                             uint64_t row_begin, uint64_t row_end, u64 *part, uint32_t *nparts,
+                             int sm_count, cudaStream_t st) {
+  GemvArgs a;
+  a.rv = rv; a.qv = qv; a.k = sp.k; a.threshold = sp.threshold; a.filter = sp.filter;
+  a.row_begin = row_begin; a.row_end = row_end; a.part = part;
+  // lanes per row: largest power of two <= min(32, chunks)
+  int lg = 0;
+  while ((2u << lg) <= rv.chunks && lg < 5) ++lg;
+  a.lpr_log2 = lg;
+  const uint64_t rows_per_tile = (uint64_t)kU * (32 >> lg) * kWarps;
+  const uint64_t nrows = row_end > row_begin ? row_end - row_begin : 0;
+  uint64_t ntiles = (nrows + rows_per_tile - 1) / rows_per_tile;
+  int grid = (int)std::min<uint64_t>(std::max<uint64_t>(ntiles, 1), (uint64_t)sm_count * 2);
+  a.nparts = grid;
+  *nparts = grid;
+  // queries per pass: as many as fit 100 KB of smem (2 CTAs/SM), at most 4
+  int qb = qv.q >= 4 ? 4 : (qv.q >= 2 ? 2 : 1);
+  while (qb > 1 && gemv_smem(rv.dtype, rv.chunks, qb, sp.k) > 100 * 1024) qb >>= 1;
+  const size_t smem = gemv_smem(rv.dtype, rv.chunks, qb, sp.k);
+  if (smem > 220 * 1024) return cudaErrorInvalidValue;
+  const bool l2 = metric_is_l2(rv.metric);
+  for (uint32_t q0 = 0; q0 < qv.q; q0 += qb) {
+    a.q0 = q0;
+    cudaError_t e;
+    if (rv.dtype == ZVB200_DT_FP32)
+      e = l2 ? launch_qb<ZVB200_DT_FP32, true>(a, qb, grid, smem, st)
+             : launch_qb<ZVB200_DT_FP32, false>(a, qb, grid, smem, st);
+    else if (rv.dtype == ZVB200_DT_FP16)
+      e = l2 ? launch_qb<ZVB200_DT_FP16, true>(a, qb, grid, smem, st)
+             : launch_qb<ZVB200_DT_FP16, false>(a, qb, grid, smem, st);
+    else
+      e = l2 ? launch_qb<ZVB200_DT_INT8, true>(a, qb, grid, smem, st)
+             : launch_qb<ZVB200_DT_INT8, false>(a, qb, grid, smem, st);
+    if (e != cudaSuccess) return e;
+  }
+  return cudaSuccess;
+}
+
+}  // namespace zvb
