@@ -197,3 +197,43 @@ def test_get_vector_round_trip():
     st = z.Store(dt, metric, sdim); st.append(stored); st.seal()
     for r in (0, 57, 99):
         assert np.array_equal(st.get_vector(r), stored[r])
+
+
+# ---- K2c tiled kernel (batched) ---------------------------------------------------------
+@pytest.mark.parametrize("kind", KINDS)
+def test_tile_kernel_parity_all_metrics(kind):
+    assert run_case(kind, 4000, 96, 70, 10, seed=31, kernel=2) == "scan_tile"
+
+
+@pytest.mark.parametrize("d", [1, 5, 16, 17, 63, 64, 65, 200, 768])
+@pytest.mark.parametrize("kind", ["fp32_l2", "fp16_ip", "qi8_l2", "i8_l2"])
+def test_tile_kernel_ragged_dimensions(kind, d):
+    run_case(kind, 1000, d, 9, 7, seed=32 + d, kernel=2)
+
+
+@pytest.mark.parametrize("k", [1, 33, 100, 128])
+def test_tile_kernel_topk_sizes(k):
+    run_case("fp32_l2", 3000, 24, 65, k, seed=33, kernel=2)
+    run_case("i8_ip", 3000, 24, 5, k, seed=34, kernel=2)     # heavy ties
+
+
+def test_tile_kernel_auto_selected_for_batches_and_filters():
+    n = 3000
+    rng = np.random.default_rng(35)
+    assert run_case("fp32_l2", n, 32, 128, 10, seed=35) == "scan_tile"
+    drop = rng.random(n) < 0.3
+    filt = rng.random(n) < 0.3
+    run_case("fp16_l2", n, 32, 40, 10, seed=36, kernel=2, drop=drop, filt=filt)
+    run_case("fp32_l2", 50, 8, 33, 100, seed=37, kernel=2)            # k > n
+    run_case("fp32_l2", n, 16, 33, 20, seed=38, kernel=2, threshold=10.0)
+    assert run_case("fp32_l2", n, 16, 33, 300, seed=39) == "scan_gemv"  # k beyond the tile kernel's lists
+
+
+def test_tile_and_gemv_agree_bitwise_on_int8():
+    metric, dt, sdim, stored, conv = make_stored("qi8_l2", 6000, 96, 40)
+    queries = np.ascontiguousarray(conv(np.random.default_rng(41).standard_normal((48, 96)).astype(np.float32)))
+    st = z.Store(dt, metric, sdim); st.append(stored); st.seal()
+    ctx = z.Context(st)
+    ctx.set_kernel(1); _, s1, i1, _ = ctx.search(queries, 100)
+    ctx.set_kernel(2); _, s2, i2, _ = ctx.search(queries, 100)
+    assert np.array_equal(s1.view(np.uint32), s2.view(np.uint32)) and np.array_equal(i1, i2)
