@@ -1,0 +1,391 @@
+#!/usr/bin/env python3
+"""bench.py — QPS@top10 of the exhaustive scan on BASELINE.json configs[1]:
+Flat fp16 inner product over synthetic 10M x 768 (Cohere-shape), batch 1024 (headline) and
+batch 1, rows sharded over N GPUs of one node (strong scaling), per-GPU top-k merged with an
+NCCL all-gather + the k-way merge kernel.
+
+  python bench.py --gpus N --steps K --warmup W            # our CUDA path (torchrun for N>1)
+  python bench.py --impl reference --gpus N ...            # the reference's CPU path, host cores
+
+A "step" is one search of one batch.  `value` is whole-job QPS with queries already in HBM,
+timed with CUDA events on the stream the kernels run on, max over ranks.  `e2e` is the same
+metric through the host-buffer C-ABI call (H2D of the queries and D2H of the results inside
+the timed region).  PyTorch is only plumbing here (device memory for synthetic data,
+torch.distributed); every kernel in the timed region is from libzvec_b200.so.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+DIM = 768
+SEED_BASE, SEED_QUERY = 2024, 4202
+CHUNK = 500_000  # rows generated per device chunk
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--rows", type=int, default=10_000_000)
+    ap.add_argument("--batch", type=int, default=1024)
+    ap.add_argument("--topk", type=int, default=10)
+    ap.add_argument("--kernel", type=int, default=0, help="0 auto, 1 gemv, 2 tile, 3 tcgen05")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--cpu-sample-rows", type=int, default=200_000)
+    return ap.parse_args()
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        d = json.load(open(p))
+        return {"hbm_gbs": d["hbm_gbs"], "tf_burst": d["bf16_tflops"], "tf_sustained": d["bf16_tflops_sustained"],
+                "source": "measured (MEASURED_PEAKS.json)"}
+    return {"hbm_gbs": 6650.0, "tf_burst": 1590.0, "tf_sustained": 1400.0, "source": "fallback (B200_PROFILING.md)"}
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.proc, self.lines = index, None, []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 7:
+                continue
+            try:
+                sm.append(float(f[0])); mx.append(float(f[1]))
+            except ValueError:
+                continue
+            for nme, v in zip(names, f[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(nme)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "samples": len(sm), "reasons": sorted(reasons)}
+
+
+# -----------------------------------------------------------------------------------------
+# reference arm / cpu baseline: the reference's own FlatSearcher on the host cores
+# -----------------------------------------------------------------------------------------
+def host_queries(n):
+    rng = np.random.default_rng(SEED_QUERY)
+    q = rng.standard_normal((n, DIM)).astype(np.float32)
+    q /= np.linalg.norm(q, axis=1, keepdims=True)
+    return q
+
+
+def cpu_reference_qps(args, min_seconds, batch):
+    """QPS of the reference CPU path on a bounded row sample, scaled to args.rows rows."""
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import support as S
+    cores = os.cpu_count() or 1
+    ns = min(args.cpu_sample_rows, args.rows)
+    rng = np.random.default_rng(SEED_BASE)
+    x = rng.standard_normal((ns, DIM)).astype(np.float32)
+    x /= np.linalg.norm(x, axis=1, keepdims=True)
+    kind = "reference"
+    if S.ref() is not None:
+        ri = S.RefIndex(x, S.DT_FP32, DIM, "InnerProduct", "HalfFloatConverter")
+        nq = max(cores * 4, 32)
+        qs = host_queries(nq)
+        ri.search(qs[:cores], args.topk, batch=1, threads=cores)  # warm-up (page in the mmap)
+        done, t0 = 0, time.perf_counter()
+        while True:
+            ri.search(qs, args.topk, batch=batch, threads=cores)
+            done += nq
+            el = time.perf_counter() - t0
+            if el >= min_seconds:
+                break
+        ri.close()
+        lib = S.ref()._name
+    else:  # the scalar restatement (1 thread)
+        kind, cores, lib = "port", 1, "libzvec_oracle.so"
+        xs = x.astype(np.float16)
+        qs = host_queries(8).astype(np.float16)
+        done, t0 = 0, time.perf_counter()
+        while True:
+            S.oracle_flat_search(S.M_IP, S.DT_FP16, xs.view(np.uint8).reshape(ns, -1), DIM,
+                                 qs.view(np.uint8).reshape(8, -1), args.topk)
+            done += 8
+            el = time.perf_counter() - t0
+            if el >= min_seconds:
+                break
+    qps_sample = done / el
+    return {"value": qps_sample * ns / args.rows, "unit": "queries/s", "cores": cores, "kind": kind,
+            "sample": "%s FlatSearcher (row-major, HalfFloatConverter, batch %d per search_impl call, %d threads) on "
+                      "%d of %d rows for %.1f s (%d queries); QPS scaled linearly by rows" %
+                      (lib, batch, cores, ns, args.rows, el, done),
+            "qps_on_sample": qps_sample}
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    # each "step" = a bounded sample timed for a few seconds; K+W steps stay within minutes
+    per_step = max(2.0, min(10.0, 60.0 / max(1, args.steps + args.warmup)))
+    for _ in range(min(args.warmup, 1)):
+        cpu_reference_qps(args, 1.0, 32)
+    vals, base = [], None
+    for _ in range(max(1, min(args.steps, 5))):
+        base = cpu_reference_qps(args, per_step, 32)
+        vals.append(base["value"])
+    v = float(np.mean(vals))
+    base["value"] = v
+    out = {"impl": "reference", "metric": "QPS@top10 (batch 1024)", "value": v, "unit": "queries/s",
+           "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+           "ms_per_step": 1000.0 * args.batch / v, "higher_is_better": True, "scaling": "strong",
+           "vs_baseline": None, "dtype": "f16", "data": "synthetic",
+           "config": workload_config(args, args.gpus), "cpu_baseline": base,
+           "e2e": {"value": v, "unit": "queries/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+           "gpu_launches": 0}
+    print(json.dumps(out), flush=True)
+
+
+def workload_config(args, n):
+    return {"workload": "Flat fp16 InnerProduct, synthetic %dx%d (Cohere-shape), top%d, batch %d (headline) and "
+                        "batch 1; rows sharded over %d GPU(s)" % (args.rows, DIM, args.topk, args.batch, n),
+            "rows": args.rows, "dim": DIM, "topk": args.topk, "batch": args.batch, "shards": n,
+            "l2_policy": "inputs larger than L2: every step streams the whole %.1f GB shard (L2 is 126 MB)" %
+                         (args.rows / n * DIM * 2 / 1e9)}
+
+
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+    import zvec_b200 as z
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world != args.gpus:
+        raise SystemExit("--gpus %d but WORLD_SIZE=%d (launch N>1 with torch.distributed.run)" % (args.gpus, world))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    pk = peaks()
+
+    # ---- the shard: rows [lo, hi) of the global matrix, generated chunk by chunk on the device
+    per = (args.rows + world - 1) // world
+    lo, hi = rank * per, min(args.rows, (rank + 1) * per)
+    st = z.Store(z.DT_FP16, z.METRIC_IP, DIM, device=local)
+    st.reserve(hi - lo)
+    g = torch.Generator(device=dev)
+    c0 = (lo // CHUNK) * CHUNK
+    while c0 < hi:
+        g.manual_seed(SEED_BASE + c0 // CHUNK)           # data depends on the global row only
+        n = min(CHUNK, args.rows - c0)
+        x = torch.randn((n, DIM), generator=g, device=dev, dtype=torch.float32)
+        x = torch.nn.functional.normalize(x, dim=1).to(torch.float16)
+        a, b = max(lo, c0) - c0, min(hi, c0 + n) - c0
+        xs = x[a:b].contiguous()
+        torch.cuda.synchronize()
+        st.append_device(xs.data_ptr(), b - a)
+        del x, xs
+        c0 += CHUNK
+    st.seal()
+    torch.cuda.empty_cache()
+    nloc = st.count()
+    shard_bytes = st.scan_bytes()
+
+    hq = torch.from_numpy(host_queries(args.batch)).to(torch.float16).pin_memory()
+    dq = hq.to(dev)
+    k, B = args.topk, args.batch
+    ctx = z.Context(st)
+    ctx.set_kernel(args.kernel)
+    stream = torch.cuda.ExternalStream(ctx.stream(), device=dev)
+    loc_s = torch.empty((B, k), dtype=torch.float32, device=dev)
+    loc_i = torch.empty((B, k), dtype=torch.int32, device=dev)
+    all_s = torch.empty((world, B, k), dtype=torch.float32, device=dev)
+    all_i = torch.empty((world, B, k), dtype=torch.int32, device=dev)
+    fin_s = torch.empty((B, k), dtype=torch.float32, device=dev)
+    fin_r = torch.empty((B, k), dtype=torch.int64, device=dev)
+    h_s = torch.empty((B, k), dtype=torch.float32).pin_memory()
+    h_r = torch.empty((B, k), dtype=torch.int64).pin_memory()
+    bases = [min(args.rows, r * per) for r in range(world)]
+
+    def step(q):
+        """one batch of q queries already in HBM -> final top-k in HBM (all on ctx's stream)"""
+        ctx.search_device(dq.data_ptr(), q, k, loc_s.data_ptr(), loc_i.data_ptr())
+        if world > 1:
+            with torch.cuda.stream(stream):
+                dist.all_gather_into_tensor(all_s[:, :q].contiguous() if q != B else all_s, loc_s[:q] if q != B else loc_s)
+                dist.all_gather_into_tensor(all_i[:, :q].contiguous() if q != B else all_i, loc_i[:q] if q != B else loc_i)
+            ctx.merge_topk_device(all_s.data_ptr(), all_i.data_ptr(), world, bases, q, k, fin_s.data_ptr(), fin_r.data_ptr())
+
+    # gather buffers for q != B need their own tight tensors
+    small = {}
+
+    def step_q(q):
+        if q == B or world == 1:
+            return step(q)
+        if q not in small:
+            small[q] = (torch.empty((world, q, k), dtype=torch.float32, device=dev),
+                        torch.empty((world, q, k), dtype=torch.int32, device=dev))
+        ss, si = small[q]
+        ctx.search_device(dq.data_ptr(), q, k, loc_s.data_ptr(), loc_i.data_ptr())
+        with torch.cuda.stream(stream):
+            dist.all_gather_into_tensor(ss, loc_s.view(-1)[: q * k].view(q, k))
+            dist.all_gather_into_tensor(si, loc_i.view(-1)[: q * k].view(q, k))
+        ctx.merge_topk_device(ss.data_ptr(), si.data_ptr(), world, bases, q, k, fin_s.data_ptr(), fin_r.data_ptr())
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(q, steps, warmup):
+        for _ in range(warmup):
+            step_q(q)
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        l0 = z.lib().zvb200_kernel_launches()
+        e0.record(stream)
+        for _ in range(steps):
+            step_q(q)
+        e1.record(stream)
+        barrier()
+        ms = e0.elapsed_time(e1)
+        launches = z.lib().zvb200_kernel_launches() - l0
+        if world > 1:
+            t = torch.tensor([ms], device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms = float(t.item())
+        return ms, launches
+
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    ms_b, launches = timed(B, args.steps, args.warmup)
+    clocks = sampler.stop() if rank == 0 else None
+    kernel_b = ctx.last_kernel()
+    # dominant-kernel duration, measured live with CUDA events around the scan kernel only
+    scan_ms = []
+    for _ in range(args.steps):
+        step_q(B)
+        scan_ms.append(ctx.last_scan_ms())
+    scan_b = float(np.mean(scan_ms))
+    # batch 1
+    s1 = max(args.steps, 30)
+    ms_1, _ = timed(1, s1, max(args.warmup, 3))
+    kernel_1 = ctx.last_kernel()
+    scan_ms = []
+    for _ in range(10):
+        step_q(1)
+        scan_ms.append(ctx.last_scan_ms())
+    scan_1 = float(np.mean(scan_ms))
+
+    # ---- e2e: the call a user makes — host buffers in, host results out
+    def e2e_step(q):
+        if world == 1:
+            ctx.search(hq.numpy()[:q], k)        # zvb200_search: H2D + kernels + D2H + sync
+            return
+        with torch.cuda.stream(stream):
+            dq[:q].copy_(hq[:q], non_blocking=True)
+        step_q(q)
+        with torch.cuda.stream(stream):
+            h_s[:q].copy_(fin_s[:q], non_blocking=True)
+            h_r[:q].copy_(fin_r[:q], non_blocking=True)
+        stream.synchronize()
+
+    def e2e_timed(q, steps):
+        for _ in range(3):
+            e2e_step(q)
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(steps):
+            e2e_step(q)
+        barrier()
+        el = time.perf_counter() - t0
+        if world > 1:
+            t = torch.tensor([el], device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            el = float(t.item())
+        return el
+
+    el_b = e2e_timed(B, args.steps)
+    el_1 = e2e_timed(1, s1)
+
+    if rank == 0:
+        qps_b = B * args.steps / (ms_b / 1e3)
+        qps_1 = s1 / (ms_1 / 1e3)
+        flops = 2.0 * nloc * DIM * B                       # per launch, this rank's shard
+        tf = flops / (scan_b / 1e3) / 1e12
+        gbs1 = shard_bytes / (scan_1 / 1e3) / 1e9
+        out = {
+            "metric": "QPS@top10 (batch 1024)", "value": qps_b, "unit": "queries/s", "n_gpus": world,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_b / args.steps,
+            "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f16",
+            "data": "synthetic", "config": workload_config(args, world),
+            "kernel": kernel_b, "clocks": clocks, "gpu_launches": int(launches),
+            "e2e": {"value": B * args.steps / el_b, "unit": "queries/s", "h2d_bytes_per_step": B * DIM * 2,
+                    "d2h_bytes_per_step": B * k * (8 if world == 1 else 12),
+                    "via": "zvb200_search (host buffers)" if world == 1 else
+                           "pinned H2D + zvb200_search_device + NCCL all-gather + zvb200_merge_topk_device + D2H"},
+            "roofline": {"bound": "tensor", "achieved": tf, "peak": pk["tf_sustained"], "unit": "TFLOP/s",
+                         "frac": tf / pk["tf_sustained"], "traffic": None, "kernel": kernel_b,
+                         "kernel_ms": scan_b, "peak_source": pk["source"] + ", sustained bf16",
+                         "algorithmic": "2*rows*dim*batch flop per launch = %.4g" % flops},
+            "batch1": {"value": qps_1, "unit": "queries/s", "steps": s1, "ms_per_step": ms_1 / s1, "kernel": kernel_1,
+                       "e2e": {"value": s1 / el_1, "unit": "queries/s", "h2d_bytes_per_step": DIM * 2,
+                               "d2h_bytes_per_step": k * (8 if world == 1 else 12)},
+                       "roofline": {"bound": "hbm", "achieved": gbs1, "peak": pk["hbm_gbs"], "unit": "GB/s",
+                                    "frac": gbs1 / pk["hbm_gbs"], "traffic": None, "kernel": kernel_1,
+                                    "kernel_ms": scan_1, "peak_source": pk["source"],
+                                    "algorithmic": "rows*dim*2 B per launch = %.4g" % shard_bytes}},
+        }
+        if world == 1 and not args.no_cpu_baseline:
+            out["cpu_baseline"] = cpu_reference_qps(args, 12.0, 32)
+            out["cpu_baseline_batch1"] = cpu_reference_qps(args, 8.0, 1)
+        print(json.dumps(out), flush=True)
+    ctx.close(); st.close()
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    a = parse()
+    if a.impl == "reference":
+        run_reference(a)
+    else:
+        run_ours(a)

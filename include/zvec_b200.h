@@ -122,6 +122,10 @@ int zvb200_search_device(zvb200_ctx *c, const void *queries_dev, uint32_t q, uin
                          float threshold, const uint32_t *filter_dev, float *out_scores_dev,
                          uint32_t *out_index_dev);
 int zvb200_ctx_sync(zvb200_ctx *c);
+/* Device time of the scan kernel(s) of the last search on this context, from CUDA events
+ * recorded on its stream around them (the IndexContext::Profiler analogue,
+ * src/include/zvec/core/framework/index_context.h:31-53).  Waits for that search. */
+int zvb200_ctx_last_scan_ms(zvb200_ctx *c, float *ms);
 /* The context's cudaStream_t (as void*) so callers can record events on it. */
 void *zvb200_ctx_stream(zvb200_ctx *c);
 /* Force a scan kernel: 0 auto, 1 GEMV scan (CUDA cores), 2 tiled CUDA-core, 3 tcgen05. */

@@ -49,6 +49,7 @@ _SIGS = {
                                        C.c_void_p, C.c_void_p, C.c_void_p]),
     "zvb200_ctx_sync": (C.c_int, [C.c_void_p]),
     "zvb200_ctx_stream": (C.c_void_p, [C.c_void_p]),
+    "zvb200_ctx_last_scan_ms": (C.c_int, [C.c_void_p, C.POINTER(C.c_float)]),
     "zvb200_ctx_set_kernel": (C.c_int, [C.c_void_p, C.c_int]),
     "zvb200_ctx_last_kernel": (C.c_char_p, [C.c_void_p]),
     "zvb200_distance_matrix": (C.c_int, [C.c_int, C.c_int, C.c_int, C.c_uint32, C.c_void_p, C.c_uint64,
@@ -172,6 +173,11 @@ class Context:
 
     def last_kernel(self):
         return lib().zvb200_ctx_last_kernel(self.h).decode()
+
+    def last_scan_ms(self):
+        ms = C.c_float()
+        _check(lib().zvb200_ctx_last_scan_ms(self.h, C.byref(ms)))
+        return ms.value
 
     def stream(self):
         return lib().zvb200_ctx_stream(self.h)

@@ -100,6 +100,8 @@ struct zvb200_ctx {
   HostBuf h_q, h_scores, h_index;
   int force_kernel = 0;
   const char *last_kernel = "none";
+  cudaEvent_t ev_scan0 = nullptr, ev_scan1 = nullptr;  // bracket the scan kernel(s) of the last search
+  bool scan_timed = false;
 };
 
 static int layout_for(int dtype, int metric, uint32_t dim, zvb200_store *s) {
@@ -343,6 +345,8 @@ int zvb200_ctx_create(zvb200_store *s, zvb200_ctx **out) {
   auto c = new zvb200_ctx();
   c->s = s;
   cudaError_t e = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking);
+  if (e == cudaSuccess) e = cudaEventCreate(&c->ev_scan0);
+  if (e == cudaSuccess) e = cudaEventCreate(&c->ev_scan1);
   if (e != cudaSuccess) { delete c; return cuda_fail(e, "ctx_create"); }
   *out = c;
   return 0;
@@ -356,6 +360,8 @@ int zvb200_ctx_destroy(zvb200_ctx *c) {
                  &c->out_index, &c->filter, &c->misc};
   for (auto b : d) b->release();
   c->h_q.release(); c->h_scores.release(); c->h_index.release();
+  if (c->ev_scan0) cudaEventDestroy(c->ev_scan0);
+  if (c->ev_scan1) cudaEventDestroy(c->ev_scan1);
   cudaStreamDestroy(c->stream);
   delete c;
   return 0;
@@ -364,6 +370,13 @@ int zvb200_ctx_destroy(zvb200_ctx *c) {
 int zvb200_ctx_sync(zvb200_ctx *c) {
   if (!c) return set_err(ZVB200_ERR_INVALID_ARGUMENT, "null ctx");
   CU(cudaStreamSynchronize(c->stream));
+  return 0;
+}
+int zvb200_ctx_last_scan_ms(zvb200_ctx *c, float *ms) {
+  if (!c || !ms) return set_err(ZVB200_ERR_INVALID_ARGUMENT, "null argument");
+  if (!c->scan_timed) return set_err(ZVB200_ERR_NOREADY, "no search yet");
+  CU(cudaEventSynchronize(c->ev_scan1));
+  CU(cudaEventElapsedTime(ms, c->ev_scan0, c->ev_scan1));
   return 0;
 }
 void *zvb200_ctx_stream(zvb200_ctx *c) { return c ? (void *)c->stream : nullptr; }
@@ -412,6 +425,8 @@ static int search_core(zvb200_ctx *c, const void *queries_dev, uint32_t q, uint3
   if (group >= 64) group &= ~63u; else if (group >= 4) group &= ~3u;
   group = std::min(group, q);
   CU(c->part.ensure((size_t)group * per_query));
+  CU(cudaEventRecord(c->ev_scan0, c->stream));
+  c->scan_timed = true;
   for (uint32_t q0 = 0; q0 < q; q0 += group) {
     const uint32_t qn = std::min(group, q - q0);
     QueryView g = qv;
@@ -427,6 +442,7 @@ static int search_core(zvb200_ctx *c, const void *queries_dev, uint32_t q, uint3
       CU(launch_scan_tile(rv, g, sp, row_begin, row_end, (u64 *)c->part.p, &nparts, s->sm_count, c->stream));
       c->last_kernel = "scan_tile";
     }
+    if (q0 + group >= q) CU(cudaEventRecord(c->ev_scan1, c->stream));
     CU(launch_merge_parts((const u64 *)c->part.p, nparts, qn, k, out_scores_dev + (size_t)q0 * k,
                           out_index_dev + (size_t)q0 * k, c->stream));
   }
