@@ -415,14 +415,17 @@ static int search_core(zvb200_ctx *c, const void *queries_dev, uint32_t q, uint3
   sp.k = k; sp.threshold = threshold; sp.filter = filter_dev;
 
   int which = c->force_kernel;
-  if (which == 0) which = (q <= 4 || !scan_tile_supports(k)) ? 1 : 2;
-  if (which == 3) return set_err(ZVB200_ERR_UNSUPPORTED, "tcgen05 scan not built yet");
+  const bool mma_ok = scan_mma_supports(rv, k);
+  if (which == 0) which = (q <= 4) ? 1 : (q >= 32 && mma_ok) ? 3 : scan_tile_supports(k) ? 2 : 1;
+  if (which == 3 && !mma_ok) return set_err(ZVB200_ERR_UNSUPPORTED, "tcgen05 scan: fp16 InnerProduct/Cosine, k <= 128 only");
   if (which == 2 && !scan_tile_supports(k)) which = 1;
-  const size_t maxparts = which == 1 ? scan_gemv_max_parts(s->sm_count) : scan_tile_max_parts(s->sm_count);
+  const size_t maxparts = which == 1 ? scan_gemv_max_parts(s->sm_count)
+                          : which == 2 ? scan_tile_max_parts(s->sm_count) : scan_mma_max_parts(s->sm_count);
   // bound the partial-list scratch to 256 MiB: process the queries in groups
   const size_t per_query = maxparts * (size_t)k * sizeof(u64);
   uint32_t group = (uint32_t)std::max<size_t>(1, ((size_t)256 << 20) / per_query);
-  if (group >= 64) group &= ~63u; else if (group >= 4) group &= ~3u;
+  if (which == 3) group = std::min<uint32_t>(group, (uint32_t)s->sm_count * 128u);
+  if (group >= 128) group &= ~127u; else if (group >= 64) group &= ~63u; else if (group >= 4) group &= ~3u;
   group = std::min(group, q);
   CU(c->part.ensure((size_t)group * per_query));
   CU(cudaEventRecord(c->ev_scan0, c->stream));
@@ -438,9 +441,12 @@ static int search_core(zvb200_ctx *c, const void *queries_dev, uint32_t q, uint3
     if (which == 1) {
       CU(launch_scan_gemv(rv, g, sp, row_begin, row_end, (u64 *)c->part.p, &nparts, s->sm_count, c->stream));
       c->last_kernel = "scan_gemv";
-    } else {
+    } else if (which == 2) {
       CU(launch_scan_tile(rv, g, sp, row_begin, row_end, (u64 *)c->part.p, &nparts, s->sm_count, c->stream));
       c->last_kernel = "scan_tile";
+    } else {
+      CU(launch_scan_mma(rv, g, sp, row_begin, row_end, (u64 *)c->part.p, &nparts, s->sm_count, c->stream));
+      c->last_kernel = "scan_mma";
     }
     if (q0 + group >= q) CU(cudaEventRecord(c->ev_scan1, c->stream));
     CU(launch_merge_parts((const u64 *)c->part.p, nparts, qn, k, out_scores_dev + (size_t)q0 * k,

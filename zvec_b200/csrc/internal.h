@@ -57,6 +57,13 @@ cudaError_t launch_scan_tile(const RowsView &rv, const QueryView &qv, const Sear
                              int sm_count, cudaStream_t st);
 size_t scan_tile_max_parts(int sm_count);
 bool scan_tile_supports(uint32_t k);
+// K2: tcgen05/TMEM contraction (fp16 stores, InnerProduct / Cosine), thread-per-query top-k
+// epilogue; at most sm_count query tiles of 128 per launch.
+cudaError_t launch_scan_mma(const RowsView &rv, const QueryView &qv, const SearchParams &sp,
+                            uint64_t row_begin, uint64_t row_end, u64 *part, uint32_t *nparts,
+                            int sm_count, cudaStream_t st);
+size_t scan_mma_max_parts(int sm_count);
+bool scan_mma_supports(const RowsView &rv, uint32_t k);
 // queries (stored layout, device) -> compute layout
 cudaError_t launch_prep_queries(const RowsView &rv, const void *queries_dev, uint32_t q,
                                 uint32_t elem_bytes, float *qf32, uint8_t *qraw, float4 *qtails,

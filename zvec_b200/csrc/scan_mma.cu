@@ -1,0 +1,474 @@
+// K2 — tcgen05 / TMEM contraction with a fused thread-per-query top-k epilogue
+// (large query batches, fp16 stores).
+//
+// Replaces FlatSearcherContext::batch_search_* (src/core/algorithm/flat/
+// flat_searcher_context.h:681-752,847-921): the XxxMatrix<Float16,32,N> tile calls
+// (inner_product_matrix_fp16.cc:492,547) and the 32*N heap inserts per tile
+// (batch_enqueue_nofilter, flat_searcher_context.h:236-261).
+//
+// Shape of the contraction (one CTA, one SM):
+//   A = 128 queries  x 64 halves  (UMMA M = 128 -> the 128 TMEM lanes)
+//   B =  BN rows     x 64 halves  (UMMA N = 256 stored rows per tile)
+//   D[query][row] accumulates in TMEM (fp32), two tiles deep (2 x 256 columns = all of TMEM)
+// Both operands are K-major, staged by TMA into 128-byte-swizzled shared memory; one
+// elected thread issues tcgen05.mma; four epilogue warps read the accumulator with
+// tcgen05.ld (32x32b: one TMEM lane = one query per thread, 32 rows per load), so every
+// thread filters ITS query's scores against ITS running k-th best held in a register.
+// Survivors go to a private queue in shared memory and are merged into the query's sorted
+// list by the owning warp (sort32 + rank merge, in place).  The score matrix never leaves
+// the SM; per CTA only 128 x k keys go back to HBM.
+//
+// CTAs are persistent: CTA c works on query tile c % QT for a contiguous range of row
+// tiles, and the QT CTAs of a group walk the SAME rows at the same time so that HBM sees
+// every stored byte once per batch (the other QT-1 reads hit L2).
+#include <cuda.h>
+
+#include "internal.h"
+#include "topk.cuh"
+
+namespace zvb {
+
+namespace {
+
+constexpr int kQM = 128;       // queries per CTA tile
+constexpr int kBK = 64;        // halves per k-block (128 B = one swizzle row)
+constexpr int kBN = 256;       // stored rows per tile
+constexpr int kThreads = 256;  // warp 0 TMA, 1 MMA, 2 TMEM alloc, 3 idle, 4-7 epilogue
+constexpr uint32_t kStageA = kQM * kBK * 2;
+constexpr uint32_t kStageB = kBN * kBK * 2;
+constexpr uint32_t kStage = kStageA + kStageB;
+constexpr uint32_t kTmemCols = 512;
+constexpr unsigned FULL = 0xffffffffu;
+
+struct MmaArgs {
+  uint32_t nq;          // queries of this launch
+  uint32_t qtiles;      // ceil(nq / 128)
+  uint32_t groups;      // row-range groups (= partial lists per query)
+  uint32_t ntiles;      // row tiles of kBN
+  uint32_t nkb;         // k-blocks of 64 halves
+  uint32_t k, qc, nstage;
+  uint32_t row_begin, row_end;  // global row numbers (tensor map B starts at row_begin)
+  int mode;             // 0: s = -dot (InnerProduct), 1: s = 1 - dot (Cosine)
+  float threshold;
+  const uint32_t *drop, *filter;
+  u64 *part;            // [nq][groups][k]
+};
+
+// ---- PTX wrappers -----------------------------------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void *p) {
+  return (uint32_t)__cvta_generic_to_shared(p);
+}
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ uint32_t mbar_try_wait(uint32_t bar, uint32_t parity) {
+  uint32_t ok;
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+      "selp.u32 %0, 1, 0, p;\n\t}"
+      : "=r"(ok)
+      : "r"(bar), "r"(parity)
+      : "memory");
+  return ok;
+}
+// A wait that can never hang the GPU: a pipeline bug traps after ~2 s instead of spinning.
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+  if (mbar_try_wait(bar, parity)) return;
+  const long long t0 = clock64();
+  uint32_t spins = 0;
+  while (!mbar_try_wait(bar, parity)) {
+    if ((++spins & 1023u) == 0 && clock64() - t0 > 4000000000ll) __trap();
+  }
+}
+__device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap *tm, uint32_t bar, int c0, int c1) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+      ::"r"(dst), "l"(tm), "r"(bar), "r"(c0), "r"(c1)
+      : "memory");
+}
+__device__ __forceinline__ void tma_load_2d_hint(uint32_t dst, const CUtensorMap *tm, uint32_t bar, int c0, int c1,
+                                                 uint64_t hint) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1, {%3, "
+      "%4}], [%2], %5;" ::"r"(dst), "l"(tm), "r"(bar), "r"(c0), "r"(c1), "l"(hint)
+      : "memory");
+}
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void umma_f16(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc, uint32_t idesc,
+                                         uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}" ::"r"(d_tmem), "l"(adesc), "l"(bdesc),
+      "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+__device__ __forceinline__ void umma_commit(uint32_t bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&v)[32]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+      "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+      : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
+        "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]),
+        "=r"(v[16]), "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]),
+        "=r"(v[24]), "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
+      : "r"(taddr)
+      : "memory");
+}
+__device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+
+// Shared-memory matrix descriptor, K-major, 128-byte swizzle: 8-row groups are 1024 B apart
+// (SBO), one swizzle atom along K (LBO unused), descriptor version 1 (sm_100).
+__device__ __forceinline__ uint64_t make_desc_sw128(uint32_t saddr) {
+  uint64_t d = (uint64_t)((saddr & 0x3ffffu) >> 4);
+  d |= (uint64_t)(1024u >> 4) << 32;
+  d |= (uint64_t)1 << 46;
+  d |= (uint64_t)2 << 61;
+  return d;
+}
+// Instruction descriptor, kind::f16: fp16 x fp16 -> fp32, A and B K-major.
+__host__ __device__ constexpr uint32_t make_idesc_f16(int M, int N) {
+  return (1u << 4) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
+}
+
+__device__ __forceinline__ bool bit_set(const uint32_t *bm, uint32_t i) { return (bm[i >> 5] >> (i & 31)) & 1u; }
+
+// Merge m (<= 32) unsorted keys Q[0..m) into the sorted list L[0..cnt) of capacity k, in
+// place; returns the new count, *tau = new k-th best (kMaxKey while the list is not full).
+// Warp-collective; scr = 32 u64 of scratch owned by this warp.
+__device__ __forceinline__ int merge_inplace(u64 *L, int cnt, const u64 *Q, int m, int k, u64 *scr, int lane,
+                                             u64 *tau) {
+  u64 v = lane < m ? Q[lane] : kMaxKey;
+  v = warp_sort32(v);
+  scr[lane] = v;
+  __syncwarp();
+  u64 e[4];
+  int np[4];
+#pragma unroll
+  for (int t = 0; t < 4; ++t) {
+    const int i = lane + 32 * t;
+    np[t] = k;
+    e[t] = 0;
+    if (i < cnt) {
+      e[t] = L[i];
+      int c = 0;
+#pragma unroll
+      for (int s = 16; s > 0; s >>= 1)
+        if (scr[c + s - 1] < e[t]) c += s;
+      if (scr[c] < e[t]) ++c;
+      np[t] = i + c;
+    }
+  }
+  int npc = k;
+  if (lane < m) {
+    int lo = 0, hi = cnt;  // list entries < v
+    while (lo < hi) {
+      const int mid = (lo + hi) >> 1;
+      if (L[mid] < v) lo = mid + 1; else hi = mid;
+    }
+    npc = lane + lo;
+  }
+  __syncwarp();
+#pragma unroll
+  for (int t = 0; t < 4; ++t)
+    if (np[t] < k) L[np[t]] = e[t];
+  if (npc < k) L[npc] = v;
+  __syncwarp();
+  const int nc = min(cnt + m, k);
+  *tau = nc == k ? L[k - 1] : kMaxKey;
+  return nc;
+}
+
+__global__ void __launch_bounds__(kThreads, 1)
+scan_mma_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmX, const MmaArgs a) {
+  extern __shared__ uint8_t smem_raw[];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t cta = blockIdx.x;
+  if (cta >= a.groups * a.qtiles) return;
+  const uint32_t qt = cta % a.qtiles, grp = cta / a.qtiles;
+  const uint32_t q0 = qt * kQM;
+  // balanced contiguous tile ranges per group
+  const uint32_t t_begin = (uint32_t)(((uint64_t)a.ntiles * grp) / a.groups);
+  const uint32_t t_end = (uint32_t)(((uint64_t)a.ntiles * (grp + 1)) / a.groups);
+  const uint32_t ntl = t_end - t_begin;
+
+  // ---- shared memory carve-up (stage buffers need 1024-B alignment for the 128-B swizzle)
+  const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  uint8_t *sbase = smem_raw + (base - smem_u32(smem_raw));
+  const uint32_t k = a.k, qc = a.qc, nstage = a.nstage;
+  u64 *lists = reinterpret_cast<u64 *>(sbase + (size_t)nstage * kStage);      // [128][k]
+  u64 *queues = lists + (size_t)kQM * k;                                      // [128][qc+1]
+  u64 *scratch = queues + (size_t)kQM * (qc + 1);                             // [4][32]
+  uint64_t *bars = reinterpret_cast<uint64_t *>(scratch + 4 * 32);            // full[ns] empty[ns] tfull[2] tempty[2]
+  uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + 2 * nstage + 4);
+  const uint32_t bar_full = smem_u32(bars), bar_empty = bar_full + 8 * nstage;
+  const uint32_t bar_tfull = bar_empty + 8 * nstage, bar_tempty = bar_tfull + 16;
+
+  if (warp == 0 && lane == 0) {
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&tmQ) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&tmX) : "memory");
+  }
+  if (warp == 1 && lane == 0) {
+    for (uint32_t s = 0; s < nstage; ++s) {
+      mbar_init(bar_full + 8 * s, 1);
+      mbar_init(bar_empty + 8 * s, 1);
+    }
+    for (uint32_t s = 0; s < 2; ++s) {
+      mbar_init(bar_tfull + 8 * s, 1);
+      mbar_init(bar_tempty + 8 * s, 4);  // one arrival per epilogue warp
+    }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 2) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)),
+                 "r"(kTmemCols)
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    // ================= TMA producer =================
+    if (lane == 0) {
+      uint32_t stage = 0, phase = 0;
+      for (uint32_t t = 0; t < ntl; ++t) {
+        const int row_c = (int)((t_begin + t) * kBN);  // row coordinate inside tensor map X
+        for (uint32_t kb = 0; kb < a.nkb; ++kb) {
+          mbar_wait(bar_empty + 8 * stage, phase ^ 1);
+          const uint32_t sa = base + stage * kStage, sb = sa + kStageA;
+          mbar_expect_tx(bar_full + 8 * stage, kStage);
+          tma_load_2d_hint(sa, &tmQ, bar_full + 8 * stage, (int)(kb * kBK), (int)q0, 0x14F0000000000000ull);
+          tma_load_2d(sb, &tmX, bar_full + 8 * stage, (int)(kb * kBK), row_c);
+          if (++stage == nstage) { stage = 0; phase ^= 1; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ================= MMA issuer =================
+    if (lane == 0) {
+      constexpr uint32_t idesc = make_idesc_f16(kQM, kBN);
+      uint32_t stage = 0, phase = 0;
+      for (uint32_t t = 0; t < ntl; ++t) {
+        const uint32_t as = t & 1, aphase = (t >> 1) & 1;
+        mbar_wait(bar_tempty + 8 * as, aphase ^ 1);
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + as * kBN;
+        for (uint32_t kb = 0; kb < a.nkb; ++kb) {
+          mbar_wait(bar_full + 8 * stage, phase);
+          tc_fence_after();
+          const uint32_t sa = base + stage * kStage, sb = sa + kStageA;
+          const uint64_t da = make_desc_sw128(sa), db = make_desc_sw128(sb);
+#pragma unroll
+          for (uint32_t kk = 0; kk < kBK / 16; ++kk)
+            umma_f16(d_tmem, da + 2 * kk, db + 2 * kk, idesc, (kb | kk) != 0);
+          umma_commit(bar_empty + 8 * stage);  // frees the stage when these MMAs retire
+          if (++stage == nstage) { stage = 0; phase ^= 1; }
+        }
+        umma_commit(bar_tfull + 8 * as);       // accumulator tile complete
+      }
+    }
+  } else if (warp >= 4) {
+    // ================= epilogue: thread-per-query filter + warp-owned top-k =================
+    const int ew = warp - 4;
+    const int slot = ew * 32 + lane;
+    const bool qvalid = q0 + slot < a.nq;
+    u64 *myqueue = queues + (size_t)slot * (qc + 1);
+    u64 *scr = scratch + ew * 32;
+    const int mode = a.mode;
+    int qn = 0, cnt = 0;
+    u64 tau_key = kMaxKey;
+    // fast filter on the raw dot product: pass iff dot >= dthr (conservative for cosine)
+    auto dthr_of = [&](float tau_f) -> float {
+      if (!qvalid) return __int_as_float(0x7f800000);
+      if (mode == 0) return -tau_f;
+      const float t = 1.0f - tau_f;
+      return t - (fabsf(t) + fabsf(tau_f) + 1.0f) * 2.4e-7f;
+    };
+    float dthr = dthr_of(a.threshold);
+
+    auto flush = [&](int min_count) {
+      unsigned mask = __ballot_sync(FULL, qn >= min_count && qn > 0);
+      while (mask) {
+        const int b = __ffs(mask) - 1;
+        mask &= mask - 1;
+        const int m = __shfl_sync(FULL, qn, b), c = __shfl_sync(FULL, cnt, b);
+        u64 tau;
+        const int nc = merge_inplace(lists + (size_t)(ew * 32 + b) * k, c, queues + (size_t)(ew * 32 + b) * (qc + 1),
+                                     m, (int)k, scr, lane, &tau);
+        if (lane == b) {
+          cnt = nc; qn = 0; tau_key = tau;
+          if (nc == (int)k) dthr = dthr_of(fminf(a.threshold, unorder_f32((uint32_t)(tau >> 32))));
+        }
+      }
+    };
+
+    for (uint32_t t = 0; t < ntl; ++t) {
+      const uint32_t as = t & 1, aphase = (t >> 1) & 1;
+      const uint32_t row0 = a.row_begin + (t_begin + t) * kBN;
+      mbar_wait(bar_tfull + 8 * as, aphase);
+      tc_fence_after();
+      const uint32_t taddr = tmem_base + ((uint32_t)(ew * 32) << 16) + as * kBN;
+#pragma unroll 1
+      for (int c0 = 0; c0 < kBN; c0 += 32) {
+        uint32_t v[32];
+        tmem_ld32(taddr + c0, v);
+        tmem_ld_wait();
+        float mx = __uint_as_float(v[0]);
+#pragma unroll
+        for (int j = 1; j < 32; ++j) mx = fmaxf(mx, __uint_as_float(v[j]));
+        const bool hit = mx >= dthr;
+        if (__any_sync(FULL, hit)) {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) {
+            const float dv = __uint_as_float(v[j]);
+            bool p = hit && dv >= dthr;
+            if (__any_sync(FULL, p)) {
+              const float s = mode == 0 ? -dv : 1.0f - dv;
+              const uint32_t row = row0 + c0 + j;
+              const u64 key = pack_key(s, row);
+              p = p && s <= a.threshold && key < tau_key && row < a.row_end;
+              if (p && a.drop) p = !bit_set(a.drop, row);
+              if (p && a.filter) p = !bit_set(a.filter, row);
+              if (__any_sync(FULL, p && qn == (int)qc)) {
+                flush(1);
+                p = p && key < tau_key;
+              }
+              if (p) myqueue[qn++] = key;
+            }
+          }
+        }
+      }
+      // accumulator stage drained: hand it back to the MMA warp
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(bar_tempty + 8 * as);
+      flush((int)(qc + 1) / 2);
+    }
+    flush(1);
+    // write this CTA's partial lists: part[q][grp][0..k)
+    for (int b = 0; b < 32; ++b) {
+      const uint32_t q = q0 + ew * 32 + b;
+      if (q >= a.nq) break;
+      const int c = __shfl_sync(FULL, cnt, b);
+      const u64 *L = lists + (size_t)(ew * 32 + b) * k;
+      u64 *dst = a.part + ((size_t)q * a.groups + grp) * k;
+      for (int i = lane; i < (int)k; i += 32) dst[i] = i < c ? L[i] : kMaxKey;
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 2) {
+    tc_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(kTmemCols) : "memory");
+  }
+}
+
+// ---- host side ---------------------------------------------------------------------------
+typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *,
+                                  const cuuint64_t *, const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+EncodeTiledFn encode_fn() {
+  static EncodeTiledFn fn = [] {
+    void *p = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qres) != cudaSuccess ||
+        qres != cudaDriverEntryPointSuccess)
+      p = nullptr;
+    return (EncodeTiledFn)p;
+  }();
+  return fn;
+}
+
+// 2-D fp16 tensor map over `rows` rows of `d` halves, `stride` bytes apart; box = 64 x box_rows,
+// 128-byte swizzle; out-of-range elements read as zero (ragged d and the last row tile).
+bool make_map(CUtensorMap *tm, const void *ptr, uint32_t d, uint64_t rows, uint32_t stride, uint32_t box_rows) {
+  EncodeTiledFn fn = encode_fn();
+  if (!fn) return false;
+  cuuint64_t dims[2] = {d, rows};
+  cuuint64_t strides[1] = {stride};
+  cuuint32_t box[2] = {(cuuint32_t)kBK, box_rows};
+  cuuint32_t estr[2] = {1, 1};
+  return fn(tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, const_cast<void *>(ptr), dims, strides, box, estr,
+            CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+            CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
+constexpr size_t kSmemMax = 232448;  // 227 KB
+
+// stages / queue depth for a given k; false when the lists do not fit next to 2 stages
+bool mma_config(uint32_t k, uint32_t *nstage, uint32_t *qc, size_t *smem) {
+  for (uint32_t ns = 4; ns >= 2; --ns) {
+    for (uint32_t q : {32u, 16u}) {
+      if (ns == 4 && q == 32u) continue;  // 4 stages leave room for the short queue only
+      const size_t need = 1024 + (size_t)ns * kStage + (size_t)kQM * k * 8 + (size_t)kQM * (q + 1) * 8 + 4 * 32 * 8 +
+                          (2 * ns + 4) * 8 + 16;
+      if (need <= kSmemMax) { *nstage = ns; *qc = q; *smem = need; return true; }
+    }
+  }
+  return false;
+}
+
+}  // namespace
+
+bool scan_mma_supports(const RowsView &rv, uint32_t k) {
+  uint32_t ns, qc; size_t smem;
+  if (rv.dtype != ZVB200_DT_FP16) return false;
+  if (rv.metric != ZVB200_METRIC_IP && rv.metric != ZVB200_METRIC_COSINE) return false;
+  if (k > 128) return false;
+  return mma_config(k, &ns, &qc, &smem) && encode_fn() != nullptr;
+}
+
+size_t scan_mma_max_parts(int sm_count) { return (size_t)sm_count; }
+
+cudaError_t launch_scan_mma(const RowsView &rv, const QueryView &qv, const SearchParams &sp,
+                            uint64_t row_begin, uint64_t row_end, u64 *part, uint32_t *nparts,
+                            int sm_count, cudaStream_t st) {
+  uint32_t ns, qc; size_t smem;
+  if (!mma_config(sp.k, &ns, &qc, &smem)) return cudaErrorInvalidValue;
+  const uint64_t nrows = row_end > row_begin ? row_end - row_begin : 0;
+  MmaArgs a;
+  a.nq = qv.q;
+  a.qtiles = (qv.q + kQM - 1) / kQM;
+  if ((int)a.qtiles > sm_count) return cudaErrorInvalidValue;  // caller splits the batch
+  a.ntiles = (uint32_t)((nrows + kBN - 1) / kBN);
+  a.groups = std::max<uint32_t>(1, std::min<uint32_t>((uint32_t)sm_count / a.qtiles, std::max<uint32_t>(a.ntiles, 1)));
+  a.nkb = (rv.d + kBK - 1) / kBK;
+  a.k = sp.k; a.qc = qc; a.nstage = ns;
+  a.row_begin = (uint32_t)row_begin; a.row_end = (uint32_t)row_end;
+  a.mode = rv.metric == ZVB200_METRIC_IP ? 0 : 1;
+  a.threshold = sp.threshold;
+  a.drop = rv.drop; a.filter = sp.filter;
+  a.part = part;
+  *nparts = a.groups;
+  CUtensorMap tmQ, tmX;
+  if (!make_map(&tmQ, qv.qraw, rv.d, qv.q, rv.row_stride, kQM)) return cudaErrorInvalidValue;
+  if (!make_map(&tmX, rv.rows + row_begin * rv.row_stride, rv.d, std::max<uint64_t>(nrows, 1), rv.row_stride, kBN))
+    return cudaErrorInvalidValue;
+  cudaError_t e = cudaFuncSetAttribute(scan_mma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  if (e != cudaSuccess) return e;
+  if (nrows == 0) {
+    // nothing to scan: every partial list is empty
+    return cudaMemsetAsync(part, 0xff, (size_t)qv.q * a.groups * sp.k * sizeof(u64), st);
+  }
+  scan_mma_kernel<<<a.groups * a.qtiles, kThreads, smem, st>>>(tmQ, tmX, a);
+  count_launch();
+  return cudaGetLastError();
+}
+
+}  // namespace zvb
