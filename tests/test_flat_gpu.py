@@ -256,7 +256,7 @@ def test_mma_kernel_ragged_row_counts(n):
     run_case("fp16_ip", n, 48, 33, 10, seed=53 + n, kernel=3)
 
 
-@pytest.mark.parametrize("k", [1, 10, 16, 17, 48, 49, 100, 110])
+@pytest.mark.parametrize("k", [1, 10, 32, 33, 80, 81, 100, 128])
 def test_mma_kernel_topk_sizes(k):
     run_case("fp16_ip", 6000, 32, 70, k, seed=54 + k, kernel=3)
 

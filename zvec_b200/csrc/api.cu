@@ -96,7 +96,7 @@ struct HostBuf {
 struct zvb200_ctx {
   zvb200_store *s = nullptr;
   cudaStream_t stream = nullptr;
-  DevBuf qin, qf32, qraw, qtails, qnorms, part, out_scores, out_index, filter, misc;
+  DevBuf qin, qf32, qraw, qtails, qnorms, part, out_scores, out_index, filter, misc, gtau;
   HostBuf h_q, h_scores, h_index;
   int force_kernel = 0;
   const char *last_kernel = "none";
@@ -357,7 +357,7 @@ int zvb200_ctx_destroy(zvb200_ctx *c) {
   cudaSetDevice(c->s->device);
   cudaStreamSynchronize(c->stream);
   DevBuf *d[] = {&c->qin, &c->qf32, &c->qraw, &c->qtails, &c->qnorms, &c->part, &c->out_scores,
-                 &c->out_index, &c->filter, &c->misc};
+                 &c->out_index, &c->filter, &c->misc, &c->gtau};
   for (auto b : d) b->release();
   c->h_q.release(); c->h_scores.release(); c->h_index.release();
   if (c->ev_scan0) cudaEventDestroy(c->ev_scan0);
@@ -445,7 +445,9 @@ static int search_core(zvb200_ctx *c, const void *queries_dev, uint32_t q, uint3
       CU(launch_scan_tile(rv, g, sp, row_begin, row_end, (u64 *)c->part.p, &nparts, s->sm_count, c->stream));
       c->last_kernel = "scan_tile";
     } else {
-      CU(launch_scan_mma(rv, g, sp, row_begin, row_end, (u64 *)c->part.p, &nparts, s->sm_count, c->stream));
+      CU(c->gtau.ensure((size_t)qn * sizeof(uint32_t)));
+      CU(launch_scan_mma(rv, g, sp, row_begin, row_end, (u64 *)c->part.p, &nparts, (uint32_t *)c->gtau.p,
+                         s->sm_count, c->stream));
       c->last_kernel = "scan_mma";
     }
     if (q0 + group >= q) CU(cudaEventRecord(c->ev_scan1, c->stream));

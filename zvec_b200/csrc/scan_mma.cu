@@ -22,6 +22,7 @@
 // tiles, and the QT CTAs of a group walk the SAME rows at the same time so that HBM sees
 // every stored byte once per batch (the other QT-1 reads hit L2).
 #include <cuda.h>
+#include <stdlib.h>
 
 #include "internal.h"
 #include "topk.cuh"
@@ -46,12 +47,14 @@ struct MmaArgs {
   uint32_t groups;      // row-range groups (= partial lists per query)
   uint32_t ntiles;      // row tiles of kBN
   uint32_t nkb;         // k-blocks of 64 halves
-  uint32_t k, qc, nstage;
+  uint32_t k, nstage;
   uint32_t row_begin, row_end;  // global row numbers (tensor map B starts at row_begin)
   int mode;             // 0: s = -dot (InnerProduct), 1: s = 1 - dot (Cosine)
   float threshold;
   const uint32_t *drop, *filter;
   u64 *part;            // [nq][groups][k]
+  uint32_t *gtau;       // [nq] ordered image of the best k-th score any CTA has reached so far
+  int dbg;              // ZVB200_MMA_DEBUG probes (perf triage only): 1 no epilogue, 2 no TMA, 4 A only, 8 B only, 16 no slow path
 };
 
 // ---- PTX wrappers -----------------------------------------------------------------------
@@ -144,52 +147,6 @@ __host__ __device__ constexpr uint32_t make_idesc_f16(int M, int N) {
 
 __device__ __forceinline__ bool bit_set(const uint32_t *bm, uint32_t i) { return (bm[i >> 5] >> (i & 31)) & 1u; }
 
-// Merge m (<= 32) unsorted keys Q[0..m) into the sorted list L[0..cnt) of capacity k, in
-// place; returns the new count, *tau = new k-th best (kMaxKey while the list is not full).
-// Warp-collective; scr = 32 u64 of scratch owned by this warp.
-__device__ __forceinline__ int merge_inplace(u64 *L, int cnt, const u64 *Q, int m, int k, u64 *scr, int lane,
-                                             u64 *tau) {
-  u64 v = lane < m ? Q[lane] : kMaxKey;
-  v = warp_sort32(v);
-  scr[lane] = v;
-  __syncwarp();
-  u64 e[4];
-  int np[4];
-#pragma unroll
-  for (int t = 0; t < 4; ++t) {
-    const int i = lane + 32 * t;
-    np[t] = k;
-    e[t] = 0;
-    if (i < cnt) {
-      e[t] = L[i];
-      int c = 0;
-#pragma unroll
-      for (int s = 16; s > 0; s >>= 1)
-        if (scr[c + s - 1] < e[t]) c += s;
-      if (scr[c] < e[t]) ++c;
-      np[t] = i + c;
-    }
-  }
-  int npc = k;
-  if (lane < m) {
-    int lo = 0, hi = cnt;  // list entries < v
-    while (lo < hi) {
-      const int mid = (lo + hi) >> 1;
-      if (L[mid] < v) lo = mid + 1; else hi = mid;
-    }
-    npc = lane + lo;
-  }
-  __syncwarp();
-#pragma unroll
-  for (int t = 0; t < 4; ++t)
-    if (np[t] < k) L[np[t]] = e[t];
-  if (npc < k) L[npc] = v;
-  __syncwarp();
-  const int nc = min(cnt + m, k);
-  *tau = nc == k ? L[k - 1] : kMaxKey;
-  return nc;
-}
-
 __global__ void __launch_bounds__(kThreads, 1)
 scan_mma_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmX, const MmaArgs a) {
   extern __shared__ uint8_t smem_raw[];
@@ -206,11 +163,9 @@ scan_mma_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
   // ---- shared memory carve-up (stage buffers need 1024-B alignment for the 128-B swizzle)
   const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   uint8_t *sbase = smem_raw + (base - smem_u32(smem_raw));
-  const uint32_t k = a.k, qc = a.qc, nstage = a.nstage;
-  u64 *lists = reinterpret_cast<u64 *>(sbase + (size_t)nstage * kStage);      // [128][k]
-  u64 *queues = lists + (size_t)kQM * k;                                      // [128][qc+1]
-  u64 *scratch = queues + (size_t)kQM * (qc + 1);                             // [4][32]
-  uint64_t *bars = reinterpret_cast<uint64_t *>(scratch + 4 * 32);            // full[ns] empty[ns] tfull[2] tempty[2]
+  const uint32_t k = a.k, nstage = a.nstage;
+  u64 *lists = reinterpret_cast<u64 *>(sbase + (size_t)nstage * kStage);      // [k][128]: entry i of query s at i*128+s
+  uint64_t *bars = reinterpret_cast<uint64_t *>(lists + (size_t)kQM * k);     // full[ns] empty[ns] tfull[2] tempty[2]
   uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + 2 * nstage + 4);
   const uint32_t bar_full = smem_u32(bars), bar_empty = bar_full + 8 * nstage;
   const uint32_t bar_tfull = bar_empty + 8 * nstage, bar_tempty = bar_tfull + 16;
@@ -250,6 +205,13 @@ scan_mma_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
         for (uint32_t kb = 0; kb < a.nkb; ++kb) {
           mbar_wait(bar_empty + 8 * stage, phase ^ 1);
           const uint32_t sa = base + stage * kStage, sb = sa + kStageA;
+          if (a.dbg & 14) {
+            if (a.dbg & 2) { mbar_arrive(bar_full + 8 * stage); }
+            else if (a.dbg & 4) { mbar_expect_tx(bar_full + 8 * stage, kStageA); tma_load_2d_hint(sa, &tmQ, bar_full + 8 * stage, (int)(kb * kBK), (int)q0, 0x14F0000000000000ull); }
+            else { mbar_expect_tx(bar_full + 8 * stage, kStageB); tma_load_2d(sb, &tmX, bar_full + 8 * stage, (int)(kb * kBK), row_c); }
+            if (++stage == nstage) { stage = 0; phase ^= 1; }
+            continue;
+          }
           mbar_expect_tx(bar_full + 8 * stage, kStage);
           tma_load_2d_hint(sa, &tmQ, bar_full + 8 * stage, (int)(kb * kBK), (int)q0, 0x14F0000000000000ull);
           tma_load_2d(sb, &tmX, bar_full + 8 * stage, (int)(kb * kBK), row_c);
@@ -282,72 +244,81 @@ scan_mma_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
       }
     }
   } else if (warp >= 4) {
-    // ================= epilogue: thread-per-query filter + warp-owned top-k =================
+    // ================= epilogue: thread-per-query filter + private sorted list =================
     const int ew = warp - 4;
     const int slot = ew * 32 + lane;
     const bool qvalid = q0 + slot < a.nq;
-    u64 *myqueue = queues + (size_t)slot * (qc + 1);
-    u64 *scr = scratch + ew * 32;
+    u64 *L = lists + slot;  // entry i at L[i * kQM]: lanes of a warp hit consecutive banks
     const int mode = a.mode;
-    int qn = 0, cnt = 0;
-    u64 tau_key = kMaxKey;
+    const int K = (int)k;
+    int cnt = 0;
+    // Accept a key only if it is < tau_key.  tau_key = min(threshold gate, this CTA's k-th best,
+    // the best k-th score ANY CTA scanning this query has published in gtau): a row that is not
+    // better than k rows already seen somewhere cannot be in the final top-k, so sharing the
+    // bound only removes work, never results.
+    u64 tau_key = qvalid ? pack_key(a.threshold, 0xffffffffu) : 0ull;
+    uint32_t *my_gtau = a.gtau + (qvalid ? q0 + slot : q0);
     // fast filter on the raw dot product: pass iff dot >= dthr (conservative for cosine)
-    auto dthr_of = [&](float tau_f) -> float {
+    auto dthr_of = [&](u64 tk) -> float {
       if (!qvalid) return __int_as_float(0x7f800000);
+      const float tau_f = unorder_f32((uint32_t)(tk >> 32));
       if (mode == 0) return -tau_f;
       const float t = 1.0f - tau_f;
       return t - (fabsf(t) + fabsf(tau_f) + 1.0f) * 2.4e-7f;
     };
-    float dthr = dthr_of(a.threshold);
-
-    auto flush = [&](int min_count) {
-      unsigned mask = __ballot_sync(FULL, qn >= min_count && qn > 0);
-      while (mask) {
-        const int b = __ffs(mask) - 1;
-        mask &= mask - 1;
-        const int m = __shfl_sync(FULL, qn, b), c = __shfl_sync(FULL, cnt, b);
-        u64 tau;
-        const int nc = merge_inplace(lists + (size_t)(ew * 32 + b) * k, c, queues + (size_t)(ew * 32 + b) * (qc + 1),
-                                     m, (int)k, scr, lane, &tau);
-        if (lane == b) {
-          cnt = nc; qn = 0; tau_key = tau;
-          if (nc == (int)k) dthr = dthr_of(fminf(a.threshold, unorder_f32((uint32_t)(tau >> 32))));
-        }
-      }
-    };
+    float dthr = dthr_of(tau_key);
+    uint32_t g_next = 0xffffffffu;
 
     for (uint32_t t = 0; t < ntl; ++t) {
       const uint32_t as = t & 1, aphase = (t >> 1) & 1;
       const uint32_t row0 = a.row_begin + (t_begin + t) * kBN;
+      {  // the bound other CTAs have reached, read while the previous tile was processed
+        const u64 gk = ((u64)g_next << 32) | 0xffffffffu;
+        if (gk < tau_key) { tau_key = gk; dthr = dthr_of(tau_key); }
+      }
       mbar_wait(bar_tfull + 8 * as, aphase);
       tc_fence_after();
       const uint32_t taddr = tmem_base + ((uint32_t)(ew * 32) << 16) + as * kBN;
 #pragma unroll 1
-      for (int c0 = 0; c0 < kBN; c0 += 32) {
+      for (int c0 = 0; c0 < ((a.dbg & 1) ? 0 : kBN); c0 += 32) {
         uint32_t v[32];
         tmem_ld32(taddr + c0, v);
         tmem_ld_wait();
         float mx = __uint_as_float(v[0]);
 #pragma unroll
         for (int j = 1; j < 32; ++j) mx = fmaxf(mx, __uint_as_float(v[j]));
-        const bool hit = mx >= dthr;
-        if (__any_sync(FULL, hit)) {
+        if (mx >= dthr && !(a.dbg & 16)) {
+          // rare: some of this query's 32 scores may enter its top-k
 #pragma unroll
           for (int j = 0; j < 32; ++j) {
             const float dv = __uint_as_float(v[j]);
-            bool p = hit && dv >= dthr;
-            if (__any_sync(FULL, p)) {
+            if (dv >= dthr) {
               const float s = mode == 0 ? -dv : 1.0f - dv;
               const uint32_t row = row0 + c0 + j;
               const u64 key = pack_key(s, row);
-              p = p && s <= a.threshold && key < tau_key && row < a.row_end;
+              bool p = key < tau_key && row < a.row_end;
               if (p && a.drop) p = !bit_set(a.drop, row);
               if (p && a.filter) p = !bit_set(a.filter, row);
-              if (__any_sync(FULL, p && qn == (int)qc)) {
-                flush(1);
-                p = p && key < tau_key;
+              if (p) {
+                // insertion into the sorted list (ailego Heap::emplace + sort, heap.h:103-115,173-175)
+                int i = cnt < K ? cnt : K - 1;
+                while (i > 0) {
+                  const u64 prev = L[(size_t)(i - 1) * kQM];
+                  if (prev < key) break;
+                  L[(size_t)i * kQM] = prev;
+                  --i;
+                }
+                L[(size_t)i * kQM] = key;
+                if (cnt < K) ++cnt;
+                if (cnt == K) {
+                  const u64 nt = L[(size_t)(K - 1) * kQM];
+                  if (nt < tau_key) {
+                    tau_key = nt;
+                    dthr = dthr_of(nt);
+                    atomicMin(my_gtau, (uint32_t)(nt >> 32));
+                  }
+                }
               }
-              if (p) myqueue[qn++] = key;
             }
           }
         }
@@ -356,17 +327,12 @@ scan_mma_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(bar_tempty + 8 * as);
-      flush((int)(qc + 1) / 2);
+      g_next = *reinterpret_cast<volatile uint32_t *>(my_gtau);
     }
-    flush(1);
     // write this CTA's partial lists: part[q][grp][0..k)
-    for (int b = 0; b < 32; ++b) {
-      const uint32_t q = q0 + ew * 32 + b;
-      if (q >= a.nq) break;
-      const int c = __shfl_sync(FULL, cnt, b);
-      const u64 *L = lists + (size_t)(ew * 32 + b) * k;
-      u64 *dst = a.part + ((size_t)q * a.groups + grp) * k;
-      for (int i = lane; i < (int)k; i += 32) dst[i] = i < c ? L[i] : kMaxKey;
+    if (qvalid) {
+      u64 *dst = a.part + ((size_t)(q0 + slot) * a.groups + grp) * k;
+      for (int i = 0; i < K; ++i) dst[i] = i < cnt ? L[(size_t)i * kQM] : kMaxKey;
     }
   }
 
@@ -411,15 +377,11 @@ bool make_map(CUtensorMap *tm, const void *ptr, uint32_t d, uint64_t rows, uint3
 
 constexpr size_t kSmemMax = 232448;  // 227 KB
 
-// stages / queue depth for a given k; false when the lists do not fit next to 2 stages
-bool mma_config(uint32_t k, uint32_t *nstage, uint32_t *qc, size_t *smem) {
+// pipeline stages that fit next to the 128 x k lists; false when not even 2 stages fit
+bool mma_config(uint32_t k, uint32_t *nstage, size_t *smem) {
   for (uint32_t ns = 4; ns >= 2; --ns) {
-    for (uint32_t q : {32u, 16u}) {
-      if (ns == 4 && q == 32u) continue;  // 4 stages leave room for the short queue only
-      const size_t need = 1024 + (size_t)ns * kStage + (size_t)kQM * k * 8 + (size_t)kQM * (q + 1) * 8 + 4 * 32 * 8 +
-                          (2 * ns + 4) * 8 + 16;
-      if (need <= kSmemMax) { *nstage = ns; *qc = q; *smem = need; return true; }
-    }
+    const size_t need = 1024 + (size_t)ns * kStage + (size_t)kQM * k * 8 + (2 * ns + 4) * 8 + 16;
+    if (need <= kSmemMax) { *nstage = ns; *smem = need; return true; }
   }
   return false;
 }
@@ -427,20 +389,20 @@ bool mma_config(uint32_t k, uint32_t *nstage, uint32_t *qc, size_t *smem) {
 }  // namespace
 
 bool scan_mma_supports(const RowsView &rv, uint32_t k) {
-  uint32_t ns, qc; size_t smem;
+  uint32_t ns; size_t smem;
   if (rv.dtype != ZVB200_DT_FP16) return false;
   if (rv.metric != ZVB200_METRIC_IP && rv.metric != ZVB200_METRIC_COSINE) return false;
   if (k > 128) return false;
-  return mma_config(k, &ns, &qc, &smem) && encode_fn() != nullptr;
+  return mma_config(k, &ns, &smem) && encode_fn() != nullptr;
 }
 
 size_t scan_mma_max_parts(int sm_count) { return (size_t)sm_count; }
 
 cudaError_t launch_scan_mma(const RowsView &rv, const QueryView &qv, const SearchParams &sp,
                             uint64_t row_begin, uint64_t row_end, u64 *part, uint32_t *nparts,
-                            int sm_count, cudaStream_t st) {
-  uint32_t ns, qc; size_t smem;
-  if (!mma_config(sp.k, &ns, &qc, &smem)) return cudaErrorInvalidValue;
+                            uint32_t *gtau, int sm_count, cudaStream_t st) {
+  uint32_t ns; size_t smem;
+  if (!mma_config(sp.k, &ns, &smem)) return cudaErrorInvalidValue;
   const uint64_t nrows = row_end > row_begin ? row_end - row_begin : 0;
   MmaArgs a;
   a.nq = qv.q;
@@ -449,12 +411,17 @@ cudaError_t launch_scan_mma(const RowsView &rv, const QueryView &qv, const Searc
   a.ntiles = (uint32_t)((nrows + kBN - 1) / kBN);
   a.groups = std::max<uint32_t>(1, std::min<uint32_t>((uint32_t)sm_count / a.qtiles, std::max<uint32_t>(a.ntiles, 1)));
   a.nkb = (rv.d + kBK - 1) / kBK;
-  a.k = sp.k; a.qc = qc; a.nstage = ns;
+  a.k = sp.k; a.nstage = ns;
   a.row_begin = (uint32_t)row_begin; a.row_end = (uint32_t)row_end;
   a.mode = rv.metric == ZVB200_METRIC_IP ? 0 : 1;
   a.threshold = sp.threshold;
   a.drop = rv.drop; a.filter = sp.filter;
   a.part = part;
+  a.gtau = gtau;
+  {
+    static const int dbg = [] { const char *e = getenv("ZVB200_MMA_DEBUG"); return e ? atoi(e) : 0; }();
+    a.dbg = dbg;
+  }
   *nparts = a.groups;
   CUtensorMap tmQ, tmX;
   if (!make_map(&tmQ, qv.qraw, rv.d, qv.q, rv.row_stride, kQM)) return cudaErrorInvalidValue;
@@ -466,6 +433,8 @@ cudaError_t launch_scan_mma(const RowsView &rv, const QueryView &qv, const Searc
     // nothing to scan: every partial list is empty
     return cudaMemsetAsync(part, 0xff, (size_t)qv.q * a.groups * sp.k * sizeof(u64), st);
   }
+  e = cudaMemsetAsync(gtau, 0xff, (size_t)qv.q * sizeof(uint32_t), st);
+  if (e != cudaSuccess) return e;
   scan_mma_kernel<<<a.groups * a.qtiles, kThreads, smem, st>>>(tmQ, tmX, a);
   count_launch();
   return cudaGetLastError();
