@@ -1,0 +1,285 @@
+// zvec index plugin: GpuFlatSearcher — the reference's IndexSearcher interface served by the
+// B200 scan behind include/zvec_b200.h.
+//
+// Host adaptor (C++, ours).  It is compiled against the reference's PUBLIC framework headers
+// (src/include/zvec/core/framework/*.h, used with -I where they lie, never copied) and
+// registered with the reference's own macro INDEX_FACTORY_REGISTER_SEARCHER
+// (src/include/zvec/core/framework/index_factory.h:237-242), so
+//   IndexFactory::CreateSearcher("GpuFlatSearcher")
+// — and, after zvb200_install_overrides(), IndexFactory::CreateSearcher("FlatSearcher") —
+// returns it; it is loaded like any zvec plugin: IndexPlugin::load(path) = dlopen
+// (src/core/framework/index_plugin.cc:20-35).  It mirrors FlatSearcher<32>
+// (src/core/algorithm/flat/flat_searcher.h:33-161, flat_searcher.cc:68-211): same load()
+// checks and error codes, same context contract (topk / filter / threshold / result(i)),
+// results sorted ascending by the internal score with key(), score(), index().
+// Everything that is arithmetic happens on the GPU through the C ABI; there is no CPU scan here.
+#include <zvec/core/framework/index_context.h>
+#include <zvec/core/framework/index_error.h>
+#include <zvec/core/framework/index_factory.h>
+#include <zvec/core/framework/index_helper.h>
+#include <zvec/core/framework/index_meta.h>
+#include <zvec/core/framework/index_searcher.h>
+
+#include <cstring>
+#include <limits>
+#include <mutex>
+#include <string>
+#include <vector>
+
+#include "../include/zvec_b200.h"
+
+namespace zvec {
+namespace core {
+
+namespace {
+
+// segment ids of a Flat index file (src/core/algorithm/flat/flat_utility.h:32-34)
+const std::string kSegKeys("flat.keys");
+const std::string kSegFeatures("flat.features");
+// QuantizedIntegerMetric's origin metric parameter (src/core/metric/quantized_integer_metric.cc:40-60)
+const std::string kOriginMetric("proxima.quantized_integer.metric.origin_metric_name");
+
+// IndexMeta (metric name [+ origin metric], data type) -> ZVB200_METRIC_* ; <0 = unsupported,
+// like InnerProductMetric::init for types it has no kernel for (inner_product_metric.cc:259-281)
+int metric_of(const IndexMeta &meta) {
+  const std::string &m = meta.metric_name();
+  if (m == "SquaredEuclidean") return ZVB200_METRIC_L2SQ;
+  if (m == "Euclidean") return ZVB200_METRIC_L2;
+  if (m == "InnerProduct") return ZVB200_METRIC_IP;
+  if (m == "Cosine") return ZVB200_METRIC_COSINE;
+  if (m == "QuantizedInteger") {
+    std::string o;
+    meta.metric_params().get(kOriginMetric, &o);
+    if (o == "SquaredEuclidean" || o.empty()) return ZVB200_METRIC_QI8_L2SQ;
+    if (o == "InnerProduct") return ZVB200_METRIC_QI8_IP;
+    if (o == "Cosine") return ZVB200_METRIC_QI8_COSINE;
+  }
+  return -1;
+}
+
+int dtype_of(const IndexMeta &meta) {
+  switch (meta.data_type()) {
+    case IndexMeta::DataType::DT_FP16: return ZVB200_DT_FP16;
+    case IndexMeta::DataType::DT_FP32: return ZVB200_DT_FP32;
+    case IndexMeta::DataType::DT_INT8: return ZVB200_DT_INT8;
+    default: return -1;
+  }
+}
+
+}  // namespace
+
+class GpuFlatSearcher;
+
+/*! Search context: FlatSearcherContext's contract (flat_searcher_context.h:187-196,
+ *  index_context.h:57-260) over a zvb200_ctx (CUDA stream + pinned staging + device scratch).
+ */
+class GpuFlatContext : public IndexContext {
+ public:
+  explicit GpuFlatContext(const GpuFlatSearcher *owner) { this->reset(owner); }
+  ~GpuFlatContext() override {
+    if (ctx_) zvb200_ctx_destroy(ctx_);
+  }
+  void set_topk(uint32_t topk) override { topk_ = topk; }
+  uint32_t topk() const override { return topk_; }
+  const IndexDocumentList &result(void) const override { return results_[0]; }
+  const IndexDocumentList &result(size_t i) const override { return results_[i]; }
+  IndexDocumentList *mutable_result(size_t i) override { return &results_[i]; }
+  uint32_t magic(void) const override { return magic_; }
+  void reset(const GpuFlatSearcher *owner);
+  zvb200_ctx *handle() const { return ctx_; }
+  void resize_results(size_t n) {
+    if (results_.size() < n) results_.resize(n);
+  }
+  // scratch reused across searches
+  std::vector<uint64_t> keys;
+  std::vector<float> scores;
+  std::vector<uint32_t> index, counts, bitmap;
+
+ private:
+  uint32_t topk_{0};
+  uint32_t magic_{0};
+  zvb200_ctx *ctx_{nullptr};
+  std::vector<IndexDocumentList> results_{1};
+};
+
+/*! GPU Flat Searcher: IndexSearcher (index_searcher.h:29-54, index_runner.h:404-640) whose
+ *  load() uploads the Flat index file to a device-resident store and whose search_impl()
+ *  is one zvb200_search call.
+ */
+class GpuFlatSearcher : public IndexSearcher {
+ public:
+  GpuFlatSearcher() = default;
+  ~GpuFlatSearcher() override { this->unload(); }
+
+  //! proxima.gpu.device selects the CUDA device (default 0)
+  int init(const ailego::Params &params) override {
+    params_ = params;
+    params.get("proxima.gpu.device", &device_);
+    return 0;
+  }
+  int cleanup(void) override { return this->unload(); }
+
+  //! Mirrors FlatSearcher::load (flat_searcher.cc:68-159): same checks, same error codes.
+  int load(IndexStorage::Pointer cntr, IndexMetric::Pointer measure) override {
+    if (!cntr) return IndexError_InvalidArgument;
+    int rc = IndexHelper::DeserializeFromStorage(cntr.get(), &meta_);
+    if (rc != 0) return rc;
+    if (measure && !measure->is_matched(meta_)) return IndexError_Mismatch;
+    const int metric = metric_of(meta_), dtype = dtype_of(meta_);
+    if (metric < 0 || dtype < 0) return IndexError_Unsupported;
+    auto keys_seg = cntr->get(kSegKeys);
+    auto feat_seg = cntr->get(kSegFeatures);
+    if (!keys_seg || !feat_seg) return IndexError_NoExist;
+    if (keys_seg->data_size() % sizeof(uint64_t) != 0) return IndexError_InvalidLength;
+    const size_t n = keys_seg->data_size() / sizeof(uint64_t);
+    const size_t es = meta_.element_size();
+    if (n * es != feat_seg->data_size()) return IndexError_Mismatch;
+    const uint64_t *keys = nullptr;
+    if (keys_seg->read(0, reinterpret_cast<const void **>(&keys), keys_seg->data_size()) != keys_seg->data_size())
+      return IndexError_ReadData;
+    keys_.assign(keys, keys + n);
+
+    zvb200_store *st = nullptr;
+    rc = zvb200_store_create(device_, dtype, metric, meta_.dimension(), &st);
+    if (rc != 0) return rc;
+    rc = zvb200_store_reserve(st, n);
+    // upload in 64 MiB reads (the reference scans in 4 MiB reads, flat_searcher_context.h:187-196)
+    const bool column = meta_.major_order() == IndexMeta::MO_COLUMN;
+    const size_t rows_per_read = std::max<size_t>(32, ((size_t)64 << 20) / es / 32 * 32);
+    std::vector<char> rowbuf;
+    for (size_t r0 = 0; rc == 0 && r0 < n; r0 += rows_per_read) {
+      const size_t m = std::min(rows_per_read, n - r0);
+      const void *p = nullptr;
+      if (feat_seg->read(r0 * es, &p, m * es) != m * es) { rc = IndexError_ReadData; break; }
+      if (column) {
+        // 32-row tiles interleaved by unit (flat_builder.cc:188-225, matrix_helper.h:24-33);
+        // a final tile of < 32 rows is stored row-major.  Undo it on the host: the store is row-major.
+        rowbuf.resize(m * es);
+        const size_t us = IndexMeta::AlignSizeof(meta_.data_type()), units = es / us;  // flat_builder.h:77-85
+        const char *src = (const char *)p;
+        size_t i = 0;
+        for (; i + 32 <= m; i += 32)
+          for (size_t u = 0; u < units; ++u)
+            for (size_t j = 0; j < 32; ++j)
+              std::memcpy(&rowbuf[(i + j) * es + u * us], src + i * es + (u * 32 + j) * us, us);
+        if (i < m) std::memcpy(&rowbuf[i * es], src + i * es, (m - i) * es);
+        p = rowbuf.data();
+      }
+      rc = zvb200_store_append(st, p, m, keys_.data() + r0);
+    }
+    if (rc == 0) rc = zvb200_store_seal(st);
+    if (rc != 0) { zvb200_store_destroy(st); return rc; }
+    store_ = st;
+    container_ = cntr;
+    magic_ = IndexContext::GenerateMagic();
+    stats_.set_loaded_count(n);
+    return 0;
+  }
+
+  int unload(void) override {
+    if (store_) zvb200_store_destroy(store_);
+    store_ = nullptr;
+    container_ = nullptr;
+    keys_.clear();
+    return 0;
+  }
+
+  int search_impl(const void *query, const IndexQueryMeta &qmeta, Context::Pointer &context) const override {
+    return this->search_impl(query, qmeta, 1, context);
+  }
+
+  //! FlatSearcher::search_impl(query, qmeta, count, ctx) (flat_searcher.cc:186-211)
+  int search_impl(const void *query, const IndexQueryMeta &qmeta, uint32_t count,
+                  Context::Pointer &context) const override {
+    if (!query || !count || !context || !store_) return IndexError_InvalidArgument;
+    if (qmeta.element_size() != meta_.element_size()) return IndexError_Mismatch;
+    auto *ctx = dynamic_cast<GpuFlatContext *>(context.get());
+    if (!ctx) return IndexError_InvalidArgument;
+    if (ctx->magic() != magic_) ctx->reset(this);
+    const uint32_t k = ctx->topk();
+    ctx->resize_results(count);
+    if (k == 0) {
+      for (uint32_t i = 0; i < count; ++i) ctx->mutable_result(i)->clear();
+      return 0;
+    }
+    const size_t n = keys_.size();
+    const uint32_t *bitmap = nullptr;
+    if (ctx->filter().is_valid()) {
+      // IndexFilter: true = drop (flat_searcher_context.h single_enqueue_filter); evaluated
+      // once per row on the host, exactly as often as the reference calls it
+      ctx->bitmap.assign((n + 31) / 32, 0u);
+      for (size_t i = 0; i < n; ++i)
+        if (ctx->filter()(keys_[i])) ctx->bitmap[i >> 5] |= 1u << (i & 31);
+      bitmap = ctx->bitmap.data();
+    }
+    const size_t nres = (size_t)count * k;
+    ctx->keys.resize(nres); ctx->scores.resize(nres); ctx->index.resize(nres); ctx->counts.resize(count);
+    const int rc = zvb200_search(ctx->handle(), query, count, k, ctx->threshold(), bitmap, ctx->keys.data(),
+                                 ctx->scores.data(), ctx->index.data(), ctx->counts.data());
+    if (rc != 0) return rc;
+    for (uint32_t i = 0; i < count; ++i) {
+      IndexDocumentList *out = ctx->mutable_result(i);
+      out->clear();
+      for (uint32_t j = 0; j < ctx->counts[i]; ++j) {
+        const size_t o = (size_t)i * k + j;
+        out->emplace_back(ctx->keys[o], ctx->scores[o], ctx->index[o]);
+      }
+    }
+    return 0;
+  }
+
+  int search_bf_impl(const void *query, const IndexQueryMeta &qmeta, Context::Pointer &context) const override {
+    return this->search_impl(query, qmeta, 1, context);
+  }
+  int search_bf_impl(const void *query, const IndexQueryMeta &qmeta, uint32_t count,
+                     Context::Pointer &context) const override {
+    return this->search_impl(query, qmeta, count, context);
+  }
+
+  Context::Pointer create_context(void) const override {
+    return Context::Pointer(new (std::nothrow) GpuFlatContext(this));
+  }
+  const Stats &stats(void) const override { return stats_; }
+  const IndexMeta &meta(void) const override { return meta_; }
+  const ailego::Params &params(void) const override { return params_; }
+
+  //! IndexRunner::get_vector(key, block): copy one stored row back (reference layout)
+  int get_vector_by_id(uint32_t id, void *out, size_t cap) const {
+    return store_ ? zvb200_store_get_vector(store_, id, out, cap) : IndexError_NoReady;
+  }
+  uint32_t magic(void) const { return magic_; }
+  zvb200_store *store(void) const { return store_; }
+
+ private:
+  ailego::Params params_{};
+  IndexMeta meta_{};
+  Stats stats_{};
+  IndexStorage::Pointer container_{};
+  std::vector<uint64_t> keys_{};
+  zvb200_store *store_{nullptr};
+  uint32_t magic_{0};
+  int device_{0};
+};
+
+void GpuFlatContext::reset(const GpuFlatSearcher *owner) {
+  if (ctx_) zvb200_ctx_destroy(ctx_);
+  ctx_ = nullptr;
+  magic_ = owner->magic();
+  if (owner->store()) zvb200_ctx_create(owner->store(), &ctx_);
+  for (auto &r : results_) r.clear();
+}
+
+INDEX_FACTORY_REGISTER_SEARCHER(GpuFlatSearcher);
+
+}  // namespace core
+}  // namespace zvec
+
+// Route the stock name to the GPU class: Factory::set() is map_[key] = func, so a later
+// registration replaces the earlier one (src/include/zvec/ailego/pattern/factory.h:119-122).
+// After this call core_interface / IVFCentroidIndex / index files whose meta says
+// searcher = "FlatSearcher" reach the GPU path unchanged.
+extern "C" int zvb200_install_overrides(void) {
+  static zvec::ailego::Factory<zvec::core::IndexSearcher>::Register<zvec::core::GpuFlatSearcher> r("FlatSearcher");
+  (void)r;
+  return 0;
+}

@@ -21,6 +21,7 @@
 #include <zvec/core/framework/index_meta.h>
 #include <zvec/core/framework/index_metric.h>
 #include <zvec/core/framework/index_reformer.h>
+#include <zvec/core/framework/index_plugin.h>
 #include <zvec/core/framework/index_searcher.h>
 
 using namespace zvec::core;
@@ -142,7 +143,14 @@ void *zref_index_create(const char *kind, const void *rows, uint64_t n, uint32_t
   ix->metric = IndexFactory::CreateMetric(ix->meta.metric_name());
   if (!ix->metric || ix->metric->init(ix->meta, ix->meta.metric_params()) != 0) { fail(-1, "metric"); return nullptr; }
 
-  std::string k(kind);
+  // kind = "Flat" | "IVF" | "<Builder kind>:<searcher class>" (e.g. "Flat:GpuFlatSearcher" after
+  // zref_load_plugin: the index is built by the reference, searched by a plugin class)
+  std::string k(kind), searcher_name;
+  {
+    size_t c = k.find(':');
+    if (c != std::string::npos) { searcher_name = k.substr(c + 1); k = k.substr(0, c); }
+    else searcher_name = k + "Searcher";
+  }
   static std::atomic<int> seq{0};
   char buf[256];
   snprintf(buf, sizeof buf, "/tmp/zref_%d_%d.index", (int)getpid(), seq++);
@@ -157,7 +165,7 @@ void *zref_index_create(const char *kind, const void *rows, uint64_t n, uint32_t
   r = IndexBuilder::TrainBuildAndDump(builder, holder, dumper);
   if (r != 0) { fail(r, "build"); return nullptr; }
   dumper->close();
-  ix->searcher = IndexFactory::CreateSearcher(k + "Searcher");
+  ix->searcher = IndexFactory::CreateSearcher(searcher_name);
   auto storage = IndexFactory::CreateStorage("MMapFileReadStorage");
   Params sp; parse_params(search_params, &sp);
   if (!ix->searcher || !storage) { fail(-1, "no searcher"); return nullptr; }
@@ -169,6 +177,26 @@ void *zref_index_create(const char *kind, const void *rows, uint64_t n, uint32_t
 }
 
 void zref_index_destroy(void *h) { delete (RefIndex *)h; }
+
+// Load an index plugin with the reference's OWN loader (IndexPluginBroker -> IndexPlugin::load
+// -> dlopen, src/core/framework/index_plugin.cc:20-56), as tools/core/bench.cc:796-803 does
+// for its trailing argv.  Returns 0 or -1 (zref_last_error()).
+int zref_load_plugin(const char *path) {
+  static IndexPluginBroker broker;
+  std::string err;
+  if (!broker.emplace(std::string(path), &err)) return fail(-1, "plugin load: " + err);
+  return 0;
+}
+// 1 if IndexFactory has a searcher class of that name
+int zref_has_searcher(const char *name) { return IndexFactory::HasSearcher(name) ? 1 : 0; }
+
+// Set a key filter on the next searches: drop keys with (key % mod) == rem (mod = 0: no filter).
+// Exercises IndexContext::set_filter (index_context.h) through whichever searcher is loaded.
+static thread_local uint64_t g_fmod = 0, g_frem = 0;
+static thread_local float g_threshold = 0.f;
+static thread_local int g_has_threshold = 0;
+void zref_set_filter(uint64_t mod, uint64_t rem) { g_fmod = mod; g_frem = rem; }
+void zref_set_threshold(int on, float v) { g_has_threshold = on; g_threshold = v; }
 
 // Stored (post-converter) layout: dtype, dimension, element bytes, metric name.
 int zref_index_info(void *h, int *dtype, uint32_t *dim, uint32_t *elem, uint64_t *n,
@@ -234,9 +262,14 @@ int zref_index_search(void *h, const void *queries, uint32_t count, uint32_t top
   uint32_t nb = (count + batch - 1) / batch;
   std::atomic<uint32_t> next{0};
   std::atomic<int> err{0};
+  const uint64_t fmod = g_fmod, frem = g_frem;
+  const int has_thr = g_has_threshold;
+  const float thr = g_threshold;
   auto work = [&]() {
     auto ctx = ix->searcher->create_context();
     ctx->set_topk(topk);
+    if (fmod) ctx->set_filter([fmod, frem](uint64_t key) { return key % fmod == frem; });
+    if (has_thr) ctx->set_threshold(thr);
     for (;;) {
       uint32_t b = next.fetch_add(1);
       if (b >= nb) break;

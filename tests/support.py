@@ -74,7 +74,9 @@ def ref():
         for c in cands:
             p = os.path.join(ORACLE_DIR, "_ref", c)
             if os.path.exists(p):
-                L = C.CDLL(p)
+                # RTLD_GLOBAL: a plugin dlopen'ed later resolves the framework symbols from here, as it
+                # would from a zvec host binary
+                L = C.CDLL(p, mode=C.RTLD_GLOBAL)
                 L.zref_index_create.restype = C.c_void_p
                 L.zref_index_create.argtypes = [C.c_char_p, C.c_void_p, C.c_uint64, C.c_uint32, C.c_int,
                                                 C.c_char_p, C.c_char_p, C.c_int, C.c_char_p, C.c_char_p]
@@ -88,10 +90,31 @@ def ref():
                 L.zref_index_distances.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p]
                 L.zref_metric_distances.argtypes = [C.c_char_p, C.c_char_p, C.c_int, C.c_uint32, C.c_void_p,
                                                     C.c_uint64, C.c_void_p, C.c_void_p]
+                L.zref_load_plugin.argtypes = [C.c_char_p]
+                L.zref_has_searcher.argtypes = [C.c_char_p]
+                L.zref_set_filter.argtypes = [C.c_uint64, C.c_uint64]
+                L.zref_set_threshold.argtypes = [C.c_int, C.c_float]
                 L._name = c
                 _ref = L
                 break
     return _ref
+
+
+PLUGIN = os.path.join(ROOT, "integration", "_build", "libzvec_b200_plugin.so")
+_plugin_loaded = False
+
+
+def load_plugin():
+    """Load the GPU plugin through the reference's own IndexPluginBroker; False if unavailable."""
+    global _plugin_loaded
+    if _plugin_loaded:
+        return True
+    if ref() is None or not os.path.exists(PLUGIN):
+        return False
+    if ref().zref_load_plugin(PLUGIN.encode()) != 0:
+        raise RuntimeError(ref().zref_last_error().decode())
+    _plugin_loaded = True
+    return True
 
 
 class RefIndex:
