@@ -223,8 +223,8 @@ def run_ours(args):
     pk = peaks()
 
     # ---- the shard: rows [lo, hi) of the global matrix, generated chunk by chunk on the device
-    per = (args.rows + world - 1) // world
-    lo, hi = rank * per, min(args.rows, (rank + 1) * per)
+    from zvec_b200 import sharding
+    lo, hi = sharding.shard_bounds(args.rows, world)[rank]
     st = z.Store(z.DT_FP16, z.METRIC_IP, DIM, device=local)
     st.reserve(hi - lo)
     g = torch.Generator(device=dev)
@@ -259,7 +259,7 @@ def run_ours(args):
     fin_r = torch.empty((B, k), dtype=torch.int64, device=dev)
     h_s = torch.empty((B, k), dtype=torch.float32).pin_memory()
     h_r = torch.empty((B, k), dtype=torch.int64).pin_memory()
-    bases = [min(args.rows, r * per) for r in range(world)]
+    bases = sharding.shard_bases(args.rows, world)
 
     def step(q):
         """one batch of q queries already in HBM -> final top-k in HBM (all on ctx's stream)"""
