@@ -23,6 +23,9 @@
 #include <zvec/core/framework/index_reformer.h>
 #include <zvec/core/framework/index_plugin.h>
 #include <zvec/core/framework/index_searcher.h>
+#include <zvec/core/framework/index_segment_storage.h>
+#include "ivf/ivf_entity.h"
+#include "ivf/ivf_index_format.h"
 
 using namespace zvec::core;
 using zvec::ailego::Params;
@@ -303,6 +306,71 @@ int zref_index_search(void *h, const void *queries, uint32_t count, uint32_t top
     for (auto &t : ts) t.join();
   }
   return err.load();
+}
+
+// Export an IVF index the reference built (what a device store must ingest, via the
+// reference's own IVFEntity reader, ivf_entity.h:89-170): centroids (row cid = centroid cid, in
+// the centroid index's stored layout), posting lists as CSR (list_offsets[nlist+1]), rows in
+// list order (stored layout, row-major) and their keys.  Call with NULL buffers for the sizes.
+int zref_ivf_export(void *h, uint32_t *nlist, uint64_t *nrows, uint32_t *elem, uint32_t *c_elem,
+                    int *c_dtype, uint32_t *c_dim, char *c_metric, uint32_t c_metric_cap,
+                    void *centroids, uint64_t *list_offsets, void *rows, uint64_t *keys) {
+  auto ix = (RefIndex *)h;
+  auto storage = IndexFactory::CreateStorage("MMapFileReadStorage");
+  if (!storage || storage->open(ix->path, false) != 0) return fail(-1, "storage open");
+  IVFEntity ent;
+  int r = ent.load(storage);
+  if (r != 0) return fail(r, "entity load");
+  const size_t nl = ent.inverted_list_count(), n = ent.vector_count(), es = ent.meta().element_size();
+  *nlist = (uint32_t)nl; *nrows = n; *elem = (uint32_t)es;
+  // centroid index = nested Flat index in segment "ivf.centroid" (ivf_searcher.cc:62-86)
+  auto seg = storage->get(IVF_CENTROID_SEG_ID, 0);
+  if (!seg) return fail(-1, "no centroid segment");
+  IndexStorage::Pointer nested = std::make_shared<IndexSegmentStorage>(seg);
+  if (nested->open(std::string(), false) != 0) return fail(-1, "nested open");
+  IndexMeta cmeta;
+  r = IndexHelper::DeserializeFromStorage(nested.get(), &cmeta);
+  if (r != 0) return fail(r, "centroid meta");
+  const size_t ces = cmeta.element_size();
+  *c_elem = (uint32_t)ces; *c_dtype = (int)cmeta.data_type(); *c_dim = cmeta.dimension();
+  if (c_metric && c_metric_cap) snprintf(c_metric, c_metric_cap, "%s", cmeta.metric_name().c_str());
+  if (!centroids) return 0;
+  auto fseg = nested->get("flat.features"), kseg = nested->get("flat.keys");
+  if (!fseg || !kseg) return fail(-1, "centroid index is not a Flat index");
+  const size_t nc = kseg->data_size() / sizeof(uint64_t);
+  if (nc != nl || fseg->data_size() != nc * ces) return fail(-1, "centroid count mismatch");
+  const void *fp = nullptr; const uint64_t *kp = nullptr;
+  if (fseg->read(0, &fp, fseg->data_size()) != fseg->data_size()) return fail(-122, "read");
+  if (kseg->read(0, (const void **)&kp, kseg->data_size()) != kseg->data_size()) return fail(-122, "read");
+  const bool col = cmeta.major_order() == IndexMeta::MO_COLUMN;
+  const size_t us = IndexMeta::AlignSizeof(cmeta.data_type()), units = ces / us;
+  for (size_t i = 0; i < nc; ++i) {
+    char *dst = (char *)centroids + (size_t)kp[i] * ces;
+    if (kp[i] >= nc) return fail(-1, "centroid key out of range");
+    const size_t blk = i / 32 * 32;
+    if (col && blk + 32 <= nc) {
+      const char *b = (const char *)fp + blk * ces;
+      for (size_t u = 0; u < units; ++u) std::memcpy(dst + u * us, b + (u * 32 + (i - blk)) * us, us);
+    } else {
+      std::memcpy(dst, (const char *)fp + i * ces, ces);
+    }
+  }
+  size_t pos = 0;
+  for (size_t l = 0; l < nl; ++l) {
+    auto lm = ent.inverted_list_meta(l);
+    if (!lm) return fail(-122, "list meta");
+    list_offsets[l] = pos;
+    auto lk = ent.get_keys(lm->id_offset, lm->vector_count);
+    if (!lk && lm->vector_count) return fail(-122, "keys");
+    for (size_t j = 0; j < lm->vector_count; ++j, ++pos) {
+      const void *v = ent.get_vector(lm->id_offset + j);
+      if (!v) return fail(-122, "vector");
+      std::memcpy((char *)rows + pos * es, v, es);
+      keys[pos] = lk[j];
+    }
+  }
+  list_offsets[nl] = pos;
+  return pos == n ? 0 : fail(-1, "row count mismatch");
 }
 
 // Raw 1x1 distance of the index's metric (IndexMetric::distance()) between

@@ -94,6 +94,7 @@ def ref():
                 L.zref_has_searcher.argtypes = [C.c_char_p]
                 L.zref_set_filter.argtypes = [C.c_uint64, C.c_uint64]
                 L.zref_set_threshold.argtypes = [C.c_int, C.c_float]
+                L.zref_ivf_export.argtypes = [C.c_void_p] + [C.c_void_p] * 6 + [C.c_char_p, C.c_uint32] + [C.c_void_p] * 4
                 L._name = c
                 _ref = L
                 break
@@ -170,6 +171,24 @@ class RefIndex:
         out = np.zeros(n, np.float32)
         assert self.L.zref_index_distances(self.h, P(stored_rows), n, P(np.ascontiguousarray(stored_query)), P(out)) == 0
         return out
+
+    def ivf_export(self):
+        """-> dict(nlist, centroids [nlist, c_elem] u8, c_dtype, c_dim, c_metric, list_offsets u64[nlist+1],
+        rows [n, elem] u8 in list order, keys u64[n]) read with the reference's own IVFEntity."""
+        nl, n, el, ce, cdt, cdm = C.c_uint32(), C.c_uint64(), C.c_uint32(), C.c_uint32(), C.c_int(), C.c_uint32()
+        name = C.create_string_buffer(64)
+        r = self.L.zref_ivf_export(self.h, C.byref(nl), C.byref(n), C.byref(el), C.byref(ce), C.byref(cdt),
+                                   C.byref(cdm), name, 64, None, None, None, None)
+        assert r == 0, self.L.zref_last_error()
+        cent = np.zeros((nl.value, ce.value), np.uint8)
+        offs = np.zeros(nl.value + 1, np.uint64)
+        rows = np.zeros((n.value, el.value), np.uint8)
+        keys = np.zeros(n.value, np.uint64)
+        r = self.L.zref_ivf_export(self.h, C.byref(nl), C.byref(n), C.byref(el), C.byref(ce), C.byref(cdt),
+                                   C.byref(cdm), name, 64, P(cent), P(offs), P(rows), P(keys))
+        assert r == 0, self.L.zref_last_error()
+        return dict(nlist=nl.value, centroids=cent, c_dtype=cdt.value, c_dim=cdm.value,
+                    c_metric=name.value.decode(), list_offsets=offs, rows=rows, keys=keys)
 
     def close(self):
         if self.h:

@@ -148,6 +148,14 @@ class Store:
         _check(lib().zvb200_store_get_vector(self.h, row, _ptr(out), out.nbytes))
         return out
 
+    def ivf_attach(self, centroids, list_offsets):
+        """centroids: nlist elements in the store's layout; rows [list_offsets[l], list_offsets[l+1]) = list l."""
+        centroids = np.ascontiguousarray(centroids)
+        nlist = centroids.nbytes // self.elem_bytes
+        offs = np.ascontiguousarray(list_offsets, dtype=np.uint64)
+        assert offs.size == nlist + 1
+        _check(lib().zvb200_ivf_attach(self.h, _ptr(centroids), nlist, _ptr(offs)))
+
     def close(self):
         if self.h:
             lib().zvb200_store_destroy(self.h)
@@ -198,6 +206,18 @@ class Context:
             filter_bitmap = np.ascontiguousarray(filter_bitmap, dtype=np.uint32)
         _check(lib().zvb200_search(self.h, _ptr(queries), q, k, threshold, _ptr(filter_bitmap),
                                    _ptr(keys), _ptr(scores), _ptr(index), _ptr(counts)))
+        return keys, scores, index, counts
+
+    def ivf_search(self, queries, k, nprobe, max_scan_count):
+        """IVFSearcher::search_impl semantics -> (keys u64, scores f32, index u32, counts u32)."""
+        queries = np.ascontiguousarray(queries)
+        q = queries.nbytes // self.store.elem_bytes
+        keys = np.empty((q, k), np.uint64)
+        scores = np.empty((q, k), np.float32)
+        index = np.empty((q, k), np.uint32)
+        counts = np.empty(q, np.uint32)
+        _check(lib().zvb200_ivf_search(self.h, _ptr(queries), q, k, nprobe, max_scan_count,
+                                       _ptr(keys), _ptr(scores), _ptr(index), _ptr(counts)))
         return keys, scores, index, counts
 
     def search_device(self, q_ptr, q, k, out_scores_ptr, out_index_ptr, threshold=FLT_MAX, filter_ptr=None):

@@ -53,6 +53,8 @@ struct zvb200_store {
   // IVF
   zvb200_store *centroids = nullptr;
   std::vector<uint64_t> list_offsets;
+  uint32_t *list_off_dev = nullptr;  // [nlist+1] first row of each posting list
+  uint32_t nlist = 0;
   std::mutex mu;
 
   RowsView view() const {
@@ -97,6 +99,8 @@ struct zvb200_ctx {
   zvb200_store *s = nullptr;
   cudaStream_t stream = nullptr;
   DevBuf qin, qf32, qraw, qtails, qnorms, part, out_scores, out_index, filter, misc, gtau;
+  DevBuf coarse_scores, coarse_index, seg_prefix, seg_row, seg_count;  // IVF
+  QueryView last_qv;
   HostBuf h_q, h_scores, h_index;
   int force_kernel = 0;
   const char *last_kernel = "none";
@@ -195,6 +199,7 @@ int zvb200_store_destroy(zvb200_store *s) {
   if (s->tails) cudaFree(s->tails);
   if (s->norms) cudaFree(s->norms);
   if (s->drop) cudaFree(s->drop);
+  if (s->list_off_dev) cudaFree(s->list_off_dev);
   if (s->staging) cudaFree(s->staging);
   if (s->stream) cudaStreamDestroy(s->stream);
   delete s;
@@ -357,7 +362,8 @@ int zvb200_ctx_destroy(zvb200_ctx *c) {
   cudaSetDevice(c->s->device);
   cudaStreamSynchronize(c->stream);
   DevBuf *d[] = {&c->qin, &c->qf32, &c->qraw, &c->qtails, &c->qnorms, &c->part, &c->out_scores,
-                 &c->out_index, &c->filter, &c->misc, &c->gtau};
+                 &c->out_index, &c->filter, &c->misc, &c->gtau, &c->coarse_scores, &c->coarse_index,
+                 &c->seg_prefix, &c->seg_row, &c->seg_count};
   for (auto b : d) b->release();
   c->h_q.release(); c->h_scores.release(); c->h_index.release();
   if (c->ev_scan0) cudaEventDestroy(c->ev_scan0);
@@ -394,10 +400,9 @@ const char *zvb200_ctx_last_kernel(const zvb200_ctx *c) { return c ? c->last_ker
 // ======================================================================================
 
 // Prepare queries and run scan + final merge for queries already on the device.
-static int search_core(zvb200_ctx *c, const void *queries_dev, uint32_t q, uint32_t k,
+static int search_core(zvb200_ctx *c, zvb200_store *s, const void *queries_dev, uint32_t q, uint32_t k,
                        float threshold, const uint32_t *filter_dev, float *out_scores_dev,
                        uint32_t *out_index_dev, uint64_t row_begin, uint64_t row_end) {
-  zvb200_store *s = c->s;
   RowsView rv = s->view();
   const uint32_t esz = s->dtype == ZVB200_DT_FP32 ? 4 : s->dtype == ZVB200_DT_FP16 ? 2 : 1;
   const size_t qf32_bytes = s->dtype == ZVB200_DT_INT8 ? 0 : (size_t)q * (s->chunks * 16 / esz) * 4;
@@ -411,6 +416,8 @@ static int search_core(zvb200_ctx *c, const void *queries_dev, uint32_t q, uint3
   QueryView qv;
   qv.qf32 = (const float *)c->qf32.p; qv.qraw = (const uint8_t *)c->qraw.p;
   qv.qtails = (const float4 *)c->qtails.p; qv.qnorms = (const float *)c->qnorms.p;
+  qv.q = q;
+  c->last_qv = qv;  // the IVF list scan reuses the prepared queries
   SearchParams sp;
   sp.k = k; sp.threshold = threshold; sp.filter = filter_dev;
 
@@ -473,7 +480,7 @@ int zvb200_search_device(zvb200_ctx *c, const void *queries_dev, uint32_t q, uin
   if (r != 0) return r;
   if (q == 0) return 0;
   CU(cudaSetDevice(c->s->device));
-  return search_core(c, queries_dev, q, k, threshold, filter_dev, out_scores_dev, out_index_dev, 0, c->s->n);
+  return search_core(c, c->s, queries_dev, q, k, threshold, filter_dev, out_scores_dev, out_index_dev, 0, c->s->n);
 }
 
 int zvb200_search(zvb200_ctx *c, const void *queries, uint32_t q, uint32_t k, float threshold,
@@ -501,7 +508,7 @@ int zvb200_search(zvb200_ctx *c, const void *queries, uint32_t q, uint32_t k, fl
     CU(cudaMemcpyAsync(c->filter.p, filter, fb, cudaMemcpyHostToDevice, c->stream));
     fdev = (const uint32_t *)c->filter.p;
   }
-  r = search_core(c, c->qin.p, q, k, threshold, fdev, (float *)c->out_scores.p,
+  r = search_core(c, s, c->qin.p, q, k, threshold, fdev, (float *)c->out_scores.p,
                   (uint32_t *)c->out_index.p, 0, s->n);
   if (r != 0) return r;
   CU(cudaMemcpyAsync(c->h_scores.p, c->out_scores.p, nres * 4, cudaMemcpyDeviceToHost, c->stream));
@@ -575,12 +582,101 @@ int zvb200_distance_matrix(int device, int metric, int dtype, uint32_t dim, cons
   return r;
 }
 
-int zvb200_ivf_attach(zvb200_store *, const void *, uint32_t, const uint64_t *) {
-  return set_err(ZVB200_ERR_UNSUPPORTED, "ivf not built yet");
+int zvb200_ivf_attach(zvb200_store *s, const void *centroids, uint32_t nlist, const uint64_t *list_offsets) {
+  if (!s || !centroids || !list_offsets || nlist == 0) return set_err(ZVB200_ERR_INVALID_ARGUMENT, "null argument");
+  if (!s->sealed) return set_err(ZVB200_ERR_NOREADY, "store not sealed");
+  if (list_offsets[0] != 0 || list_offsets[nlist] != s->n) return set_err(ZVB200_ERR_MISMATCH, "list offsets do not cover the rows");
+  for (uint32_t l = 0; l < nlist; ++l)
+    if (list_offsets[l] > list_offsets[l + 1]) return set_err(ZVB200_ERR_INVALID_ARGUMENT, "list offsets not ascending");
+  zvb200_store *cs = nullptr;
+  int r = zvb200_store_create(s->device, s->dtype, s->metric, s->dim, &cs);
+  if (r == 0) r = zvb200_store_append(cs, centroids, nlist, nullptr);
+  if (r == 0) r = zvb200_store_seal(cs);
+  if (r != 0) { if (cs) zvb200_store_destroy(cs); return r; }
+  std::lock_guard<std::mutex> g(s->mu);
+  CU(cudaSetDevice(s->device));
+  std::vector<uint32_t> off32(nlist + 1);
+  for (uint32_t l = 0; l <= nlist; ++l) off32[l] = (uint32_t)list_offsets[l];
+  uint32_t *d = nullptr;
+  CU(cudaMalloc((void **)&d, (size_t)(nlist + 1) * 4));
+  CU(cudaMemcpy(d, off32.data(), (size_t)(nlist + 1) * 4, cudaMemcpyHostToDevice));
+  if (s->centroids) zvb200_store_destroy(s->centroids);
+  if (s->list_off_dev) cudaFree(s->list_off_dev);
+  s->centroids = cs; s->list_off_dev = d; s->nlist = nlist;
+  s->list_offsets.assign(list_offsets, list_offsets + nlist + 1);
+  return 0;
 }
-int zvb200_ivf_search(zvb200_ctx *, const void *, uint32_t, uint32_t, uint32_t, uint64_t, uint64_t *,
-                      float *, uint32_t *, uint32_t *) {
-  return set_err(ZVB200_ERR_UNSUPPORTED, "ivf not built yet");
+
+int zvb200_ivf_search(zvb200_ctx *c, const void *queries, uint32_t q, uint32_t k, uint32_t nprobe,
+                      uint64_t max_scan_count, uint64_t *out_keys, float *out_scores, uint32_t *out_index,
+                      uint32_t *out_counts) {
+  int r = check_search_args(c, queries, q, k);
+  if (r != 0) return r;
+  if (!out_scores) return set_err(ZVB200_ERR_INVALID_ARGUMENT, "null out_scores");
+  zvb200_store *s = c->s;
+  if (!s->centroids) return set_err(ZVB200_ERR_NOREADY, "no IVF structure attached");
+  if (nprobe == 0 || nprobe > ZVB200_MAX_TOPK) return set_err(ZVB200_ERR_INVALID_ARGUMENT, "nprobe must be 1..1024");
+  if (q == 0) return 0;
+  nprobe = std::min(nprobe, s->nlist);
+  CU(cudaSetDevice(s->device));
+  const size_t qbytes = (size_t)q * s->elem_bytes, nres = (size_t)q * k;
+  CU(c->h_q.ensure(qbytes));
+  CU(c->qin.ensure(qbytes));
+  CU(c->out_scores.ensure(nres * 4));
+  CU(c->out_index.ensure(nres * 4));
+  CU(c->h_scores.ensure(nres * 4));
+  CU(c->h_index.ensure(nres * 4));
+  CU(c->coarse_scores.ensure((size_t)q * nprobe * 4));
+  CU(c->coarse_index.ensure((size_t)q * nprobe * 4));
+  CU(c->seg_prefix.ensure((size_t)q * (nprobe + 1) * 4));
+  CU(c->seg_row.ensure((size_t)q * nprobe * 4));
+  CU(c->seg_count.ensure((size_t)q * 4));
+  memcpy(c->h_q.p, queries, qbytes);
+  CU(cudaMemcpyAsync(c->qin.p, c->h_q.p, qbytes, cudaMemcpyHostToDevice, c->stream));
+  // 1. coarse: top-nprobe centroids per query (IVFCentroidIndex::search, ivf_centroid_index.cc:273-295)
+  const int keep = c->force_kernel;
+  if (keep == 3) c->force_kernel = 0;
+  r = search_core(c, s->centroids, c->qin.p, q, nprobe, FLT_MAX, nullptr, (float *)c->coarse_scores.p,
+                  (uint32_t *)c->coarse_index.p, 0, s->centroids->n);
+  c->force_kernel = keep;
+  if (r != 0) return r;
+  // 2. which lists each query scans under the budget (ivf_searcher.cc:216-231)
+  CU(launch_ivf_plan((const uint32_t *)c->coarse_index.p, q, nprobe, s->list_off_dev, max_scan_count,
+                     (uint32_t *)c->seg_prefix.p, (uint32_t *)c->seg_row.p, (uint32_t *)c->seg_count.p, c->stream));
+  // 3. posting-list scan, queries already in compute layout (same dtype / metric / dim as the centroids)
+  RowsView rv = s->view();
+  SearchParams sp;
+  sp.k = k; sp.threshold = FLT_MAX; sp.filter = nullptr;
+  const size_t parts = scan_lists_parts(q, s->sm_count);
+  CU(c->part.ensure((size_t)q * parts * k * sizeof(u64)));
+  uint32_t nparts = 0;
+  CU(cudaEventRecord(c->ev_scan0, c->stream));
+  c->scan_timed = true;
+  CU(launch_scan_lists(rv, c->last_qv, sp, (const uint32_t *)c->seg_prefix.p, (const uint32_t *)c->seg_row.p,
+                       (const uint32_t *)c->seg_count.p, nprobe, (u64 *)c->part.p, &nparts, s->sm_count, c->stream));
+  CU(cudaEventRecord(c->ev_scan1, c->stream));
+  c->last_kernel = "scan_lists";
+  CU(launch_merge_parts((const u64 *)c->part.p, nparts, q, k, (float *)c->out_scores.p, (uint32_t *)c->out_index.p,
+                        c->stream));
+  CU(cudaMemcpyAsync(c->h_scores.p, c->out_scores.p, nres * 4, cudaMemcpyDeviceToHost, c->stream));
+  CU(cudaMemcpyAsync(c->h_index.p, c->out_index.p, nres * 4, cudaMemcpyDeviceToHost, c->stream));
+  CU(cudaStreamSynchronize(c->stream));
+  const float *hs = (const float *)c->h_scores.p;
+  const uint32_t *hi = (const uint32_t *)c->h_index.p;
+  memcpy(out_scores, hs, nres * 4);
+  if (out_index) memcpy(out_index, hi, nres * 4);
+  for (uint32_t i = 0; i < q; ++i) {
+    uint32_t cnt = 0;
+    for (uint32_t j = 0; j < k; ++j) {
+      const uint32_t ix = hi[(size_t)i * k + j];
+      if (ix != ZVB200_INVALID_INDEX) ++cnt;
+      if (out_keys)
+        out_keys[(size_t)i * k + j] = ix == ZVB200_INVALID_INDEX ? ZVB200_INVALID_KEY
+                                      : (s->keys.empty() ? (uint64_t)ix : s->keys[ix]);
+    }
+    if (out_counts) out_counts[i] = cnt;
+  }
+  return 0;
 }
 
 }  // extern "C"

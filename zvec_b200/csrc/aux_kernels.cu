@@ -336,4 +336,41 @@ cudaError_t launch_distance_matrix(const RowsView &rv, const QueryView &qv, floa
   return cudaGetLastError();
 }
 
+// ---- IVF: which posting lists a query scans -------------------------------------------------
+// The loop header of IVFSearcher::search_impl (src/core/algorithm/ivf/ivf_searcher.cc:216-219):
+// lists are visited in coarse order while the rows scanned so far are < max_scan_count (a list
+// is always scanned whole).  One thread per query; nprobe <= 1024.
+namespace {
+__global__ void ivf_plan_kernel(const uint32_t *coarse_index, uint32_t q, uint32_t nprobe, const uint32_t *list_off,
+                                uint64_t max_scan_count, uint32_t *seg_prefix, uint32_t *seg_row,
+                                uint32_t *seg_count) {
+  const uint32_t qi = blockIdx.x * blockDim.x + threadIdx.x;
+  if (qi >= q) return;
+  const uint32_t *ci = coarse_index + (size_t)qi * nprobe;
+  uint32_t *pre = seg_prefix + (size_t)qi * (nprobe + 1), *row = seg_row + (size_t)qi * nprobe;
+  uint64_t total = 0;
+  uint32_t n = 0;
+  pre[0] = 0;
+  for (uint32_t i = 0; i < nprobe && total < max_scan_count; ++i) {
+    const uint32_t cid = ci[i];
+    if (cid == ZVB200_INVALID_INDEX) break;
+    const uint32_t b = list_off[cid], e = list_off[cid + 1];
+    total += e - b;
+    if (e == b) continue;
+    row[n] = b;
+    pre[++n] = (uint32_t)total;
+  }
+  seg_count[qi] = n;
+}
+}  // namespace
+
+cudaError_t launch_ivf_plan(const uint32_t *coarse_index, uint32_t q, uint32_t nprobe, const uint32_t *list_off,
+                            uint64_t max_scan_count, uint32_t *seg_prefix, uint32_t *seg_row, uint32_t *seg_count,
+                            cudaStream_t st) {
+  ivf_plan_kernel<<<(q + 127) / 128, 128, 0, st>>>(coarse_index, q, nprobe, list_off, max_scan_count, seg_prefix,
+                                                  seg_row, seg_count);
+  count_launch();
+  return cudaGetLastError();
+}
+
 }  // namespace zvb

@@ -84,6 +84,15 @@ cudaError_t launch_row_norms(const RowsView &rv, uint64_t row_begin, uint64_t ro
 cudaError_t launch_distance_matrix(const RowsView &rv, const QueryView &qv, float *out,
                                    cudaStream_t st);
 
+// K4: IVF — list selection under the scan budget, then the posting-list scan (grid.y = query)
+cudaError_t launch_ivf_plan(const uint32_t *coarse_index, uint32_t q, uint32_t nprobe, const uint32_t *list_off,
+                            uint64_t max_scan_count, uint32_t *seg_prefix, uint32_t *seg_row, uint32_t *seg_count,
+                            cudaStream_t st);
+cudaError_t launch_scan_lists(const RowsView &rv, const QueryView &qv, const SearchParams &sp,
+                              const uint32_t *seg_prefix, const uint32_t *seg_row, const uint32_t *seg_count,
+                              uint32_t seg_cap, u64 *part, uint32_t *nparts, int sm_count, cudaStream_t st);
+size_t scan_lists_parts(uint32_t q, int sm_count);
+
 void count_launch(int n = 1);
 
 }  // namespace zvb

@@ -30,6 +30,11 @@ struct GemvArgs {
   u64 *part;          // [q][nparts][k]
   uint32_t nparts;
   int lpr_log2;       // lanes per row = 1 << lpr_log2
+  // SEG mode (IVF posting-list scan): query blockIdx.y scans the concatenation of its selected
+  // lists; virtual row v of segment i (seg_prefix[i] <= v < seg_prefix[i+1]) is stored row
+  // seg_row[i] + v - seg_prefix[i].  Arrays are [q][seg_cap(+1)].
+  const uint32_t *seg_prefix, *seg_row, *seg_count;
+  uint32_t seg_cap;
 };
 
 __device__ __forceinline__ bool bit_set(const uint32_t *bm, uint64_t i) {
@@ -101,7 +106,7 @@ struct Chunk<ZVB200_DT_INT8, L2> {
   static __host__ __device__ size_t qbytes(uint32_t chunks) { return (size_t)chunks * 16; }
 };
 
-template <int DT, bool L2, int QB>
+template <int DT, bool L2, int QB, bool SEG>
 __global__ void __launch_bounds__(kThreads, QB == 1 ? 2 : 1) scan_gemv_kernel(const GemvArgs a) {
   typedef Chunk<DT, L2> CK;
   typedef typename CK::Acc Acc;
@@ -109,7 +114,8 @@ __global__ void __launch_bounds__(kThreads, QB == 1 ? 2 : 1) scan_gemv_kernel(co
   const int lane = lane_id(), warp = threadIdx.x >> 5;
   const uint32_t C = a.rv.chunks;
   const size_t qbytes = CK::qbytes(C);
-  const int nq = min((uint32_t)QB, a.qv.q - a.q0);  // live queries of this launch
+  const uint32_t qbase = SEG ? a.q0 + blockIdx.y : a.q0;
+  const int nq = min((uint32_t)QB, a.qv.q - qbase);  // live queries of this launch
   const int k = a.k;
 
   // ---- smem: QB queries | int qq[QB] | meta[kWarps*QB] | top-k storage ----
@@ -118,13 +124,22 @@ __global__ void __launch_bounds__(kThreads, QB == 1 ? 2 : 1) scan_gemv_kernel(co
   int2 *meta = reinterpret_cast<int2 *>(qq + QB + (QB & 1));  // {list offset in u64s, cnt}
   u64 *tkbase = reinterpret_cast<u64 *>(meta + kWarps * QB);
   const size_t tk_u64 = (size_t)2 * k + 32;
+  // SEG: this query's segment table behind the top-k storage
+  uint32_t *sprefix = reinterpret_cast<uint32_t *>(tkbase + (size_t)kWarps * QB * tk_u64);
+  uint32_t *srow = sprefix + a.seg_cap + 1;
+  uint32_t nseg = 0;
+  if (SEG) {
+    nseg = a.seg_count[qbase];
+    for (uint32_t i = threadIdx.x; i <= nseg; i += kThreads) sprefix[i] = a.seg_prefix[(size_t)qbase * (a.seg_cap + 1) + i];
+    for (uint32_t i = threadIdx.x; i < nseg; i += kThreads) srow[i] = a.seg_row[(size_t)qbase * a.seg_cap + i];
+  }
 
   // load queries (compute layout) into smem
   for (int j = 0; j < QB; ++j) {
     const bool live = j < nq;
     const uint8_t *src = (DT == ZVB200_DT_INT8)
-                             ? a.qv.qraw + (size_t)(a.q0 + j) * a.rv.row_stride
-                             : reinterpret_cast<const uint8_t *>(a.qv.qf32) + (size_t)(a.q0 + j) * qbytes;
+                             ? a.qv.qraw + (size_t)(qbase + j) * a.rv.row_stride
+                             : reinterpret_cast<const uint8_t *>(a.qv.qf32) + (size_t)(qbase + j) * qbytes;
     for (size_t o = (size_t)threadIdx.x * 16; o < qbytes; o += (size_t)kThreads * 16) {
       uint4 v = make_uint4(0, 0, 0, 0);
       if (live) v = *reinterpret_cast<const uint4 *>(src + o);
@@ -151,27 +166,39 @@ __global__ void __launch_bounds__(kThreads, QB == 1 ? 2 : 1) scan_gemv_kernel(co
   const int l = lane & (lpr - 1), sub = lane >> a.lpr_log2;
   const uint64_t rows_per_warp_step = (uint64_t)kU * R;
   const uint64_t rows_per_tile = rows_per_warp_step * kWarps;
-  const uint64_t nrows = a.row_end - a.row_begin;
+  // row space walked by this CTA: the store's [row_begin, row_end), or the virtual rows of the query's lists
+  const uint64_t vbegin = SEG ? 0 : a.row_begin;
+  const uint64_t vend = SEG ? (uint64_t)sprefix[nseg] : a.row_end;
+  const uint64_t nrows = vend - vbegin;
   const uint64_t ntiles = (nrows + rows_per_tile - 1) / rows_per_tile;
+  auto to_row = [&](uint64_t v) -> uint64_t {
+    if (!SEG) return v;
+    uint32_t lo = 0, hi = nseg;  // last segment with prefix <= v
+    while (hi - lo > 1) {
+      const uint32_t mid = (lo + hi) >> 1;
+      if (sprefix[mid] <= (uint32_t)v) lo = mid; else hi = mid;
+    }
+    return (uint64_t)srow[lo] + ((uint32_t)v - sprefix[lo]);
+  };
   const int metric = a.rv.metric;
   const float dq = (float)a.rv.d;
 
   float4 qt[QB];
   if (metric_is_qi8(metric)) {
 #pragma unroll
-    for (int j = 0; j < QB; ++j) qt[j] = j < nq ? a.qv.qtails[a.q0 + j] : make_float4(0, 0, 0, 0);
+    for (int j = 0; j < QB; ++j) qt[j] = j < nq ? a.qv.qtails[qbase + j] : make_float4(0, 0, 0, 0);
   }
 
   for (uint64_t t = blockIdx.x; t < ntiles; t += gridDim.x) {
-    const uint64_t base = a.row_begin + t * rows_per_tile + (uint64_t)warp * rows_per_warp_step;
-    if (base >= a.row_end) continue;  // warp-uniform
+    const uint64_t base = vbegin + t * rows_per_tile + (uint64_t)warp * rows_per_warp_step;
+    if (base >= vend) continue;  // warp-uniform
     Acc acc[kU][QB], aa[kU];
     const uint8_t *rp[kU];
 #pragma unroll
     for (int u = 0; u < kU; ++u) {
       uint64_t r = base + (uint64_t)u * R + sub;
-      if (r >= a.row_end) r = a.row_end - 1;  // clamp: loaded, result discarded
-      rp[u] = a.rv.rows + r * a.rv.row_stride;
+      if (r >= vend) r = vend - 1;  // clamp: loaded, result discarded
+      rp[u] = a.rv.rows + to_row(r) * a.rv.row_stride;
       aa[u] = 0;
 #pragma unroll
       for (int j = 0; j < QB; ++j) acc[u][j] = 0;
@@ -201,8 +228,9 @@ __global__ void __launch_bounds__(kThreads, QB == 1 ? 2 : 1) scan_gemv_kernel(co
     // epilogue: score, gate, push
 #pragma unroll
     for (int u = 0; u < kU; ++u) {
-      const uint64_t r = base + (uint64_t)u * R + sub;
-      bool valid = (l == 0) && r < a.row_end;
+      const uint64_t rv_ = base + (uint64_t)u * R + sub;
+      bool valid = (l == 0) && rv_ < vend;
+      const uint64_t r = SEG ? (uint64_t)((rp[u] - a.rv.rows) / a.rv.row_stride) : rv_;
       if (valid && a.rv.drop) valid = !bit_set(a.rv.drop, r);
       if (valid && a.filter) valid = !bit_set(a.filter, r);
       float4 mt = make_float4(0, 0, 0, 0);
@@ -251,17 +279,17 @@ __global__ void __launch_bounds__(kThreads, QB == 1 ? 2 : 1) scan_gemv_kernel(co
       }
     }
     tk[j].finish(kMaxKey);
-    u64 *dst = a.part + ((size_t)(a.q0 + j) * a.nparts + blockIdx.x) * k;
+    u64 *dst = a.part + ((size_t)(qbase + j) * a.nparts + blockIdx.x) * k;
     for (int i = lane; i < k; i += 32) dst[i] = i < tk[j].cnt ? tk[j].list[i] : kMaxKey;
   }
 }
 
-template <int DT, bool L2, int QB>
-cudaError_t launch_one(const GemvArgs &a, int grid, size_t smem, cudaStream_t st) {
-  auto kern = scan_gemv_kernel<DT, L2, QB>;
+template <int DT, bool L2, int QB, bool SEG = false>
+cudaError_t launch_one(const GemvArgs &a, int grid, size_t smem, cudaStream_t st, int grid_y = 1) {
+  auto kern = scan_gemv_kernel<DT, L2, QB, SEG>;
   cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return e;
-  kern<<<grid, kThreads, smem, st>>>(a);
+  kern<<<dim3(grid, grid_y), kThreads, smem, st>>>(a);
   count_launch();
   return cudaGetLastError();
 }
@@ -275,10 +303,10 @@ cudaError_t launch_qb(const GemvArgs &a, int qb, int grid, size_t smem, cudaStre
   }
 }
 
-size_t gemv_smem(int dtype, uint32_t chunks, int qb, uint32_t k) {
+size_t gemv_smem(int dtype, uint32_t chunks, int qb, uint32_t k, uint32_t seg_cap = 0) {
   size_t qbytes = dtype == ZVB200_DT_FP16 ? (size_t)chunks * 32 : (size_t)chunks * 16;
   return (size_t)qb * qbytes + sizeof(int) * (qb + (qb & 1)) + sizeof(int2) * kWarps * qb +
-         (size_t)kWarps * qb * (2 * (size_t)k + 32) * sizeof(u64);
+         (size_t)kWarps * qb * (2 * (size_t)k + 32) * sizeof(u64) + (seg_cap ? (2 * (size_t)seg_cap + 2) * 4 : 0);
 }
 
 }  // namespace
@@ -289,6 +317,7 @@ cudaError_t launch_scan_gemv(const RowsView &rv, const QueryView &qv, const Sear
                              uint64_t row_begin, uint64_t row_end, u64 *part, uint32_t *nparts,
                              int sm_count, cudaStream_t st) {
   GemvArgs a;
+  a.seg_prefix = a.seg_row = a.seg_count = nullptr; a.seg_cap = 0;
   a.rv = rv; a.qv = qv; a.k = sp.k; a.threshold = sp.threshold; a.filter = sp.filter;
   a.row_begin = row_begin; a.row_end = row_end; a.part = part;
   // lanes per row: largest power of two <= min(32, chunks)
@@ -319,6 +348,49 @@ cudaError_t launch_scan_gemv(const RowsView &rv, const QueryView &qv, const Sear
     else
       e = l2 ? launch_qb<ZVB200_DT_INT8, true>(a, qb, grid, smem, st)
              : launch_qb<ZVB200_DT_INT8, false>(a, qb, grid, smem, st);
+    if (e != cudaSuccess) return e;
+  }
+  return cudaSuccess;
+}
+
+// K4 — IVF posting-list scan: grid.y = query, each query walks ITS selected lists.
+// Replaces the per-list loop of IVFSearcher::search_impl (src/core/algorithm/ivf/
+// ivf_searcher.cc:216-231) -> IVFEntity::search(list, query, ...) (ivf_entity.cc:662-716).
+size_t scan_lists_parts(uint32_t q, int sm_count) {
+  const uint32_t target = (uint32_t)sm_count * 8;  // CTAs wanted in flight (2 resident per SM, 4 waves)
+  return std::max<uint32_t>(1, std::min<uint32_t>((target + q - 1) / q, (uint32_t)sm_count * 2));
+}
+
+cudaError_t launch_scan_lists(const RowsView &rv, const QueryView &qv, const SearchParams &sp,
+                              const uint32_t *seg_prefix, const uint32_t *seg_row, const uint32_t *seg_count,
+                              uint32_t seg_cap, u64 *part, uint32_t *nparts, int sm_count, cudaStream_t st) {
+  GemvArgs a;
+  a.rv = rv; a.qv = qv; a.k = sp.k; a.threshold = sp.threshold; a.filter = sp.filter;
+  a.row_begin = 0; a.row_end = rv.n; a.part = part; a.q0 = 0;
+  a.seg_prefix = seg_prefix; a.seg_row = seg_row; a.seg_count = seg_count; a.seg_cap = seg_cap;
+  int lg = 0;
+  while ((2u << lg) <= rv.chunks && lg < 5) ++lg;
+  a.lpr_log2 = lg;
+  const int grid = (int)scan_lists_parts(qv.q, sm_count);
+  a.nparts = grid;
+  *nparts = grid;
+  const size_t smem = gemv_smem(rv.dtype, rv.chunks, 1, sp.k, seg_cap);
+  if (smem > 220 * 1024) return cudaErrorInvalidValue;
+  const bool l2 = metric_is_l2(rv.metric);
+  const uint32_t ymax = 65535;
+  for (uint32_t q0 = 0; q0 < qv.q; q0 += ymax) {
+    a.q0 = q0;
+    const int gy = (int)std::min<uint32_t>(ymax, qv.q - q0);
+    cudaError_t e;
+    if (rv.dtype == ZVB200_DT_FP32)
+      e = l2 ? launch_one<ZVB200_DT_FP32, true, 1, true>(a, grid, smem, st, gy)
+             : launch_one<ZVB200_DT_FP32, false, 1, true>(a, grid, smem, st, gy);
+    else if (rv.dtype == ZVB200_DT_FP16)
+      e = l2 ? launch_one<ZVB200_DT_FP16, true, 1, true>(a, grid, smem, st, gy)
+             : launch_one<ZVB200_DT_FP16, false, 1, true>(a, grid, smem, st, gy);
+    else
+      e = l2 ? launch_one<ZVB200_DT_INT8, true, 1, true>(a, grid, smem, st, gy)
+             : launch_one<ZVB200_DT_INT8, false, 1, true>(a, grid, smem, st, gy);
     if (e != cudaSuccess) return e;
   }
   return cudaSuccess;
