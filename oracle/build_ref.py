@@ -87,7 +87,10 @@ def build(march, jobs):
     newest = max(os.path.getmtime(o) for o in objs)
     if not os.path.exists(so) or os.path.getmtime(so) < newest:
         subprocess.check_call(["g++", "-shared", "-o", so] + objs +
-                              ["-lpthread", "-ldl", "-lrt", "-static-libstdc++", "-static-libgcc"])
+                              # --exclude-libs: keep the static libstdc++ private, so that loading this library
+                              # RTLD_GLOBAL (for plugins) cannot interpose on torch's or anyone else's C++ runtime
+                              ["-lpthread", "-ldl", "-lrt", "-static-libstdc++", "-static-libgcc",
+                               "-Wl,--exclude-libs,ALL"])
     return so
 
 

@@ -162,7 +162,9 @@ class RefIndex:
         counts = np.zeros(q, np.uint32)
         r = self.L.zref_index_search(self.h, P(queries), q, k, batch, threads, int(normalize), P(keys),
                                      P(scores), P(index), P(counts))
-        assert r == 0, r
+        if r != 0:
+            import zvec_b200
+            raise AssertionError("search_impl returned %d (%s)" % (r, zvec_b200.lib().zvb200_last_error().decode()))
         return keys, scores, index, counts
 
     def distances(self, stored_rows, stored_query):

@@ -97,6 +97,7 @@ struct HostBuf {
 
 struct zvb200_ctx {
   zvb200_store *s = nullptr;
+  int device = 0;  // copy: a context may outlive its store (destruction order is the caller's)
   cudaStream_t stream = nullptr;
   DevBuf qin, qf32, qraw, qtails, qnorms, part, out_scores, out_index, filter, misc, gtau;
   DevBuf coarse_scores, coarse_index, seg_prefix, seg_row, seg_count;  // IVF
@@ -349,6 +350,7 @@ int zvb200_ctx_create(zvb200_store *s, zvb200_ctx **out) {
   CU(cudaSetDevice(s->device));
   auto c = new zvb200_ctx();
   c->s = s;
+  c->device = s->device;
   cudaError_t e = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking);
   if (e == cudaSuccess) e = cudaEventCreate(&c->ev_scan0);
   if (e == cudaSuccess) e = cudaEventCreate(&c->ev_scan1);
@@ -359,7 +361,7 @@ int zvb200_ctx_create(zvb200_store *s, zvb200_ctx **out) {
 
 int zvb200_ctx_destroy(zvb200_ctx *c) {
   if (!c) return 0;
-  cudaSetDevice(c->s->device);
+  cudaSetDevice(c->device);
   cudaStreamSynchronize(c->stream);
   DevBuf *d[] = {&c->qin, &c->qf32, &c->qraw, &c->qtails, &c->qnorms, &c->part, &c->out_scores,
                  &c->out_index, &c->filter, &c->misc, &c->gtau, &c->coarse_scores, &c->coarse_index,
@@ -452,7 +454,7 @@ static int search_core(zvb200_ctx *c, zvb200_store *s, const void *queries_dev, 
       CU(launch_scan_tile(rv, g, sp, row_begin, row_end, (u64 *)c->part.p, &nparts, s->sm_count, c->stream));
       c->last_kernel = "scan_tile";
     } else {
-      CU(c->gtau.ensure((size_t)qn * sizeof(uint32_t)));
+      CU(c->gtau.ensure((size_t)qn * scan_mma_max_parts(s->sm_count) * sizeof(uint32_t)));
       CU(launch_scan_mma(rv, g, sp, row_begin, row_end, (u64 *)c->part.p, &nparts, (uint32_t *)c->gtau.p,
                          s->sm_count, c->stream));
       c->last_kernel = "scan_mma";
@@ -465,6 +467,7 @@ static int search_core(zvb200_ctx *c, zvb200_store *s, const void *queries_dev, 
 }
 
 static int check_search_args(zvb200_ctx *c, const void *queries, uint32_t q, uint32_t k) {
+  cudaGetLastError();  // a stale non-sticky error of an unrelated call must not fail this search
   if (!c || (!queries && q)) return set_err(ZVB200_ERR_INVALID_ARGUMENT, "null argument");
   if (k == 0 || k > ZVB200_MAX_TOPK) return set_err(ZVB200_ERR_INVALID_ARGUMENT, "topk must be 1..1024");
   if (!c->s->sealed) return set_err(ZVB200_ERR_NOREADY, "store not sealed");

@@ -61,7 +61,7 @@ bool scan_tile_supports(uint32_t k);
 // epilogue; at most sm_count query tiles of 128 per launch.
 cudaError_t launch_scan_mma(const RowsView &rv, const QueryView &qv, const SearchParams &sp,
                             uint64_t row_begin, uint64_t row_end, u64 *part, uint32_t *nparts,
-                            uint32_t *gtau /* qv.q words of scratch */, int sm_count, cudaStream_t st);
+                            uint32_t *pub /* qv.q * scan_mma_max_parts words of scratch */, int sm_count, cudaStream_t st);
 size_t scan_mma_max_parts(int sm_count);
 bool scan_mma_supports(const RowsView &rv, uint32_t k);
 // queries (stored layout, device) -> compute layout

@@ -53,7 +53,9 @@ struct MmaArgs {
   float threshold;
   const uint32_t *drop, *filter;
   u64 *part;            // [nq][groups][k]
-  uint32_t *gtau;       // [nq] ordered image of the best k-th score any CTA has reached so far
+  uint32_t *pub;        // [groups][nq] ordered image of each CTA's pub_j-th best score per query
+  uint32_t pub_j;       // which list entry a CTA publishes (1-based)
+  uint32_t pub_m;       // pub_m * pub_j >= k: the pub_m-th smallest published score bounds the global k-th best
   int dbg;              // ZVB200_MMA_DEBUG probes (perf triage only): 1 no epilogue, 2 no TMA, 4 A only, 8 B only, 16 no slow path
 };
 
@@ -252,12 +254,18 @@ scan_mma_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
     const int mode = a.mode;
     const int K = (int)k;
     int cnt = 0;
-    // Accept a key only if it is < tau_key.  tau_key = min(threshold gate, this CTA's k-th best,
-    // the best k-th score ANY CTA scanning this query has published in gtau): a row that is not
-    // better than k rows already seen somewhere cannot be in the final top-k, so sharing the
-    // bound only removes work, never results.
+    // Accept a key only if it is < tau_key = min(threshold gate, this CTA's k-th best, union bound).
+    // Union bound: every CTA scanning this query publishes the score of its pub_j-th best row
+    // (one word, only ever decreasing).  CTAs hold disjoint rows, so the pub_m-th smallest of the
+    // published words has pub_m * pub_j >= k rows at or below it somewhere: the global k-th best
+    // cannot be worse.  With G groups and k <= G this tracks the best-of-G minima, i.e. almost the
+    // true global k-th best, so a CTA stops inserting rows that only look good locally.  Sharing
+    // the bound only removes work, never results: the final lists stay exact and deterministic.
     u64 tau_key = qvalid ? pack_key(a.threshold, 0xffffffffu) : 0ull;
-    uint32_t *my_gtau = a.gtau + (qvalid ? q0 + slot : q0);
+    const uint32_t qcol = qvalid ? q0 + slot : q0;
+    volatile uint32_t *my_pub = a.pub + (size_t)grp * a.nq + qcol;
+    uint32_t pub_val = 0xffffffffu;
+    const int pubj = (int)a.pub_j - 1;
     // fast filter on the raw dot product: pass iff dot >= dthr (conservative for cosine)
     auto dthr_of = [&](u64 tk) -> float {
       if (!qvalid) return __int_as_float(0x7f800000);
@@ -267,15 +275,30 @@ scan_mma_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
       return t - (fabsf(t) + fabsf(tau_f) + 1.0f) * 2.4e-7f;
     };
     float dthr = dthr_of(tau_key);
-    uint32_t g_next = 0xffffffffu;
+    auto union_bound = [&]() {
+      uint32_t best[16];
+#pragma unroll
+      for (int i = 0; i < 16; ++i) best[i] = 0xffffffffu;
+      for (uint32_t g = 0; g < a.groups; ++g) {
+        uint32_t x = *reinterpret_cast<volatile uint32_t *>(a.pub + (size_t)g * a.nq + qcol);
+#pragma unroll
+        for (int i = 0; i < 16; ++i) {  // sorted insert: best[] keeps the 16 smallest, ascending
+          const uint32_t lo = min(best[i], x);
+          x = max(best[i], x);
+          best[i] = lo;
+        }
+      }
+      uint32_t b = best[0];
+#pragma unroll
+      for (int i = 1; i < 16; ++i) b = (int)a.pub_m == i + 1 ? best[i] : b;
+      const u64 gk = ((u64)b << 32) | 0xffffffffu;
+      if (gk < tau_key) { tau_key = gk; dthr = dthr_of(tau_key); }
+    };
+    uint32_t next_eval = 1;
 
     for (uint32_t t = 0; t < ntl; ++t) {
       const uint32_t as = t & 1, aphase = (t >> 1) & 1;
       const uint32_t row0 = a.row_begin + (t_begin + t) * kBN;
-      {  // the bound other CTAs have reached, read while the previous tile was processed
-        const u64 gk = ((u64)g_next << 32) | 0xffffffffu;
-        if (gk < tau_key) { tau_key = gk; dthr = dthr_of(tau_key); }
-      }
       mbar_wait(bar_tfull + 8 * as, aphase);
       tc_fence_after();
       const uint32_t taddr = tmem_base + ((uint32_t)(ew * 32) << 16) + as * kBN;
@@ -312,11 +335,11 @@ scan_mma_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
                 if (cnt < K) ++cnt;
                 if (cnt == K) {
                   const u64 nt = L[(size_t)(K - 1) * kQM];
-                  if (nt < tau_key) {
-                    tau_key = nt;
-                    dthr = dthr_of(nt);
-                    atomicMin(my_gtau, (uint32_t)(nt >> 32));
-                  }
+                  if (nt < tau_key) { tau_key = nt; dthr = dthr_of(nt); }
+                }
+                if (i <= pubj && cnt > pubj) {
+                  const uint32_t pv = (uint32_t)(L[(size_t)pubj * kQM] >> 32);
+                  if (pv != pub_val) { pub_val = pv; *my_pub = pv; }
                 }
               }
             }
@@ -327,7 +350,11 @@ scan_mma_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(bar_tempty + 8 * as);
-      g_next = *reinterpret_cast<volatile uint32_t *>(my_gtau);
+      // off the MMA's critical path: refresh the union bound at tiles 1,2,3,4,6,9,13,19,... of this CTA
+      if (a.groups > 1 && t + 1 == next_eval) {
+        union_bound();
+        next_eval += max(1u, next_eval >> 1);
+      }
     }
     // write this CTA's partial lists: part[q][grp][0..k)
     if (qvalid) {
@@ -400,7 +427,7 @@ size_t scan_mma_max_parts(int sm_count) { return (size_t)sm_count; }
 
 cudaError_t launch_scan_mma(const RowsView &rv, const QueryView &qv, const SearchParams &sp,
                             uint64_t row_begin, uint64_t row_end, u64 *part, uint32_t *nparts,
-                            uint32_t *gtau, int sm_count, cudaStream_t st) {
+                            uint32_t *pub, int sm_count, cudaStream_t st) {
   uint32_t ns; size_t smem;
   if (!mma_config(sp.k, &ns, &smem)) return cudaErrorInvalidValue;
   const uint64_t nrows = row_end > row_begin ? row_end - row_begin : 0;
@@ -417,7 +444,13 @@ cudaError_t launch_scan_mma(const RowsView &rv, const QueryView &qv, const Searc
   a.threshold = sp.threshold;
   a.drop = rv.drop; a.filter = sp.filter;
   a.part = part;
-  a.gtau = gtau;
+  a.pub = pub;
+  {
+    // publish the j-th best so that the m-th smallest of the G published words covers k rows (m <= min(G,16))
+    const uint32_t mmax = std::min<uint32_t>(a.groups, 16u);
+    a.pub_j = (sp.k + mmax - 1) / mmax;
+    a.pub_m = (sp.k + a.pub_j - 1) / a.pub_j;
+  }
   {
     static const int dbg = [] { const char *e = getenv("ZVB200_MMA_DEBUG"); return e ? atoi(e) : 0; }();
     a.dbg = dbg;
@@ -433,7 +466,7 @@ cudaError_t launch_scan_mma(const RowsView &rv, const QueryView &qv, const Searc
     // nothing to scan: every partial list is empty
     return cudaMemsetAsync(part, 0xff, (size_t)qv.q * a.groups * sp.k * sizeof(u64), st);
   }
-  e = cudaMemsetAsync(gtau, 0xff, (size_t)qv.q * sizeof(uint32_t), st);
+  e = cudaMemsetAsync(pub, 0xff, (size_t)qv.q * a.groups * sizeof(uint32_t), st);
   if (e != cudaSuccess) return e;
   scan_mma_kernel<<<a.groups * a.qtiles, kThreads, smem, st>>>(tmQ, tmX, a);
   count_launch();
