@@ -128,7 +128,7 @@ int zvb200_ctx_sync(zvb200_ctx *c);
 int zvb200_ctx_last_scan_ms(zvb200_ctx *c, float *ms);
 /* The context's cudaStream_t (as void*) so callers can record events on it. */
 void *zvb200_ctx_stream(zvb200_ctx *c);
-/* Force a scan kernel: 0 auto, 1 GEMV scan (CUDA cores), 2 tiled CUDA-core, 3 tcgen05. */
+/* Force a scan kernel: 0 auto, 1 GEMV scan (LDG), 2 tiled CUDA-core, 3 tcgen05, 4 bulk-async streaming scan. */
 int zvb200_ctx_set_kernel(zvb200_ctx *c, int which);
 /* Name of the scan kernel the last search on this context used. */
 const char *zvb200_ctx_last_kernel(const zvb200_ctx *c);

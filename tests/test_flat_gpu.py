@@ -95,26 +95,39 @@ def run_case(kind, n, d, q, k, seed, kernel=0, drop=None, keys=None, threshold=N
     return name
 
 
+STREAMING = {0: ("scan_gemv", "scan_mma"), 1: ("scan_gemv",), 4: ("scan_stream",)}
+
+
+@pytest.mark.parametrize("kernel", [0, 1, 4])      # auto, LDG scan, bulk-async scan
 @pytest.mark.parametrize("kind", KINDS)
-def test_batch1_parity_all_metrics(kind):
-    assert run_case(kind, 5000, 96, 1, 10, seed=11) == "scan_gemv"
+def test_batch1_parity_all_metrics(kind, kernel):
+    assert run_case(kind, 5000, 96, 1, 10, seed=11, kernel=kernel) in STREAMING[kernel]
 
 
+@pytest.mark.parametrize("kernel", [0, 1, 4])
 @pytest.mark.parametrize("kind", KINDS)
-def test_small_batch_parity(kind):
-    run_case(kind, 3000, 64, 7, 10, seed=12)
+def test_small_batch_parity(kind, kernel):
+    run_case(kind, 3000, 64, 7, 10, seed=12, kernel=kernel)
 
 
-@pytest.mark.parametrize("d", [1, 3, 4, 7, 17, 33, 100, 128, 257, 768, 1536])
+@pytest.mark.parametrize("kernel", [1, 4])
+@pytest.mark.parametrize("d", [1, 3, 4, 7, 17, 33, 100, 128, 257, 768, 1536, 4100])
 @pytest.mark.parametrize("kind", ["fp32_l2", "fp16_ip", "qi8_l2"])
-def test_ragged_dimensions(kind, d):
-    run_case(kind, 1500, d, 2, 5, seed=13 + d)
+def test_ragged_dimensions(kind, d, kernel):
+    run_case(kind, 1500, d, 2, 5, seed=13 + d, kernel=kernel)
 
 
+@pytest.mark.parametrize("kernel", [1, 4])
 @pytest.mark.parametrize("k", [1, 2, 31, 32, 33, 100, 257, 1024])
-def test_topk_sizes(k):
-    run_case("fp32_l2", 4000, 32, 2, k, seed=14)
-    run_case("i8_l2", 4000, 32, 1, k, seed=15)   # heavy ties
+def test_topk_sizes(k, kernel):
+    run_case("fp32_l2", 4000, 32, 2, k, seed=14, kernel=kernel)
+    run_case("i8_l2", 4000, 32, 1, k, seed=15, kernel=kernel)   # heavy ties
+
+
+@pytest.mark.parametrize("n", [1, 7, 8, 9, 255, 257, 70001])
+def test_stream_kernel_ragged_row_counts(n):
+    run_case("fp32_l2", n, 40, 3, 10, seed=16 + n, kernel=4)
+    run_case("qi8_ip", n, 40, 1, 10, seed=17 + n, kernel=4)
 
 
 def test_k_larger_than_n_and_tiny_stores():

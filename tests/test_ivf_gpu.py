@@ -31,7 +31,8 @@ def budget(n, nlist, ratio, bf_threshold=1000):
     ("SquaredEuclidean", "HalfFloatConverter", None), ("SquaredEuclidean", "Int8StreamingConverter", "SquaredEuclidean"),
 ])
 @pytest.mark.parametrize("ratio", [0.05, 0.25])
-def test_ivf_search_equals_reference(metric, conv, origin, ratio):
+@pytest.mark.parametrize("kernel", [0, 4])
+def test_ivf_search_equals_reference(metric, conv, origin, ratio, kernel):
     n, d, nlist, k = 30000, 48, 100, 10
     x, qs = clustered(n, d, nlist, 3)
     ri = S.RefIndex(x, S.DT_FP32, d, metric, conv, kind="IVF",
@@ -44,6 +45,7 @@ def test_ivf_search_equals_reference(metric, conv, origin, ratio):
     st.append(e["rows"], e["keys"]); st.seal()
     st.ivf_attach(e["centroids"], e["list_offsets"])
     ctx = z.Context(st)
+    ctx.set_kernel(kernel)
     tq = ri.transform_queries(qs)
     nprobe, max_scan = budget(n, e["nlist"], ratio)
     rk, rs, _, rc = ri.search(qs, k)
@@ -51,7 +53,7 @@ def test_ivf_search_equals_reference(metric, conv, origin, ratio):
     for batch in (1, len(qs)):
         for b0 in range(0, len(qs), batch):
             gk, gs, gi, gc = ctx.ivf_search(tq[b0:b0 + batch], k, nprobe, max_scan)
-            assert ctx.last_kernel() == "scan_lists"
+            assert ctx.last_kernel() == ("scan_lists_stream" if kernel == 4 else "scan_lists")
             for j in range(gk.shape[0]):
                 i = b0 + j
                 assert gc[j] == rc[i]

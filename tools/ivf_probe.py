@@ -38,6 +38,7 @@ cn = centres.norm(dim=1, keepdim=True)
 cent = torch.cat([centres / cn, cn], dim=1).cpu().numpy()
 st.ivf_attach(cent, offs)
 ctx = z.Context(st)
+ctx.set_kernel(int(os.environ.get("ZVB200_PROBE_KERNEL", "0")))
 ratio = nprobe / nlist
 max_scan = max(1000, int(math.ceil(rows * ratio)))
 qsel = torch.randint(0, nlist, (max(batches),), generator=g, device=dev)

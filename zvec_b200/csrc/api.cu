@@ -389,7 +389,7 @@ int zvb200_ctx_last_scan_ms(zvb200_ctx *c, float *ms) {
 }
 void *zvb200_ctx_stream(zvb200_ctx *c) { return c ? (void *)c->stream : nullptr; }
 int zvb200_ctx_set_kernel(zvb200_ctx *c, int which) {
-  if (!c || which < 0 || which > 3) return set_err(ZVB200_ERR_INVALID_ARGUMENT, "bad kernel id");
+  if (!c || which < 0 || which > 4) return set_err(ZVB200_ERR_INVALID_ARGUMENT, "bad kernel id");
   c->force_kernel = which;
   return 0;
 }
@@ -408,28 +408,39 @@ static int search_core(zvb200_ctx *c, zvb200_store *s, const void *queries_dev, 
   RowsView rv = s->view();
   const uint32_t esz = s->dtype == ZVB200_DT_FP32 ? 4 : s->dtype == ZVB200_DT_FP16 ? 2 : 1;
   const size_t qf32_bytes = s->dtype == ZVB200_DT_INT8 ? 0 : (size_t)q * (s->chunks * 16 / esz) * 4;
-  const size_t qraw_bytes = s->dtype == ZVB200_DT_FP32 ? 0 : (size_t)q * s->row_stride;
+  // raw queries are padded with zero rows to a whole number of 128-query tiles: the tensor-core
+  // scan's TMA box then never leaves the tensor (out-of-range boxes are filled much more slowly)
+  const uint32_t qpad = (q + 127u) & ~127u;
+  const size_t qraw_bytes = s->dtype == ZVB200_DT_FP32 ? 0 : (size_t)qpad * s->row_stride;
   CU(c->qf32.ensure(qf32_bytes));
   CU(c->qraw.ensure(qraw_bytes));
   CU(c->qtails.ensure((size_t)q * sizeof(float4)));
   CU(c->qnorms.ensure((size_t)q * sizeof(float)));
+  if (qraw_bytes && qpad > q)
+    CU(cudaMemsetAsync((uint8_t *)c->qraw.p + (size_t)q * s->row_stride, 0, (size_t)(qpad - q) * s->row_stride, c->stream));
   CU(launch_prep_queries(rv, queries_dev, q, s->elem_bytes, (float *)c->qf32.p, (uint8_t *)c->qraw.p,
                          (float4 *)c->qtails.p, (float *)c->qnorms.p, c->stream));
   QueryView qv;
   qv.qf32 = (const float *)c->qf32.p; qv.qraw = (const uint8_t *)c->qraw.p;
   qv.qtails = (const float4 *)c->qtails.p; qv.qnorms = (const float *)c->qnorms.p;
   qv.q = q;
+  qv.qpad_rows = qraw_bytes != 0;
   c->last_qv = qv;  // the IVF list scan reuses the prepared queries
   SearchParams sp;
   sp.k = k; sp.threshold = threshold; sp.filter = filter_dev;
 
   int which = c->force_kernel;
   const bool mma_ok = scan_mma_supports(rv, k);
-  if (which == 0) which = (q <= 4) ? 1 : (q >= 32 && mma_ok) ? 3 : scan_tile_supports(k) ? 2 : 1;
+  // batch 1 streams best through the GEMV scan; from 2 queries on the tensor-core scan wins where it
+  // applies (it is HBM-bound below ~200 queries and reads the rows once for the whole batch)
+  const bool stream_ok = scan_stream_supports(rv, k, 0);
+  if (which == 0) which = mma_ok ? 3 : (q <= 4) ? 1 : scan_tile_supports(k) ? 2 : 1;
+  if (which == 4 && !stream_ok) which = 1;
   if (which == 3 && !mma_ok) return set_err(ZVB200_ERR_UNSUPPORTED, "tcgen05 scan: fp16 InnerProduct/Cosine, k <= 128 only");
   if (which == 2 && !scan_tile_supports(k)) which = 1;
   const size_t maxparts = which == 1 ? scan_gemv_max_parts(s->sm_count)
-                          : which == 2 ? scan_tile_max_parts(s->sm_count) : scan_mma_max_parts(s->sm_count);
+                          : which == 2 ? scan_tile_max_parts(s->sm_count)
+                          : which == 3 ? scan_mma_max_parts(s->sm_count) : scan_stream_max_parts(s->sm_count);
   // bound the partial-list scratch to 256 MiB: process the queries in groups
   const size_t per_query = maxparts * (size_t)k * sizeof(u64);
   uint32_t group = (uint32_t)std::max<size_t>(1, ((size_t)256 << 20) / per_query);
@@ -453,6 +464,9 @@ static int search_core(zvb200_ctx *c, zvb200_store *s, const void *queries_dev, 
     } else if (which == 2) {
       CU(launch_scan_tile(rv, g, sp, row_begin, row_end, (u64 *)c->part.p, &nparts, s->sm_count, c->stream));
       c->last_kernel = "scan_tile";
+    } else if (which == 4) {
+      CU(launch_scan_stream(rv, g, sp, row_begin, row_end, (u64 *)c->part.p, &nparts, s->sm_count, c->stream));
+      c->last_kernel = "scan_stream";
     } else {
       CU(c->gtau.ensure((size_t)qn * scan_mma_max_parts(s->sm_count) * sizeof(uint32_t)));
       CU(launch_scan_mma(rv, g, sp, row_begin, row_end, (u64 *)c->part.p, &nparts, (uint32_t *)c->gtau.p,
@@ -650,15 +664,21 @@ int zvb200_ivf_search(zvb200_ctx *c, const void *queries, uint32_t q, uint32_t k
   RowsView rv = s->view();
   SearchParams sp;
   sp.k = k; sp.threshold = FLT_MAX; sp.filter = nullptr;
-  const size_t parts = scan_lists_parts(q, s->sm_count);
+  const bool lists_stream = c->force_kernel == 4 && scan_stream_supports(rv, k, nprobe);
+  const size_t parts = lists_stream ? scan_lists_stream_parts(q, s->sm_count) : scan_lists_parts(q, s->sm_count);
   CU(c->part.ensure((size_t)q * parts * k * sizeof(u64)));
   uint32_t nparts = 0;
   CU(cudaEventRecord(c->ev_scan0, c->stream));
   c->scan_timed = true;
-  CU(launch_scan_lists(rv, c->last_qv, sp, (const uint32_t *)c->seg_prefix.p, (const uint32_t *)c->seg_row.p,
-                       (const uint32_t *)c->seg_count.p, nprobe, (u64 *)c->part.p, &nparts, s->sm_count, c->stream));
+  if (lists_stream)
+    CU(launch_scan_lists_stream(rv, c->last_qv, sp, (const uint32_t *)c->seg_prefix.p, (const uint32_t *)c->seg_row.p,
+                                (const uint32_t *)c->seg_count.p, nprobe, (u64 *)c->part.p, &nparts, s->sm_count,
+                                c->stream));
+  else
+    CU(launch_scan_lists(rv, c->last_qv, sp, (const uint32_t *)c->seg_prefix.p, (const uint32_t *)c->seg_row.p,
+                         (const uint32_t *)c->seg_count.p, nprobe, (u64 *)c->part.p, &nparts, s->sm_count, c->stream));
   CU(cudaEventRecord(c->ev_scan1, c->stream));
-  c->last_kernel = "scan_lists";
+  c->last_kernel = lists_stream ? "scan_lists_stream" : "scan_lists";
   CU(launch_merge_parts((const u64 *)c->part.p, nparts, q, k, (float *)c->out_scores.p, (uint32_t *)c->out_index.p,
                         c->stream));
   CU(cudaMemcpyAsync(c->h_scores.p, c->out_scores.p, nres * 4, cudaMemcpyDeviceToHost, c->stream));

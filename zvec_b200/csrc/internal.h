@@ -1,6 +1,7 @@
 // Host-side structures shared by the C ABI and the kernel launchers.
 #pragma once
 #include <cuda_runtime.h>
+#include <stdlib.h>
 #include <stdint.h>
 
 #include <mutex>
@@ -31,6 +32,7 @@ struct QueryView {
   const float4 *qtails = nullptr;  // QI8 query tails
   const float *qnorms = nullptr;   // |q|^2
   uint32_t q = 0;
+  bool qpad_rows = false;          // qraw holds zero rows up to the next multiple of 128 queries
 };
 
 struct SearchParams {
@@ -51,6 +53,12 @@ cudaError_t launch_scan_gemv(const RowsView &rv, const QueryView &qv, const Sear
                              uint64_t row_begin, uint64_t row_end, u64 *part, uint32_t *nparts,
                              int sm_count, cudaStream_t st);
 size_t scan_gemv_max_parts(int sm_count);
+// K1s: bulk-async (cp.async.bulk + mbarrier ring) streaming scan, exact arithmetic, grid.y = query
+cudaError_t launch_scan_stream(const RowsView &rv, const QueryView &qv, const SearchParams &sp,
+                               uint64_t row_begin, uint64_t row_end, u64 *part, uint32_t *nparts,
+                               int sm_count, cudaStream_t st);
+size_t scan_stream_max_parts(int sm_count);
+bool scan_stream_supports(const RowsView &rv, uint32_t k, uint32_t seg_cap);
 // K2c: tiled CUDA-core contraction, exact (x-q)^2 for L2; any q.
 cudaError_t launch_scan_tile(const RowsView &rv, const QueryView &qv, const SearchParams &sp,
                              uint64_t row_begin, uint64_t row_end, u64 *part, uint32_t *nparts,
@@ -92,6 +100,28 @@ cudaError_t launch_scan_lists(const RowsView &rv, const QueryView &qv, const Sea
                               const uint32_t *seg_prefix, const uint32_t *seg_row, const uint32_t *seg_count,
                               uint32_t seg_cap, u64 *part, uint32_t *nparts, int sm_count, cudaStream_t st);
 size_t scan_lists_parts(uint32_t q, int sm_count);
+cudaError_t launch_scan_lists_stream(const RowsView &rv, const QueryView &qv, const SearchParams &sp,
+                                     const uint32_t *seg_prefix, const uint32_t *seg_row, const uint32_t *seg_count,
+                                     uint32_t seg_cap, u64 *part, uint32_t *nparts, int sm_count, cudaStream_t st);
+size_t scan_lists_stream_parts(uint32_t q, int sm_count);
+
+// Lanes of a warp that share one stored row in the streaming scans (log2).  Measured on B200
+// (tools/scan_probe.py, 10M rows, batch 1): ~6 sixteen-byte chunks per lane is the sweet spot —
+// fewer lanes per row saves shuffle-reduction steps and top-k pushes per byte, but below 2 lanes
+// the per-lane strides defeat sector coalescing.  512-B rows: 32 lanes 3.4 TB/s, 4 lanes 7.0 TB/s.
+inline int max_lpr_log2(uint32_t chunks) {
+  int lg = 0;
+  while ((2u << lg) <= chunks && lg < 5) ++lg;
+  return lg;
+}
+inline int pick_lpr_log2(uint32_t chunks) {
+  static const int force = [] { const char *e = getenv("ZVB200_LPR_LOG2"); return e ? atoi(e) : -1; }();
+  const int top = max_lpr_log2(chunks);
+  if (force >= 0) return force < top ? force : top;
+  int lg = 1;
+  while (lg < 5 && chunks >= 9u << lg) ++lg;  // chunks / lanes in [4.5, 9)
+  return lg < top ? lg : top;
+}
 
 void count_launch(int n = 1);
 

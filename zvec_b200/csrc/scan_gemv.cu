@@ -8,6 +8,9 @@
 // heap->emplace.  HBM-bound: every stored byte is read exactly once with 128-bit
 // L1-bypassing loads, the queries live in shared memory, nothing but k keys per CTA
 // goes back to HBM.
+#include <stdlib.h>
+
+#include "chunk.cuh"
 #include "internal.h"
 #include "topk.cuh"
 
@@ -37,74 +40,6 @@ struct GemvArgs {
   uint32_t seg_cap;
 };
 
-__device__ __forceinline__ bool bit_set(const uint32_t *bm, uint64_t i) {
-  return (bm[i >> 5] >> (i & 31)) & 1u;
-}
-
-// accumulate one 16-byte chunk of a stored row against the query chunk in smem
-template <int DT, bool L2>
-struct Chunk;
-
-template <bool L2>
-struct Chunk<ZVB200_DT_FP32, L2> {
-  typedef float Acc;
-  static __device__ __forceinline__ void fma(Acc &acc, Acc &, const uint4 &v, const uint8_t *qs, int c) {
-    const float4 q = *reinterpret_cast<const float4 *>(qs + (size_t)c * 16);
-    const float x0 = __uint_as_float(v.x), x1 = __uint_as_float(v.y), x2 = __uint_as_float(v.z),
-                x3 = __uint_as_float(v.w);
-    if (L2) {
-      float d0 = x0 - q.x, d1 = x1 - q.y, d2 = x2 - q.z, d3 = x3 - q.w;
-      acc = fmaf(d0, d0, acc); acc = fmaf(d1, d1, acc); acc = fmaf(d2, d2, acc); acc = fmaf(d3, d3, acc);
-    } else {
-      acc = fmaf(x0, q.x, acc); acc = fmaf(x1, q.y, acc); acc = fmaf(x2, q.z, acc); acc = fmaf(x3, q.w, acc);
-    }
-  }
-  static __host__ __device__ size_t qbytes(uint32_t chunks) { return (size_t)chunks * 16; }
-};
-
-template <bool L2>
-struct Chunk<ZVB200_DT_FP16, L2> {
-  typedef float Acc;
-  // query kept as fp32 in smem (32 B per 16-B chunk of halves): widen once, like the
-  // reference's F16C path (inner_product_matrix_fp16.cc:144-189), accumulate in fp32.
-  static __device__ __forceinline__ void fma(Acc &acc, Acc &, const uint4 &v, const uint8_t *qs, int c) {
-    const float4 qa = *reinterpret_cast<const float4 *>(qs + (size_t)c * 32);
-    const float4 qb = *reinterpret_cast<const float4 *>(qs + (size_t)c * 32 + 16);
-    const float2 a = __half22float2(*reinterpret_cast<const __half2 *>(&v.x));
-    const float2 b = __half22float2(*reinterpret_cast<const __half2 *>(&v.y));
-    const float2 e = __half22float2(*reinterpret_cast<const __half2 *>(&v.z));
-    const float2 f = __half22float2(*reinterpret_cast<const __half2 *>(&v.w));
-    if (L2) {
-      float d;
-      d = a.x - qa.x; acc = fmaf(d, d, acc); d = a.y - qa.y; acc = fmaf(d, d, acc);
-      d = b.x - qa.z; acc = fmaf(d, d, acc); d = b.y - qa.w; acc = fmaf(d, d, acc);
-      d = e.x - qb.x; acc = fmaf(d, d, acc); d = e.y - qb.y; acc = fmaf(d, d, acc);
-      d = f.x - qb.z; acc = fmaf(d, d, acc); d = f.y - qb.w; acc = fmaf(d, d, acc);
-    } else {
-      acc = fmaf(a.x, qa.x, acc); acc = fmaf(a.y, qa.y, acc); acc = fmaf(b.x, qa.z, acc);
-      acc = fmaf(b.y, qa.w, acc); acc = fmaf(e.x, qb.x, acc); acc = fmaf(e.y, qb.y, acc);
-      acc = fmaf(f.x, qb.z, acc); acc = fmaf(f.y, qb.w, acc);
-    }
-  }
-  static __host__ __device__ size_t qbytes(uint32_t chunks) { return (size_t)chunks * 32; }
-};
-
-template <bool L2>
-struct Chunk<ZVB200_DT_INT8, L2> {
-  typedef int Acc;
-  // exact int32 accumulation as euclidean_distance_matrix_int8.cc:33-120 /
-  // inner_product_matrix_int8.cc:319-368; L2 = aa - 2ab + qq with aa gathered here.
-  static __device__ __forceinline__ void fma(Acc &ab, Acc &aa, const uint4 &v, const uint8_t *qs, int c) {
-    const uint4 q = *reinterpret_cast<const uint4 *>(qs + (size_t)c * 16);
-    ab = __dp4a((int)v.x, (int)q.x, ab); ab = __dp4a((int)v.y, (int)q.y, ab);
-    ab = __dp4a((int)v.z, (int)q.z, ab); ab = __dp4a((int)v.w, (int)q.w, ab);
-    if (L2) {
-      aa = __dp4a((int)v.x, (int)v.x, aa); aa = __dp4a((int)v.y, (int)v.y, aa);
-      aa = __dp4a((int)v.z, (int)v.z, aa); aa = __dp4a((int)v.w, (int)v.w, aa);
-    }
-  }
-  static __host__ __device__ size_t qbytes(uint32_t chunks) { return (size_t)chunks * 16; }
-};
 
 template <int DT, bool L2, int QB, bool SEG>
 __global__ void __launch_bounds__(kThreads, QB == 1 ? 2 : 1) scan_gemv_kernel(const GemvArgs a) {
@@ -320,9 +255,7 @@ cudaError_t launch_scan_gemv(const RowsView &rv, const QueryView &qv, const Sear
   a.seg_prefix = a.seg_row = a.seg_count = nullptr; a.seg_cap = 0;
   a.rv = rv; a.qv = qv; a.k = sp.k; a.threshold = sp.threshold; a.filter = sp.filter;
   a.row_begin = row_begin; a.row_end = row_end; a.part = part;
-  // lanes per row: largest power of two <= min(32, chunks)
-  int lg = 0;
-  while ((2u << lg) <= rv.chunks && lg < 5) ++lg;
+  const int lg = pick_lpr_log2(rv.chunks);
   a.lpr_log2 = lg;
   const uint64_t rows_per_tile = (uint64_t)kU * (32 >> lg) * kWarps;
   const uint64_t nrows = row_end > row_begin ? row_end - row_begin : 0;
@@ -332,6 +265,10 @@ cudaError_t launch_scan_gemv(const RowsView &rv, const QueryView &qv, const Sear
   *nparts = grid;
   // queries per pass: as many as fit 100 KB of smem (2 CTAs/SM), at most 4
   int qb = qv.q >= 4 ? 4 : (qv.q >= 2 ? 2 : 1);
+  {
+    static const int force = [] { const char *e = getenv("ZVB200_GEMV_QB"); return e ? atoi(e) : 0; }();
+    if (force == 1 || force == 2 || force == 4) qb = std::min(force, qb);
+  }
   while (qb > 1 && gemv_smem(rv.dtype, rv.chunks, qb, sp.k) > 100 * 1024) qb >>= 1;
   const size_t smem = gemv_smem(rv.dtype, rv.chunks, qb, sp.k);
   if (smem > 220 * 1024) return cudaErrorInvalidValue;
@@ -368,9 +305,7 @@ cudaError_t launch_scan_lists(const RowsView &rv, const QueryView &qv, const Sea
   a.rv = rv; a.qv = qv; a.k = sp.k; a.threshold = sp.threshold; a.filter = sp.filter;
   a.row_begin = 0; a.row_end = rv.n; a.part = part; a.q0 = 0;
   a.seg_prefix = seg_prefix; a.seg_row = seg_row; a.seg_count = seg_count; a.seg_cap = seg_cap;
-  int lg = 0;
-  while ((2u << lg) <= rv.chunks && lg < 5) ++lg;
-  a.lpr_log2 = lg;
+  a.lpr_log2 = pick_lpr_log2(rv.chunks);
   const int grid = (int)scan_lists_parts(qv.q, sm_count);
   a.nparts = grid;
   *nparts = grid;

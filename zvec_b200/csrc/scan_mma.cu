@@ -457,7 +457,9 @@ cudaError_t launch_scan_mma(const RowsView &rv, const QueryView &qv, const Searc
   }
   *nparts = a.groups;
   CUtensorMap tmQ, tmX;
-  if (!make_map(&tmQ, qv.qraw, rv.d, qv.q, rv.row_stride, kQM)) return cudaErrorInvalidValue;
+  // the caller pads qraw with zero rows up to a whole tile when this is the last group of the batch
+  const uint64_t qrows = qv.qpad_rows ? (uint64_t)a.qtiles * kQM : qv.q;
+  if (!make_map(&tmQ, qv.qraw, rv.d, qrows, rv.row_stride, kQM)) return cudaErrorInvalidValue;
   if (!make_map(&tmX, rv.rows + row_begin * rv.row_stride, rv.d, std::max<uint64_t>(nrows, 1), rv.row_stride, kBN))
     return cudaErrorInvalidValue;
   cudaError_t e = cudaFuncSetAttribute(scan_mma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
