@@ -364,6 +364,17 @@ def run_ours(args):
     el_1 = e2e_timed(1, s1)
 
     if rank == 0:
+        def traffic(kernel, batch):
+            """measured DRAM bytes per launch (ncu capture committed under profiles/), when one exists for
+            exactly this kernel and shard shape; else null"""
+            try:
+                with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
+                    for e in json.load(f)["entries"]:
+                        if (e["kernel"], e["rows"], e["dim"], e["batch"]) == (kernel, nloc, DIM, batch):
+                            return e["bytes"]
+            except (OSError, ValueError, KeyError):
+                pass
+            return None
         qps_b = B * args.steps / (ms_b / 1e3)
         qps_1 = s1 / (ms_1 / 1e3)
         flops = 2.0 * nloc * DIM * B                       # per launch, this rank's shard
@@ -380,14 +391,14 @@ def run_ours(args):
                     "via": "zvb200_search (host buffers)" if world == 1 else
                            "pinned H2D + zvb200_search_device + NCCL all-gather + zvb200_merge_topk_device + D2H"},
             "roofline": {"bound": "tensor", "achieved": tf, "peak": pk["tf_sustained"], "unit": "TFLOP/s",
-                         "frac": tf / pk["tf_sustained"], "traffic": None, "kernel": kernel_b,
+                         "frac": tf / pk["tf_sustained"], "traffic": traffic(kernel_b, B), "kernel": kernel_b,
                          "kernel_ms": scan_b, "peak_source": pk["source"] + ", sustained bf16",
                          "algorithmic": "2*rows*dim*batch flop per launch = %.4g" % flops},
             "batch1": {"value": qps_1, "unit": "queries/s", "steps": s1, "ms_per_step": ms_1 / s1, "kernel": kernel_1,
                        "e2e": {"value": s1 / el_1, "unit": "queries/s", "h2d_bytes_per_step": DIM * 2,
                                "d2h_bytes_per_step": k * (8 if world == 1 else 12)},
                        "roofline": {"bound": "hbm", "achieved": gbs1, "peak": pk["hbm_gbs"], "unit": "GB/s",
-                                    "frac": gbs1 / pk["hbm_gbs"], "traffic": None, "kernel": kernel_1,
+                                    "frac": gbs1 / pk["hbm_gbs"], "traffic": traffic(kernel_1, 1), "kernel": kernel_1,
                                     "kernel_ms": scan_1, "peak_source": pk["source"],
                                     "algorithmic": "rows*dim*2 B per launch = %.4g" % shard_bytes}},
         }
