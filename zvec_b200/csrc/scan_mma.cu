@@ -23,6 +23,7 @@
 // every stored byte once per batch (the other QT-1 reads hit L2).
 #include <cuda.h>
 #include <stdlib.h>
+#include <stdio.h>
 
 #include "internal.h"
 #include "topk.cuh"
@@ -149,6 +150,12 @@ __host__ __device__ constexpr uint32_t make_idesc_f16(int M, int N) {
 
 __device__ __forceinline__ bool bit_set(const uint32_t *bm, uint32_t i) { return (bm[i >> 5] >> (i & 31)) & 1u; }
 
+// KR > 0: the epilogue keeps each query's top-k in KR REGISTER slots (k <= KR); KR == 0: in shared memory.
+// While the tensor pipe runs, tcgen05.mma operand fetch takes ~3/4 of the SM's shared-memory bandwidth
+// (48 KB per 128x256x64 block every ~520 cycles), and an epilogue LDS/STS queues behind it for hundreds
+// of cycles (measured: ~1000 cycles per accepted candidate with a shared-memory pool, tools/mma_probe.py
+// ZVB200_MMA_DEBUG=128) — so for small k the pool never touches shared memory.
+template <int KR>
 __global__ void __launch_bounds__(kThreads, 1)
 scan_mma_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmX, const MmaArgs a) {
   extern __shared__ uint8_t smem_raw[];
@@ -246,14 +253,26 @@ scan_mma_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
       }
     }
   } else if (warp >= 4) {
-    // ================= epilogue: thread-per-query filter + private sorted list =================
+    // ================= epilogue: thread-per-query filter + private top-k pool =================
     const int ew = warp - 4;
     const int slot = ew * 32 + lane;
     const bool qvalid = q0 + slot < a.nq;
     u64 *L = lists + slot;  // entry i at L[i * kQM]: lanes of a warp hit consecutive banks
     const int mode = a.mode;
     const int K = (int)k;
-    int cnt = 0;
+    // The pool is UNSORTED: the k smallest keys accepted so far, with the position of the largest
+    // cached.  Accepting a key replaces the largest and rescans the pool for the new one — k
+    // independent shared-memory loads, instead of the dependent load/compare/store chain of a
+    // sorted insertion (ailego Heap::emplace, heap.h:103-115, keeps a heap for the same reason).
+    // The partial lists leave unsorted; merge_parts does not need order.
+    int cnt = 0, maxpos = 0;
+    // KR > 0: R[] ascending; the KR - k slots in front hold 0 (never displaced), the rest start at kMaxKey.
+    u64 R[KR > 0 ? KR : 1];
+    const int rfirst = KR - K;
+    if (KR > 0) {
+#pragma unroll
+      for (int i = 0; i < KR; ++i) R[i] = i < rfirst ? 0ull : kMaxKey;
+    }
     // Accept a key only if it is < tau_key = min(threshold gate, this CTA's k-th best, union bound).
     // Union bound: every CTA scanning this query publishes the score of its pub_j-th best row
     // (one word, only ever decreasing).  CTAs hold disjoint rows, so the pub_m-th smallest of the
@@ -265,7 +284,7 @@ scan_mma_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
     const uint32_t qcol = qvalid ? q0 + slot : q0;
     volatile uint32_t *my_pub = a.pub + (size_t)grp * a.nq + qcol;
     uint32_t pub_val = 0xffffffffu;
-    const int pubj = (int)a.pub_j - 1;
+    const int pubj = (int)a.pub_j;  // 1-based; pubj == K publishes the pool's largest once it is full
     // fast filter on the raw dot product: pass iff dot >= dthr (conservative for cosine)
     auto dthr_of = [&](u64 tk) -> float {
       if (!qvalid) return __int_as_float(0x7f800000);
@@ -275,17 +294,83 @@ scan_mma_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
       return t - (fabsf(t) + fabsf(tau_f) + 1.0f) * 2.4e-7f;
     };
     float dthr = dthr_of(tau_key);
+    auto accept = [&](u64 key) {
+      if (KR > 0) {
+        // position-based insertion, every slot decided independently: slot i takes its lower neighbour
+        // if the key goes below that one, the key itself if it lands here, else keeps its entry
+#pragma unroll
+        for (int i = KR - 1; i >= 1; --i) R[i] = key < R[i - 1] ? R[i - 1] : (key < R[i] ? key : R[i]);
+        R[0] = key < R[0] ? key : R[0];
+        const u64 nt = R[KR - 1];
+        if (nt < tau_key) { tau_key = nt; dthr = dthr_of(nt); }
+        return;
+      }
+      if (cnt < K) {
+        L[(size_t)cnt * kQM] = key;
+        if (++cnt < K) return;
+      } else {
+        L[(size_t)maxpos * kQM] = key;
+      }
+      u64 mx = 0;
+      int mp = 0;
+#pragma unroll 16
+      for (int i = 0; i < K; ++i) {
+        const u64 x = L[(size_t)i * kQM];
+        if (x > mx) { mx = x; mp = i; }
+      }
+      maxpos = mp;
+      if (mx < tau_key) { tau_key = mx; dthr = dthr_of(mx); }
+    };
+    auto publish = [&]() {  // score word of this CTA's pub_j-th best, once it has that many rows
+      uint32_t pv = 0xffffffffu;
+      if (KR > 0) {
+        // masked OR, not a select chain: the compiler turns the latter into R[dynamic] and R into local memory
+        uint32_t acc = 0;
+#pragma unroll
+        for (int i = 0; i < KR; ++i) acc |= (uint32_t)(R[i] >> 32) & (0u - (uint32_t)(i == rfirst + pubj - 1));
+        pv = acc;
+      } else if (cnt < pubj) {
+        return;
+      } else if (pubj == K) {
+        pv = (uint32_t)(L[(size_t)maxpos * kQM] >> 32);
+      } else {           // pub_j <= 8: the pub_j-th smallest score word of the pool
+        uint32_t sel[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) sel[i] = 0xffffffffu;
+        for (int e = 0; e < cnt; ++e) {
+          uint32_t x = (uint32_t)(L[(size_t)e * kQM] >> 32);
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            const uint32_t lo = min(sel[i], x);
+            x = max(sel[i], x);
+            sel[i] = lo;
+          }
+        }
+        pv = sel[0];
+#pragma unroll
+        for (int i = 1; i < 8; ++i) pv = pubj == i + 1 ? sel[i] : pv;
+      }
+      if (pv != pub_val) { pub_val = pv; *my_pub = pv; }
+    };
     auto union_bound = [&]() {
       uint32_t best[16];
 #pragma unroll
       for (int i = 0; i < 16; ++i) best[i] = 0xffffffffu;
-      for (uint32_t g = 0; g < a.groups; ++g) {
-        uint32_t x = *reinterpret_cast<volatile uint32_t *>(a.pub + (size_t)g * a.nq + qcol);
+      for (uint32_t g0 = 0; g0 < a.groups; g0 += 8) {
+        uint32_t x[8];
 #pragma unroll
-        for (int i = 0; i < 16; ++i) {  // sorted insert: best[] keeps the 16 smallest, ascending
-          const uint32_t lo = min(best[i], x);
-          x = max(best[i], x);
-          best[i] = lo;
+        for (int u = 0; u < 8; ++u)  // the loads first, so their latencies overlap
+          x[u] = g0 + u < a.groups ? *reinterpret_cast<volatile uint32_t *>(a.pub + (size_t)(g0 + u) * a.nq + qcol)
+                                   : 0xffffffffu;
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+          uint32_t y = x[u];
+#pragma unroll
+          for (int i = 0; i < 16; ++i) {  // sorted insert: best[] keeps the 16 smallest, ascending
+            const uint32_t lo = min(best[i], y);
+            y = max(best[i], y);
+            best[i] = lo;
+          }
         }
       }
       uint32_t b = best[0];
@@ -295,11 +380,18 @@ scan_mma_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
       if (gk < tau_key) { tau_key = gk; dthr = dthr_of(tau_key); }
     };
     uint32_t next_eval = 1;
+    const bool prof = (a.dbg & 128) != 0;  // triage: where the epilogue's cycles go (printed by CTA 0)
+    long long c_wait = 0, c_slow = 0, c_ub = 0, c_t0 = 0, c_first4 = 0, c_tiles = 0;
+    uint32_t n_slow = 0, n_ev = 0;
+    const long long c_begin = prof ? clock64() : 0;
 
     for (uint32_t t = 0; t < ntl; ++t) {
       const uint32_t as = t & 1, aphase = (t >> 1) & 1;
       const uint32_t row0 = a.row_begin + (t_begin + t) * kBN;
+      const long long c0w = prof ? clock64() : 0;
       mbar_wait(bar_tfull + 8 * as, aphase);
+      if (prof) c_wait += clock64() - c0w;
+      const long long c_tile = prof ? clock64() : 0;
       tc_fence_after();
       const uint32_t taddr = tmem_base + ((uint32_t)(ew * 32) << 16) + as * kBN;
 #pragma unroll 1
@@ -310,56 +402,79 @@ scan_mma_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
         float mx = __uint_as_float(v[0]);
 #pragma unroll
         for (int j = 1; j < 32; ++j) mx = fmaxf(mx, __uint_as_float(v[j]));
-        if (mx >= dthr && !(a.dbg & 16)) {
-          // rare: some of this query's 32 scores may enter its top-k
+        if (__any_sync(FULL, mx >= dthr) && !(a.dbg & 16)) {
+          // rare once the bounds are warm: some query of this warp has a candidate among its 32 scores.
+          // The warp walks the UNION of its lanes' candidate columns (one copy of the accept code,
+          // a warp-uniform column index), each lane acting only on its own candidates.
+          const long long c0s = prof ? clock64() : 0;
+          if (prof) ++n_slow;
+          uint32_t m = 0;
 #pragma unroll
-          for (int j = 0; j < 32; ++j) {
-            const float dv = __uint_as_float(v[j]);
-            if (dv >= dthr) {
-              const float s = mode == 0 ? -dv : 1.0f - dv;
-              const uint32_t row = row0 + c0 + j;
-              const u64 key = pack_key(s, row);
-              bool p = key < tau_key && row < a.row_end;
-              if (p && a.drop) p = !bit_set(a.drop, row);
-              if (p && a.filter) p = !bit_set(a.filter, row);
-              if (p) {
-                // insertion into the sorted list (ailego Heap::emplace + sort, heap.h:103-115,173-175)
-                int i = cnt < K ? cnt : K - 1;
-                while (i > 0) {
-                  const u64 prev = L[(size_t)(i - 1) * kQM];
-                  if (prev < key) break;
-                  L[(size_t)i * kQM] = prev;
-                  --i;
-                }
-                L[(size_t)i * kQM] = key;
-                if (cnt < K) ++cnt;
-                if (cnt == K) {
-                  const u64 nt = L[(size_t)(K - 1) * kQM];
-                  if (nt < tau_key) { tau_key = nt; dthr = dthr_of(nt); }
-                }
-                if (i <= pubj && cnt > pubj) {
-                  const uint32_t pv = (uint32_t)(L[(size_t)pubj * kQM] >> 32);
-                  if (pv != pub_val) { pub_val = pv; *my_pub = pv; }
-                }
+          for (int j = 0; j < 32; ++j) m |= (__uint_as_float(v[j]) >= dthr ? 1u : 0u) << j;
+          uint32_t wm = __reduce_or_sync(FULL, m);
+          while (wm) {
+            const int j = __ffs(wm) - 1;
+            wm &= wm - 1;
+            if (prof) ++n_ev;
+            if ((m >> j) & 1u) {
+              uint32_t raw;
+              switch (j) {  // warp-uniform: a jump, not a local-memory index
+#define ZVB_PICK(J) case J: raw = v[J]; break;
+                ZVB_PICK(0) ZVB_PICK(1) ZVB_PICK(2) ZVB_PICK(3) ZVB_PICK(4) ZVB_PICK(5) ZVB_PICK(6) ZVB_PICK(7)
+                ZVB_PICK(8) ZVB_PICK(9) ZVB_PICK(10) ZVB_PICK(11) ZVB_PICK(12) ZVB_PICK(13) ZVB_PICK(14) ZVB_PICK(15)
+                ZVB_PICK(16) ZVB_PICK(17) ZVB_PICK(18) ZVB_PICK(19) ZVB_PICK(20) ZVB_PICK(21) ZVB_PICK(22) ZVB_PICK(23)
+                ZVB_PICK(24) ZVB_PICK(25) ZVB_PICK(26) ZVB_PICK(27) ZVB_PICK(28) ZVB_PICK(29) ZVB_PICK(30)
+                default: raw = v[31]; break;
+#undef ZVB_PICK
+              }
+              const float dv = __uint_as_float(raw);
+              if (dv >= dthr) {  // dthr may have tightened since the mask was built
+                const float s = mode == 0 ? -dv : 1.0f - dv;
+                const uint32_t row = row0 + c0 + j;
+                const u64 key = pack_key(s, row);
+                bool p = key < tau_key && row < a.row_end;
+                if (p && a.drop) p = !bit_set(a.drop, row);
+                if (p && a.filter) p = !bit_set(a.filter, row);
+                if (p) accept(key);
               }
             }
+            __syncwarp();
           }
+          if (prof) c_slow += clock64() - c0s;
         }
+      }
+      if (prof) {
+        const long long dt = clock64() - c_tile;
+        if (t == 0) c_t0 = dt;
+        if (t < 4) c_first4 += dt;
+        c_tiles += dt;
       }
       // accumulator stage drained: hand it back to the MMA warp
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(bar_tempty + 8 * as);
       // off the MMA's critical path: refresh the union bound at tiles 1,2,3,4,6,9,13,19,... of this CTA
-      if (a.groups > 1 && t + 1 == next_eval) {
+      if (a.groups > 1 && t + 1 == next_eval && !(a.dbg & 32)) {
+        const long long c0u = prof ? clock64() : 0;
+        publish();
         union_bound();
+        if (prof) c_ub += clock64() - c0u;
         next_eval += max(1u, next_eval >> 1);
       }
     }
-    // write this CTA's partial lists: part[q][grp][0..k)
+    if (prof && blockIdx.x == 0 && lane == 0)
+      printf("cta0 warp%d: total %lld  wait %lld  slow %lld (%u chunks, %u column events)  union %lld  tile0 %lld  first4 %lld  all tiles %lld (%u)\n",
+             warp, clock64() - c_begin, c_wait, c_slow, n_slow, n_ev, c_ub, c_t0, c_first4, c_tiles, ntl);
+    // write this CTA's partial lists (unsorted): part[q][grp][0..k)
     if (qvalid) {
       u64 *dst = a.part + ((size_t)(q0 + slot) * a.groups + grp) * k;
-      for (int i = 0; i < K; ++i) dst[i] = i < cnt ? L[(size_t)i * kQM] : kMaxKey;
+      if (KR > 0) {
+#pragma unroll
+        for (int i = 0; i < KR; ++i)
+          if (i >= rfirst) dst[i - rfirst] = R[i];
+      } else {
+        for (int i = 0; i < K; ++i) dst[i] = i < cnt ? L[(size_t)i * kQM] : kMaxKey;
+      }
     }
   }
 
@@ -450,6 +565,7 @@ cudaError_t launch_scan_mma(const RowsView &rv, const QueryView &qv, const Searc
     const uint32_t mmax = std::min<uint32_t>(a.groups, 16u);
     a.pub_j = (sp.k + mmax - 1) / mmax;
     a.pub_m = (sp.k + a.pub_j - 1) / a.pub_j;
+    if (a.pub_j > 8) { a.pub_j = sp.k; a.pub_m = 1; }  // few groups, large k: share the pools' k-th bests
   }
   {
     static const int dbg = [] { const char *e = getenv("ZVB200_MMA_DEBUG"); return e ? atoi(e) : 0; }();
@@ -462,7 +578,8 @@ cudaError_t launch_scan_mma(const RowsView &rv, const QueryView &qv, const Searc
   if (!make_map(&tmQ, qv.qraw, rv.d, qrows, rv.row_stride, kQM)) return cudaErrorInvalidValue;
   if (!make_map(&tmX, rv.rows + row_begin * rv.row_stride, rv.d, std::max<uint64_t>(nrows, 1), rv.row_stride, kBN))
     return cudaErrorInvalidValue;
-  cudaError_t e = cudaFuncSetAttribute(scan_mma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  auto kern = sp.k <= 8 ? scan_mma_kernel<8> : sp.k <= 16 ? scan_mma_kernel<16> : scan_mma_kernel<0>;
+  cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return e;
   if (nrows == 0) {
     // nothing to scan: every partial list is empty
@@ -470,7 +587,7 @@ cudaError_t launch_scan_mma(const RowsView &rv, const QueryView &qv, const Searc
   }
   e = cudaMemsetAsync(pub, 0xff, (size_t)qv.q * a.groups * sizeof(uint32_t), st);
   if (e != cudaSuccess) return e;
-  scan_mma_kernel<<<a.groups * a.qtiles, kThreads, smem, st>>>(tmQ, tmX, a);
+  kern<<<a.groups * a.qtiles, kThreads, smem, st>>>(tmQ, tmX, a);
   count_launch();
   return cudaGetLastError();
 }
