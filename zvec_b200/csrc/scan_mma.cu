@@ -133,6 +133,16 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&v)[32]) {
       : "memory");
 }
 __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+__device__ __forceinline__ uint32_t tmem_ld1(uint32_t taddr) {  // one column of this warp's 32 lanes, waited for
+  uint32_t r;
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x1.b32 {%0}, [%1];\n\t"
+      "tcgen05.wait::ld.sync.aligned;"
+      : "=r"(r)
+      : "r"(taddr)
+      : "memory");
+  return r;
+}
 
 // Shared-memory matrix descriptor, K-major, 128-byte swizzle: 8-row groups are 1024 B apart
 // (SBO), one swizzle atom along K (LBO unused), descriptor version 1 (sm_100).
@@ -350,9 +360,9 @@ scan_mma_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
 #pragma unroll
         for (int i = 1; i < 8; ++i) pv = pubj == i + 1 ? sel[i] : pv;
       }
-      if (pv != pub_val) { pub_val = pv; *my_pub = pv; }
+      if (pv < pub_val) { pub_val = pv; *my_pub = pv; }
     };
-    auto union_bound = [&]() {
+    auto union_bound = [&]() -> bool {
       uint32_t best[16];
 #pragma unroll
       for (int i = 0; i < 16; ++i) best[i] = 0xffffffffu;
@@ -378,8 +388,12 @@ scan_mma_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
       for (int i = 1; i < 16; ++i) b = (int)a.pub_m == i + 1 ? best[i] : b;
       const u64 gk = ((u64)b << 32) | 0xffffffffu;
       if (gk < tau_key) { tau_key = gk; dthr = dthr_of(tau_key); }
+      return b != 0xffffffffu;
     };
     uint32_t next_eval = 1;
+    // the first-tile bootstrap needs every row of that tile to be a live row
+    const bool boot = a.groups > 1 && pubj <= 8 && !a.drop && !a.filter && ntl > 1 &&
+                      a.row_begin + (t_begin + 1) * kBN <= a.row_end && !(a.dbg & (1 | 16 | 32 | 64));
     const bool prof = (a.dbg & 128) != 0;  // triage: where the epilogue's cycles go (printed by CTA 0)
     long long c_wait = 0, c_slow = 0, c_ub = 0, c_t0 = 0, c_first4 = 0, c_tiles = 0;
     uint32_t n_slow = 0, n_ev = 0;
@@ -394,6 +408,42 @@ scan_mma_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
       const long long c_tile = prof ? clock64() : 0;
       tc_fence_after();
       const uint32_t taddr = tmem_base + ((uint32_t)(ew * 32) << 16) + as * kBN;
+      if (t == 0 && boot) {
+        // Bootstrap.  With empty pools every score of the first tile is a candidate and the warp pays one
+        // accept per COLUMN (256 of them, ~10% of a 1.25M-row shard's run time).  Instead: a first pass
+        // over the tile takes only the best score of each 32-column chunk (8 distinct rows), publishes the
+        // pub_j-th best of those, and waits briefly for the other CTAs scanning this query to do the same;
+        // the union bound over G x 8 rows then lets the exact pass below skip almost every column.
+        // The wait is bounded and only about speed: a late CTA just starts with a looser bound.
+        uint32_t cm[8];  // ascending: the 8 chunk bests as score words
+#pragma unroll
+        for (int i = 0; i < 8; ++i) cm[i] = 0xffffffffu;
+#pragma unroll 1
+        for (int c = 0; c < kBN; c += 32) {
+          uint32_t v[32];
+          tmem_ld32(taddr + c, v);
+          tmem_ld_wait();
+          float mx = __uint_as_float(v[0]);
+#pragma unroll
+          for (int j = 1; j < 32; ++j) mx = fmaxf(mx, __uint_as_float(v[j]));
+          uint32_t x = order_f32(mode == 0 ? -mx : 1.0f - mx);
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            const uint32_t lo = min(cm[i], x);
+            x = max(cm[i], x);
+            cm[i] = lo;
+          }
+        }
+        uint32_t pv = 0;
+#pragma unroll
+        for (int i = 0; i < 8; ++i) pv |= cm[i] & (0u - (uint32_t)(i == pubj - 1));
+        if (qvalid && pv < pub_val) { pub_val = pv; *my_pub = pv; }
+        for (int tries = 0; tries < 8; ++tries) {
+          const bool ready = union_bound() || !qvalid;
+          if (__all_sync(FULL, ready)) break;
+          __nanosleep(256);
+        }
+      }
 #pragma unroll 1
       for (int c0 = 0; c0 < ((a.dbg & 1) ? 0 : kBN); c0 += 32) {
         uint32_t v[32];
@@ -416,17 +466,10 @@ scan_mma_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
             const int j = __ffs(wm) - 1;
             wm &= wm - 1;
             if (prof) ++n_ev;
+            // the column again, straight from TMEM (collective, warp-uniform address): indexing v[] with a
+            // run-time j would cost a branch tree or local memory
+            const uint32_t raw = tmem_ld1(taddr + c0 + j);
             if ((m >> j) & 1u) {
-              uint32_t raw;
-              switch (j) {  // warp-uniform: a jump, not a local-memory index
-#define ZVB_PICK(J) case J: raw = v[J]; break;
-                ZVB_PICK(0) ZVB_PICK(1) ZVB_PICK(2) ZVB_PICK(3) ZVB_PICK(4) ZVB_PICK(5) ZVB_PICK(6) ZVB_PICK(7)
-                ZVB_PICK(8) ZVB_PICK(9) ZVB_PICK(10) ZVB_PICK(11) ZVB_PICK(12) ZVB_PICK(13) ZVB_PICK(14) ZVB_PICK(15)
-                ZVB_PICK(16) ZVB_PICK(17) ZVB_PICK(18) ZVB_PICK(19) ZVB_PICK(20) ZVB_PICK(21) ZVB_PICK(22) ZVB_PICK(23)
-                ZVB_PICK(24) ZVB_PICK(25) ZVB_PICK(26) ZVB_PICK(27) ZVB_PICK(28) ZVB_PICK(29) ZVB_PICK(30)
-                default: raw = v[31]; break;
-#undef ZVB_PICK
-              }
               const float dv = __uint_as_float(raw);
               if (dv >= dthr) {  // dthr may have tightened since the mask was built
                 const float s = mode == 0 ? -dv : 1.0f - dv;
