@@ -407,7 +407,8 @@ static int search_core(zvb200_ctx *c, zvb200_store *s, const void *queries_dev, 
                        uint32_t *out_index_dev, uint64_t row_begin, uint64_t row_end) {
   RowsView rv = s->view();
   const uint32_t esz = s->dtype == ZVB200_DT_FP32 ? 4 : s->dtype == ZVB200_DT_FP16 ? 2 : 1;
-  const size_t qf32_bytes = s->dtype == ZVB200_DT_INT8 ? 0 : (size_t)q * (s->chunks * 16 / esz) * 4;
+  const size_t qf32_row = (size_t)(s->chunks * 16 / esz) * 4;
+  const size_t qf32_bytes = s->dtype == ZVB200_DT_INT8 ? 0 : (size_t)((q + 127u) & ~127u) * qf32_row;
   // raw queries are padded with zero rows to a whole number of 128-query tiles: the tensor-core
   // scan's TMA box then never leaves the tensor (out-of-range boxes are filled much more slowly)
   const uint32_t qpad = (q + 127u) & ~127u;
@@ -418,13 +419,15 @@ static int search_core(zvb200_ctx *c, zvb200_store *s, const void *queries_dev, 
   CU(c->qnorms.ensure((size_t)q * sizeof(float)));
   if (qraw_bytes && qpad > q)
     CU(cudaMemsetAsync((uint8_t *)c->qraw.p + (size_t)q * s->row_stride, 0, (size_t)(qpad - q) * s->row_stride, c->stream));
+  if (s->dtype == ZVB200_DT_FP32 && qpad > q)
+    CU(cudaMemsetAsync((uint8_t *)c->qf32.p + (size_t)q * qf32_row, 0, (size_t)(qpad - q) * qf32_row, c->stream));
   CU(launch_prep_queries(rv, queries_dev, q, s->elem_bytes, (float *)c->qf32.p, (uint8_t *)c->qraw.p,
                          (float4 *)c->qtails.p, (float *)c->qnorms.p, c->stream));
   QueryView qv;
   qv.qf32 = (const float *)c->qf32.p; qv.qraw = (const uint8_t *)c->qraw.p;
   qv.qtails = (const float4 *)c->qtails.p; qv.qnorms = (const float *)c->qnorms.p;
   qv.q = q;
-  qv.qpad_rows = qraw_bytes != 0;
+  qv.qpad_rows = s->dtype != ZVB200_DT_INT8;
   c->last_qv = qv;  // the IVF list scan reuses the prepared queries
   SearchParams sp;
   sp.k = k; sp.threshold = threshold; sp.filter = filter_dev;
@@ -434,9 +437,12 @@ static int search_core(zvb200_ctx *c, zvb200_store *s, const void *queries_dev, 
   // batch 1 streams best through the GEMV scan; from 2 queries on the tensor-core scan wins where it
   // applies (it is HBM-bound below ~200 queries and reads the rows once for the whole batch)
   const bool stream_ok = scan_stream_supports(rv, k, 0);
-  if (which == 0) which = mma_ok ? 3 : (q <= 4) ? 1 : scan_tile_supports(k) ? 2 : 1;
+  // tensor cores: fp16 InnerProduct / Cosine at any batch (scores straight from the accumulator); fp16 L2 and
+  // fp32 (tf32 filter + exact re-score) from 5 queries on — below that the streaming scan is as fast and simpler
+  const bool mma_direct = mma_ok && s->dtype == ZVB200_DT_FP16 && !metric_is_l2(s->metric);
+  if (which == 0) which = (mma_direct || (mma_ok && q > 4)) ? 3 : (q <= 4) ? 1 : scan_tile_supports(k) ? 2 : 1;
   if (which == 4 && !stream_ok) which = 1;
-  if (which == 3 && !mma_ok) return set_err(ZVB200_ERR_UNSUPPORTED, "tcgen05 scan: fp16 InnerProduct/Cosine, k <= 128 only");
+  if (which == 3 && !mma_ok) return set_err(ZVB200_ERR_UNSUPPORTED, "tcgen05 scan: fp16 / fp32 stores, k <= 128 only");
   if (which == 2 && !scan_tile_supports(k)) which = 1;
   const size_t maxparts = which == 1 ? scan_gemv_max_parts(s->sm_count)
                           : which == 2 ? scan_tile_max_parts(s->sm_count)

@@ -25,6 +25,7 @@
 #include <stdlib.h>
 #include <stdio.h>
 
+#include "chunk.cuh"
 #include "internal.h"
 #include "topk.cuh"
 
@@ -50,7 +51,16 @@ struct MmaArgs {
   uint32_t nkb;         // k-blocks of 64 halves
   uint32_t k, nstage;
   uint32_t row_begin, row_end;  // global row numbers (tensor map B starts at row_begin)
-  int mode;             // 0: s = -dot (InnerProduct), 1: s = 1 - dot (Cosine)
+  int mode;             // 0: s = -dot (InnerProduct), 1: s = 1 - dot (Cosine) straight from the accumulator;
+                        // 2/3/4: L2 / InnerProduct / Cosine with the accumulator as a FILTER and an exact re-score
+  int metric;           // ZVB200_METRIC_* (the exact re-score's formula)
+  const uint8_t *rows;  // store rows (absolute row 0), row_stride bytes apart, `chunks` 16-byte chunks each
+  uint32_t row_stride, chunks;
+  const float *qf32;    // queries widened to fp32, qstride floats apart
+  uint32_t qstride;
+  const float *norms;   // |x|^2 per stored row (absolute row index)
+  const float *qnorms;  // |q|^2 per query
+  float eps;            // |accumulator - exact dot| <= eps * (|x|^2 + |q|^2) / 2
   float threshold;
   const uint32_t *drop, *filter;
   u64 *part;            // [nq][groups][k]
@@ -117,6 +127,15 @@ __device__ __forceinline__ void umma_f16(uint32_t d_tmem, uint64_t adesc, uint64
       "r"(idesc), "r"(accumulate)
       : "memory");
 }
+__device__ __forceinline__ void umma_tf32(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc, uint32_t idesc,
+                                          uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}" ::"r"(d_tmem), "l"(adesc), "l"(bdesc),
+      "r"(idesc), "r"(accumulate)
+      : "memory");
+}
 __device__ __forceinline__ void umma_commit(uint32_t bar) {
   asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
 }
@@ -158,14 +177,38 @@ __host__ __device__ constexpr uint32_t make_idesc_f16(int M, int N) {
   return (1u << 4) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
 }
 
-__device__ __forceinline__ bool bit_set(const uint32_t *bm, uint32_t i) { return (bm[i >> 5] >> (i & 31)) & 1u; }
+// kind::tf32: fp32 words in shared memory, the tensor core reads the top 19 bits; fp32 accumulate.
+__host__ __device__ constexpr uint32_t make_idesc_tf32(int M, int N) {
+  return (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
+}
+
+// Exact score of (row, query) by the whole warp, same arithmetic as K1 (scan_gemv.cu) with 32 lanes per
+// row: fp32 FMA over 16-byte chunks, xor-shuffle tree.  Result on every lane.
+template <int DT>
+__device__ __forceinline__ float exact_score(const MmaArgs &a, uint32_t row, uint32_t qidx, int lane) {
+  const uint8_t *rp = a.rows + (size_t)row * a.row_stride;
+  const uint8_t *qp = reinterpret_cast<const uint8_t *>(a.qf32 + (size_t)qidx * a.qstride);
+  float acc = 0.f, aa = 0.f;
+  if (metric_is_l2(a.metric)) {
+    for (uint32_t c = lane; c < a.chunks; c += 32)
+      Chunk<DT, true>::fma(acc, aa, __ldg(reinterpret_cast<const uint4 *>(rp) + c), qp, c);
+  } else {
+    for (uint32_t c = lane; c < a.chunks; c += 32)
+      Chunk<DT, false>::fma(acc, aa, __ldg(reinterpret_cast<const uint4 *>(rp) + c), qp, c);
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(FULL, acc, o);
+  return a.metric == ZVB200_METRIC_L2SQ ? acc : a.metric == ZVB200_METRIC_L2 ? sqrtf(acc)
+         : a.metric == ZVB200_METRIC_IP ? -acc : 1.0f - acc;
+}
 
 // KR > 0: the epilogue keeps each query's top-k in KR REGISTER slots (k <= KR); KR == 0: in shared memory.
 // While the tensor pipe runs, tcgen05.mma operand fetch takes ~3/4 of the SM's shared-memory bandwidth
 // (48 KB per 128x256x64 block every ~520 cycles), and an epilogue LDS/STS queues behind it for hundreds
 // of cycles (measured: ~1000 cycles per accepted candidate with a shared-memory pool, tools/mma_probe.py
 // ZVB200_MMA_DEBUG=128) — so for small k the pool never touches shared memory.
-template <int KR>
+// KIND 0: fp16 rows, kind::f16 (64 halves per 128-byte k-block); KIND 1: fp32 rows, kind::tf32 (32 floats).
+template <int KIND, int KR>
 __global__ void __launch_bounds__(kThreads, 1)
 scan_mma_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmX, const MmaArgs a) {
   extern __shared__ uint8_t smem_raw[];
@@ -186,6 +229,8 @@ scan_mma_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
   u64 *lists = reinterpret_cast<u64 *>(sbase + (size_t)nstage * kStage);      // [k][128]: entry i of query s at i*128+s
   uint64_t *bars = reinterpret_cast<uint64_t *>(lists + (size_t)kQM * k);     // full[ns] empty[ns] tfull[2] tempty[2]
   uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + 2 * nstage + 4);
+  float *colc = reinterpret_cast<float *>(tmem_slot + 4);                      // [2][kBN] per-column constants
+  constexpr int kBKe = KIND == 0 ? 64 : 32;                                    // elements per 128-byte k-block
   const uint32_t bar_full = smem_u32(bars), bar_empty = bar_full + 8 * nstage;
   const uint32_t bar_tfull = bar_empty + 8 * nstage, bar_tempty = bar_tfull + 16;
 
@@ -226,14 +271,14 @@ scan_mma_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
           const uint32_t sa = base + stage * kStage, sb = sa + kStageA;
           if (a.dbg & 14) {
             if (a.dbg & 2) { mbar_arrive(bar_full + 8 * stage); }
-            else if (a.dbg & 4) { mbar_expect_tx(bar_full + 8 * stage, kStageA); tma_load_2d_hint(sa, &tmQ, bar_full + 8 * stage, (int)(kb * kBK), (int)q0, 0x14F0000000000000ull); }
-            else { mbar_expect_tx(bar_full + 8 * stage, kStageB); tma_load_2d(sb, &tmX, bar_full + 8 * stage, (int)(kb * kBK), row_c); }
+            else if (a.dbg & 4) { mbar_expect_tx(bar_full + 8 * stage, kStageA); tma_load_2d_hint(sa, &tmQ, bar_full + 8 * stage, (int)(kb * kBKe), (int)q0, 0x14F0000000000000ull); }
+            else { mbar_expect_tx(bar_full + 8 * stage, kStageB); tma_load_2d(sb, &tmX, bar_full + 8 * stage, (int)(kb * kBKe), row_c); }
             if (++stage == nstage) { stage = 0; phase ^= 1; }
             continue;
           }
           mbar_expect_tx(bar_full + 8 * stage, kStage);
-          tma_load_2d_hint(sa, &tmQ, bar_full + 8 * stage, (int)(kb * kBK), (int)q0, 0x14F0000000000000ull);
-          tma_load_2d(sb, &tmX, bar_full + 8 * stage, (int)(kb * kBK), row_c);
+          tma_load_2d_hint(sa, &tmQ, bar_full + 8 * stage, (int)(kb * kBKe), (int)q0, 0x14F0000000000000ull);
+          tma_load_2d(sb, &tmX, bar_full + 8 * stage, (int)(kb * kBKe), row_c);
           if (++stage == nstage) { stage = 0; phase ^= 1; }
         }
       }
@@ -241,7 +286,7 @@ scan_mma_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
   } else if (warp == 1) {
     // ================= MMA issuer =================
     if (lane == 0) {
-      constexpr uint32_t idesc = make_idesc_f16(kQM, kBN);
+      constexpr uint32_t idesc = KIND == 0 ? make_idesc_f16(kQM, kBN) : make_idesc_tf32(kQM, kBN);
       uint32_t stage = 0, phase = 0;
       for (uint32_t t = 0; t < ntl; ++t) {
         const uint32_t as = t & 1, aphase = (t >> 1) & 1;
@@ -254,8 +299,10 @@ scan_mma_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
           const uint32_t sa = base + stage * kStage, sb = sa + kStageA;
           const uint64_t da = make_desc_sw128(sa), db = make_desc_sw128(sb);
 #pragma unroll
-          for (uint32_t kk = 0; kk < kBK / 16; ++kk)
-            umma_f16(d_tmem, da + 2 * kk, db + 2 * kk, idesc, (kb | kk) != 0);
+          for (uint32_t kk = 0; kk < 4; ++kk) {  // four 32-byte K slices per 128-byte k-block
+            if (KIND == 0) umma_f16(d_tmem, da + 2 * kk, db + 2 * kk, idesc, (kb | kk) != 0);
+            else umma_tf32(d_tmem, da + 2 * kk, db + 2 * kk, idesc, (kb | kk) != 0);
+          }
           umma_commit(bar_empty + 8 * stage);  // frees the stage when these MMAs retire
           if (++stage == nstage) { stage = 0; phase ^= 1; }
         }
@@ -295,13 +342,35 @@ scan_mma_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
     volatile uint32_t *my_pub = a.pub + (size_t)grp * a.nq + qcol;
     uint32_t pub_val = 0xffffffffu;
     const int pubj = (int)a.pub_j;  // 1-based; pubj == K publishes the pool's largest once it is full
-    // fast filter on the raw dot product: pass iff dot >= dthr (conservative for cosine)
+    // Fast filter: column value f = accumulator + colc[column]; a column is a candidate iff f >= dthr.
+    //   mode 0/1: colc = 0, dthr from the score bound directly (conservative for cosine).
+    //   mode 2 (L2): exact s = |x|^2 + |q|^2 - 2 x.q <= T  <=>  x.q - hx >= hq - T/2 (hx = |x|^2/2, hq = |q|^2/2);
+    //     the accumulator is within eps (hx + hq) of x.q, so colc = -(1 - eps) hx and dthr = hq - T/2 - eps hq.
+    //   mode 3/4 (IP / cosine through tf32): colc = +eps hx, dthr = (-T | 1 - T) - eps hq.
+    // Modes 2-4 never use f as a score: a candidate is re-scored exactly (exact_score) before it is offered.
+    const bool resc = mode >= 2;
+    const float hq = (resc && qvalid) ? 0.5f * a.qnorms[q0 + slot] : 0.f;
     auto dthr_of = [&](u64 tk) -> float {
       if (!qvalid) return __int_as_float(0x7f800000);
       const float tau_f = unorder_f32((uint32_t)(tk >> 32));
       if (mode == 0) return -tau_f;
-      const float t = 1.0f - tau_f;
-      return t - (fabsf(t) + fabsf(tau_f) + 1.0f) * 2.4e-7f;
+      if (mode == 1) {
+        const float t = 1.0f - tau_f;
+        return t - (fabsf(t) + fabsf(tau_f) + 1.0f) * 2.4e-7f;
+      }
+      if (mode == 2) {
+        const float T = a.metric == ZVB200_METRIC_L2 ? tau_f * tau_f * 1.000001f : tau_f;
+        const float hT = 0.5f * T;
+        return hq - hT - a.eps * hq - (hq + fabsf(hT)) * 4.8e-7f;
+      }
+      const float b = mode == 3 ? -tau_f : 1.0f - tau_f;
+      return b - a.eps * hq - (fabsf(b) + fabsf(tau_f) + 1.0f) * 4.8e-7f;
+    };
+    // per-column constants of the rows of a tile (modes 2-4), fetched one tile ahead by the epilogue threads
+    auto cval = [&](uint32_t row) -> float {
+      if (row >= a.row_end) return __int_as_float(0xff800000);  // never a candidate
+      const float hx = 0.5f * a.norms[row];
+      return mode == 2 ? -(1.0f - a.eps) * hx : a.eps * hx;
     };
     float dthr = dthr_of(tau_key);
     auto accept = [&](u64 key) {
@@ -392,8 +461,15 @@ scan_mma_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
     };
     uint32_t next_eval = 1;
     // the first-tile bootstrap needs every row of that tile to be a live row
-    const bool boot = a.groups > 1 && pubj <= 8 && !a.drop && !a.filter && ntl > 1 &&
+    const bool boot = !resc && a.groups > 1 && pubj <= 8 && !a.drop && !a.filter && ntl > 1 &&
                       a.row_begin + (t_begin + 1) * kBN <= a.row_end && !(a.dbg & (1 | 16 | 32 | 64));
+    const int etid = ew * 32 + lane;
+    if (resc) {
+      const uint32_t r0 = a.row_begin + t_begin * kBN;
+      colc[etid] = cval(r0 + etid);
+      colc[etid + 128] = cval(r0 + 128 + etid);
+      asm volatile("bar.sync 1, 128;" ::: "memory");
+    }
     const bool prof = (a.dbg & 128) != 0;  // triage: where the epilogue's cycles go (printed by CTA 0)
     long long c_wait = 0, c_slow = 0, c_ub = 0, c_t0 = 0, c_first4 = 0, c_tiles = 0;
     uint32_t n_slow = 0, n_ev = 0;
@@ -402,6 +478,9 @@ scan_mma_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
     for (uint32_t t = 0; t < ntl; ++t) {
       const uint32_t as = t & 1, aphase = (t >> 1) & 1;
       const uint32_t row0 = a.row_begin + (t_begin + t) * kBN;
+      float pc0 = 0.f, pc1 = 0.f;
+      if (resc && t + 1 < ntl) { pc0 = cval(row0 + kBN + etid); pc1 = cval(row0 + kBN + 128 + etid); }
+      const float *cc = colc + (t & 1) * kBN;
       const long long c0w = prof ? clock64() : 0;
       mbar_wait(bar_tfull + 8 * as, aphase);
       if (prof) c_wait += clock64() - c0w;
@@ -449,6 +528,16 @@ scan_mma_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
         uint32_t v[32];
         tmem_ld32(taddr + c0, v);
         tmem_ld_wait();
+        if (resc) {
+#pragma unroll
+          for (int j = 0; j < 32; j += 4) {
+            const float4 c4 = *reinterpret_cast<const float4 *>(cc + c0 + j);  // broadcast read
+            v[j] = __float_as_uint(__uint_as_float(v[j]) + c4.x);
+            v[j + 1] = __float_as_uint(__uint_as_float(v[j + 1]) + c4.y);
+            v[j + 2] = __float_as_uint(__uint_as_float(v[j + 2]) + c4.z);
+            v[j + 3] = __float_as_uint(__uint_as_float(v[j + 3]) + c4.w);
+          }
+        }
         float mx = __uint_as_float(v[0]);
 #pragma unroll
         for (int j = 1; j < 32; ++j) mx = fmaxf(mx, __uint_as_float(v[j]));
@@ -469,17 +558,27 @@ scan_mma_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
             // the column again, straight from TMEM (collective, warp-uniform address): indexing v[] with a
             // run-time j would cost a branch tree or local memory
             const uint32_t raw = tmem_ld1(taddr + c0 + j);
-            if ((m >> j) & 1u) {
-              const float dv = __uint_as_float(raw);
-              if (dv >= dthr) {  // dthr may have tightened since the mask was built
-                const float s = mode == 0 ? -dv : 1.0f - dv;
-                const uint32_t row = row0 + c0 + j;
-                const u64 key = pack_key(s, row);
-                bool p = key < tau_key && row < a.row_end;
-                if (p && a.drop) p = !bit_set(a.drop, row);
-                if (p && a.filter) p = !bit_set(a.filter, row);
-                if (p) accept(key);
+            const uint32_t row = row0 + c0 + j;
+            const float dv = __uint_as_float(raw) + (resc ? cc[c0 + j] : 0.f);
+            bool cand = ((m >> j) & 1u) && dv >= dthr;  // dthr may have tightened since the mask was built
+            float s = mode == 0 ? -dv : 1.0f - dv;
+            if (resc) {
+              // the accumulator only nominated the row: its score is recomputed exactly, by the whole warp,
+              // one nominating lane (query) at a time
+              uint32_t cb = __ballot_sync(FULL, cand);
+              while (cb) {
+                const int src = __ffs(cb) - 1;
+                cb &= cb - 1;
+                const float e = exact_score<KIND == 0 ? ZVB200_DT_FP16 : ZVB200_DT_FP32>(a, row, q0 + ew * 32 + src, lane);
+                if (lane == src) s = e;
               }
+            }
+            if (cand) {
+              const u64 key = pack_key(s, row);
+              bool p = key < tau_key && row < a.row_end;
+              if (p && a.drop) p = !bit_set(a.drop, row);
+              if (p && a.filter) p = !bit_set(a.filter, row);
+              if (p) accept(key);
             }
             __syncwarp();
           }
@@ -496,6 +595,14 @@ scan_mma_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(bar_tempty + 8 * as);
+      if (resc) {
+        if (t + 1 < ntl) {
+          float *cn = colc + ((t + 1) & 1) * kBN;
+          cn[etid] = pc0;
+          cn[etid + 128] = pc1;
+        }
+        asm volatile("bar.sync 1, 128;" ::: "memory");
+      }
       // off the MMA's critical path: refresh the union bound at tiles 1,2,3,4,6,9,13,19,... of this CTA
       if (a.groups > 1 && t + 1 == next_eval && !(a.dbg & 32)) {
         const long long c0u = prof ? clock64() : 0;
@@ -546,26 +653,27 @@ EncodeTiledFn encode_fn() {
   return fn;
 }
 
-// 2-D fp16 tensor map over `rows` rows of `d` halves, `stride` bytes apart; box = 64 x box_rows,
-// 128-byte swizzle; out-of-range elements read as zero (ragged d and the last row tile).
-bool make_map(CUtensorMap *tm, const void *ptr, uint32_t d, uint64_t rows, uint32_t stride, uint32_t box_rows) {
+// 2-D tensor map over `rows` rows of `d` elements (fp16 or fp32), `stride` bytes apart; box = one
+// 128-byte k-block x box_rows, 128-byte swizzle; out-of-range elements read as zero (ragged d and
+// the last row tile).
+bool make_map(CUtensorMap *tm, const void *ptr, bool f32, uint32_t d, uint64_t rows, uint32_t stride, uint32_t box_rows) {
   EncodeTiledFn fn = encode_fn();
   if (!fn) return false;
   cuuint64_t dims[2] = {d, rows};
   cuuint64_t strides[1] = {stride};
-  cuuint32_t box[2] = {(cuuint32_t)kBK, box_rows};
+  cuuint32_t box[2] = {(cuuint32_t)(f32 ? 32 : 64), box_rows};
   cuuint32_t estr[2] = {1, 1};
-  return fn(tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, const_cast<void *>(ptr), dims, strides, box, estr,
-            CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
-            CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+  return fn(tm, f32 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, const_cast<void *>(ptr), dims,
+            strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+            CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
 }
 
 constexpr size_t kSmemMax = 232448;  // 227 KB
 
 // pipeline stages that fit next to the 128 x k lists; false when not even 2 stages fit
-bool mma_config(uint32_t k, uint32_t *nstage, size_t *smem) {
+bool mma_config(uint32_t k, bool colc, uint32_t *nstage, size_t *smem) {
   for (uint32_t ns = 4; ns >= 2; --ns) {
-    const size_t need = 1024 + (size_t)ns * kStage + (size_t)kQM * k * 8 + (2 * ns + 4) * 8 + 16;
+    const size_t need = 1024 + (size_t)ns * kStage + (size_t)kQM * k * 8 + (2 * ns + 4) * 8 + 16 + (colc ? 2 * kBN * 4 : 0);
     if (need <= kSmemMax) { *nstage = ns; *smem = need; return true; }
   }
   return false;
@@ -575,10 +683,14 @@ bool mma_config(uint32_t k, uint32_t *nstage, size_t *smem) {
 
 bool scan_mma_supports(const RowsView &rv, uint32_t k) {
   uint32_t ns; size_t smem;
-  if (rv.dtype != ZVB200_DT_FP16) return false;
-  if (rv.metric != ZVB200_METRIC_IP && rv.metric != ZVB200_METRIC_COSINE) return false;
+  if (rv.dtype != ZVB200_DT_FP16 && rv.dtype != ZVB200_DT_FP32) return false;
+  if (rv.metric != ZVB200_METRIC_IP && rv.metric != ZVB200_METRIC_COSINE && rv.metric != ZVB200_METRIC_L2SQ &&
+      rv.metric != ZVB200_METRIC_L2)
+    return false;
+  const bool direct = rv.dtype == ZVB200_DT_FP16 && !metric_is_l2(rv.metric);
+  if (!direct && !rv.norms) return false;  // the filter + re-score modes need |x|^2 (computed at seal)
   if (k > 128) return false;
-  return mma_config(k, &ns, &smem) && encode_fn() != nullptr;
+  return mma_config(k, !direct, &ns, &smem) && encode_fn() != nullptr;
 }
 
 size_t scan_mma_max_parts(int sm_count) { return (size_t)sm_count; }
@@ -587,7 +699,7 @@ cudaError_t launch_scan_mma(const RowsView &rv, const QueryView &qv, const Searc
                             uint64_t row_begin, uint64_t row_end, u64 *part, uint32_t *nparts,
                             uint32_t *pub, int sm_count, cudaStream_t st) {
   uint32_t ns; size_t smem;
-  if (!mma_config(sp.k, &ns, &smem)) return cudaErrorInvalidValue;
+  if (!mma_config(sp.k, !(rv.dtype == ZVB200_DT_FP16 && !metric_is_l2(rv.metric)), &ns, &smem)) return cudaErrorInvalidValue;
   const uint64_t nrows = row_end > row_begin ? row_end - row_begin : 0;
   MmaArgs a;
   a.nq = qv.q;
@@ -595,10 +707,21 @@ cudaError_t launch_scan_mma(const RowsView &rv, const QueryView &qv, const Searc
   if ((int)a.qtiles > sm_count) return cudaErrorInvalidValue;  // caller splits the batch
   a.ntiles = (uint32_t)((nrows + kBN - 1) / kBN);
   a.groups = std::max<uint32_t>(1, std::min<uint32_t>((uint32_t)sm_count / a.qtiles, std::max<uint32_t>(a.ntiles, 1)));
-  a.nkb = (rv.d + kBK - 1) / kBK;
+  const bool f32 = rv.dtype == ZVB200_DT_FP32;
+  const uint32_t bke = f32 ? 32 : 64;
+  a.nkb = (rv.d + bke - 1) / bke;
   a.k = sp.k; a.nstage = ns;
   a.row_begin = (uint32_t)row_begin; a.row_end = (uint32_t)row_end;
-  a.mode = rv.metric == ZVB200_METRIC_IP ? 0 : 1;
+  const bool l2 = metric_is_l2(rv.metric);
+  if (!f32 && !l2) a.mode = rv.metric == ZVB200_METRIC_IP ? 0 : 1;
+  else a.mode = l2 ? 2 : rv.metric == ZVB200_METRIC_IP ? 3 : 4;
+  a.metric = rv.metric;
+  a.rows = rv.rows; a.row_stride = rv.row_stride; a.chunks = rv.chunks;
+  a.qf32 = qv.qf32; a.qstride = rv.chunks * (f32 ? 4 : 8);
+  a.norms = rv.norms; a.qnorms = qv.qnorms;
+  // error bound of the accumulator against the exact dot product, relative to (|x|^2 + |q|^2) / 2 >= |x||q|:
+  // fp32 accumulation of d exact products (fp16 inputs), plus two 10-bit-mantissa operands for tf32
+  a.eps = (float)rv.d * 2.4e-7f + (f32 ? 2.2e-3f : 0.f);
   a.threshold = sp.threshold;
   a.drop = rv.drop; a.filter = sp.filter;
   a.part = part;
@@ -618,10 +741,15 @@ cudaError_t launch_scan_mma(const RowsView &rv, const QueryView &qv, const Searc
   CUtensorMap tmQ, tmX;
   // the caller pads qraw with zero rows up to a whole tile when this is the last group of the batch
   const uint64_t qrows = qv.qpad_rows ? (uint64_t)a.qtiles * kQM : qv.q;
-  if (!make_map(&tmQ, qv.qraw, rv.d, qrows, rv.row_stride, kQM)) return cudaErrorInvalidValue;
-  if (!make_map(&tmX, rv.rows + row_begin * rv.row_stride, rv.d, std::max<uint64_t>(nrows, 1), rv.row_stride, kBN))
+  if (f32) {
+    if (!make_map(&tmQ, qv.qf32, true, rv.d, qrows, a.qstride * 4, kQM)) return cudaErrorInvalidValue;
+  } else {
+    if (!make_map(&tmQ, qv.qraw, false, rv.d, qrows, rv.row_stride, kQM)) return cudaErrorInvalidValue;
+  }
+  if (!make_map(&tmX, rv.rows + row_begin * rv.row_stride, f32, rv.d, std::max<uint64_t>(nrows, 1), rv.row_stride, kBN))
     return cudaErrorInvalidValue;
-  auto kern = sp.k <= 8 ? scan_mma_kernel<8> : sp.k <= 16 ? scan_mma_kernel<16> : scan_mma_kernel<0>;
+  auto kern = f32 ? (sp.k <= 8 ? scan_mma_kernel<1, 8> : sp.k <= 16 ? scan_mma_kernel<1, 16> : scan_mma_kernel<1, 0>)
+                  : (sp.k <= 8 ? scan_mma_kernel<0, 8> : sp.k <= 16 ? scan_mma_kernel<0, 16> : scan_mma_kernel<0, 0>);
   cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return e;
   if (nrows == 0) {
