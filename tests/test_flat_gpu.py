@@ -11,10 +11,10 @@ pytestmark = pytest.mark.gpu
 ESZ = {S.DT_FP32: 4, S.DT_FP16: 2, S.DT_INT8: 1}
 
 
-def make_stored(kind, n, d, seed):
+def make_stored(kind, n, d, seed, base=None):
     """-> (metric id, dtype, stored dim, stored rows bytes [n, elem], stored queries fn)"""
     rng = np.random.default_rng(seed)
-    x = rng.standard_normal((n, d)).astype(np.float32)
+    x = rng.standard_normal((n, d)).astype(np.float32) if base is None else base
 
     def conv(a):
         if kind in ("fp32_l2", "fp32_ip", "fp32_l2sqrt"):
@@ -299,6 +299,36 @@ def test_mma_kernel_filters_threshold_and_auto_selection():
     run_case("fp32_l2", n, 64, 64, 10, seed=65, kernel=3, drop=drop, filt=filt)
     run_case("fp32_cos", n, 64, 64, 20, seed=66, kernel=3, threshold=0.8)
     run_case("fp16_l2", n, 64, 64, 20, seed=67, kernel=3, threshold=100.0, drop=drop)
+
+
+@pytest.mark.parametrize("kind", ["fp16_l2", "fp32_l2", "fp32_ip"])
+@pytest.mark.parametrize("shape", ["offset", "norm_spread", "near_duplicates"])
+def test_mma_rescore_filter_is_sound_on_hostile_data(kind, shape):
+    """The tensor-core accumulator only nominates rows; these inputs maximise its error against the exact
+    score (cancellation in |x|^2 - 2xq + |q|^2, tf32 truncation) — the results must still equal the oracle's."""
+    n, d, q, k = 20000, 64, 48, 10
+    rng = np.random.default_rng(70)
+    base = rng.standard_normal((n, d)).astype(np.float32)
+    qs = rng.standard_normal((q, d)).astype(np.float32)
+    if shape == "offset":                       # large common component: distances << norms
+        base = base * 0.05 + 30.0
+        qs = qs * 0.05 + 30.0
+    elif shape == "norm_spread":                # norms over 4 decades
+        base *= (10.0 ** rng.uniform(-2, 2, (n, 1))).astype(np.float32)
+    else:                                       # the queries are (almost) stored rows
+        qs = base[rng.integers(0, n, q)] + 1e-3 * rng.standard_normal((q, d)).astype(np.float32)
+    metric, dt, sdim, stored, conv = make_stored(kind, n, d, 71, base=base)
+    queries = np.ascontiguousarray(conv(qs))
+    st = z.Store(dt, metric, sdim); st.append(stored); st.seal()
+    ctx = z.Context(st); ctx.set_kernel(3)
+    gk, gs, gi, gc = ctx.search(queries, k)
+    assert ctx.last_kernel() == "scan_mma"
+    ctx.set_kernel(1)
+    ek, es, ei, ec = ctx.search(queries, k)      # the streaming scan: exact arithmetic, oracle-checked elsewhere
+    for i in range(q):
+        alld = S.oracle_distances(metric, dt, stored, sdim, queries[i])
+        S.check_topk_parity(gi[i], gs[i], ei[i], es[i], all_dist=alld, exact=False, what="%s %s q%d" % (kind, shape, i))
+    ctx.close(); st.close()
 
 
 def test_mma_and_tile_agree_on_ids():

@@ -450,7 +450,13 @@ static int search_core(zvb200_ctx *c, zvb200_store *s, const void *queries_dev, 
   // bound the partial-list scratch to 256 MiB: process the queries in groups
   const size_t per_query = maxparts * (size_t)k * sizeof(u64);
   uint32_t group = (uint32_t)std::max<size_t>(1, ((size_t)256 << 20) / per_query);
-  if (which == 3) group = std::min<uint32_t>(group, (uint32_t)s->sm_count * 128u);
+  // tensor-core scan: 8 query tiles x 18 row groups per launch fill the 148 SMs and keep the union bound strong
+  // (one launch of 79 query tiles would leave 1 row group and 69 idle SMs); the rows are re-read per launch,
+  // which stays far below the launch's MMA time
+  if (which == 3) {
+    static const uint32_t cap = [] { const char *e = getenv("ZVB200_MMA_GROUP"); return e ? (uint32_t)atoi(e) : 1024u; }();
+    group = std::min<uint32_t>(group, std::min<uint32_t>(std::max(cap, 128u), (uint32_t)s->sm_count * 128u));
+  }
   if (group >= 128) group &= ~127u; else if (group >= 64) group &= ~63u; else if (group >= 4) group &= ~3u;
   group = std::min(group, q);
   CU(c->part.ensure((size_t)group * per_query));

@@ -461,7 +461,7 @@ scan_mma_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
     };
     uint32_t next_eval = 1;
     // the first-tile bootstrap needs every row of that tile to be a live row
-    const bool boot = !resc && a.groups > 1 && pubj <= 8 && !a.drop && !a.filter && ntl > 1 &&
+    const bool boot = a.groups > 1 && pubj <= 8 && !a.drop && !a.filter && ntl > 1 &&
                       a.row_begin + (t_begin + 1) * kBN <= a.row_end && !(a.dbg & (1 | 16 | 32 | 64));
     const int etid = ew * 32 + lane;
     if (resc) {
@@ -502,10 +502,23 @@ scan_mma_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
           uint32_t v[32];
           tmem_ld32(taddr + c, v);
           tmem_ld_wait();
+          if (resc) {  // pessimistic side of the error bound: g = acc - (1 + eps) hx (L2), acc - eps hx (IP, cosine)
+            const float cb = mode == 2 ? (1.0f + a.eps) / (1.0f - a.eps) * 1.000001f : -1.0f;
+#pragma unroll
+            for (int j = 0; j < 32; ++j) v[j] = __float_as_uint(fmaf(cc[c + j], cb, __uint_as_float(v[j])));
+          }
           float mx = __uint_as_float(v[0]);
 #pragma unroll
           for (int j = 1; j < 32; ++j) mx = fmaxf(mx, __uint_as_float(v[j]));
-          uint32_t x = order_f32(mode == 0 ? -mx : 1.0f - mx);
+          float su;  // an upper bound of the exact score of the chunk's best row
+          if (mode == 0) su = -mx;
+          else if (mode == 1) su = 1.0f - mx;
+          else {
+            su = mode == 2 ? 2.0f * ((1.0f + a.eps) * hq - mx) : (mode == 3 ? -mx : 1.0f - mx) + a.eps * hq;
+            su += (fabsf(su) + fabsf(mx) + hq + 1.0f) * 1e-6f;
+            if (a.metric == ZVB200_METRIC_L2) su = sqrtf(fmaxf(su, 0.f)) * 1.000001f;
+          }
+          uint32_t x = order_f32(su);
 #pragma unroll
           for (int i = 0; i < 8; ++i) {
             const uint32_t lo = min(cm[i], x);
