@@ -148,6 +148,27 @@ int zvb200_merge_topk_device(zvb200_ctx *c, const float *scores_dev, const uint3
                              uint32_t g, const uint64_t *shard_base, uint32_t q, uint32_t k,
                              float *out_scores_dev, uint64_t *out_rows_dev);
 
+/* ---- multi-vector fusion: replaces RrfReRanker.rerank / WeightedReRanker.rerank
+ * (python/zvec/extension/multi_vector_reranker.py:62-89,135-174) applied by the query executor to
+ * the per-field results of a multi-vector query (python/zvec/executor/query_executor.py:178-206,
+ * 276-287).  HOST buffers.  keys [F][q][k] (document keys as returned by zvb200_search), counts
+ * [F][q] valid entries per list, lists in field order.  Output per query: topn (key, fp64 score)
+ * sorted like heapq.nlargest (score descending, ties in first-seen order), padded with
+ * ZVB200_INVALID_KEY / NaN; out_counts[q] = documents returned.  F*k <= 1536.
+ *   rrf:      score = sum 1 / (rank_constant + rank + 1)
+ *   weighted: score = sum normalize(s) * weights[f]; fuse_metric ZVB200_METRIC_L2 | _L2SQ:
+ *             1 - 2 atan(s)/pi, ZVB200_METRIC_IP: 0.5 + atan(s)/pi, ZVB200_METRIC_COSINE: 1 - s/2;
+ *             s = the user-facing score (Doc.score): pass negate = 1 to hand in the internal
+ *             InnerProduct scores of zvb200_search (IndexMetric::normalize flips their sign,
+ *             src/core/metric/inner_product_metric.cc:377-379). */
+int zvb200_fuse_rrf(zvb200_ctx *c, const uint64_t *keys, const uint32_t *counts, uint32_t nfields,
+                    uint32_t q, uint32_t k, uint32_t topn, uint32_t rank_constant,
+                    uint64_t *out_keys, double *out_scores, uint32_t *out_counts);
+int zvb200_fuse_weighted(zvb200_ctx *c, const uint64_t *keys, const float *scores,
+                         const uint32_t *counts, uint32_t nfields, uint32_t q, uint32_t k,
+                         uint32_t topn, int fuse_metric, const double *weights, int negate,
+                         uint64_t *out_keys, double *out_scores, uint32_t *out_counts);
+
 /* ---- IVF: replaces IVFSearcher::search_impl (src/core/algorithm/ivf/ivf_searcher.cc:
  * 183-250): coarse search over centroids (IVFCentroidIndex::search, ivf_centroid_index.cc:
  * 273-295) + IVFEntity::search per list (ivf_entity.cc:662-716) under the scan budget of

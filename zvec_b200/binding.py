@@ -56,6 +56,11 @@ _SIGS = {
                                          C.c_void_p, C.c_uint32, C.c_void_p]),
     "zvb200_merge_topk_device": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p,
                                            C.c_uint32, C.c_uint32, C.c_void_p, C.c_void_p]),
+    "zvb200_fuse_rrf": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32,
+                                  C.c_uint32, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "zvb200_fuse_weighted": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32,
+                                       C.c_uint32, C.c_uint32, C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p,
+                                       C.c_void_p]),
     "zvb200_ivf_attach": (C.c_int, [C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p]),
     "zvb200_ivf_search": (C.c_int, [C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint64,
                                     C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
@@ -219,6 +224,28 @@ class Context:
         _check(lib().zvb200_ivf_search(self.h, _ptr(queries), q, k, nprobe, max_scan_count,
                                        _ptr(keys), _ptr(scores), _ptr(index), _ptr(counts)))
         return keys, scores, index, counts
+
+    def fuse_rrf(self, keys, counts, topn, rank_constant=60):
+        """RrfReRanker.rerank over F per-field lists: keys [F][q][k] u64, counts [F][q] -> (keys, fp64 scores, counts)."""
+        keys = np.ascontiguousarray(keys, np.uint64)
+        counts = np.ascontiguousarray(counts, np.uint32)
+        F, q, k = keys.shape
+        ok = np.empty((q, topn), np.uint64); os_ = np.empty((q, topn), np.float64); oc = np.empty(q, np.uint32)
+        _check(lib().zvb200_fuse_rrf(self.h, _ptr(keys), _ptr(counts), F, q, k, topn, rank_constant,
+                                     _ptr(ok), _ptr(os_), _ptr(oc)))
+        return ok, os_, oc
+
+    def fuse_weighted(self, keys, scores, counts, topn, fuse_metric, weights, negate=False):
+        """WeightedReRanker.rerank: scores [F][q][k] f32 are Doc.score (negate=True: internal InnerProduct scores)."""
+        keys = np.ascontiguousarray(keys, np.uint64)
+        scores = np.ascontiguousarray(scores, np.float32)
+        counts = np.ascontiguousarray(counts, np.uint32)
+        weights = np.ascontiguousarray(weights, np.float64)
+        F, q, k = keys.shape
+        ok = np.empty((q, topn), np.uint64); os_ = np.empty((q, topn), np.float64); oc = np.empty(q, np.uint32)
+        _check(lib().zvb200_fuse_weighted(self.h, _ptr(keys), _ptr(scores), _ptr(counts), F, q, k, topn, fuse_metric,
+                                          _ptr(weights), 1 if negate else 0, _ptr(ok), _ptr(os_), _ptr(oc)))
+        return ok, os_, oc
 
     def search_device(self, q_ptr, q, k, out_scores_ptr, out_index_ptr, threshold=FLT_MAX, filter_ptr=None):
         _check(lib().zvb200_search_device(self.h, C.c_void_p(q_ptr), q, k, threshold,

@@ -574,6 +574,59 @@ int zvb200_merge_topk_device(zvb200_ctx *c, const float *scores_dev, const uint3
   return 0;
 }
 
+// fusion: H2D of the lists, one kernel, D2H of the fused lists
+static int fuse_common(zvb200_ctx *c, const uint64_t *keys, const float *scores, const uint32_t *counts,
+                       uint32_t F, uint32_t q, uint32_t k, uint32_t topn, uint32_t rank_constant, int mode,
+                       const double *weights, int negate, uint64_t *out_keys, double *out_scores,
+                       uint32_t *out_counts) {
+  if (!c || !keys || !counts || !out_keys || !out_scores || !out_counts || F == 0 || k == 0 || topn == 0)
+    return set_err(ZVB200_ERR_INVALID_ARGUMENT, "bad argument");
+  if (mode != 0 && (!scores || !weights)) return set_err(ZVB200_ERR_INVALID_ARGUMENT, "weighted fusion needs scores and weights");
+  if ((size_t)F * k > fuse_max_entries()) return set_err(ZVB200_ERR_UNSUPPORTED, "fusion: nfields * k > 1536");
+  if (q == 0) return 0;
+  CU(cudaSetDevice(c->device));
+  const size_t nin = (size_t)F * q * k, nout = (size_t)q * topn;
+  const size_t off_scores = nin * 8, off_counts = off_scores + nin * 4, off_w = (off_counts + (size_t)F * q * 4 + 7) & ~(size_t)7;
+  const size_t off_ok = off_w + (size_t)F * 8, off_os = off_ok + nout * 8, off_oc = off_os + nout * 8;
+  CU(c->misc.ensure(off_oc + (size_t)q * 4));
+  uint8_t *d = (uint8_t *)c->misc.p;
+  CU(cudaMemcpyAsync(d, keys, nin * 8, cudaMemcpyHostToDevice, c->stream));
+  if (mode != 0) {
+    CU(cudaMemcpyAsync(d + off_scores, scores, nin * 4, cudaMemcpyHostToDevice, c->stream));
+    CU(cudaMemcpyAsync(d + off_w, weights, (size_t)F * 8, cudaMemcpyHostToDevice, c->stream));
+  }
+  CU(cudaMemcpyAsync(d + off_counts, counts, (size_t)F * q * 4, cudaMemcpyHostToDevice, c->stream));
+  CU(launch_fuse((const uint64_t *)d, (const float *)(d + off_scores), (const uint32_t *)(d + off_counts),
+                 (const double *)(d + off_w), F, q, k, topn, rank_constant, mode, negate, (uint64_t *)(d + off_ok),
+                 (double *)(d + off_os), (uint32_t *)(d + off_oc), c->stream));
+  CU(cudaMemcpyAsync(out_keys, d + off_ok, nout * 8, cudaMemcpyDeviceToHost, c->stream));
+  CU(cudaMemcpyAsync(out_scores, d + off_os, nout * 8, cudaMemcpyDeviceToHost, c->stream));
+  CU(cudaMemcpyAsync(out_counts, d + off_oc, (size_t)q * 4, cudaMemcpyDeviceToHost, c->stream));
+  CU(cudaStreamSynchronize(c->stream));
+  c->last_kernel = "fuse";
+  return 0;
+}
+
+int zvb200_fuse_rrf(zvb200_ctx *c, const uint64_t *keys, const uint32_t *counts, uint32_t nfields, uint32_t q,
+                    uint32_t k, uint32_t topn, uint32_t rank_constant, uint64_t *out_keys, double *out_scores,
+                    uint32_t *out_counts) {
+  return fuse_common(c, keys, nullptr, counts, nfields, q, k, topn, rank_constant, 0, nullptr, 0, out_keys,
+                     out_scores, out_counts);
+}
+
+int zvb200_fuse_weighted(zvb200_ctx *c, const uint64_t *keys, const float *scores, const uint32_t *counts,
+                         uint32_t nfields, uint32_t q, uint32_t k, uint32_t topn, int fuse_metric,
+                         const double *weights, int negate, uint64_t *out_keys, double *out_scores,
+                         uint32_t *out_counts) {
+  int mode;
+  if (fuse_metric == ZVB200_METRIC_L2 || fuse_metric == ZVB200_METRIC_L2SQ) mode = 1;
+  else if (fuse_metric == ZVB200_METRIC_IP) mode = 2;
+  else if (fuse_metric == ZVB200_METRIC_COSINE) mode = 3;
+  else return set_err(ZVB200_ERR_UNSUPPORTED, "weighted fusion: L2, InnerProduct or Cosine only");  // ValueError in the reference
+  return fuse_common(c, keys, scores, counts, nfields, q, k, topn, 0, mode, weights, negate, out_keys, out_scores,
+                     out_counts);
+}
+
 int zvb200_distance_matrix(int device, int metric, int dtype, uint32_t dim, const void *m,
                            uint64_t n, const void *q, uint32_t nq, float *out) {
   if (!m || !q || !out) return set_err(ZVB200_ERR_INVALID_ARGUMENT, "null argument");

@@ -123,6 +123,12 @@ inline int pick_lpr_log2(uint32_t chunks) {
   return lg < top ? lg : top;
 }
 
+// K6: multi-vector fusion (RRF / weighted) of F per-field lists, one CTA per query (fuse.cu)
+cudaError_t launch_fuse(const uint64_t *keys, const float *scores, const uint32_t *counts, const double *weights,
+                        uint32_t F, uint32_t q, uint32_t k, uint32_t topn, uint32_t rank_constant, int mode, int negate,
+                        uint64_t *out_keys, double *out_scores, uint32_t *out_counts, cudaStream_t st);
+size_t fuse_max_entries();
+
 void count_launch(int n = 1);
 
 }  // namespace zvb
