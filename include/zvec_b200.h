@@ -86,6 +86,10 @@ int zvb200_store_seal(zvb200_store *s);
 uint64_t zvb200_store_count(const zvb200_store *s);
 /* Mark a row deleted / undeleted (FlatStreamerEntity DeletionMap, flat_index_format.h:106-126). */
 int zvb200_store_set_deleted(zvb200_store *s, uint64_t row, int deleted);
+/* Overwrite row `row` (< count) with a new vector and key: the in-place branch of
+ * FlatStreamerEntity::add_vector_with_id (flat_streamer_entity.cc:969-985).  A key of
+ * ZVB200_INVALID_KEY turns the row into a hole, any other key makes it live again. */
+int zvb200_store_write(zvb200_store *s, uint64_t row, const void *vec, uint64_t key);
 /* Copy one stored row back in the reference layout (IndexSearcher::get_vector). */
 int zvb200_store_get_vector(const zvb200_store *s, uint64_t row, void *out, size_t cap);
 /* Bytes of HBM one full scan must read (the roofline's algorithmic bytes). */

@@ -19,6 +19,7 @@
 #include <zvec/core/framework/index_helper.h>
 #include <zvec/core/framework/index_meta.h>
 #include <zvec/core/framework/index_searcher.h>
+#include <zvec/core/framework/index_streamer.h>
 
 #include <cstring>
 #include <limits>
@@ -271,6 +272,253 @@ void GpuFlatContext::reset(const GpuFlatSearcher *owner) {
 
 INDEX_FACTORY_REGISTER_SEARCHER(GpuFlatSearcher);
 
+// ======================================================================================
+// GpuFlatStreamer — FlatStreamer's interface (flat_streamer.h:28-160): rows arrive one by one
+// between searches.  Composition: persistence (storage blocks, key maps, flush / dump / provider /
+// get_vector, duplicate-key refusal) stays with an embedded stock FlatStreamer<32>, created under
+// its never-overridden alias "FlatStreamer32" (flat_streamer.cc:486-489); every accepted add is
+// mirrored into the device store, and every search is the GPU scan.
+// ======================================================================================
+class GpuFlatStreamer;
+
+class GpuFlatStreamerContext : public IndexContext {
+ public:
+  GpuFlatStreamerContext(const GpuFlatStreamer *owner, IndexContext::Pointer inner) : inner_(std::move(inner)) {
+    this->reset(owner);
+  }
+  ~GpuFlatStreamerContext() override {
+    if (ctx_) zvb200_ctx_destroy(ctx_);
+  }
+  void set_topk(uint32_t topk) override { topk_ = topk; if (inner_) inner_->set_topk(topk); }
+  uint32_t topk() const override { return topk_; }
+  const IndexDocumentList &result(void) const override { return results_[0]; }
+  const IndexDocumentList &result(size_t i) const override { return results_[i]; }
+  IndexDocumentList *mutable_result(size_t i) override { return &results_[i]; }
+  uint32_t magic(void) const override { return magic_; }
+  void reset(const GpuFlatStreamer *owner);
+  zvb200_ctx *handle() const { return ctx_; }
+  IndexContext::Pointer &inner() { return inner_; }
+  void resize_results(size_t n) {
+    if (results_.size() < n) results_.resize(n);
+  }
+  std::vector<uint64_t> keys;
+  std::vector<float> scores;
+  std::vector<uint32_t> index, counts, bitmap;
+
+ private:
+  uint32_t topk_{0};
+  uint32_t magic_{0};
+  zvb200_ctx *ctx_{nullptr};
+  IndexContext::Pointer inner_{};
+  std::vector<IndexDocumentList> results_{1};
+};
+
+class GpuFlatStreamer : public IndexStreamer {
+ public:
+  GpuFlatStreamer() = default;
+  ~GpuFlatStreamer() override { this->cleanup(); }
+
+  int init(const IndexMeta &meta, const ailego::Params &params) override {
+    stock_ = IndexFactory::CreateStreamer("FlatStreamer32");
+    if (!stock_) return IndexError_NoExist;
+    int rc = stock_->init(meta, params);
+    if (rc != 0) return rc;
+    meta_ = stock_->meta();
+    meta_.set_streamer("GpuFlatStreamer", 0U, params);
+    params.get("proxima.gpu.device", &device_);
+    if (metric_of(meta_) < 0 || dtype_of(meta_) < 0) return IndexError_Unsupported;
+    return 0;
+  }
+
+  int cleanup(void) override {
+    this->close();
+    if (stock_) stock_->cleanup();
+    stock_.reset();
+    return 0;
+  }
+
+  //! open = the stock open (it validates / recovers the storage), then every row it holds goes to the GPU
+  int open(IndexStorage::Pointer stg) override {
+    if (!stock_) return IndexError_NoReady;
+    int rc = stock_->open(stg);
+    if (rc != 0) return rc;
+    std::lock_guard<std::mutex> g(mu_);
+    rc = zvb200_store_create(device_, dtype_of(meta_), metric_of(meta_), meta_.dimension(), &store_);
+    if (rc != 0) return rc;
+    auto provider = stock_->create_provider();
+    if (provider) {
+      const size_t es = meta_.element_size();
+      for (auto it = provider->create_iterator(); it && it->is_valid(); it->next()) {
+        pend_keys_.push_back(it->key());
+        const char *v = static_cast<const char *>(it->data());
+        pend_rows_.insert(pend_rows_.end(), v, v + es);
+        if (pend_rows_.size() >= ((size_t)64 << 20) && (rc = flush_pending()) != 0) return rc;
+      }
+    }
+    magic_ = IndexContext::GenerateMagic();
+    return flush_pending();
+  }
+
+  int close(void) override {
+    {
+      std::lock_guard<std::mutex> g(mu_);
+      if (store_) zvb200_store_destroy(store_);
+      store_ = nullptr;
+      pend_rows_.clear(); pend_keys_.clear();
+    }
+    return stock_ ? stock_->close() : 0;
+  }
+  int flush(uint64_t checkpoint) override { return stock_ ? stock_->flush(checkpoint) : IndexError_NoReady; }
+  int dump(const IndexDumper::Pointer &dumper) override { return stock_ ? stock_->dump(dumper) : IndexError_NoReady; }
+
+  Context::Pointer create_context(void) const override {
+    if (!stock_) return Context::Pointer();
+    return Context::Pointer(new (std::nothrow) GpuFlatStreamerContext(this, stock_->create_context()));
+  }
+  IndexProvider::Pointer create_provider(void) const override { return stock_ ? stock_->create_provider() : nullptr; }
+
+  //! FlatStreamer::add_impl (flat_streamer.cc) -> FlatStreamerEntity::add (flat_streamer_entity.cc:149-210)
+  int add_impl(uint64_t pkey, const void *vec, const IndexQueryMeta &qmeta, Context::Pointer &context) override {
+    auto *ctx = dynamic_cast<GpuFlatStreamerContext *>(context.get());
+    if (!ctx || !stock_ || !store_) return IndexError_InvalidArgument;
+    const int rc = stock_->add_impl(pkey, vec, qmeta, ctx->inner());
+    if (rc != 0) return rc;  // duplicate key, size mismatch, index full: nothing to mirror
+    std::lock_guard<std::mutex> g(mu_);
+    const char *v = static_cast<const char *>(vec);
+    pend_rows_.insert(pend_rows_.end(), v, v + meta_.element_size());
+    pend_keys_.push_back(pkey);
+    return 0;
+  }
+
+  //! FlatStreamerEntity::add_vector_with_id (flat_streamer_entity.cc:900-991): rows up to `id` become
+  //! kInvalidKey holes, row `id` gets key = id; an existing id is overwritten in place
+  int add_with_id_impl(uint32_t id, const void *vec, const IndexQueryMeta &qmeta, Context::Pointer &context) override {
+    auto *ctx = dynamic_cast<GpuFlatStreamerContext *>(context.get());
+    if (!ctx || !stock_ || !store_) return IndexError_InvalidArgument;
+    int rc = stock_->add_with_id_impl(id, vec, qmeta, ctx->inner());
+    if (rc != 0) return rc;
+    std::lock_guard<std::mutex> g(mu_);
+    const size_t es = meta_.element_size();
+    const uint64_t on_device = zvb200_store_count(store_);
+    const uint64_t total = on_device + pend_keys_.size();
+    const char *v = static_cast<const char *>(vec);
+    if (id >= total) {
+      for (uint64_t r = total; r < id; ++r) {
+        pend_rows_.insert(pend_rows_.end(), es, 0);
+        pend_keys_.push_back(ZVB200_INVALID_KEY);
+      }
+      pend_rows_.insert(pend_rows_.end(), v, v + es);
+      pend_keys_.push_back(id);
+    } else if (id >= on_device) {
+      std::memcpy(&pend_rows_[(id - on_device) * es], v, es);
+      pend_keys_[id - on_device] = id;
+    } else {
+      rc = zvb200_store_write(store_, id, vec, id);
+      if (rc == 0) all_keys_[id] = id;
+    }
+    return rc;
+  }
+
+  int search_impl(const void *query, const IndexQueryMeta &qmeta, Context::Pointer &context) const override {
+    return this->search_bf_impl(query, qmeta, 1, context);
+  }
+  int search_impl(const void *query, const IndexQueryMeta &qmeta, uint32_t count, Context::Pointer &context) const override {
+    return this->search_bf_impl(query, qmeta, count, context);
+  }
+  int search_bf_impl(const void *query, const IndexQueryMeta &qmeta, Context::Pointer &context) const override {
+    return this->search_bf_impl(query, qmeta, 1, context);
+  }
+
+  //! FlatStreamer::search_bf_impl -> FlatStreamerEntity::search / search_block (flat_streamer_entity.cc:212-316)
+  int search_bf_impl(const void *query, const IndexQueryMeta &qmeta, uint32_t count, Context::Pointer &context) const override {
+    if (!query || !count || !context || !store_) return IndexError_InvalidArgument;
+    if (qmeta.element_size() != meta_.element_size()) return IndexError_Mismatch;
+    auto *ctx = dynamic_cast<GpuFlatStreamerContext *>(context.get());
+    if (!ctx) return IndexError_InvalidArgument;
+    if (ctx->magic() != magic_) ctx->reset(this);
+    const uint32_t k = ctx->topk();
+    ctx->resize_results(count);
+    for (uint32_t i = 0; i < count; ++i) ctx->mutable_result(i)->clear();
+    if (k == 0) return 0;
+    std::vector<uint64_t> host_keys;
+    {
+      std::lock_guard<std::mutex> g(mu_);
+      int rc = const_cast<GpuFlatStreamer *>(this)->flush_pending();  // publish the rows added since the last search
+      if (rc != 0) return rc;
+      if (ctx->filter().is_valid()) host_keys = all_keys_;
+    }
+    const size_t n = zvb200_store_count(store_);
+    if (n == 0) return 0;
+    const uint32_t *bitmap = nullptr;
+    if (ctx->filter().is_valid()) {
+      ctx->bitmap.assign((n + 31) / 32, 0u);
+      for (size_t i = 0; i < n && i < host_keys.size(); ++i)
+        if (host_keys[i] != ZVB200_INVALID_KEY && ctx->filter()(host_keys[i])) ctx->bitmap[i >> 5] |= 1u << (i & 31);
+      bitmap = ctx->bitmap.data();
+    }
+    const size_t nres = (size_t)count * k;
+    ctx->keys.resize(nres); ctx->scores.resize(nres); ctx->index.resize(nres); ctx->counts.resize(count);
+    const int rc = zvb200_search(ctx->handle(), query, count, k, ctx->threshold(), bitmap, ctx->keys.data(),
+                                 ctx->scores.data(), ctx->index.data(), ctx->counts.data());
+    if (rc != 0) return rc;
+    for (uint32_t i = 0; i < count; ++i) {
+      IndexDocumentList *out = ctx->mutable_result(i);
+      for (uint32_t j = 0; j < ctx->counts[i]; ++j) {
+        const size_t o = (size_t)i * k + j;
+        out->emplace_back(ctx->keys[o], ctx->scores[o], ctx->keys[o]);  // index() = key (flat_streamer_context.h:125)
+      }
+    }
+    return 0;
+  }
+
+  const Stats &stats(void) const override { return stock_->stats(); }
+  const IndexMeta &meta(void) const override { return meta_; }
+  const void *get_vector(uint64_t key) const override { return stock_ ? stock_->get_vector(key) : nullptr; }
+  int get_vector(const uint64_t key, IndexStorage::MemoryBlock &block) const override {
+    return stock_ ? stock_->get_vector(key, block) : IndexError_NoReady;
+  }
+  uint32_t magic(void) const { return magic_; }
+  zvb200_store *store(void) const { return store_; }
+
+ private:
+  //! pending host rows -> device store; caller holds mu_
+  int flush_pending(void) {
+    if (!pend_keys_.empty()) {
+      const int rc = zvb200_store_append(store_, pend_rows_.data(), pend_keys_.size(), pend_keys_.data());
+      if (rc != 0) return rc;
+      all_keys_.insert(all_keys_.end(), pend_keys_.begin(), pend_keys_.end());
+      pend_rows_.clear(); pend_keys_.clear();
+      dirty_ = true;
+    }
+    if (dirty_) {
+      const int rc = zvb200_store_seal(store_);
+      if (rc != 0) return rc;
+      dirty_ = false;
+    }
+    return 0;
+  }
+
+  IndexStreamer::Pointer stock_{};
+  IndexMeta meta_{};
+  mutable std::mutex mu_{};
+  zvb200_store *store_{nullptr};
+  std::vector<char> pend_rows_{};
+  std::vector<uint64_t> pend_keys_{}, all_keys_{};
+  bool dirty_{true};
+  uint32_t magic_{0};
+  int device_{0};
+};
+
+void GpuFlatStreamerContext::reset(const GpuFlatStreamer *owner) {
+  if (ctx_) zvb200_ctx_destroy(ctx_);
+  ctx_ = nullptr;
+  magic_ = owner->magic();
+  if (owner->store()) zvb200_ctx_create(owner->store(), &ctx_);
+  for (auto &r : results_) r.clear();
+}
+
+INDEX_FACTORY_REGISTER_STREAMER(GpuFlatStreamer);
+
 }  // namespace core
 }  // namespace zvec
 
@@ -280,6 +528,7 @@ INDEX_FACTORY_REGISTER_SEARCHER(GpuFlatSearcher);
 // searcher = "FlatSearcher" reach the GPU path unchanged.
 extern "C" int zvb200_install_overrides(void) {
   static zvec::ailego::Factory<zvec::core::IndexSearcher>::Register<zvec::core::GpuFlatSearcher> r("FlatSearcher");
-  (void)r;
+  static zvec::ailego::Factory<zvec::core::IndexStreamer>::Register<zvec::core::GpuFlatStreamer> rs("FlatStreamer");
+  (void)r; (void)rs;
   return 0;
 }

@@ -24,6 +24,7 @@
 #include <zvec/core/framework/index_plugin.h>
 #include <zvec/core/framework/index_searcher.h>
 #include <zvec/core/framework/index_segment_storage.h>
+#include <zvec/core/framework/index_streamer.h>
 #include "ivf/ivf_entity.h"
 #include "ivf/ivf_index_format.h"
 
@@ -306,6 +307,81 @@ int zref_index_search(void *h, const void *queries, uint32_t count, uint32_t top
     for (auto &t : ts) t.join();
   }
   return err.load();
+}
+
+// ---- streamers (rows arrive between searches): drives any registered IndexStreamer class the way
+// tests/core/algorithm/flat/flat_streamer_test.cc:180-212,1038-1060 does ------------------------------
+struct RefStreamer {
+  IndexStreamer::Pointer st;
+  IndexStorage::Pointer storage;
+  IndexContext::Pointer ctx;
+  IndexMeta meta;
+};
+
+void *zref_streamer_open(const char *cls, int dtype, uint32_t dim, const char *metric, const char *path) {
+  auto h = new RefStreamer();
+  h->meta = IndexMeta((IndexMeta::DataType)dtype, dim);
+  h->meta.set_metric(metric, 0, Params());
+  h->st = IndexFactory::CreateStreamer(cls);
+  if (!h->st) { delete h; fail(-1, std::string("no streamer class ") + cls); return nullptr; }
+  h->storage = IndexFactory::CreateStorage("MMapFileStorage");
+  Params sp;
+  int r = h->storage ? h->storage->init(sp) : -1;
+  if (r == 0) r = h->storage->open(path, true);
+  if (r == 0) r = h->st->init(h->meta, Params());
+  if (r == 0) r = h->st->open(h->storage);
+  if (r != 0) { delete h; fail(r, "streamer init/open"); return nullptr; }
+  h->ctx = h->st->create_context();
+  if (!h->ctx) { delete h; fail(-1, "streamer context"); return nullptr; }
+  return h;
+}
+
+int zref_streamer_add(void *hh, uint64_t key, const void *vec) {
+  auto h = (RefStreamer *)hh;
+  IndexQueryMeta qm(h->meta.data_type(), h->meta.dimension());
+  return h->st->add_impl(key, vec, qm, h->ctx);
+}
+
+int zref_streamer_add_with_id(void *hh, uint32_t id, const void *vec) {
+  auto h = (RefStreamer *)hh;
+  IndexQueryMeta qm(h->meta.data_type(), h->meta.dimension());
+  return h->st->add_with_id_impl(id, vec, qm, h->ctx);
+}
+
+int zref_streamer_search(void *hh, const void *queries, uint32_t count, uint32_t topk, uint64_t *out_keys,
+                         float *out_scores, uint32_t *out_counts) {
+  auto h = (RefStreamer *)hh;
+  IndexQueryMeta qm(h->meta.data_type(), h->meta.dimension());
+  auto ctx = h->st->create_context();
+  if (!ctx) return fail(-1, "context");
+  ctx->set_topk(topk);
+  const uint64_t fmod = g_fmod, frem = g_frem;
+  if (fmod) ctx->set_filter([fmod, frem](uint64_t key) { return key % fmod == frem; });
+  if (g_has_threshold) ctx->set_threshold(g_threshold);
+  int rc = count == 1 ? h->st->search_impl(queries, qm, ctx) : h->st->search_impl(queries, qm, count, ctx);
+  if (rc != 0) return fail(rc, "streamer search");
+  for (uint32_t i = 0; i < count; ++i) {
+    const auto &res = ctx->result(i);
+    const uint32_t c = (uint32_t)std::min<size_t>(res.size(), topk);
+    out_counts[i] = c;
+    for (uint32_t j = 0; j < topk; ++j) {
+      out_keys[(size_t)i * topk + j] = j < c ? res[j].key() : ~0ull;
+      out_scores[(size_t)i * topk + j] = j < c ? res[j].score() : __builtin_nanf("");
+    }
+  }
+  return 0;
+}
+
+int zref_streamer_close(void *hh, int flush_first) {
+  auto h = (RefStreamer *)hh;
+  int r = 0;
+  if (flush_first) r = h->st->flush(0);
+  h->ctx.reset();
+  int r2 = h->st->close();
+  h->st->cleanup();
+  if (h->storage) h->storage->close();
+  delete h;
+  return r ? r : r2;
 }
 
 // Export an IVF index the reference built (what a device store must ingest, via the

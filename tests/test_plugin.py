@@ -98,3 +98,157 @@ def test_gpu_searcher_filter_threshold_and_normalized_scores():
     finally:
         L.zref_set_filter(0, 0); L.zref_set_threshold(0, 0.0)
     ref.close(); gpu.close()
+
+
+# ---- GpuFlatStreamer: rows arrive between searches (flat_streamer_test.cc:180-212,731-801,1038-1117) ----
+class _Streamer:
+    def __init__(self, cls, dtype, dim, metric, path):
+        import ctypes as C
+        L = S.ref()
+        L.zref_streamer_open.restype = C.c_void_p
+        L.zref_streamer_open.argtypes = [C.c_char_p, C.c_int, C.c_uint32, C.c_char_p, C.c_char_p]
+        L.zref_streamer_add.argtypes = [C.c_void_p, C.c_uint64, C.c_void_p]
+        L.zref_streamer_add_with_id.argtypes = [C.c_void_p, C.c_uint32, C.c_void_p]
+        L.zref_streamer_search.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_void_p, C.c_void_p, C.c_void_p]
+        L.zref_streamer_close.argtypes = [C.c_void_p, C.c_int]
+        self.L, self.dim = L, dim
+        self.h = L.zref_streamer_open(cls.encode(), dtype, dim, metric.encode(), path.encode())
+        if not self.h:
+            raise RuntimeError(L.zref_last_error().decode())
+
+    def add(self, key, vec):
+        return self.L.zref_streamer_add(self.h, key, S.P(np.ascontiguousarray(vec)))
+
+    def add_with_id(self, i, vec):
+        return self.L.zref_streamer_add_with_id(self.h, i, S.P(np.ascontiguousarray(vec)))
+
+    def search(self, queries, k):
+        queries = np.ascontiguousarray(queries)
+        q = len(queries)
+        keys = np.empty((q, k), np.uint64); scores = np.empty((q, k), np.float32); counts = np.empty(q, np.uint32)
+        rc = self.L.zref_streamer_search(self.h, S.P(queries), q, k, S.P(keys), S.P(scores), S.P(counts))
+        if rc != 0:
+            raise RuntimeError(self.L.zref_last_error().decode())
+        return keys, scores, counts
+
+    def search_each(self, queries, k):
+        """one search_impl call per query.  The stock FlatStreamer's batch loop (flat_streamer.cc:330-342)
+        never clears its result heap between the queries of a batch, so query i of a batch also returns
+        rows scored against queries 0..i-1 — a defect of the reference, not reproduced by the GPU class;
+        per-query calls are what core_interface issues (src/core/interface/index.cc:617, count = 1)."""
+        parts = [self.search(queries[i:i + 1], k) for i in range(len(queries))]
+        return tuple(np.concatenate([p[j] for p in parts]) for j in range(3))
+
+    def close(self, flush=False):
+        rc = self.L.zref_streamer_close(self.h, int(flush)); self.h = None
+        return rc
+
+
+def _same(a, b, what):
+    (ak, as_, ac), (bk, bs, bc) = a, b
+    assert np.array_equal(ac, bc), what
+    for i in range(len(ac)):
+        n = int(ac[i])
+        assert np.allclose(as_[i][:n], bs[i][:n], rtol=1e-4, atol=1e-5), what
+        assert np.array_equal(ak[i][:n], bk[i][:n]), what
+
+
+@needs_plugin
+@pytest.mark.gpu
+@pytest.mark.parametrize("metric", ["SquaredEuclidean", "InnerProduct"])
+def test_gpu_streamer_add_search_interleaved_equals_flat_streamer(metric, tmp_path):
+    assert S.ref().zref_has_searcher(b"GpuFlatSearcher") == 1
+    d, k = 24, 10
+    rng = np.random.default_rng(5)
+    x = rng.standard_normal((3000, d)).astype(np.float32)
+    qs = rng.standard_normal((16, d)).astype(np.float32)
+    g = _Streamer("GpuFlatStreamer", S.DT_FP32, d, metric, str(tmp_path / "gpu.index"))
+    r = _Streamer("FlatStreamer", S.DT_FP32, d, metric, str(tmp_path / "ref.index"))
+    # searches on an empty streamer, then after every batch of adds (keys are not row numbers)
+    _same(g.search(qs[:2], k), r.search_each(qs[:2], k), "empty")
+    pos = 0
+    for step in (1, 4, 60, 935, 2000):
+        for i in range(pos, pos + step):
+            key = 1000003 * (i + 1) % 2**40
+            assert g.add(key, x[i]) == r.add(key, x[i]) == 0
+        pos += step
+        _same(g.search(qs, k), r.search_each(qs, k), "after %d rows" % pos)          # batch
+        _same(g.search(qs[:1], k), r.search(qs[:1], k), "after %d rows, one query" % pos)
+    # a duplicate key is refused by both, with the same code, and changes nothing
+    assert g.add(1000003, x[0]) == r.add(1000003, x[0]) != 0
+    _same(g.search(qs, k), r.search_each(qs, k), "after duplicate")
+    # key filter + radius threshold through IndexContext
+    S.ref().zref_set_filter(3, 1)
+    _same(g.search(qs, k), r.search_each(qs, k), "filter")
+    S.ref().zref_set_filter(0, 0)
+    thr = float(np.median(r.search_each(qs, k)[1]))
+    S.ref().zref_set_threshold(1, thr)
+    try:
+        _same(g.search(qs, k), r.search_each(qs, k), "threshold")
+    finally:
+        S.ref().zref_set_threshold(0, 0.0)
+    assert g.close(flush=True) == 0 and r.close(flush=True) == 0
+    # re-open the storage the GPU streamer wrote: the rows come back from the stock format
+    g2 = _Streamer("GpuFlatStreamer", S.DT_FP32, d, metric, str(tmp_path / "gpu.index"))
+    r2 = _Streamer("FlatStreamer", S.DT_FP32, d, metric, str(tmp_path / "ref.index"))
+    _same(g2.search(qs, k), r2.search_each(qs, k), "re-opened")
+    g2.close(); r2.close()
+
+
+@needs_plugin
+@pytest.mark.gpu
+def test_gpu_streamer_add_with_id_holes_and_overwrite(tmp_path):
+    d, k = 16, 8
+    rng = np.random.default_rng(6)
+    x = rng.standard_normal((600, d)).astype(np.float32)
+    qs = rng.standard_normal((8, d)).astype(np.float32)
+    g = _Streamer("GpuFlatStreamer", S.DT_FP32, d, "SquaredEuclidean", str(tmp_path / "gpu.index"))
+    r = _Streamer("FlatStreamer", S.DT_FP32, d, "SquaredEuclidean", str(tmp_path / "ref.index"))
+    for i in range(0, 400, 2):                       # even ids first: odd ids are kInvalidKey holes
+        assert g.add_with_id(i, x[i]) == r.add_with_id(i, x[i]) == 0
+    _same(g.search(qs, k), r.search_each(qs, k), "holes")
+    for i in range(1, 400, 2):                       # fill the holes: in-place writes on the device
+        assert g.add_with_id(i, x[i]) == r.add_with_id(i, x[i]) == 0
+    _same(g.search(qs, k), r.search_each(qs, k), "filled")
+    for i in (3, 77, 398):                           # overwrite live rows
+        assert g.add_with_id(i, x[500 + i % 50]) == r.add_with_id(i, x[500 + i % 50]) == 0
+    _same(g.search(qs, k), r.search_each(qs, k), "overwritten")
+    g.close(); r.close()
+
+
+OVERRIDE_SCRIPT = r"""
+import ctypes as C, sys, numpy as np
+sys.path.insert(0, %(tests)r); sys.path.insert(0, %(root)r)
+import support as S
+import test_plugin as T
+import zvec_b200 as z
+assert S.load_plugin()
+plug = C.CDLL(S.PLUGIN)
+assert plug.zvb200_install_overrides() == 0
+before = z.lib().zvb200_kernel_launches()
+s = T._Streamer("FlatStreamer", S.DT_FP32, 8, "SquaredEuclidean", %(path)r)      # the STOCK name
+x = np.random.default_rng(7).standard_normal((50, 8)).astype(np.float32)
+for i in range(50):
+    assert s.add(i, x[i]) == 0
+keys, scores, counts = s.search(x[:3], 5)
+assert list(keys[:, 0]) == [0, 1, 2]
+assert z.lib().zvb200_kernel_launches() > before, "the stock name did not reach the GPU class"
+s.close()
+ri = S.RefIndex(x, S.DT_FP32, 8, "SquaredEuclidean", "", kind="Flat")              # stock FlatSearcher name
+before = z.lib().zvb200_kernel_launches()
+k2, s2, _, c2 = ri.search(x[:3], 5)
+assert list(k2[:, 0]) == [0, 1, 2] and z.lib().zvb200_kernel_launches() > before
+print("OVERRIDES-OK")
+"""
+
+
+@needs_plugin
+@pytest.mark.gpu
+def test_install_overrides_routes_stock_names_to_the_gpu_classes(tmp_path):
+    """zvb200_install_overrides() re-registers "FlatSearcher" / "FlatStreamer": in its own process, because the
+    rest of this suite uses the stock classes under those names as the oracle."""
+    import os, subprocess, sys
+    here = os.path.dirname(os.path.abspath(__file__))
+    code = OVERRIDE_SCRIPT % {"tests": here, "root": os.path.dirname(here), "path": str(tmp_path / "o.index")}
+    out = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=600)
+    assert out.returncode == 0 and "OVERRIDES-OK" in out.stdout, out.stdout + out.stderr

@@ -39,6 +39,7 @@ _SIGS = {
     "zvb200_store_seal": (C.c_int, [C.c_void_p]),
     "zvb200_store_count": (C.c_uint64, [C.c_void_p]),
     "zvb200_store_set_deleted": (C.c_int, [C.c_void_p, C.c_uint64, C.c_int]),
+    "zvb200_store_write": (C.c_int, [C.c_void_p, C.c_uint64, C.c_void_p, C.c_uint64]),
     "zvb200_store_get_vector": (C.c_int, [C.c_void_p, C.c_uint64, C.c_void_p, C.c_size_t]),
     "zvb200_store_scan_bytes": (C.c_uint64, [C.c_void_p]),
     "zvb200_ctx_create": (C.c_int, [C.c_void_p, C.POINTER(C.c_void_p)]),
@@ -152,6 +153,11 @@ class Store:
         out = np.zeros(self.elem_bytes, np.uint8)
         _check(lib().zvb200_store_get_vector(self.h, row, _ptr(out), out.nbytes))
         return out
+
+    def write(self, row, vec, key):
+        """overwrite one row in place (FlatStreamerEntity::add_vector_with_id, id < count)"""
+        vec = np.ascontiguousarray(vec)
+        _check(lib().zvb200_store_write(self.h, row, _ptr(vec), key))
 
     def ivf_attach(self, centroids, list_offsets):
         """centroids: nlist elements in the store's layout; rows [list_offsets[l], list_offsets[l+1]) = list l."""

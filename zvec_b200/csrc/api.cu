@@ -334,6 +334,36 @@ int zvb200_store_set_deleted(zvb200_store *s, uint64_t row, int deleted) {
   return sync_drop(s);
 }
 
+int zvb200_store_write(zvb200_store *s, uint64_t row, const void *vec, uint64_t key) {
+  if (!s || !vec || row >= s->n) return set_err(ZVB200_ERR_INVALID_ARGUMENT, "bad argument");
+  std::lock_guard<std::mutex> g(s->mu);
+  CU(cudaSetDevice(s->device));
+  if (!s->staging) {
+    s->staging_bytes = std::max<size_t>(1, ((size_t)64 << 20) / s->elem_bytes) * s->elem_bytes;
+    CU(cudaMalloc((void **)&s->staging, s->staging_bytes));
+  }
+  CU(cudaMemcpyAsync(s->staging, vec, s->elem_bytes, cudaMemcpyHostToDevice, s->stream));
+  CU(launch_repack_rows(s->staging, s->elem_bytes, 1, s->rows + row * s->row_stride, s->row_stride, s->vec_bytes,
+                        s->has_tail ? s->tails + row : nullptr, s->tail_off, s->stream));
+  if (s->norms && row < s->normed) {
+    RowsView v = s->view();
+    CU(launch_row_norms(v, row, row + 1, s->norms, s->stream));
+  }
+  CU(cudaStreamSynchronize(s->stream));
+  if (s->keys.empty() && key != row) { s->keys.resize(s->n); for (uint64_t i = 0; i < s->n; ++i) s->keys[i] = i; }
+  if (!s->keys.empty()) s->keys[row] = key;
+  const bool hole = key == ZVB200_INVALID_KEY;
+  const bool was = s->has_drop && (row >> 5) < s->drop_host.size() && ((s->drop_host[row >> 5] >> (row & 31)) & 1u);
+  if (hole != was) {
+    s->drop_host.resize((s->n + 31) / 32, 0u);
+    if (hole) s->drop_host[row >> 5] |= 1u << (row & 31);
+    else s->drop_host[row >> 5] &= ~(1u << (row & 31));
+    s->has_drop = true; s->drop_dirty = true;
+    return sync_drop(s);
+  }
+  return 0;
+}
+
 int zvb200_store_get_vector(const zvb200_store *s, uint64_t row, void *out, size_t cap) {
   if (!s || !out || row >= s->n) return set_err(ZVB200_ERR_INVALID_ARGUMENT, "bad argument");
   if (cap < s->elem_bytes) return set_err(ZVB200_ERR_INVALID_ARGUMENT, "buffer too small");
