@@ -185,8 +185,12 @@ int zvb200_ivf_attach(zvb200_store *s, const void *centroids, uint32_t nlist,
  * ceil(N*scan_ratio)): lists are visited in coarse order while the rows scanned so far
  * are < max_scan_count. */
 int zvb200_ivf_search(zvb200_ctx *c, const void *queries, uint32_t q, uint32_t k,
-                      uint32_t nprobe, uint64_t max_scan_count, uint64_t *out_keys,
-                      float *out_scores, uint32_t *out_index, uint32_t *out_counts);
+                      uint32_t nprobe, uint64_t max_scan_count, float threshold,
+                      const uint32_t *filter_bitmap, uint64_t *out_keys, float *out_scores,
+                      uint32_t *out_index, uint32_t *out_counts);
+/* threshold / filter_bitmap as in zvb200_search (bit i = drop stored row i, list order): a filtered list
+ * still counts whole against the scan budget, like IVFEntity::search(list, query, filter, ...)
+ * (ivf_entity.cc:587-659). */
 
 #ifdef __cplusplus
 }

@@ -23,9 +23,15 @@
 
 #include <cstring>
 #include <limits>
+#include <map>
 #include <mutex>
 #include <string>
 #include <vector>
+
+#include <cmath>
+
+#include <zvec/core/framework/index_segment_storage.h>
+#include "core/algorithm/ivf/ivf_searcher.h"  // the stock IVF classes, used by type (composition)
 
 #include "../include/zvec_b200.h"
 
@@ -519,6 +525,288 @@ void GpuFlatStreamerContext::reset(const GpuFlatStreamer *owner) {
 
 INDEX_FACTORY_REGISTER_STREAMER(GpuFlatStreamer);
 
+// ======================================================================================
+// GpuIVFSearcher — IVFSearcher's interface (ivf_searcher.h:28-118).  Composition: a stock
+// IVFSearcher loads the index (centroid index, reformer wiring, brute-force / group-by paths,
+// integer-quantised variants whose scores need per-list scales) and serves whatever is not
+// accelerated; the posting lists it holds are exported ONCE through the reference's own
+// IVFEntity reader into a device store grouped by list, the centroids of its nested Flat index
+// become the coarse store, and search_impl is zvb200_ivf_search.
+// ======================================================================================
+class GpuIVFSearcher;
+
+class GpuIVFContext : public IndexContext {
+ public:
+  GpuIVFContext(const GpuIVFSearcher *owner, IndexContext::Pointer inner) : inner_(std::move(inner)) { this->reset(owner); }
+  ~GpuIVFContext() override {
+    if (ctx_) zvb200_ctx_destroy(ctx_);
+  }
+  void set_topk(uint32_t topk) override { topk_ = topk; if (inner_) inner_->set_topk(topk); }
+  uint32_t topk() const override { return topk_; }
+  const IndexDocumentList &result(void) const override { return results_[0]; }
+  const IndexDocumentList &result(size_t i) const override { return results_[i]; }
+  IndexDocumentList *mutable_result(size_t i) override { return &results_[i]; }
+  uint32_t magic(void) const override { return magic_; }
+  int update(const ailego::Params &params) override;
+  void reset(const GpuIVFSearcher *owner);
+  zvb200_ctx *handle() const { return ctx_; }
+  IndexContext::Pointer &inner() { return inner_; }
+  void resize_results(size_t n) {
+    if (results_.size() < n) results_.resize(n);
+  }
+  uint32_t nprobe{1};
+  uint64_t max_scan{0};
+  std::vector<uint64_t> keys;
+  std::vector<float> scores;
+  std::vector<uint32_t> index, counts, bitmap;
+
+ private:
+  const GpuIVFSearcher *owner_{nullptr};
+  uint32_t topk_{0};
+  uint32_t magic_{0};
+  zvb200_ctx *ctx_{nullptr};
+  IndexContext::Pointer inner_{};
+  std::vector<IndexDocumentList> results_{1};
+};
+
+class GpuIVFSearcher : public IndexSearcher {
+ public:
+  GpuIVFSearcher() = default;
+  ~GpuIVFSearcher() override { this->unload(); }
+
+  int init(const ailego::Params &params) override {
+    params_ = params;
+    params.get("proxima.gpu.device", &device_);
+    params.get(PARAM_IVF_SEARCHER_BRUTE_FORCE_THRESHOLD, &bf_threshold_);
+    return stock_.init(params);
+  }
+  int cleanup(void) override {
+    this->unload();
+    return stock_.cleanup();
+  }
+
+  int load(IndexStorage::Pointer cntr, IndexMetric::Pointer measure) override {
+    int rc = stock_.load(cntr, measure);
+    if (rc != 0) return rc;
+    meta_ = stock_.meta();
+    magic_ = IndexContext::GenerateMagic();
+    rc = entity_.load(cntr);
+    if (rc != 0) return rc;
+    // scores of the integer-quantised variants carry per-list / global scales (IVFEntity::load,
+    // ivf_entity.cc:541-564; IVFReformerWrapper::normalize :325-353): those stay on the stock path
+    const std::string &rf = meta_.reformer_name();
+    accelerated_ = !cntr->get(IVF_INT8_QUANTIZED_PARAMS_SEG_ID) && !cntr->get(IVF_INT4_QUANTIZED_PARAMS_SEG_ID) &&
+                   rf != kInt8ReformerName && rf != kInt4ReformerName && metric_of(meta_) >= 0 && dtype_of(meta_) >= 0 &&
+                   entity_.vector_count() > bf_threshold_;
+    if (!accelerated_) return 0;
+    // centroids = the nested Flat index in segment "ivf.centroid" (ivf_searcher.cc:62-86); row cid = centroid cid
+    auto seg = cntr->get(IVF_CENTROID_SEG_ID, 0);
+    if (!seg) return IndexError_InvalidFormat;
+    IndexStorage::Pointer nested = std::make_shared<IndexSegmentStorage>(seg);
+    if ((rc = nested->open(std::string(), false)) != 0) return rc;
+    IndexMeta cmeta;
+    if ((rc = IndexHelper::DeserializeFromStorage(nested.get(), &cmeta)) != 0) return rc;
+    auto fseg = nested->get(kSegFeatures), kseg = nested->get(kSegKeys);
+    const size_t nl = entity_.inverted_list_count(), n = entity_.vector_count(), es = meta_.element_size();
+    if (!fseg || !kseg || cmeta.element_size() != es || cmeta.data_type() != meta_.data_type() ||
+        kseg->data_size() != nl * sizeof(uint64_t) || fseg->data_size() != nl * es) {
+      accelerated_ = false;  // a centroid index of another shape (e.g. HNSW over centroids): stock path
+      return 0;
+    }
+    const void *fp = nullptr;
+    const uint64_t *kp = nullptr;
+    if (fseg->read(0, &fp, fseg->data_size()) != fseg->data_size()) return IndexError_ReadData;
+    if (kseg->read(0, reinterpret_cast<const void **>(&kp), kseg->data_size()) != kseg->data_size()) return IndexError_ReadData;
+    std::vector<char> cent(nl * es);
+    const bool col = cmeta.major_order() == IndexMeta::MO_COLUMN;
+    const size_t us = IndexMeta::AlignSizeof(cmeta.data_type()), units = es / us;
+    for (size_t i = 0; i < nl; ++i) {
+      if (kp[i] >= nl) return IndexError_InvalidFormat;
+      char *dst = &cent[(size_t)kp[i] * es];
+      const size_t blk = i / 32 * 32;
+      if (col && blk + 32 <= nl) {
+        const char *b = static_cast<const char *>(fp) + blk * es;
+        for (size_t u = 0; u < units; ++u) std::memcpy(dst + u * us, b + (u * 32 + (i - blk)) * us, us);
+      } else {
+        std::memcpy(dst, static_cast<const char *>(fp) + i * es, es);
+      }
+    }
+    // posting lists in list order through IVFEntity (ivf_entity.h:89-170): rows + keys + offsets
+    zvb200_store *st = nullptr;
+    if ((rc = zvb200_store_create(device_, dtype_of(meta_), metric_of(meta_), meta_.dimension(), &st)) != 0) return rc;
+    rc = zvb200_store_reserve(st, n);
+    std::vector<uint64_t> offs(nl + 1, 0);
+    std::vector<char> rows;
+    std::vector<uint64_t> keys;
+    keys_.clear(); keys_.reserve(n);
+    size_t pos = 0;
+    auto flush = [&]() -> int {
+      if (keys.empty()) return 0;
+      const int r = zvb200_store_append(st, rows.data(), keys.size(), keys.data());
+      rows.clear(); keys.clear();
+      return r;
+    };
+    for (size_t l = 0; rc == 0 && l < nl; ++l) {
+      auto lm = entity_.inverted_list_meta(l);
+      if (!lm) { rc = IndexError_ReadData; break; }
+      offs[l] = pos;
+      auto lk = entity_.get_keys(lm->id_offset, lm->vector_count);
+      if (!lk && lm->vector_count) { rc = IndexError_ReadData; break; }
+      for (size_t j = 0; j < lm->vector_count; ++j, ++pos) {
+        const void *v = entity_.get_vector(lm->id_offset + j);
+        if (!v) { rc = IndexError_ReadData; break; }
+        rows.insert(rows.end(), static_cast<const char *>(v), static_cast<const char *>(v) + es);
+        keys.push_back(lk[j]);
+        keys_.push_back(lk[j]);
+      }
+      if (rows.size() >= ((size_t)64 << 20)) rc = flush();
+    }
+    if (rc == 0) rc = flush();
+    offs[nl] = pos;
+    if (rc == 0 && pos != n) rc = IndexError_InvalidFormat;
+    if (rc == 0) rc = zvb200_store_seal(st);
+    if (rc == 0) rc = zvb200_ivf_attach(st, cent.data(), (uint32_t)nl, offs.data());
+    if (rc != 0) { zvb200_store_destroy(st); return rc; }
+    store_ = st;
+    return 0;
+  }
+
+  int unload(void) override {
+    if (store_) zvb200_store_destroy(store_);
+    store_ = nullptr;
+    keys_.clear();
+    return 0;
+  }
+
+  int search_bf_impl(const void *query, const IndexQueryMeta &qmeta, Context::Pointer &context) const override {
+    return this->search_bf_impl(query, qmeta, 1, context);
+  }
+  int search_bf_impl(const void *query, const IndexQueryMeta &qmeta, uint32_t count, Context::Pointer &context) const override {
+    return delegate(true, query, qmeta, count, context);
+  }
+  int search_impl(const void *query, const IndexQueryMeta &qmeta, Context::Pointer &context) const override {
+    return this->search_impl(query, qmeta, 1, context);
+  }
+
+  //! IVFSearcher::search_impl (ivf_searcher.cc:183-250)
+  int search_impl(const void *query, const IndexQueryMeta &qmeta, uint32_t count, Context::Pointer &context) const override {
+    auto *ctx = dynamic_cast<GpuIVFContext *>(context.get());
+    if (!ctx || ctx->topk() == 0) return IndexError_InvalidArgument;
+    if (!accelerated_ || !store_ || ctx->group_by().is_valid()) return delegate(false, query, qmeta, count, context);
+    if (!query || qmeta.element_size() != meta_.element_size()) return IndexError_InvalidArgument;
+    if (ctx->magic() != magic_) ctx->reset(this);
+    // queries into the posting lists' format (entity->transform, ivf_searcher.cc:211-214)
+    const void *tq = query;
+    IndexQueryMeta iv_qmeta;
+    int rc = entity_for(ctx)->transform(query, qmeta, count, &tq, &iv_qmeta);
+    if (rc != 0) return rc;
+    const uint32_t k = ctx->topk();
+    const size_t n = keys_.size();
+    const uint32_t *bitmap = nullptr;
+    if (ctx->filter().is_valid()) {
+      ctx->bitmap.assign((n + 31) / 32, 0u);
+      for (size_t i = 0; i < n; ++i)
+        if (ctx->filter()(keys_[i])) ctx->bitmap[i >> 5] |= 1u << (i & 31);
+      bitmap = ctx->bitmap.data();
+    }
+    const size_t nres = (size_t)count * k;
+    ctx->keys.resize(nres); ctx->scores.resize(nres); ctx->index.resize(nres); ctx->counts.resize(count);
+    rc = zvb200_ivf_search(ctx->handle(), tq, count, k, ctx->nprobe, ctx->max_scan, ctx->threshold(), bitmap,
+                           ctx->keys.data(), ctx->scores.data(), ctx->index.data(), ctx->counts.data());
+    if (rc != 0) return rc;
+    ctx->resize_results(count);
+    for (uint32_t i = 0; i < count; ++i) {
+      IndexDocumentList *out = ctx->mutable_result(i);
+      out->clear();
+      for (uint32_t j = 0; j < ctx->counts[i]; ++j) {
+        const size_t o = (size_t)i * k + j;
+        out->emplace_back(ctx->keys[o], ctx->scores[o]);  // key and score only (ivf_searcher_context.h:196)
+      }
+    }
+    return 0;
+  }
+
+  Context::Pointer create_context(void) const override {
+    auto inner = stock_.create_context();
+    if (!inner) return Context::Pointer();
+    auto *c = new (std::nothrow) GpuIVFContext(this, std::move(inner));
+    if (c) c->update(params_);
+    return Context::Pointer(c);
+  }
+  IndexProvider::Pointer create_provider(void) const override { return stock_.create_provider(); }
+  const Stats &stats(void) const override { return stock_.stats(); }
+  const IndexMeta &meta(void) const override { return meta_; }
+  const ailego::Params &params(void) const override { return params_; }
+  uint32_t magic(void) const { return magic_; }
+  zvb200_store *store(void) const { return store_; }
+  size_t list_count(void) const { return entity_.inverted_list_count(); }
+  size_t vector_count(void) const { return entity_.vector_count(); }
+  uint32_t bf_threshold(void) const { return bf_threshold_; }
+
+ private:
+  // the reformer inside an IVFEntity keeps a scratch buffer: one clone per context (IVFSearcher::update_context)
+  IVFEntity *entity_for(GpuIVFContext *ctx) const {
+    std::lock_guard<std::mutex> g(mu_);
+    auto &e = clones_[ctx];
+    if (!e) e = entity_.clone();
+    return e.get();
+  }
+  //! what is not accelerated runs on the stock searcher with the caller's settings, results copied back
+  int delegate(bool bf, const void *query, const IndexQueryMeta &qmeta, uint32_t count, Context::Pointer &context) const {
+    auto *ctx = dynamic_cast<GpuIVFContext *>(context.get());
+    if (!ctx) return IndexError_InvalidArgument;
+    auto &in = ctx->inner();
+    in->set_topk(ctx->topk());
+    if (ctx->filter().is_valid()) in->set_filter(ctx->filter());
+    in->set_threshold(ctx->threshold());
+    const int rc = bf ? stock_.search_bf_impl(query, qmeta, count, in) : stock_.search_impl(query, qmeta, count, in);
+    if (rc != 0) return rc;
+    ctx->resize_results(count);
+    for (uint32_t i = 0; i < count; ++i) *ctx->mutable_result(i) = in->result(i);
+    return 0;
+  }
+
+  IVFSearcher stock_{};
+  IVFEntity entity_{};
+  mutable std::mutex mu_{};
+  mutable std::map<const GpuIVFContext *, IVFEntity::Pointer> clones_{};
+  ailego::Params params_{};
+  IndexMeta meta_{};
+  std::vector<uint64_t> keys_{};
+  zvb200_store *store_{nullptr};
+  uint32_t bf_threshold_{1000u};
+  uint32_t magic_{0};
+  int device_{0};
+  bool accelerated_{false};
+};
+
+//! IVFSearcherContext::update (ivf_searcher_context.h:61-79)
+int GpuIVFContext::update(const ailego::Params &params) {
+  if (!owner_) return IndexError_NoReady;
+  uint32_t bf = owner_->bf_threshold();
+  float ratio = 0.1f;  // kDefaultScanRatio (ivf_searcher_context.h:205)
+  owner_->params().get(PARAM_IVF_SEARCHER_SCAN_RATIO, &ratio);
+  owner_->params().get(PARAM_IVF_SEARCHER_BRUTE_FORCE_THRESHOLD, &bf);
+  params.get(PARAM_IVF_SEARCHER_BRUTE_FORCE_THRESHOLD, &bf);
+  params.get(PARAM_IVF_SEARCHER_SCAN_RATIO, &ratio);
+  if (ratio <= 0.0f) return IndexError_InvalidArgument;
+  nprobe = std::max(static_cast<uint32_t>(std::round(owner_->list_count() * ratio)), 1u);
+  max_scan = std::max(bf, static_cast<uint32_t>(std::ceil(owner_->vector_count() * ratio)));
+  return inner_ ? inner_->update(params) : 0;
+}
+
+void GpuIVFContext::reset(const GpuIVFSearcher *owner) {
+  if (ctx_) zvb200_ctx_destroy(ctx_);
+  ctx_ = nullptr;
+  owner_ = owner;
+  magic_ = owner->magic();
+  if (owner->store()) zvb200_ctx_create(owner->store(), &ctx_);
+  for (auto &r : results_) r.clear();
+  this->update(owner->params());
+}
+
+INDEX_FACTORY_REGISTER_SEARCHER(GpuIVFSearcher);
+
 }  // namespace core
 }  // namespace zvec
 
@@ -529,6 +817,7 @@ INDEX_FACTORY_REGISTER_STREAMER(GpuFlatStreamer);
 extern "C" int zvb200_install_overrides(void) {
   static zvec::ailego::Factory<zvec::core::IndexSearcher>::Register<zvec::core::GpuFlatSearcher> r("FlatSearcher");
   static zvec::ailego::Factory<zvec::core::IndexStreamer>::Register<zvec::core::GpuFlatStreamer> rs("FlatStreamer");
-  (void)r; (void)rs;
+  static zvec::ailego::Factory<zvec::core::IndexSearcher>::Register<zvec::core::GpuIVFSearcher> ri("IVFSearcher");
+  (void)r; (void)rs; (void)ri;
   return 0;
 }

@@ -182,6 +182,24 @@ void *zref_index_create(const char *kind, const void *rows, uint64_t n, uint32_t
 
 void zref_index_destroy(void *h) { delete (RefIndex *)h; }
 
+// Replace the index's searcher by another registered class over the SAME file (an IVF build trains
+// k-means with threads: two builds of the same rows are two different indexes).
+int zref_index_use_searcher(void *h, const char *searcher_name, const char *search_params) {
+  auto ix = (RefIndex *)h;
+  auto sr = IndexFactory::CreateSearcher(searcher_name);
+  auto storage = IndexFactory::CreateStorage("MMapFileReadStorage");
+  if (!sr || !storage) return fail(-1, "no searcher");
+  Params sp; parse_params(search_params, &sp);
+  int r = sr->init(sp);
+  if (r != 0) return fail(r, "searcher init");
+  if (storage->open(ix->path, false) != 0) return fail(-1, "storage open");
+  r = sr->load(storage, IndexMetric::Pointer());
+  if (r != 0) return fail(r, "searcher load");
+  if (ix->searcher) { ix->searcher->unload(); ix->searcher->cleanup(); }
+  ix->searcher = sr;
+  return 0;
+}
+
 // Load an index plugin with the reference's OWN loader (IndexPluginBroker -> IndexPlugin::load
 // -> dlopen, src/core/framework/index_plugin.cc:20-56), as tools/core/bench.cc:796-803 does
 // for its trailing argv.  Returns 0 or -1 (zref_last_error()).

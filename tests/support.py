@@ -167,6 +167,12 @@ class RefIndex:
             raise AssertionError("search_impl returned %d (%s)" % (r, zvec_b200.lib().zvb200_last_error().decode()))
         return keys, scores, index, counts
 
+    def use_searcher(self, name, search_params=""):
+        """search the same index file with another registered searcher class"""
+        self.L.zref_index_use_searcher.argtypes = [C.c_void_p, C.c_char_p, C.c_char_p]
+        if self.L.zref_index_use_searcher(self.h, name.encode(), search_params.encode()) != 0:
+            raise RuntimeError(self.L.zref_last_error().decode())
+
     def distances(self, stored_rows, stored_query):
         stored_rows = np.ascontiguousarray(stored_rows)
         n = stored_rows.nbytes // self.elem

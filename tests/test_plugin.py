@@ -252,3 +252,55 @@ def test_install_overrides_routes_stock_names_to_the_gpu_classes(tmp_path):
     code = OVERRIDE_SCRIPT % {"tests": here, "root": os.path.dirname(here), "path": str(tmp_path / "o.index")}
     out = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=600)
     assert out.returncode == 0 and "OVERRIDES-OK" in out.stdout, out.stdout + out.stderr
+
+
+# ---- GpuIVFSearcher: the reference's IVFBuilder builds, both searcher classes search the same file ----
+@needs_plugin
+@pytest.mark.gpu
+@pytest.mark.parametrize("metric,conv", [("SquaredEuclidean", ""), ("Cosine", "CosineNormalizeConverter"),
+                                         ("SquaredEuclidean", "HalfFloatConverter"),
+                                         ("SquaredEuclidean", "Int8StreamingConverter")])
+def test_gpu_ivf_searcher_equals_ivf_searcher(metric, conv):
+    assert S.ref().zref_has_searcher(b"GpuIVFSearcher") == 1
+    n, d, nlist, k = 20000, 32, 64, 10
+    rng = np.random.default_rng(8)
+    centres = rng.standard_normal((nlist, d)).astype(np.float32)
+    x = (centres[np.arange(n) % nlist] + 0.3 * rng.standard_normal((n, d))).astype(np.float32)
+    qs = (centres[rng.integers(0, nlist, 40)] + 0.3 * rng.standard_normal((40, d))).astype(np.float32)
+    bp = "proxima.ivf.builder.centroid_count=%d" % nlist
+    sp = "proxima.ivf.searcher.scan_ratio=0.1"
+    ix = S.RefIndex(x, S.DT_FP32, d, metric, conv, kind="IVF", build_params=bp, search_params=sp)
+    import zvec_b200 as z
+    exact = conv == "Int8StreamingConverter"
+
+    def same(a, b, what):
+        for i in range(len(a[3])):
+            assert a[3][i] == b[3][i], what
+            nv = int(a[3][i])
+            if exact:
+                assert np.array_equal(a[1][i][:nv].view(np.uint32), b[1][i][:nv].view(np.uint32)), what
+            else:
+                assert np.allclose(a[1][i][:nv], b[1][i][:nv], rtol=1e-4, atol=1e-6), what
+            diff = a[0][i][:nv] != b[0][i][:nv]           # ids: equal, or swapped only inside near-ties
+            if diff.any():
+                assert np.allclose(a[1][i][:nv][diff], b[1][i][:nv][diff], rtol=1e-4), what
+            assert np.array_equal(a[2][i][:nv][~diff], b[2][i][:nv][~diff]), what      # index() = local id
+
+    # the stock IVFSearcher first, then the GPU class over the SAME file (two builds would be two clusterings)
+    r_batch = ix.search(qs, k, batch=len(qs)); r_one = ix.search(qs, k, batch=1)
+    S.ref().zref_set_filter(4, 2)
+    try:
+        r_filt = ix.search(qs, k, batch=8)
+    finally:
+        S.ref().zref_set_filter(0, 0)
+    ix.use_searcher("GpuIVFSearcher", sp)
+    before = z.lib().zvb200_kernel_launches()
+    same(ix.search(qs, k, batch=len(qs)), r_batch, "batch")
+    same(ix.search(qs, k, batch=1), r_one, "one by one")
+    assert z.lib().zvb200_kernel_launches() > before              # the GPU path ran, not the delegate
+    S.ref().zref_set_filter(4, 2)
+    try:
+        same(ix.search(qs, k, batch=8), r_filt, "filter")
+    finally:
+        S.ref().zref_set_filter(0, 0)
+    ix.close()

@@ -63,8 +63,8 @@ _SIGS = {
                                        C.c_uint32, C.c_uint32, C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p,
                                        C.c_void_p]),
     "zvb200_ivf_attach": (C.c_int, [C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p]),
-    "zvb200_ivf_search": (C.c_int, [C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint64,
-                                    C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "zvb200_ivf_search": (C.c_int, [C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint64, C.c_float,
+                                    C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
 }
 
 
@@ -219,16 +219,18 @@ class Context:
                                    _ptr(keys), _ptr(scores), _ptr(index), _ptr(counts)))
         return keys, scores, index, counts
 
-    def ivf_search(self, queries, k, nprobe, max_scan_count):
+    def ivf_search(self, queries, k, nprobe, max_scan_count, threshold=FLT_MAX, filter_bitmap=None):
         """IVFSearcher::search_impl semantics -> (keys u64, scores f32, index u32, counts u32)."""
         queries = np.ascontiguousarray(queries)
+        if filter_bitmap is not None:
+            filter_bitmap = np.ascontiguousarray(filter_bitmap, np.uint32)
         q = queries.nbytes // self.store.elem_bytes
         keys = np.empty((q, k), np.uint64)
         scores = np.empty((q, k), np.float32)
         index = np.empty((q, k), np.uint32)
         counts = np.empty(q, np.uint32)
-        _check(lib().zvb200_ivf_search(self.h, _ptr(queries), q, k, nprobe, max_scan_count,
-                                       _ptr(keys), _ptr(scores), _ptr(index), _ptr(counts)))
+        _check(lib().zvb200_ivf_search(self.h, _ptr(queries), q, k, nprobe, max_scan_count, threshold,
+                                       _ptr(filter_bitmap), _ptr(keys), _ptr(scores), _ptr(index), _ptr(counts)))
         return keys, scores, index, counts
 
     def fuse_rrf(self, keys, counts, topn, rank_constant=60):

@@ -720,8 +720,8 @@ int zvb200_ivf_attach(zvb200_store *s, const void *centroids, uint32_t nlist, co
 }
 
 int zvb200_ivf_search(zvb200_ctx *c, const void *queries, uint32_t q, uint32_t k, uint32_t nprobe,
-                      uint64_t max_scan_count, uint64_t *out_keys, float *out_scores, uint32_t *out_index,
-                      uint32_t *out_counts) {
+                      uint64_t max_scan_count, float threshold, const uint32_t *filter_bitmap, uint64_t *out_keys,
+                      float *out_scores, uint32_t *out_index, uint32_t *out_counts) {
   int r = check_search_args(c, queries, q, k);
   if (r != 0) return r;
   if (!out_scores) return set_err(ZVB200_ERR_INVALID_ARGUMENT, "null out_scores");
@@ -758,7 +758,13 @@ int zvb200_ivf_search(zvb200_ctx *c, const void *queries, uint32_t q, uint32_t k
   // 3. posting-list scan, queries already in compute layout (same dtype / metric / dim as the centroids)
   RowsView rv = s->view();
   SearchParams sp;
-  sp.k = k; sp.threshold = FLT_MAX; sp.filter = nullptr;
+  sp.k = k; sp.threshold = threshold; sp.filter = nullptr;
+  if (filter_bitmap) {
+    const size_t fb = (size_t)((s->n + 31) / 32) * 4;
+    CU(c->filter.ensure(fb));
+    CU(cudaMemcpyAsync(c->filter.p, filter_bitmap, fb, cudaMemcpyHostToDevice, c->stream));
+    sp.filter = (const uint32_t *)c->filter.p;
+  }
   const bool lists_stream = c->force_kernel == 4 && scan_stream_supports(rv, k, nprobe);
   const size_t parts = lists_stream ? scan_lists_stream_parts(q, s->sm_count) : scan_lists_parts(q, s->sm_count);
   CU(c->part.ensure((size_t)q * parts * k * sizeof(u64)));
