@@ -233,7 +233,7 @@ def test_tile_kernel_topk_sizes(k):
 def test_tile_kernel_auto_selected_for_batches_and_filters():
     n = 3000
     rng = np.random.default_rng(35)
-    assert run_case("qi8_l2", n, 32, 128, 10, seed=35) == "scan_tile"
+    assert run_case("i8_l2", 600, 1100, 40, 10, seed=35) == "scan_tile"     # int8 beyond d = 1040: exact CUDA-core tile
     drop = rng.random(n) < 0.3
     filt = rng.random(n) < 0.3
     run_case("fp16_l2", n, 32, 40, 10, seed=36, kernel=2, drop=drop, filt=filt)
@@ -253,8 +253,10 @@ def test_tile_and_gemv_agree_bitwise_on_int8():
 
 
 # ---- K2 tcgen05 / TMEM kernel: fp16 InnerProduct / Cosine straight from the accumulator; fp16 L2 and
-# every fp32 metric (kind::tf32) with the accumulator as filter + exact re-score -------------------
-MMA_KINDS = ["fp16_ip", "fp16_cos", "fp16_l2", "fp32_l2", "fp32_l2sqrt", "fp32_ip", "fp32_cos"]
+# every fp32 metric (kind::tf32) with the accumulator as filter + exact re-score; int8 and QuantizedInteger
+# (kind::i8, exact int32 accumulators, the reference's float epilogue per column: bit-exact) ------------
+MMA_KINDS = ["fp16_ip", "fp16_cos", "fp16_l2", "fp32_l2", "fp32_l2sqrt", "fp32_ip", "fp32_cos",
+             "i8_l2", "i8_ip", "qi8_l2", "qi8_ip", "qi8_cos"]
 
 
 @pytest.mark.parametrize("kind", MMA_KINDS)
@@ -263,23 +265,23 @@ def test_mma_kernel_parity(kind, q):
     assert run_case(kind, 5000, 96, q, 10, seed=51 + q, kernel=3) == "scan_mma"
 
 
-@pytest.mark.parametrize("kind", ["fp16_ip", "fp16_l2", "fp32_l2", "fp32_cos"])
+@pytest.mark.parametrize("kind", ["fp16_ip", "fp16_l2", "fp32_l2", "fp32_cos", "qi8_l2", "i8_l2"])
 @pytest.mark.parametrize("d", [1, 8, 33, 64, 65, 100, 200, 768])
 def test_mma_kernel_ragged_dimensions(kind, d):
     run_case(kind, 3000, d, 40, 7, seed=52 + d, kernel=3)
 
 
-@pytest.mark.parametrize("kind", ["fp16_ip", "fp16_l2", "fp32_l2"])
+@pytest.mark.parametrize("kind", ["fp16_ip", "fp16_l2", "fp32_l2", "qi8_l2"])
 @pytest.mark.parametrize("n", [1, 37, 255, 256, 257, 40000])
 def test_mma_kernel_ragged_row_counts(kind, n):
     run_case(kind, n, 48, 33, 10, seed=53 + n, kernel=3)
 
 
-@pytest.mark.parametrize("kind", ["fp16_ip", "fp32_l2"])
+@pytest.mark.parametrize("kind", ["fp16_ip", "fp32_l2", "qi8_l2"])
 @pytest.mark.parametrize("k", [1, 10, 32, 33, 80, 81, 100, 128])
 def test_mma_kernel_topk_sizes(kind, k):
-    if kind == "fp32_l2" and k == 128:
-        k = 120     # the re-score modes keep 2 KB of shared memory for column constants
+    if kind != "fp16_ip" and k == 128:
+        k = 112     # these modes keep 2-8 KB of shared memory for column constants
     run_case(kind, 6000, 32, 70, k, seed=54 + k, kernel=3)
 
 
@@ -295,7 +297,10 @@ def test_mma_kernel_filters_threshold_and_auto_selection():
     assert run_case("fp16_l2", n, 64, 256, 10, seed=59) == "scan_mma"      # L2: tensor-core filter + exact re-score
     assert run_case("fp32_l2", n, 64, 256, 10, seed=62) == "scan_mma"      # fp32: kind::tf32 filter + exact re-score
     assert run_case("fp32_l2", n, 64, 3, 10, seed=63) == "scan_gemv"       # tiny batches stay on the streaming scan
-    assert run_case("qi8_l2", n, 64, 256, 10, seed=64) == "scan_tile"      # int8 batched: exact CUDA-core tile
+    assert run_case("qi8_l2", n, 64, 256, 10, seed=64) == "scan_mma"       # int8 batched: kind::i8, exact
+    assert run_case("i8_ip", n, 64, 256, 10, seed=68) == "scan_mma"
+    run_case("qi8_l2", n, 64, 64, 10, seed=69, kernel=3, drop=drop, filt=filt)
+    run_case("qi8_ip", n, 64, 64, 20, seed=70, kernel=3, threshold=-0.5)
     run_case("fp32_l2", n, 64, 64, 10, seed=65, kernel=3, drop=drop, filt=filt)
     run_case("fp32_cos", n, 64, 64, 20, seed=66, kernel=3, threshold=0.8)
     run_case("fp16_l2", n, 64, 64, 20, seed=67, kernel=3, threshold=100.0, drop=drop)

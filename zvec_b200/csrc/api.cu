@@ -303,7 +303,8 @@ int zvb200_store_seal(zvb200_store *s) {
   CU(cudaSetDevice(s->device));
   int r = sync_drop(s);
   if (r != 0) return r;
-  if (s->dtype != ZVB200_DT_INT8 && s->n > 0) {
+  // |x|^2 per row: the tensor-core L2 / tf32 paths (fp16, fp32) and plain int8 L2
+  if ((s->dtype != ZVB200_DT_INT8 || (!s->has_tail && s->chunks * 16 <= 1040)) && s->n > 0) {
     if (!s->norms) { CU(cudaMalloc((void **)&s->norms, s->cap * sizeof(float))); s->normed = 0; }
     if (s->normed < s->n) {
       RowsView v = s->view();
@@ -457,7 +458,7 @@ static int search_core(zvb200_ctx *c, zvb200_store *s, const void *queries_dev, 
   qv.qf32 = (const float *)c->qf32.p; qv.qraw = (const uint8_t *)c->qraw.p;
   qv.qtails = (const float4 *)c->qtails.p; qv.qnorms = (const float *)c->qnorms.p;
   qv.q = q;
-  qv.qpad_rows = s->dtype != ZVB200_DT_INT8;
+  qv.qpad_rows = true;
   c->last_qv = qv;  // the IVF list scan reuses the prepared queries
   SearchParams sp;
   sp.k = k; sp.threshold = threshold; sp.filter = filter_dev;

@@ -95,7 +95,11 @@ __global__ void row_norms_kernel(RowsView rv, uint64_t row_begin, uint64_t row_e
   float s = 0.f;
   for (uint32_t c = lane; c < rv.chunks; c += 32) {
     const uint4 v = *reinterpret_cast<const uint4 *>(p + (size_t)c * 16);
-    if (rv.dtype == ZVB200_DT_FP32) {
+    if (rv.dtype == ZVB200_DT_INT8) {  // exact: the sum stays below 2^24 for d <= 1040
+      int t = __dp4a((int)v.x, (int)v.x, 0);
+      t = __dp4a((int)v.y, (int)v.y, t); t = __dp4a((int)v.z, (int)v.z, t); t = __dp4a((int)v.w, (int)v.w, t);
+      s += (float)t;
+    } else if (rv.dtype == ZVB200_DT_FP32) {
       const float x0 = __uint_as_float(v.x), x1 = __uint_as_float(v.y), x2 = __uint_as_float(v.z),
                   x3 = __uint_as_float(v.w);
       s = fmaf(x0, x0, s); s = fmaf(x1, x1, s); s = fmaf(x2, x2, s); s = fmaf(x3, x3, s);

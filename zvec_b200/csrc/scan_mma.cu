@@ -61,6 +61,12 @@ struct MmaArgs {
   const float *norms;   // |x|^2 per stored row (absolute row index)
   const float *qnorms;  // |q|^2 per query
   float eps;            // |accumulator - exact dot| <= eps * (|x|^2 + |q|^2) / 2
+  // int8 stores (kind::i8, exact int32 accumulators): mode 5 plain -IP, 6 plain L2, 7 QuantizedInteger L2,
+  // 8 QuantizedInteger -IP; the score formulas are evaluated per column exactly as K1 does
+  const float4 *tails;  // QuantizedInteger row tails {a, b, s, s2} (absolute row index)
+  const float4 *qtails; // query tails
+  const uint8_t *qraw;  // int8 query codes, row_stride apart
+  uint32_t d;           // elements of the dot product
   float threshold;
   const uint32_t *drop, *filter;
   u64 *part;            // [nq][groups][k]
@@ -136,6 +142,15 @@ __device__ __forceinline__ void umma_tf32(uint32_t d_tmem, uint64_t adesc, uint6
       "r"(idesc), "r"(accumulate)
       : "memory");
 }
+__device__ __forceinline__ void umma_i8(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc, uint32_t idesc,
+                                        uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::i8 [%0], %1, %2, %3, p;\n\t}" ::"r"(d_tmem), "l"(adesc), "l"(bdesc),
+      "r"(idesc), "r"(accumulate)
+      : "memory");
+}
 __device__ __forceinline__ void umma_commit(uint32_t bar) {
   asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
 }
@@ -182,6 +197,11 @@ __host__ __device__ constexpr uint32_t make_idesc_tf32(int M, int N) {
   return (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
 }
 
+// kind::i8: signed 8-bit operands, int32 accumulate (exact).
+__host__ __device__ constexpr uint32_t make_idesc_i8(int M, int N) {
+  return (2u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
+}
+
 // Exact score of (row, query) by the whole warp, same arithmetic as K1 (scan_gemv.cu) with 32 lanes per
 // row: fp32 FMA over 16-byte chunks, xor-shuffle tree.  Result on every lane.
 template <int DT>
@@ -207,7 +227,8 @@ __device__ __forceinline__ float exact_score(const MmaArgs &a, uint32_t row, uin
 // (48 KB per 128x256x64 block every ~520 cycles), and an epilogue LDS/STS queues behind it for hundreds
 // of cycles (measured: ~1000 cycles per accepted candidate with a shared-memory pool, tools/mma_probe.py
 // ZVB200_MMA_DEBUG=128) — so for small k the pool never touches shared memory.
-// KIND 0: fp16 rows, kind::f16 (64 halves per 128-byte k-block); KIND 1: fp32 rows, kind::tf32 (32 floats).
+// KIND 0: fp16 rows, kind::f16 (64 halves per 128-byte k-block); KIND 1: fp32 rows, kind::tf32 (32 floats);
+// KIND 2: int8 rows, kind::i8 (128 codes).
 template <int KIND, int KR>
 __global__ void __launch_bounds__(kThreads, 1)
 scan_mma_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmX, const MmaArgs a) {
@@ -229,8 +250,8 @@ scan_mma_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
   u64 *lists = reinterpret_cast<u64 *>(sbase + (size_t)nstage * kStage);      // [k][128]: entry i of query s at i*128+s
   uint64_t *bars = reinterpret_cast<uint64_t *>(lists + (size_t)kQM * k);     // full[ns] empty[ns] tfull[2] tempty[2]
   uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + 2 * nstage + 4);
-  float *colc = reinterpret_cast<float *>(tmem_slot + 4);                      // [2][kBN] per-column constants
-  constexpr int kBKe = KIND == 0 ? 64 : 32;                                    // elements per 128-byte k-block
+  float *colc = reinterpret_cast<float *>((reinterpret_cast<uintptr_t>(tmem_slot + 4) + 15) & ~(uintptr_t)15);  // [2][kBN] per-column constants (float, or float4 for int8)
+  constexpr int kBKe = KIND == 0 ? 64 : KIND == 1 ? 32 : 128;                  // elements per 128-byte k-block
   const uint32_t bar_full = smem_u32(bars), bar_empty = bar_full + 8 * nstage;
   const uint32_t bar_tfull = bar_empty + 8 * nstage, bar_tempty = bar_tfull + 16;
 
@@ -286,7 +307,8 @@ scan_mma_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
   } else if (warp == 1) {
     // ================= MMA issuer =================
     if (lane == 0) {
-      constexpr uint32_t idesc = KIND == 0 ? make_idesc_f16(kQM, kBN) : make_idesc_tf32(kQM, kBN);
+      constexpr uint32_t idesc = KIND == 0 ? make_idesc_f16(kQM, kBN) : KIND == 1 ? make_idesc_tf32(kQM, kBN)
+                                                                                  : make_idesc_i8(kQM, kBN);
       uint32_t stage = 0, phase = 0;
       for (uint32_t t = 0; t < ntl; ++t) {
         const uint32_t as = t & 1, aphase = (t >> 1) & 1;
@@ -301,7 +323,8 @@ scan_mma_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
 #pragma unroll
           for (uint32_t kk = 0; kk < 4; ++kk) {  // four 32-byte K slices per 128-byte k-block
             if (KIND == 0) umma_f16(d_tmem, da + 2 * kk, db + 2 * kk, idesc, (kb | kk) != 0);
-            else umma_tf32(d_tmem, da + 2 * kk, db + 2 * kk, idesc, (kb | kk) != 0);
+            else if (KIND == 1) umma_tf32(d_tmem, da + 2 * kk, db + 2 * kk, idesc, (kb | kk) != 0);
+            else umma_i8(d_tmem, da + 2 * kk, db + 2 * kk, idesc, (kb | kk) != 0);
           }
           umma_commit(bar_empty + 8 * stage);  // frees the stage when these MMAs retire
           if (++stage == nstage) { stage = 0; phase ^= 1; }
@@ -315,7 +338,9 @@ scan_mma_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
     const int slot = ew * 32 + lane;
     const bool qvalid = q0 + slot < a.nq;
     u64 *L = lists + slot;  // entry i at L[i * kQM]: lanes of a warp hit consecutive banks
-    const int mode = a.mode;
+    // int8: the column value is MINUS the exact score, so the rest of the epilogue runs as mode 0 (s = -value)
+    const int mode = KIND == 2 ? 0 : a.mode;
+    const int imode = a.mode;
     const int K = (int)k;
     // The pool is UNSORTED: the k smallest keys accepted so far, with the position of the largest
     // cached.  Accepting a key replaces the largest and rescans the pool for the new one — k
@@ -371,6 +396,34 @@ scan_mma_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
       if (row >= a.row_end) return __int_as_float(0xff800000);  // never a candidate
       const float hx = 0.5f * a.norms[row];
       return mode == 2 ? -(1.0f - a.eps) * hx : a.eps * hx;
+    };
+    // ---- int8: per-thread query constants and the per-column score, the formulas of K1 (scan_gemv.cu) ----
+    const bool ic4 = KIND == 2 && imode != 5;  // per-row constants: {|x|^2 as int} (plain L2) or the row tail
+    float4 *colc4 = reinterpret_cast<float4 *>(colc);
+    const float4 qt = (KIND == 2 && imode >= 7 && qvalid) ? a.qtails[q0 + slot] : make_float4(0, 0, 0, 0);
+    const float dq = (float)a.d;
+    int qq_i = 0;
+    if (KIND == 2 && imode == 6 && qvalid) {
+      const int8_t *qp = reinterpret_cast<const int8_t *>(a.qraw + (size_t)(q0 + slot) * a.row_stride);
+      for (uint32_t i = 0; i < a.d; ++i) qq_i += (int)qp[i] * (int)qp[i];
+    }
+    auto ival = [&](uint32_t raw, const float4 c4) -> float {  // = -score
+      const int ip = (int)raw;
+      if (imode == 5) return (float)ip;
+      if (imode == 6) {
+        float sc = (float)(__float_as_int(c4.x) - 2 * ip + qq_i);
+        if (a.metric == ZVB200_METRIC_L2) sc = sqrtf(sc);
+        return -sc;
+      }
+      return imode == 7 ? -qi8_l2sq((float)ip, c4, qt, dq) : -qi8_mip((float)ip, c4, qt, dq);
+    };
+    auto cval4 = [&](uint32_t row) -> float4 {
+      if (row >= a.row_end) {
+        const float nan = __int_as_float(0x7fc00000);
+        return imode == 6 ? make_float4(0, 0, 0, 0) : make_float4(nan, nan, nan, nan);  // NaN score: never a candidate
+      }
+      if (imode == 6) return make_float4(__int_as_float((int)a.norms[row]), 0, 0, 0);
+      return a.tails[row];
     };
     float dthr = dthr_of(tau_key);
     auto accept = [&](u64 key) {
@@ -464,10 +517,15 @@ scan_mma_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
     const bool boot = a.groups > 1 && pubj <= 8 && !a.drop && !a.filter && ntl > 1 &&
                       a.row_begin + (t_begin + 1) * kBN <= a.row_end && !(a.dbg & (1 | 16 | 32 | 64));
     const int etid = ew * 32 + lane;
-    if (resc) {
+    if (resc || ic4) {
       const uint32_t r0 = a.row_begin + t_begin * kBN;
-      colc[etid] = cval(r0 + etid);
-      colc[etid + 128] = cval(r0 + 128 + etid);
+      if (ic4) {
+        colc4[etid] = cval4(r0 + etid);
+        colc4[etid + 128] = cval4(r0 + 128 + etid);
+      } else {
+        colc[etid] = cval(r0 + etid);
+        colc[etid + 128] = cval(r0 + 128 + etid);
+      }
       asm volatile("bar.sync 1, 128;" ::: "memory");
     }
     const bool prof = (a.dbg & 128) != 0;  // triage: where the epilogue's cycles go (printed by CTA 0)
@@ -479,8 +537,11 @@ scan_mma_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
       const uint32_t as = t & 1, aphase = (t >> 1) & 1;
       const uint32_t row0 = a.row_begin + (t_begin + t) * kBN;
       float pc0 = 0.f, pc1 = 0.f;
+      float4 pd0 = make_float4(0, 0, 0, 0), pd1 = pd0;
       if (resc && t + 1 < ntl) { pc0 = cval(row0 + kBN + etid); pc1 = cval(row0 + kBN + 128 + etid); }
+      if (ic4 && t + 1 < ntl) { pd0 = cval4(row0 + kBN + etid); pd1 = cval4(row0 + kBN + 128 + etid); }
       const float *cc = colc + (t & 1) * kBN;
+      const float4 *cc4 = colc4 + (t & 1) * kBN;
       const long long c0w = prof ? clock64() : 0;
       mbar_wait(bar_tfull + 8 * as, aphase);
       if (prof) c_wait += clock64() - c0w;
@@ -502,6 +563,10 @@ scan_mma_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
           uint32_t v[32];
           tmem_ld32(taddr + c, v);
           tmem_ld_wait();
+          if (KIND == 2) {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) v[j] = __float_as_uint(ival(v[j], ic4 ? cc4[c + j] : make_float4(0, 0, 0, 0)));
+          }
           if (resc) {  // pessimistic side of the error bound: g = acc - (1 + eps) hx (L2), acc - eps hx (IP, cosine)
             const float cb = mode == 2 ? (1.0f + a.eps) / (1.0f - a.eps) * 1.000001f : -1.0f;
 #pragma unroll
@@ -541,6 +606,10 @@ scan_mma_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
         uint32_t v[32];
         tmem_ld32(taddr + c0, v);
         tmem_ld_wait();
+        if (KIND == 2) {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) v[j] = __float_as_uint(ival(v[j], ic4 ? cc4[c0 + j] : make_float4(0, 0, 0, 0)));
+        }
         if (resc) {
 #pragma unroll
           for (int j = 0; j < 32; j += 4) {
@@ -572,7 +641,8 @@ scan_mma_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
             // run-time j would cost a branch tree or local memory
             const uint32_t raw = tmem_ld1(taddr + c0 + j);
             const uint32_t row = row0 + c0 + j;
-            const float dv = __uint_as_float(raw) + (resc ? cc[c0 + j] : 0.f);
+            const float dv = KIND == 2 ? ival(raw, ic4 ? cc4[c0 + j] : make_float4(0, 0, 0, 0))
+                                       : __uint_as_float(raw) + (resc ? cc[c0 + j] : 0.f);
             bool cand = ((m >> j) & 1u) && dv >= dthr;  // dthr may have tightened since the mask was built
             float s = mode == 0 ? -dv : 1.0f - dv;
             if (resc) {
@@ -582,7 +652,7 @@ scan_mma_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
               while (cb) {
                 const int src = __ffs(cb) - 1;
                 cb &= cb - 1;
-                const float e = exact_score<KIND == 0 ? ZVB200_DT_FP16 : ZVB200_DT_FP32>(a, row, q0 + ew * 32 + src, lane);
+                const float e = exact_score<KIND == 1 ? ZVB200_DT_FP32 : ZVB200_DT_FP16>(a, row, q0 + ew * 32 + src, lane);
                 if (lane == src) s = e;
               }
             }
@@ -608,11 +678,17 @@ scan_mma_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(bar_tempty + 8 * as);
-      if (resc) {
+      if (resc || ic4) {
         if (t + 1 < ntl) {
-          float *cn = colc + ((t + 1) & 1) * kBN;
-          cn[etid] = pc0;
-          cn[etid + 128] = pc1;
+          if (ic4) {
+            float4 *cn = colc4 + ((t + 1) & 1) * kBN;
+            cn[etid] = pd0;
+            cn[etid + 128] = pd1;
+          } else {
+            float *cn = colc + ((t + 1) & 1) * kBN;
+            cn[etid] = pc0;
+            cn[etid + 128] = pc1;
+          }
         }
         asm volatile("bar.sync 1, 128;" ::: "memory");
       }
@@ -669,24 +745,26 @@ EncodeTiledFn encode_fn() {
 // 2-D tensor map over `rows` rows of `d` elements (fp16 or fp32), `stride` bytes apart; box = one
 // 128-byte k-block x box_rows, 128-byte swizzle; out-of-range elements read as zero (ragged d and
 // the last row tile).
-bool make_map(CUtensorMap *tm, const void *ptr, bool f32, uint32_t d, uint64_t rows, uint32_t stride, uint32_t box_rows) {
+bool make_map(CUtensorMap *tm, const void *ptr, int kind, uint32_t d, uint64_t rows, uint32_t stride, uint32_t box_rows) {
   EncodeTiledFn fn = encode_fn();
   if (!fn) return false;
   cuuint64_t dims[2] = {d, rows};
   cuuint64_t strides[1] = {stride};
-  cuuint32_t box[2] = {(cuuint32_t)(f32 ? 32 : 64), box_rows};
+  cuuint32_t box[2] = {(cuuint32_t)(kind == 0 ? 64 : kind == 1 ? 32 : 128), box_rows};
   cuuint32_t estr[2] = {1, 1};
-  return fn(tm, f32 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, const_cast<void *>(ptr), dims,
-            strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
-            CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+  const CUtensorMapDataType dt = kind == 0 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16
+                                 : kind == 1 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_UINT8;
+  return fn(tm, dt, 2, const_cast<void *>(ptr), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+            CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+            CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
 }
 
 constexpr size_t kSmemMax = 232448;  // 227 KB
 
 // pipeline stages that fit next to the 128 x k lists; false when not even 2 stages fit
-bool mma_config(uint32_t k, bool colc, uint32_t *nstage, size_t *smem) {
+bool mma_config(uint32_t k, size_t colc_bytes, uint32_t *nstage, size_t *smem) {
   for (uint32_t ns = 4; ns >= 2; --ns) {
-    const size_t need = 1024 + (size_t)ns * kStage + (size_t)kQM * k * 8 + (2 * ns + 4) * 8 + 16 + (colc ? 2 * kBN * 4 : 0);
+    const size_t need = 1024 + (size_t)ns * kStage + (size_t)kQM * k * 8 + (2 * ns + 4) * 8 + 32 + colc_bytes;
     if (need <= kSmemMax) { *nstage = ns; *smem = need; return true; }
   }
   return false;
@@ -694,16 +772,31 @@ bool mma_config(uint32_t k, bool colc, uint32_t *nstage, size_t *smem) {
 
 }  // namespace
 
+// bytes of per-column constants the epilogue stages in shared memory for this store type
+static size_t colc_bytes_for(const RowsView &rv) {
+  if (rv.dtype == ZVB200_DT_INT8) return rv.metric == ZVB200_METRIC_IP ? 0 : 2 * kBN * sizeof(float4);
+  const bool direct = rv.dtype == ZVB200_DT_FP16 && !metric_is_l2(rv.metric);
+  return direct ? 0 : 2 * kBN * sizeof(float);
+}
+
 bool scan_mma_supports(const RowsView &rv, uint32_t k) {
   uint32_t ns; size_t smem;
-  if (rv.dtype != ZVB200_DT_FP16 && rv.dtype != ZVB200_DT_FP32) return false;
-  if (rv.metric != ZVB200_METRIC_IP && rv.metric != ZVB200_METRIC_COSINE && rv.metric != ZVB200_METRIC_L2SQ &&
-      rv.metric != ZVB200_METRIC_L2)
-    return false;
-  const bool direct = rv.dtype == ZVB200_DT_FP16 && !metric_is_l2(rv.metric);
-  if (!direct && !rv.norms) return false;  // the filter + re-score modes need |x|^2 (computed at seal)
+  if (rv.dtype == ZVB200_DT_INT8) {
+    // exact while the int32 sums convert to float exactly, like the reference's own int8 kernels
+    if (rv.d > 1040) return false;
+    if (metric_is_qi8(rv.metric)) { if (!rv.tails) return false; }
+    else if (rv.metric == ZVB200_METRIC_L2SQ || rv.metric == ZVB200_METRIC_L2) { if (!rv.norms) return false; }
+    else if (rv.metric != ZVB200_METRIC_IP) return false;
+  } else {
+    if (rv.dtype != ZVB200_DT_FP16 && rv.dtype != ZVB200_DT_FP32) return false;
+    if (rv.metric != ZVB200_METRIC_IP && rv.metric != ZVB200_METRIC_COSINE && rv.metric != ZVB200_METRIC_L2SQ &&
+        rv.metric != ZVB200_METRIC_L2)
+      return false;
+    const bool direct = rv.dtype == ZVB200_DT_FP16 && !metric_is_l2(rv.metric);
+    if (!direct && !rv.norms) return false;  // the filter + re-score modes need |x|^2 (computed at seal)
+  }
   if (k > 128) return false;
-  return mma_config(k, !direct, &ns, &smem) && encode_fn() != nullptr;
+  return mma_config(k, colc_bytes_for(rv), &ns, &smem) && encode_fn() != nullptr;
 }
 
 size_t scan_mma_max_parts(int sm_count) { return (size_t)sm_count; }
@@ -712,7 +805,7 @@ cudaError_t launch_scan_mma(const RowsView &rv, const QueryView &qv, const Searc
                             uint64_t row_begin, uint64_t row_end, u64 *part, uint32_t *nparts,
                             uint32_t *pub, int sm_count, cudaStream_t st) {
   uint32_t ns; size_t smem;
-  if (!mma_config(sp.k, !(rv.dtype == ZVB200_DT_FP16 && !metric_is_l2(rv.metric)), &ns, &smem)) return cudaErrorInvalidValue;
+  if (!mma_config(sp.k, colc_bytes_for(rv), &ns, &smem)) return cudaErrorInvalidValue;
   const uint64_t nrows = row_end > row_begin ? row_end - row_begin : 0;
   MmaArgs a;
   a.nq = qv.q;
@@ -720,14 +813,17 @@ cudaError_t launch_scan_mma(const RowsView &rv, const QueryView &qv, const Searc
   if ((int)a.qtiles > sm_count) return cudaErrorInvalidValue;  // caller splits the batch
   a.ntiles = (uint32_t)((nrows + kBN - 1) / kBN);
   a.groups = std::max<uint32_t>(1, std::min<uint32_t>((uint32_t)sm_count / a.qtiles, std::max<uint32_t>(a.ntiles, 1)));
-  const bool f32 = rv.dtype == ZVB200_DT_FP32;
-  const uint32_t bke = f32 ? 32 : 64;
+  const bool f32 = rv.dtype == ZVB200_DT_FP32, i8 = rv.dtype == ZVB200_DT_INT8;
+  const int kind = f32 ? 1 : i8 ? 2 : 0;
+  const uint32_t bke = f32 ? 32 : i8 ? 128 : 64;
   a.nkb = (rv.d + bke - 1) / bke;
   a.k = sp.k; a.nstage = ns;
   a.row_begin = (uint32_t)row_begin; a.row_end = (uint32_t)row_end;
   const bool l2 = metric_is_l2(rv.metric);
-  if (!f32 && !l2) a.mode = rv.metric == ZVB200_METRIC_IP ? 0 : 1;
+  if (i8) a.mode = metric_is_qi8(rv.metric) ? (rv.metric == ZVB200_METRIC_QI8_L2SQ ? 7 : 8) : (l2 ? 6 : 5);
+  else if (!f32 && !l2) a.mode = rv.metric == ZVB200_METRIC_IP ? 0 : 1;
   else a.mode = l2 ? 2 : rv.metric == ZVB200_METRIC_IP ? 3 : 4;
+  a.tails = rv.tails; a.qtails = qv.qtails; a.qraw = qv.qraw; a.d = rv.d;
   a.metric = rv.metric;
   a.rows = rv.rows; a.row_stride = rv.row_stride; a.chunks = rv.chunks;
   a.qf32 = qv.qf32; a.qstride = rv.chunks * (f32 ? 4 : 8);
@@ -755,14 +851,15 @@ cudaError_t launch_scan_mma(const RowsView &rv, const QueryView &qv, const Searc
   // the caller pads qraw with zero rows up to a whole tile when this is the last group of the batch
   const uint64_t qrows = qv.qpad_rows ? (uint64_t)a.qtiles * kQM : qv.q;
   if (f32) {
-    if (!make_map(&tmQ, qv.qf32, true, rv.d, qrows, a.qstride * 4, kQM)) return cudaErrorInvalidValue;
+    if (!make_map(&tmQ, qv.qf32, 1, rv.d, qrows, a.qstride * 4, kQM)) return cudaErrorInvalidValue;
   } else {
-    if (!make_map(&tmQ, qv.qraw, false, rv.d, qrows, rv.row_stride, kQM)) return cudaErrorInvalidValue;
+    if (!make_map(&tmQ, qv.qraw, kind, rv.d, qrows, rv.row_stride, kQM)) return cudaErrorInvalidValue;
   }
-  if (!make_map(&tmX, rv.rows + row_begin * rv.row_stride, f32, rv.d, std::max<uint64_t>(nrows, 1), rv.row_stride, kBN))
+  if (!make_map(&tmX, rv.rows + row_begin * rv.row_stride, kind, rv.d, std::max<uint64_t>(nrows, 1), rv.row_stride, kBN))
     return cudaErrorInvalidValue;
-  auto kern = f32 ? (sp.k <= 8 ? scan_mma_kernel<1, 8> : sp.k <= 16 ? scan_mma_kernel<1, 16> : scan_mma_kernel<1, 0>)
-                  : (sp.k <= 8 ? scan_mma_kernel<0, 8> : sp.k <= 16 ? scan_mma_kernel<0, 16> : scan_mma_kernel<0, 0>);
+  auto kern = f32  ? (sp.k <= 8 ? scan_mma_kernel<1, 8> : sp.k <= 16 ? scan_mma_kernel<1, 16> : scan_mma_kernel<1, 0>)
+              : i8 ? (sp.k <= 8 ? scan_mma_kernel<2, 8> : sp.k <= 16 ? scan_mma_kernel<2, 16> : scan_mma_kernel<2, 0>)
+                   : (sp.k <= 8 ? scan_mma_kernel<0, 8> : sp.k <= 16 ? scan_mma_kernel<0, 16> : scan_mma_kernel<0, 0>);
   cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return e;
   if (nrows == 0) {
