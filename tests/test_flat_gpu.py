@@ -306,7 +306,7 @@ def test_mma_kernel_filters_threshold_and_auto_selection():
     run_case("fp16_l2", n, 64, 64, 20, seed=67, kernel=3, threshold=100.0, drop=drop)
 
 
-@pytest.mark.parametrize("kind", ["fp16_l2", "fp32_l2", "fp32_ip"])
+@pytest.mark.parametrize("kind", ["fp16_l2", "fp32_l2", "fp32_ip", "qi8_l2"])
 @pytest.mark.parametrize("shape", ["offset", "norm_spread", "near_duplicates"])
 def test_mma_rescore_filter_is_sound_on_hostile_data(kind, shape):
     """The tensor-core accumulator only nominates rows; these inputs maximise its error against the exact
@@ -332,7 +332,8 @@ def test_mma_rescore_filter_is_sound_on_hostile_data(kind, shape):
     ek, es, ei, ec = ctx.search(queries, k)      # the streaming scan: exact arithmetic, oracle-checked elsewhere
     for i in range(q):
         alld = S.oracle_distances(metric, dt, stored, sdim, queries[i])
-        S.check_topk_parity(gi[i], gs[i], ei[i], es[i], all_dist=alld, exact=False, what="%s %s q%d" % (kind, shape, i))
+        S.check_topk_parity(gi[i], gs[i], ei[i], es[i], all_dist=alld, exact=kind == "qi8_l2",
+                            what="%s %s q%d" % (kind, shape, i))
     ctx.close(); st.close()
 
 

@@ -373,11 +373,69 @@ scan_mma_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
     //     the accumulator is within eps (hx + hq) of x.q, so colc = -(1 - eps) hx and dthr = hq - T/2 - eps hq.
     //   mode 3/4 (IP / cosine through tf32): colc = +eps hx, dthr = (-T | 1 - T) - eps hq.
     // Modes 2-4 never use f as a score: a candidate is re-scored exactly (exact_score) before it is offered.
+    // ---- int8: per-thread query constants and the per-column score, the formulas of K1 (scan_gemv.cu) ----
+    const bool ic4 = KIND == 2;  // per-row constants, always staged (unconditional loads in the hot loop): {|x|^2 as int} (plain L2), the row tail or its filter form (QuantizedInteger), zeros (plain -IP)
+    float4 *colc4 = reinterpret_cast<float4 *>(colc);
+    const float4 qt = (KIND == 2 && imode >= 7 && qvalid) ? a.qtails[q0 + slot] : make_float4(0, 0, 0, 0);
+    const float dq = (float)a.d;
+    int qq_i = 0;
+    if (KIND == 2 && imode == 6 && qvalid) {
+      const int8_t *qp = reinterpret_cast<const int8_t *>(a.qraw + (size_t)(q0 + slot) * a.row_stride);
+      for (uint32_t i = 0; i < a.d; ++i) qq_i += (int)qp[i] * (int)qp[i];
+    }
+    // QuantizedInteger L2 filter constants of this query; kEpsQ bounds the difference between the filter's
+    // value and the reference-order score: both are <= 12 roundings of sums whose absolute terms total
+    // <= 8 [(ma^2 ms2 + mb^2 d) + (qa^2 qs2 + qb^2 d)] (Cauchy-Schwarz on ip, ms, qs), so
+    // 2 * 12 * 2^-24 * 8 = 1.2e-5 < kEpsQ
+    constexpr float kEpsQ = 3.1e-5f;
+    const bool small_ip = a.d <= 260;
+    const float qsum = qt.x * qt.z, qsum2 = qt.x * qt.x * qt.w;  // qa*qs, qa*qa*qs2
+    const float nQ1 = 2.0f * (qt.y * dq + qsum), nQ2 = 2.0f * qt.y, nQa = 2.0f * qt.x;
+    const float Q0 = qsum2 + qt.y * qt.y * dq + 2.0f * qt.y * qsum;
+    const float Mthr = kEpsQ * (qsum2 + qt.y * qt.y * dq);
+    auto ival = [&](uint32_t raw, const float4 c4) -> float {  // = -score
+      const int ip = (int)raw;
+      if (imode == 5) return (float)ip;
+      if (imode == 6) {
+        float sc = (float)(__float_as_int(c4.x) - 2 * ip + qq_i);
+        if (a.metric == ZVB200_METRIC_L2) sc = sqrtf(sc);
+        return -sc;
+      }
+      if (imode == 7) {
+        // FILTER value for QuantizedInteger L2: minus the score in its expanded, linear-in-ip form
+        //   s = [ma^2 ms2 + mb^2 d + 2 mb ms ma] + [qa^2 qs2 + qb^2 d + 2 qb qa qs] - 2 mb (qb d + qa qs)
+        //       - 2 (ms ma) qb - 2 ma qa ip
+        // with the row bracket (and the row's share of the rounding margin) staged as c4.x = -(c0 - Mrow),
+        // c4 = {.., mb, ms*ma, ma}; 1 mul + 3 fma per column instead of the 13 operations of the exact form.
+        // Candidates are re-scored with the exact formula (qi8_l2sq) before they are offered.
+        // int -> float without I2F (a quarter-rate instruction, the hot loop's bottleneck): exact for
+        // |ip| < 2^22, i.e. d <= 260 at +-127 codes
+        const float ipf = small_ip ? __int_as_float(ip + 0x4B400000) - 12582912.0f : (float)ip;
+        return fmaf(__fmul_rn(c4.w, ipf), nQa, fmaf(c4.z, nQ2, fmaf(c4.y, nQ1, c4.x)));
+      }
+      return -qi8_mip((float)ip, c4, qt, dq);
+    };
+    auto cval4 = [&](uint32_t row) -> float4 {
+      if (row >= a.row_end) {
+        const float nan = __int_as_float(0x7fc00000);
+        return imode <= 6 ? make_float4(0, 0, 0, 0) : make_float4(nan, nan, nan, nan);  // NaN score: never a candidate
+      }
+      if (imode == 5) return make_float4(0, 0, 0, 0);
+      if (imode == 6) return make_float4(__int_as_float((int)a.norms[row]), 0, 0, 0);
+      const float4 m = a.tails[row];
+      if (imode == 7) {
+        const float t1 = m.x * m.x * m.w, mbd = m.y * m.y * dq, msma = m.z * m.x;
+        const float c0 = t1 + mbd + 2.0f * m.y * msma;
+        return make_float4(-(c0 - kEpsQ * (t1 + mbd)), m.y, msma, m.x);
+      }
+      return m;
+    };
     const bool resc = mode >= 2;
     const float hq = (resc && qvalid) ? 0.5f * a.qnorms[q0 + slot] : 0.f;
     auto dthr_of = [&](u64 tk) -> float {
       if (!qvalid) return __int_as_float(0x7f800000);
       const float tau_f = unorder_f32((uint32_t)(tk >> 32));
+      if (KIND == 2 && imode == 7) return Q0 - tau_f - Mthr - (fabsf(Q0) + fabsf(tau_f)) * 4.8e-7f;
       if (mode == 0) return -tau_f;
       if (mode == 1) {
         const float t = 1.0f - tau_f;
@@ -396,34 +454,6 @@ scan_mma_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
       if (row >= a.row_end) return __int_as_float(0xff800000);  // never a candidate
       const float hx = 0.5f * a.norms[row];
       return mode == 2 ? -(1.0f - a.eps) * hx : a.eps * hx;
-    };
-    // ---- int8: per-thread query constants and the per-column score, the formulas of K1 (scan_gemv.cu) ----
-    const bool ic4 = KIND == 2 && imode != 5;  // per-row constants: {|x|^2 as int} (plain L2) or the row tail
-    float4 *colc4 = reinterpret_cast<float4 *>(colc);
-    const float4 qt = (KIND == 2 && imode >= 7 && qvalid) ? a.qtails[q0 + slot] : make_float4(0, 0, 0, 0);
-    const float dq = (float)a.d;
-    int qq_i = 0;
-    if (KIND == 2 && imode == 6 && qvalid) {
-      const int8_t *qp = reinterpret_cast<const int8_t *>(a.qraw + (size_t)(q0 + slot) * a.row_stride);
-      for (uint32_t i = 0; i < a.d; ++i) qq_i += (int)qp[i] * (int)qp[i];
-    }
-    auto ival = [&](uint32_t raw, const float4 c4) -> float {  // = -score
-      const int ip = (int)raw;
-      if (imode == 5) return (float)ip;
-      if (imode == 6) {
-        float sc = (float)(__float_as_int(c4.x) - 2 * ip + qq_i);
-        if (a.metric == ZVB200_METRIC_L2) sc = sqrtf(sc);
-        return -sc;
-      }
-      return imode == 7 ? -qi8_l2sq((float)ip, c4, qt, dq) : -qi8_mip((float)ip, c4, qt, dq);
-    };
-    auto cval4 = [&](uint32_t row) -> float4 {
-      if (row >= a.row_end) {
-        const float nan = __int_as_float(0x7fc00000);
-        return imode == 6 ? make_float4(0, 0, 0, 0) : make_float4(nan, nan, nan, nan);  // NaN score: never a candidate
-      }
-      if (imode == 6) return make_float4(__int_as_float((int)a.norms[row]), 0, 0, 0);
-      return a.tails[row];
     };
     float dthr = dthr_of(tau_key);
     auto accept = [&](u64 key) {
@@ -514,7 +544,7 @@ scan_mma_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
     };
     uint32_t next_eval = 1;
     // the first-tile bootstrap needs every row of that tile to be a live row
-    const bool boot = a.groups > 1 && pubj <= 8 && !a.drop && !a.filter && ntl > 1 &&
+    const bool boot = !(KIND == 2 && imode == 7) && a.groups > 1 && pubj <= 8 && !a.drop && !a.filter && ntl > 1 &&
                       a.row_begin + (t_begin + 1) * kBN <= a.row_end && !(a.dbg & (1 | 16 | 32 | 64));
     const int etid = ew * 32 + lane;
     if (resc || ic4) {
@@ -565,7 +595,7 @@ scan_mma_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
           tmem_ld_wait();
           if (KIND == 2) {
 #pragma unroll
-            for (int j = 0; j < 32; ++j) v[j] = __float_as_uint(ival(v[j], ic4 ? cc4[c + j] : make_float4(0, 0, 0, 0)));
+            for (int j = 0; j < 32; ++j) v[j] = __float_as_uint(ival(v[j], cc4[c + j]));
           }
           if (resc) {  // pessimistic side of the error bound: g = acc - (1 + eps) hx (L2), acc - eps hx (IP, cosine)
             const float cb = mode == 2 ? (1.0f + a.eps) / (1.0f - a.eps) * 1.000001f : -1.0f;
@@ -608,7 +638,7 @@ scan_mma_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
         tmem_ld_wait();
         if (KIND == 2) {
 #pragma unroll
-          for (int j = 0; j < 32; ++j) v[j] = __float_as_uint(ival(v[j], ic4 ? cc4[c0 + j] : make_float4(0, 0, 0, 0)));
+          for (int j = 0; j < 32; ++j) v[j] = __float_as_uint(ival(v[j], cc4[c0 + j]));
         }
         if (resc) {
 #pragma unroll
@@ -641,10 +671,13 @@ scan_mma_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
             // run-time j would cost a branch tree or local memory
             const uint32_t raw = tmem_ld1(taddr + c0 + j);
             const uint32_t row = row0 + c0 + j;
-            const float dv = KIND == 2 ? ival(raw, ic4 ? cc4[c0 + j] : make_float4(0, 0, 0, 0))
+            const float dv = KIND == 2 ? ival(raw, cc4[c0 + j])
                                        : __uint_as_float(raw) + (resc ? cc[c0 + j] : 0.f);
             bool cand = ((m >> j) & 1u) && dv >= dthr;  // dthr may have tightened since the mask was built
             float s = mode == 0 ? -dv : 1.0f - dv;
+            if (KIND == 2 && imode == 7) {  // the filter nominated it: the exact reference-order score
+              if (cand) s = qi8_l2sq((float)(int)raw, a.tails[row], qt, dq);
+            }
             if (resc) {
               // the accumulator only nominated the row: its score is recomputed exactly, by the whole warp,
               // one nominating lane (query) at a time
@@ -774,7 +807,7 @@ bool mma_config(uint32_t k, size_t colc_bytes, uint32_t *nstage, size_t *smem) {
 
 // bytes of per-column constants the epilogue stages in shared memory for this store type
 static size_t colc_bytes_for(const RowsView &rv) {
-  if (rv.dtype == ZVB200_DT_INT8) return rv.metric == ZVB200_METRIC_IP ? 0 : 2 * kBN * sizeof(float4);
+  if (rv.dtype == ZVB200_DT_INT8) return 2 * kBN * sizeof(float4);
   const bool direct = rv.dtype == ZVB200_DT_FP16 && !metric_is_l2(rv.metric);
   return direct ? 0 : 2 * kBN * sizeof(float);
 }
