@@ -181,6 +181,10 @@ int zvb200_fuse_weighted(zvb200_ctx *c, const uint64_t *keys, const float *score
  * belong to list l.  centroids: nlist elements of the store's dtype/metric layout, HOST. */
 int zvb200_ivf_attach(zvb200_store *s, const void *centroids, uint32_t nlist,
                       const uint64_t *list_offsets);
+/* Sharded IVF (each GPU holds a slice of EVERY posting list): list_sizes[l] = rows of list l in the
+ * whole index.  The scan budget of zvb200_ivf_search then counts these, so every shard visits exactly the lists
+ * the unsharded index would (IVFSearcher::search_impl's loop header, ivf_searcher.cc:216-219).  NULL = unsharded. */
+int zvb200_ivf_set_budget_sizes(zvb200_store *s, const uint64_t *list_sizes);
 /* nprobe = max(1, round(nlist*scan_ratio)); max_scan_count = max(bf_threshold,
  * ceil(N*scan_ratio)): lists are visited in coarse order while the rows scanned so far
  * are < max_scan_count. */

@@ -111,3 +111,68 @@ def test_merge_shards_kernel_equals_host_merge(g, q, k):
     es, er = sharding.merge_topk_host(s, ix, bases, k)
     assert np.array_equal(os_.cpu().numpy(), es, equal_nan=True)
     assert np.array_equal(or_.cpu().numpy().view(np.uint64), er)
+
+
+# ---- sharded IVF: every shard holds a slice of every posting list ----------------------------------------
+def test_ivf_shard_plan_partitions_every_list():
+    rng = np.random.default_rng(3)
+    sizes = rng.integers(0, 40, 50)
+    off = np.zeros(51, np.uint64); off[1:] = np.cumsum(sizes)
+    for world in (1, 2, 3, 8):
+        seen = []
+        for r in range(world):
+            lo, hi, local = sharding.ivf_shard_plan(off, r, world)
+            assert (lo <= hi).all() and local[-1] == (hi - lo).sum()
+            rows = sharding.ivf_shard_rows(lo, hi)
+            assert len(rows) == local[-1]
+            # local -> global is the inverse of the local order
+            back = sharding.ivf_local_to_global(np.arange(len(rows), dtype=np.uint32), lo, local)
+            assert np.array_equal(back.astype(np.int64), rows)
+            seen.append(rows)
+        allrows = np.sort(np.concatenate(seen))
+        assert np.array_equal(allrows, np.arange(int(off[-1])))            # every row exactly once
+    keep = sharding.ivf_local_to_global(np.array([0xFFFFFFFF], np.uint32), *sharding.ivf_shard_plan(off, 0, 2)[::2])
+    assert keep[0] == np.uint64(0xFFFFFFFFFFFFFFFF)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("world", [2, 3])
+def test_sharded_ivf_search_equals_unsharded(world):
+    """G stores on one device, each holding its slice of every list + the whole index's list sizes as budget:
+    merged by (score, global row) the result IS the unsharded zvb200_ivf_search result (same lists visited)."""
+    import zvec_b200 as z
+    rng = np.random.default_rng(11)
+    n, d, nlist, k, q = 30000, 32, 80, 10, 24
+    centres = rng.standard_normal((nlist, d)).astype(np.float32)
+    assign = np.sort(rng.integers(0, nlist, n))
+    x = (centres[assign] + 0.3 * rng.standard_normal((n, d))).astype(np.float32)
+    off = np.zeros(nlist + 1, np.uint64); off[1:] = np.cumsum(np.bincount(assign, minlength=nlist))
+    qs = (centres[rng.integers(0, nlist, q)] + 0.3 * rng.standard_normal((q, d))).astype(np.float32)
+    nprobe, max_scan = 8, 2500
+
+    def build(rows, offsets):
+        st = z.Store(z.DT_FP32, z.METRIC_L2SQ, d)
+        st.append(np.ascontiguousarray(rows).view(np.uint8).reshape(len(rows), -1)); st.seal()
+        st.ivf_attach(centres.view(np.uint8).reshape(nlist, -1), np.asarray(offsets, np.uint64))
+        return st
+
+    whole = build(x, off); cw = z.Context(whole)
+    _, es, ei, ec = cw.ivf_search(qs, k, nprobe, max_scan)
+    sizes = (off[1:] - off[:-1]).astype(np.uint64)
+    all_s, all_r, keep = [], [], []
+    for r in range(world):
+        lo, hi, local = sharding.ivf_shard_plan(off, r, world)
+        st = build(x[sharding.ivf_shard_rows(lo, hi)], local)
+        st.ivf_set_budget_sizes(sizes)
+        c = z.Context(st); keep.append((st, c))
+        _, s, i, _ = c.ivf_search(qs, k, nprobe, max_scan)
+        all_s.append(s); all_r.append(sharding.ivf_local_to_global(i, lo, local))
+    ms, mr = sharding.merge_topk_global(np.stack(all_s), np.stack(all_r), k)
+    for j in range(q):
+        nv = int(ec[j])
+        assert np.array_equal(ms[j][:nv].view(np.uint32), es[j][:nv].view(np.uint32))
+        assert np.array_equal(mr[j][:nv], ei[j][:nv].astype(np.uint64))
+        assert np.isnan(ms[j][nv:]).all()
+    for st, c in keep:
+        c.close(); st.close()
+    cw.close(); whole.close()

@@ -63,6 +63,7 @@ _SIGS = {
                                        C.c_uint32, C.c_uint32, C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p,
                                        C.c_void_p]),
     "zvb200_ivf_attach": (C.c_int, [C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p]),
+    "zvb200_ivf_set_budget_sizes": (C.c_int, [C.c_void_p, C.c_void_p]),
     "zvb200_ivf_search": (C.c_int, [C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint64, C.c_float,
                                     C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
 }
@@ -153,6 +154,10 @@ class Store:
         out = np.zeros(self.elem_bytes, np.uint8)
         _check(lib().zvb200_store_get_vector(self.h, row, _ptr(out), out.nbytes))
         return out
+
+    def ivf_set_budget_sizes(self, list_sizes):
+        ls = None if list_sizes is None else np.ascontiguousarray(list_sizes, np.uint64)
+        _check(lib().zvb200_ivf_set_budget_sizes(self.h, _ptr(ls)))
 
     def write(self, row, vec, key):
         """overwrite one row in place (FlatStreamerEntity::add_vector_with_id, id < count)"""

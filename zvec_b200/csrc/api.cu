@@ -54,6 +54,7 @@ struct zvb200_store {
   zvb200_store *centroids = nullptr;
   std::vector<uint64_t> list_offsets;
   uint32_t *list_off_dev = nullptr;  // [nlist+1] first row of each posting list
+  uint32_t *budget_dev = nullptr;    // [nlist] list sizes in the whole index (sharded IVF), or null
   uint32_t nlist = 0;
   std::mutex mu;
 
@@ -201,6 +202,7 @@ int zvb200_store_destroy(zvb200_store *s) {
   if (s->norms) cudaFree(s->norms);
   if (s->drop) cudaFree(s->drop);
   if (s->list_off_dev) cudaFree(s->list_off_dev);
+  if (s->budget_dev) cudaFree(s->budget_dev);
   if (s->staging) cudaFree(s->staging);
   if (s->stream) cudaStreamDestroy(s->stream);
   delete s;
@@ -715,8 +717,22 @@ int zvb200_ivf_attach(zvb200_store *s, const void *centroids, uint32_t nlist, co
   CU(cudaMemcpy(d, off32.data(), (size_t)(nlist + 1) * 4, cudaMemcpyHostToDevice));
   if (s->centroids) zvb200_store_destroy(s->centroids);
   if (s->list_off_dev) cudaFree(s->list_off_dev);
+  if (s->budget_dev) { cudaFree(s->budget_dev); s->budget_dev = nullptr; }
   s->centroids = cs; s->list_off_dev = d; s->nlist = nlist;
   s->list_offsets.assign(list_offsets, list_offsets + nlist + 1);
+  return 0;
+}
+
+int zvb200_ivf_set_budget_sizes(zvb200_store *s, const uint64_t *list_sizes) {
+  if (!s || !s->centroids) return set_err(ZVB200_ERR_NOREADY, "no IVF structure attached");
+  std::lock_guard<std::mutex> g(s->mu);
+  CU(cudaSetDevice(s->device));
+  if (s->budget_dev) { cudaFree(s->budget_dev); s->budget_dev = nullptr; }
+  if (!list_sizes) return 0;
+  std::vector<uint32_t> b(s->nlist);
+  for (uint32_t l = 0; l < s->nlist; ++l) b[l] = (uint32_t)list_sizes[l];
+  CU(cudaMalloc((void **)&s->budget_dev, (size_t)s->nlist * 4));
+  CU(cudaMemcpy(s->budget_dev, b.data(), (size_t)s->nlist * 4, cudaMemcpyHostToDevice));
   return 0;
 }
 
@@ -754,7 +770,7 @@ int zvb200_ivf_search(zvb200_ctx *c, const void *queries, uint32_t q, uint32_t k
   c->force_kernel = keep;
   if (r != 0) return r;
   // 2. which lists each query scans under the budget (ivf_searcher.cc:216-231)
-  CU(launch_ivf_plan((const uint32_t *)c->coarse_index.p, q, nprobe, s->list_off_dev, max_scan_count,
+  CU(launch_ivf_plan((const uint32_t *)c->coarse_index.p, q, nprobe, s->list_off_dev, s->budget_dev, max_scan_count,
                      (uint32_t *)c->seg_prefix.p, (uint32_t *)c->seg_row.p, (uint32_t *)c->seg_count.p, c->stream));
   // 3. posting-list scan, queries already in compute layout (same dtype / metric / dim as the centroids)
   RowsView rv = s->view();

@@ -346,33 +346,36 @@ cudaError_t launch_distance_matrix(const RowsView &rv, const QueryView &qv, floa
 // is always scanned whole).  One thread per query; nprobe <= 1024.
 namespace {
 __global__ void ivf_plan_kernel(const uint32_t *coarse_index, uint32_t q, uint32_t nprobe, const uint32_t *list_off,
-                                uint64_t max_scan_count, uint32_t *seg_prefix, uint32_t *seg_row,
-                                uint32_t *seg_count) {
+                                const uint32_t *budget_sizes, uint64_t max_scan_count, uint32_t *seg_prefix,
+                                uint32_t *seg_row, uint32_t *seg_count) {
   const uint32_t qi = blockIdx.x * blockDim.x + threadIdx.x;
   if (qi >= q) return;
   const uint32_t *ci = coarse_index + (size_t)qi * nprobe;
   uint32_t *pre = seg_prefix + (size_t)qi * (nprobe + 1), *row = seg_row + (size_t)qi * nprobe;
+  // `total` is what the budget counts: the list's size in the WHOLE index (budget_sizes, when this store holds
+  // one shard of every list) — every shard then visits exactly the lists the unsharded index would
   uint64_t total = 0;
-  uint32_t n = 0;
+  uint32_t n = 0, local = 0;
   pre[0] = 0;
   for (uint32_t i = 0; i < nprobe && total < max_scan_count; ++i) {
     const uint32_t cid = ci[i];
     if (cid == ZVB200_INVALID_INDEX) break;
     const uint32_t b = list_off[cid], e = list_off[cid + 1];
-    total += e - b;
+    total += budget_sizes ? budget_sizes[cid] : e - b;
     if (e == b) continue;
     row[n] = b;
-    pre[++n] = (uint32_t)total;
+    local += e - b;
+    pre[++n] = local;
   }
   seg_count[qi] = n;
 }
 }  // namespace
 
 cudaError_t launch_ivf_plan(const uint32_t *coarse_index, uint32_t q, uint32_t nprobe, const uint32_t *list_off,
-                            uint64_t max_scan_count, uint32_t *seg_prefix, uint32_t *seg_row, uint32_t *seg_count,
-                            cudaStream_t st) {
-  ivf_plan_kernel<<<(q + 127) / 128, 128, 0, st>>>(coarse_index, q, nprobe, list_off, max_scan_count, seg_prefix,
-                                                  seg_row, seg_count);
+                            const uint32_t *budget_sizes, uint64_t max_scan_count, uint32_t *seg_prefix,
+                            uint32_t *seg_row, uint32_t *seg_count, cudaStream_t st) {
+  ivf_plan_kernel<<<(q + 127) / 128, 128, 0, st>>>(coarse_index, q, nprobe, list_off, budget_sizes, max_scan_count,
+                                                  seg_prefix, seg_row, seg_count);
   count_launch();
   return cudaGetLastError();
 }

@@ -94,8 +94,8 @@ cudaError_t launch_distance_matrix(const RowsView &rv, const QueryView &qv, floa
 
 // K4: IVF — list selection under the scan budget, then the posting-list scan (grid.y = query)
 cudaError_t launch_ivf_plan(const uint32_t *coarse_index, uint32_t q, uint32_t nprobe, const uint32_t *list_off,
-                            uint64_t max_scan_count, uint32_t *seg_prefix, uint32_t *seg_row, uint32_t *seg_count,
-                            cudaStream_t st);
+                            const uint32_t *budget_sizes, uint64_t max_scan_count, uint32_t *seg_prefix,
+                            uint32_t *seg_row, uint32_t *seg_count, cudaStream_t st);
 cudaError_t launch_scan_lists(const RowsView &rv, const QueryView &qv, const SearchParams &sp,
                               const uint32_t *seg_prefix, const uint32_t *seg_row, const uint32_t *seg_count,
                               uint32_t seg_cap, u64 *part, uint32_t *nparts, int sm_count, cudaStream_t st);

@@ -60,3 +60,52 @@ def merge_topk_host(all_scores, all_index, bases, k):
         out_s[i, :order.size] = scv[order]
         out_r[i, :order.size] = rows[order]
     return out_s, out_r
+
+
+# ---- IVF: every rank holds a slice of EVERY posting list ---------------------------------------
+def ivf_shard_plan(list_offsets, rank, world):
+    """list_offsets u64[nlist+1] of the whole index (rows grouped by list) ->
+    (lo, hi, local_offsets): rank `rank` holds rows [lo[l], hi[l]) of list l (global row numbers), stored
+    list after list at local_offsets[l] .. local_offsets[l+1]."""
+    off = np.asarray(list_offsets, np.uint64).astype(np.int64)
+    sizes = off[1:] - off[:-1]
+    lo = off[:-1] + sizes * rank // world
+    hi = off[:-1] + sizes * (rank + 1) // world
+    local = np.zeros(len(off), np.int64)
+    local[1:] = np.cumsum(hi - lo)
+    return lo, hi, local
+
+
+def ivf_shard_rows(lo, hi):
+    """global row numbers of the rank's rows, in local order"""
+    if len(lo) == 0:
+        return np.zeros(0, np.int64)
+    return np.concatenate([np.arange(a, b, dtype=np.int64) for a, b in zip(lo, hi)]) if (hi > lo).any() \
+        else np.zeros(0, np.int64)
+
+
+def ivf_local_to_global(local_index, lo, local_offsets):
+    """local row indices (any shape, INVALID_INDEX kept) -> global row numbers u64"""
+    li = np.asarray(local_index).astype(np.int64) & 0xFFFFFFFF
+    valid = li != INVALID_INDEX
+    lst = np.searchsorted(local_offsets, np.where(valid, li, 0), side="right") - 1
+    lst = np.clip(lst, 0, len(lo) - 1)
+    g = lo[lst] + (np.where(valid, li, 0) - local_offsets[lst])
+    return np.where(valid, g.astype(np.uint64), np.uint64(0xFFFFFFFFFFFFFFFF))
+
+
+def merge_topk_global(all_scores, all_rows, k):
+    """[g,q,k] per-rank lists with GLOBAL row numbers (u64, 2^64-1 = unused) -> [q,k] by (score, global row)"""
+    s = np.asarray(all_scores, np.float32)
+    r = np.asarray(all_rows, np.uint64)
+    g, q, _ = s.shape
+    out_s = np.full((q, k), np.nan, np.float32)
+    out_r = np.full((q, k), np.uint64(0xFFFFFFFFFFFFFFFF), np.uint64)
+    for i in range(q):
+        sc, rw = s[:, i, :].ravel(), r[:, i, :].ravel()
+        valid = (rw != np.uint64(0xFFFFFFFFFFFFFFFF)) & ~np.isnan(sc)
+        scv, rwv = sc[valid] + np.float32(0.0), rw[valid]
+        order = np.lexsort((rwv, scv))[:k]
+        out_s[i, :order.size] = scv[order]
+        out_r[i, :order.size] = rwv[order]
+    return out_s, out_r
