@@ -167,6 +167,29 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&v)[32]) {
       : "memory");
 }
 __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+// the same wait, carrying the 32 destination registers of an earlier tmem_ld32 through it: nothing that
+// reads them can be scheduled ahead of the wait (needed when another chunk is processed in between)
+__device__ __forceinline__ void tmem_ld_wait_on(uint32_t (&v)[32]) {
+  asm volatile("tcgen05.wait::ld.sync.aligned;"
+               : "+r"(v[0]), "+r"(v[1]), "+r"(v[2]), "+r"(v[3]), "+r"(v[4]), "+r"(v[5]), "+r"(v[6]), "+r"(v[7]),
+                 "+r"(v[8]), "+r"(v[9]), "+r"(v[10]), "+r"(v[11]), "+r"(v[12]), "+r"(v[13]), "+r"(v[14]), "+r"(v[15]),
+                 "+r"(v[16]), "+r"(v[17]), "+r"(v[18]), "+r"(v[19]), "+r"(v[20]), "+r"(v[21]), "+r"(v[22]), "+r"(v[23]),
+                 "+r"(v[24]), "+r"(v[25]), "+r"(v[26]), "+r"(v[27]), "+r"(v[28]), "+r"(v[29]), "+r"(v[30]), "+r"(v[31])
+               :
+               : "memory");
+}
+// max of 32 score words as floats, as a depth-5 tree (a running max is a 31-deep dependent chain)
+__device__ __forceinline__ float max32(const uint32_t (&v)[32]) {
+  float m[16];
+#pragma unroll
+  for (int i = 0; i < 16; ++i) m[i] = fmaxf(__uint_as_float(v[2 * i]), __uint_as_float(v[2 * i + 1]));
+#pragma unroll
+  for (int s = 8; s > 0; s >>= 1) {
+#pragma unroll
+    for (int i = 0; i < s; ++i) m[i] = fmaxf(m[i], m[i + s]);
+  }
+  return m[0];
+}
 __device__ __forceinline__ uint32_t tmem_ld1(uint32_t taddr) {  // one column of this warp's 32 lanes, waited for
   uint32_t r;
   asm volatile(
@@ -229,7 +252,10 @@ __device__ __forceinline__ float exact_score(const MmaArgs &a, uint32_t row, uin
 // ZVB200_MMA_DEBUG=128) — so for small k the pool never touches shared memory.
 // KIND 0: fp16 rows, kind::f16 (64 halves per 128-byte k-block); KIND 1: fp32 rows, kind::tf32 (32 floats);
 // KIND 2: int8 rows, kind::i8 (128 codes).
-template <int KIND, int KR>
+// IM: the int8 score form (5 plain -IP, 6 plain L2, 7 QuantizedInteger L2, 8 QuantizedInteger -IP) as a
+// compile-time constant — as a run-time value the per-column code kept a branch tree and one waited-for load
+// per column (27k-44k cycles per tile); 0 for the other kinds, whose mode stays a run-time argument.
+template <int KIND, int KR, int IM>
 __global__ void __launch_bounds__(kThreads, 1)
 scan_mma_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmX, const MmaArgs a) {
   extern __shared__ uint8_t smem_raw[];
@@ -340,7 +366,7 @@ scan_mma_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
     u64 *L = lists + slot;  // entry i at L[i * kQM]: lanes of a warp hit consecutive banks
     // int8: the column value is MINUS the exact score, so the rest of the epilogue runs as mode 0 (s = -value)
     const int mode = KIND == 2 ? 0 : a.mode;
-    const int imode = a.mode;
+    constexpr int imode = IM;
     const int K = (int)k;
     // The pool is UNSORTED: the k smallest keys accepted so far, with the position of the largest
     // cached.  Accepting a key replaces the largest and rescans the pool for the new one — k
@@ -374,7 +400,7 @@ scan_mma_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
     //   mode 3/4 (IP / cosine through tf32): colc = +eps hx, dthr = (-T | 1 - T) - eps hq.
     // Modes 2-4 never use f as a score: a candidate is re-scored exactly (exact_score) before it is offered.
     // ---- int8: per-thread query constants and the per-column score, the formulas of K1 (scan_gemv.cu) ----
-    const bool ic4 = KIND == 2;  // per-row constants, always staged (unconditional loads in the hot loop): {|x|^2 as int} (plain L2), the row tail or its filter form (QuantizedInteger), zeros (plain -IP)
+    const bool ic4 = KIND == 2 && IM != 5;  // per-row constants, always staged (unconditional loads in the hot loop): {|x|^2 as int} (plain L2), the row tail or its filter form (QuantizedInteger), zeros (plain -IP)
     float4 *colc4 = reinterpret_cast<float4 *>(colc);
     const float4 qt = (KIND == 2 && imode >= 7 && qvalid) ? a.qtails[q0 + slot] : make_float4(0, 0, 0, 0);
     const float dq = (float)a.d;
@@ -397,9 +423,9 @@ scan_mma_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
       const int ip = (int)raw;
       if (imode == 5) return (float)ip;
       if (imode == 6) {
-        float sc = (float)(__float_as_int(c4.x) - 2 * ip + qq_i);
-        if (a.metric == ZVB200_METRIC_L2) sc = sqrtf(sc);
-        return -sc;
+        // minus the SQUARED distance for both L2 metrics (exact integer): the root is taken only for the
+        // few candidates (root6 below), a per-column sqrt would cost more than the rest of the filter
+        return -(float)(__float_as_int(c4.x) - 2 * ip + qq_i);
       }
       if (imode == 7) {
         // FILTER value for QuantizedInteger L2: minus the score in its expanded, linear-in-ip form
@@ -431,11 +457,13 @@ scan_mma_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
       return m;
     };
     const bool resc = mode >= 2;
+    const bool root6 = KIND == 2 && imode == 6 && a.metric == ZVB200_METRIC_L2;
     const float hq = (resc && qvalid) ? 0.5f * a.qnorms[q0 + slot] : 0.f;
     auto dthr_of = [&](u64 tk) -> float {
       if (!qvalid) return __int_as_float(0x7f800000);
       const float tau_f = unorder_f32((uint32_t)(tk >> 32));
       if (KIND == 2 && imode == 7) return Q0 - tau_f - Mthr - (fabsf(Q0) + fabsf(tau_f)) * 4.8e-7f;
+      if (root6) return -(tau_f * tau_f * 1.000001f);  // a superset; the candidate's own root decides
       if (mode == 0) return -tau_f;
       if (mode == 1) {
         const float t = 1.0f - tau_f;
@@ -602,11 +630,9 @@ scan_mma_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
 #pragma unroll
             for (int j = 0; j < 32; ++j) v[j] = __float_as_uint(fmaf(cc[c + j], cb, __uint_as_float(v[j])));
           }
-          float mx = __uint_as_float(v[0]);
-#pragma unroll
-          for (int j = 1; j < 32; ++j) mx = fmaxf(mx, __uint_as_float(v[j]));
+          const float mx = max32(v);
           float su;  // an upper bound of the exact score of the chunk's best row
-          if (mode == 0) su = -mx;
+          if (mode == 0) su = root6 ? sqrtf(-mx) : -mx;
           else if (mode == 1) su = 1.0f - mx;
           else {
             su = mode == 2 ? 2.0f * ((1.0f + a.eps) * hq - mx) : (mode == 3 ? -mx : 1.0f - mx) + a.eps * hq;
@@ -631,11 +657,8 @@ scan_mma_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
           __nanosleep(256);
         }
       }
-#pragma unroll 1
-      for (int c0 = 0; c0 < ((a.dbg & 1) ? 0 : kBN); c0 += 32) {
-        uint32_t v[32];
-        tmem_ld32(taddr + c0, v);
-        tmem_ld_wait();
+      // one 32-column chunk of this thread's query: filter by the chunk's best score, rarely more
+      auto chunk = [&](uint32_t (&v)[32], const int c0) {
         if (KIND == 2) {
 #pragma unroll
           for (int j = 0; j < 32; ++j) v[j] = __float_as_uint(ival(v[j], cc4[c0 + j]));
@@ -650,9 +673,7 @@ scan_mma_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
             v[j + 3] = __float_as_uint(__uint_as_float(v[j + 3]) + c4.w);
           }
         }
-        float mx = __uint_as_float(v[0]);
-#pragma unroll
-        for (int j = 1; j < 32; ++j) mx = fmaxf(mx, __uint_as_float(v[j]));
+        const float mx = max32(v);
         if (__any_sync(FULL, mx >= dthr) && !(a.dbg & 16)) {
           // rare once the bounds are warm: some query of this warp has a candidate among its 32 scores.
           // The warp walks the UNION of its lanes' candidate columns (one copy of the accept code,
@@ -675,6 +696,7 @@ scan_mma_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
                                        : __uint_as_float(raw) + (resc ? cc[c0 + j] : 0.f);
             bool cand = ((m >> j) & 1u) && dv >= dthr;  // dthr may have tightened since the mask was built
             float s = mode == 0 ? -dv : 1.0f - dv;
+            if (root6) s = sqrtf(s);
             if (KIND == 2 && imode == 7) {  // the filter nominated it: the exact reference-order score
               if (cand) s = qi8_l2sq((float)(int)raw, a.tails[row], qt, dq);
             }
@@ -699,6 +721,21 @@ scan_mma_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
             __syncwarp();
           }
           if (prof) c_slow += clock64() - c0s;
+        }
+      };
+      // the TMEM read of the next chunk is in flight while this one is filtered
+      {
+        const int cend = (a.dbg & 1) ? 0 : kBN;
+        uint32_t va[32], vb[32];
+        if (cend) tmem_ld32(taddr, va);
+#pragma unroll 1
+        for (int c0 = 0; c0 < cend; c0 += 64) {
+          tmem_ld_wait_on(va);
+          tmem_ld32(taddr + c0 + 32, vb);
+          chunk(va, c0);
+          tmem_ld_wait_on(vb);
+          if (c0 + 64 < cend) tmem_ld32(taddr + c0 + 64, va);
+          chunk(vb, c0 + 32);
         }
       }
       if (prof) {
@@ -891,9 +928,16 @@ cudaError_t launch_scan_mma(const RowsView &rv, const QueryView &qv, const Searc
   }
   if (!make_map(&tmX, rv.rows + row_begin * rv.row_stride, kind, rv.d, std::max<uint64_t>(nrows, 1), rv.row_stride, kBN))
     return cudaErrorInvalidValue;
-  auto kern = f32  ? (sp.k <= 8 ? scan_mma_kernel<1, 8> : sp.k <= 16 ? scan_mma_kernel<1, 16> : scan_mma_kernel<1, 0>)
-              : i8 ? (sp.k <= 8 ? scan_mma_kernel<2, 8> : sp.k <= 16 ? scan_mma_kernel<2, 16> : scan_mma_kernel<2, 0>)
-                   : (sp.k <= 8 ? scan_mma_kernel<0, 8> : sp.k <= 16 ? scan_mma_kernel<0, 16> : scan_mma_kernel<0, 0>);
+  typedef void (*KernFn)(const CUtensorMap, const CUtensorMap, const MmaArgs);
+#define ZVB_MMA_KR(KIND, IM) \
+  (sp.k <= 8 ? (KernFn)scan_mma_kernel<KIND, 8, IM> : sp.k <= 16 ? (KernFn)scan_mma_kernel<KIND, 16, IM> : (KernFn)scan_mma_kernel<KIND, 0, IM>)
+  KernFn kern = f32 ? ZVB_MMA_KR(1, 0)
+                : !i8 ? ZVB_MMA_KR(0, 0)
+                : a.mode == 5 ? ZVB_MMA_KR(2, 5)
+                : a.mode == 6 ? ZVB_MMA_KR(2, 6)
+                : a.mode == 7 ? ZVB_MMA_KR(2, 7)
+                              : ZVB_MMA_KR(2, 8);
+#undef ZVB_MMA_KR
   cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return e;
   if (nrows == 0) {
