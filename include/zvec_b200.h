@@ -54,6 +54,7 @@ extern "C" {
 #define ZVB200_INVALID_INDEX 0xffffffffu
 #define ZVB200_INVALID_KEY 0xffffffffffffffffull /* kInvalidKey, index_helper / flat_streamer_entity.cc:269 */
 #define ZVB200_MAX_TOPK 1024u
+#define ZVB200_MAX_CANDIDATES 8192u /* candidate rows per query of zvb200_search_rows */
 
 typedef struct zvb200_store zvb200_store; /* device-resident vector store on ONE GPU */
 typedef struct zvb200_ctx zvb200_ctx;     /* per-thread search context (IndexContext) */
@@ -195,6 +196,47 @@ int zvb200_ivf_search(zvb200_ctx *c, const void *queries, uint32_t q, uint32_t k
 /* threshold / filter_bitmap as in zvb200_search (bit i = drop stored row i, list order): a filtered list
  * still counts whole against the scan budget, like IVFEntity::search(list, query, filter, ...)
  * (ivf_entity.cc:587-659). */
+
+/* ---- query reformers on the device: replace IndexReformer::transform, the per-query CPU work in front of a
+ * search of a converted index (called from core_interface::Index::_prepare_for_search).  The reformer is the
+ * one the store's (dtype, metric) implies:
+ *   fp16                    HalfFloatReformer          src/core/quantizer/half_float_reformer.cc
+ *   cosine fp32 / fp16      CosineReformer             src/core/quantizer/cosine_reformer.cc:66-112
+ *   QuantizedInteger int8   IntegerStreamingReformer   src/core/quantizer/integer_quantizer_reformer.cc:308-370
+ *                           (RecordQuantizer::quantize_record, record_quantizer.h:24-83)
+ *   fp32 L2 / IP            none (copied)
+ * queries_fp32: q x dim floats, dim = the ORIGINAL dimension (the store's dimension minus its tail).
+ * out: q stored elements (the store's elem bytes each), i.e. what transform() returns.  int8 records are
+ * bit-identical to the reference's; fp16 conversions too; the cosine norm may differ from the reference's
+ * SIMD sum in the last place.  ZVB200_ERR_UNSUPPORTED for plain int8 stores (they take int8 queries). */
+int zvb200_reform_queries(zvb200_ctx *c, const float *queries_fp32, uint32_t q, uint32_t dim, void *out);
+int zvb200_reform_queries_device(zvb200_ctx *c, const float *queries_fp32_dev, uint32_t q, uint32_t dim,
+                                 void *out_dev);
+/* zvb200_search for ORIGINAL fp32 queries: reformer + scan in one call, nothing returns to the host in
+ * between (core_interface::Index::Search = _prepare_for_search + _dense_search, index.cc:380-410). */
+int zvb200_search_fp32(zvb200_ctx *c, const float *queries_fp32, uint32_t q, uint32_t dim, uint32_t k,
+                       float threshold, const uint32_t *filter, uint64_t *out_keys, float *out_scores,
+                       uint32_t *out_index, uint32_t *out_counts);
+
+/* ---- brute force over given rows: replaces FlatStreamer::search_bf_by_p_keys_impl
+ * (src/core/algorithm/flat/flat_streamer.cc:347-389) with stored-row indices for keys (the caller owns the
+ * key -> row map).  rows: [q][m] HOST, ZVB200_INVALID_INDEX / out-of-range entries are skipped like keys the
+ * entity does not hold; deleted and filtered rows are skipped; a row listed twice is scored twice, as there.
+ * queries in the store's layout.  m <= ZVB200_MAX_CANDIDATES.  Outputs as zvb200_search. */
+int zvb200_search_rows(zvb200_ctx *c, const void *queries, uint32_t q, const uint32_t *rows, uint32_t m,
+                       uint32_t k, float threshold, const uint32_t *filter, uint64_t *out_keys,
+                       float *out_scores, uint32_t *out_index, uint32_t *out_counts);
+
+/* ---- refiner: replaces core_interface::Index::Search with a refiner_param (src/core/interface/index.cc:
+ * 408-445): a coarse search for floor(k * scale_factor) rows (scale_factor 0 = 1, index.cc:794-801) on the
+ * quantised index `coarse`, then the exact brute force over those candidates on the reference index `exact`
+ * (a Flat index in the reference, index.cc:417-420), best k.  Both stores hold the same documents in the same
+ * row order on one device; the candidates never leave the device.  queries_fp32 / dim as in
+ * zvb200_reform_queries; filter applies to both stages (index.cc:439); results carry the exact store's keys. */
+int zvb200_search_refined(zvb200_ctx *coarse, zvb200_ctx *exact, const float *queries_fp32, uint32_t q,
+                          uint32_t dim, uint32_t k, float scale_factor, const uint32_t *filter,
+                          uint64_t *out_keys, float *out_scores, uint32_t *out_index,
+                          uint32_t *out_counts);
 
 #ifdef __cplusplus
 }

@@ -66,6 +66,14 @@ _SIGS = {
     "zvb200_ivf_set_budget_sizes": (C.c_int, [C.c_void_p, C.c_void_p]),
     "zvb200_ivf_search": (C.c_int, [C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint64, C.c_float,
                                     C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "zvb200_reform_queries": (C.c_int, [C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_void_p]),
+    "zvb200_reform_queries_device": (C.c_int, [C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_void_p]),
+    "zvb200_search_fp32": (C.c_int, [C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32, C.c_float, C.c_void_p,
+                                     C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "zvb200_search_rows": (C.c_int, [C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p, C.c_uint32, C.c_uint32, C.c_float,
+                                     C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "zvb200_search_refined": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32,
+                                        C.c_float, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
 }
 
 
@@ -259,6 +267,53 @@ class Context:
         _check(lib().zvb200_fuse_weighted(self.h, _ptr(keys), _ptr(scores), _ptr(counts), F, q, k, topn, fuse_metric,
                                           _ptr(weights), 1 if negate else 0, _ptr(ok), _ptr(os_), _ptr(oc)))
         return ok, os_, oc
+
+    def _outs(self, q, k):
+        return (np.empty((q, k), np.uint64), np.empty((q, k), np.float32), np.empty((q, k), np.uint32),
+                np.empty(q, np.uint32))
+
+    def reform_queries(self, queries_fp32):
+        """IndexReformer::transform of the store's type on the device: [q, dim] fp32 -> [q, elem_bytes] u8."""
+        queries_fp32 = np.ascontiguousarray(queries_fp32, np.float32)
+        q, dim = queries_fp32.shape
+        out = np.empty((q, self.store.elem_bytes), np.uint8)
+        _check(lib().zvb200_reform_queries(self.h, _ptr(queries_fp32), q, dim, _ptr(out)))
+        return out
+
+    def search_fp32(self, queries_fp32, k, threshold=FLT_MAX, filter_bitmap=None):
+        """Original fp32 queries: reformer + scan on the device."""
+        queries_fp32 = np.ascontiguousarray(queries_fp32, np.float32)
+        q, dim = queries_fp32.shape
+        if filter_bitmap is not None:
+            filter_bitmap = np.ascontiguousarray(filter_bitmap, np.uint32)
+        keys, scores, index, counts = self._outs(q, k)
+        _check(lib().zvb200_search_fp32(self.h, _ptr(queries_fp32), q, dim, k, threshold, _ptr(filter_bitmap),
+                                        _ptr(keys), _ptr(scores), _ptr(index), _ptr(counts)))
+        return keys, scores, index, counts
+
+    def search_rows(self, queries, rows, k, threshold=FLT_MAX, filter_bitmap=None):
+        """FlatStreamer::search_bf_by_p_keys_impl with stored rows for keys: rows [q, m] u32."""
+        queries = np.ascontiguousarray(queries)
+        rows = np.ascontiguousarray(rows, np.uint32)
+        q, m = rows.shape
+        assert q * self.store.elem_bytes == queries.nbytes
+        if filter_bitmap is not None:
+            filter_bitmap = np.ascontiguousarray(filter_bitmap, np.uint32)
+        keys, scores, index, counts = self._outs(q, k)
+        _check(lib().zvb200_search_rows(self.h, _ptr(queries), q, _ptr(rows), m, k, threshold, _ptr(filter_bitmap),
+                                        _ptr(keys), _ptr(scores), _ptr(index), _ptr(counts)))
+        return keys, scores, index, counts
+
+    def search_refined(self, exact_ctx, queries_fp32, k, scale_factor, filter_bitmap=None):
+        """The refiner flow (self = the quantised index's context, exact_ctx = the reference Flat index's)."""
+        queries_fp32 = np.ascontiguousarray(queries_fp32, np.float32)
+        q, dim = queries_fp32.shape
+        if filter_bitmap is not None:
+            filter_bitmap = np.ascontiguousarray(filter_bitmap, np.uint32)
+        keys, scores, index, counts = self._outs(q, k)
+        _check(lib().zvb200_search_refined(self.h, exact_ctx.h, _ptr(queries_fp32), q, dim, k, scale_factor,
+                                           _ptr(filter_bitmap), _ptr(keys), _ptr(scores), _ptr(index), _ptr(counts)))
+        return keys, scores, index, counts
 
     def search_device(self, q_ptr, q, k, out_scores_ptr, out_index_ptr, threshold=FLT_MAX, filter_ptr=None):
         _check(lib().zvb200_search_device(self.h, C.c_void_p(q_ptr), q, k, threshold,

@@ -4,6 +4,7 @@
 #include <float.h>
 
 #include <algorithm>
+#include <cmath>
 #include <atomic>
 #include <cstdio>
 #include <cstring>
@@ -102,6 +103,7 @@ struct zvb200_ctx {
   cudaStream_t stream = nullptr;
   DevBuf qin, qf32, qraw, qtails, qnorms, part, out_scores, out_index, filter, misc, gtau;
   DevBuf coarse_scores, coarse_index, seg_prefix, seg_row, seg_count;  // IVF
+  DevBuf qsrc, cand;  // fp32 queries before the reformer; candidate rows of the refiner
   QueryView last_qv;
   HostBuf h_q, h_scores, h_index;
   int force_kernel = 0;
@@ -398,7 +400,7 @@ int zvb200_ctx_destroy(zvb200_ctx *c) {
   cudaStreamSynchronize(c->stream);
   DevBuf *d[] = {&c->qin, &c->qf32, &c->qraw, &c->qtails, &c->qnorms, &c->part, &c->out_scores,
                  &c->out_index, &c->filter, &c->misc, &c->gtau, &c->coarse_scores, &c->coarse_index,
-                 &c->seg_prefix, &c->seg_row, &c->seg_count};
+                 &c->seg_prefix, &c->seg_row, &c->seg_count, &c->qsrc, &c->cand};
   for (auto b : d) b->release();
   c->h_q.release(); c->h_scores.release(); c->h_index.release();
   if (c->ev_scan0) cudaEventDestroy(c->ev_scan0);
@@ -434,10 +436,8 @@ const char *zvb200_ctx_last_kernel(const zvb200_ctx *c) { return c ? c->last_ker
 // search
 // ======================================================================================
 
-// Prepare queries and run scan + final merge for queries already on the device.
-static int search_core(zvb200_ctx *c, zvb200_store *s, const void *queries_dev, uint32_t q, uint32_t k,
-                       float threshold, const uint32_t *filter_dev, float *out_scores_dev,
-                       uint32_t *out_index_dev, uint64_t row_begin, uint64_t row_end) {
+// queries (stored layout, device) -> compute layout in the context's buffers
+static int prep_core(zvb200_ctx *c, zvb200_store *s, const void *queries_dev, uint32_t q, QueryView *out) {
   RowsView rv = s->view();
   const uint32_t esz = s->dtype == ZVB200_DT_FP32 ? 4 : s->dtype == ZVB200_DT_FP16 ? 2 : 1;
   const size_t qf32_row = (size_t)(s->chunks * 16 / esz) * 4;
@@ -462,6 +462,21 @@ static int search_core(zvb200_ctx *c, zvb200_store *s, const void *queries_dev, 
   qv.q = q;
   qv.qpad_rows = true;
   c->last_qv = qv;  // the IVF list scan reuses the prepared queries
+  *out = qv;
+  return 0;
+}
+
+// Prepare queries and run scan + final merge for queries already on the device.
+static int search_core(zvb200_ctx *c, zvb200_store *s, const void *queries_dev, uint32_t q, uint32_t k,
+                       float threshold, const uint32_t *filter_dev, float *out_scores_dev,
+                       uint32_t *out_index_dev, uint64_t row_begin, uint64_t row_end) {
+  RowsView rv = s->view();
+  const uint32_t esz = s->dtype == ZVB200_DT_FP32 ? 4 : s->dtype == ZVB200_DT_FP16 ? 2 : 1;
+  QueryView qv;
+  {
+    const int r = prep_core(c, s, queries_dev, q, &qv);
+    if (r != 0) return r;
+  }
   SearchParams sp;
   sp.k = k; sp.threshold = threshold; sp.filter = filter_dev;
 
@@ -525,6 +540,74 @@ static int search_core(zvb200_ctx *c, zvb200_store *s, const void *queries_dev, 
   return 0;
 }
 
+// device results of the context -> host outputs, document keys and per-query counts
+static int finish_results(zvb200_ctx *c, zvb200_store *s, uint32_t q, uint32_t k, uint64_t *out_keys, float *out_scores,
+                          uint32_t *out_index, uint32_t *out_counts) {
+  const size_t nres = (size_t)q * k;
+  CU(c->h_scores.ensure(nres * 4));
+  CU(c->h_index.ensure(nres * 4));
+  CU(cudaMemcpyAsync(c->h_scores.p, c->out_scores.p, nres * 4, cudaMemcpyDeviceToHost, c->stream));
+  CU(cudaMemcpyAsync(c->h_index.p, c->out_index.p, nres * 4, cudaMemcpyDeviceToHost, c->stream));
+  CU(cudaStreamSynchronize(c->stream));
+  const float *hs = (const float *)c->h_scores.p;
+  const uint32_t *hi = (const uint32_t *)c->h_index.p;
+  memcpy(out_scores, hs, nres * 4);
+  if (out_index) memcpy(out_index, hi, nres * 4);
+  for (uint32_t i = 0; i < q; ++i) {
+    uint32_t cnt = 0;
+    for (uint32_t j = 0; j < k; ++j) {
+      const uint32_t ix = hi[(size_t)i * k + j];
+      if (ix != ZVB200_INVALID_INDEX) ++cnt;
+      if (out_keys)
+        out_keys[(size_t)i * k + j] = ix == ZVB200_INVALID_INDEX ? ZVB200_INVALID_KEY
+                                      : (s->keys.empty() ? (uint64_t)ix : s->keys[ix]);
+    }
+    if (out_counts) out_counts[i] = cnt;
+  }
+  return 0;
+}
+
+// The refiner's second stage on the device: exact scores of each query's candidate rows, best k
+// (FlatStreamer::search_bf_by_p_keys_impl, flat_streamer.cc:347-389, with rows for keys).
+static int rows_core(zvb200_ctx *c, zvb200_store *s, const void *queries_dev, uint32_t q, const uint32_t *rows_dev,
+                     uint32_t m, uint32_t k, float threshold, const uint32_t *filter_dev, float *out_scores_dev,
+                     uint32_t *out_index_dev) {
+  QueryView qv;
+  int r = prep_core(c, s, queries_dev, q, &qv);
+  if (r != 0) return r;
+  CU(c->seg_prefix.ensure((size_t)q * (m + 1) * 4));
+  CU(c->seg_row.ensure((size_t)q * m * 4));
+  CU(c->seg_count.ensure((size_t)q * 4));
+  CU(launch_rows_plan(rows_dev, q, m, s->n, (uint32_t *)c->seg_prefix.p, (uint32_t *)c->seg_row.p,
+                      (uint32_t *)c->seg_count.p, c->stream));
+  RowsView rv = s->view();
+  SearchParams sp;
+  sp.k = k; sp.threshold = threshold; sp.filter = filter_dev;
+  const size_t parts = scan_lists_parts(q, s->sm_count);
+  CU(c->part.ensure((size_t)q * parts * k * sizeof(u64)));
+  uint32_t nparts = 0;
+  CU(cudaEventRecord(c->ev_scan0, c->stream));
+  c->scan_timed = true;
+  CU(launch_scan_lists(rv, qv, sp, (const uint32_t *)c->seg_prefix.p, (const uint32_t *)c->seg_row.p,
+                       (const uint32_t *)c->seg_count.p, m, (u64 *)c->part.p, &nparts, s->sm_count, c->stream));
+  CU(cudaEventRecord(c->ev_scan1, c->stream));
+  c->last_kernel = "scan_rows";
+  CU(launch_merge_parts((const u64 *)c->part.p, nparts, q, k, out_scores_dev, out_index_dev, c->stream));
+  return 0;
+}
+
+// fp32 queries on the device -> the store's query layout in c->qin (the reformer the store's type implies)
+static int reform_core(zvb200_ctx *c, zvb200_store *s, const float *in_dev, uint32_t q, uint32_t dim) {
+  const int kind = reform_kind(s->dtype, s->metric);
+  if (kind < 0) return set_err(ZVB200_ERR_UNSUPPORTED, "no fp32 query reformer for this store type");
+  if (dim != s->d) return set_err(ZVB200_ERR_MISMATCH, "query dimension does not match the store");
+  CU(c->qin.ensure((size_t)q * s->elem_bytes));
+  cudaError_t e = launch_reform(in_dev, q, dim, kind, (uint8_t *)c->qin.p, s->elem_bytes, c->stream);
+  if (e == cudaErrorInvalidValue) return set_err(ZVB200_ERR_UNSUPPORTED, "reformer: dimension too large");
+  CU(e);
+  return 0;
+}
+
 static int check_search_args(zvb200_ctx *c, const void *queries, uint32_t q, uint32_t k) {
   cudaGetLastError();  // a stale non-sticky error of an unrelated call must not fail this search
   if (!c || (!queries && q)) return set_err(ZVB200_ERR_INVALID_ARGUMENT, "null argument");
@@ -573,25 +656,7 @@ int zvb200_search(zvb200_ctx *c, const void *queries, uint32_t q, uint32_t k, fl
   r = search_core(c, s, c->qin.p, q, k, threshold, fdev, (float *)c->out_scores.p,
                   (uint32_t *)c->out_index.p, 0, s->n);
   if (r != 0) return r;
-  CU(cudaMemcpyAsync(c->h_scores.p, c->out_scores.p, nres * 4, cudaMemcpyDeviceToHost, c->stream));
-  CU(cudaMemcpyAsync(c->h_index.p, c->out_index.p, nres * 4, cudaMemcpyDeviceToHost, c->stream));
-  CU(cudaStreamSynchronize(c->stream));
-  const float *hs = (const float *)c->h_scores.p;
-  const uint32_t *hi = (const uint32_t *)c->h_index.p;
-  memcpy(out_scores, hs, nres * 4);
-  if (out_index) memcpy(out_index, hi, nres * 4);
-  for (uint32_t i = 0; i < q; ++i) {
-    uint32_t cnt = 0;
-    for (uint32_t j = 0; j < k; ++j) {
-      const uint32_t ix = hi[(size_t)i * k + j];
-      if (ix != ZVB200_INVALID_INDEX) ++cnt;
-      if (out_keys)
-        out_keys[(size_t)i * k + j] = ix == ZVB200_INVALID_INDEX ? ZVB200_INVALID_KEY
-                                      : (s->keys.empty() ? (uint64_t)ix : s->keys[ix]);
-    }
-    if (out_counts) out_counts[i] = cnt;
-  }
-  return 0;
+  return finish_results(c, s, q, k, out_keys, out_scores, out_index, out_counts);
 }
 
 int zvb200_merge_topk_device(zvb200_ctx *c, const float *scores_dev, const uint32_t *index_dev,
@@ -799,25 +864,161 @@ int zvb200_ivf_search(zvb200_ctx *c, const void *queries, uint32_t q, uint32_t k
   c->last_kernel = lists_stream ? "scan_lists_stream" : "scan_lists";
   CU(launch_merge_parts((const u64 *)c->part.p, nparts, q, k, (float *)c->out_scores.p, (uint32_t *)c->out_index.p,
                         c->stream));
-  CU(cudaMemcpyAsync(c->h_scores.p, c->out_scores.p, nres * 4, cudaMemcpyDeviceToHost, c->stream));
-  CU(cudaMemcpyAsync(c->h_index.p, c->out_index.p, nres * 4, cudaMemcpyDeviceToHost, c->stream));
-  CU(cudaStreamSynchronize(c->stream));
-  const float *hs = (const float *)c->h_scores.p;
-  const uint32_t *hi = (const uint32_t *)c->h_index.p;
-  memcpy(out_scores, hs, nres * 4);
-  if (out_index) memcpy(out_index, hi, nres * 4);
-  for (uint32_t i = 0; i < q; ++i) {
-    uint32_t cnt = 0;
-    for (uint32_t j = 0; j < k; ++j) {
-      const uint32_t ix = hi[(size_t)i * k + j];
-      if (ix != ZVB200_INVALID_INDEX) ++cnt;
-      if (out_keys)
-        out_keys[(size_t)i * k + j] = ix == ZVB200_INVALID_INDEX ? ZVB200_INVALID_KEY
-                                      : (s->keys.empty() ? (uint64_t)ix : s->keys[ix]);
-    }
-    if (out_counts) out_counts[i] = cnt;
-  }
+  return finish_results(c, s, q, k, out_keys, out_scores, out_index, out_counts);
+}
+
+// ---- query reformers and the refiner --------------------------------------------------
+
+static int upload_fp32_queries(zvb200_ctx *c, const float *queries, uint32_t q, uint32_t dim) {
+  const size_t b = (size_t)q * dim * 4;
+  CU(c->h_q.ensure(b));
+  CU(c->qsrc.ensure(b));
+  memcpy(c->h_q.p, queries, b);
+  CU(cudaMemcpyAsync(c->qsrc.p, c->h_q.p, b, cudaMemcpyHostToDevice, c->stream));
   return 0;
+}
+
+static const uint32_t *upload_filter(zvb200_ctx *c, zvb200_store *s, const uint32_t *filter, int *err) {
+  *err = 0;
+  if (!filter) return nullptr;
+  const size_t fb = ((s->n + 31) / 32) * 4;
+  cudaError_t e = c->filter.ensure(fb);
+  if (e == cudaSuccess) e = cudaMemcpyAsync(c->filter.p, filter, fb, cudaMemcpyHostToDevice, c->stream);
+  if (e != cudaSuccess) { *err = cuda_fail(e, "filter upload"); return nullptr; }
+  return (const uint32_t *)c->filter.p;
+}
+
+int zvb200_reform_queries(zvb200_ctx *c, const float *queries_fp32, uint32_t q, uint32_t dim, void *out) {
+  cudaGetLastError();
+  if (!c || (!queries_fp32 && q) || (!out && q)) return set_err(ZVB200_ERR_INVALID_ARGUMENT, "null argument");
+  if (q == 0) return 0;
+  zvb200_store *s = c->s;
+  CU(cudaSetDevice(s->device));
+  int r = upload_fp32_queries(c, queries_fp32, q, dim);
+  if (r == 0) r = reform_core(c, s, (const float *)c->qsrc.p, q, dim);
+  if (r != 0) return r;
+  const size_t ob = (size_t)q * s->elem_bytes;
+  CU(c->h_scores.ensure(ob));
+  CU(cudaMemcpyAsync(c->h_scores.p, c->qin.p, ob, cudaMemcpyDeviceToHost, c->stream));
+  CU(cudaStreamSynchronize(c->stream));
+  memcpy(out, c->h_scores.p, ob);
+  c->last_kernel = "reform";
+  return 0;
+}
+
+int zvb200_reform_queries_device(zvb200_ctx *c, const float *queries_fp32_dev, uint32_t q, uint32_t dim, void *out_dev) {
+  cudaGetLastError();
+  if (!c || (!queries_fp32_dev && q) || (!out_dev && q)) return set_err(ZVB200_ERR_INVALID_ARGUMENT, "null argument");
+  if (q == 0) return 0;
+  zvb200_store *s = c->s;
+  CU(cudaSetDevice(s->device));
+  const int kind = reform_kind(s->dtype, s->metric);
+  if (kind < 0) return set_err(ZVB200_ERR_UNSUPPORTED, "no fp32 query reformer for this store type");
+  if (dim != s->d) return set_err(ZVB200_ERR_MISMATCH, "query dimension does not match the store");
+  cudaError_t e = launch_reform(queries_fp32_dev, q, dim, kind, (uint8_t *)out_dev, s->elem_bytes, c->stream);
+  if (e == cudaErrorInvalidValue) return set_err(ZVB200_ERR_UNSUPPORTED, "reformer: dimension too large");
+  CU(e);
+  c->last_kernel = "reform";
+  return 0;
+}
+
+int zvb200_search_fp32(zvb200_ctx *c, const float *queries_fp32, uint32_t q, uint32_t dim, uint32_t k, float threshold,
+                       const uint32_t *filter, uint64_t *out_keys, float *out_scores, uint32_t *out_index,
+                       uint32_t *out_counts) {
+  int r = check_search_args(c, queries_fp32, q, k);
+  if (r != 0) return r;
+  if (!out_scores) return set_err(ZVB200_ERR_INVALID_ARGUMENT, "null out_scores");
+  if (q == 0) return 0;
+  zvb200_store *s = c->s;
+  CU(cudaSetDevice(s->device));
+  const size_t nres = (size_t)q * k;
+  CU(c->out_scores.ensure(nres * 4));
+  CU(c->out_index.ensure(nres * 4));
+  r = upload_fp32_queries(c, queries_fp32, q, dim);
+  if (r == 0) r = reform_core(c, s, (const float *)c->qsrc.p, q, dim);
+  if (r != 0) return r;
+  const uint32_t *fdev = upload_filter(c, s, filter, &r);
+  if (r != 0) return r;
+  r = search_core(c, s, c->qin.p, q, k, threshold, fdev, (float *)c->out_scores.p, (uint32_t *)c->out_index.p, 0, s->n);
+  if (r != 0) return r;
+  return finish_results(c, s, q, k, out_keys, out_scores, out_index, out_counts);
+}
+
+int zvb200_search_rows(zvb200_ctx *c, const void *queries, uint32_t q, const uint32_t *rows, uint32_t m, uint32_t k,
+                       float threshold, const uint32_t *filter, uint64_t *out_keys, float *out_scores,
+                       uint32_t *out_index, uint32_t *out_counts) {
+  int r = check_search_args(c, queries, q, k);
+  if (r != 0) return r;
+  if (!out_scores || (!rows && q && m)) return set_err(ZVB200_ERR_INVALID_ARGUMENT, "null argument");
+  if (m == 0 || m > ZVB200_MAX_CANDIDATES) return set_err(ZVB200_ERR_INVALID_ARGUMENT, "candidates per query must be 1..8192");
+  if (q == 0) return 0;
+  zvb200_store *s = c->s;
+  CU(cudaSetDevice(s->device));
+  const size_t qbytes = (size_t)q * s->elem_bytes, nres = (size_t)q * k, rbytes = (size_t)q * m * 4;
+  CU(c->h_q.ensure(std::max(qbytes, rbytes)));
+  CU(c->qin.ensure(qbytes));
+  CU(c->cand.ensure(rbytes));
+  CU(c->out_scores.ensure(nres * 4));
+  CU(c->out_index.ensure(nres * 4));
+  memcpy(c->h_q.p, queries, qbytes);
+  CU(cudaMemcpyAsync(c->qin.p, c->h_q.p, qbytes, cudaMemcpyHostToDevice, c->stream));
+  CU(cudaStreamSynchronize(c->stream));  // h_q is reused for the candidate rows
+  memcpy(c->h_q.p, rows, rbytes);
+  CU(cudaMemcpyAsync(c->cand.p, c->h_q.p, rbytes, cudaMemcpyHostToDevice, c->stream));
+  const uint32_t *fdev = upload_filter(c, s, filter, &r);
+  if (r != 0) return r;
+  r = rows_core(c, s, c->qin.p, q, (const uint32_t *)c->cand.p, m, k, threshold, fdev, (float *)c->out_scores.p,
+                (uint32_t *)c->out_index.p);
+  if (r != 0) return r;
+  return finish_results(c, s, q, k, out_keys, out_scores, out_index, out_counts);
+}
+
+int zvb200_search_refined(zvb200_ctx *coarse, zvb200_ctx *exact, const float *queries_fp32, uint32_t q, uint32_t dim,
+                          uint32_t k, float scale_factor, const uint32_t *filter, uint64_t *out_keys, float *out_scores,
+                          uint32_t *out_index, uint32_t *out_counts) {
+  int r = check_search_args(coarse, queries_fp32, q, k);
+  if (r == 0) r = check_search_args(exact, queries_fp32, q, k);
+  if (r != 0) return r;
+  if (!out_scores) return set_err(ZVB200_ERR_INVALID_ARGUMENT, "null out_scores");
+  zvb200_store *sc = coarse->s, *se = exact->s;
+  if (sc->device != se->device) return set_err(ZVB200_ERR_MISMATCH, "refiner: both stores must be on one device");
+  if (sc->n != se->n) return set_err(ZVB200_ERR_MISMATCH, "refiner: the stores must hold the same rows");
+  // Index::_get_coarse_search_topk (src/core/interface/index.cc:794-801)
+  if (scale_factor == 0.f) scale_factor = 1.f;
+  const double kc = floor((double)k * (double)scale_factor);
+  if (!(kc >= 1.0) || kc > (double)ZVB200_MAX_TOPK) return set_err(ZVB200_ERR_INVALID_ARGUMENT, "refiner: coarse topk must be 1..1024");
+  const uint32_t m = (uint32_t)kc;
+  if (q == 0) return 0;
+  CU(cudaSetDevice(sc->device));
+  const size_t nres = (size_t)q * k;
+  // everything runs on the coarse context's stream; the exact context lends its buffers
+  const cudaStream_t keep = exact->stream;
+  exact->stream = coarse->stream;
+  auto body = [&]() -> int {
+    CU(coarse->out_scores.ensure((size_t)q * m * 4));
+    CU(coarse->out_index.ensure((size_t)q * m * 4));
+    CU(exact->out_scores.ensure(nres * 4));
+    CU(exact->out_index.ensure(nres * 4));
+    int e = upload_fp32_queries(coarse, queries_fp32, q, dim);
+    if (e == 0) e = reform_core(coarse, sc, (const float *)coarse->qsrc.p, q, dim);
+    if (e != 0) return e;
+    const uint32_t *fdev = upload_filter(coarse, sc, filter, &e);
+    if (e != 0) return e;
+    // 1. coarse: floor(topk * scale_factor) rows per query from the quantised store
+    e = search_core(coarse, sc, coarse->qin.p, q, m, FLT_MAX, fdev, (float *)coarse->out_scores.p,
+                    (uint32_t *)coarse->out_index.p, 0, sc->n);
+    if (e != 0) return e;
+    // 2. exact scores of those rows in the reference store, best topk
+    e = reform_core(exact, se, (const float *)coarse->qsrc.p, q, dim);
+    if (e != 0) return e;
+    e = rows_core(exact, se, exact->qin.p, q, (const uint32_t *)coarse->out_index.p, m, k, FLT_MAX, fdev,
+                  (float *)exact->out_scores.p, (uint32_t *)exact->out_index.p);
+    if (e != 0) return e;
+    return finish_results(exact, se, q, k, out_keys, out_scores, out_index, out_counts);
+  };
+  r = body();
+  exact->stream = keep;
+  return r;
 }
 
 }  // extern "C"

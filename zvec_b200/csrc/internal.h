@@ -129,6 +129,14 @@ cudaError_t launch_fuse(const uint64_t *keys, const float *scores, const uint32_
                         uint64_t *out_keys, double *out_scores, uint32_t *out_counts, cudaStream_t st);
 size_t fuse_max_entries();
 
+// K7: query reformers (fp32 -> the store's query layout) and the refiner's candidate plan (refine.cu)
+enum { RF_NONE = 0, RF_FP16 = 1, RF_COS_FP32 = 2, RF_COS_FP16 = 3, RF_QI8_L2 = 4, RF_QI8_IP = 5 };
+int reform_kind(int dtype, int metric);  // -1: the store type has no fp32 reformer
+cudaError_t launch_reform(const float *in, uint32_t q, uint32_t dim, int kind, uint8_t *out, uint32_t elem_bytes,
+                          cudaStream_t st);
+cudaError_t launch_rows_plan(const uint32_t *rows, uint32_t q, uint32_t m, uint64_t n, uint32_t *seg_prefix,
+                             uint32_t *seg_row, uint32_t *seg_count, cudaStream_t st);
+
 void count_launch(int n = 1);
 
 }  // namespace zvb
