@@ -742,6 +742,17 @@ class GpuIVFSearcher : public IndexSearcher {
   size_t list_count(void) const { return entity_.inverted_list_count(); }
   size_t vector_count(void) const { return entity_.vector_count(); }
   uint32_t bf_threshold(void) const { return bf_threshold_; }
+  //! what IVFStreamer::get_vector_by_id reads (ivf_streamer.h:79-82)
+  int vector_by_key(uint64_t key, IndexStorage::MemoryBlock &block) const { return entity_.get_vector_by_key(key, block); }
+  //! the device store AND the stock searcher's index (IVFStreamer::unload, ivf_streamer.cc:119-129)
+  int unload_all(void) {
+    this->unload();
+    {
+      std::lock_guard<std::mutex> g(mu_);
+      clones_.clear();
+    }
+    return stock_.unload();
+  }
 
  private:
   // the reformer inside an IVFEntity keeps a scratch buffer: one clone per context (IVFSearcher::update_context)
@@ -807,6 +818,77 @@ void GpuIVFContext::reset(const GpuIVFSearcher *owner) {
 
 INDEX_FACTORY_REGISTER_SEARCHER(GpuIVFSearcher);
 
+// ======================================================================================
+// GpuIVFStreamer — IVFStreamer's interface (ivf_streamer.h:27-120).  The reference's IVFStreamer
+// is a read-only view of a built IVF index behind the streamer interface (open() loads what
+// IVFSearcher::load loads, flush() is a no-op, there is no add_impl: ivf_streamer.cc:52-117), which
+// is what core_interface::IVFIndex creates by name (indexes/ivf_index.cc:38-39).  Same composition
+// here: the GPU searcher above does the work, this class maps the streamer life cycle onto it.
+// ======================================================================================
+class GpuIVFStreamer : public IndexStreamer {
+ public:
+  GpuIVFStreamer() = default;
+  ~GpuIVFStreamer() override { this->unload(); }
+
+  int init(const IndexMeta &meta, const ailego::Params &params) override {
+    meta_ = meta;
+    state_ = 1;
+    return impl_.init(params);
+  }
+  int cleanup(void) override {
+    this->unload();
+    state_ = 0;
+    return impl_.cleanup();
+  }
+  //! IVFStreamer::open (ivf_streamer.cc:52-117): meta comes from the storage, then centroids + lists
+  int open(IndexStorage::Pointer storage) override {
+    if (!storage) return IndexError_InvalidArgument;
+    if (state_ != 1) return IndexError_Runtime;
+    const int rc = impl_.load(storage, IndexMetric::Pointer());
+    if (rc != 0) return rc;
+    meta_ = impl_.meta();
+    state_ = 2;
+    return 0;
+  }
+  int flush(uint64_t /*check_point*/) override { return 0; }
+  int close(void) override { return this->unload(); }
+  int unload(void) override {
+    if (state_ == 2) state_ = 1;
+    return impl_.unload_all();
+  }
+
+  int search_bf_impl(const void *query, const IndexQueryMeta &qmeta, Context::Pointer &context) const override {
+    return impl_.search_bf_impl(query, qmeta, 1, context);
+  }
+  int search_bf_impl(const void *query, const IndexQueryMeta &qmeta, uint32_t count, Context::Pointer &context) const override {
+    return impl_.search_bf_impl(query, qmeta, count, context);
+  }
+  int search_impl(const void *query, const IndexQueryMeta &qmeta, Context::Pointer &context) const override {
+    return impl_.search_impl(query, qmeta, 1, context);
+  }
+  int search_impl(const void *query, const IndexQueryMeta &qmeta, uint32_t count, Context::Pointer &context) const override {
+    return impl_.search_impl(query, qmeta, count, context);
+  }
+  Context::Pointer create_context(void) const override {
+    return state_ == 2 ? impl_.create_context() : Context::Pointer();
+  }
+  IndexProvider::Pointer create_provider(void) const override {
+    return state_ == 2 ? impl_.create_provider() : IndexProvider::Pointer();
+  }
+  const Stats &stats(void) const override { return impl_.stats(); }
+  const IndexMeta &meta(void) const override { return meta_; }
+  int get_vector_by_id(const uint32_t id, IndexStorage::MemoryBlock &block) const override {
+    return impl_.vector_by_key(id, block);
+  }
+
+ private:
+  GpuIVFSearcher impl_{};
+  IndexMeta meta_{};
+  int state_{0};
+};
+
+INDEX_FACTORY_REGISTER_STREAMER(GpuIVFStreamer);
+
 }  // namespace core
 }  // namespace zvec
 
@@ -818,6 +900,7 @@ extern "C" int zvb200_install_overrides(void) {
   static zvec::ailego::Factory<zvec::core::IndexSearcher>::Register<zvec::core::GpuFlatSearcher> r("FlatSearcher");
   static zvec::ailego::Factory<zvec::core::IndexStreamer>::Register<zvec::core::GpuFlatStreamer> rs("FlatStreamer");
   static zvec::ailego::Factory<zvec::core::IndexSearcher>::Register<zvec::core::GpuIVFSearcher> ri("IVFSearcher");
-  (void)r; (void)rs; (void)ri;
+  static zvec::ailego::Factory<zvec::core::IndexStreamer>::Register<zvec::core::GpuIVFStreamer> ris("IVFStreamer");
+  (void)r; (void)rs; (void)ri; (void)ris;
   return 0;
 }

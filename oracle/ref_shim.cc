@@ -65,10 +65,14 @@ struct RefIndex {
   IndexReformer::Pointer reformer;
   IndexMetric::Pointer metric;
   IndexSearcher::Pointer searcher;
+  IndexStreamer::Pointer streamer;  // set by zref_index_use_streamer: searches then go through it
+  IndexStorage::Pointer streamer_storage;
   std::string path;
   std::string stored;           // converted rows, row-major, n * meta.element_size()
   size_t n{0};
+  IndexRunner *runner() { return streamer ? static_cast<IndexRunner *>(streamer.get()) : searcher.get(); }
   ~RefIndex() {
+    if (streamer) { streamer->close(); streamer->cleanup(); }
     if (searcher) { searcher->unload(); searcher->cleanup(); }
     if (!path.empty()) ::unlink(path.c_str());
   }
@@ -200,6 +204,29 @@ int zref_index_use_searcher(void *h, const char *searcher_name, const char *sear
   return 0;
 }
 
+// Search the index's file through a registered IndexStreamer class instead (IVFStreamer and the like are
+// read-only streamers: init(meta, params) -> open(storage), as core_interface::IVFIndex does,
+// src/core/interface/indexes/ivf_index.cc:38-39).  An empty class name goes back to the searcher.
+int zref_index_use_streamer(void *h, const char *streamer_name, const char *search_params) {
+  auto ix = (RefIndex *)h;
+  if (ix->streamer) { ix->streamer->close(); ix->streamer->cleanup(); ix->streamer.reset(); ix->streamer_storage.reset(); }
+  if (!streamer_name || !*streamer_name) return 0;
+  auto st = IndexFactory::CreateStreamer(streamer_name);
+  auto storage = IndexFactory::CreateStorage("MMapFileReadStorage");
+  if (!st || !storage) return fail(-1, "no streamer");
+  Params sp; parse_params(search_params, &sp);
+  int r = st->init(ix->meta, sp);
+  if (r != 0) return fail(r, "streamer init");
+  if (storage->open(ix->path, false) != 0) return fail(-1, "storage open");
+  r = st->open(storage);
+  if (r != 0) return fail(r, "streamer open");
+  ix->streamer = st;
+  ix->streamer_storage = storage;
+  return 0;
+}
+// 1 if IndexFactory has a streamer class of that name
+int zref_has_streamer(const char *name) { return IndexFactory::HasStreamer(name) ? 1 : 0; }
+
 // Load an index plugin with the reference's OWN loader (IndexPluginBroker -> IndexPlugin::load
 // -> dlopen, src/core/framework/index_plugin.cc:20-56), as tools/core/bench.cc:796-803 does
 // for its trailing argv.  Returns 0 or -1 (zref_last_error()).
@@ -288,7 +315,9 @@ int zref_index_search(void *h, const void *queries, uint32_t count, uint32_t top
   const int has_thr = g_has_threshold;
   const float thr = g_threshold;
   auto work = [&]() {
-    auto ctx = ix->searcher->create_context();
+    IndexRunner *run = ix->runner();
+    auto ctx = run->create_context();
+    if (!ctx) { err = -1; return; }
     ctx->set_topk(topk);
     if (fmod) ctx->set_filter([fmod, frem](uint64_t key) { return key % fmod == frem; });
     if (has_thr) ctx->set_threshold(thr);
@@ -296,8 +325,8 @@ int zref_index_search(void *h, const void *queries, uint32_t count, uint32_t top
       uint32_t b = next.fetch_add(1);
       if (b >= nb) break;
       uint32_t q0 = b * batch, qn = std::min(batch, count - q0);
-      int rc = (qn == 1) ? ix->searcher->search_impl(&tq[(size_t)q0 * oes], qm, ctx)
-                         : ix->searcher->search_impl(&tq[(size_t)q0 * oes], qm, qn, ctx);
+      int rc = (qn == 1) ? run->search_impl(&tq[(size_t)q0 * oes], qm, ctx)
+                         : run->search_impl(&tq[(size_t)q0 * oes], qm, qn, ctx);
       if (rc != 0) { err = rc; break; }
       for (uint32_t i = 0; i < qn; ++i) {
         const auto &res = ctx->result(i);

@@ -173,6 +173,13 @@ class RefIndex:
         if self.L.zref_index_use_searcher(self.h, name.encode(), search_params.encode()) != 0:
             raise RuntimeError(self.L.zref_last_error().decode())
 
+    def use_streamer(self, name, search_params=""):
+        """search the same index file through a registered IndexStreamer class (IVFStreamer and the like);
+        an empty name goes back to the searcher"""
+        self.L.zref_index_use_streamer.argtypes = [C.c_void_p, C.c_char_p, C.c_char_p]
+        if self.L.zref_index_use_streamer(self.h, name.encode(), search_params.encode()) != 0:
+            raise RuntimeError(self.L.zref_last_error().decode())
+
     def distances(self, stored_rows, stored_query):
         stored_rows = np.ascontiguousarray(stored_rows)
         n = stored_rows.nbytes // self.elem

@@ -304,3 +304,50 @@ def test_gpu_ivf_searcher_equals_ivf_searcher(metric, conv):
     finally:
         S.ref().zref_set_filter(0, 0)
     ix.close()
+
+
+# ---- GpuIVFStreamer: the streamer-interface twin (what core_interface::IVFIndex creates by name) ----
+@needs_plugin
+@pytest.mark.gpu
+@pytest.mark.parametrize("metric,conv", [("SquaredEuclidean", ""), ("Cosine", "CosineNormalizeConverter")])
+def test_gpu_ivf_streamer_equals_ivf_streamer(metric, conv):
+    S.ref().zref_has_streamer.argtypes = [S.C.c_char_p]
+    assert S.ref().zref_has_streamer(b"GpuIVFStreamer") == 1
+    n, d, nlist, k = 20000, 32, 64, 10
+    rng = np.random.default_rng(18)
+    centres = rng.standard_normal((nlist, d)).astype(np.float32)
+    x = (centres[np.arange(n) % nlist] + 0.3 * rng.standard_normal((n, d))).astype(np.float32)
+    qs = (centres[rng.integers(0, nlist, 40)] + 0.3 * rng.standard_normal((40, d))).astype(np.float32)
+    bp = "proxima.ivf.builder.centroid_count=%d" % nlist
+    sp = "proxima.ivf.searcher.scan_ratio=0.1"
+    ix = S.RefIndex(x, S.DT_FP32, d, metric, conv, kind="IVF", build_params=bp, search_params=sp)
+    import zvec_b200 as z
+
+    def same(a, b, what):
+        for i in range(len(a[3])):
+            assert a[3][i] == b[3][i], what
+            nv = int(a[3][i])
+            assert np.allclose(a[1][i][:nv], b[1][i][:nv], rtol=1e-4, atol=1e-6), what
+            diff = a[0][i][:nv] != b[0][i][:nv]
+            if diff.any():
+                assert np.allclose(a[1][i][:nv][diff], b[1][i][:nv][diff], rtol=1e-4), what
+
+    ix.use_streamer("IVFStreamer", sp)                      # the stock streamer over the file
+    r_batch = ix.search(qs, k, batch=len(qs)); r_one = ix.search(qs, k, batch=1)
+    S.ref().zref_set_filter(4, 2)
+    try:
+        r_filt = ix.search(qs, k, batch=8)
+    finally:
+        S.ref().zref_set_filter(0, 0)
+    ix.use_streamer("GpuIVFStreamer", sp)                   # the GPU class over the SAME file
+    before = z.lib().zvb200_kernel_launches()
+    same(ix.search(qs, k, batch=len(qs)), r_batch, "batch")
+    same(ix.search(qs, k, batch=1), r_one, "one by one")
+    assert z.lib().zvb200_kernel_launches() > before
+    S.ref().zref_set_filter(4, 2)
+    try:
+        same(ix.search(qs, k, batch=8), r_filt, "filter")
+    finally:
+        S.ref().zref_set_filter(0, 0)
+    ix.use_streamer("")
+    ix.close()
