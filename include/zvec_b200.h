@@ -133,10 +133,15 @@ int zvb200_ctx_sync(zvb200_ctx *c);
 int zvb200_ctx_last_scan_ms(zvb200_ctx *c, float *ms);
 /* The context's cudaStream_t (as void*) so callers can record events on it. */
 void *zvb200_ctx_stream(zvb200_ctx *c);
-/* Force a scan kernel: 0 auto, 1 GEMV scan (LDG), 2 tiled CUDA-core, 3 tcgen05, 4 bulk-async streaming scan. */
+/* Force a scan kernel: 0 auto, 1 GEMV scan (LDG), 2 tiled CUDA-core, 3 tcgen05, 4 bulk-async streaming scan,
+ * 5 tcgen05 on the int8 codes themselves (kind::i8) where 3 would contract a QuantizedInteger L2 store's bf16
+ * shadow operands. */
 int zvb200_ctx_set_kernel(zvb200_ctx *c, int which);
 /* Name of the scan kernel the last search on this context used. */
 const char *zvb200_ctx_last_kernel(const zvb200_ctx *c);
+/* Operand kind of the last tcgen05 scan on this context: 0 kind::f16, 1 kind::tf32, 2 kind::i8,
+ * 3 kind::f16 on the bf16 shadow operands of a QuantizedInteger L2 store; -1 none yet. */
+int zvb200_ctx_last_mma_kind(const zvb200_ctx *c);
 
 /* ---- distance functions: replaces ailego XxxDistanceMatrix<T,1,1>::Compute as handed out
  * by IndexMetric::distance() (src/core/metric/euclidean_metric.cc:785-851): out[j*n+i] =

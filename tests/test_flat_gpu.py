@@ -337,6 +337,85 @@ def test_mma_rescore_filter_is_sound_on_hostile_data(kind, shape):
     ctx.close(); st.close()
 
 
+# ---- QuantizedInteger L2: two tensor-core forms.  Kernel 3 contracts the store's bf16 shadow operands
+# (kind::f16, no per-column constants), kernel 5 the int8 codes themselves (kind::i8); both only nominate
+# with a sound margin and re-score from the int8 codes, so both must be bit-exact -------------------------
+@pytest.mark.parametrize("kernel,mma_kind", [(3, 3), (5, 2)])
+@pytest.mark.parametrize("d,q,k", [(96, 300, 100), (96, 64, 10), (7, 33, 10), (200, 130, 32), (1000, 40, 16)])
+def test_qi8_l2_tensor_core_forms_are_bit_exact(kernel, mma_kind, d, q, k):
+    metric, dt, sdim, stored, conv = make_stored("qi8_l2", 30000, d, 90 + d)
+    queries = np.ascontiguousarray(conv(np.random.default_rng(91 + d).standard_normal((q, d)).astype(np.float32)))
+    st = z.Store(dt, metric, sdim); st.append(stored); st.seal()
+    ctx = z.Context(st); ctx.set_kernel(kernel)
+    gk, gs, gi, gc = ctx.search(queries, k)
+    # the shadow operands are kept only up to 320 dimensions (beyond, bf16's half rate loses to kind::i8)
+    assert ctx.last_kernel() == "scan_mma" and ctx.last_mma_kind() == (mma_kind if d <= 320 else 2)
+    ek, es, ei, ec = S.oracle_flat_search(metric, dt, stored, sdim, queries, k)
+    for i in range(q):
+        alld = S.oracle_distances(metric, dt, stored, sdim, queries[i])
+        S.check_topk_parity(gi[i], gs[i], ei[i], es[i], all_dist=alld, exact=True, what="qi8_l2 kernel %d q%d" % (kernel, i))
+    ctx.close(); st.close()
+
+
+@pytest.mark.parametrize("kernel", [3, 5])
+@pytest.mark.parametrize("shape", ["offset", "norm_spread", "near_duplicates", "constant_rows", "huge_values"])
+def test_qi8_l2_tensor_core_filter_is_sound_on_hostile_data(kernel, shape):
+    """Per-record scales over many decades, large common offsets (mb >> ma * codes), constant records (the
+    quantiser's epsilon scale), values far beyond fp16's range: the bf16 / int8 filters must still nominate
+    every true neighbour, and the results must equal the streaming scan's bit for bit."""
+    n, d, q, k = 20000, 96, 48, 10
+    rng = np.random.default_rng(92)
+    base = rng.standard_normal((n, d)).astype(np.float32)
+    qs = rng.standard_normal((q, d)).astype(np.float32)
+    if shape == "offset":
+        base = base * 0.05 + 30.0; qs = qs * 0.05 + 30.0
+    elif shape == "norm_spread":
+        base *= (10.0 ** rng.uniform(-3, 3, (n, 1))).astype(np.float32)
+        qs *= (10.0 ** rng.uniform(-3, 3, (q, 1))).astype(np.float32)
+    elif shape == "near_duplicates":
+        qs = base[rng.integers(0, n, q)] + 1e-3 * rng.standard_normal((q, d)).astype(np.float32)
+    elif shape == "constant_rows":
+        base[::7] = rng.standard_normal((len(base[::7]), 1)).astype(np.float32)      # max == min inside a record
+        qs[::5] = 0.25
+    else:
+        base *= 1.0e4; qs *= 1.0e4
+    metric, dt, sdim, stored, conv = make_stored("qi8_l2", n, d, 93, base=base)
+    queries = np.ascontiguousarray(conv(qs))
+    st = z.Store(dt, metric, sdim); st.append(stored); st.seal()
+    ctx = z.Context(st); ctx.set_kernel(kernel)
+    gk, gs, gi, gc = ctx.search(queries, k)
+    assert ctx.last_kernel() == "scan_mma"
+    ctx.set_kernel(1)
+    ek, es, ei, ec = ctx.search(queries, k)
+    for i in range(q):
+        alld = S.oracle_distances(metric, dt, stored, sdim, queries[i])
+        S.check_topk_parity(gi[i], gs[i], ei[i], es[i], all_dist=alld, exact=True, what="qi8_l2 %s q%d" % (shape, i))
+    ctx.close(); st.close()
+
+
+def test_qi8_l2_shadow_follows_appends_and_overwrites():
+    """rows added after a seal and rows overwritten in place (FlatStreamer add / add_with_id) must reach the
+    shadow operands too"""
+    d, k = 64, 10
+    metric, dt, sdim, stored, conv = make_stored("qi8_l2", 6000, d, 94)
+    queries = np.ascontiguousarray(conv(np.random.default_rng(95).standard_normal((40, d)).astype(np.float32)))
+    st = z.Store(dt, metric, sdim); st.append(stored[:2000]); st.seal()
+    ctx = z.Context(st); ctx.set_kernel(3)
+    ctx.search(queries, k)
+    st.append(stored[2000:]); st.seal()
+    cur = stored.copy()
+    for r in (5, 2500, 5999):
+        cur[r] = queries[r % 40]                      # a stored row equal to a query: distance 0 must win
+        st.write(r, cur[r], r)
+    gk, gs, gi, gc = ctx.search(queries, k)
+    assert ctx.last_mma_kind() == 3
+    ek, es, ei, ec = S.oracle_flat_search(metric, dt, cur, sdim, queries, k)
+    for i in range(40):
+        alld = S.oracle_distances(metric, dt, cur, sdim, queries[i])
+        S.check_topk_parity(gi[i], gs[i], ei[i], es[i], all_dist=alld, exact=True, what="after appends q%d" % i)
+    ctx.close(); st.close()
+
+
 def test_mma_and_tile_agree_on_ids():
     metric, dt, sdim, stored, conv = make_stored("fp16_ip", 50000, 768, 60)
     queries = np.ascontiguousarray(conv(np.random.default_rng(61).standard_normal((256, 768)).astype(np.float32)))

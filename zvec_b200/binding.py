@@ -53,6 +53,7 @@ _SIGS = {
     "zvb200_ctx_last_scan_ms": (C.c_int, [C.c_void_p, C.POINTER(C.c_float)]),
     "zvb200_ctx_set_kernel": (C.c_int, [C.c_void_p, C.c_int]),
     "zvb200_ctx_last_kernel": (C.c_char_p, [C.c_void_p]),
+    "zvb200_ctx_last_mma_kind": (C.c_int, [C.c_void_p]),
     "zvb200_distance_matrix": (C.c_int, [C.c_int, C.c_int, C.c_int, C.c_uint32, C.c_void_p, C.c_uint64,
                                          C.c_void_p, C.c_uint32, C.c_void_p]),
     "zvb200_merge_topk_device": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p,
@@ -205,6 +206,9 @@ class Context:
 
     def last_kernel(self):
         return lib().zvb200_ctx_last_kernel(self.h).decode()
+
+    def last_mma_kind(self):
+        return lib().zvb200_ctx_last_mma_kind(self.h)
 
     def last_scan_ms(self):
         ms = C.c_float()

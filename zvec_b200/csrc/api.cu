@@ -42,6 +42,9 @@ struct zvb200_store {
   uint8_t *rows = nullptr;
   float4 *tails = nullptr;
   float *norms = nullptr;
+  uint8_t *shadow = nullptr;      // QuantizedInteger L2: bf16 operands of the tensor-core filter (built at seal)
+  uint32_t shadow_k = 0;
+  uint64_t shadowed = 0;
   uint32_t *drop = nullptr;       // device bitmap (allocated lazily)
   uint64_t drop_words = 0;
   uint64_t n = 0, cap = 0, normed = 0;
@@ -64,6 +67,7 @@ struct zvb200_store {
     v.rows = rows; v.n = n; v.row_stride = row_stride; v.chunks = chunks; v.d = d;
     v.dtype = dtype; v.metric = metric; v.tails = tails; v.norms = norms;
     v.drop = has_drop ? drop : nullptr;
+    if (shadow && shadowed >= n) { v.shadow = shadow; v.shadow_k = shadow_k; }
     return v;
   }
 };
@@ -101,12 +105,14 @@ struct zvb200_ctx {
   zvb200_store *s = nullptr;
   int device = 0;  // copy: a context may outlive its store (destruction order is the caller's)
   cudaStream_t stream = nullptr;
+  DevBuf qshadow;
   DevBuf qin, qf32, qraw, qtails, qnorms, part, out_scores, out_index, filter, misc, gtau;
   DevBuf coarse_scores, coarse_index, seg_prefix, seg_row, seg_count;  // IVF
   DevBuf qsrc, cand;  // fp32 queries before the reformer; candidate rows of the refiner
   QueryView last_qv;
   HostBuf h_q, h_scores, h_index;
   int force_kernel = 0;
+  int last_mma_kind = -1;
   const char *last_kernel = "none";
   cudaEvent_t ev_scan0 = nullptr, ev_scan1 = nullptr;  // bracket the scan kernel(s) of the last search
   bool scan_timed = false;
@@ -161,6 +167,7 @@ static int store_grow(zvb200_store *s, uint64_t want) {
   if (s->rows) cudaFree(s->rows);
   if (s->tails) cudaFree(s->tails);
   if (s->norms) { cudaFree(s->norms); s->norms = nullptr; s->normed = 0; }
+  if (s->shadow) { cudaFree(s->shadow); s->shadow = nullptr; s->shadowed = 0; }
   s->rows = nr; s->tails = nt; s->cap = ncap;
   return 0;
 }
@@ -202,6 +209,7 @@ int zvb200_store_destroy(zvb200_store *s) {
   if (s->rows) cudaFree(s->rows);
   if (s->tails) cudaFree(s->tails);
   if (s->norms) cudaFree(s->norms);
+  if (s->shadow) cudaFree(s->shadow);
   if (s->drop) cudaFree(s->drop);
   if (s->list_off_dev) cudaFree(s->list_off_dev);
   if (s->budget_dev) cudaFree(s->budget_dev);
@@ -317,6 +325,28 @@ int zvb200_store_seal(zvb200_store *s) {
       s->normed = s->n;
     }
   }
+  // QuantizedInteger L2: the bf16 shadow operands of the tensor-core filter (scan_mma.cu KIND 3).  Extra HBM
+  // (2 * round_up(d + 9, 64) bytes per row); when it does not fit the int8 kind::i8 scan stays in charge.
+  static const bool shadow_off = [] { const char *e = getenv("ZVB200_QI8_SHADOW"); return e && atoi(e) == 0; }();
+  // Worth it while the epilogue, not the tensor pipe, bounds the int8 form: measured 3.1x at d = 96 and 0.7x at
+  // d = 768 (bf16 contracts at half the int8 rate), so only up to ZVB200_QI8_SHADOW_MAXD dimensions (default 320).
+  static const uint32_t shadow_maxd = [] { const char *e = getenv("ZVB200_QI8_SHADOW_MAXD"); return e ? (uint32_t)atoi(e) : 320u; }();
+  if (s->metric == ZVB200_METRIC_QI8_L2SQ && s->d <= std::min(1040u, shadow_maxd) && s->n > 0 && !shadow_off) {
+    if (!s->shadow) {
+      s->shadow_k = qi8_shadow_k(s->d);
+      s->shadowed = 0;
+      if (cudaMalloc((void **)&s->shadow, s->cap * (size_t)s->shadow_k * 2) != cudaSuccess) {
+        cudaGetLastError();
+        s->shadow = nullptr;
+      }
+    }
+    if (s->shadow && s->shadowed < s->n) {
+      RowsView v = s->view();
+      CU(launch_qi8_shadow_rows(v, s->shadowed, s->n, s->shadow, s->shadow_k, s->stream));
+      CU(cudaStreamSynchronize(s->stream));
+      s->shadowed = s->n;
+    }
+  }
   s->sealed = true;
   return 0;
 }
@@ -353,6 +383,10 @@ int zvb200_store_write(zvb200_store *s, uint64_t row, const void *vec, uint64_t 
   if (s->norms && row < s->normed) {
     RowsView v = s->view();
     CU(launch_row_norms(v, row, row + 1, s->norms, s->stream));
+  }
+  if (s->shadow && row < s->shadowed) {
+    RowsView v = s->view();
+    CU(launch_qi8_shadow_rows(v, row, row + 1, s->shadow, s->shadow_k, s->stream));
   }
   CU(cudaStreamSynchronize(s->stream));
   if (s->keys.empty() && key != row) { s->keys.resize(s->n); for (uint64_t i = 0; i < s->n; ++i) s->keys[i] = i; }
@@ -400,7 +434,7 @@ int zvb200_ctx_destroy(zvb200_ctx *c) {
   cudaStreamSynchronize(c->stream);
   DevBuf *d[] = {&c->qin, &c->qf32, &c->qraw, &c->qtails, &c->qnorms, &c->part, &c->out_scores,
                  &c->out_index, &c->filter, &c->misc, &c->gtau, &c->coarse_scores, &c->coarse_index,
-                 &c->seg_prefix, &c->seg_row, &c->seg_count, &c->qsrc, &c->cand};
+                 &c->seg_prefix, &c->seg_row, &c->seg_count, &c->qsrc, &c->cand, &c->qshadow};
   for (auto b : d) b->release();
   c->h_q.release(); c->h_scores.release(); c->h_index.release();
   if (c->ev_scan0) cudaEventDestroy(c->ev_scan0);
@@ -424,11 +458,12 @@ int zvb200_ctx_last_scan_ms(zvb200_ctx *c, float *ms) {
 }
 void *zvb200_ctx_stream(zvb200_ctx *c) { return c ? (void *)c->stream : nullptr; }
 int zvb200_ctx_set_kernel(zvb200_ctx *c, int which) {
-  if (!c || which < 0 || which > 4) return set_err(ZVB200_ERR_INVALID_ARGUMENT, "bad kernel id");
+  if (!c || which < 0 || which > 5) return set_err(ZVB200_ERR_INVALID_ARGUMENT, "bad kernel id");
   c->force_kernel = which;
   return 0;
 }
 const char *zvb200_ctx_last_kernel(const zvb200_ctx *c) { return c ? c->last_kernel : "none"; }
+int zvb200_ctx_last_mma_kind(const zvb200_ctx *c) { return c ? c->last_mma_kind : -1; }
 
 }  // extern "C"
 
@@ -459,6 +494,14 @@ static int prep_core(zvb200_ctx *c, zvb200_store *s, const void *queries_dev, ui
   QueryView qv;
   qv.qf32 = (const float *)c->qf32.p; qv.qraw = (const uint8_t *)c->qraw.p;
   qv.qtails = (const float4 *)c->qtails.p; qv.qnorms = (const float *)c->qnorms.p;
+  if (rv.shadow) {
+    const size_t srow = (size_t)rv.shadow_k * 2;
+    CU(c->qshadow.ensure((size_t)qpad * srow));
+    if (qpad > q) CU(cudaMemsetAsync((uint8_t *)c->qshadow.p + (size_t)q * srow, 0, (size_t)(qpad - q) * srow, c->stream));
+    CU(launch_qi8_shadow_queries(rv, (const uint8_t *)c->qraw.p, (const float4 *)c->qtails.p, q, (uint8_t *)c->qshadow.p,
+                                 rv.shadow_k, c->stream));
+    qv.qshadow = (const uint8_t *)c->qshadow.p;
+  }
   qv.q = q;
   qv.qpad_rows = true;
   c->last_qv = qv;  // the IVF list scan reuses the prepared queries
@@ -481,6 +524,7 @@ static int search_core(zvb200_ctx *c, zvb200_store *s, const void *queries_dev, 
   sp.k = k; sp.threshold = threshold; sp.filter = filter_dev;
 
   int which = c->force_kernel;
+  if (which == 5) { which = 3; sp.no_shadow = true; }  // the tcgen05 scan on the int8 codes themselves
   const bool mma_ok = scan_mma_supports(rv, k);
   // batch 1 streams best through the GEMV scan; from 2 queries on the tensor-core scan wins where it
   // applies (it is HBM-bound below ~200 queries and reads the rows once for the whole batch)
@@ -516,6 +560,7 @@ static int search_core(zvb200_ctx *c, zvb200_store *s, const void *queries_dev, 
     g.q = qn;
     if (g.qf32) g.qf32 += (size_t)q0 * (s->chunks * 16 / esz);
     if (g.qraw) g.qraw += (size_t)q0 * s->row_stride;
+    if (g.qshadow) g.qshadow += (size_t)q0 * rv.shadow_k * 2;
     g.qtails += q0; g.qnorms += q0;
     uint32_t nparts = 0;
     if (which == 1) {
@@ -530,7 +575,7 @@ static int search_core(zvb200_ctx *c, zvb200_store *s, const void *queries_dev, 
     } else {
       CU(c->gtau.ensure((size_t)qn * scan_mma_max_parts(s->sm_count) * sizeof(uint32_t)));
       CU(launch_scan_mma(rv, g, sp, row_begin, row_end, (u64 *)c->part.p, &nparts, (uint32_t *)c->gtau.p,
-                         s->sm_count, c->stream));
+                         s->sm_count, c->stream, &c->last_mma_kind));
       c->last_kernel = "scan_mma";
     }
     if (q0 + group >= q) CU(cudaEventRecord(c->ev_scan1, c->stream));
@@ -829,7 +874,7 @@ int zvb200_ivf_search(zvb200_ctx *c, const void *queries, uint32_t q, uint32_t k
   CU(cudaMemcpyAsync(c->qin.p, c->h_q.p, qbytes, cudaMemcpyHostToDevice, c->stream));
   // 1. coarse: top-nprobe centroids per query (IVFCentroidIndex::search, ivf_centroid_index.cc:273-295)
   const int keep = c->force_kernel;
-  if (keep == 3) c->force_kernel = 0;
+  if (keep == 3 || keep == 5) c->force_kernel = 0;
   r = search_core(c, s->centroids, c->qin.p, q, nprobe, FLT_MAX, nullptr, (float *)c->coarse_scores.p,
                   (uint32_t *)c->coarse_index.p, 0, s->centroids->n);
   c->force_kernel = keep;

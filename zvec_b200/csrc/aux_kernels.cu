@@ -1,5 +1,6 @@
 // Small kernels around the scan: query preparation, row repacking on ingest, the final
 // per-query merge of partial lists (K5a) and the multi-GPU shard merge (K5b).
+#include <cuda_bf16.h>
 #include <math_constants.h>
 
 #include "internal.h"
@@ -114,6 +115,98 @@ __global__ void row_norms_kernel(RowsView rv, uint64_t row_begin, uint64_t row_e
   }
   for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
   if (lane == 0) norms[r] = s;
+}
+
+// ---- QuantizedInteger L2 on tensor cores: the "shadow" operands ------------------------------------
+// The score (quantized_integer_metric_matrix.h:36-60) in real arithmetic is
+//   s = R_r + Q0_q - [ ma*nQa*ip + mb*nQ1 + (ms*ma)*nQ2 ],   R_r = ma^2 ms2 + mb^2 d + 2 mb ms ma,
+//   nQa = 2 qa, nQ1 = 2 (qb d + qa qs), nQ2 = 2 qb,  Q0_q = qa^2 qs2 + qb^2 d + 2 qb qa qs
+// so (R_r - s) / nQa = sum_i (ma c_i) qc_i + mb (nQ1/nQa) + (ms ma)(nQ2/nQa) is BILINEAR in (row, query):
+// one contraction over d + 9 bf16 columns yields g = (Q0 - s) / nQa up to the margin qi8_shadow_eps, and the
+// epilogue compares g with a per-query register — no per-column constants (which cost the int8 kernel four
+// shared-memory wavefronts per column).  Row side: bf16(ma c_i), then {u_hi, u_hi, u_lo} for u = -(R_r - margin),
+// mb, ms*ma; query side: the codes (exact in bf16), then {v_hi, v_lo, v_hi} for v = 1/nQa, nQ1/nQa, nQ2/nQa.
+// The filter only nominates; candidates get the exact reference-order score from the int8 codes.
+__device__ __forceinline__ void bf16_split(float x, __nv_bfloat16 *hi, __nv_bfloat16 *lo) {
+  *hi = __float2bfloat16_rn(x);
+  *lo = __float2bfloat16_rn(x - __bfloat162float(*hi));
+}
+
+__global__ void qi8_shadow_rows_kernel(RowsView rv, uint64_t row_begin, uint64_t row_end, uint8_t *shadow,
+                                       uint32_t shadow_k) {
+  const uint32_t cpr = shadow_k / 8;  // 16-byte output chunks per row
+  const uint64_t idx = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const uint64_t r = row_begin + idx / cpr;
+  if (r >= row_end) return;
+  const uint32_t c = (uint32_t)(idx % cpr);
+  const int8_t *codes = reinterpret_cast<const int8_t *>(rv.rows + r * rv.row_stride);
+  const float4 m = rv.tails[r];
+  const uint32_t d = rv.d;
+  __align__(16) __nv_bfloat16 o[8];
+  __nv_bfloat16 ex[9];
+  bool have_ex = false;
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    const uint32_t i = c * 8 + j;
+    if (i < d) {
+      o[j] = __float2bfloat16_rn(m.x * (float)codes[i]);
+    } else if (i < d + 9) {
+      if (!have_ex) {
+        const float dq = (float)d;
+        const float t1 = m.x * m.x * m.w, mbd = m.y * m.y * dq, msma = m.z * m.x;
+        const float c0 = t1 + mbd + 2.0f * m.y * msma;
+        const float u1 = -(c0 - qi8_shadow_eps(d) * (t1 + mbd));
+        bf16_split(u1, &ex[0], &ex[2]); ex[1] = ex[0];
+        bf16_split(m.y, &ex[3], &ex[5]); ex[4] = ex[3];
+        bf16_split(msma, &ex[6], &ex[8]); ex[7] = ex[6];
+        have_ex = true;
+      }
+      __nv_bfloat16 v = ex[0];
+#pragma unroll
+      for (int e = 1; e < 9; ++e) v = (i - d) == (uint32_t)e ? ex[e] : v;
+      o[j] = v;
+    } else {
+      o[j] = __float2bfloat16_rn(0.f);
+    }
+  }
+  *reinterpret_cast<uint4 *>(shadow + (r * shadow_k + (size_t)c * 8) * 2) = *reinterpret_cast<const uint4 *>(o);
+}
+
+__global__ void qi8_shadow_queries_kernel(const uint8_t *qraw, uint32_t row_stride, const float4 *qtails, uint32_t q,
+                                          uint32_t d, uint8_t *out, uint32_t shadow_k) {
+  const uint32_t cpr = shadow_k / 8;
+  const uint32_t idx = blockIdx.x * blockDim.x + threadIdx.x;
+  const uint32_t qi = idx / cpr, c = idx % cpr;
+  if (qi >= q) return;
+  const int8_t *codes = reinterpret_cast<const int8_t *>(qraw + (size_t)qi * row_stride);
+  const float4 t = qtails[qi];
+  __align__(16) __nv_bfloat16 o[8];
+  __nv_bfloat16 ex[9];
+  bool have_ex = false;
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    const uint32_t i = c * 8 + j;
+    if (i < d) {
+      o[j] = __float2bfloat16_rn((float)codes[i]);  // |code| <= 128: exact
+    } else if (i < d + 9) {
+      if (!have_ex) {
+        const float dq = (float)d;
+        const float nQa = 2.0f * t.x, nQ1 = 2.0f * (t.y * dq + t.x * t.z), nQ2 = 2.0f * t.y;
+        const float inv = 1.0f / nQa;
+        bf16_split(inv, &ex[0], &ex[1]); ex[2] = ex[0];
+        bf16_split(nQ1 * inv, &ex[3], &ex[4]); ex[5] = ex[3];
+        bf16_split(nQ2 * inv, &ex[6], &ex[7]); ex[8] = ex[6];
+        have_ex = true;
+      }
+      __nv_bfloat16 v = ex[0];
+#pragma unroll
+      for (int e = 1; e < 9; ++e) v = (i - d) == (uint32_t)e ? ex[e] : v;
+      o[j] = v;
+    } else {
+      o[j] = __float2bfloat16_rn(0.f);
+    }
+  }
+  *reinterpret_cast<uint4 *>(out + ((size_t)qi * shadow_k + (size_t)c * 8) * 2) = *reinterpret_cast<const uint4 *>(o);
 }
 
 // ---- K5a: part[q][nparts][k] -> final q*k ---------------------------------------------
@@ -301,6 +394,29 @@ cudaError_t launch_row_norms(const RowsView &rv, uint64_t row_begin, uint64_t ro
   const uint64_t rows = row_end - row_begin;
   const uint64_t blocks = (rows + 7) / 8;
   row_norms_kernel<<<(unsigned)blocks, 256, 0, st>>>(rv, row_begin, row_end, norms);
+  count_launch();
+  return cudaGetLastError();
+}
+
+cudaError_t launch_qi8_shadow_rows(const RowsView &rv, uint64_t row_begin, uint64_t row_end, uint8_t *shadow,
+                                   uint32_t shadow_k, cudaStream_t st) {
+  if (row_end <= row_begin) return cudaSuccess;
+  const uint64_t cpr = shadow_k / 8;
+  const uint64_t per_launch = ((uint64_t)1 << 31) / 256 * 256 / cpr;  // rows per launch: grid.x stays below 2^31
+  for (uint64_t r0 = row_begin; r0 < row_end; r0 += per_launch) {
+    const uint64_t r1 = std::min(row_end, r0 + per_launch);
+    const uint64_t threads = (r1 - r0) * cpr;
+    qi8_shadow_rows_kernel<<<(unsigned)((threads + 255) / 256), 256, 0, st>>>(rv, r0, r1, shadow, shadow_k);
+    count_launch();
+  }
+  return cudaGetLastError();
+}
+
+cudaError_t launch_qi8_shadow_queries(const RowsView &rv, const uint8_t *qraw, const float4 *qtails, uint32_t q,
+                                      uint8_t *out, uint32_t shadow_k, cudaStream_t st) {
+  if (q == 0) return cudaSuccess;
+  const uint32_t threads = q * (shadow_k / 8);
+  qi8_shadow_queries_kernel<<<(threads + 255) / 256, 256, 0, st>>>(qraw, rv.row_stride, qtails, q, rv.d, out, shadow_k);
   count_launch();
   return cudaGetLastError();
 }

@@ -68,6 +68,18 @@ __device__ __forceinline__ float qi8_mip(float ipf, float4 m, float4 q, float d)
   return -r;
 }
 
+// Relative margin of the bf16 "shadow" filter for QuantizedInteger L2 (scan_mma.cu KIND 3, aux_kernels.cu):
+// |filter value - real-arithmetic score| <= eps * [(ma^2 ms2 + mb^2 d) + (qa^2 qs2 + qb^2 d)].
+//   2^-8           scaled codes rounded to bf16 (8-bit significand), query codes exact; Cauchy-Schwarz on the sum
+//   4.1 * 4.6e-5   the three bilinear extra terms as two-piece bf16 splits without the low*low product
+//                  (3 * 2^-16 each), their absolute values total <= 4.1 [row terms] + 3 [query terms]
+//   3.1e-5         fp32 evaluation of the constants and of the reference-order score (the int8 filter's margin)
+//   (d+9) * 2.5e-6 fp32 accumulation of d + 9 exact products inside the tensor core (4.8e-7 per term, the bound the
+//                  other filter modes use) over absolute terms that total <= 5.1 [row + query terms]
+__host__ __device__ __forceinline__ float qi8_shadow_eps(uint32_t d) {
+  return 4.2e-3f + (float)(d + 9u) * 2.5e-6f;
+}
+
 // 128-bit streaming load: read-only path, do not allocate in L1 (each stored byte is
 // read once per scan).
 __device__ __forceinline__ uint4 ldg_stream(const void *p) {

@@ -23,6 +23,10 @@ struct RowsView {
   const float4 *tails = nullptr;    // QI8: {a, b, s, s2} per row
   const float *norms = nullptr;     // |x|^2 per row (tensor-core L2 path)
   const uint32_t *drop = nullptr;   // bit set = deleted row or kInvalidKey hole
+  // QuantizedInteger L2: bf16 image of every row (scaled codes + the row's share of the score's bilinear
+  // terms), shadow_k halves per row — what the tcgen05 scan contracts instead of the int8 codes (scan_mma.cu)
+  const uint8_t *shadow = nullptr;
+  uint32_t shadow_k = 0;
 };
 
 // Queries in "compute layout", produced by prep_queries() on the device.
@@ -31,6 +35,7 @@ struct QueryView {
   const uint8_t *qraw = nullptr;   // raw codes/halves: q x row_stride bytes, zero padded
   const float4 *qtails = nullptr;  // QI8 query tails
   const float *qnorms = nullptr;   // |q|^2
+  const uint8_t *qshadow = nullptr;  // QuantizedInteger L2: bf16 image of the queries (the rows' counterpart)
   uint32_t q = 0;
   bool qpad_rows = false;          // qraw holds zero rows up to the next multiple of 128 queries
 };
@@ -39,6 +44,7 @@ struct SearchParams {
   uint32_t k = 0;
   float threshold = 0.f;
   const uint32_t *filter = nullptr;  // device bitmap, bit set = drop
+  bool no_shadow = false;            // QuantizedInteger L2: contract the int8 codes (kind::i8), not the bf16 shadow
 };
 
 // Partial top-k lists: part[query][nparts][k] packed keys, padded with kMaxKey.
@@ -69,7 +75,8 @@ bool scan_tile_supports(uint32_t k);
 // epilogue; at most sm_count query tiles of 128 per launch.
 cudaError_t launch_scan_mma(const RowsView &rv, const QueryView &qv, const SearchParams &sp,
                             uint64_t row_begin, uint64_t row_end, u64 *part, uint32_t *nparts,
-                            uint32_t *pub /* qv.q * scan_mma_max_parts words of scratch */, int sm_count, cudaStream_t st);
+                            uint32_t *pub /* qv.q * scan_mma_max_parts words of scratch */, int sm_count, cudaStream_t st,
+                            int *kind_out = nullptr /* 0 f16, 1 tf32, 2 i8, 3 bf16 shadow */);
 size_t scan_mma_max_parts(int sm_count);
 bool scan_mma_supports(const RowsView &rv, uint32_t k);
 // queries (stored layout, device) -> compute layout
@@ -89,6 +96,12 @@ cudaError_t launch_repack_rows(const uint8_t *src, uint32_t elem_bytes, uint64_t
                                uint32_t tail_off, cudaStream_t st);
 cudaError_t launch_row_norms(const RowsView &rv, uint64_t row_begin, uint64_t row_end,
                              float *norms, cudaStream_t st);
+// QuantizedInteger L2 shadow operands (aux_kernels.cu): rows [row_begin, row_end) of the store, and a query batch
+inline uint32_t qi8_shadow_k(uint32_t d) { return (d + 9u + 63u) & ~63u; }
+cudaError_t launch_qi8_shadow_rows(const RowsView &rv, uint64_t row_begin, uint64_t row_end, uint8_t *shadow,
+                                   uint32_t shadow_k, cudaStream_t st);
+cudaError_t launch_qi8_shadow_queries(const RowsView &rv, const uint8_t *qraw, const float4 *qtails, uint32_t q,
+                                      uint8_t *out, uint32_t shadow_k, cudaStream_t st);
 cudaError_t launch_distance_matrix(const RowsView &rv, const QueryView &qv, float *out,
                                    cudaStream_t st);
 

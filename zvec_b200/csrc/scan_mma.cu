@@ -215,6 +215,11 @@ __host__ __device__ constexpr uint32_t make_idesc_f16(int M, int N) {
   return (1u << 4) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
 }
 
+// kind::f16 with bf16 operands (the QuantizedInteger L2 shadow operands): bf16 x bf16 -> fp32.
+__host__ __device__ constexpr uint32_t make_idesc_bf16(int M, int N) {
+  return make_idesc_f16(M, N) | (1u << 7) | (1u << 10);
+}
+
 // kind::tf32: fp32 words in shared memory, the tensor core reads the top 19 bits; fp32 accumulate.
 __host__ __device__ constexpr uint32_t make_idesc_tf32(int M, int N) {
   return (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
@@ -245,6 +250,20 @@ __device__ __forceinline__ float exact_score(const MmaArgs &a, uint32_t row, uin
          : a.metric == ZVB200_METRIC_IP ? -acc : 1.0f - acc;
 }
 
+// Exact QuantizedInteger L2 score of (row, query) by ONE lane: the int8 dot product with dp4a, then the reference's
+// float epilogue in its own order — what K1 computes per row (scan_gemv.cu).
+__device__ __forceinline__ float exact_qi8_l2(const MmaArgs &a, uint32_t row, uint32_t qidx, const float4 qt, float dq) {
+  const uint4 *rp = reinterpret_cast<const uint4 *>(a.rows + (size_t)row * a.row_stride);
+  const uint4 *qp = reinterpret_cast<const uint4 *>(a.qraw + (size_t)qidx * a.row_stride);
+  int ip = 0;
+  for (uint32_t c = 0; c < a.chunks; ++c) {
+    const uint4 x = __ldg(rp + c), y = __ldg(qp + c);
+    ip = __dp4a((int)x.x, (int)y.x, ip); ip = __dp4a((int)x.y, (int)y.y, ip);
+    ip = __dp4a((int)x.z, (int)y.z, ip); ip = __dp4a((int)x.w, (int)y.w, ip);
+  }
+  return qi8_l2sq((float)ip, a.tails[row], qt, dq);
+}
+
 // KR > 0: the epilogue keeps each query's top-k in KR REGISTER slots (k <= KR); KR == 0: in shared memory.
 // While the tensor pipe runs, tcgen05.mma operand fetch takes ~3/4 of the SM's shared-memory bandwidth
 // (48 KB per 128x256x64 block every ~520 cycles), and an epilogue LDS/STS queues behind it for hundreds
@@ -252,6 +271,9 @@ __device__ __forceinline__ float exact_score(const MmaArgs &a, uint32_t row, uin
 // ZVB200_MMA_DEBUG=128) — so for small k the pool never touches shared memory.
 // KIND 0: fp16 rows, kind::f16 (64 halves per 128-byte k-block); KIND 1: fp32 rows, kind::tf32 (32 floats);
 // KIND 2: int8 rows, kind::i8 (128 codes).
+// KIND 3: QuantizedInteger L2 through the bf16 shadow operands (aux_kernels.cu: qi8_shadow_*): kind::f16 on bf16,
+// the accumulator is g = (Q0 - s) / nQa up to the margin qi8_shadow_eps — compared with a per-query register like
+// an fp16 inner product, no per-column constants; nominated rows get the exact score from the int8 codes.
 // IM: the int8 score form (5 plain -IP, 6 plain L2, 7 QuantizedInteger L2, 8 QuantizedInteger -IP) as a
 // compile-time constant — as a run-time value the per-column code kept a branch tree and one waited-for load
 // per column (27k-44k cycles per tile); 0 for the other kinds, whose mode stays a run-time argument.
@@ -277,7 +299,7 @@ scan_mma_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
   uint64_t *bars = reinterpret_cast<uint64_t *>(lists + (size_t)kQM * k);     // full[ns] empty[ns] tfull[2] tempty[2]
   uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + 2 * nstage + 4);
   float *colc = reinterpret_cast<float *>((reinterpret_cast<uintptr_t>(tmem_slot + 4) + 15) & ~(uintptr_t)15);  // [2][kBN] per-column constants (float, or float4 for int8)
-  constexpr int kBKe = KIND == 0 ? 64 : KIND == 1 ? 32 : 128;                  // elements per 128-byte k-block
+  constexpr int kBKe = (KIND == 0 || KIND == 3) ? 64 : KIND == 1 ? 32 : 128;   // elements per 128-byte k-block
   const uint32_t bar_full = smem_u32(bars), bar_empty = bar_full + 8 * nstage;
   const uint32_t bar_tfull = bar_empty + 8 * nstage, bar_tempty = bar_tfull + 16;
 
@@ -334,7 +356,7 @@ scan_mma_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
     // ================= MMA issuer =================
     if (lane == 0) {
       constexpr uint32_t idesc = KIND == 0 ? make_idesc_f16(kQM, kBN) : KIND == 1 ? make_idesc_tf32(kQM, kBN)
-                                                                                  : make_idesc_i8(kQM, kBN);
+                                 : KIND == 2 ? make_idesc_i8(kQM, kBN) : make_idesc_bf16(kQM, kBN);
       uint32_t stage = 0, phase = 0;
       for (uint32_t t = 0; t < ntl; ++t) {
         const uint32_t as = t & 1, aphase = (t >> 1) & 1;
@@ -348,7 +370,7 @@ scan_mma_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
           const uint64_t da = make_desc_sw128(sa), db = make_desc_sw128(sb);
 #pragma unroll
           for (uint32_t kk = 0; kk < 4; ++kk) {  // four 32-byte K slices per 128-byte k-block
-            if (KIND == 0) umma_f16(d_tmem, da + 2 * kk, db + 2 * kk, idesc, (kb | kk) != 0);
+            if (KIND == 0 || KIND == 3) umma_f16(d_tmem, da + 2 * kk, db + 2 * kk, idesc, (kb | kk) != 0);
             else if (KIND == 1) umma_tf32(d_tmem, da + 2 * kk, db + 2 * kk, idesc, (kb | kk) != 0);
             else umma_i8(d_tmem, da + 2 * kk, db + 2 * kk, idesc, (kb | kk) != 0);
           }
@@ -363,15 +385,21 @@ scan_mma_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
     const int ew = warp - 4;
     const int slot = ew * 32 + lane;
     const bool qvalid = q0 + slot < a.nq;
-    u64 *L = lists + slot;  // entry i at L[i * kQM]: lanes of a warp hit consecutive banks
+    // entry i of the query in lane l of this warp lives at lists[i * 128 + ew * 32 + (l ^ (i & 31))]: for a fixed i the
+    // 32 lanes (one query each) hit 32 different banks, and so do 32 consecutive entries of ONE query — the whole warp
+    // can rescan a single query's pool (accept_coop below) as well as every lane its own
+    u64 *Lw = lists + ew * 32;
+#define ZVB_POOL(i) Lw[(size_t)(i) * kQM + (lane ^ ((i) & 31))]
     // int8: the column value is MINUS the exact score, so the rest of the epilogue runs as mode 0 (s = -value)
-    const int mode = KIND == 2 ? 0 : a.mode;
+    const int mode = (KIND == 2 || KIND == 3) ? 0 : a.mode;
+    constexpr bool SH = KIND == 3;
     constexpr int imode = IM;
     const int K = (int)k;
     // The pool is UNSORTED: the k smallest keys accepted so far, with the position of the largest
     // cached.  Accepting a key replaces the largest and rescans the pool for the new one — k
-    // independent shared-memory loads, instead of the dependent load/compare/store chain of a
-    // sorted insertion (ailego Heap::emplace, heap.h:103-115, keeps a heap for the same reason).
+    // independent shared-memory loads (spread over the warp, accept_coop), instead of the dependent
+    // load/compare/store chain of a sorted insertion (ailego Heap::emplace, heap.h:103-115, keeps a heap
+    // for the same reason).
     // The partial lists leave unsorted; merge_parts does not need order.
     int cnt = 0, maxpos = 0;
     // KR > 0: R[] ascending; the KR - k slots in front hold 0 (never displaced), the rest start at kMaxKey.
@@ -402,7 +430,7 @@ scan_mma_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
     // ---- int8: per-thread query constants and the per-column score, the formulas of K1 (scan_gemv.cu) ----
     const bool ic4 = KIND == 2 && IM != 5;  // per-row constants, always staged (unconditional loads in the hot loop): {|x|^2 as int} (plain L2), the row tail or its filter form (QuantizedInteger), zeros (plain -IP)
     float4 *colc4 = reinterpret_cast<float4 *>(colc);
-    const float4 qt = (KIND == 2 && imode >= 7 && qvalid) ? a.qtails[q0 + slot] : make_float4(0, 0, 0, 0);
+    const float4 qt = (((KIND == 2 && imode >= 7) || SH) && qvalid) ? a.qtails[q0 + slot] : make_float4(0, 0, 0, 0);
     const float dq = (float)a.d;
     int qq_i = 0;
     if (KIND == 2 && imode == 6 && qvalid) {
@@ -418,7 +446,8 @@ scan_mma_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
     const float qsum = qt.x * qt.z, qsum2 = qt.x * qt.x * qt.w;  // qa*qs, qa*qa*qs2
     const float nQ1 = 2.0f * (qt.y * dq + qsum), nQ2 = 2.0f * qt.y, nQa = 2.0f * qt.x;
     const float Q0 = qsum2 + qt.y * qt.y * dq + 2.0f * qt.y * qsum;
-    const float Mthr = kEpsQ * (qsum2 + qt.y * qt.y * dq);
+    const float Mthr = (SH ? qi8_shadow_eps(a.d) : kEpsQ) * (qsum2 + qt.y * qt.y * dq);
+    const float inv_nQa = 1.0f / nQa;
     auto ival = [&](uint32_t raw, const float4 c4) -> float {  // = -score
       const int ip = (int)raw;
       if (imode == 5) return (float)ip;
@@ -463,6 +492,11 @@ scan_mma_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
       if (!qvalid) return __int_as_float(0x7f800000);
       const float tau_f = unorder_f32((uint32_t)(tk >> 32));
       if (KIND == 2 && imode == 7) return Q0 - tau_f - Mthr - (fabsf(Q0) + fabsf(tau_f)) * 4.8e-7f;
+      if (SH) {  // the accumulator is (Q0 - s) / nQa within the margin: a candidate iff it reaches (Q0 - tau - margin) / nQa
+        const float x = Q0 - tau_f - Mthr - (fabsf(Q0) + fabsf(tau_f) + Mthr) * 4.8e-7f;
+        const float y = x * inv_nQa;
+        return y - fabsf(y) * 4.8e-7f;
+      }
       if (root6) return -(tau_f * tau_f * 1.000001f);  // a superset; the candidate's own root decides
       if (mode == 0) return -tau_f;
       if (mode == 1) {
@@ -495,21 +529,81 @@ scan_mma_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
         if (nt < tau_key) { tau_key = nt; dthr = dthr_of(nt); }
         return;
       }
-      if (cnt < K) {
-        L[(size_t)cnt * kQM] = key;
-        if (++cnt < K) return;
-      } else {
-        L[(size_t)maxpos * kQM] = key;
+    };
+    // k > 16: the pool is in shared memory.  Warp-collective: `p` lanes accept their `key` one after the other; the
+    // accepting lane stores (appends, or replaces its pool's largest), then ALL 32 lanes rescan that one pool for the
+    // new largest — 4 loads per lane and a shuffle arg-max instead of k dependent loads by a single lane while 31 idle
+    // (measured: 1900 cycles per accepted candidate at k = 100 before, the largest share of the k = 100 epilogue).
+    auto accept_coop = [&](bool p, u64 key) {
+      // filling a pool needs no rescan until its last slot: those lanes append on their own, in parallel (in the
+      // first tiles every lane accepts every column; one at a time that alone cost 4M cycles)
+      if (p && cnt + 1 < K) {
+        ZVB_POOL(cnt) = key;
+        ++cnt;
+        p = false;
       }
-      u64 mx = 0;
-      int mp = 0;
-#pragma unroll 16
-      for (int i = 0; i < K; ++i) {
-        const u64 x = L[(size_t)i * kQM];
-        if (x > mx) { mx = x; mp = i; }
+      uint32_t pb = __ballot_sync(FULL, p);
+      if (__popc(pb) >= 4) {
+        // many lanes at once (early tiles, loose bounds): every lane rescans its own pool, all of them together
+        if (p) {
+          if (cnt < K) { ZVB_POOL(cnt) = key; ++cnt; }  // (the macro evaluates its argument twice)
+          else ZVB_POOL(maxpos) = key;
+          u64 m4[4] = {0, 0, 0, 0};
+          int p4[4] = {0, 0, 0, 0};
+          int i = 0;
+#pragma unroll 4
+          for (; i + 3 < K; i += 4) {
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+              const u64 x = ZVB_POOL(i + u);
+              if (x > m4[u]) { m4[u] = x; p4[u] = i + u; }
+            }
+          }
+          for (; i < K; ++i) {
+            const u64 x = ZVB_POOL(i);
+            if (x > m4[0]) { m4[0] = x; p4[0] = i; }
+          }
+          if (m4[1] > m4[0]) { m4[0] = m4[1]; p4[0] = p4[1]; }
+          if (m4[3] > m4[2]) { m4[2] = m4[3]; p4[2] = p4[3]; }
+          if (m4[2] > m4[0]) { m4[0] = m4[2]; p4[0] = p4[2]; }
+          maxpos = p4[0];
+          if (m4[0] < tau_key) { tau_key = m4[0]; dthr = dthr_of(m4[0]); }
+        }
+        return;
       }
-      maxpos = mp;
-      if (mx < tau_key) { tau_key = mx; dthr = dthr_of(mx); }
+      while (pb) {
+        const int src = __ffs(pb) - 1;
+        pb &= pb - 1;
+        bool rescan = false;
+        if (lane == src) {
+          if (cnt < K) {
+            ZVB_POOL(cnt) = key;
+            rescan = ++cnt == K;
+          } else {
+            ZVB_POOL(maxpos) = key;
+            rescan = true;
+          }
+        }
+        rescan = __shfl_sync(FULL, (int)rescan, src) != 0;
+        if (!rescan) continue;
+        __syncwarp();
+        u64 mx = 0;
+        int mp = 0;
+        for (int i = lane; i < K; i += 32) {  // i & 31 == lane: entry i of lane src's query
+          const u64 x = Lw[(size_t)i * kQM + (src ^ lane)];
+          if (x > mx) { mx = x; mp = i; }
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+          const u64 ox = __shfl_xor_sync(FULL, mx, o);
+          const int op = __shfl_xor_sync(FULL, mp, o);
+          if (ox > mx) { mx = ox; mp = op; }
+        }
+        if (lane == src) {
+          maxpos = mp;
+          if (mx < tau_key) { tau_key = mx; dthr = dthr_of(mx); }
+        }
+      }
     };
     auto publish = [&]() {  // score word of this CTA's pub_j-th best, once it has that many rows
       uint32_t pv = 0xffffffffu;
@@ -522,13 +616,13 @@ scan_mma_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
       } else if (cnt < pubj) {
         return;
       } else if (pubj == K) {
-        pv = (uint32_t)(L[(size_t)maxpos * kQM] >> 32);
+        pv = (uint32_t)(ZVB_POOL(maxpos) >> 32);
       } else {           // pub_j <= 8: the pub_j-th smallest score word of the pool
         uint32_t sel[8];
 #pragma unroll
         for (int i = 0; i < 8; ++i) sel[i] = 0xffffffffu;
         for (int e = 0; e < cnt; ++e) {
-          uint32_t x = (uint32_t)(L[(size_t)e * kQM] >> 32);
+          uint32_t x = (uint32_t)(ZVB_POOL(e) >> 32);
 #pragma unroll
           for (int i = 0; i < 8; ++i) {
             const uint32_t lo = min(sel[i], x);
@@ -572,7 +666,7 @@ scan_mma_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
     };
     uint32_t next_eval = 1;
     // the first-tile bootstrap needs every row of that tile to be a live row
-    const bool boot = !(KIND == 2 && imode == 7) && a.groups > 1 && pubj <= 8 && !a.drop && !a.filter && ntl > 1 &&
+    const bool boot = !(KIND == 2 && imode == 7) && !SH && a.groups > 1 && pubj <= 8 && !a.drop && !a.filter && ntl > 1 &&
                       a.row_begin + (t_begin + 1) * kBN <= a.row_end && !(a.dbg & (1 | 16 | 32 | 64));
     const int etid = ew * 32 + lane;
     if (resc || ic4) {
@@ -587,7 +681,7 @@ scan_mma_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
       asm volatile("bar.sync 1, 128;" ::: "memory");
     }
     const bool prof = (a.dbg & 128) != 0;  // triage: where the epilogue's cycles go (printed by CTA 0)
-    long long c_wait = 0, c_slow = 0, c_ub = 0, c_t0 = 0, c_first4 = 0, c_tiles = 0;
+    long long c_wait = 0, c_slow = 0, c_ub = 0, c_t0 = 0, c_first4 = 0, c_tiles = 0, c_ex = 0, c_acc = 0, c_ld1 = 0;
     uint32_t n_slow = 0, n_ev = 0;
     const long long c_begin = prof ? clock64() : 0;
 
@@ -684,13 +778,23 @@ scan_mma_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
 #pragma unroll
           for (int j = 0; j < 32; ++j) m |= (__uint_as_float(v[j]) >= dthr ? 1u : 0u) << j;
           uint32_t wm = __reduce_or_sync(FULL, m);
+          if (SH) {  // the int8 rows of the nominated columns: start their trips from HBM together
+            for (uint32_t pm = wm; pm; pm &= pm - 1) {
+              const uint32_t prow = row0 + c0 + (__ffs(pm) - 1);
+              if (prow < a.row_end && (uint32_t)lane < a.chunks)
+                asm volatile("prefetch.global.L2 [%0];" ::"l"(a.rows + (size_t)prow * a.row_stride + (size_t)lane * 16));
+              if (prow < a.row_end && lane == 31) asm volatile("prefetch.global.L2 [%0];" ::"l"(a.tails + prow));
+            }
+          }
           while (wm) {
             const int j = __ffs(wm) - 1;
             wm &= wm - 1;
             if (prof) ++n_ev;
             // the column again, straight from TMEM (collective, warp-uniform address): indexing v[] with a
             // run-time j would cost a branch tree or local memory
+            const long long c0l = prof ? clock64() : 0;
             const uint32_t raw = tmem_ld1(taddr + c0 + j);
+            if (prof) c_ld1 += clock64() - c0l;
             const uint32_t row = row0 + c0 + j;
             const float dv = KIND == 2 ? ival(raw, cc4[c0 + j])
                                        : __uint_as_float(raw) + (resc ? cc[c0 + j] : 0.f);
@@ -699,6 +803,43 @@ scan_mma_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
             if (root6) s = sqrtf(s);
             if (KIND == 2 && imode == 7) {  // the filter nominated it: the exact reference-order score
               if (cand) s = qi8_l2sq((float)(int)raw, a.tails[row], qt, dq);
+            }
+            const long long c0e = prof ? clock64() : 0;
+            if (SH) {
+              // the exact score from the int8 codes.  The row is the same for every nominating lane: with few of
+              // them the warp fetches it ONCE (lane c holds chunk c: one HBM round trip instead of a serial walk by a
+              // single lane) and scores one query at a time; with many (the first tiles) each lane scores its own.
+              uint32_t cb = __ballot_sync(FULL, cand);
+              if (__popc(cb) >= 8) {
+                if (cand) s = exact_qi8_l2(a, row, q0 + slot, qt, dq);
+              } else if (cb) {
+                const uint4 *rp = reinterpret_cast<const uint4 *>(a.rows + (size_t)row * a.row_stride);
+                uint4 rx[3];
+#pragma unroll
+                for (int u = 0; u < 3; ++u) {
+                  const uint32_t c = lane + 32 * u;
+                  rx[u] = c < a.chunks ? __ldg(rp + c) : make_uint4(0, 0, 0, 0);
+                }
+                const float4 mt = a.tails[row];
+                while (cb) {
+                  const int src = __ffs(cb) - 1;
+                  cb &= cb - 1;
+                  const uint4 *qp = reinterpret_cast<const uint4 *>(a.qraw + (size_t)(q0 + ew * 32 + src) * a.row_stride);
+                  int ip = 0;
+#pragma unroll
+                  for (int u = 0; u < 3; ++u) {
+                    const uint32_t c = lane + 32 * u;
+                    if (c < a.chunks) {
+                      const uint4 y = __ldg(qp + c);
+                      ip = __dp4a((int)rx[u].x, (int)y.x, ip); ip = __dp4a((int)rx[u].y, (int)y.y, ip);
+                      ip = __dp4a((int)rx[u].z, (int)y.z, ip); ip = __dp4a((int)rx[u].w, (int)y.w, ip);
+                    }
+                  }
+#pragma unroll
+                  for (int o = 16; o > 0; o >>= 1) ip += __shfl_xor_sync(FULL, ip, o);
+                  if (lane == src) s = qi8_l2sq((float)ip, mt, qt, dq);
+                }
+              }
             }
             if (resc) {
               // the accumulator only nominated the row: its score is recomputed exactly, by the whole warp,
@@ -711,14 +852,18 @@ scan_mma_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
                 if (lane == src) s = e;
               }
             }
-            if (cand) {
+            const long long c0a = prof ? clock64() : 0;
+            if (prof) c_ex += c0a - c0e;
+            {
               const u64 key = pack_key(s, row);
-              bool p = key < tau_key && row < a.row_end;
+              bool p = cand && key < tau_key && row < a.row_end;
               if (p && a.drop) p = !bit_set(a.drop, row);
               if (p && a.filter) p = !bit_set(a.filter, row);
-              if (p) accept(key);
+              if (KR > 0) { if (p) accept(key); }
+              else accept_coop(p, key);
             }
             __syncwarp();
+            if (prof) c_acc += clock64() - c0a;
           }
           if (prof) c_slow += clock64() - c0s;
         }
@@ -772,8 +917,8 @@ scan_mma_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
       }
     }
     if (prof && blockIdx.x == 0 && lane == 0)
-      printf("cta0 warp%d: total %lld  wait %lld  slow %lld (%u chunks, %u column events)  union %lld  tile0 %lld  first4 %lld  all tiles %lld (%u)\n",
-             warp, clock64() - c_begin, c_wait, c_slow, n_slow, n_ev, c_ub, c_t0, c_first4, c_tiles, ntl);
+      printf("cta0 warp%d: total %lld  wait %lld  slow %lld (%u chunks, %u column events: tmem re-read %lld, exact %lld, accept %lld)  union %lld  tile0 %lld  first4 %lld  all tiles %lld (%u)\n",
+             warp, clock64() - c_begin, c_wait, c_slow, n_slow, n_ev, c_ld1, c_ex, c_acc, c_ub, c_t0, c_first4, c_tiles, ntl);
     // write this CTA's partial lists (unsorted): part[q][grp][0..k)
     if (qvalid) {
       u64 *dst = a.part + ((size_t)(q0 + slot) * a.groups + grp) * k;
@@ -782,7 +927,7 @@ scan_mma_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
         for (int i = 0; i < KR; ++i)
           if (i >= rfirst) dst[i - rfirst] = R[i];
       } else {
-        for (int i = 0; i < K; ++i) dst[i] = i < cnt ? L[(size_t)i * kQM] : kMaxKey;
+        for (int i = 0; i < K; ++i) dst[i] = i < cnt ? ZVB_POOL(i) : kMaxKey;
       }
     }
   }
@@ -840,10 +985,18 @@ bool mma_config(uint32_t k, size_t colc_bytes, uint32_t *nstage, size_t *smem) {
   return false;
 }
 
+#undef ZVB_POOL
+
 }  // namespace
 
 // bytes of per-column constants the epilogue stages in shared memory for this store type
-static size_t colc_bytes_for(const RowsView &rv) {
+static bool use_shadow(const RowsView &rv) {
+  static const bool off = [] { const char *e = getenv("ZVB200_QI8_SHADOW"); return e && atoi(e) == 0; }();
+  return !off && rv.dtype == ZVB200_DT_INT8 && rv.metric == ZVB200_METRIC_QI8_L2SQ && rv.shadow && rv.tails;
+}
+
+static size_t colc_bytes_for(const RowsView &rv, bool shadow = false) {
+  if (shadow) return 0;
   if (rv.dtype == ZVB200_DT_INT8) return 2 * kBN * sizeof(float4);
   const bool direct = rv.dtype == ZVB200_DT_FP16 && !metric_is_l2(rv.metric);
   return direct ? 0 : 2 * kBN * sizeof(float);
@@ -873,9 +1026,10 @@ size_t scan_mma_max_parts(int sm_count) { return (size_t)sm_count; }
 
 cudaError_t launch_scan_mma(const RowsView &rv, const QueryView &qv, const SearchParams &sp,
                             uint64_t row_begin, uint64_t row_end, u64 *part, uint32_t *nparts,
-                            uint32_t *pub, int sm_count, cudaStream_t st) {
+                            uint32_t *pub, int sm_count, cudaStream_t st, int *kind_out) {
   uint32_t ns; size_t smem;
-  if (!mma_config(sp.k, colc_bytes_for(rv), &ns, &smem)) return cudaErrorInvalidValue;
+  const bool sh = use_shadow(rv) && qv.qshadow && !sp.no_shadow;
+  if (!mma_config(sp.k, colc_bytes_for(rv, sh), &ns, &smem)) return cudaErrorInvalidValue;
   const uint64_t nrows = row_end > row_begin ? row_end - row_begin : 0;
   MmaArgs a;
   a.nq = qv.q;
@@ -884,9 +1038,9 @@ cudaError_t launch_scan_mma(const RowsView &rv, const QueryView &qv, const Searc
   a.ntiles = (uint32_t)((nrows + kBN - 1) / kBN);
   a.groups = std::max<uint32_t>(1, std::min<uint32_t>((uint32_t)sm_count / a.qtiles, std::max<uint32_t>(a.ntiles, 1)));
   const bool f32 = rv.dtype == ZVB200_DT_FP32, i8 = rv.dtype == ZVB200_DT_INT8;
-  const int kind = f32 ? 1 : i8 ? 2 : 0;
-  const uint32_t bke = f32 ? 32 : i8 ? 128 : 64;
-  a.nkb = (rv.d + bke - 1) / bke;
+  const int kind = f32 ? 1 : sh ? 3 : i8 ? 2 : 0;
+  const uint32_t bke = f32 ? 32 : sh ? 64 : i8 ? 128 : 64;
+  a.nkb = sh ? rv.shadow_k / 64 : (rv.d + bke - 1) / bke;
   a.k = sp.k; a.nstage = ns;
   a.row_begin = (uint32_t)row_begin; a.row_end = (uint32_t)row_end;
   const bool l2 = metric_is_l2(rv.metric);
@@ -918,20 +1072,28 @@ cudaError_t launch_scan_mma(const RowsView &rv, const QueryView &qv, const Searc
     a.dbg = dbg;
   }
   *nparts = a.groups;
+  if (kind_out) *kind_out = kind;
   CUtensorMap tmQ, tmX;
   // the caller pads qraw with zero rows up to a whole tile when this is the last group of the batch
   const uint64_t qrows = qv.qpad_rows ? (uint64_t)a.qtiles * kQM : qv.q;
-  if (f32) {
+  if (sh) {
+    if (!make_map(&tmQ, qv.qshadow, 0, rv.shadow_k, qrows, rv.shadow_k * 2, kQM)) return cudaErrorInvalidValue;
+  } else if (f32) {
     if (!make_map(&tmQ, qv.qf32, 1, rv.d, qrows, a.qstride * 4, kQM)) return cudaErrorInvalidValue;
   } else {
     if (!make_map(&tmQ, qv.qraw, kind, rv.d, qrows, rv.row_stride, kQM)) return cudaErrorInvalidValue;
   }
-  if (!make_map(&tmX, rv.rows + row_begin * rv.row_stride, kind, rv.d, std::max<uint64_t>(nrows, 1), rv.row_stride, kBN))
+  if (sh) {
+    if (!make_map(&tmX, rv.shadow + row_begin * rv.shadow_k * 2, 0, rv.shadow_k, std::max<uint64_t>(nrows, 1),
+                  rv.shadow_k * 2, kBN))
+      return cudaErrorInvalidValue;
+  } else if (!make_map(&tmX, rv.rows + row_begin * rv.row_stride, kind, rv.d, std::max<uint64_t>(nrows, 1), rv.row_stride, kBN))
     return cudaErrorInvalidValue;
   typedef void (*KernFn)(const CUtensorMap, const CUtensorMap, const MmaArgs);
 #define ZVB_MMA_KR(KIND, IM) \
   (sp.k <= 8 ? (KernFn)scan_mma_kernel<KIND, 8, IM> : sp.k <= 16 ? (KernFn)scan_mma_kernel<KIND, 16, IM> : (KernFn)scan_mma_kernel<KIND, 0, IM>)
   KernFn kern = f32 ? ZVB_MMA_KR(1, 0)
+                : sh ? ZVB_MMA_KR(3, 0)
                 : !i8 ? ZVB_MMA_KR(0, 0)
                 : a.mode == 5 ? ZVB_MMA_KR(2, 5)
                 : a.mode == 6 ? ZVB_MMA_KR(2, 6)
