@@ -243,6 +243,24 @@ int zvb200_search_refined(zvb200_ctx *coarse, zvb200_ctx *exact, const float *qu
                           uint64_t *out_keys, float *out_scores, uint32_t *out_index,
                           uint32_t *out_counts);
 
+/* ---- k-means: replaces KmeansCluster::cluster + label (src/core/algorithm/cluster/
+ * kmeans_cluster.cc:469-535, 571-610) as IVFBuilder trains its centroids with (ivf_builder.cc:442-485).
+ * rows: n x dim fp32 (HOST for zvb200_kmeans, DEVICE for zvb200_kmeans_device).  centroids: k x dim fp32 HOST,
+ * the initial centroids going in (the caller samples them, KmeansCluster::init_centroids is a reservoir sample
+ * of the rows), the trained ones coming out.  Each iteration assigns every row to its nearest centroid under
+ * `metric` (ZVB200_METRIC_L2SQ / L2 / IP; the strict '<' of LinearSeeker::seek, linear_seeker.cc:29-37 = the
+ * lower centroid wins a tie), accumulates per-cluster sums in double and sets centroid = (float)(sum / count)
+ * (vector_mean.h:204-226; an empty cluster becomes NaN and is never chosen again, as there).  Stops after
+ * max_iterations or when |cost - previous cost| < epsilon (kmeans_cluster.cc:519-529).  Optional outputs:
+ * labels[n] = nearest of the RETURNED centroids (label()), follows[k] = rows per cluster and *sse = cost of the
+ * last assignment pass, *iterations = passes run.  Nothing is purged. */
+int zvb200_kmeans(int device, int metric, const float *rows, uint64_t n, uint32_t dim, float *centroids,
+                  uint32_t k, uint32_t max_iterations, double epsilon, uint32_t *labels, uint64_t *follows,
+                  double *sse, uint32_t *iterations);
+int zvb200_kmeans_device(int device, int metric, const float *rows_dev, uint64_t n, uint32_t dim,
+                         float *centroids, uint32_t k, uint32_t max_iterations, double epsilon,
+                         uint32_t *labels, uint64_t *follows, double *sse, uint32_t *iterations);
+
 #ifdef __cplusplus
 }
 #endif

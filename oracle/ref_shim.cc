@@ -15,6 +15,8 @@
 #include <thread>
 #include <vector>
 #include <zvec/core/framework/index_builder.h>
+#include <zvec/core/framework/index_cluster.h>
+#include <zvec/core/framework/index_features.h>
 #include <zvec/core/framework/index_converter.h>
 #include <zvec/core/framework/index_factory.h>
 #include <zvec/core/framework/index_holder.h>
@@ -527,6 +529,49 @@ int zref_metric_distances(const char *metric, const char *origin_metric, int dty
   if (!f) return fail(-12, "no distance");
   size_t es = meta.element_size();
   for (uint64_t i = 0; i < n; ++i) f((const char *)m + i * es, q, dim, out + i);
+  return 0;
+}
+
+// The reference's k-means (KmeansCluster::cluster / label, src/core/algorithm/cluster/kmeans_cluster.cc:469-535,
+// 571-610) on caller rows from caller centroids: `centroids` holds k initial centroids going in and the
+// updated ones coming out (an empty cluster's mean is 0/0 = NaN, vector_mean.h:217-226; nothing is purged);
+// follows[k] = rows per cluster and *sse = the cost of the LAST clustering pass; labels[n] = label() against the
+// returned centroids.  Returns 0 or a negative IndexError.
+int zref_kmeans(const char *metric, const float *rows, uint64_t n, uint32_t dim, float *centroids, uint32_t k,
+                uint32_t max_iterations, uint32_t threads, uint32_t *labels, uint64_t *follows, double *sse) {
+  IndexMeta meta(IndexMeta::DT_FP32, dim);
+  meta.set_metric(metric, 0, Params());
+  auto cl = IndexFactory::CreateCluster("KmeansCluster");
+  if (!cl) return fail(-1, "no KmeansCluster");
+  Params p;
+  p.set("proxima.kmeans.cluster.max_iterations", max_iterations);
+  p.set("proxima.general.cluster.thread_count", threads ? threads : 1u);
+  p.set("proxima.kmeans.cluster.purge_empty", false);
+  p.set("proxima.kmeans.cluster.epsilon", 0.0);
+  int r = cl->init(meta, p);
+  if (r != 0) return fail(r, "cluster init");
+  auto feats = std::make_shared<CoherentIndexFeatures>(meta, rows, (size_t)n * dim * sizeof(float));
+  r = cl->mount(feats);
+  if (r != 0) return fail(r, "cluster mount");
+  IndexCluster::CentroidList cents;
+  for (uint32_t c = 0; c < k; ++c) cents.emplace_back(centroids + (size_t)c * dim, (size_t)dim * sizeof(float));
+  r = cl->cluster(cents);
+  if (r != 0) return fail(r, "cluster");
+  if (cents.size() != k) return fail(-1, "centroids were purged");
+  double total = 0.0;
+  for (uint32_t c = 0; c < k; ++c) {
+    std::memcpy(centroids + (size_t)c * dim, cents[c].buffer().data(), (size_t)dim * sizeof(float));
+    if (follows) follows[c] = cents[c].follows();
+    total += cents[c].score();
+  }
+  if (sse) *sse = total;
+  if (labels) {
+    std::vector<uint32_t> out;
+    r = cl->label(cents, &out);
+    if (r != 0) return fail(r, "label");
+    std::memcpy(labels, out.data(), (size_t)n * sizeof(uint32_t));
+  }
+  cl->cleanup();
   return 0;
 }
 

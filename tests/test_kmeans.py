@@ -1,0 +1,133 @@
+"""k-means on the device against the reference's KmeansCluster (compiled from its own sources,
+oracle/_ref) and the numpy restatement oracle/kmeans_oracle.py.  Sums are accumulated in double on all three
+sides, so the centroids agree to fp32 rounding as long as the assignments agree; rows whose two nearest
+centroids are closer than 1e-4 relative are near-ties and may be assigned either way."""
+import ctypes as C
+import os
+import sys
+
+import numpy as np
+import pytest
+
+import support as S
+
+sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), "..", "oracle"))
+import kmeans_oracle as KO  # noqa: E402
+
+
+def _data(n, d, k, seed, spread=0.5):
+    rng = np.random.default_rng(seed)
+    centres = rng.standard_normal((k, d)).astype(np.float32)
+    x = (centres[rng.integers(0, k, n)] + spread * rng.standard_normal((n, d))).astype(np.float32)
+    init = x[rng.choice(n, k, replace=False)].copy()
+    return x, init
+
+
+def _ref_kmeans(metric_name, x, init, iters, threads=4):
+    L = S.ref()
+    L.zref_kmeans.argtypes = [C.c_char_p, C.c_void_p, C.c_uint64, C.c_uint32, C.c_void_p, C.c_uint32, C.c_uint32,
+                              C.c_uint32, C.c_void_p, C.c_void_p, C.POINTER(C.c_double)]
+    n, d = x.shape
+    k = len(init)
+    cent = init.copy()
+    lab = np.zeros(n, np.uint32); fol = np.zeros(k, np.uint64); sse = C.c_double()
+    rc = L.zref_kmeans(metric_name.encode(), x.ctypes.data, n, d, cent.ctypes.data, k, iters, threads,
+                       lab.ctypes.data, fol.ctypes.data, C.byref(sse))
+    assert rc == 0, L.zref_last_error()
+    return cent, lab, fol, sse.value
+
+
+def _near_tie_rows(d, rtol=1e-4):
+    part = np.partition(d, 1, axis=1)
+    return (part[:, 1] - part[:, 0]) <= rtol * np.maximum(np.abs(part[:, 1]), 1e-6)
+
+
+needs_ref = pytest.mark.skipif(S.ref() is None, reason="oracle/_ref not built")
+
+
+@needs_ref
+@pytest.mark.parametrize("iters", [1, 4])
+def test_oracle_kmeans_equals_the_reference(iters):
+    x, init = _data(6000, 24, 16, 3)
+    rc, rl, rf, rs = _ref_kmeans("SquaredEuclidean", x, init, iters)
+    oc, ol, of, os_, d = KO.kmeans(x, init, iters)
+    ties = _near_tie_rows(d)
+    assert np.array_equal(rl[~ties], ol[~ties])
+    assert np.allclose(rc, oc, rtol=1e-5, atol=1e-6, equal_nan=True)
+    assert np.array_equal(rf, of) or ties.any()
+    assert abs(rs - os_) <= 1e-5 * abs(rs)
+
+
+def test_oracle_kmeans_empty_cluster_is_nan():
+    x, init = _data(500, 8, 4, 4)
+    init[3] = 1e6                                   # nobody's nearest centroid
+    c, cnt, cost, lab, _ = KO.lloyd_pass(x, init)
+    assert cnt[3] == 0 and np.isnan(c[3]).all() and not np.isnan(c[:3]).any()
+    c2, cnt2, _, _, _ = KO.lloyd_pass(x, c)         # a NaN centroid is never chosen again
+    assert cnt2[3] == 0
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("n,d,k,iters", [(20000, 32, 64, 1), (20000, 32, 64, 5), (5000, 100, 7, 3), (70000, 16, 300, 2)])
+def test_gpu_kmeans_equals_oracle_and_reference(n, d, k, iters):
+    import zvec_b200 as z
+    x, init = _data(n, d, k, 10 + k)
+    gc, gl, gf, gs, git = z.kmeans(x, init, max_iterations=iters, epsilon=0.0)
+    assert git == iters
+    oc, ol, of, os_, dmat = KO.kmeans(x, init, iters)
+    ties = _near_tie_rows(dmat)
+    assert ties.mean() < 0.01
+    assert np.array_equal(gl[~ties], ol[~ties])
+    # identical assignments in every pass <=> identical follows; then the centroids agree to fp32 rounding
+    if np.array_equal(gf, of):
+        assert np.allclose(gc, oc, rtol=1e-5, atol=1e-6, equal_nan=True)
+    else:
+        assert np.abs(gf.astype(np.int64) - of.astype(np.int64)).sum() <= 4 * max(1, int(ties.sum()))
+        assert np.allclose(gc, oc, rtol=1e-2, atol=1e-3, equal_nan=True)
+    assert abs(gs - os_) <= 1e-4 * abs(os_)
+    if S.ref() is not None:
+        rc, rl, rf, rs = _ref_kmeans("SquaredEuclidean", x, init, iters)
+        assert np.array_equal(gl[~ties], rl[~ties])
+        if np.array_equal(gf, rf):
+            assert np.allclose(gc, rc, rtol=1e-5, atol=1e-6, equal_nan=True)
+        assert abs(gs - rs) <= 1e-4 * abs(rs)
+
+
+@pytest.mark.gpu
+def test_gpu_kmeans_empty_cluster_nan_and_epsilon_stop():
+    import zvec_b200 as z
+    x, init = _data(4000, 8, 4, 21)
+    init[3] = 1e6
+    gc, gl, gf, gs, git = z.kmeans(x, init, max_iterations=2, epsilon=0.0)
+    assert gf[3] == 0 and np.isnan(gc[3]).all() and not np.isnan(gc[:3]).any()
+    assert (gl != 3).all()
+    oc, ol, of, os_, _ = KO.kmeans(x, init, 2)
+    assert np.array_equal(gf, of) and np.allclose(gc, oc, rtol=1e-5, atol=1e-6, equal_nan=True)
+    # a huge epsilon stops after the second pass (the first compares with cost 0, kmeans_cluster.cc:510-529)
+    _, _, _, _, it2 = z.kmeans(x, init, max_iterations=20, epsilon=1e30)
+    assert it2 == 1
+
+
+@pytest.mark.gpu
+def test_gpu_kmeans_feeds_the_gpu_ivf_index():
+    """train on the device, group the rows by label, attach: the IVF search then finds each row in its own list"""
+    import zvec_b200 as z
+    n, d, k = 30000, 32, 64
+    x, init = _data(n, d, k, 33, spread=0.3)
+    cent, lab, fol, _, _ = z.kmeans(x, init, max_iterations=8, epsilon=0.0)
+    fol = np.bincount(lab, minlength=k)              # list sizes under label() (follows is the last pass's)
+    keep = fol > 0                                   # IVFBuilder drops empty clusters (purge)
+    remap = np.cumsum(keep) - 1
+    order = np.argsort(lab, kind="stable")
+    offs = np.zeros(int(keep.sum()) + 1, np.uint64)
+    offs[1:] = np.cumsum(fol[keep])
+    st = z.Store(z.DT_FP32, z.METRIC_L2SQ, d)
+    st.append(x[order], order.astype(np.uint64)); st.seal()
+    st.ivf_attach(cent[keep], offs)
+    ctx = z.Context(st)
+    qs = x[:200]
+    keys, scores, index, counts = ctx.ivf_search(qs, 1, 1, n)        # 1 probe: the row's own list
+    assert (counts == 1).all()
+    assert (keys[:, 0] == np.arange(200)).mean() > 0.99 and (scores[:, 0] <= 1e-6).mean() > 0.99
+    assert np.array_equal(remap[lab[:200]], np.searchsorted(offs, index[:, 0].astype(np.uint64), side="right") - 1)
+    ctx.close(); st.close()

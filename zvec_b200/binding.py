@@ -75,6 +75,10 @@ _SIGS = {
                                      C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     "zvb200_search_refined": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32,
                                         C.c_float, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "zvb200_kmeans": (C.c_int, [C.c_int, C.c_int, C.c_void_p, C.c_uint64, C.c_uint32, C.c_void_p, C.c_uint32, C.c_uint32,
+                                C.c_double, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "zvb200_kmeans_device": (C.c_int, [C.c_int, C.c_int, C.c_void_p, C.c_uint64, C.c_uint32, C.c_void_p, C.c_uint32,
+                                       C.c_uint32, C.c_double, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
 }
 
 
@@ -352,3 +356,26 @@ def distance_matrix(metric, dtype, dim, rows, queries, device=0):
     out = np.empty((nq, n), np.float32)
     _check(lib().zvb200_distance_matrix(device, metric, dtype, dim, _ptr(rows), n, _ptr(queries), nq, _ptr(out)))
     return out
+
+
+def kmeans(rows, centroids, metric=None, max_iterations=20, epsilon=float(np.finfo(np.float32).eps), device=0,
+           rows_device_ptr=None, n=None):
+    """Lloyd iterations on the device (zvb200_kmeans): rows [n, dim] fp32 (or a device pointer + n), centroids [k, dim]
+    fp32 = the initial centroids.  -> (centroids, labels u32[n], follows u64[k], sse, iterations)"""
+    cent = np.ascontiguousarray(centroids, np.float32).copy()
+    k, dim = cent.shape
+    metric = METRIC_L2SQ if metric is None else metric
+    if rows_device_ptr is None:
+        rows = np.ascontiguousarray(rows, np.float32)
+        n = rows.shape[0]
+    labels = np.zeros(n, np.uint32)
+    follows = np.zeros(k, np.uint64)
+    sse = C.c_double()
+    iters = C.c_uint32()
+    if rows_device_ptr is None:
+        _check(lib().zvb200_kmeans(device, metric, _ptr(rows), n, dim, _ptr(cent), k, max_iterations, epsilon,
+                                   _ptr(labels), _ptr(follows), C.addressof(sse), C.addressof(iters)))
+    else:
+        _check(lib().zvb200_kmeans_device(device, metric, rows_device_ptr, n, dim, _ptr(cent), k, max_iterations, epsilon,
+                                          _ptr(labels), _ptr(follows), C.addressof(sse), C.addressof(iters)))
+    return cent, labels, follows, sse.value, iters.value

@@ -112,6 +112,7 @@ struct zvb200_ctx {
   QueryView last_qv;
   HostBuf h_q, h_scores, h_index;
   int force_kernel = 0;
+  uint32_t mma_group_cap = 0;  // queries per tcgen05 launch (0: ZVB200_MMA_GROUP or 1024)
   int last_mma_kind = -1;
   const char *last_kernel = "none";
   cudaEvent_t ev_scan0 = nullptr, ev_scan1 = nullptr;  // bracket the scan kernel(s) of the last search
@@ -547,7 +548,8 @@ static int search_core(zvb200_ctx *c, zvb200_store *s, const void *queries_dev, 
   // which stays far below the launch's MMA time
   if (which == 3) {
     static const uint32_t cap = [] { const char *e = getenv("ZVB200_MMA_GROUP"); return e ? (uint32_t)atoi(e) : 1024u; }();
-    group = std::min<uint32_t>(group, std::min<uint32_t>(std::max(cap, 128u), (uint32_t)s->sm_count * 128u));
+    const uint32_t want = c->mma_group_cap ? c->mma_group_cap : cap;
+    group = std::min<uint32_t>(group, std::min<uint32_t>(std::max(want, 128u), (uint32_t)s->sm_count * 128u));
   }
   if (group >= 128) group &= ~127u; else if (group >= 64) group &= ~63u; else if (group >= 4) group &= ~3u;
   group = std::min(group, q);
@@ -1064,6 +1066,123 @@ int zvb200_search_refined(zvb200_ctx *coarse, zvb200_ctx *exact, const float *qu
   r = body();
   exact->stream = keep;
   return r;
+}
+
+}  // extern "C"
+
+// ---- k-means on the device: KmeansCluster::cluster / label ---------------------------------
+// (src/core/algorithm/cluster/kmeans_cluster.cc:469-535, 571-610).  A Lloyd iteration = the scan with k = 1
+// over a store of the current centroids (queries = the rows, 18 944 per tcgen05 launch) + the update kernels.
+
+static void store_reset(zvb200_store *s) {
+  std::lock_guard<std::mutex> g(s->mu);
+  s->n = 0; s->normed = 0; s->shadowed = 0;
+  s->keys.clear(); s->drop_host.clear();
+  s->has_drop = false; s->drop_dirty = false; s->sealed = false;
+}
+
+struct KmeansScratch {
+  zvb200_store *cs = nullptr;
+  zvb200_ctx *ctx = nullptr;
+  float *cent = nullptr, *dist = nullptr, *rows_own = nullptr;
+  uint32_t *lab = nullptr;
+  double *sums = nullptr, *scores = nullptr, *sse = nullptr;
+  unsigned long long *counts = nullptr;
+  ~KmeansScratch() {
+    if (ctx) zvb200_ctx_destroy(ctx);
+    if (cs) zvb200_store_destroy(cs);
+    void *p[] = {cent, dist, rows_own, lab, sums, scores, sse, counts};
+    for (void *x : p) if (x) cudaFree(x);
+  }
+};
+
+static int kmeans_core(int device, int metric, const float *rows_dev, const float *rows_host, uint64_t n, uint32_t dim,
+                       float *centroids, uint32_t k, uint32_t max_iterations, double epsilon, uint32_t *labels,
+                       uint64_t *follows, double *sse_out, uint32_t *iterations_out) {
+  if ((!rows_dev && !rows_host) || !centroids || n == 0 || dim == 0 || k == 0)
+    return set_err(ZVB200_ERR_INVALID_ARGUMENT, "kmeans: null or empty argument");
+  if (n >= 0xffffffffull || k >= 0xffffffffu) return set_err(ZVB200_ERR_INVALID_ARGUMENT, "kmeans: too many rows");
+  if (metric != ZVB200_METRIC_L2SQ && metric != ZVB200_METRIC_L2 && metric != ZVB200_METRIC_IP)
+    return set_err(ZVB200_ERR_UNSUPPORTED, "kmeans: fp32 rows with SquaredEuclidean / Euclidean / InnerProduct");
+  KmeansScratch w;
+  int r = zvb200_store_create(device, ZVB200_DT_FP32, metric, dim, &w.cs);
+  if (r == 0) r = zvb200_store_reserve(w.cs, k);
+  if (r == 0) r = zvb200_ctx_create(w.cs, &w.ctx);
+  if (r != 0) return r;
+  CU(cudaSetDevice(device));
+  const size_t cbytes = (size_t)k * dim * sizeof(float);
+  CU(cudaMalloc((void **)&w.cent, cbytes));
+  CU(cudaMalloc((void **)&w.dist, n * sizeof(float)));
+  CU(cudaMalloc((void **)&w.lab, n * sizeof(uint32_t)));
+  CU(cudaMalloc((void **)&w.sums, (size_t)k * dim * sizeof(double)));
+  CU(cudaMalloc((void **)&w.scores, (size_t)k * sizeof(double)));
+  CU(cudaMalloc((void **)&w.counts, (size_t)k * sizeof(unsigned long long)));
+  CU(cudaMalloc((void **)&w.sse, sizeof(double)));
+  if (!rows_dev) {
+    CU(cudaMalloc((void **)&w.rows_own, n * dim * sizeof(float)));
+    CU(cudaMemcpy(w.rows_own, rows_host, n * dim * sizeof(float), cudaMemcpyHostToDevice));
+    rows_dev = w.rows_own;
+  }
+  CU(cudaMemcpy(w.cent, centroids, cbytes, cudaMemcpyHostToDevice));
+  zvb200_ctx *c = w.ctx;
+  c->mma_group_cap = (uint32_t)w.cs->sm_count * 128u;  // one query tile per SM, every CTA walks all the centroids
+  const uint64_t chunk = (uint64_t)w.cs->sm_count * 128u * 4u;
+  auto assign = [&]() -> int {  // nearest centroid of every row: LinearSeeker::seek (linear_seeker.cc:20-42)
+    store_reset(w.cs);
+    int e = zvb200_store_append_device(w.cs, w.cent, k);
+    if (e == 0) e = zvb200_store_seal(w.cs);
+    for (uint64_t off = 0; e == 0 && off < n; off += chunk) {
+      const uint32_t qn = (uint32_t)std::min<uint64_t>(chunk, n - off);
+      e = search_core(c, w.cs, rows_dev + off * dim, qn, 1, FLT_MAX, nullptr, w.dist + off, w.lab + off, 0, k);
+    }
+    return e;
+  };
+  double cost = 0.0, new_cost = 0.0;
+  uint32_t it = 0;
+  for (; it < max_iterations; ++it) {
+    r = assign();
+    if (r != 0) return r;
+    CU(cudaMemsetAsync(w.sums, 0, (size_t)k * dim * sizeof(double), c->stream));
+    CU(cudaMemsetAsync(w.scores, 0, (size_t)k * sizeof(double), c->stream));
+    CU(cudaMemsetAsync(w.counts, 0, (size_t)k * sizeof(unsigned long long), c->stream));
+    CU(launch_kmeans_accumulate(rows_dev, n, dim, w.lab, w.dist, w.sums, w.counts, w.scores, c->stream));
+    CU(launch_kmeans_finalize(w.sums, w.counts, w.scores, k, dim, w.cent, w.counts, w.sse, c->stream));
+    CU(cudaMemcpyAsync(&new_cost, w.sse, sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    // the stopping rule of KmeansCluster::cluster (kmeans_cluster.cc:519-529)
+    if (fabs(new_cost - cost) < epsilon) { ++it; break; }
+    cost = new_cost;
+  }
+  if (labels) {  // KmeansCluster::label: against the centroids as returned
+    r = assign();
+    if (r != 0) return r;
+    CU(cudaMemcpyAsync(labels, w.lab, n * sizeof(uint32_t), cudaMemcpyDeviceToHost, c->stream));
+  }
+  CU(cudaMemcpyAsync(centroids, w.cent, cbytes, cudaMemcpyDeviceToHost, c->stream));
+  if (follows) {
+    static_assert(sizeof(unsigned long long) == sizeof(uint64_t), "follows layout");
+    CU(cudaMemcpyAsync(follows, w.counts, (size_t)k * sizeof(uint64_t), cudaMemcpyDeviceToHost, c->stream));
+  }
+  CU(cudaStreamSynchronize(c->stream));
+  if (sse_out) *sse_out = new_cost;
+  if (iterations_out) *iterations_out = it;
+  return 0;
+}
+
+extern "C" {
+
+int zvb200_kmeans(int device, int metric, const float *rows, uint64_t n, uint32_t dim, float *centroids, uint32_t k,
+                  uint32_t max_iterations, double epsilon, uint32_t *labels, uint64_t *follows, double *sse,
+                  uint32_t *iterations) {
+  return kmeans_core(device, metric, nullptr, rows, n, dim, centroids, k, max_iterations, epsilon, labels, follows, sse,
+                     iterations);
+}
+
+int zvb200_kmeans_device(int device, int metric, const float *rows_dev, uint64_t n, uint32_t dim, float *centroids,
+                         uint32_t k, uint32_t max_iterations, double epsilon, uint32_t *labels, uint64_t *follows,
+                         double *sse, uint32_t *iterations) {
+  return kmeans_core(device, metric, rows_dev, nullptr, n, dim, centroids, k, max_iterations, epsilon, labels, follows,
+                     sse, iterations);
 }
 
 }  // extern "C"

@@ -150,6 +150,14 @@ cudaError_t launch_reform(const float *in, uint32_t q, uint32_t dim, int kind, u
 cudaError_t launch_rows_plan(const uint32_t *rows, uint32_t q, uint32_t m, uint64_t n, uint32_t *seg_prefix,
                              uint32_t *seg_row, uint32_t *seg_count, cudaStream_t st);
 
+// K8: Lloyd update (kmeans.cu)
+cudaError_t launch_kmeans_accumulate(const float *rows, uint64_t n, uint32_t dim, const uint32_t *labels,
+                                     const float *dist, double *sums, unsigned long long *counts, double *scores,
+                                     cudaStream_t st);
+cudaError_t launch_kmeans_finalize(const double *sums, const unsigned long long *counts, const double *scores,
+                                   uint32_t k, uint32_t dim, float *centroids, unsigned long long *follows,
+                                   double *sse, cudaStream_t st);
+
 void count_launch(int n = 1);
 
 }  // namespace zvb
