@@ -212,13 +212,20 @@ __global__ void qi8_shadow_queries_kernel(const uint8_t *qraw, uint32_t row_stri
 // ---- K5a: part[q][nparts][k] -> final q*k ---------------------------------------------
 constexpr int kMergeWarps = 8;
 
+// SLICED: blockIdx.y merges `per_cta` consecutive partial lists of its query and writes the k best keys back over the
+// first of them (in place: a CTA only touches its own slice); the final pass then reads one list per slice
+// (`stride` = per_cta lists apart).  A single CTA per query took 57 us for the 256 x 64 keys of an IVF coarse search.
+template <bool SLICED>
 __global__ void __launch_bounds__(kMergeWarps * 32) merge_parts_kernel(
-    const u64 *part, uint32_t nparts, uint32_t k, float *out_scores, uint32_t *out_index) {
+    u64 *part, uint32_t nparts, uint32_t ninputs, uint32_t stride, uint32_t per_cta, uint32_t k, float *out_scores,
+    uint32_t *out_index) {
   extern __shared__ __align__(16) uint8_t smem[];
   const int lane = lane_id(), warp = threadIdx.x >> 5;
   const uint32_t qi = blockIdx.x;
-  const size_t total = (size_t)nparts * k;
-  const u64 *src = part + (size_t)qi * total;
+  const uint32_t in0 = SLICED ? blockIdx.y * per_cta : 0;
+  const uint32_t in1 = SLICED ? min(ninputs, in0 + per_cta) : ninputs;
+  const size_t total = in1 > in0 ? (size_t)(in1 - in0) * k : 0;
+  u64 *src = part + ((size_t)qi * nparts + (size_t)in0 * stride) * k;
   int2 *meta = reinterpret_cast<int2 *>(smem);
   u64 *tkbase = reinterpret_cast<u64 *>(smem + sizeof(int2) * kMergeWarps);
   const size_t tk_u64 = (size_t)2 * k + 32;
@@ -227,7 +234,11 @@ __global__ void __launch_bounds__(kMergeWarps * 32) merge_parts_kernel(
   tk.init(b, b + k, b + 2 * k, (int)k, kMaxKey);
   for (size_t i0 = (size_t)warp * 32; i0 < total; i0 += (size_t)kMergeWarps * 32) {
     const size_t i = i0 + lane;
-    const u64 e = i < total ? src[i] : kMaxKey;
+    u64 e = kMaxKey;
+    if (i < total) {
+      if (stride == 1) e = src[i];
+      else { const size_t li = i / k; e = src[li * stride * k + (i - li * k)]; }
+    }
     tk.push(e < tk.tau, e, kMaxKey);
   }
   tk.finish(kMaxKey);
@@ -247,8 +258,12 @@ __global__ void __launch_bounds__(kMergeWarps * 32) merge_parts_kernel(
   for (uint32_t i = lane; i < k; i += 32) {
     const bool ok = (int)i < tk.cnt;
     const u64 e = ok ? tk.list[i] : kMaxKey;
-    out_scores[(size_t)qi * k + i] = ok ? unorder_f32((uint32_t)(e >> 32)) : CUDART_NAN_F;
-    out_index[(size_t)qi * k + i] = ok ? (uint32_t)e : ZVB200_INVALID_INDEX;
+    if (SLICED) {
+      if (total) src[i] = e;
+    } else {
+      out_scores[(size_t)qi * k + i] = ok ? unorder_f32((uint32_t)(e >> 32)) : CUDART_NAN_F;
+      out_index[(size_t)qi * k + i] = ok ? (uint32_t)e : ZVB200_INVALID_INDEX;
+    }
   }
 }
 
@@ -427,11 +442,23 @@ cudaError_t launch_merge_parts(const u64 *part, uint32_t nparts, uint32_t q, uin
   const size_t smem = sizeof(int2) * kMergeWarps + (size_t)kMergeWarps * (2 * (size_t)k + 32) * sizeof(u64);
   static bool attr_set = false;
   if (!attr_set) {
-    cudaError_t e = cudaFuncSetAttribute(merge_parts_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+    cudaError_t e = cudaFuncSetAttribute(merge_parts_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+    if (e == cudaSuccess)
+      e = cudaFuncSetAttribute(merge_parts_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
     if (e != cudaSuccess) return e;
     attr_set = true;
   }
-  merge_parts_kernel<<<q, kMergeWarps * 32, smem, st>>>(part, nparts, k, out_scores, out_index);
+  u64 *p = const_cast<u64 *>(part);  // the sliced pass reuses the scratch lists in place
+  // few queries, many keys each: slices of the lists first (grid.y), then one list per slice
+  if ((size_t)nparts * k >= 4096 && q <= 64 && nparts >= 32) {
+    const uint32_t per_cta = 16, slices = (nparts + per_cta - 1) / per_cta;
+    merge_parts_kernel<true><<<dim3(q, slices), kMergeWarps * 32, smem, st>>>(p, nparts, nparts, 1, per_cta, k, nullptr, nullptr);
+    count_launch();
+    merge_parts_kernel<false><<<q, kMergeWarps * 32, smem, st>>>(p, nparts, slices, per_cta, 0, k, out_scores, out_index);
+    count_launch();
+    return cudaGetLastError();
+  }
+  merge_parts_kernel<false><<<q, kMergeWarps * 32, smem, st>>>(p, nparts, nparts, 1, 0, k, out_scores, out_index);
   count_launch();
   return cudaGetLastError();
 }
@@ -464,33 +491,66 @@ namespace {
 __global__ void ivf_plan_kernel(const uint32_t *coarse_index, uint32_t q, uint32_t nprobe, const uint32_t *list_off,
                                 const uint32_t *budget_sizes, uint64_t max_scan_count, uint32_t *seg_prefix,
                                 uint32_t *seg_row, uint32_t *seg_count) {
-  const uint32_t qi = blockIdx.x * blockDim.x + threadIdx.x;
+  // one WARP per query, 32 probes at a time (a single thread walking 64 probes through two dependent global loads
+  // each cost 35 us at batch 1 — half of the posting-list scan it prepares)
+  const uint32_t qi = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   if (qi >= q) return;
+  const int lane = threadIdx.x & 31;
+  const uint32_t lt = (1u << lane) - 1u;
   const uint32_t *ci = coarse_index + (size_t)qi * nprobe;
   uint32_t *pre = seg_prefix + (size_t)qi * (nprobe + 1), *row = seg_row + (size_t)qi * nprobe;
   // `total` is what the budget counts: the list's size in the WHOLE index (budget_sizes, when this store holds
   // one shard of every list) — every shard then visits exactly the lists the unsharded index would
   uint64_t total = 0;
   uint32_t n = 0, local = 0;
-  pre[0] = 0;
-  for (uint32_t i = 0; i < nprobe && total < max_scan_count; ++i) {
-    const uint32_t cid = ci[i];
-    if (cid == ZVB200_INVALID_INDEX) break;
-    const uint32_t b = list_off[cid], e = list_off[cid + 1];
-    total += budget_sizes ? budget_sizes[cid] : e - b;
-    if (e == b) continue;
-    row[n] = b;
-    local += e - b;
-    pre[++n] = local;
+  if (lane == 0) pre[0] = 0;
+  for (uint32_t c0 = 0; c0 < nprobe; c0 += 32) {
+    const uint32_t i = c0 + lane;
+    const uint32_t cid = i < nprobe ? ci[i] : ZVB200_INVALID_INDEX;
+    const bool valid = cid != ZVB200_INVALID_INDEX;
+    uint32_t b = 0, e = 0, bud = 0;
+    if (valid) {
+      b = list_off[cid]; e = list_off[cid + 1];
+      bud = budget_sizes ? budget_sizes[cid] : e - b;
+    }
+    // the loop of IVFSearcher::search_impl stops at the first missing centroid and once the budget is spent
+    const uint32_t dead = __ballot_sync(0xffffffffu, !valid);
+    const bool alive = dead == 0 || lane < __ffs(dead) - 1;
+    uint64_t inc = alive ? bud : 0;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const uint64_t v = __shfl_up_sync(0xffffffffu, inc, o);
+      if (lane >= o) inc += v;
+    }
+    const uint64_t excl = total + inc - (alive ? bud : 0);
+    const bool visit = alive && excl < max_scan_count;
+    const bool emit = visit && e != b;
+    const uint32_t em = __ballot_sync(0xffffffffu, emit);
+    uint32_t linc = emit ? e - b : 0;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const uint32_t v = __shfl_up_sync(0xffffffffu, linc, o);
+      if (lane >= o) linc += v;
+    }
+    if (emit) {
+      const uint32_t pos = n + __popc(em & lt);
+      row[pos] = b;
+      pre[pos + 1] = local + linc;
+    }
+    const uint32_t vis = __ballot_sync(0xffffffffu, visit);
+    total += __shfl_sync(0xffffffffu, visit ? inc : 0, vis ? 31 - __clz(vis) : 0);
+    n += __popc(em);
+    local += __shfl_sync(0xffffffffu, linc, 31);
+    if (vis != 0xffffffffu) break;  // a probe was not visited: nothing after it is
   }
-  seg_count[qi] = n;
+  if (lane == 0) seg_count[qi] = n;
 }
 }  // namespace
 
 cudaError_t launch_ivf_plan(const uint32_t *coarse_index, uint32_t q, uint32_t nprobe, const uint32_t *list_off,
                             const uint32_t *budget_sizes, uint64_t max_scan_count, uint32_t *seg_prefix,
                             uint32_t *seg_row, uint32_t *seg_count, cudaStream_t st) {
-  ivf_plan_kernel<<<(q + 127) / 128, 128, 0, st>>>(coarse_index, q, nprobe, list_off, budget_sizes, max_scan_count,
+  ivf_plan_kernel<<<(q + 3) / 4, 128, 0, st>>>(coarse_index, q, nprobe, list_off, budget_sizes, max_scan_count,
                                                   seg_prefix, seg_row, seg_count);
   count_launch();
   return cudaGetLastError();
