@@ -1,8 +1,12 @@
 set -x
 cd $GRAFT_REPO_ROOT
-python bench.py > gpurun_out/bench_1gpu.json 2> gpurun_out/bench_1gpu.err; tail -c 600 gpurun_out/bench_1gpu.json
-python bench.py --impl reference --steps 3 --warmup 1 > gpurun_out/bench_ref.json 2> gpurun_out/bench_ref.err; tail -c 400 gpurun_out/bench_ref.json
-ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/launches.csv python bench.py --steps 2 --warmup 1 > gpurun_out/ncu_bench.log 2>&1
-ncu --set full --clock-control none --import-source on -k regex:scan_mma -s 2 -c 1 -f -o gpurun_out/prof_qi8_shadow python tools/scan_probe.py --rows 20000000 --dim 96 --batch 1024 --k 100 --dtype int8q --metric l2 --iters 4 > gpurun_out/ncu_shadow.log 2>&1
-ncu --set full --clock-control none --import-source on -k regex:scan_mma -s 2 -c 1 -f -o gpurun_out/prof_f16_b1024 python tools/mma_probe.py 10000000 1024 768 10 > gpurun_out/ncu_f16.log 2>&1
-ls -la gpurun_out/*.ncu-rep
+( time timeout 900 python -m pytest tests/test_flat_gpu.py -m gpu -x -q -k "qi8 or batch1 or small_batch or ragged" ) > gpurun_out/pytest_gpu.log 2>&1; tail -4 gpurun_out/pytest_gpu.log
+P="python tools/scan_probe.py"
+{
+$P --rows 100000000 --dim 96 --batch 1 --k 100 --dtype int8q --metric l2 --iters 8
+$P --rows 100000000 --dim 96 --batch 1 --k 10 --dtype int8q --metric l2 --iters 8
+$P --rows 100000000 --dim 96 --batch 4 --k 100 --dtype int8q --metric l2 --iters 8
+$P --rows 10000000 --dim 768 --batch 1 --k 10 --dtype int8q --metric l2 --iters 8
+python tools/ivf_probe.py 10000000 1536 16384 64 1,8,64,1024
+} > gpurun_out/triage.log 2>&1
+grep -v "^+" gpurun_out/triage.log | tail -12

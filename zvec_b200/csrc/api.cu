@@ -533,7 +533,10 @@ static int search_core(zvb200_ctx *c, zvb200_store *s, const void *queries_dev, 
   // tensor cores: fp16 InnerProduct / Cosine at any batch (scores straight from the accumulator); fp16 L2 and
   // fp32 (tf32 filter + exact re-score) from 5 queries on — below that the streaming scan is as fast and simpler
   const bool mma_direct = mma_ok && s->dtype == ZVB200_DT_FP16 && !metric_is_l2(s->metric);
-  if (which == 0) which = (mma_direct || (mma_ok && q > 4)) ? 3 : (q <= 4) ? 1 : scan_tile_supports(k) ? 2 : 1;
+  // QuantizedInteger L2 with shadow operands: the streaming scan costs 2.5 / 8.2 ms at 1 / 4 queries (100M x 96), the
+  // tensor-core scan 5.2 ms for any batch up to 128 — it takes over from 3 queries
+  const bool mma_early = mma_ok && rv.shadow && q > 2;
+  if (which == 0) which = (mma_direct || (mma_ok && q > 4) || mma_early) ? 3 : (q <= 4) ? 1 : scan_tile_supports(k) ? 2 : 1;
   if (which == 4 && !stream_ok) which = 1;
   if (which == 3 && !mma_ok) return set_err(ZVB200_ERR_UNSUPPORTED, "tcgen05 scan: fp16 / fp32 stores, k <= 128 only");
   if (which == 2 && !scan_tile_supports(k)) which = 1;

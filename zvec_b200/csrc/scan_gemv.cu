@@ -133,7 +133,11 @@ __global__ void __launch_bounds__(kThreads, QB == 1 ? 2 : 1) scan_gemv_kernel(co
     for (int u = 0; u < kU; ++u) {
       uint64_t r = base + (uint64_t)u * R + sub;
       if (r >= vend) r = vend - 1;  // clamp: loaded, result discarded
-      rp[u] = a.rv.rows + to_row(r) * a.rv.row_stride;
+      const uint64_t sr = to_row(r);
+      rp[u] = a.rv.rows + sr * a.rv.row_stride;
+      // QuantizedInteger: the row's tail is read only after the dot product; start its trip from HBM now (no
+      // register held: the 128-register budget of 2 CTAs per SM is full) so that read finds it in L2
+      if (metric_is_qi8(metric) && l == 0) asm volatile("prefetch.global.L2 [%0];" ::"l"(a.rv.tails + sr));
       aa[u] = 0;
 #pragma unroll
       for (int j = 0; j < QB; ++j) acc[u][j] = 0;
