@@ -195,7 +195,7 @@ def run_reference(args):
            "config": workload_config(args, args.gpus), "cpu_baseline": base,
            "e2e": {"value": v, "unit": "queries/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
            "gpu_launches": 0}
-    print(json.dumps(out), flush=True)
+    emit(out)
 
 
 def workload_config(args, n):
@@ -406,7 +406,7 @@ def run_ours(args):
             arm = CpuArm(args)
             out["cpu_baseline"] = arm.best(20.0)
             arm.close()
-        print(json.dumps(out), flush=True)
+        emit(out)
     # torch tensors that were used on the context's stream must go before that stream does
     del loc_s, loc_i, all_s, all_i, fin_s, fin_r, h_s, h_r, dq, hq
     small.clear()
@@ -418,7 +418,19 @@ def run_ours(args):
     ctx.close(); st.close()
 
 
+def emit(obj):
+    """the ONE JSON line of the contract, on the process's real stdout"""
+    os.write(_REAL_STDOUT, (json.dumps(obj) + "\n").encode())
+
+
+# Libraries may chatter on fd 1 (NCCL prints its version banner there when NCCL_DEBUG is set): keep the real
+# stdout for the JSON line only and send everything else to stderr.
+_REAL_STDOUT = 1
+
+
 if __name__ == "__main__":
+    _REAL_STDOUT = os.dup(1)
+    os.dup2(2, 1)
     a = parse()
     if a.impl == "reference":
         run_reference(a)

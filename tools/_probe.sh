@@ -1,12 +1,5 @@
 set -x
 cd $GRAFT_REPO_ROOT
-( time timeout 900 python -m pytest tests/test_flat_gpu.py -m gpu -x -q -k "qi8 or batch1 or small_batch or ragged" ) > gpurun_out/pytest_gpu.log 2>&1; tail -4 gpurun_out/pytest_gpu.log
-P="python tools/scan_probe.py"
-{
-$P --rows 100000000 --dim 96 --batch 1 --k 100 --dtype int8q --metric l2 --iters 8
-$P --rows 100000000 --dim 96 --batch 1 --k 10 --dtype int8q --metric l2 --iters 8
-$P --rows 100000000 --dim 96 --batch 4 --k 100 --dtype int8q --metric l2 --iters 8
-$P --rows 10000000 --dim 768 --batch 1 --k 10 --dtype int8q --metric l2 --iters 8
-python tools/ivf_probe.py 10000000 1536 16384 64 1,8,64,1024
-} > gpurun_out/triage.log 2>&1
-grep -v "^+" gpurun_out/triage.log | tail -12
+python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29511 bench.py --gpus 2 --steps 10 --warmup 3 > gpurun_out/bench_2gpu.json 2> gpurun_out/bench_2gpu.err; tail -c 300 gpurun_out/bench_2gpu.json; tail -3 gpurun_out/bench_2gpu.err
+python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29512 tools/multigpu_probe.py ivf > gpurun_out/mg_ivf_2.json 2> gpurun_out/mg_ivf_2.err; tail -c 600 gpurun_out/mg_ivf_2.json
+python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29513 tools/multigpu_probe.py mv > gpurun_out/mg_mv_2.json 2> gpurun_out/mg_mv_2.err; tail -c 600 gpurun_out/mg_mv_2.json
