@@ -1,5 +1,18 @@
 set -x
 cd $GRAFT_REPO_ROOT
-python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29511 bench.py --gpus 2 --steps 10 --warmup 3 > gpurun_out/bench_2gpu.json 2> gpurun_out/bench_2gpu.err; tail -c 300 gpurun_out/bench_2gpu.json; tail -3 gpurun_out/bench_2gpu.err
-python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29512 tools/multigpu_probe.py ivf > gpurun_out/mg_ivf_2.json 2> gpurun_out/mg_ivf_2.err; tail -c 600 gpurun_out/mg_ivf_2.json
-python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29513 tools/multigpu_probe.py mv > gpurun_out/mg_mv_2.json 2> gpurun_out/mg_mv_2.err; tail -c 600 gpurun_out/mg_mv_2.json
+( time timeout 900 python -m pytest tests/test_flat_gpu.py tests/test_refine.py tests/test_kmeans.py tests/test_ivf_gpu.py -m gpu -x -q ) > gpurun_out/pytest_gpu.log 2>&1; tail -4 gpurun_out/pytest_gpu.log
+P="python tools/scan_probe.py"
+{
+$P --rows 20000000 --dim 96 --batch 1024 --k 100 --dtype fp16 --metric l2 --iters 6
+$P --rows 20000000 --dim 96 --batch 1024 --k 10 --dtype fp16 --metric l2 --iters 6
+ZVB200_MMA_DEBUG=128 $P --rows 20000000 --dim 96 --batch 1024 --k 10 --dtype fp16 --metric l2 --iters 3 | tail -3
+$P --rows 10000000 --dim 768 --batch 1024 --k 10 --dtype fp16 --metric l2 --iters 6
+$P --rows 1000000 --dim 128 --batch 1024 --k 10 --dtype fp32 --metric l2 --iters 8
+$P --rows 1000000 --dim 128 --batch 10000 --k 10 --dtype fp32 --metric l2 --iters 8
+$P --rows 10000000 --dim 128 --batch 1024 --k 10 --dtype fp32 --metric l2 --iters 8
+$P --rows 1000000 --dim 1536 --batch 1024 --k 10 --dtype fp32 --metric cos --iters 8
+ZVB200_QI8_SHADOW=0 $P --rows 20000000 --dim 96 --batch 1024 --k 10 --dtype int8q --metric l2 --iters 6
+$P --rows 10000000 --dim 768 --batch 1024 --k 10 --dtype int8q --metric l2 --iters 6
+$P --rows 10000000 --dim 768 --batch 1024 --k 10 --dtype int8 --metric l2 --iters 6
+} > gpurun_out/triage.log 2>&1
+grep -v "^+" gpurun_out/triage.log | tail -16

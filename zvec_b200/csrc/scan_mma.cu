@@ -36,7 +36,7 @@ namespace {
 constexpr int kQM = 128;       // queries per CTA tile
 constexpr int kBK = 64;        // halves per k-block (128 B = one swizzle row)
 constexpr int kBN = 256;       // stored rows per tile
-constexpr int kThreads = 256;  // warp 0 TMA, 1 MMA, 2 TMEM alloc, 3 idle, 4-7 epilogue
+constexpr int kThreads = 256;  // warp 0 TMA, 1 MMA, 2 TMEM alloc, 3 per-column constants, 4-7 epilogue
 constexpr uint32_t kStageA = kQM * kBK * 2;
 constexpr uint32_t kStageB = kBN * kBK * 2;
 constexpr uint32_t kStage = kStageA + kStageB;
@@ -296,12 +296,45 @@ scan_mma_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
   uint8_t *sbase = smem_raw + (base - smem_u32(smem_raw));
   const uint32_t k = a.k, nstage = a.nstage;
   u64 *lists = reinterpret_cast<u64 *>(sbase + (size_t)nstage * kStage);      // [k][128]: entry i of query s at i*128+s
-  uint64_t *bars = reinterpret_cast<uint64_t *>(lists + (size_t)kQM * k);     // full[ns] empty[ns] tfull[2] tempty[2]
-  uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + 2 * nstage + 4);
+  uint64_t *bars = reinterpret_cast<uint64_t *>(lists + (size_t)kQM * k);     // full[ns] empty[ns] tfull[2] tempty[2] cfull[4] cempty[4]
+  uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + 2 * nstage + 12);
   float *colc = reinterpret_cast<float *>((reinterpret_cast<uintptr_t>(tmem_slot + 4) + 15) & ~(uintptr_t)15);  // [2][kBN] per-column constants (float, or float4 for int8)
   constexpr int kBKe = (KIND == 0 || KIND == 3) ? 64 : KIND == 1 ? 32 : 128;   // elements per 128-byte k-block
   const uint32_t bar_full = smem_u32(bars), bar_empty = bar_full + 8 * nstage;
   const uint32_t bar_tfull = bar_empty + 8 * nstage, bar_tempty = bar_tfull + 16;
+  const uint32_t bar_cfull = bar_tempty + 16, bar_cempty = bar_cfull + 32;
+  // ---- per-column constants (one float, or a float4 for the int8 forms): produced one or more tiles ahead by
+  // warp 3 into a ring of kCB buffers, consumed by the epilogue warps through cfull / cempty mbarriers.  (The
+  // epilogue threads used to fetch and store them themselves behind a bar.sync per tile: every tile then cost the
+  // slowest of the four warps plus their LDG / STS issue — 2200 cycles per tile of 5000 for fp16 L2 at d = 96.)
+  const int mode = (KIND == 2 || KIND == 3) ? 0 : a.mode;
+  constexpr int imode = IM;
+  constexpr bool ic4 = KIND == 2 && IM != 5;  // {|x|^2 as int} (plain int8 L2), the row tail or its filter form (QuantizedInteger)
+  const bool resc = mode >= 2;
+  constexpr uint32_t kCB = ic4 ? 2 : 4;
+  float4 *colc4 = reinterpret_cast<float4 *>(colc);
+  const float dq = (float)a.d;
+  constexpr float kEpsQ = 3.1e-5f;  // see the QuantizedInteger L2 filter below
+  auto cval4 = [&](uint32_t row) -> float4 {
+    if (row >= a.row_end) {
+      const float nan = __int_as_float(0x7fc00000);
+      return imode <= 6 ? make_float4(0, 0, 0, 0) : make_float4(nan, nan, nan, nan);  // NaN score: never a candidate
+    }
+    if (imode == 5) return make_float4(0, 0, 0, 0);
+    if (imode == 6) return make_float4(__int_as_float((int)a.norms[row]), 0, 0, 0);
+    const float4 m = a.tails[row];
+    if (imode == 7) {
+      const float t1 = m.x * m.x * m.w, mbd = m.y * m.y * dq, msma = m.z * m.x;
+      const float c0 = t1 + mbd + 2.0f * m.y * msma;
+      return make_float4(-(c0 - kEpsQ * (t1 + mbd)), m.y, msma, m.x);
+    }
+    return m;
+  };
+  auto cval = [&](uint32_t row) -> float {
+    if (row >= a.row_end) return __int_as_float(0xff800000);  // never a candidate
+    const float hx = 0.5f * a.norms[row];
+    return mode == 2 ? -(1.0f - a.eps) * hx : a.eps * hx;
+  };
 
   if (warp == 0 && lane == 0) {
     asm volatile("prefetch.tensormap [%0];" ::"l"(&tmQ) : "memory");
@@ -315,6 +348,10 @@ scan_mma_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
     for (uint32_t s = 0; s < 2; ++s) {
       mbar_init(bar_tfull + 8 * s, 1);
       mbar_init(bar_tempty + 8 * s, 4);  // one arrival per epilogue warp
+    }
+    for (uint32_t s = 0; s < 4; ++s) {
+      mbar_init(bar_cfull + 8 * s, 1);
+      mbar_init(bar_cempty + 8 * s, 4);
     }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
@@ -380,6 +417,30 @@ scan_mma_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
         umma_commit(bar_tfull + 8 * as);       // accumulator tile complete
       }
     }
+  } else if (warp == 3) {
+    // ================= per-column constants producer =================
+    if (resc || ic4) {
+      for (uint32_t t = 0; t < ntl; ++t) {
+        const uint32_t cb = t % kCB;
+        if (t >= kCB) mbar_wait(bar_cempty + 8 * cb, ((t / kCB) - 1) & 1);
+        const uint32_t row0 = a.row_begin + (t_begin + t) * kBN;
+        if (ic4) {
+          float4 v[8];
+#pragma unroll
+          for (int i = 0; i < 8; ++i) v[i] = cval4(row0 + lane + 32 * i);
+#pragma unroll
+          for (int i = 0; i < 8; ++i) colc4[cb * kBN + lane + 32 * i] = v[i];
+        } else {
+          float v[8];
+#pragma unroll
+          for (int i = 0; i < 8; ++i) v[i] = cval(row0 + lane + 32 * i);
+#pragma unroll
+          for (int i = 0; i < 8; ++i) colc[cb * kBN + lane + 32 * i] = v[i];
+        }
+        __syncwarp();
+        if (lane == 0) mbar_arrive(bar_cfull + 8 * cb);
+      }
+    }
   } else if (warp >= 4) {
     // ================= epilogue: thread-per-query filter + private top-k pool =================
     const int ew = warp - 4;
@@ -391,9 +452,7 @@ scan_mma_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
     u64 *Lw = lists + ew * 32;
 #define ZVB_POOL(i) Lw[(size_t)(i) * kQM + (lane ^ ((i) & 31))]
     // int8: the column value is MINUS the exact score, so the rest of the epilogue runs as mode 0 (s = -value)
-    const int mode = (KIND == 2 || KIND == 3) ? 0 : a.mode;
     constexpr bool SH = KIND == 3;
-    constexpr int imode = IM;
     const int K = (int)k;
     // The pool is UNSORTED: the k smallest keys accepted so far, with the position of the largest
     // cached.  Accepting a key replaces the largest and rescans the pool for the new one — k
@@ -428,10 +487,7 @@ scan_mma_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
     //   mode 3/4 (IP / cosine through tf32): colc = +eps hx, dthr = (-T | 1 - T) - eps hq.
     // Modes 2-4 never use f as a score: a candidate is re-scored exactly (exact_score) before it is offered.
     // ---- int8: per-thread query constants and the per-column score, the formulas of K1 (scan_gemv.cu) ----
-    const bool ic4 = KIND == 2 && IM != 5;  // per-row constants, always staged (unconditional loads in the hot loop): {|x|^2 as int} (plain L2), the row tail or its filter form (QuantizedInteger), zeros (plain -IP)
-    float4 *colc4 = reinterpret_cast<float4 *>(colc);
     const float4 qt = (((KIND == 2 && imode >= 7) || SH) && qvalid) ? a.qtails[q0 + slot] : make_float4(0, 0, 0, 0);
-    const float dq = (float)a.d;
     int qq_i = 0;
     if (KIND == 2 && imode == 6 && qvalid) {
       const int8_t *qp = reinterpret_cast<const int8_t *>(a.qraw + (size_t)(q0 + slot) * a.row_stride);
@@ -441,7 +497,6 @@ scan_mma_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
     // value and the reference-order score: both are <= 12 roundings of sums whose absolute terms total
     // <= 8 [(ma^2 ms2 + mb^2 d) + (qa^2 qs2 + qb^2 d)] (Cauchy-Schwarz on ip, ms, qs), so
     // 2 * 12 * 2^-24 * 8 = 1.2e-5 < kEpsQ
-    constexpr float kEpsQ = 3.1e-5f;
     const bool small_ip = a.d <= 260;
     const float qsum = qt.x * qt.z, qsum2 = qt.x * qt.x * qt.w;  // qa*qs, qa*qa*qs2
     const float nQ1 = 2.0f * (qt.y * dq + qsum), nQ2 = 2.0f * qt.y, nQa = 2.0f * qt.x;
@@ -470,22 +525,6 @@ scan_mma_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
       }
       return -qi8_mip((float)ip, c4, qt, dq);
     };
-    auto cval4 = [&](uint32_t row) -> float4 {
-      if (row >= a.row_end) {
-        const float nan = __int_as_float(0x7fc00000);
-        return imode <= 6 ? make_float4(0, 0, 0, 0) : make_float4(nan, nan, nan, nan);  // NaN score: never a candidate
-      }
-      if (imode == 5) return make_float4(0, 0, 0, 0);
-      if (imode == 6) return make_float4(__int_as_float((int)a.norms[row]), 0, 0, 0);
-      const float4 m = a.tails[row];
-      if (imode == 7) {
-        const float t1 = m.x * m.x * m.w, mbd = m.y * m.y * dq, msma = m.z * m.x;
-        const float c0 = t1 + mbd + 2.0f * m.y * msma;
-        return make_float4(-(c0 - kEpsQ * (t1 + mbd)), m.y, msma, m.x);
-      }
-      return m;
-    };
-    const bool resc = mode >= 2;
     const bool root6 = KIND == 2 && imode == 6 && a.metric == ZVB200_METRIC_L2;
     const float hq = (resc && qvalid) ? 0.5f * a.qnorms[q0 + slot] : 0.f;
     auto dthr_of = [&](u64 tk) -> float {
@@ -510,12 +549,6 @@ scan_mma_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
       }
       const float b = mode == 3 ? -tau_f : 1.0f - tau_f;
       return b - a.eps * hq - (fabsf(b) + fabsf(tau_f) + 1.0f) * 4.8e-7f;
-    };
-    // per-column constants of the rows of a tile (modes 2-4), fetched one tile ahead by the epilogue threads
-    auto cval = [&](uint32_t row) -> float {
-      if (row >= a.row_end) return __int_as_float(0xff800000);  // never a candidate
-      const float hx = 0.5f * a.norms[row];
-      return mode == 2 ? -(1.0f - a.eps) * hx : a.eps * hx;
     };
     float dthr = dthr_of(tau_key);
     auto accept = [&](u64 key) {
@@ -668,18 +701,6 @@ scan_mma_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
     // the first-tile bootstrap needs every row of that tile to be a live row
     const bool boot = !(KIND == 2 && imode == 7) && !SH && a.groups > 1 && pubj <= 8 && !a.drop && !a.filter && ntl > 1 &&
                       a.row_begin + (t_begin + 1) * kBN <= a.row_end && !(a.dbg & (1 | 16 | 32 | 64));
-    const int etid = ew * 32 + lane;
-    if (resc || ic4) {
-      const uint32_t r0 = a.row_begin + t_begin * kBN;
-      if (ic4) {
-        colc4[etid] = cval4(r0 + etid);
-        colc4[etid + 128] = cval4(r0 + 128 + etid);
-      } else {
-        colc[etid] = cval(r0 + etid);
-        colc[etid + 128] = cval(r0 + 128 + etid);
-      }
-      asm volatile("bar.sync 1, 128;" ::: "memory");
-    }
     const bool prof = (a.dbg & 128) != 0;  // triage: where the epilogue's cycles go (printed by CTA 0)
     long long c_wait = 0, c_slow = 0, c_ub = 0, c_t0 = 0, c_first4 = 0, c_tiles = 0, c_ex = 0, c_acc = 0, c_ld1 = 0;
     uint32_t n_slow = 0, n_ev = 0;
@@ -688,13 +709,11 @@ scan_mma_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
     for (uint32_t t = 0; t < ntl; ++t) {
       const uint32_t as = t & 1, aphase = (t >> 1) & 1;
       const uint32_t row0 = a.row_begin + (t_begin + t) * kBN;
-      float pc0 = 0.f, pc1 = 0.f;
-      float4 pd0 = make_float4(0, 0, 0, 0), pd1 = pd0;
-      if (resc && t + 1 < ntl) { pc0 = cval(row0 + kBN + etid); pc1 = cval(row0 + kBN + 128 + etid); }
-      if (ic4 && t + 1 < ntl) { pd0 = cval4(row0 + kBN + etid); pd1 = cval4(row0 + kBN + 128 + etid); }
-      const float *cc = colc + (t & 1) * kBN;
-      const float4 *cc4 = colc4 + (t & 1) * kBN;
+      const uint32_t cb = t % kCB;
+      const float *cc = colc + cb * kBN;
+      const float4 *cc4 = colc4 + cb * kBN;
       const long long c0w = prof ? clock64() : 0;
+      if (resc || ic4) mbar_wait(bar_cfull + 8 * cb, (t / kCB) & 1);  // this tile's constants (warp 3, tiles ahead)
       mbar_wait(bar_tfull + 8 * as, aphase);
       if (prof) c_wait += clock64() - c0w;
       const long long c_tile = prof ? clock64() : 0;
@@ -893,20 +912,7 @@ scan_mma_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(bar_tempty + 8 * as);
-      if (resc || ic4) {
-        if (t + 1 < ntl) {
-          if (ic4) {
-            float4 *cn = colc4 + ((t + 1) & 1) * kBN;
-            cn[etid] = pd0;
-            cn[etid + 128] = pd1;
-          } else {
-            float *cn = colc + ((t + 1) & 1) * kBN;
-            cn[etid] = pc0;
-            cn[etid + 128] = pc1;
-          }
-        }
-        asm volatile("bar.sync 1, 128;" ::: "memory");
-      }
+      if ((resc || ic4) && lane == 0) mbar_arrive(bar_cempty + 8 * cb);  // (after the __syncwarp above)
       // off the MMA's critical path: refresh the union bound at tiles 1,2,3,4,6,9,13,19,... of this CTA
       if (a.groups > 1 && t + 1 == next_eval && !(a.dbg & 32)) {
         const long long c0u = prof ? clock64() : 0;
@@ -979,7 +985,7 @@ constexpr size_t kSmemMax = 232448;  // 227 KB
 // pipeline stages that fit next to the 128 x k lists; false when not even 2 stages fit
 bool mma_config(uint32_t k, size_t colc_bytes, uint32_t *nstage, size_t *smem) {
   for (uint32_t ns = 4; ns >= 2; --ns) {
-    const size_t need = 1024 + (size_t)ns * kStage + (size_t)kQM * k * 8 + (2 * ns + 4) * 8 + 32 + colc_bytes;
+    const size_t need = 1024 + (size_t)ns * kStage + (size_t)kQM * k * 8 + (2 * ns + 12) * 8 + 32 + colc_bytes;
     if (need <= kSmemMax) { *nstage = ns; *smem = need; return true; }
   }
   return false;
@@ -999,7 +1005,7 @@ static size_t colc_bytes_for(const RowsView &rv, bool shadow = false) {
   if (shadow) return 0;
   if (rv.dtype == ZVB200_DT_INT8) return 2 * kBN * sizeof(float4);
   const bool direct = rv.dtype == ZVB200_DT_FP16 && !metric_is_l2(rv.metric);
-  return direct ? 0 : 2 * kBN * sizeof(float);
+  return direct ? 0 : 4 * kBN * sizeof(float);  // ring of 4 tiles
 }
 
 bool scan_mma_supports(const RowsView &rv, uint32_t k) {
