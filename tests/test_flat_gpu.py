@@ -425,3 +425,25 @@ def test_mma_and_tile_agree_on_ids():
     ctx.set_kernel(3); _, s3, i3, _ = ctx.search(queries, 10)
     assert np.allclose(s2, s3, rtol=1e-4, atol=1e-6)
     assert (i2 == i3).mean() > 0.999        # order may differ only inside near-ties
+
+
+@pytest.mark.parametrize("kind,k", [("fp16_ip", 100), ("fp16_l2", 10), ("fp32_l2", 100), ("qi8_l2", 100), ("i8_l2", 33)])
+def test_mma_results_are_deterministic_across_runs(kind, k):
+    """races would show as run-to-run differences: the cooperative pool (k > 16), the constants ring fed by warp 3
+    and the union bound across CTAs only ever remove work — the lists must be bit-identical every time, and equal
+    to the streaming scan's"""
+    metric, dt, sdim, stored, conv = make_stored(kind, 300000, 64, 97)
+    queries = np.ascontiguousarray(conv(np.random.default_rng(98).standard_normal((257, 64)).astype(np.float32)))
+    st = z.Store(dt, metric, sdim); st.append(stored); st.seal()
+    ctx = z.Context(st); ctx.set_kernel(3)
+    _, s0, i0, c0 = ctx.search(queries, k)
+    assert ctx.last_kernel() == "scan_mma"
+    for _ in range(12):
+        _, s1, i1, c1 = ctx.search(queries, k)
+        assert np.array_equal(i0, i1) and np.array_equal(s0.view(np.uint32), s1.view(np.uint32)) and np.array_equal(c0, c1)
+    ctx.set_kernel(1)
+    _, s2, i2, _ = ctx.search(queries[:16], k)
+    for q in range(16):
+        alld = S.oracle_distances(metric, dt, stored, sdim, queries[q])
+        S.check_topk_parity(i0[q], s0[q], i2[q], s2[q], all_dist=alld, exact=dt == S.DT_INT8, what="%s q%d" % (kind, q))
+    ctx.close(); st.close()

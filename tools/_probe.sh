@@ -11,8 +11,6 @@ $P --rows 1000000 --dim 128 --batch 1024 --k 10 --dtype fp32 --metric l2 --iters
 $P --rows 1000000 --dim 128 --batch 10000 --k 10 --dtype fp32 --metric l2 --iters 8
 $P --rows 10000000 --dim 128 --batch 1024 --k 10 --dtype fp32 --metric l2 --iters 8
 $P --rows 1000000 --dim 1536 --batch 1024 --k 10 --dtype fp32 --metric cos --iters 8
-ZVB200_QI8_SHADOW=0 $P --rows 20000000 --dim 96 --batch 1024 --k 10 --dtype int8q --metric l2 --iters 6
-$P --rows 10000000 --dim 768 --batch 1024 --k 10 --dtype int8q --metric l2 --iters 6
-$P --rows 10000000 --dim 768 --batch 1024 --k 10 --dtype int8 --metric l2 --iters 6
+python tools/kmeans_probe.py 1000000 1536 16384 2
 } > gpurun_out/triage.log 2>&1
 grep -v "^+" gpurun_out/triage.log | tail -16
