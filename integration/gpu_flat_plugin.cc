@@ -446,21 +446,23 @@ class GpuFlatStreamer : public IndexStreamer {
     ctx->resize_results(count);
     for (uint32_t i = 0; i < count; ++i) ctx->mutable_result(i)->clear();
     if (k == 0) return 0;
-    std::vector<uint64_t> host_keys;
+    // publish the rows added since the last search.  A filtered search keeps the lock until it returns: its bitmap
+    // is sized for the rows the store holds NOW, and another thread's search must not publish more in between
+    std::unique_lock<std::mutex> g(mu_);
     {
-      std::lock_guard<std::mutex> g(mu_);
-      int rc = const_cast<GpuFlatStreamer *>(this)->flush_pending();  // publish the rows added since the last search
+      int rc = const_cast<GpuFlatStreamer *>(this)->flush_pending();
       if (rc != 0) return rc;
-      if (ctx->filter().is_valid()) host_keys = all_keys_;
     }
     const size_t n = zvb200_store_count(store_);
     if (n == 0) return 0;
     const uint32_t *bitmap = nullptr;
     if (ctx->filter().is_valid()) {
       ctx->bitmap.assign((n + 31) / 32, 0u);
-      for (size_t i = 0; i < n && i < host_keys.size(); ++i)
-        if (host_keys[i] != ZVB200_INVALID_KEY && ctx->filter()(host_keys[i])) ctx->bitmap[i >> 5] |= 1u << (i & 31);
+      for (size_t i = 0; i < n && i < all_keys_.size(); ++i)
+        if (all_keys_[i] != ZVB200_INVALID_KEY && ctx->filter()(all_keys_[i])) ctx->bitmap[i >> 5] |= 1u << (i & 31);
       bitmap = ctx->bitmap.data();
+    } else {
+      g.unlock();
     }
     const size_t nres = (size_t)count * k;
     ctx->keys.resize(nres); ctx->scores.resize(nres); ctx->index.resize(nres); ctx->counts.resize(count);

@@ -447,3 +447,35 @@ def test_mma_results_are_deterministic_across_runs(kind, k):
         alld = S.oracle_distances(metric, dt, stored, sdim, queries[q])
         S.check_topk_parity(i0[q], s0[q], i2[q], s2[q], all_dist=alld, exact=dt == S.DT_INT8, what="%s q%d" % (kind, q))
     ctx.close(); st.close()
+
+
+def test_concurrent_contexts_on_one_store():
+    """IndexSearcher::search_impl is const and called from many threads, one context each
+    (src/core/interface/index.cc:24-45; flat_streamer_test.cc:509-730): eight threads, own context and stream each,
+    different batch sizes / kernels at the same time — every result equals the serial one"""
+    import threading
+    metric, dt, sdim, stored, conv = make_stored("fp16_ip", 200000, 96, 99)
+    queries = np.ascontiguousarray(conv(np.random.default_rng(100).standard_normal((192, 96)).astype(np.float32)))
+    st = z.Store(dt, metric, sdim); st.append(stored); st.seal()
+    plans = [(1, 10), (3, 10), (64, 10), (192, 100), (1, 100), (130, 16), (40, 33), (7, 10)]
+    serial = []
+    for q, k in plans:
+        c = z.Context(st); serial.append(c.search(queries[:q], k)); c.close()
+    errors = []
+
+    def work(i):
+        try:
+            q, k = plans[i]
+            c = z.Context(st)
+            for _ in range(6):
+                got = c.search(queries[:q], k)
+                for a, b in zip(got, serial[i]):
+                    assert np.array_equal(np.asarray(a).view(np.uint8), np.asarray(b).view(np.uint8))
+            c.close()
+        except BaseException as e:  # noqa: BLE001
+            errors.append((i, repr(e)))
+
+    ts = [threading.Thread(target=work, args=(i,)) for i in range(len(plans))]
+    [t.start() for t in ts]; [t.join() for t in ts]
+    assert not errors, errors
+    st.close()

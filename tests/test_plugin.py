@@ -351,3 +351,64 @@ def test_gpu_ivf_streamer_equals_ivf_streamer(metric, conv):
         S.ref().zref_set_filter(0, 0)
     ix.use_streamer("")
     ix.close()
+
+
+# ---- threading contract: many threads, one context each; adds race with searches ----
+@needs_plugin
+@pytest.mark.gpu
+def test_gpu_searcher_from_many_threads_equals_single_thread():
+    n, d, k = 30000, 48, 10
+    x = _tie_free(n, d, 31)
+    qs = np.random.default_rng(32).standard_normal((96, d)).astype(np.float32)
+    ix = S.RefIndex(x, S.DT_FP32, d, "SquaredEuclidean", "", kind="Flat:GpuFlatSearcher")
+    one = ix.search(qs, k, batch=8, threads=1)
+    many = ix.search(qs, k, batch=8, threads=6)          # six threads, own create_context() each (ref_shim.cc)
+    for a, b in zip(one, many):
+        assert np.array_equal(np.asarray(a).view(np.uint8), np.asarray(b).view(np.uint8))
+    ix.close()
+
+
+@needs_plugin
+@pytest.mark.gpu
+def test_gpu_streamer_adds_race_with_searches(tmp_path):
+    """flat_streamer_test.cc:509-730 in spirit: one thread adds, two threads search; every answer must be a valid
+    answer for SOME prefix of the adds (keys that exist, scores of those rows), and the final state equals the
+    stock streamer's"""
+    import threading
+    d, k, n = 16, 5, 4000
+    rng = np.random.default_rng(33)
+    x = rng.standard_normal((n, d)).astype(np.float32)
+    qs = rng.standard_normal((8, d)).astype(np.float32)
+    g = _Streamer("GpuFlatStreamer", S.DT_FP32, d, "SquaredEuclidean", str(tmp_path / "gpu.index"))
+    r = _Streamer("FlatStreamer", S.DT_FP32, d, "SquaredEuclidean", str(tmp_path / "ref.index"))
+    errors, done = [], threading.Event()
+
+    def adder():
+        try:
+            for i in range(n):
+                assert g.add(i + 1, x[i]) == 0
+        except BaseException as e:  # noqa: BLE001
+            errors.append(repr(e))
+        finally:
+            done.set()
+
+    def searcher():
+        try:
+            while not done.is_set():
+                keys, scores, counts = g.search(qs, k)
+                for qi in range(len(qs)):
+                    for j in range(int(counts[qi])):
+                        key = int(keys[qi][j])
+                        assert 1 <= key <= n
+                        exact = float(((x[key - 1] - qs[qi]) ** 2).sum())
+                        assert abs(scores[qi][j] - exact) <= 1e-4 * max(exact, 1.0)
+        except BaseException as e:  # noqa: BLE001
+            errors.append(repr(e))
+
+    ts = [threading.Thread(target=adder)] + [threading.Thread(target=searcher) for _ in range(2)]
+    [t.start() for t in ts]; [t.join() for t in ts]
+    assert not errors, errors
+    for i in range(n):
+        assert r.add(i + 1, x[i]) == 0
+    _same(g.search(qs, k), r.search_each(qs, k), "after the race")
+    g.close(); r.close()

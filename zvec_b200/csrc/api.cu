@@ -4,6 +4,7 @@
 #include <float.h>
 
 #include <algorithm>
+#include <shared_mutex>
 #include <cmath>
 #include <atomic>
 #include <cstdio>
@@ -60,7 +61,11 @@ struct zvb200_store {
   uint32_t *list_off_dev = nullptr;  // [nlist+1] first row of each posting list
   uint32_t *budget_dev = nullptr;    // [nlist] list sizes in the whole index (sharded IVF), or null
   uint32_t nlist = 0;
-  std::mutex mu;
+  // writers (append / seal / write / set_deleted / attach) exclusive; the host-synchronous searches shared, from the
+  // first look at the store to the stream sync that ends them: an append that re-allocates the rows (store_grow)
+  // cannot free them under a search another thread has in flight (FlatStreamer adds race with searches,
+  // tests/core/algorithm/flat/flat_streamer_test.cc:509-730)
+  std::shared_mutex mu;
 
   RowsView view() const {
     RowsView v;
@@ -222,7 +227,7 @@ int zvb200_store_destroy(zvb200_store *s) {
 
 int zvb200_store_reserve(zvb200_store *s, uint64_t rows) {
   if (!s) return set_err(ZVB200_ERR_INVALID_ARGUMENT, "null store");
-  std::lock_guard<std::mutex> g(s->mu);
+  std::lock_guard<std::shared_mutex> g(s->mu);
   CU(cudaSetDevice(s->device));
   if (rows <= s->cap) return 0;
   uint64_t keep = s->cap;
@@ -240,7 +245,7 @@ static int append_common(zvb200_store *s, const uint8_t *src_dev, uint64_t n) {
 
 int zvb200_store_append(zvb200_store *s, const void *rows, uint64_t n, const uint64_t *keys) {
   if (!s || (!rows && n)) return set_err(ZVB200_ERR_INVALID_ARGUMENT, "null argument");
-  std::lock_guard<std::mutex> g(s->mu);
+  std::lock_guard<std::shared_mutex> g(s->mu);
   if (s->n + n >= 0xffffffffull) return set_err(ZVB200_ERR_INVALID_ARGUMENT, "store holds < 2^32-1 rows");
   CU(cudaSetDevice(s->device));
   int r = store_grow(s, s->n + n);
@@ -280,7 +285,7 @@ int zvb200_store_append(zvb200_store *s, const void *rows, uint64_t n, const uin
 
 int zvb200_store_append_device(zvb200_store *s, const void *rows_dev, uint64_t n) {
   if (!s || (!rows_dev && n)) return set_err(ZVB200_ERR_INVALID_ARGUMENT, "null argument");
-  std::lock_guard<std::mutex> g(s->mu);
+  std::lock_guard<std::shared_mutex> g(s->mu);
   if (s->n + n >= 0xffffffffull) return set_err(ZVB200_ERR_INVALID_ARGUMENT, "store holds < 2^32-1 rows");
   CU(cudaSetDevice(s->device));
   int r = store_grow(s, s->n + n);
@@ -312,7 +317,7 @@ static int sync_drop(zvb200_store *s) {
 
 int zvb200_store_seal(zvb200_store *s) {
   if (!s) return set_err(ZVB200_ERR_INVALID_ARGUMENT, "null store");
-  std::lock_guard<std::mutex> g(s->mu);
+  std::lock_guard<std::shared_mutex> g(s->mu);
   CU(cudaSetDevice(s->device));
   int r = sync_drop(s);
   if (r != 0) return r;
@@ -361,7 +366,7 @@ uint64_t zvb200_store_scan_bytes(const zvb200_store *s) {
 
 int zvb200_store_set_deleted(zvb200_store *s, uint64_t row, int deleted) {
   if (!s || row >= s->n) return set_err(ZVB200_ERR_INVALID_ARGUMENT, "bad row");
-  std::lock_guard<std::mutex> g(s->mu);
+  std::lock_guard<std::shared_mutex> g(s->mu);
   s->drop_host.resize((s->n + 31) / 32, 0u);
   if (deleted) s->drop_host[row >> 5] |= 1u << (row & 31);
   else s->drop_host[row >> 5] &= ~(1u << (row & 31));
@@ -372,7 +377,7 @@ int zvb200_store_set_deleted(zvb200_store *s, uint64_t row, int deleted) {
 
 int zvb200_store_write(zvb200_store *s, uint64_t row, const void *vec, uint64_t key) {
   if (!s || !vec || row >= s->n) return set_err(ZVB200_ERR_INVALID_ARGUMENT, "bad argument");
-  std::lock_guard<std::mutex> g(s->mu);
+  std::lock_guard<std::shared_mutex> g(s->mu);
   CU(cudaSetDevice(s->device));
   if (!s->staging) {
     s->staging_bytes = std::max<size_t>(1, ((size_t)64 << 20) / s->elem_bytes) * s->elem_bytes;
@@ -681,6 +686,8 @@ int zvb200_search_device(zvb200_ctx *c, const void *queries_dev, uint32_t q, uin
 int zvb200_search(zvb200_ctx *c, const void *queries, uint32_t q, uint32_t k, float threshold,
                   const uint32_t *filter, uint64_t *out_keys, float *out_scores,
                   uint32_t *out_index, uint32_t *out_counts) {
+  if (!c) return set_err(ZVB200_ERR_INVALID_ARGUMENT, "null argument");
+  std::shared_lock<std::shared_mutex> rl(c->s->mu);
   int r = check_search_args(c, queries, q, k);
   if (r != 0) return r;
   if (!out_scores) return set_err(ZVB200_ERR_INVALID_ARGUMENT, "null out_scores");
@@ -823,7 +830,7 @@ int zvb200_ivf_attach(zvb200_store *s, const void *centroids, uint32_t nlist, co
   if (r == 0) r = zvb200_store_append(cs, centroids, nlist, nullptr);
   if (r == 0) r = zvb200_store_seal(cs);
   if (r != 0) { if (cs) zvb200_store_destroy(cs); return r; }
-  std::lock_guard<std::mutex> g(s->mu);
+  std::lock_guard<std::shared_mutex> g(s->mu);
   CU(cudaSetDevice(s->device));
   std::vector<uint32_t> off32(nlist + 1);
   for (uint32_t l = 0; l <= nlist; ++l) off32[l] = (uint32_t)list_offsets[l];
@@ -840,7 +847,7 @@ int zvb200_ivf_attach(zvb200_store *s, const void *centroids, uint32_t nlist, co
 
 int zvb200_ivf_set_budget_sizes(zvb200_store *s, const uint64_t *list_sizes) {
   if (!s || !s->centroids) return set_err(ZVB200_ERR_NOREADY, "no IVF structure attached");
-  std::lock_guard<std::mutex> g(s->mu);
+  std::lock_guard<std::shared_mutex> g(s->mu);
   CU(cudaSetDevice(s->device));
   if (s->budget_dev) { cudaFree(s->budget_dev); s->budget_dev = nullptr; }
   if (!list_sizes) return 0;
@@ -854,6 +861,8 @@ int zvb200_ivf_set_budget_sizes(zvb200_store *s, const uint64_t *list_sizes) {
 int zvb200_ivf_search(zvb200_ctx *c, const void *queries, uint32_t q, uint32_t k, uint32_t nprobe,
                       uint64_t max_scan_count, float threshold, const uint32_t *filter_bitmap, uint64_t *out_keys,
                       float *out_scores, uint32_t *out_index, uint32_t *out_counts) {
+  if (!c) return set_err(ZVB200_ERR_INVALID_ARGUMENT, "null argument");
+  std::shared_lock<std::shared_mutex> rl(c->s->mu);
   int r = check_search_args(c, queries, q, k);
   if (r != 0) return r;
   if (!out_scores) return set_err(ZVB200_ERR_INVALID_ARGUMENT, "null out_scores");
@@ -975,6 +984,8 @@ int zvb200_reform_queries_device(zvb200_ctx *c, const float *queries_fp32_dev, u
 int zvb200_search_fp32(zvb200_ctx *c, const float *queries_fp32, uint32_t q, uint32_t dim, uint32_t k, float threshold,
                        const uint32_t *filter, uint64_t *out_keys, float *out_scores, uint32_t *out_index,
                        uint32_t *out_counts) {
+  if (!c) return set_err(ZVB200_ERR_INVALID_ARGUMENT, "null argument");
+  std::shared_lock<std::shared_mutex> rl(c->s->mu);
   int r = check_search_args(c, queries_fp32, q, k);
   if (r != 0) return r;
   if (!out_scores) return set_err(ZVB200_ERR_INVALID_ARGUMENT, "null out_scores");
@@ -997,6 +1008,8 @@ int zvb200_search_fp32(zvb200_ctx *c, const float *queries_fp32, uint32_t q, uin
 int zvb200_search_rows(zvb200_ctx *c, const void *queries, uint32_t q, const uint32_t *rows, uint32_t m, uint32_t k,
                        float threshold, const uint32_t *filter, uint64_t *out_keys, float *out_scores,
                        uint32_t *out_index, uint32_t *out_counts) {
+  if (!c) return set_err(ZVB200_ERR_INVALID_ARGUMENT, "null argument");
+  std::shared_lock<std::shared_mutex> rl(c->s->mu);
   int r = check_search_args(c, queries, q, k);
   if (r != 0) return r;
   if (!out_scores || (!rows && q && m)) return set_err(ZVB200_ERR_INVALID_ARGUMENT, "null argument");
@@ -1026,6 +1039,10 @@ int zvb200_search_rows(zvb200_ctx *c, const void *queries, uint32_t q, const uin
 int zvb200_search_refined(zvb200_ctx *coarse, zvb200_ctx *exact, const float *queries_fp32, uint32_t q, uint32_t dim,
                           uint32_t k, float scale_factor, const uint32_t *filter, uint64_t *out_keys, float *out_scores,
                           uint32_t *out_index, uint32_t *out_counts) {
+  if (!coarse || !exact) return set_err(ZVB200_ERR_INVALID_ARGUMENT, "null argument");
+  std::shared_lock<std::shared_mutex> rl1(coarse->s->mu);
+  std::shared_lock<std::shared_mutex> rl2;
+  if (exact->s != coarse->s) rl2 = std::shared_lock<std::shared_mutex>(exact->s->mu);
   int r = check_search_args(coarse, queries_fp32, q, k);
   if (r == 0) r = check_search_args(exact, queries_fp32, q, k);
   if (r != 0) return r;
@@ -1078,7 +1095,7 @@ int zvb200_search_refined(zvb200_ctx *coarse, zvb200_ctx *exact, const float *qu
 // over a store of the current centroids (queries = the rows, 18 944 per tcgen05 launch) + the update kernels.
 
 static void store_reset(zvb200_store *s) {
-  std::lock_guard<std::mutex> g(s->mu);
+  std::lock_guard<std::shared_mutex> g(s->mu);
   s->n = 0; s->normed = 0; s->shadowed = 0;
   s->keys.clear(); s->drop_host.clear();
   s->has_drop = false; s->drop_dirty = false; s->sealed = false;
