@@ -46,6 +46,8 @@ struct zvb200_store {
   uint8_t *shadow = nullptr;      // QuantizedInteger L2: bf16 operands of the tensor-core filter (built at seal)
   uint32_t shadow_k = 0;
   uint64_t shadowed = 0;
+  float *shadow_mmax_dev = nullptr;  // running maximum of the rows' margin shares
+  float shadow_mrow_max = 0.f;
   uint32_t *drop = nullptr;       // device bitmap (allocated lazily)
   uint64_t drop_words = 0;
   uint64_t n = 0, cap = 0, normed = 0;
@@ -72,7 +74,7 @@ struct zvb200_store {
     v.rows = rows; v.n = n; v.row_stride = row_stride; v.chunks = chunks; v.d = d;
     v.dtype = dtype; v.metric = metric; v.tails = tails; v.norms = norms;
     v.drop = has_drop ? drop : nullptr;
-    if (shadow && shadowed >= n) { v.shadow = shadow; v.shadow_k = shadow_k; }
+    if (shadow && shadowed >= n) { v.shadow = shadow; v.shadow_k = shadow_k; v.shadow_mrow_max = shadow_mrow_max; }
     return v;
   }
 };
@@ -216,6 +218,7 @@ int zvb200_store_destroy(zvb200_store *s) {
   if (s->tails) cudaFree(s->tails);
   if (s->norms) cudaFree(s->norms);
   if (s->shadow) cudaFree(s->shadow);
+  if (s->shadow_mmax_dev) cudaFree(s->shadow_mmax_dev);
   if (s->drop) cudaFree(s->drop);
   if (s->list_off_dev) cudaFree(s->list_off_dev);
   if (s->budget_dev) cudaFree(s->budget_dev);
@@ -346,9 +349,14 @@ int zvb200_store_seal(zvb200_store *s) {
         s->shadow = nullptr;
       }
     }
+    if (s->shadow && !s->shadow_mmax_dev) {
+      CU(cudaMalloc((void **)&s->shadow_mmax_dev, sizeof(float)));
+      CU(cudaMemset(s->shadow_mmax_dev, 0, sizeof(float)));
+    }
     if (s->shadow && s->shadowed < s->n) {
       RowsView v = s->view();
-      CU(launch_qi8_shadow_rows(v, s->shadowed, s->n, s->shadow, s->shadow_k, s->stream));
+      CU(launch_qi8_shadow_rows(v, s->shadowed, s->n, s->shadow, s->shadow_k, s->shadow_mmax_dev, s->stream));
+      CU(cudaMemcpyAsync(&s->shadow_mrow_max, s->shadow_mmax_dev, sizeof(float), cudaMemcpyDeviceToHost, s->stream));
       CU(cudaStreamSynchronize(s->stream));
       s->shadowed = s->n;
     }
@@ -392,7 +400,8 @@ int zvb200_store_write(zvb200_store *s, uint64_t row, const void *vec, uint64_t 
   }
   if (s->shadow && row < s->shadowed) {
     RowsView v = s->view();
-    CU(launch_qi8_shadow_rows(v, row, row + 1, s->shadow, s->shadow_k, s->stream));
+    CU(launch_qi8_shadow_rows(v, row, row + 1, s->shadow, s->shadow_k, s->shadow_mmax_dev, s->stream));
+    CU(cudaMemcpyAsync(&s->shadow_mrow_max, s->shadow_mmax_dev, sizeof(float), cudaMemcpyDeviceToHost, s->stream));
   }
   CU(cudaStreamSynchronize(s->stream));
   if (s->keys.empty() && key != row) { s->keys.resize(s->n); for (uint64_t i = 0; i < s->n; ++i) s->keys[i] = i; }

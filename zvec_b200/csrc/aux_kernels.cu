@@ -133,7 +133,7 @@ __device__ __forceinline__ void bf16_split(float x, __nv_bfloat16 *hi, __nv_bflo
 }
 
 __global__ void qi8_shadow_rows_kernel(RowsView rv, uint64_t row_begin, uint64_t row_end, uint8_t *shadow,
-                                       uint32_t shadow_k) {
+                                       uint32_t shadow_k, float *mrow_max) {
   const uint32_t cpr = shadow_k / 8;  // 16-byte output chunks per row
   const uint64_t idx = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
   const uint64_t r = row_begin + idx / cpr;
@@ -155,7 +155,10 @@ __global__ void qi8_shadow_rows_kernel(RowsView rv, uint64_t row_begin, uint64_t
         const float dq = (float)d;
         const float t1 = m.x * m.x * m.w, mbd = m.y * m.y * dq, msma = m.z * m.x;
         const float c0 = t1 + mbd + 2.0f * m.y * msma;
-        const float u1 = -(c0 - qi8_shadow_eps(d) * (t1 + mbd));
+        const float mrow = qi8_shadow_eps(d) * (t1 + mbd);
+        const float u1 = -(c0 - mrow);
+        // the largest margin of any row: non-negative floats order like their bit patterns
+        if (i == d && mrow == mrow) atomicMax(reinterpret_cast<int *>(mrow_max), __float_as_int(mrow));
         bf16_split(u1, &ex[0], &ex[2]); ex[1] = ex[0];
         bf16_split(m.y, &ex[3], &ex[5]); ex[4] = ex[3];
         bf16_split(msma, &ex[6], &ex[8]); ex[7] = ex[6];
@@ -414,14 +417,14 @@ cudaError_t launch_row_norms(const RowsView &rv, uint64_t row_begin, uint64_t ro
 }
 
 cudaError_t launch_qi8_shadow_rows(const RowsView &rv, uint64_t row_begin, uint64_t row_end, uint8_t *shadow,
-                                   uint32_t shadow_k, cudaStream_t st) {
+                                   uint32_t shadow_k, float *mrow_max, cudaStream_t st) {
   if (row_end <= row_begin) return cudaSuccess;
   const uint64_t cpr = shadow_k / 8;
   const uint64_t per_launch = ((uint64_t)1 << 31) / 256 * 256 / cpr;  // rows per launch: grid.x stays below 2^31
   for (uint64_t r0 = row_begin; r0 < row_end; r0 += per_launch) {
     const uint64_t r1 = std::min(row_end, r0 + per_launch);
     const uint64_t threads = (r1 - r0) * cpr;
-    qi8_shadow_rows_kernel<<<(unsigned)((threads + 255) / 256), 256, 0, st>>>(rv, r0, r1, shadow, shadow_k);
+    qi8_shadow_rows_kernel<<<(unsigned)((threads + 255) / 256), 256, 0, st>>>(rv, r0, r1, shadow, shadow_k, mrow_max);
     count_launch();
   }
   return cudaGetLastError();

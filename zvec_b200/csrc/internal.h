@@ -27,6 +27,7 @@ struct RowsView {
   // terms), shadow_k halves per row — what the tcgen05 scan contracts instead of the int8 codes (scan_mma.cu)
   const uint8_t *shadow = nullptr;
   uint32_t shadow_k = 0;
+  float shadow_mrow_max = 0.f;      // largest row share of the shadow filter's margin (the first-tile bootstrap's bound)
 };
 
 // Queries in "compute layout", produced by prep_queries() on the device.
@@ -99,7 +100,7 @@ cudaError_t launch_row_norms(const RowsView &rv, uint64_t row_begin, uint64_t ro
 // QuantizedInteger L2 shadow operands (aux_kernels.cu): rows [row_begin, row_end) of the store, and a query batch
 inline uint32_t qi8_shadow_k(uint32_t d) { return (d + 9u + 63u) & ~63u; }
 cudaError_t launch_qi8_shadow_rows(const RowsView &rv, uint64_t row_begin, uint64_t row_end, uint8_t *shadow,
-                                   uint32_t shadow_k, cudaStream_t st);
+                                   uint32_t shadow_k, float *mrow_max /* device, running maximum */, cudaStream_t st);
 cudaError_t launch_qi8_shadow_queries(const RowsView &rv, const uint8_t *qraw, const float4 *qtails, uint32_t q,
                                       uint8_t *out, uint32_t shadow_k, cudaStream_t st);
 cudaError_t launch_distance_matrix(const RowsView &rv, const QueryView &qv, float *out,

@@ -73,6 +73,7 @@ struct MmaArgs {
   uint32_t *pub;        // [groups][nq] ordered image of each CTA's pub_j-th best score per query
   uint32_t pub_j;       // which list entry a CTA publishes (1-based)
   uint32_t pub_m;       // pub_m * pub_j >= k: the pub_m-th smallest published score bounds the global k-th best
+  float sh_mrow_max;    // KIND 3: largest row share of the filter margin in the store (bootstrap bound)
   int dbg;              // ZVB200_MMA_DEBUG probes (perf triage only): 1 no epilogue, 2 no TMA, 4 A only, 8 B only, 16 no slow path
 };
 
@@ -699,7 +700,7 @@ scan_mma_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
     };
     uint32_t next_eval = 1;
     // the first-tile bootstrap needs every row of that tile to be a live row
-    const bool boot = !(KIND == 2 && imode == 7) && !SH && a.groups > 1 && pubj <= 8 && !a.drop && !a.filter && ntl > 1 &&
+    const bool boot = !(KIND == 2 && imode == 7) && a.groups > 1 && pubj <= 8 && !a.drop && !a.filter && ntl > 1 &&
                       a.row_begin + (t_begin + 1) * kBN <= a.row_end && !(a.dbg & (1 | 16 | 32 | 64));
     const bool prof = (a.dbg & 128) != 0;  // triage: where the epilogue's cycles go (printed by CTA 0)
     long long c_wait = 0, c_slow = 0, c_ub = 0, c_t0 = 0, c_first4 = 0, c_tiles = 0, c_ex = 0, c_acc = 0, c_ld1 = 0;
@@ -745,7 +746,11 @@ scan_mma_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
           }
           const float mx = max32(v);
           float su;  // an upper bound of the exact score of the chunk's best row
-          if (mode == 0) su = root6 ? sqrtf(-mx) : -mx;
+          if (SH) {
+            // g nQa = (Q0 - s) + Mrow +- (Mrow + Mthr)  =>  s <= Q0 - g nQa + 2 Mrow + Mthr, Mrow <= the store's largest
+            su = Q0 - nQa * mx + 2.0f * a.sh_mrow_max + Mthr;
+            su += (fabsf(Q0) + fabsf(nQa * mx) + a.sh_mrow_max + Mthr) * 1e-6f;
+          } else if (mode == 0) su = root6 ? sqrtf(-mx) : -mx;
           else if (mode == 1) su = 1.0f - mx;
           else {
             su = mode == 2 ? 2.0f * ((1.0f + a.eps) * hq - mx) : (mode == 3 ? -mx : 1.0f - mx) + a.eps * hq;
@@ -1062,6 +1067,7 @@ cudaError_t launch_scan_mma(const RowsView &rv, const QueryView &qv, const Searc
   // fp32 accumulation of d exact products (fp16 inputs), plus two 10-bit-mantissa operands for tf32
   // (2x headroom on the accumulation term: the tensor core's internal alignment of partial sums is not IEEE)
   a.eps = (float)rv.d * 4.8e-7f + (f32 ? 2.2e-3f : 0.f);
+  a.sh_mrow_max = rv.shadow_mrow_max;
   a.threshold = sp.threshold;
   a.drop = rv.drop; a.filter = sp.filter;
   a.part = part;
