@@ -198,6 +198,23 @@ int zvb200_ivf_search(zvb200_ctx *c, const void *queries, uint32_t q, uint32_t k
                       uint32_t nprobe, uint64_t max_scan_count, float threshold,
                       const uint32_t *filter_bitmap, uint64_t *out_keys, float *out_scores,
                       uint32_t *out_index, uint32_t *out_counts);
+/* The same search with queries, filter and outputs on the device, asynchronous on the context's stream (the
+ * multi-GPU layer: per-shard results stay on the GPU for the exchange). */
+int zvb200_ivf_search_device(zvb200_ctx *c, const void *queries_dev, uint32_t q, uint32_t k,
+                             uint32_t nprobe, uint64_t max_scan_count, float threshold,
+                             const uint32_t *filter_dev, float *out_scores_dev, uint32_t *out_index_dev);
+/* Sharded IVF, the merge on the device: list_global_base[l] = row of the WHOLE index (lists in order, each list's
+ * rows in order) at which this store's slice of list l starts.  zvb200_ivf_global_rows_device maps local result
+ * rows to rows of the whole index (ZVB200_INVALID_INDEX -> ZVB200_INVALID_KEY); after the all-gather,
+ * zvb200_merge_topk_rows_device merges G lists [g][q][k] of (score, global row) by that pair — the result of the
+ * unsharded zvb200_ivf_search, bit for bit (CombinedVectorColumnIndexer::Search's concat + sort + truncate,
+ * combined_vector_column_indexer.cc:167-222, with the row-index tie-break kept global). */
+int zvb200_ivf_set_global_bases(zvb200_store *s, const uint64_t *list_global_base);
+int zvb200_ivf_global_rows_device(zvb200_ctx *c, const uint32_t *index_dev, uint64_t count,
+                                  uint64_t *out_rows_dev);
+int zvb200_merge_topk_rows_device(zvb200_ctx *c, const float *scores_dev, const uint64_t *rows_dev,
+                                  uint32_t g, uint32_t q, uint32_t k, float *out_scores_dev,
+                                  uint64_t *out_rows_dev);
 /* threshold / filter_bitmap as in zvb200_search (bit i = drop stored row i, list order): a filtered list
  * still counts whole against the scan budget, like IVFEntity::search(list, query, filter, ...)
  * (ivf_entity.cc:587-659). */

@@ -173,6 +173,27 @@ def test_sharded_ivf_search_equals_unsharded(world):
         assert np.array_equal(ms[j][:nv].view(np.uint32), es[j][:nv].view(np.uint32))
         assert np.array_equal(mr[j][:nv], ei[j][:nv].astype(np.uint64))
         assert np.isnan(ms[j][nv:]).all()
+    # the same exchange without leaving the device: per-shard zvb200_ivf_search_device, local -> global rows through
+    # the per-list bases, one merge kernel by (score, global row)
+    import torch
+    dev = torch.device("cuda", 0)
+    dq = torch.from_numpy(qs).to(dev)
+    g_s = torch.empty((world, q, k), dtype=torch.float32, device=dev)
+    g_i = torch.empty((world, q, k), dtype=torch.int32, device=dev)
+    g_r = torch.empty((world, q, k), dtype=torch.int64, device=dev)
+    torch.cuda.synchronize()
+    for r, (st, c) in enumerate(keep):
+        lo, hi, local = sharding.ivf_shard_plan(off, r, world)
+        st.ivf_set_global_bases(lo.astype(np.uint64))
+        c.ivf_search_device(dq.data_ptr(), q, k, nprobe, max_scan, g_s[r].data_ptr(), g_i[r].data_ptr())
+        c.ivf_global_rows_device(g_i[r].data_ptr(), q * k, g_r[r].data_ptr())
+        c.sync()
+    f_s = torch.empty((q, k), dtype=torch.float32, device=dev)
+    f_r = torch.empty((q, k), dtype=torch.int64, device=dev)
+    c0 = keep[0][1]
+    c0.merge_topk_rows_device(g_s.data_ptr(), g_r.data_ptr(), world, q, k, f_s.data_ptr(), f_r.data_ptr()); c0.sync()
+    ds, dr = f_s.cpu().numpy(), f_r.cpu().numpy().view(np.uint64)
+    assert np.array_equal(ds.view(np.uint32), ms.view(np.uint32)) and np.array_equal(dr, mr)
     for st, c in keep:
         c.close(); st.close()
     cw.close(); whole.close()

@@ -69,27 +69,35 @@ if mode == "ivf":
     qsel = torch.randint(0, nlist, (batch,), generator=gq, device=dev)
     q = centres[qsel] + 0.3 * torch.randn((batch, dim), generator=gq, device=dev)
     qn = q.norm(dim=1, keepdim=True)
-    hq = torch.cat([q / qn, qn], dim=1).cpu().numpy()
+    hq = torch.cat([q / qn, qn], dim=1).contiguous()               # pinned-host -> device inside the step (e2e)
+    hq_host = hq.cpu().pin_memory()
+    st.ivf_set_global_bases(lo.astype(np.uint64))
     scan = []
+    dq = torch.empty_like(hq)
+    l_s = torch.empty((batch, k), dtype=torch.float32, device=dev); l_i = torch.empty((batch, k), dtype=torch.int32, device=dev)
+    l_r = torch.empty((batch, k), dtype=torch.int64, device=dev)
+    a_s = torch.empty((world, batch, k), dtype=torch.float32, device=dev); a_r = torch.empty((world, batch, k), dtype=torch.int64, device=dev)
+    f_s = torch.empty((batch, k), dtype=torch.float32, device=dev); f_r = torch.empty((batch, k), dtype=torch.int64, device=dev)
 
     def step():
-        _, s, i, _ = ctx.ivf_search(hq, k, nprobe, max_scan)
+        # everything stays on the device: search, local -> global rows, all-gather, merge by (score, global row)
+        dq.copy_(hq_host, non_blocking=True); torch.cuda.synchronize()
+        ctx.ivf_search_device(dq.data_ptr(), batch, k, nprobe, max_scan, l_s.data_ptr(), l_i.data_ptr())
+        ctx.ivf_global_rows_device(l_i.data_ptr(), batch * k, l_r.data_ptr())
+        ctx.sync()
         scan.append(ctx.last_scan_ms())
-        gr = sharding.ivf_local_to_global(i, lo, loff)
         if world > 1:
-            ts = torch.from_numpy(s).to(dev); tr = torch.from_numpy(gr.view(np.int64)).to(dev)
-            a_s = torch.empty((world,) + ts.shape, dtype=ts.dtype, device=dev); a_r = torch.empty((world,) + tr.shape, dtype=tr.dtype, device=dev)
-            dist.all_gather_into_tensor(a_s.view(world * batch, k), ts); dist.all_gather_into_tensor(a_r.view(world * batch, k), tr)
-            if rank == 0:
-                return sharding.merge_topk_global(a_s.cpu().numpy(), a_r.cpu().numpy().view(np.uint64), k)
-            return None
-        return s, gr
+            dist.all_gather_into_tensor(a_s.view(world * batch, k), l_s); dist.all_gather_into_tensor(a_r.view(world * batch, k), l_r)
+            torch.cuda.synchronize()
+            ctx.merge_topk_rows_device(a_s.data_ptr(), a_r.data_ptr(), world, batch, k, f_s.data_ptr(), f_r.data_ptr()); ctx.sync()
+            return f_s.cpu(), f_r.cpu()
+        return l_s.cpu(), l_r.cpu()
 
     ms = timed(step, 5) * 1e3
     if rank == 0:
         print(json.dumps({"workload": "IVF nlist %d nprobe %d fp32 cosine %dx%d, every list sharded over %d GPU(s), batch %d" % (nlist, nprobe, rows, dim, world, batch),
                           "n_gpus": world, "qps_e2e": batch / (ms / 1e3), "ms_per_batch": ms, "list_scan_ms_rank0": float(np.mean(scan[3:])),
-                          "merge": "host numpy (score, global row)"}))
+                          "merge": "device: zvb200_ivf_global_rows_device + NCCL all-gather + zvb200_merge_topk_rows_device"}))
 else:
     rows = int(sys.argv[2]) if len(sys.argv) > 2 else 10_000_000
     batch = int(sys.argv[3]) if len(sys.argv) > 3 else 64

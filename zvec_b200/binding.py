@@ -67,6 +67,12 @@ _SIGS = {
     "zvb200_ivf_set_budget_sizes": (C.c_int, [C.c_void_p, C.c_void_p]),
     "zvb200_ivf_search": (C.c_int, [C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint64, C.c_float,
                                     C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "zvb200_ivf_search_device": (C.c_int, [C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint64,
+                                           C.c_float, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "zvb200_ivf_set_global_bases": (C.c_int, [C.c_void_p, C.c_void_p]),
+    "zvb200_ivf_global_rows_device": (C.c_int, [C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p]),
+    "zvb200_merge_topk_rows_device": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32,
+                                                C.c_void_p, C.c_void_p]),
     "zvb200_reform_queries": (C.c_int, [C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_void_p]),
     "zvb200_reform_queries_device": (C.c_int, [C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_void_p]),
     "zvb200_search_fp32": (C.c_int, [C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32, C.c_float, C.c_void_p,
@@ -172,6 +178,10 @@ class Store:
         ls = None if list_sizes is None else np.ascontiguousarray(list_sizes, np.uint64)
         _check(lib().zvb200_ivf_set_budget_sizes(self.h, _ptr(ls)))
 
+    def ivf_set_global_bases(self, list_global_base):
+        gb = None if list_global_base is None else np.ascontiguousarray(list_global_base, np.uint64)
+        _check(lib().zvb200_ivf_set_global_bases(self.h, _ptr(gb)))
+
     def write(self, row, vec, key):
         """overwrite one row in place (FlatStreamerEntity::add_vector_with_id, id < count)"""
         vec = np.ascontiguousarray(vec)
@@ -253,6 +263,19 @@ class Context:
         _check(lib().zvb200_ivf_search(self.h, _ptr(queries), q, k, nprobe, max_scan_count, threshold,
                                        _ptr(filter_bitmap), _ptr(keys), _ptr(scores), _ptr(index), _ptr(counts)))
         return keys, scores, index, counts
+
+    def ivf_search_device(self, queries_ptr, q, k, nprobe, max_scan_count, out_scores_ptr, out_index_ptr,
+                          threshold=FLT_MAX, filter_ptr=None):
+        _check(lib().zvb200_ivf_search_device(self.h, C.c_void_p(queries_ptr), q, k, nprobe, max_scan_count, threshold,
+                                              C.c_void_p(filter_ptr) if filter_ptr else None,
+                                              C.c_void_p(out_scores_ptr), C.c_void_p(out_index_ptr)))
+
+    def ivf_global_rows_device(self, index_ptr, count, out_rows_ptr):
+        _check(lib().zvb200_ivf_global_rows_device(self.h, C.c_void_p(index_ptr), count, C.c_void_p(out_rows_ptr)))
+
+    def merge_topk_rows_device(self, scores_ptr, rows_ptr, g, q, k, out_scores_ptr, out_rows_ptr):
+        _check(lib().zvb200_merge_topk_rows_device(self.h, C.c_void_p(scores_ptr), C.c_void_p(rows_ptr), g, q, k,
+                                                   C.c_void_p(out_scores_ptr), C.c_void_p(out_rows_ptr)))
 
     def fuse_rrf(self, keys, counts, topn, rank_constant=60):
         """RrfReRanker.rerank over F per-field lists: keys [F][q][k] u64, counts [F][q] -> (keys, fp64 scores, counts)."""

@@ -62,6 +62,7 @@ struct zvb200_store {
   std::vector<uint64_t> list_offsets;
   uint32_t *list_off_dev = nullptr;  // [nlist+1] first row of each posting list
   uint32_t *budget_dev = nullptr;    // [nlist] list sizes in the whole index (sharded IVF), or null
+  uint64_t *gbase_dev = nullptr;     // [nlist] row of the whole index where this store's slice of each list starts
   uint32_t nlist = 0;
   // writers (append / seal / write / set_deleted / attach) exclusive; the host-synchronous searches shared, from the
   // first look at the store to the stream sync that ends them: an append that re-allocates the rows (store_grow)
@@ -222,6 +223,7 @@ int zvb200_store_destroy(zvb200_store *s) {
   if (s->drop) cudaFree(s->drop);
   if (s->list_off_dev) cudaFree(s->list_off_dev);
   if (s->budget_dev) cudaFree(s->budget_dev);
+  if (s->gbase_dev) cudaFree(s->gbase_dev);
   if (s->staging) cudaFree(s->staging);
   if (s->stream) cudaStreamDestroy(s->stream);
   delete s;
@@ -849,6 +851,7 @@ int zvb200_ivf_attach(zvb200_store *s, const void *centroids, uint32_t nlist, co
   if (s->centroids) zvb200_store_destroy(s->centroids);
   if (s->list_off_dev) cudaFree(s->list_off_dev);
   if (s->budget_dev) { cudaFree(s->budget_dev); s->budget_dev = nullptr; }
+  if (s->gbase_dev) { cudaFree(s->gbase_dev); s->gbase_dev = nullptr; }
   s->centroids = cs; s->list_off_dev = d; s->nlist = nlist;
   s->list_offsets.assign(list_offsets, list_offsets + nlist + 1);
   return 0;
@@ -867,39 +870,22 @@ int zvb200_ivf_set_budget_sizes(zvb200_store *s, const uint64_t *list_sizes) {
   return 0;
 }
 
-int zvb200_ivf_search(zvb200_ctx *c, const void *queries, uint32_t q, uint32_t k, uint32_t nprobe,
-                      uint64_t max_scan_count, float threshold, const uint32_t *filter_bitmap, uint64_t *out_keys,
-                      float *out_scores, uint32_t *out_index, uint32_t *out_counts) {
-  if (!c) return set_err(ZVB200_ERR_INVALID_ARGUMENT, "null argument");
-  std::shared_lock<std::shared_mutex> rl(c->s->mu);
-  int r = check_search_args(c, queries, q, k);
-  if (r != 0) return r;
-  if (!out_scores) return set_err(ZVB200_ERR_INVALID_ARGUMENT, "null out_scores");
+// coarse search -> list plan -> posting-list scan -> merge, everything on the context's stream; queries, filter and
+// outputs on the device
+static int ivf_core(zvb200_ctx *c, const void *queries_dev, uint32_t q, uint32_t k, uint32_t nprobe,
+                    uint64_t max_scan_count, float threshold, const uint32_t *filter_dev, float *out_scores_dev,
+                    uint32_t *out_index_dev) {
   zvb200_store *s = c->s;
-  if (!s->centroids) return set_err(ZVB200_ERR_NOREADY, "no IVF structure attached");
-  if (nprobe == 0 || nprobe > ZVB200_MAX_TOPK) return set_err(ZVB200_ERR_INVALID_ARGUMENT, "nprobe must be 1..1024");
-  if (q == 0) return 0;
-  nprobe = std::min(nprobe, s->nlist);
-  CU(cudaSetDevice(s->device));
-  const size_t qbytes = (size_t)q * s->elem_bytes, nres = (size_t)q * k;
-  CU(c->h_q.ensure(qbytes));
-  CU(c->qin.ensure(qbytes));
-  CU(c->out_scores.ensure(nres * 4));
-  CU(c->out_index.ensure(nres * 4));
-  CU(c->h_scores.ensure(nres * 4));
-  CU(c->h_index.ensure(nres * 4));
   CU(c->coarse_scores.ensure((size_t)q * nprobe * 4));
   CU(c->coarse_index.ensure((size_t)q * nprobe * 4));
   CU(c->seg_prefix.ensure((size_t)q * (nprobe + 1) * 4));
   CU(c->seg_row.ensure((size_t)q * nprobe * 4));
   CU(c->seg_count.ensure((size_t)q * 4));
-  memcpy(c->h_q.p, queries, qbytes);
-  CU(cudaMemcpyAsync(c->qin.p, c->h_q.p, qbytes, cudaMemcpyHostToDevice, c->stream));
   // 1. coarse: top-nprobe centroids per query (IVFCentroidIndex::search, ivf_centroid_index.cc:273-295)
   const int keep = c->force_kernel;
   if (keep == 3 || keep == 5) c->force_kernel = 0;
-  r = search_core(c, s->centroids, c->qin.p, q, nprobe, FLT_MAX, nullptr, (float *)c->coarse_scores.p,
-                  (uint32_t *)c->coarse_index.p, 0, s->centroids->n);
+  int r = search_core(c, s->centroids, queries_dev, q, nprobe, FLT_MAX, nullptr, (float *)c->coarse_scores.p,
+                      (uint32_t *)c->coarse_index.p, 0, s->centroids->n);
   c->force_kernel = keep;
   if (r != 0) return r;
   // 2. which lists each query scans under the budget (ivf_searcher.cc:216-231)
@@ -908,13 +894,7 @@ int zvb200_ivf_search(zvb200_ctx *c, const void *queries, uint32_t q, uint32_t k
   // 3. posting-list scan, queries already in compute layout (same dtype / metric / dim as the centroids)
   RowsView rv = s->view();
   SearchParams sp;
-  sp.k = k; sp.threshold = threshold; sp.filter = nullptr;
-  if (filter_bitmap) {
-    const size_t fb = (size_t)((s->n + 31) / 32) * 4;
-    CU(c->filter.ensure(fb));
-    CU(cudaMemcpyAsync(c->filter.p, filter_bitmap, fb, cudaMemcpyHostToDevice, c->stream));
-    sp.filter = (const uint32_t *)c->filter.p;
-  }
+  sp.k = k; sp.threshold = threshold; sp.filter = filter_dev;
   const bool lists_stream = c->force_kernel == 4 && scan_stream_supports(rv, k, nprobe);
   const size_t parts = lists_stream ? scan_lists_stream_parts(q, s->sm_count) : scan_lists_parts(q, s->sm_count);
   CU(c->part.ensure((size_t)q * parts * k * sizeof(u64)));
@@ -930,9 +910,91 @@ int zvb200_ivf_search(zvb200_ctx *c, const void *queries, uint32_t q, uint32_t k
                          (const uint32_t *)c->seg_count.p, nprobe, (u64 *)c->part.p, &nparts, s->sm_count, c->stream));
   CU(cudaEventRecord(c->ev_scan1, c->stream));
   c->last_kernel = lists_stream ? "scan_lists_stream" : "scan_lists";
-  CU(launch_merge_parts((const u64 *)c->part.p, nparts, q, k, (float *)c->out_scores.p, (uint32_t *)c->out_index.p,
-                        c->stream));
+  CU(launch_merge_parts((const u64 *)c->part.p, nparts, q, k, out_scores_dev, out_index_dev, c->stream));
+  return 0;
+}
+
+static int ivf_check(zvb200_ctx *c, const void *queries, uint32_t q, uint32_t k, uint32_t *nprobe) {
+  int r = check_search_args(c, queries, q, k);
+  if (r != 0) return r;
+  if (!c->s->centroids) return set_err(ZVB200_ERR_NOREADY, "no IVF structure attached");
+  if (*nprobe == 0 || *nprobe > ZVB200_MAX_TOPK) return set_err(ZVB200_ERR_INVALID_ARGUMENT, "nprobe must be 1..1024");
+  *nprobe = std::min(*nprobe, c->s->nlist);
+  return 0;
+}
+
+int zvb200_ivf_search(zvb200_ctx *c, const void *queries, uint32_t q, uint32_t k, uint32_t nprobe,
+                      uint64_t max_scan_count, float threshold, const uint32_t *filter_bitmap, uint64_t *out_keys,
+                      float *out_scores, uint32_t *out_index, uint32_t *out_counts) {
+  if (!c) return set_err(ZVB200_ERR_INVALID_ARGUMENT, "null argument");
+  std::shared_lock<std::shared_mutex> rl(c->s->mu);
+  int r = ivf_check(c, queries, q, k, &nprobe);
+  if (r != 0) return r;
+  if (!out_scores) return set_err(ZVB200_ERR_INVALID_ARGUMENT, "null out_scores");
+  zvb200_store *s = c->s;
+  if (q == 0) return 0;
+  CU(cudaSetDevice(s->device));
+  const size_t qbytes = (size_t)q * s->elem_bytes, nres = (size_t)q * k;
+  CU(c->h_q.ensure(qbytes));
+  CU(c->qin.ensure(qbytes));
+  CU(c->out_scores.ensure(nres * 4));
+  CU(c->out_index.ensure(nres * 4));
+  CU(c->h_scores.ensure(nres * 4));
+  CU(c->h_index.ensure(nres * 4));
+  memcpy(c->h_q.p, queries, qbytes);
+  CU(cudaMemcpyAsync(c->qin.p, c->h_q.p, qbytes, cudaMemcpyHostToDevice, c->stream));
+  const uint32_t *fdev = nullptr;
+  if (filter_bitmap) {
+    const size_t fb = (size_t)((s->n + 31) / 32) * 4;
+    CU(c->filter.ensure(fb));
+    CU(cudaMemcpyAsync(c->filter.p, filter_bitmap, fb, cudaMemcpyHostToDevice, c->stream));
+    fdev = (const uint32_t *)c->filter.p;
+  }
+  r = ivf_core(c, c->qin.p, q, k, nprobe, max_scan_count, threshold, fdev, (float *)c->out_scores.p,
+               (uint32_t *)c->out_index.p);
+  if (r != 0) return r;
   return finish_results(c, s, q, k, out_keys, out_scores, out_index, out_counts);
+}
+
+int zvb200_ivf_search_device(zvb200_ctx *c, const void *queries_dev, uint32_t q, uint32_t k, uint32_t nprobe,
+                             uint64_t max_scan_count, float threshold, const uint32_t *filter_dev,
+                             float *out_scores_dev, uint32_t *out_index_dev) {
+  if (!c) return set_err(ZVB200_ERR_INVALID_ARGUMENT, "null argument");
+  int r = ivf_check(c, queries_dev, q, k, &nprobe);
+  if (r != 0) return r;
+  if (!out_scores_dev || !out_index_dev) return set_err(ZVB200_ERR_INVALID_ARGUMENT, "null output");
+  if (q == 0) return 0;
+  CU(cudaSetDevice(c->s->device));
+  return ivf_core(c, queries_dev, q, k, nprobe, max_scan_count, threshold, filter_dev, out_scores_dev, out_index_dev);
+}
+
+int zvb200_ivf_set_global_bases(zvb200_store *s, const uint64_t *list_global_base) {
+  if (!s || !s->centroids) return set_err(ZVB200_ERR_NOREADY, "no IVF structure attached");
+  std::lock_guard<std::shared_mutex> g(s->mu);
+  CU(cudaSetDevice(s->device));
+  if (s->gbase_dev) { cudaFree(s->gbase_dev); s->gbase_dev = nullptr; }
+  if (!list_global_base) return 0;
+  CU(cudaMalloc((void **)&s->gbase_dev, (size_t)s->nlist * 8));
+  CU(cudaMemcpy(s->gbase_dev, list_global_base, (size_t)s->nlist * 8, cudaMemcpyHostToDevice));
+  return 0;
+}
+
+int zvb200_ivf_global_rows_device(zvb200_ctx *c, const uint32_t *index_dev, uint64_t count, uint64_t *out_rows_dev) {
+  if (!c || !index_dev || !out_rows_dev) return set_err(ZVB200_ERR_INVALID_ARGUMENT, "null argument");
+  zvb200_store *s = c->s;
+  if (!s->centroids || !s->gbase_dev) return set_err(ZVB200_ERR_NOREADY, "no global list bases set");
+  CU(cudaSetDevice(s->device));
+  CU(launch_ivf_global_rows(index_dev, count, s->list_off_dev, s->gbase_dev, s->nlist, out_rows_dev, c->stream));
+  return 0;
+}
+
+int zvb200_merge_topk_rows_device(zvb200_ctx *c, const float *scores_dev, const uint64_t *rows_dev, uint32_t g,
+                                  uint32_t q, uint32_t k, float *out_scores_dev, uint64_t *out_rows_dev) {
+  if (!c || !scores_dev || !rows_dev || !out_scores_dev || !out_rows_dev || g == 0 || k == 0)
+    return set_err(ZVB200_ERR_INVALID_ARGUMENT, "bad argument");
+  CU(cudaSetDevice(c->s->device));
+  CU(launch_merge_rows(scores_dev, rows_dev, g, q, k, out_scores_dev, out_rows_dev, c->stream));
+  return 0;
 }
 
 // ---- query reformers and the refiner --------------------------------------------------

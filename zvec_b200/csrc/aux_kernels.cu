@@ -317,6 +317,61 @@ __global__ void merge_shards_kernel(const float *scores, const uint32_t *index, 
   }
 }
 
+// K5c: the same merge for lists that carry explicit rows of the whole index (sharded IVF: a shard's local rows
+// map to global rows list by list).  Every list is ascending by (score, row); rank by that pair.
+__global__ void merge_rows_kernel(const float *scores, const uint64_t *rows, uint32_t g, uint32_t q, uint32_t k,
+                                  float *out_scores, uint64_t *out_rows) {
+  const uint32_t qi = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (qi >= q) return;
+  const int lane = threadIdx.x & 31;
+  for (uint32_t i = lane; i < k; i += 32) {
+    out_scores[(size_t)qi * k + i] = CUDART_NAN_F;
+    out_rows[(size_t)qi * k + i] = ZVB200_INVALID_KEY;
+  }
+  __syncwarp();
+  const size_t gstride = (size_t)q * k;
+  for (uint32_t c = lane; c < g * k; c += 32) {
+    const uint32_t gi = c / k, i = c % k;
+    const float s = scores[gi * gstride + (size_t)qi * k + i];
+    const uint64_t row = rows[gi * gstride + (size_t)qi * k + i];
+    if (row == ZVB200_INVALID_KEY || s != s) continue;
+    const uint32_t so = order_f32(s);
+    uint32_t rank = i;
+    for (uint32_t g2 = 0; g2 < g; ++g2) {
+      if (g2 == gi) continue;
+      const float *l2 = scores + g2 * gstride + (size_t)qi * k;
+      const uint64_t *r2 = rows + g2 * gstride + (size_t)qi * k;
+      uint32_t lo = 0, hi = k;
+      while (lo < hi) {
+        const uint32_t mid = (lo + hi) >> 1;
+        const uint32_t mo = r2[mid] == ZVB200_INVALID_KEY ? 0xffffffffu : ord_or_max(l2[mid]);
+        const bool before = mo < so || (mo == so && r2[mid] < row);
+        if (before) lo = mid + 1; else hi = mid;
+      }
+      rank += lo;
+    }
+    if (rank < k) {
+      out_scores[(size_t)qi * k + rank] = s;
+      out_rows[(size_t)qi * k + rank] = row;
+    }
+  }
+}
+
+// local row of a list-grouped store -> row of the whole index: gbase[list] + offset inside the list's local slice
+__global__ void ivf_global_rows_kernel(const uint32_t *index, uint64_t count, const uint32_t *list_off,
+                                       const uint64_t *gbase, uint32_t nlist, uint64_t *out) {
+  const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= count) return;
+  const uint32_t r = index[i];
+  if (r == ZVB200_INVALID_INDEX || r >= list_off[nlist]) { out[i] = ZVB200_INVALID_KEY; return; }
+  uint32_t lo = 0, hi = nlist;  // last list with list_off <= r (empty lists share an offset: the LAST of them holds r)
+  while (hi - lo > 1) {
+    const uint32_t mid = (lo + hi) >> 1;
+    if (list_off[mid] <= r) lo = mid; else hi = mid;
+  }
+  out[i] = gbase[lo] + (r - list_off[lo]);
+}
+
 // ---- distance matrix: out[j*n + i] = dist(row i, query j) ----------------------------
 // The ailego <T,1,1>::Compute contract (IndexMetric::distance(), euclidean_metric.cc:785-851)
 // one warp per row, queries looped.
@@ -473,6 +528,23 @@ cudaError_t launch_merge_shards(const float *scores, const uint32_t *index, uint
   const int wpb = 4;
   merge_shards_kernel<<<(q + wpb - 1) / wpb, wpb * 32, 0, st>>>(scores, index, g, shard_base_dev, q,
                                                                k, out_scores, out_rows);
+  count_launch();
+  return cudaGetLastError();
+}
+
+cudaError_t launch_merge_rows(const float *scores, const uint64_t *rows, uint32_t g, uint32_t q, uint32_t k,
+                              float *out_scores, uint64_t *out_rows, cudaStream_t st) {
+  if (q == 0) return cudaSuccess;
+  const int wpb = 4;
+  merge_rows_kernel<<<(q + wpb - 1) / wpb, wpb * 32, 0, st>>>(scores, rows, g, q, k, out_scores, out_rows);
+  count_launch();
+  return cudaGetLastError();
+}
+
+cudaError_t launch_ivf_global_rows(const uint32_t *index, uint64_t count, const uint32_t *list_off,
+                                   const uint64_t *gbase, uint32_t nlist, uint64_t *out, cudaStream_t st) {
+  if (count == 0) return cudaSuccess;
+  ivf_global_rows_kernel<<<(unsigned)((count + 255) / 256), 256, 0, st>>>(index, count, list_off, gbase, nlist, out);
   count_launch();
   return cudaGetLastError();
 }

@@ -91,6 +91,12 @@ cudaError_t launch_merge_parts(const u64 *part, uint32_t nparts, uint32_t q, uin
 cudaError_t launch_merge_shards(const float *scores, const uint32_t *index, uint32_t g,
                                 const uint64_t *shard_base_dev, uint32_t q, uint32_t k,
                                 float *out_scores, uint64_t *out_rows, cudaStream_t st);
+// G sorted lists [g][q][k] with explicit rows of the whole index -> q*k by (score, row)
+cudaError_t launch_merge_rows(const float *scores, const uint64_t *rows, uint32_t g, uint32_t q, uint32_t k,
+                              float *out_scores, uint64_t *out_rows, cudaStream_t st);
+// local rows of a list-grouped store -> rows of the whole index
+cudaError_t launch_ivf_global_rows(const uint32_t *index, uint64_t count, const uint32_t *list_off,
+                                   const uint64_t *gbase, uint32_t nlist, uint64_t *out, cudaStream_t st);
 // reference element layout (host order) -> store layout
 cudaError_t launch_repack_rows(const uint8_t *src, uint32_t elem_bytes, uint64_t n, uint8_t *dst,
                                uint32_t row_stride, uint32_t vec_bytes, float4 *tails,
