@@ -467,7 +467,7 @@ def test_concurrent_contexts_on_one_store():
         try:
             q, k = plans[i]
             c = z.Context(st)
-            for _ in range(6):
+            for _ in range(20):
                 got = c.search(queries[:q], k)
                 for a, b in zip(got, serial[i]):
                     assert np.array_equal(np.asarray(a).view(np.uint8), np.asarray(b).view(np.uint8))

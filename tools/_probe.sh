@@ -1,5 +1,5 @@
 set -x
 cd $GRAFT_REPO_ROOT
-N=${1:-8}
-python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29511 bench.py --gpus $N --steps 10 --warmup 3 > gpurun_out/bench_${N}gpu.json 2> gpurun_out/bench_${N}gpu.err; head -c 250 gpurun_out/bench_${N}gpu.json; tail -2 gpurun_out/bench_${N}gpu.err
-python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29512 tools/multigpu_probe.py ivf > gpurun_out/mg_ivf_${N}.json 2> gpurun_out/mg_ivf_${N}.err; grep "^{" gpurun_out/mg_ivf_${N}.json | cut -c1-500
+for i in 1 2 3 4; do timeout 300 python -m pytest tests/test_flat_gpu.py tests/test_plugin.py -m gpu -x -q -k "concurrent or many_threads or race" 2>&1 | tail -1; done
+( time timeout 1200 python -m pytest tests -m gpu -x -q ) > gpurun_out/pytest_gpu.log 2>&1; grep -E "passed|failed" gpurun_out/pytest_gpu.log
+python bench.py > gpurun_out/bench_1gpu.json 2> gpurun_out/bench_1gpu.err; wc -l gpurun_out/bench_1gpu.json; head -c 200 gpurun_out/bench_1gpu.json

@@ -498,13 +498,11 @@ cudaError_t launch_merge_parts(const u64 *part, uint32_t nparts, uint32_t q, uin
                                float *out_scores, uint32_t *out_index, cudaStream_t st) {
   if (q == 0) return cudaSuccess;
   const size_t smem = sizeof(int2) * kMergeWarps + (size_t)kMergeWarps * (2 * (size_t)k + 32) * sizeof(u64);
-  static bool attr_set = false;
-  if (!attr_set) {
+  {  // a constant, every time: the attribute is per function AND per device, and shared by all host threads
     cudaError_t e = cudaFuncSetAttribute(merge_parts_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
     if (e == cudaSuccess)
       e = cudaFuncSetAttribute(merge_parts_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
     if (e != cudaSuccess) return e;
-    attr_set = true;
   }
   u64 *p = const_cast<u64 *>(part);  // the sliced pass reuses the scratch lists in place
   // few queries, many keys each: slices of the lists first (grid.y), then one list per slice

@@ -165,6 +165,11 @@ cudaError_t launch_kmeans_finalize(const double *sums, const unsigned long long 
                                    uint32_t k, uint32_t dim, float *centroids, unsigned long long *follows,
                                    double *sse, cudaStream_t st);
 
+// cudaFuncAttributeMaxDynamicSharedMemorySize is per-FUNCTION state shared by every host thread: setting it to each
+// launch's own size lets one thread lower it between another thread's set and its launch ("too many resources
+// requested for launch", seen with eight contexts searching at once).  Every launcher sets this one constant.
+constexpr int kMaxDynSmem = 232448;  // 227 KB, the per-CTA limit of sm_100
+
 void count_launch(int n = 1);
 
 }  // namespace zvb

@@ -152,7 +152,7 @@ cudaError_t launch_reform(const float *in, uint32_t q, uint32_t dim, int kind, u
   const size_t smem = kind == RF_FP16 ? 0 : (size_t)dim * 4;
   if (smem > 200 * 1024) return cudaErrorInvalidValue;
   if (smem > 48 * 1024) {
-    cudaError_t e = cudaFuncSetAttribute(reform_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    cudaError_t e = cudaFuncSetAttribute(reform_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
     if (e != cudaSuccess) return e;
   }
   reform_kernel<<<q, 32, smem, st>>>(in, q, dim, kind, out, elem_bytes);

@@ -226,7 +226,8 @@ __global__ void __launch_bounds__(kThreads, QB == 1 ? 2 : 1) scan_gemv_kernel(co
 template <int DT, bool L2, int QB, bool SEG = false>
 cudaError_t launch_one(const GemvArgs &a, int grid, size_t smem, cudaStream_t st, int grid_y = 1) {
   auto kern = scan_gemv_kernel<DT, L2, QB, SEG>;
-  cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kMaxDynSmem);
+  if (e == cudaSuccess && smem > (size_t)kMaxDynSmem) e = cudaErrorInvalidValue;
   if (e != cudaSuccess) return e;
   kern<<<dim3(grid, grid_y), kThreads, smem, st>>>(a);
   count_launch();

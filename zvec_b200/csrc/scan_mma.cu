@@ -1112,7 +1112,7 @@ cudaError_t launch_scan_mma(const RowsView &rv, const QueryView &qv, const Searc
                 : a.mode == 7 ? ZVB_MMA_KR(2, 7)
                               : ZVB_MMA_KR(2, 8);
 #undef ZVB_MMA_KR
-  cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kMaxDynSmem);
   if (e != cudaSuccess) return e;
   if (nrows == 0) {
     // nothing to scan: every partial list is empty

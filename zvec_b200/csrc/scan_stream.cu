@@ -317,7 +317,8 @@ bool stream_config(const RowsView &rv, uint32_t k, uint32_t seg_cap, StreamCfg *
 template <int DT, bool L2, bool SEG>
 cudaError_t launch_s(const StreamArgs &a, dim3 grid, size_t smem, cudaStream_t st) {
   auto kern = scan_stream_kernel<DT, L2, SEG>;
-  cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kMaxDynSmem);
+  if (e == cudaSuccess && smem > (size_t)kMaxDynSmem) e = cudaErrorInvalidValue;
   if (e != cudaSuccess) return e;
   kern<<<grid, (a.cwarps + 1) * 32, smem, st>>>(a);
   count_launch();

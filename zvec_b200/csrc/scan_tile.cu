@@ -290,7 +290,8 @@ size_t tile_smem(int dtype, uint32_t k) {
 template <int DT, bool L2>
 cudaError_t launch_t(const TileArgs &a, int grid, size_t smem, cudaStream_t st) {
   auto kern = scan_tile_kernel<DT, L2>;
-  cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kMaxDynSmem);
+  if (e == cudaSuccess && smem > (size_t)kMaxDynSmem) e = cudaErrorInvalidValue;
   if (e != cudaSuccess) return e;
   kern<<<grid, kThreads, smem, st>>>(a);
   count_launch();
