@@ -1,22 +1,26 @@
-// K2 — tcgen05 / TMEM contraction with a fused thread-per-query top-k epilogue
-// (large query batches, fp16 stores).
+// K2 — tcgen05 / TMEM contraction with a fused thread-per-query top-k epilogue (query batches).
 //
 // Replaces FlatSearcherContext::batch_search_* (src/core/algorithm/flat/
-// flat_searcher_context.h:681-752,847-921): the XxxMatrix<Float16,32,N> tile calls
-// (inner_product_matrix_fp16.cc:492,547) and the 32*N heap inserts per tile
-// (batch_enqueue_nofilter, flat_searcher_context.h:236-261).
+// flat_searcher_context.h:681-752,847-921): the XxxMatrix<T,32,N> tile calls
+// (inner_product_matrix_fp16.cc:492,547, euclidean_distance_matrix_fp32.cc:521,601, the int8 siblings) and
+// the 32*N heap inserts per tile (batch_enqueue_nofilter, flat_searcher_context.h:236-261).
 //
-// Shape of the contraction (one CTA, one SM):
-//   A = 128 queries  x 64 halves  (UMMA M = 128 -> the 128 TMEM lanes)
-//   B =  BN rows     x 64 halves  (UMMA N = 256 stored rows per tile)
-//   D[query][row] accumulates in TMEM (fp32), two tiles deep (2 x 256 columns = all of TMEM)
-// Both operands are K-major, staged by TMA into 128-byte-swizzled shared memory; one
-// elected thread issues tcgen05.mma; four epilogue warps read the accumulator with
-// tcgen05.ld (32x32b: one TMEM lane = one query per thread, 32 rows per load), so every
-// thread filters ITS query's scores against ITS running k-th best held in a register.
-// Survivors go to a private queue in shared memory and are merged into the query's sorted
-// list by the owning warp (sort32 + rank merge, in place).  The score matrix never leaves
-// the SM; per CTA only 128 x k keys go back to HBM.
+// Shape of the contraction (one CTA, one SM), per 128-byte k-block:
+//   A = 128 queries x {64 halves | 32 floats | 128 int8}   (UMMA M = 128 -> the 128 TMEM lanes)
+//   B = 256 rows    x the same                              (UMMA N = 256 stored rows per tile)
+//   D[query][row] accumulates in TMEM (fp32 or int32), two tiles deep (2 x 256 columns = all of TMEM)
+// Operand kinds (template KIND): 0 kind::f16 on fp16 rows, 1 kind::tf32 on fp32 rows, 2 kind::i8 on int8 rows,
+// 3 kind::f16 on the bf16 shadow operands of a QuantizedInteger L2 store.
+// Both operands are K-major, staged by TMA into 128-byte-swizzled shared memory; one elected thread issues
+// tcgen05.mma; four epilogue warps read the accumulator with tcgen05.ld (32x32b: one TMEM lane = one query per
+// thread, 32 rows per load), so every thread filters ITS query's scores against ITS running bound held in a
+// register.  Where the accumulator IS the score (fp16 InnerProduct / Cosine, plain int8) survivors enter the
+// query's top-k pool directly; elsewhere it only NOMINATES rows with a sound margin and the exact score is
+// recomputed (fp32 FMA over the stored row, or dp4a + the reference's float epilogue) before the pool sees it.
+// Pools: k <= 16 in registers, larger k unsorted in XOR-swizzled shared memory with a warp-cooperative rescan.
+// Warp 3 produces the per-column constants of the filter modes through an mbarrier ring.  CTAs that scan the same
+// query publish their j-th best score; the m-th smallest published word bounds the global k-th best (union bound).
+// The score matrix never leaves the SM; per CTA only 128 x k keys go back to HBM.
 //
 // CTAs are persistent: CTA c works on query tile c % QT for a contiguous range of row
 // tiles, and the QT CTAs of a group walk the SAME rows at the same time so that HBM sees
