@@ -548,7 +548,9 @@ static int search_core(zvb200_ctx *c, zvb200_store *s, const void *queries_dev, 
   const bool stream_ok = scan_stream_supports(rv, k, 0);
   // tensor cores: fp16 InnerProduct / Cosine at any batch (scores straight from the accumulator); fp16 L2 and
   // fp32 (tf32 filter + exact re-score) from 5 queries on — below that the streaming scan is as fast and simpler
-  const bool mma_direct = mma_ok && s->dtype == ZVB200_DT_FP16 && !metric_is_l2(s->metric);
+  // (one query with k > 80: the pools leave the tensor-core scan only 2 pipeline stages, 5.7 TB/s; the GEMV scan
+  // streams the same rows at 6.6 TB/s — measured at 10M x 768, k = 100)
+  const bool mma_direct = mma_ok && s->dtype == ZVB200_DT_FP16 && !metric_is_l2(s->metric) && !(q == 1 && k > 80);
   // QuantizedInteger L2 with shadow operands: the streaming scan costs 2.5 / 8.2 ms at 1 / 4 queries (100M x 96), the
   // tensor-core scan 5.2 ms for any batch up to 128 — it takes over from 3 queries
   const bool mma_early = mma_ok && rv.shadow && q > 2;
