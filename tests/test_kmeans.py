@@ -131,3 +131,29 @@ def test_gpu_kmeans_feeds_the_gpu_ivf_index():
     assert (keys[:, 0] == np.arange(200)).mean() > 0.99 and (scores[:, 0] <= 1e-6).mean() > 0.99
     assert np.array_equal(remap[lab[:200]], np.searchsorted(offs, index[:, 0].astype(np.uint64), side="right") - 1)
     ctx.close(); st.close()
+
+
+# ---- golden vectors written by the reference's KmeansCluster (tests/golden/make_kmeans_golden.py) ----
+def _golden_cases():
+    import json
+    g = json.load(open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "kmeans.json")))
+    for c in g["cases"]:
+        n, d, k = c["n"], c["dim"], c["k"]
+        x = (np.array(c["rows_times_8"], np.float32) / 8).reshape(n, d)
+        init = (np.array(c["init_times_8"], np.float32) / 8).reshape(k, d)
+        ref = np.array(c["centroids_bits"], np.uint32).view(np.float32).reshape(k, d)
+        yield c, x, init, ref
+
+
+def _same_centroids(got, ref):
+    assert np.array_equal(np.isnan(got), np.isnan(ref))
+    live = ~np.isnan(ref)
+    assert np.array_equal(got.view(np.uint32)[live], ref.view(np.uint32)[live])     # sums are exact in double: bit for bit
+
+
+def test_oracle_kmeans_reproduces_the_golden_vectors():
+    for c, x, init, ref in _golden_cases():
+        oc, ol, of, os_, _ = KO.kmeans(x, init, c["iterations"])
+        _same_centroids(oc, ref)
+        assert np.array_equal(ol, np.array(c["labels"], np.uint32)) and of.tolist() == c["follows"]
+        assert abs(os_ - c["sse"]) <= 1e-5 * abs(c["sse"])
