@@ -157,3 +157,11 @@ def test_oracle_kmeans_reproduces_the_golden_vectors():
         _same_centroids(oc, ref)
         assert np.array_equal(ol, np.array(c["labels"], np.uint32)) and of.tolist() == c["follows"]
         assert abs(os_ - c["sse"]) <= 1e-5 * abs(c["sse"])
+@pytest.mark.gpu
+def test_gpu_kmeans_reproduces_the_golden_vectors():
+    import zvec_b200 as z
+    for c, x, init, ref in _golden_cases():
+        gc, gl, gf, gs, git = z.kmeans(x, init, max_iterations=c["iterations"], epsilon=0.0)
+        _same_centroids(gc, ref)
+        assert np.array_equal(gl, np.array(c["labels"], np.uint32)) and gf.astype(int).tolist() == c["follows"]
+        assert abs(gs - c["sse"]) <= 1e-5 * abs(c["sse"])

@@ -1,3 +1,4 @@
+# scratch: the command list of the latest gpurun call (see profiles/ for what was kept)
 set -x
 cd $GRAFT_REPO_ROOT
-timeout 300 python -m pytest tests/test_kmeans.py -x -q 2>&1 | tail -8
+python -m pytest tests -m gpu -x -q 2>&1 | tail -3
