@@ -56,8 +56,9 @@ extern "C" {
 #define ZVB200_MAX_TOPK 1024u
 #define ZVB200_MAX_CANDIDATES 8192u /* candidate rows per query of zvb200_search_rows */
 
-typedef struct zvb200_store zvb200_store; /* device-resident vector store on ONE GPU */
+typedef struct zvb200_store zvb200_store; /* device-resident vector store: on one GPU, or row-sharded over several */
 typedef struct zvb200_ctx zvb200_ctx;     /* per-thread search context (IndexContext) */
+typedef struct zvb200_comm zvb200_comm;   /* one rank of a multi-process, one-GPU-per-process row-sharded search */
 
 const char *zvb200_version(void);
 /* Message of the last failing call on this thread. */
@@ -73,6 +74,18 @@ uint64_t zvb200_kernel_launches(void);
  * one element is IndexMeta::element_size() bytes: dim*4 (fp32), dim*2 (fp16), dim (int8).
  */
 int zvb200_store_create(int device, int dtype, int metric, uint32_t dim, zvb200_store **out);
+/* The multi-GPU layer inside ONE process (what a zvec process gets with proxima.gpu.devices =
+ * "0,1,2,3"): the same handle, rows sharded over `devices` as contiguous ranges — shard g holds rows
+ * [g * S, (g + 1) * S), S = ceil(N / ndev) rounded up to 1024, N = the FIRST zvb200_store_reserve() (required before
+ * the first append; appends beyond it fail).  Every store / context / search entry point below works on it unchanged
+ * with GLOBAL row numbers; a search runs the scan on every device, each device's k best per query travel to
+ * devices[0] over NVLink and are merged there by (score, global row) — the device form of
+ * CombinedVectorColumnIndexer::Search's concat + sort + truncate (combined_vector_column_indexer.cc:98-232), bit
+ * identical to the same rows in one store.  Not on a sharded store (ZVB200_ERR_UNSUPPORTED): zvb200_ivf_*,
+ * zvb200_reform_queries*, zvb200_search_fp32, zvb200_search_refined.  ndev = 1 is zvb200_store_create.  A store
+ * holds at most 2^32 - 2 rows either way (ZVB200_ERR_INVALID_ARGUMENT beyond). */
+int zvb200_store_create_sharded(const int *devices, uint32_t ndev, int dtype, int metric, uint32_t dim,
+                                zvb200_store **out);
 int zvb200_store_destroy(zvb200_store *s);
 /* Pre-size the device arrays for `rows` rows (optional; append grows geometrically). */
 int zvb200_store_reserve(zvb200_store *s, uint64_t rows);
@@ -137,6 +150,10 @@ void *zvb200_ctx_stream(zvb200_ctx *c);
  * 5 tcgen05 on the int8 codes themselves (kind::i8) where 3 would contract a QuantizedInteger L2 store's bf16
  * shadow operands. */
 int zvb200_ctx_set_kernel(zvb200_ctx *c, int which);
+/* Snapshot reads (FlatStreamer adds race with searches, tests/core/algorithm/flat/flat_streamer_test.cc:509-730):
+ * the next searches on this context see rows [0, rows) only, and a filter bitmap handed to them covers exactly
+ * those rows; 0 = every row (the default). */
+int zvb200_ctx_set_row_limit(zvb200_ctx *c, uint64_t rows);
 /* Name of the scan kernel the last search on this context used. */
 const char *zvb200_ctx_last_kernel(const zvb200_ctx *c);
 /* Operand kind of the last tcgen05 scan on this context: 0 kind::f16, 1 kind::tf32, 2 kind::i8,
@@ -157,6 +174,33 @@ int zvb200_distance_matrix(int device, int metric, int dtype, uint32_t dim, cons
 int zvb200_merge_topk_device(zvb200_ctx *c, const float *scores_dev, const uint32_t *index_dev,
                              uint32_t g, const uint64_t *shard_base, uint32_t q, uint32_t k,
                              float *out_scores_dev, uint64_t *out_rows_dev);
+
+/* ---- the multi-GPU layer across processes (one process per GPU: bench.py under torchrun, any multi-process
+ * server).  Each rank holds a plain store with ITS contiguous row range and calls zvb200_search_sharded_device
+ * collectively: scan -> exchange of the packed (score, row) keys -> merge by (score, global row), all on the
+ * context's stream, every rank ends up with the merged result.  Exchange transport, agreed by all ranks at init:
+ *   1  peer mailboxes: every rank stores its keys straight into a CUDA-IPC-mapped buffer of each peer over NVLink
+ *      and raises a release flag; the merge kernel acquires the flags.  No collective launch (SURVEY §5's batch-1
+ *      fast path); used whenever q * k <= 131072.
+ *   0  one ncclAllGather of the u64 keys (CUDA IPC unavailable, ZVB200_COMM_MAILBOX=0, or a larger q * k).
+ * NCCL is bound at run time (dlopen libnccl.so.2): the process's own copy if it has one (PyTorch's), else the
+ * system's.  zvb200_comm_unique_id on one rank, the 128 bytes carried to the others by the caller (any side
+ * channel), then zvb200_comm_init on every rank (collective).  Before zvb200_comm_destroy the caller makes sure no
+ * peer is still inside a search (a barrier). */
+#define ZVB200_COMM_ID_BYTES 128
+int zvb200_comm_unique_id(void *id128);
+int zvb200_comm_init(zvb200_ctx *c, int rank, int world, const void *id128, zvb200_comm **out);
+int zvb200_comm_destroy(zvb200_comm *cm);
+/* bases[r] = first global row of rank r's shard (ascending with r). */
+int zvb200_comm_set_shard_bases(zvb200_comm *cm, const uint64_t *bases);
+int zvb200_comm_transport(const zvb200_comm *cm);
+/* ZVB200_ERR_RUNTIME if an exchange timed out (a peer never delivered) since init; synchronises the device. */
+int zvb200_comm_status(zvb200_comm *cm);
+/* queries / filter / outputs in DEVICE memory; out_scores_dev f32 [q][k], out_rows_dev u64 [q][k] (global rows,
+ * ZVB200_INVALID_KEY / NaN padded).  zvb200_ctx_sync() waits. */
+int zvb200_search_sharded_device(zvb200_ctx *c, zvb200_comm *cm, const void *queries_dev, uint32_t q, uint32_t k,
+                                 float threshold, const uint32_t *filter_dev, float *out_scores_dev,
+                                 uint64_t *out_rows_dev);
 
 /* ---- multi-vector fusion: replaces RrfReRanker.rerank / WeightedReRanker.rerank
  * (python/zvec/extension/multi_vector_reranker.py:62-89,135-174) applied by the query executor to

@@ -1,34 +1,40 @@
-// zvec index plugin: GpuFlatSearcher — the reference's IndexSearcher interface served by the
-// B200 scan behind include/zvec_b200.h.
+// zvec index plugin: GpuFlatSearcher / GpuFlatStreamer / GpuIVFSearcher / GpuIVFStreamer — the reference's
+// IndexSearcher / IndexStreamer interfaces served by the B200 scan behind include/zvec_b200.h.
 //
 // Host adaptor (C++, ours).  It is compiled against the reference's PUBLIC framework headers
 // (src/include/zvec/core/framework/*.h, used with -I where they lie, never copied) and
-// registered with the reference's own macro INDEX_FACTORY_REGISTER_SEARCHER
+// registered with the reference's own macros INDEX_FACTORY_REGISTER_SEARCHER / _STREAMER
 // (src/include/zvec/core/framework/index_factory.h:237-242), so
 //   IndexFactory::CreateSearcher("GpuFlatSearcher")
 // — and, after zvb200_install_overrides(), IndexFactory::CreateSearcher("FlatSearcher") —
 // returns it; it is loaded like any zvec plugin: IndexPlugin::load(path) = dlopen
-// (src/core/framework/index_plugin.cc:20-35).  It mirrors FlatSearcher<32>
-// (src/core/algorithm/flat/flat_searcher.h:33-161, flat_searcher.cc:68-211): same load()
-// checks and error codes, same context contract (topk / filter / threshold / result(i)),
-// results sorted ascending by the internal score with key(), score(), index().
-// Everything that is arithmetic happens on the GPU through the C ABI; there is no CPU scan here.
+// (src/core/framework/index_plugin.cc:20-35).
+//
+// Division of labour (composition): every class embeds the STOCK class it stands in for, created under
+// a name that is never overridden ("FlatSearcher32", "FlatStreamer32", IVFSearcher by type).  The stock object owns
+// what is not arithmetic — file validation and its error codes, key maps, providers / get_vector / fetch_vector,
+// persistence, group-by bookkeeping.  Every scan (search_impl, search_bf_impl, search_bf_by_p_keys_impl) runs on the
+// GPU through the C ABI; the only searches the stock object still answers are group-by searches (SURVEY 8b allows
+// delegating those) and IVF indexes whose layout the device store cannot hold, each logged once.
 #include <zvec/core/framework/index_context.h>
 #include <zvec/core/framework/index_error.h>
 #include <zvec/core/framework/index_factory.h>
 #include <zvec/core/framework/index_helper.h>
+#include <zvec/core/framework/index_logger.h>
 #include <zvec/core/framework/index_meta.h>
 #include <zvec/core/framework/index_searcher.h>
 #include <zvec/core/framework/index_streamer.h>
 
+#include <algorithm>
+#include <atomic>
+#include <cmath>
 #include <cstring>
 #include <limits>
-#include <map>
 #include <mutex>
+#include <shared_mutex>
 #include <string>
+#include <unordered_map>
 #include <vector>
-
-#include <cmath>
 
 #include <zvec/core/framework/index_segment_storage.h>
 #include "core/algorithm/ivf/ivf_searcher.h"  // the stock IVF classes, used by type (composition)
@@ -45,6 +51,9 @@ const std::string kSegKeys("flat.keys");
 const std::string kSegFeatures("flat.features");
 // QuantizedIntegerMetric's origin metric parameter (src/core/metric/quantized_integer_metric.cc:40-60)
 const std::string kOriginMetric("proxima.quantized_integer.metric.origin_metric_name");
+// proxima.gpu.* keys read through the same ailego::Params as every other searcher parameter
+const std::string kParamDevice("proxima.gpu.device");    // one CUDA device (default 0)
+const std::string kParamDevices("proxima.gpu.devices");  // "0,1,2,3": rows sharded over these devices (GpuFlatSearcher)
 
 // IndexMeta (metric name [+ origin metric], data type) -> ZVB200_METRIC_* ; <0 = unsupported,
 // like InnerProductMetric::init for types it has no kernel for (inner_product_metric.cc:259-281)
@@ -73,65 +82,200 @@ int dtype_of(const IndexMeta &meta) {
   }
 }
 
+std::vector<int> parse_devices(const ailego::Params &params) {
+  std::vector<int> out;
+  std::string s;
+  if (params.get(kParamDevices, &s) && !s.empty()) {
+    size_t pos = 0;
+    while (pos <= s.size()) {
+      size_t e = s.find(',', pos);
+      if (e == std::string::npos) e = s.size();
+      if (e > pos) out.push_back(std::atoi(s.substr(pos, e - pos).c_str()));
+      pos = e + 1;
+    }
+  }
+  if (out.empty()) {
+    int d = 0;
+    params.get(kParamDevice, &d);
+    out.push_back(d);
+  }
+  return out;
+}
+
+void log_delegated_once(std::atomic<bool> *flag, const char *cls, const char *why) {
+  bool expected = false;
+  if (flag->compare_exchange_strong(expected, true))
+    LOG_WARN("%s: %s is answered by the stock CPU class (logged once)", cls, why);
+}
+
 }  // namespace
 
-class GpuFlatSearcher;
-
-/*! Search context: FlatSearcherContext's contract (flat_searcher_context.h:187-196,
- *  index_context.h:57-260) over a zvb200_ctx (CUDA stream + pinned staging + device scratch).
+/*! Search context shared by the four classes: the IndexContext contract (index_context.h:57-260 — topk, filter,
+ *  threshold, group params, fetch_vector, result(i), group_result(i), magic) over a zvb200_ctx (CUDA stream + pinned
+ *  staging + device scratch) and the stock class's own context for what the stock object answers.
  */
-class GpuFlatContext : public IndexContext {
+class GpuContext : public IndexContext {
  public:
-  explicit GpuFlatContext(const GpuFlatSearcher *owner) { this->reset(owner); }
-  ~GpuFlatContext() override {
+  explicit GpuContext(IndexContext::Pointer inner) : inner_(std::move(inner)) {}
+  ~GpuContext() override {
     if (ctx_) zvb200_ctx_destroy(ctx_);
   }
-  void set_topk(uint32_t topk) override { topk_ = topk; }
+  void set_topk(uint32_t topk) override {
+    topk_ = topk;
+    if (inner_) inner_->set_topk(topk);
+  }
   uint32_t topk() const override { return topk_; }
+  //! FlatSearcherContext::set_group_params (flat_searcher_context.h:178-182): group_num > 0 = group-by search
+  void set_group_params(uint32_t group_num, uint32_t group_topk) override {
+    group_num_ = group_num;
+    if (inner_) inner_->set_group_params(group_num, group_topk);
+  }
+  void set_fetch_vector(bool v) override {
+    fetch_vector_ = v;
+    if (inner_) inner_->set_fetch_vector(v);
+  }
+  bool fetch_vector() const override { return fetch_vector_; }
   const IndexDocumentList &result(void) const override { return results_[0]; }
   const IndexDocumentList &result(size_t i) const override { return results_[i]; }
   IndexDocumentList *mutable_result(size_t i) override { return &results_[i]; }
-  uint32_t magic(void) const override { return magic_; }
-  void reset(const GpuFlatSearcher *owner);
-  zvb200_ctx *handle() const { return ctx_; }
-  void resize_results(size_t n) {
-    if (results_.size() < n) results_.resize(n);
+  const IndexGroupDocumentList &group_result(void) const override {
+    return inner_ ? inner_->group_result() : IndexContext::group_result();
   }
-  // scratch reused across searches
+  const IndexGroupDocumentList &group_result(size_t i) const override {
+    return inner_ ? inner_->group_result(i) : IndexContext::group_result();
+  }
+  uint32_t magic(void) const override { return magic_; }
+
+  bool group_by_search(void) const { return group_num_ > 0; }
+  zvb200_ctx *handle() const { return ctx_; }
+  IndexContext::Pointer &inner() { return inner_; }
+  //! (re)bind to a device store; results are cleared like every reference context's reset(owner)
+  void bind(zvb200_store *store, uint32_t magic) {
+    if (ctx_) zvb200_ctx_destroy(ctx_);
+    ctx_ = nullptr;
+    magic_ = magic;
+    if (store) zvb200_ctx_create(store, &ctx_);
+    for (auto &r : results_) r.clear();
+  }
+  //! `count` empty result lists and cleared per-query statistics (reset_results of the reference contexts)
+  void begin(size_t count) {
+    if (results_.size() < count) results_.resize(count);
+    for (size_t i = 0; i < count; ++i) results_[i].clear();
+    stats_vec_.resize(count);
+    for (auto &s : stats_vec_) s.clear();
+    const size_t nres = count * (size_t)topk_;
+    keys.resize(nres); scores.resize(nres); index.resize(nres); counts.resize(count);
+  }
+  //! per-query statistics (FlatStreamerContext::mutable_stats, flat_streamer_context.h:219-222): filled from the
+  //! host after the kernel with what the reference's scan loops count (flat_streamer_entity.cc:246,306-314)
+  Stats *mutable_stats(size_t idx = 0) { return &stats_vec_[idx]; }
+  const Stats &stats(size_t idx = 0) const { return stats_vec_[idx]; }
+  void fill_stats(size_t count, size_t calced, size_t filtered) {
+    for (size_t i = 0; i < count && i < stats_vec_.size(); ++i) {
+      stats_vec_[i].set_dist_calced_count(calced);
+      stats_vec_[i].set_filtered_count(filtered);
+    }
+  }
+  //! what the caller set on this context, mirrored onto the stock context before the stock object answers:
+  //! a filter / group-by / threshold that was cleared here is cleared there too
+  void sync_inner(void) {
+    if (!inner_) return;
+    inner_->set_topk(topk_);
+    if (this->filter().is_valid()) inner_->set_filter(this->filter()); else inner_->reset_filter();
+    if (this->group_by().is_valid()) inner_->set_group_by(this->group_by()); else inner_->reset_group_by();
+    inner_->set_threshold(this->threshold());  // stock contexts carry no metric: the value is taken as it is
+    inner_->set_fetch_vector(fetch_vector_);
+  }
+  void take_inner_results(size_t count) {
+    if (results_.size() < count) results_.resize(count);
+    for (size_t i = 0; i < count; ++i) results_[i] = inner_->result(i);
+  }
+
+  // host scratch reused across searches
   std::vector<uint64_t> keys;
   std::vector<float> scores;
-  std::vector<uint32_t> index, counts, bitmap;
+  std::vector<uint32_t> index, counts, bitmap, rows;
 
- private:
+ protected:
   uint32_t topk_{0};
   uint32_t magic_{0};
+  uint32_t group_num_{0};
+  bool fetch_vector_{false};
   zvb200_ctx *ctx_{nullptr};
+  IndexContext::Pointer inner_{};
   std::vector<IndexDocumentList> results_{1};
+  std::vector<Stats> stats_vec_{1};
 };
 
-/*! GPU Flat Searcher: IndexSearcher (index_searcher.h:29-54, index_runner.h:404-640) whose
- *  load() uploads the Flat index file to a device-resident store and whose search_impl()
- *  is one zvb200_search call.
+namespace {
+
+//! one search_bf_by_p_keys pass: each query's listed rows (ZVB200_INVALID_INDEX = skipped) in slices of
+//! ZVB200_MAX_CANDIDATES, the slices' best-k merged by (score, row) on the host — k entries per slice, not a scan
+int search_rows_sliced(GpuContext *ctx, const void *query, uint32_t count, const std::vector<std::vector<uint32_t>> &rows,
+                       uint32_t k, std::vector<std::vector<std::pair<float, std::pair<uint32_t, uint64_t>>>> *out) {
+  size_t longest = 0;
+  for (auto &r : rows) longest = std::max(longest, r.size());
+  out->assign(count, {});
+  if (longest == 0) return 0;
+  for (size_t s0 = 0; s0 < longest; s0 += ZVB200_MAX_CANDIDATES) {
+    const uint32_t m = (uint32_t)std::min<size_t>(ZVB200_MAX_CANDIDATES, longest - s0);
+    ctx->rows.assign((size_t)count * m, ZVB200_INVALID_INDEX);
+    for (uint32_t i = 0; i < count; ++i)
+      for (size_t j = s0; j < rows[i].size() && j < s0 + m; ++j) ctx->rows[(size_t)i * m + (j - s0)] = rows[i][j];
+    const int rc = zvb200_search_rows(ctx->handle(), query, count, ctx->rows.data(), m, k, ctx->threshold(), nullptr,
+                                      ctx->keys.data(), ctx->scores.data(), ctx->index.data(), ctx->counts.data());
+    if (rc != 0) return rc;
+    for (uint32_t i = 0; i < count; ++i)
+      for (uint32_t j = 0; j < ctx->counts[i]; ++j) {
+        const size_t o = (size_t)i * k + j;
+        (*out)[i].push_back({ctx->scores[o], {ctx->index[o], ctx->keys[o]}});
+      }
+  }
+  if (longest > ZVB200_MAX_CANDIDATES)
+    for (auto &l : *out) {
+      std::sort(l.begin(), l.end(), [](const auto &a, const auto &b) {
+        return a.first < b.first || (a.first == b.first && a.second.first < b.second.first);
+      });
+      if (l.size() > k) l.resize(k);
+    }
+  return 0;
+}
+
+}  // namespace
+
+/*! GPU Flat Searcher: IndexSearcher (index_searcher.h:29-54, index_runner.h:404-640) whose load() uploads the Flat
+ *  index file to a device-resident store and whose searches are zvb200_search / zvb200_search_rows calls.
+ *  Mirrors FlatSearcher<32> (src/core/algorithm/flat/flat_searcher.h:33-161, flat_searcher.cc:68-245): the embedded
+ *  stock FlatSearcher<32> runs the same load() checks with the same error codes and keeps serving
+ *  create_provider() / get_vector(key) / fetch_vector / group-by over the same mmap'ed file.
  */
 class GpuFlatSearcher : public IndexSearcher {
  public:
   GpuFlatSearcher() = default;
   ~GpuFlatSearcher() override { this->unload(); }
 
-  //! proxima.gpu.device selects the CUDA device (default 0)
   int init(const ailego::Params &params) override {
     params_ = params;
-    params.get("proxima.gpu.device", &device_);
-    return 0;
+    devices_ = parse_devices(params);
+    stock_ = IndexFactory::CreateSearcher("FlatSearcher32");  // never overridden (flat_searcher.cc:250)
+    if (!stock_) return IndexError_NoExist;
+    return stock_->init(params);
   }
-  int cleanup(void) override { return this->unload(); }
+  int cleanup(void) override {
+    this->unload();
+    return stock_ ? stock_->cleanup() : 0;
+  }
 
-  //! Mirrors FlatSearcher::load (flat_searcher.cc:68-159): same checks, same error codes.
+  //! FlatSearcher::load (flat_searcher.cc:68-159) — by the stock object itself — then the upload
   int load(IndexStorage::Pointer cntr, IndexMetric::Pointer measure) override {
     if (!cntr) return IndexError_InvalidArgument;
-    int rc = IndexHelper::DeserializeFromStorage(cntr.get(), &meta_);
+    if (!stock_) {
+      const int r = this->init(params_);
+      if (r != 0) return r;
+    }
+    int rc = stock_->load(cntr, measure);
     if (rc != 0) return rc;
-    if (measure && !measure->is_matched(meta_)) return IndexError_Mismatch;
+    meta_ = stock_->meta();
     const int metric = metric_of(meta_), dtype = dtype_of(meta_);
     if (metric < 0 || dtype < 0) return IndexError_Unsupported;
     auto keys_seg = cntr->get(kSegKeys);
@@ -147,7 +291,7 @@ class GpuFlatSearcher : public IndexSearcher {
     keys_.assign(keys, keys + n);
 
     zvb200_store *st = nullptr;
-    rc = zvb200_store_create(device_, dtype, metric, meta_.dimension(), &st);
+    rc = zvb200_store_create_sharded(devices_.data(), (uint32_t)devices_.size(), dtype, metric, meta_.dimension(), &st);
     if (rc != 0) return rc;
     rc = zvb200_store_reserve(st, n);
     // upload in 64 MiB reads (the reference scans in 4 MiB reads, flat_searcher_context.h:187-196)
@@ -177,7 +321,6 @@ class GpuFlatSearcher : public IndexSearcher {
     if (rc == 0) rc = zvb200_store_seal(st);
     if (rc != 0) { zvb200_store_destroy(st); return rc; }
     store_ = st;
-    container_ = cntr;
     magic_ = IndexContext::GenerateMagic();
     stats_.set_loaded_count(n);
     return 0;
@@ -186,9 +329,13 @@ class GpuFlatSearcher : public IndexSearcher {
   int unload(void) override {
     if (store_) zvb200_store_destroy(store_);
     store_ = nullptr;
-    container_ = nullptr;
     keys_.clear();
-    return 0;
+    {
+      std::lock_guard<std::mutex> g(map_mu_);
+      key_row_.clear();
+      key_row_built_ = false;
+    }
+    return stock_ ? stock_->unload() : 0;
   }
 
   int search_impl(const void *query, const IndexQueryMeta &qmeta, Context::Pointer &context) const override {
@@ -200,38 +347,33 @@ class GpuFlatSearcher : public IndexSearcher {
                   Context::Pointer &context) const override {
     if (!query || !count || !context || !store_) return IndexError_InvalidArgument;
     if (qmeta.element_size() != meta_.element_size()) return IndexError_Mismatch;
-    auto *ctx = dynamic_cast<GpuFlatContext *>(context.get());
+    auto *ctx = dynamic_cast<GpuContext *>(context.get());
     if (!ctx) return IndexError_InvalidArgument;
-    if (ctx->magic() != magic_) ctx->reset(this);
-    const uint32_t k = ctx->topk();
-    ctx->resize_results(count);
-    if (k == 0) {
-      for (uint32_t i = 0; i < count; ++i) ctx->mutable_result(i)->clear();
-      return 0;
+    if (ctx->magic() != magic_) this->rebind(ctx);
+    if (ctx->group_by_search()) {  // flat_searcher.cc:178-179,205-206: bookkeeping per group id, the stock object's
+      log_delegated_once(&logged_group_by_, "GpuFlatSearcher", "a group-by search");
+      ctx->sync_inner();
+      return stock_->search_impl(query, qmeta, count, ctx->inner());
     }
+    const uint32_t k = ctx->topk();
+    ctx->begin(count);
+    if (k == 0) return 0;
     const size_t n = keys_.size();
     const uint32_t *bitmap = nullptr;
+    size_t dropped = 0;
     if (ctx->filter().is_valid()) {
       // IndexFilter: true = drop (flat_searcher_context.h single_enqueue_filter); evaluated
       // once per row on the host, exactly as often as the reference calls it
       ctx->bitmap.assign((n + 31) / 32, 0u);
       for (size_t i = 0; i < n; ++i)
-        if (ctx->filter()(keys_[i])) ctx->bitmap[i >> 5] |= 1u << (i & 31);
+        if (ctx->filter()(keys_[i])) { ctx->bitmap[i >> 5] |= 1u << (i & 31); ++dropped; }
       bitmap = ctx->bitmap.data();
     }
-    const size_t nres = (size_t)count * k;
-    ctx->keys.resize(nres); ctx->scores.resize(nres); ctx->index.resize(nres); ctx->counts.resize(count);
     const int rc = zvb200_search(ctx->handle(), query, count, k, ctx->threshold(), bitmap, ctx->keys.data(),
                                  ctx->scores.data(), ctx->index.data(), ctx->counts.data());
     if (rc != 0) return rc;
-    for (uint32_t i = 0; i < count; ++i) {
-      IndexDocumentList *out = ctx->mutable_result(i);
-      out->clear();
-      for (uint32_t j = 0; j < ctx->counts[i]; ++j) {
-        const size_t o = (size_t)i * k + j;
-        out->emplace_back(ctx->keys[o], ctx->scores[o], ctx->index[o]);
-      }
-    }
+    ctx->fill_stats(count, n - dropped, dropped);
+    this->emit(ctx, count, k);
     return 0;
   }
 
@@ -243,14 +385,69 @@ class GpuFlatSearcher : public IndexSearcher {
     return this->search_impl(query, qmeta, count, context);
   }
 
-  Context::Pointer create_context(void) const override {
-    return Context::Pointer(new (std::nothrow) GpuFlatContext(this));
+  int search_bf_by_p_keys_impl(const void *query, const std::vector<std::vector<uint64_t>> &p_keys,
+                               const IndexQueryMeta &qmeta, Context::Pointer &context) const override {
+    return this->search_bf_by_p_keys_impl(query, p_keys, qmeta, 1, context);
   }
+
+  //! FlatSearcher::search_bf_by_p_keys_impl (flat_searcher.cc:213-237; the loop is
+  //! FlatSearcherContext::search_bf_by_p_keys_impl, the streamer's twin is flat_streamer.cc:347-389): only the listed
+  //! keys are scored — filtered keys and keys the index does not hold are skipped, a key listed twice is scored twice
+  int search_bf_by_p_keys_impl(const void *query, const std::vector<std::vector<uint64_t>> &p_keys,
+                               const IndexQueryMeta &qmeta, uint32_t count, Context::Pointer &context) const override {
+    if (!query || !count || !context || !store_) return IndexError_InvalidArgument;
+    if (p_keys.size() != count) return IndexError_InvalidArgument;
+    if (qmeta.element_size() != meta_.element_size()) return IndexError_Mismatch;
+    auto *ctx = dynamic_cast<GpuContext *>(context.get());
+    if (!ctx) return IndexError_InvalidArgument;
+    if (ctx->magic() != magic_) this->rebind(ctx);
+    if (ctx->group_by_search()) {
+      log_delegated_once(&logged_group_by_, "GpuFlatSearcher", "a group-by search");
+      ctx->sync_inner();
+      return stock_->search_bf_by_p_keys_impl(query, p_keys, qmeta, count, ctx->inner());
+    }
+    const uint32_t k = ctx->topk();
+    ctx->begin(count);
+    if (k == 0) return 0;
+    this->build_key_map();
+    std::vector<std::vector<uint32_t>> rows(count);
+    size_t calced = 0, filtered = 0;
+    for (uint32_t i = 0; i < count; ++i) {
+      rows[i].reserve(p_keys[i].size());
+      for (uint64_t key : p_keys[i]) {
+        if (ctx->filter().is_valid() && ctx->filter()(key)) { ++filtered; continue; }
+        auto it = key_row_.find(key);
+        if (it == key_row_.end()) continue;
+        rows[i].push_back(it->second);
+        ++calced;
+      }
+    }
+    std::vector<std::vector<std::pair<float, std::pair<uint32_t, uint64_t>>>> lists;
+    const int rc = search_rows_sliced(ctx, query, count, rows, k, &lists);
+    if (rc != 0) return rc;
+    for (uint32_t i = 0; i < count; ++i) {
+      IndexDocumentList *out = ctx->mutable_result(i);
+      for (auto &e : lists[i]) this->push_doc(ctx, out, e.second.second, e.first, e.second.first);
+    }
+    ctx->fill_stats(count, calced / count, filtered / count);
+    return 0;
+  }
+
+  Context::Pointer create_context(void) const override {
+    if (!stock_) return Context::Pointer();
+    auto *c = new (std::nothrow) GpuContext(stock_->create_context());
+    if (c) c->bind(store_, magic_);
+    return Context::Pointer(c);
+  }
+  //! FlatSearcher::create_provider (flat_searcher.cc:26-65) / get_vector (flat_searcher.h:158-160): the stock
+  //! object's, over the same mmap'ed file
+  IndexProvider::Pointer create_provider(void) const override { return stock_ ? stock_->create_provider() : nullptr; }
+  const void *get_vector(uint64_t key) const override { return stock_ ? stock_->get_vector(key) : nullptr; }
   const Stats &stats(void) const override { return stats_; }
   const IndexMeta &meta(void) const override { return meta_; }
   const ailego::Params &params(void) const override { return params_; }
 
-  //! IndexRunner::get_vector(key, block): copy one stored row back (reference layout)
+  //! copy one stored row back from the device (reference layout)
   int get_vector_by_id(uint32_t id, void *out, size_t cap) const {
     return store_ ? zvb200_store_get_vector(store_, id, out, cap) : IndexError_NoReady;
   }
@@ -258,23 +455,41 @@ class GpuFlatSearcher : public IndexSearcher {
   zvb200_store *store(void) const { return store_; }
 
  private:
+  void rebind(GpuContext *ctx) const { ctx->bind(store_, magic_); }
+  void build_key_map(void) const {
+    std::lock_guard<std::mutex> g(map_mu_);
+    if (key_row_built_) return;
+    key_row_.reserve(keys_.size());
+    for (size_t i = 0; i < keys_.size(); ++i) key_row_.emplace(keys_[i], (uint32_t)i);  // first row wins, as get_id()
+    key_row_built_ = true;
+  }
+  void push_doc(GpuContext *ctx, IndexDocumentList *out, uint64_t key, float score, uint32_t row) const {
+    if (ctx->fetch_vector()) out->emplace_back(key, score, row, stock_->get_vector(key));  // flat_searcher_context.h:162
+    else out->emplace_back(key, score, row);
+  }
+  void emit(GpuContext *ctx, uint32_t count, uint32_t k) const {
+    for (uint32_t i = 0; i < count; ++i) {
+      IndexDocumentList *out = ctx->mutable_result(i);
+      for (uint32_t j = 0; j < ctx->counts[i]; ++j) {
+        const size_t o = (size_t)i * k + j;
+        this->push_doc(ctx, out, ctx->keys[o], ctx->scores[o], ctx->index[o]);
+      }
+    }
+  }
+
   ailego::Params params_{};
   IndexMeta meta_{};
   Stats stats_{};
-  IndexStorage::Pointer container_{};
+  IndexSearcher::Pointer stock_{};
   std::vector<uint64_t> keys_{};
+  mutable std::mutex map_mu_{};
+  mutable std::unordered_map<uint64_t, uint32_t> key_row_{};
+  mutable bool key_row_built_{false};
+  mutable std::atomic<bool> logged_group_by_{false};
   zvb200_store *store_{nullptr};
   uint32_t magic_{0};
-  int device_{0};
+  std::vector<int> devices_{0};
 };
-
-void GpuFlatContext::reset(const GpuFlatSearcher *owner) {
-  if (ctx_) zvb200_ctx_destroy(ctx_);
-  ctx_ = nullptr;
-  magic_ = owner->magic();
-  if (owner->store()) zvb200_ctx_create(owner->store(), &ctx_);
-  for (auto &r : results_) r.clear();
-}
 
 INDEX_FACTORY_REGISTER_SEARCHER(GpuFlatSearcher);
 
@@ -285,40 +500,6 @@ INDEX_FACTORY_REGISTER_SEARCHER(GpuFlatSearcher);
 // its never-overridden alias "FlatStreamer32" (flat_streamer.cc:486-489); every accepted add is
 // mirrored into the device store, and every search is the GPU scan.
 // ======================================================================================
-class GpuFlatStreamer;
-
-class GpuFlatStreamerContext : public IndexContext {
- public:
-  GpuFlatStreamerContext(const GpuFlatStreamer *owner, IndexContext::Pointer inner) : inner_(std::move(inner)) {
-    this->reset(owner);
-  }
-  ~GpuFlatStreamerContext() override {
-    if (ctx_) zvb200_ctx_destroy(ctx_);
-  }
-  void set_topk(uint32_t topk) override { topk_ = topk; if (inner_) inner_->set_topk(topk); }
-  uint32_t topk() const override { return topk_; }
-  const IndexDocumentList &result(void) const override { return results_[0]; }
-  const IndexDocumentList &result(size_t i) const override { return results_[i]; }
-  IndexDocumentList *mutable_result(size_t i) override { return &results_[i]; }
-  uint32_t magic(void) const override { return magic_; }
-  void reset(const GpuFlatStreamer *owner);
-  zvb200_ctx *handle() const { return ctx_; }
-  IndexContext::Pointer &inner() { return inner_; }
-  void resize_results(size_t n) {
-    if (results_.size() < n) results_.resize(n);
-  }
-  std::vector<uint64_t> keys;
-  std::vector<float> scores;
-  std::vector<uint32_t> index, counts, bitmap;
-
- private:
-  uint32_t topk_{0};
-  uint32_t magic_{0};
-  zvb200_ctx *ctx_{nullptr};
-  IndexContext::Pointer inner_{};
-  std::vector<IndexDocumentList> results_{1};
-};
-
 class GpuFlatStreamer : public IndexStreamer {
  public:
   GpuFlatStreamer() = default;
@@ -331,7 +512,7 @@ class GpuFlatStreamer : public IndexStreamer {
     if (rc != 0) return rc;
     meta_ = stock_->meta();
     meta_.set_streamer("GpuFlatStreamer", 0U, params);
-    params.get("proxima.gpu.device", &device_);
+    params.get(kParamDevice, &device_);
     if (metric_of(meta_) < 0 || dtype_of(meta_) < 0) return IndexError_Unsupported;
     return 0;
   }
@@ -348,7 +529,7 @@ class GpuFlatStreamer : public IndexStreamer {
     if (!stock_) return IndexError_NoReady;
     int rc = stock_->open(stg);
     if (rc != 0) return rc;
-    std::lock_guard<std::mutex> g(mu_);
+    std::unique_lock<std::shared_mutex> g(mu_);
     rc = zvb200_store_create(device_, dtype_of(meta_), metric_of(meta_), meta_.dimension(), &store_);
     if (rc != 0) return rc;
     auto provider = stock_->create_provider();
@@ -367,10 +548,11 @@ class GpuFlatStreamer : public IndexStreamer {
 
   int close(void) override {
     {
-      std::lock_guard<std::mutex> g(mu_);
+      std::unique_lock<std::shared_mutex> g(mu_);
       if (store_) zvb200_store_destroy(store_);
       store_ = nullptr;
-      pend_rows_.clear(); pend_keys_.clear();
+      pend_rows_.clear(); pend_keys_.clear(); all_keys_.clear(); key_row_.clear();
+      identity_ = true; live_ = 0; pending_.store(0);
     }
     return stock_ ? stock_->close() : 0;
   }
@@ -379,31 +561,36 @@ class GpuFlatStreamer : public IndexStreamer {
 
   Context::Pointer create_context(void) const override {
     if (!stock_) return Context::Pointer();
-    return Context::Pointer(new (std::nothrow) GpuFlatStreamerContext(this, stock_->create_context()));
+    auto inner = stock_->create_context();
+    if (!inner) return Context::Pointer();  // FlatStreamer::create_context: "open storage first" (flat_streamer.cc:197-205)
+    auto *c = new (std::nothrow) GpuContext(std::move(inner));
+    if (c) c->bind(store_, magic_);
+    return Context::Pointer(c);
   }
   IndexProvider::Pointer create_provider(void) const override { return stock_ ? stock_->create_provider() : nullptr; }
 
   //! FlatStreamer::add_impl (flat_streamer.cc) -> FlatStreamerEntity::add (flat_streamer_entity.cc:149-210)
   int add_impl(uint64_t pkey, const void *vec, const IndexQueryMeta &qmeta, Context::Pointer &context) override {
-    auto *ctx = dynamic_cast<GpuFlatStreamerContext *>(context.get());
+    auto *ctx = dynamic_cast<GpuContext *>(context.get());
     if (!ctx || !stock_ || !store_) return IndexError_InvalidArgument;
     const int rc = stock_->add_impl(pkey, vec, qmeta, ctx->inner());
     if (rc != 0) return rc;  // duplicate key, size mismatch, index full: nothing to mirror
-    std::lock_guard<std::mutex> g(mu_);
+    std::unique_lock<std::shared_mutex> g(mu_);
     const char *v = static_cast<const char *>(vec);
     pend_rows_.insert(pend_rows_.end(), v, v + meta_.element_size());
     pend_keys_.push_back(pkey);
+    pending_.fetch_add(1);
     return 0;
   }
 
   //! FlatStreamerEntity::add_vector_with_id (flat_streamer_entity.cc:900-991): rows up to `id` become
   //! kInvalidKey holes, row `id` gets key = id; an existing id is overwritten in place
   int add_with_id_impl(uint32_t id, const void *vec, const IndexQueryMeta &qmeta, Context::Pointer &context) override {
-    auto *ctx = dynamic_cast<GpuFlatStreamerContext *>(context.get());
+    auto *ctx = dynamic_cast<GpuContext *>(context.get());
     if (!ctx || !stock_ || !store_) return IndexError_InvalidArgument;
     int rc = stock_->add_with_id_impl(id, vec, qmeta, ctx->inner());
     if (rc != 0) return rc;
-    std::lock_guard<std::mutex> g(mu_);
+    std::unique_lock<std::shared_mutex> g(mu_);
     const size_t es = meta_.element_size();
     const uint64_t on_device = zvb200_store_count(store_);
     const uint64_t total = on_device + pend_keys_.size();
@@ -415,12 +602,17 @@ class GpuFlatStreamer : public IndexStreamer {
       }
       pend_rows_.insert(pend_rows_.end(), v, v + es);
       pend_keys_.push_back(id);
+      pending_.fetch_add(1);
     } else if (id >= on_device) {
       std::memcpy(&pend_rows_[(id - on_device) * es], v, es);
       pend_keys_[id - on_device] = id;
     } else {
       rc = zvb200_store_write(store_, id, vec, id);
-      if (rc == 0) all_keys_[id] = id;
+      if (rc == 0) {
+        if (all_keys_[id] == ZVB200_INVALID_KEY) ++live_;
+        this->note_key(id, id);
+        all_keys_[id] = id;
+      }
     }
     return rc;
   }
@@ -437,45 +629,105 @@ class GpuFlatStreamer : public IndexStreamer {
 
   //! FlatStreamer::search_bf_impl -> FlatStreamerEntity::search / search_block (flat_streamer_entity.cc:212-316)
   int search_bf_impl(const void *query, const IndexQueryMeta &qmeta, uint32_t count, Context::Pointer &context) const override {
-    if (!query || !count || !context || !store_) return IndexError_InvalidArgument;
-    if (qmeta.element_size() != meta_.element_size()) return IndexError_Mismatch;
-    auto *ctx = dynamic_cast<GpuFlatStreamerContext *>(context.get());
-    if (!ctx) return IndexError_InvalidArgument;
-    if (ctx->magic() != magic_) ctx->reset(this);
-    const uint32_t k = ctx->topk();
-    ctx->resize_results(count);
-    for (uint32_t i = 0; i < count; ++i) ctx->mutable_result(i)->clear();
-    if (k == 0) return 0;
-    // publish the rows added since the last search.  A filtered search keeps the lock until it returns: its bitmap
-    // is sized for the rows the store holds NOW, and another thread's search must not publish more in between
-    std::unique_lock<std::mutex> g(mu_);
-    {
-      int rc = const_cast<GpuFlatStreamer *>(this)->flush_pending();
-      if (rc != 0) return rc;
-    }
-    const size_t n = zvb200_store_count(store_);
-    if (n == 0) return 0;
-    const uint32_t *bitmap = nullptr;
-    if (ctx->filter().is_valid()) {
-      ctx->bitmap.assign((n + 31) / 32, 0u);
-      for (size_t i = 0; i < n && i < all_keys_.size(); ++i)
-        if (all_keys_[i] != ZVB200_INVALID_KEY && ctx->filter()(all_keys_[i])) ctx->bitmap[i >> 5] |= 1u << (i & 31);
-      bitmap = ctx->bitmap.data();
-    } else {
-      g.unlock();
-    }
-    const size_t nres = (size_t)count * k;
-    ctx->keys.resize(nres); ctx->scores.resize(nres); ctx->index.resize(nres); ctx->counts.resize(count);
-    const int rc = zvb200_search(ctx->handle(), query, count, k, ctx->threshold(), bitmap, ctx->keys.data(),
-                                 ctx->scores.data(), ctx->index.data(), ctx->counts.data());
+    GpuContext *ctx = nullptr;
+    int rc = this->enter(query, qmeta, count, context, &ctx);
     if (rc != 0) return rc;
+    if (ctx->group_by_search()) {  // flat_streamer.cc:321-323
+      log_delegated_once(&logged_group_by_, "GpuFlatStreamer", "a group-by search");
+      ctx->sync_inner();
+      return stock_->search_bf_impl(query, qmeta, count, ctx->inner());
+    }
+    const uint32_t k = ctx->topk();
+    ctx->begin(count);
+    if (k == 0) return 0;
+    // The rows this search sees = the rows published when it starts.  The filter is evaluated over THAT many keys
+    // under the shared lock (adds wait, other searches do not), and the GPU call runs outside every plugin lock
+    // with the scan limited to the snapshot's rows: rows another thread publishes meanwhile are simply not seen.
+    size_t n = 0, dropped = 0;
+    const uint32_t *bitmap = nullptr;
+    {
+      std::shared_lock<std::shared_mutex> g(mu_);
+      n = all_keys_.size();
+      if (n == 0) return 0;
+      dropped = n - live_;
+      if (ctx->filter().is_valid()) {
+        ctx->bitmap.assign((n + 31) / 32, 0u);
+        for (size_t i = 0; i < n; ++i)
+          if (all_keys_[i] != ZVB200_INVALID_KEY && ctx->filter()(all_keys_[i])) {
+            ctx->bitmap[i >> 5] |= 1u << (i & 31);
+            ++dropped;
+          }
+        bitmap = ctx->bitmap.data();
+      }
+    }
+    zvb200_ctx_set_row_limit(ctx->handle(), n);
+    rc = zvb200_search(ctx->handle(), query, count, k, ctx->threshold(), bitmap, ctx->keys.data(),
+                       ctx->scores.data(), ctx->index.data(), ctx->counts.data());
+    zvb200_ctx_set_row_limit(ctx->handle(), 0);
+    if (rc != 0) return rc;
+    // flat_streamer_entity.cc:246 (no filter, no deletion: every row of a block counts) / :306-314
+    ctx->fill_stats(count, bitmap || dropped ? n - dropped : n, bitmap || dropped ? dropped : 0);
     for (uint32_t i = 0; i < count; ++i) {
       IndexDocumentList *out = ctx->mutable_result(i);
       for (uint32_t j = 0; j < ctx->counts[i]; ++j) {
         const size_t o = (size_t)i * k + j;
-        out->emplace_back(ctx->keys[o], ctx->scores[o], ctx->keys[o]);  // index() = key (flat_streamer_context.h:125)
+        this->push_doc(ctx, out, ctx->keys[o], ctx->scores[o]);
       }
     }
+    return 0;
+  }
+
+  int search_bf_by_p_keys_impl(const void *query, const std::vector<std::vector<uint64_t>> &p_keys,
+                               const IndexQueryMeta &qmeta, Context::Pointer &context) const override {
+    return this->search_bf_by_p_keys_impl(query, p_keys, qmeta, 1, context);
+  }
+
+  //! FlatStreamer::search_bf_by_p_keys_impl (flat_streamer.cc:347-389): what core_interface::Index::_dense_search
+  //! calls whenever bf_pks is set (index.cc:603-610) — the second stage of the refiner flow (index.cc:408-445)
+  int search_bf_by_p_keys_impl(const void *query, const std::vector<std::vector<uint64_t>> &p_keys,
+                               const IndexQueryMeta &qmeta, uint32_t count, Context::Pointer &context) const override {
+    GpuContext *ctx = nullptr;
+    int rc = this->enter(query, qmeta, count, context, &ctx);
+    if (rc != 0) return rc;
+    if (p_keys.size() < count) return IndexError_InvalidArgument;
+    if (ctx->group_by_search()) {  // flat_streamer.cc:365-367
+      log_delegated_once(&logged_group_by_, "GpuFlatStreamer", "a group-by search");
+      ctx->sync_inner();
+      return stock_->search_bf_by_p_keys_impl(query, p_keys, qmeta, count, ctx->inner());
+    }
+    const uint32_t k = ctx->topk();
+    ctx->begin(count);
+    if (k == 0) return 0;
+    std::vector<std::vector<uint32_t>> rows(count);
+    size_t calced = 0, filtered = 0;
+    {
+      std::shared_lock<std::shared_mutex> g(mu_);
+      const size_t n = all_keys_.size();
+      for (uint32_t i = 0; i < count; ++i) {
+        rows[i].reserve(p_keys[i].size());
+        for (uint64_t key : p_keys[i]) {
+          if (ctx->filter().is_valid() && ctx->filter()(key)) { ++filtered; continue; }
+          uint32_t row = ZVB200_INVALID_INDEX;
+          if (identity_) {
+            if (key < n && all_keys_[key] == key) row = (uint32_t)key;
+          } else {
+            auto it = key_row_.find(key);
+            if (it != key_row_.end()) row = it->second;
+          }
+          if (row == ZVB200_INVALID_INDEX) continue;  // get_vector_by_key fails: skipped (flat_streamer.cc:379)
+          rows[i].push_back(row);
+          ++calced;
+        }
+      }
+    }
+    std::vector<std::vector<std::pair<float, std::pair<uint32_t, uint64_t>>>> lists;
+    rc = search_rows_sliced(ctx, query, count, rows, k, &lists);
+    if (rc != 0) return rc;
+    for (uint32_t i = 0; i < count; ++i) {
+      IndexDocumentList *out = ctx->mutable_result(i);
+      for (auto &e : lists[i]) this->push_doc(ctx, out, e.second.second, e.first);
+    }
+    ctx->fill_stats(count, calced / count, filtered / count);
     return 0;
   }
 
@@ -485,19 +737,63 @@ class GpuFlatStreamer : public IndexStreamer {
   int get_vector(const uint64_t key, IndexStorage::MemoryBlock &block) const override {
     return stock_ ? stock_->get_vector(key, block) : IndexError_NoReady;
   }
+  const void *get_vector_by_id(uint32_t id) const override { return stock_ ? stock_->get_vector_by_id(id) : nullptr; }
+  int get_vector_by_id(const uint32_t id, IndexStorage::MemoryBlock &block) const override {
+    return stock_ ? stock_->get_vector_by_id(id, block) : IndexError_NoReady;
+  }
   uint32_t magic(void) const { return magic_; }
   zvb200_store *store(void) const { return store_; }
 
  private:
-  //! pending host rows -> device store; caller holds mu_
+  //! argument checks, context rebinding and publication of pending rows shared by every search entry
+  int enter(const void *query, const IndexQueryMeta &qmeta, uint32_t count, Context::Pointer &context,
+            GpuContext **out) const {
+    if (!query || !count || !context || !store_) return IndexError_InvalidArgument;
+    if (qmeta.element_size() != meta_.element_size()) return IndexError_Mismatch;
+    auto *ctx = dynamic_cast<GpuContext *>(context.get());
+    if (!ctx) return IndexError_InvalidArgument;
+    if (ctx->magic() != magic_) ctx->bind(store_, magic_);
+    if (pending_.load() != 0) {
+      std::unique_lock<std::shared_mutex> g(mu_);
+      const int rc = const_cast<GpuFlatStreamer *>(this)->flush_pending();
+      if (rc != 0) return rc;
+    }
+    *out = ctx;
+    return 0;
+  }
+  void push_doc(GpuContext *ctx, IndexDocumentList *out, uint64_t key, float score) const {
+    if (ctx->fetch_vector()) {  // FlatStreamerContext::topk_to_result (flat_streamer_context.h:119-124)
+      IndexStorage::MemoryBlock block;
+      stock_->get_vector(key, block);
+      out->emplace_back(key, score, key, block);
+    } else {
+      out->emplace_back(key, score, key);  // index() = key (flat_streamer_context.h:125)
+    }
+  }
+  void note_key(uint64_t row, uint64_t key) {
+    if (key == ZVB200_INVALID_KEY) return;
+    if (identity_ && key != row) {  // first key that is not its row: from now on a real map
+      identity_ = false;
+      key_row_.reserve(all_keys_.size() + 1024);
+      for (size_t i = 0; i < all_keys_.size(); ++i)
+        if (all_keys_[i] != ZVB200_INVALID_KEY) key_row_.emplace(all_keys_[i], (uint32_t)i);
+    }
+    if (!identity_) key_row_[key] = (uint32_t)row;
+  }
+  //! pending host rows -> device store; caller holds mu_ exclusively
   int flush_pending(void) {
     if (!pend_keys_.empty()) {
       const int rc = zvb200_store_append(store_, pend_rows_.data(), pend_keys_.size(), pend_keys_.data());
       if (rc != 0) return rc;
-      all_keys_.insert(all_keys_.end(), pend_keys_.begin(), pend_keys_.end());
+      for (uint64_t key : pend_keys_) {
+        this->note_key(all_keys_.size(), key);
+        all_keys_.push_back(key);
+        if (key != ZVB200_INVALID_KEY) ++live_;
+      }
       pend_rows_.clear(); pend_keys_.clear();
       dirty_ = true;
     }
+    pending_.store(0);
     if (dirty_) {
       const int rc = zvb200_store_seal(store_);
       if (rc != 0) return rc;
@@ -508,67 +804,47 @@ class GpuFlatStreamer : public IndexStreamer {
 
   IndexStreamer::Pointer stock_{};
   IndexMeta meta_{};
-  mutable std::mutex mu_{};
+  mutable std::shared_mutex mu_{};
   zvb200_store *store_{nullptr};
   std::vector<char> pend_rows_{};
   std::vector<uint64_t> pend_keys_{}, all_keys_{};
+  std::unordered_map<uint64_t, uint32_t> key_row_{};  // only once a key differs from its row (add_impl with own keys)
+  bool identity_{true};
+  size_t live_{0};
+  std::atomic<size_t> pending_{0};
+  mutable std::atomic<bool> logged_group_by_{false};
   bool dirty_{true};
   uint32_t magic_{0};
   int device_{0};
 };
 
-void GpuFlatStreamerContext::reset(const GpuFlatStreamer *owner) {
-  if (ctx_) zvb200_ctx_destroy(ctx_);
-  ctx_ = nullptr;
-  magic_ = owner->magic();
-  if (owner->store()) zvb200_ctx_create(owner->store(), &ctx_);
-  for (auto &r : results_) r.clear();
-}
-
 INDEX_FACTORY_REGISTER_STREAMER(GpuFlatStreamer);
 
 // ======================================================================================
 // GpuIVFSearcher — IVFSearcher's interface (ivf_searcher.h:28-118).  Composition: a stock
-// IVFSearcher loads the index (centroid index, reformer wiring, brute-force / group-by paths,
-// integer-quantised variants whose scores need per-list scales) and serves whatever is not
-// accelerated; the posting lists it holds are exported ONCE through the reference's own
+// IVFSearcher loads the index (centroid index, reformer wiring, group-by, and the index layouts the
+// device store cannot hold); the posting lists it holds are exported ONCE through the reference's own
 // IVFEntity reader into a device store grouped by list, the centroids of its nested Flat index
-// become the coarse store, and search_impl is zvb200_ivf_search.
+// become the coarse store, search_impl is zvb200_ivf_search and search_bf_impl (every list, and what
+// search_impl does for an index at or below brute_force_threshold, ivf_searcher.cc:185-187) is zvb200_search
+// over the same store.
 // ======================================================================================
 class GpuIVFSearcher;
 
-class GpuIVFContext : public IndexContext {
+class GpuIVFContext : public GpuContext {
  public:
-  GpuIVFContext(const GpuIVFSearcher *owner, IndexContext::Pointer inner) : inner_(std::move(inner)) { this->reset(owner); }
-  ~GpuIVFContext() override {
-    if (ctx_) zvb200_ctx_destroy(ctx_);
-  }
-  void set_topk(uint32_t topk) override { topk_ = topk; if (inner_) inner_->set_topk(topk); }
-  uint32_t topk() const override { return topk_; }
-  const IndexDocumentList &result(void) const override { return results_[0]; }
-  const IndexDocumentList &result(size_t i) const override { return results_[i]; }
-  IndexDocumentList *mutable_result(size_t i) override { return &results_[i]; }
-  uint32_t magic(void) const override { return magic_; }
+  GpuIVFContext(const GpuIVFSearcher *owner, IndexContext::Pointer inner) : GpuContext(std::move(inner)) { this->reset(owner); }
   int update(const ailego::Params &params) override;
   void reset(const GpuIVFSearcher *owner);
-  zvb200_ctx *handle() const { return ctx_; }
-  IndexContext::Pointer &inner() { return inner_; }
-  void resize_results(size_t n) {
-    if (results_.size() < n) results_.resize(n);
-  }
+  //! the reformer inside an IVFEntity keeps a scratch buffer: one clone per context, owned by the context
+  //! (IVFSearcher::update_context does the same for its own contexts)
+  IVFEntity *entity() { return entity_.get(); }
   uint32_t nprobe{1};
   uint64_t max_scan{0};
-  std::vector<uint64_t> keys;
-  std::vector<float> scores;
-  std::vector<uint32_t> index, counts, bitmap;
 
  private:
   const GpuIVFSearcher *owner_{nullptr};
-  uint32_t topk_{0};
-  uint32_t magic_{0};
-  zvb200_ctx *ctx_{nullptr};
-  IndexContext::Pointer inner_{};
-  std::vector<IndexDocumentList> results_{1};
+  IVFEntity::Pointer entity_{};
 };
 
 class GpuIVFSearcher : public IndexSearcher {
@@ -578,7 +854,7 @@ class GpuIVFSearcher : public IndexSearcher {
 
   int init(const ailego::Params &params) override {
     params_ = params;
-    params.get("proxima.gpu.device", &device_);
+    params.get(kParamDevice, &device_);
     params.get(PARAM_IVF_SEARCHER_BRUTE_FORCE_THRESHOLD, &bf_threshold_);
     return stock_.init(params);
   }
@@ -595,12 +871,15 @@ class GpuIVFSearcher : public IndexSearcher {
     rc = entity_.load(cntr);
     if (rc != 0) return rc;
     // scores of the integer-quantised variants carry per-list / global scales (IVFEntity::load,
-    // ivf_entity.cc:541-564; IVFReformerWrapper::normalize :325-353): those stay on the stock path
+    // ivf_entity.cc:541-564; IVFReformerWrapper::normalize :325-353): the device store has no per-list scale
     const std::string &rf = meta_.reformer_name();
     accelerated_ = !cntr->get(IVF_INT8_QUANTIZED_PARAMS_SEG_ID) && !cntr->get(IVF_INT4_QUANTIZED_PARAMS_SEG_ID) &&
                    rf != kInt8ReformerName && rf != kInt4ReformerName && metric_of(meta_) >= 0 && dtype_of(meta_) >= 0 &&
-                   entity_.vector_count() > bf_threshold_;
-    if (!accelerated_) return 0;
+                   entity_.vector_count() > 0;
+    if (!accelerated_) {
+      why_not_ = "an index with integer-quantiser scales or an unsupported type";
+      return 0;
+    }
     // centroids = the nested Flat index in segment "ivf.centroid" (ivf_searcher.cc:62-86); row cid = centroid cid
     auto seg = cntr->get(IVF_CENTROID_SEG_ID, 0);
     if (!seg) return IndexError_InvalidFormat;
@@ -612,7 +891,8 @@ class GpuIVFSearcher : public IndexSearcher {
     const size_t nl = entity_.inverted_list_count(), n = entity_.vector_count(), es = meta_.element_size();
     if (!fseg || !kseg || cmeta.element_size() != es || cmeta.data_type() != meta_.data_type() ||
         kseg->data_size() != nl * sizeof(uint64_t) || fseg->data_size() != nl * es) {
-      accelerated_ = false;  // a centroid index of another shape (e.g. HNSW over centroids): stock path
+      accelerated_ = false;  // a centroid index of another shape (e.g. HNSW over centroids)
+      why_not_ = "an index whose centroid index is not a Flat index of the lists' type";
       return 0;
     }
     const void *fp = nullptr;
@@ -683,56 +963,23 @@ class GpuIVFSearcher : public IndexSearcher {
   int search_bf_impl(const void *query, const IndexQueryMeta &qmeta, Context::Pointer &context) const override {
     return this->search_bf_impl(query, qmeta, 1, context);
   }
+  //! IVFSearcher::search_bf_impl (ivf_searcher.cc:125-176): every posting list = one flat scan of the store
   int search_bf_impl(const void *query, const IndexQueryMeta &qmeta, uint32_t count, Context::Pointer &context) const override {
-    return delegate(true, query, qmeta, count, context);
+    return this->run(true, query, qmeta, count, context);
   }
   int search_impl(const void *query, const IndexQueryMeta &qmeta, Context::Pointer &context) const override {
     return this->search_impl(query, qmeta, 1, context);
   }
-
   //! IVFSearcher::search_impl (ivf_searcher.cc:183-250)
   int search_impl(const void *query, const IndexQueryMeta &qmeta, uint32_t count, Context::Pointer &context) const override {
-    auto *ctx = dynamic_cast<GpuIVFContext *>(context.get());
-    if (!ctx || ctx->topk() == 0) return IndexError_InvalidArgument;
-    if (!accelerated_ || !store_ || ctx->group_by().is_valid()) return delegate(false, query, qmeta, count, context);
-    if (!query || qmeta.element_size() != meta_.element_size()) return IndexError_InvalidArgument;
-    if (ctx->magic() != magic_) ctx->reset(this);
-    // queries into the posting lists' format (entity->transform, ivf_searcher.cc:211-214)
-    const void *tq = query;
-    IndexQueryMeta iv_qmeta;
-    int rc = entity_for(ctx)->transform(query, qmeta, count, &tq, &iv_qmeta);
-    if (rc != 0) return rc;
-    const uint32_t k = ctx->topk();
-    const size_t n = keys_.size();
-    const uint32_t *bitmap = nullptr;
-    if (ctx->filter().is_valid()) {
-      ctx->bitmap.assign((n + 31) / 32, 0u);
-      for (size_t i = 0; i < n; ++i)
-        if (ctx->filter()(keys_[i])) ctx->bitmap[i >> 5] |= 1u << (i & 31);
-      bitmap = ctx->bitmap.data();
-    }
-    const size_t nres = (size_t)count * k;
-    ctx->keys.resize(nres); ctx->scores.resize(nres); ctx->index.resize(nres); ctx->counts.resize(count);
-    rc = zvb200_ivf_search(ctx->handle(), tq, count, k, ctx->nprobe, ctx->max_scan, ctx->threshold(), bitmap,
-                           ctx->keys.data(), ctx->scores.data(), ctx->index.data(), ctx->counts.data());
-    if (rc != 0) return rc;
-    ctx->resize_results(count);
-    for (uint32_t i = 0; i < count; ++i) {
-      IndexDocumentList *out = ctx->mutable_result(i);
-      out->clear();
-      for (uint32_t j = 0; j < ctx->counts[i]; ++j) {
-        const size_t o = (size_t)i * k + j;
-        out->emplace_back(ctx->keys[o], ctx->scores[o]);  // key and score only (ivf_searcher_context.h:196)
-      }
-    }
-    return 0;
+    // an index at or below the brute-force threshold is scanned whole (ivf_searcher.cc:185-187)
+    return this->run(entity_.vector_count() <= bf_threshold_, query, qmeta, count, context);
   }
 
   Context::Pointer create_context(void) const override {
     auto inner = stock_.create_context();
     if (!inner) return Context::Pointer();
     auto *c = new (std::nothrow) GpuIVFContext(this, std::move(inner));
-    if (c) c->update(params_);
     return Context::Pointer(c);
   }
   IndexProvider::Pointer create_provider(void) const override { return stock_.create_provider(); }
@@ -744,49 +991,89 @@ class GpuIVFSearcher : public IndexSearcher {
   size_t list_count(void) const { return entity_.inverted_list_count(); }
   size_t vector_count(void) const { return entity_.vector_count(); }
   uint32_t bf_threshold(void) const { return bf_threshold_; }
+  IVFEntity::Pointer clone_entity(void) const { return entity_.clone(); }
   //! what IVFStreamer::get_vector_by_id reads (ivf_streamer.h:79-82)
   int vector_by_key(uint64_t key, IndexStorage::MemoryBlock &block) const { return entity_.get_vector_by_key(key, block); }
   //! the device store AND the stock searcher's index (IVFStreamer::unload, ivf_streamer.cc:119-129)
   int unload_all(void) {
     this->unload();
-    {
-      std::lock_guard<std::mutex> g(mu_);
-      clones_.clear();
-    }
     return stock_.unload();
   }
 
  private:
-  // the reformer inside an IVFEntity keeps a scratch buffer: one clone per context (IVFSearcher::update_context)
-  IVFEntity *entity_for(GpuIVFContext *ctx) const {
-    std::lock_guard<std::mutex> g(mu_);
-    auto &e = clones_[ctx];
-    if (!e) e = entity_.clone();
-    return e.get();
+  int run(bool brute_force, const void *query, const IndexQueryMeta &qmeta, uint32_t count, Context::Pointer &context) const {
+    auto *ctx = dynamic_cast<GpuIVFContext *>(context.get());
+    if (!ctx || ctx->topk() == 0) return IndexError_InvalidArgument;
+    if (!accelerated_ || !store_) {
+      log_delegated_once(&logged_layout_, "GpuIVFSearcher", why_not_);
+      return this->delegate(brute_force, query, qmeta, count, context);
+    }
+    if (ctx->group_by_search() || ctx->group_by().is_valid()) {
+      log_delegated_once(&logged_group_by_, "GpuIVFSearcher", "a group-by search");
+      return this->delegate(brute_force, query, qmeta, count, context);
+    }
+    if (!query || !count) return IndexError_InvalidArgument;
+    if (ctx->magic() != magic_) ctx->reset(this);
+    // queries into the posting lists' format (entity->transform, ivf_searcher.cc:211-214)
+    const void *tq = query;
+    IndexQueryMeta iv_qmeta;
+    int rc = ctx->entity()->transform(query, qmeta, count, &tq, &iv_qmeta);
+    if (rc != 0) return rc;
+    if (iv_qmeta.element_size() != meta_.element_size()) return IndexError_Mismatch;
+    const uint32_t k = ctx->topk();
+    ctx->begin(count);
+    const size_t n = keys_.size();
+    const uint32_t *bitmap = nullptr;
+    size_t dropped = 0;
+    if (ctx->filter().is_valid()) {
+      ctx->bitmap.assign((n + 31) / 32, 0u);
+      for (size_t i = 0; i < n; ++i)
+        if (ctx->filter()(keys_[i])) { ctx->bitmap[i >> 5] |= 1u << (i & 31); ++dropped; }
+      bitmap = ctx->bitmap.data();
+    }
+    if (brute_force)
+      rc = zvb200_search(ctx->handle(), tq, count, k, ctx->threshold(), bitmap, ctx->keys.data(), ctx->scores.data(),
+                         ctx->index.data(), ctx->counts.data());
+    else
+      rc = zvb200_ivf_search(ctx->handle(), tq, count, k, ctx->nprobe, ctx->max_scan, ctx->threshold(), bitmap,
+                             ctx->keys.data(), ctx->scores.data(), ctx->index.data(), ctx->counts.data());
+    if (rc != 0) return rc;
+    if (brute_force) ctx->fill_stats(count, n - dropped, dropped);
+    for (uint32_t i = 0; i < count; ++i) {
+      IndexDocumentList *out = ctx->mutable_result(i);
+      for (uint32_t j = 0; j < ctx->counts[i]; ++j) {
+        const size_t o = (size_t)i * k + j;
+        if (ctx->fetch_vector()) {  // IVFSearcherContext::topk_to_result (ivf_searcher_context.h:190-197)
+          IndexStorage::MemoryBlock block;
+          entity_.get_vector_by_key(ctx->keys[o], block);
+          out->emplace_back(ctx->keys[o], ctx->scores[o], ctx->keys[o], block);
+        } else {
+          out->emplace_back(ctx->keys[o], ctx->scores[o]);  // key and score only (ivf_searcher_context.h:196)
+        }
+      }
+    }
+    return 0;
   }
-  //! what is not accelerated runs on the stock searcher with the caller's settings, results copied back
+  //! the stock searcher with the caller's settings, results copied back
   int delegate(bool bf, const void *query, const IndexQueryMeta &qmeta, uint32_t count, Context::Pointer &context) const {
     auto *ctx = dynamic_cast<GpuIVFContext *>(context.get());
     if (!ctx) return IndexError_InvalidArgument;
+    ctx->sync_inner();
     auto &in = ctx->inner();
-    in->set_topk(ctx->topk());
-    if (ctx->filter().is_valid()) in->set_filter(ctx->filter());
-    in->set_threshold(ctx->threshold());
     const int rc = bf ? stock_.search_bf_impl(query, qmeta, count, in) : stock_.search_impl(query, qmeta, count, in);
     if (rc != 0) return rc;
-    ctx->resize_results(count);
-    for (uint32_t i = 0; i < count; ++i) *ctx->mutable_result(i) = in->result(i);
+    ctx->take_inner_results(count);
     return 0;
   }
 
   IVFSearcher stock_{};
   IVFEntity entity_{};
-  mutable std::mutex mu_{};
-  mutable std::map<const GpuIVFContext *, IVFEntity::Pointer> clones_{};
   ailego::Params params_{};
   IndexMeta meta_{};
   std::vector<uint64_t> keys_{};
   zvb200_store *store_{nullptr};
+  const char *why_not_{"an index that was not loaded"};
+  mutable std::atomic<bool> logged_group_by_{false}, logged_layout_{false};
   uint32_t bf_threshold_{1000u};
   uint32_t magic_{0};
   int device_{0};
@@ -809,12 +1096,9 @@ int GpuIVFContext::update(const ailego::Params &params) {
 }
 
 void GpuIVFContext::reset(const GpuIVFSearcher *owner) {
-  if (ctx_) zvb200_ctx_destroy(ctx_);
-  ctx_ = nullptr;
   owner_ = owner;
-  magic_ = owner->magic();
-  if (owner->store()) zvb200_ctx_create(owner->store(), &ctx_);
-  for (auto &r : results_) r.clear();
+  this->bind(owner->store(), owner->magic());
+  entity_ = owner->clone_entity();
   this->update(owner->params());
 }
 

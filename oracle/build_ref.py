@@ -7,7 +7,7 @@ bench.py's cpu_baseline / --impl reference legs do.
 
 Recipe: every *.cc under src/ailego except
 ailego/buffer/buffer_manager.cc (needs Arrow), ailego/encoding/json/mod_json.c,
-every *.cc of src/core/{framework,metric,quantizer}, src/core/algorithm/
+every *.cc of src/core/{framework,metric,quantizer,interface}, src/core/algorithm/
 {flat,cluster,ivf} and src/core/utility except buffer_storage.cc, compiled where
 they lie under /root/reference (never copied), plus oracle/ref_shim.cc (ours: a
 C ABI over the reference's builder/searcher/converter classes) and a 3-method
@@ -25,6 +25,7 @@ import subprocess
 import sys
 
 HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(HERE)
 REF = os.environ.get("ZVEC_REFERENCE", "/root/reference")
 OUT = os.path.join(HERE, "_ref")
 
@@ -38,8 +39,11 @@ def sources():
             if f.endswith(".cc") and not p.endswith("buffer/buffer_manager.cc"):
                 tus.append(p)
     tus.append(os.path.join(src, "ailego/encoding/json/mod_json.c"))
+    # core/interface = core_interface::Index / FlatIndex / IVFIndex / IndexFactory: the layer the DB calls
+    # (vector_column_indexer.cc:195); it needs only the vendored header-only magic_enum
     for d in ("core/framework", "core/metric", "core/quantizer", "core/utility",
-              "core/algorithm/flat", "core/algorithm/cluster", "core/algorithm/ivf"):
+              "core/algorithm/flat", "core/algorithm/cluster", "core/algorithm/ivf",
+              "core/interface", "core/interface/indexes"):
         for f in sorted(os.listdir(os.path.join(src, d))):
             if f.endswith(".cc") and f != "buffer_storage.cc":
                 tus.append(os.path.join(src, d, f))
@@ -53,7 +57,9 @@ def compile_one(args):
     os.makedirs(os.path.dirname(objp), exist_ok=True)
     src = os.path.join(REF, "src")
     inc = ["-I" + os.path.join(HERE, "stub"), "-I" + src, "-I" + os.path.join(src, "include"),
-           "-I" + os.path.join(src, "core"), "-I" + os.path.join(src, "core/algorithm")]
+           "-I" + os.path.join(src, "core"), "-I" + os.path.join(src, "core/algorithm"),
+           "-I" + os.path.join(REF, "thirdparty/magic_enum/magic_enum-0.9.7/include"),
+           "-I" + os.path.join(ROOT, "include"), "-I" + os.path.join(ROOT, "integration")]
     if srcp.endswith(".c"):
         cmd = ["gcc", "-O2", "-fPIC", "-march=" + march] + inc + ["-c", srcp, "-o", objp]
     else:

@@ -6,6 +6,7 @@
 // reformer->transform(query) -> searcher->search_impl(query, qmeta, count, ctx)
 // -> metric->normalize(score); and how tests build indexes
 // (tests/core/algorithm/flat/flat_searcher_test.cpp:29-78).
+#include <stdlib.h>
 #include <unistd.h>
 #include <atomic>
 #include <cstdio>
@@ -20,6 +21,7 @@
 #include <zvec/core/framework/index_converter.h>
 #include <zvec/core/framework/index_factory.h>
 #include <zvec/core/framework/index_holder.h>
+#include <zvec/core/framework/index_memory.h>
 #include <zvec/core/framework/index_meta.h>
 #include <zvec/core/framework/index_metric.h>
 #include <zvec/core/framework/index_reformer.h>
@@ -27,6 +29,8 @@
 #include <zvec/core/framework/index_searcher.h>
 #include <zvec/core/framework/index_segment_storage.h>
 #include <zvec/core/framework/index_streamer.h>
+#include <zvec/core/interface/index.h>
+#include <zvec/core/interface/index_factory.h>
 #include "ivf/ivf_entity.h"
 #include "ivf/ivf_index_format.h"
 
@@ -76,7 +80,10 @@ struct RefIndex {
   ~RefIndex() {
     if (streamer) { streamer->close(); streamer->cleanup(); }
     if (searcher) { searcher->unload(); searcher->cleanup(); }
-    if (!path.empty()) ::unlink(path.c_str());
+    if (!path.empty()) {
+      ::unlink(path.c_str());
+      IndexMemory::Instance()->remove(path);  // a ZREF_MEMORY_INDEX index
+    }
   }
 };
 
@@ -141,8 +148,9 @@ void *zref_index_create(const char *kind, const void *rows, uint64_t n, uint32_t
     }
   }
   ix->meta.set_major_order(column_major ? IndexMeta::MO_COLUMN : IndexMeta::MO_ROW);
-  // keep the stored bytes (what a device store must ingest)
-  {
+  // keep the stored bytes (what a device store must ingest); ZREF_NO_STORED_COPY=1 skips the copy (full-size CPU arm)
+  const char *nocopy = getenv("ZREF_NO_STORED_COPY");
+  if (!(nocopy && atoi(nocopy) != 0)) {
     size_t es = ix->meta.element_size();
     ix->stored.resize(n * es);
     auto it = holder->create_iterator();
@@ -165,8 +173,12 @@ void *zref_index_create(const char *kind, const void *rows, uint64_t n, uint32_t
   char buf[256];
   snprintf(buf, sizeof buf, "/tmp/zref_%d_%d.index", (int)getpid(), seq++);
   ix->path = buf;
+  // ZREF_MEMORY_INDEX=1: MemoryDumper / MemoryReadStorage instead of a file under /tmp (the full-size CPU arm of
+  // bench.py: 15 GB must not depend on the box's disk)
+  const char *memenv = getenv("ZREF_MEMORY_INDEX");
+  const bool in_memory = memenv && atoi(memenv) != 0;
   auto builder = IndexFactory::CreateBuilder(k + "Builder");
-  auto dumper = IndexFactory::CreateDumper("FileDumper");
+  auto dumper = IndexFactory::CreateDumper(in_memory ? "MemoryDumper" : "FileDumper");
   if (!builder || !dumper) { fail(-1, "no builder"); return nullptr; }
   Params bp; parse_params(build_params, &bp);
   int r = builder->init(ix->meta, bp);
@@ -176,7 +188,7 @@ void *zref_index_create(const char *kind, const void *rows, uint64_t n, uint32_t
   if (r != 0) { fail(r, "build"); return nullptr; }
   dumper->close();
   ix->searcher = IndexFactory::CreateSearcher(searcher_name);
-  auto storage = IndexFactory::CreateStorage("MMapFileReadStorage");
+  auto storage = IndexFactory::CreateStorage(in_memory ? "MemoryReadStorage" : "MMapFileReadStorage");
   Params sp; parse_params(search_params, &sp);
   if (!ix->searcher || !storage) { fail(-1, "no searcher"); return nullptr; }
   if (ix->searcher->init(sp) != 0) { fail(-1, "searcher init"); return nullptr; }
@@ -247,6 +259,11 @@ static thread_local uint64_t g_fmod = 0, g_frem = 0;
 static thread_local float g_threshold = 0.f;
 static thread_local int g_has_threshold = 0;
 void zref_set_filter(uint64_t mod, uint64_t rem) { g_fmod = mod; g_frem = rem; }
+// Group-by on the next streamer searches: group id = decimal string of (key % mod); group_num groups of group_topk
+// documents (IndexContext::set_group_params / set_group_by).  mod = 0: off.
+static thread_local uint64_t g_gmod = 0;
+static thread_local uint32_t g_gnum = 0, g_gtopk = 0;
+void zref_set_group_by(uint64_t mod, uint32_t group_num, uint32_t group_topk) { g_gmod = mod; g_gnum = group_num; g_gtopk = group_topk; }
 void zref_set_threshold(int on, float v) { g_has_threshold = on; g_threshold = v; }
 
 // Stored (post-converter) layout: dtype, dimension, element bytes, metric name.
@@ -358,6 +375,70 @@ int zref_index_search(void *h, const void *queries, uint32_t count, uint32_t top
   return err.load();
 }
 
+// search_bf_by_p_keys_impl through whichever searcher / streamer the index holds: the same key list for every query
+// (FlatSearcher::search_bf_by_p_keys_impl, flat_searcher.cc:213-237).  With zref_set_group_by the call is a group-by
+// search and the groups come back flattened.  Stored-format queries are made by the index's reformer.
+int zref_index_search_keys(void *h, const void *queries, uint32_t count, const uint64_t *pks, uint32_t npks,
+                           uint32_t topk, uint64_t *out_keys, float *out_scores, uint32_t *out_counts) {
+  auto ix = (RefIndex *)h;
+  size_t oes = ix->meta.element_size();
+  std::string tq((size_t)count * oes, '\0');
+  int r = zref_index_transform_queries(h, queries, count, &tq[0], tq.size());
+  if (r < 0) return r;
+  IndexQueryMeta qm(ix->meta.data_type(), ix->meta.dimension());
+  IndexRunner *run = ix->runner();
+  auto ctx = run->create_context();
+  if (!ctx) return fail(-1, "context");
+  ctx->set_topk(topk);
+  const uint64_t fmod = g_fmod, frem = g_frem, gm = g_gmod;
+  if (fmod) ctx->set_filter([fmod, frem](uint64_t key) { return key % fmod == frem; });
+  if (gm) {
+    ctx->set_group_params(g_gnum, g_gtopk);
+    ctx->set_group_by([gm](uint64_t key) { return std::to_string(key % gm); });
+  }
+  int rc;
+  if (pks) {
+    std::vector<std::vector<uint64_t>> keys(count, std::vector<uint64_t>(pks, pks + npks));
+    rc = run->search_bf_by_p_keys_impl(tq.data(), keys, qm, count, ctx);
+  } else {
+    rc = run->search_impl(tq.data(), qm, count, ctx);
+  }
+  if (rc != 0) return fail(rc, "search");
+  for (uint32_t i = 0; i < count; ++i) {
+    uint32_t c = 0;
+    auto put = [&](const IndexDocument &doc) {
+      if (c >= topk) return;
+      out_keys[(size_t)i * topk + c] = doc.key();
+      out_scores[(size_t)i * topk + c] = doc.score();
+      ++c;
+    };
+    if (gm) { for (const auto &grp : ctx->group_result(i)) for (const auto &doc : grp.docs()) put(doc); }
+    else { for (const auto &doc : ctx->result(i)) put(doc); }
+    out_counts[i] = c;
+    for (uint32_t j = c; j < topk; ++j) { out_keys[(size_t)i * topk + j] = ~0ull; out_scores[(size_t)i * topk + j] = __builtin_nanf(""); }
+  }
+  return 0;
+}
+
+// IndexSearcher::get_vector(key) and create_provider()->get_vector(key): the stored bytes of one document, twice
+// (out = 2 * element_size bytes).  Returns element_size, or < 0 when either lookup fails.
+int zref_index_get_vector(void *h, uint64_t key, void *out, uint64_t cap) {
+  auto ix = (RefIndex *)h;
+  const size_t es = ix->meta.element_size();
+  if (cap < 2 * es) return fail(-31, "cap");
+  IndexRunner *run = ix->runner();
+  const void *v = run->get_vector(key);
+  if (!v) return fail(-1, "get_vector");
+  std::memcpy(out, v, es);
+  auto prov = run->create_provider();
+  if (!prov) return fail(-1, "create_provider");
+  const void *pv = prov->get_vector(key);
+  if (!pv) return fail(-1, "provider get_vector");
+  std::memcpy((char *)out + es, pv, es);
+  if (prov->count() != ix->n) return fail(-1, "provider count");
+  return (int)es;
+}
+
 // ---- streamers (rows arrive between searches): drives any registered IndexStreamer class the way
 // tests/core/algorithm/flat/flat_streamer_test.cc:180-212,1038-1060 does ------------------------------
 struct RefStreamer {
@@ -407,8 +488,54 @@ int zref_streamer_search(void *hh, const void *queries, uint32_t count, uint32_t
   const uint64_t fmod = g_fmod, frem = g_frem;
   if (fmod) ctx->set_filter([fmod, frem](uint64_t key) { return key % fmod == frem; });
   if (g_has_threshold) ctx->set_threshold(g_threshold);
+  if (g_gmod) {
+    const uint64_t gm = g_gmod;
+    ctx->set_group_params(g_gnum, g_gtopk);
+    ctx->set_group_by([gm](uint64_t key) { return std::to_string(key % gm); });
+  }
   int rc = count == 1 ? h->st->search_impl(queries, qm, ctx) : h->st->search_impl(queries, qm, count, ctx);
   if (rc != 0) return fail(rc, "streamer search");
+  if (g_gmod) {  // groups flattened in result order: out_counts[i] = documents over all groups of query i
+    for (uint32_t i = 0; i < count; ++i) {
+      uint32_t c = 0;
+      for (const auto &grp : ctx->group_result(i))
+        for (const auto &doc : grp.docs()) {
+          if (c >= topk) break;
+          out_keys[(size_t)i * topk + c] = doc.key();
+          out_scores[(size_t)i * topk + c] = doc.score();
+          ++c;
+        }
+      out_counts[i] = c;
+      for (uint32_t j = c; j < topk; ++j) { out_keys[(size_t)i * topk + j] = ~0ull; out_scores[(size_t)i * topk + j] = __builtin_nanf(""); }
+    }
+    return 0;
+  }
+  for (uint32_t i = 0; i < count; ++i) {
+    const auto &res = ctx->result(i);
+    const uint32_t c = (uint32_t)std::min<size_t>(res.size(), topk);
+    out_counts[i] = c;
+    for (uint32_t j = 0; j < topk; ++j) {
+      out_keys[(size_t)i * topk + j] = j < c ? res[j].key() : ~0ull;
+      out_scores[(size_t)i * topk + j] = j < c ? res[j].score() : __builtin_nanf("");
+    }
+  }
+  return 0;
+}
+
+// search_bf_by_p_keys_impl: the same key list for every query (core_interface::Index::_dense_search with bf_pks,
+// src/core/interface/index.cc:603-610)
+int zref_streamer_search_keys(void *hh, const void *queries, uint32_t count, const uint64_t *pks, uint32_t npks,
+                              uint32_t topk, uint64_t *out_keys, float *out_scores, uint32_t *out_counts) {
+  auto h = (RefStreamer *)hh;
+  IndexQueryMeta qm(h->meta.data_type(), h->meta.dimension());
+  auto ctx = h->st->create_context();
+  if (!ctx) return fail(-1, "context");
+  ctx->set_topk(topk);
+  const uint64_t fmod = g_fmod, frem = g_frem;
+  if (fmod) ctx->set_filter([fmod, frem](uint64_t key) { return key % fmod == frem; });
+  std::vector<std::vector<uint64_t>> keys(count, std::vector<uint64_t>(pks, pks + npks));
+  int rc = h->st->search_bf_by_p_keys_impl(queries, keys, qm, count, ctx);
+  if (rc != 0) return fail(rc, "streamer search_bf_by_p_keys");
   for (uint32_t i = 0; i < count; ++i) {
     const auto &res = ctx->result(i);
     const uint32_t c = (uint32_t)std::min<size_t>(res.size(), topk);
@@ -572,6 +699,158 @@ int zref_kmeans(const char *metric, const float *rows, uint64_t n, uint32_t dim,
     std::memcpy(labels, out.data(), (size_t)n * sizeof(uint32_t));
   }
   cl->cleanup();
+  return 0;
+}
+
+// ---- core_interface::Index (src/core/interface): the layer the DB calls (vector_column_indexer.cc:195).  The index
+// creates its streamer BY NAME (indexes/flat_index.cc:31, indexes/ivf_index.cc:38-39), so after a plugin's
+// zvb200_install_overrides() the very same calls reach the GPU classes. ----------------------------------------
+namespace ci = zvec::core_interface;
+
+// zvb200_index_search_batch of the loaded plugin (the plugin is dlopen'ed RTLD_LOCAL by IndexPlugin::load, so the
+// caller hands the address over)
+typedef int (*zref_batch_fn_t)(void *, const void *, uint32_t, const void *, void *);
+static zref_batch_fn_t g_batch_fn = nullptr;
+void zref_set_batch_fn(void *fn) { g_batch_fn = (zref_batch_fn_t)fn; }
+
+struct CiIndex {
+  ci::Index::Pointer index;
+  std::string path;
+  bool ivf{false}, keep_file{false};
+  uint32_t dim{0};
+  size_t in_es{0};
+};
+
+// kind "Flat" | "IVF"; metric "L2" | "IP" | "COSINE"; quantizer "" | "fp16" | "int8"; dtype of the caller's vectors
+// open_existing != 0: open the index file at `path` as it is (an IVF index another object trained), read-only
+void *zref_ci_create(const char *kind, int dtype, uint32_t dim, const char *metric, const char *quantizer, int nlist,
+                     const char *path, int open_existing) {
+  auto h = std::make_unique<CiIndex>();
+  h->ivf = std::string(kind) == "IVF";
+  std::shared_ptr<ci::BaseIndexParam> p;
+  if (h->ivf) {
+    auto ip = std::make_shared<ci::IVFIndexParam>();
+    ip->nlist = nlist;
+    p = ip;
+  } else {
+    p = std::make_shared<ci::FlatIndexParam>();
+  }
+  const std::string m(metric), qz(quantizer ? quantizer : "");
+  p->metric_type = m == "L2" ? ci::MetricType::kL2sq : m == "IP" ? ci::MetricType::kInnerProduct : ci::MetricType::kCosine;
+  p->dimension = (int)dim;
+  p->data_type = (IndexMeta::DataType)dtype;
+  p->quantizer_param.type = qz == "fp16" ? ci::QuantizerType::kFP16 : qz == "int8" ? ci::QuantizerType::kInt8
+                                                                                   : ci::QuantizerType::kNone;
+  h->index = ci::IndexFactory::CreateAndInitIndex(*p);
+  if (!h->index) { fail(-1, "CreateAndInitIndex"); return nullptr; }
+  h->path = path;
+  h->dim = dim;
+  h->in_es = IndexQueryMeta((IndexMeta::DataType)dtype, dim).element_size();
+  if (!open_existing) ::unlink(path);
+  ci::StorageOptions so;
+  so.type = ci::StorageOptions::StorageType::kMMAP;
+  so.create_new = !open_existing;
+  so.read_only = open_existing != 0;
+  h->keep_file = open_existing != 0;
+  if (h->index->Open(path, so) != 0) { fail(-1, "Index::Open"); return nullptr; }
+  return h.release();
+}
+
+int zref_ci_add(void *hh, const void *rows, uint64_t n, uint32_t first_id) {
+  auto h = (CiIndex *)hh;
+  for (uint64_t i = 0; i < n; ++i) {
+    ci::VectorData v;
+    v.vector = ci::DenseVector{(const char *)rows + i * h->in_es};
+    int r = h->index->Add(v, first_id + (uint32_t)i);
+    if (r != 0) return fail(r, "Index::Add");
+  }
+  return 0;
+}
+
+int zref_ci_train(void *hh) { return ((CiIndex *)hh)->index->Train(); }
+uint32_t zref_ci_count(void *hh) { return ((CiIndex *)hh)->index->GetDocCount(); }
+
+int zref_ci_fetch(void *hh, uint32_t doc_id, void *out, uint64_t cap) {
+  auto h = (CiIndex *)hh;
+  ci::VectorDataBuffer b;
+  int r = h->index->Fetch(doc_id, &b);
+  if (r != 0) return fail(r, "Index::Fetch");
+  auto &d = std::get<ci::DenseVectorBuffer>(b.vector_buffer).data;
+  if (d.size() > cap) return fail(-31, "cap");
+  std::memcpy(out, d.data(), d.size());
+  return (int)d.size();
+}
+
+void zref_ci_destroy(void *hh) {
+  auto h = (CiIndex *)hh;
+  if (h->index) h->index->Close();
+  h->index.reset();
+  if (!h->keep_file) ::unlink(h->path.c_str());
+  delete h;
+}
+
+// Index::Search per query (batch = 0: what the reference's callers do, index.cc:617 count = 1) or ONE
+// zvb200_index_search_batch call (batch = 1: integration/index_batch.cc, bound by symbol from the loaded plugin).
+// bf_pks / npks: FlatQueryParam::bf_pks; refiner: another zref_ci index (the reference Flat index) + scale_factor;
+// the filter of zref_set_filter applies; out_vectors (optional): count * topk * in_es bytes, the fetched vectors
+// reverted to the input layout (SearchResult::reverted_vector_list_, or the stored bytes when no reformer reverts).
+int zref_ci_search(void *hh, const void *queries, uint32_t count, uint32_t topk, int batch, const uint64_t *bf_pks,
+                   uint32_t npks, int is_linear, float radius, void *refiner, float scale_factor, int fetch_vector,
+                   uint64_t *out_keys, float *out_scores, uint32_t *out_counts, void *out_vectors) {
+  auto h = (CiIndex *)hh;
+  const uint64_t fmod = g_fmod, frem = g_frem;
+  auto make_param = [&]() -> ci::BaseIndexQueryParam::Pointer {
+    ci::BaseIndexQueryParam::Pointer p;
+    if (h->ivf) { auto ip = std::make_shared<ci::IVFQueryParam>(); ip->nprobe = 0; p = ip; }
+    else p = std::make_shared<ci::FlatQueryParam>();
+    p->topk = topk;
+    p->is_linear = is_linear != 0;
+    p->radius = radius;
+    p->fetch_vector = fetch_vector != 0;
+    if (fmod) p->filter = std::make_shared<ci::IndexFilter>();
+    if (fmod) p->filter->set([fmod, frem](uint64_t key) { return key % fmod == frem; });
+    if (bf_pks) p->bf_pks = std::make_shared<std::vector<uint64_t>>(bf_pks, bf_pks + npks);
+    if (refiner) {
+      p->refiner_param = std::make_shared<ci::RefinerParam>();
+      p->refiner_param->scale_factor_ = scale_factor;
+      p->refiner_param->reference_index = ((CiIndex *)refiner)->index;
+    }
+    return p;
+  };
+  std::vector<ci::SearchResult> results(count);
+  if (batch) {
+    auto fn = g_batch_fn;
+    if (!fn) return fail(-1, "zref_set_batch_fn(zvb200_index_search_batch of the loaded plugin) first");
+    auto p = make_param();
+    int r = fn(h->index.get(), queries, count, &p, &results);
+    if (r != 0) return fail(r, "SearchBatch");
+  } else {
+    for (uint32_t i = 0; i < count; ++i) {
+      auto p = make_param();  // Index::Search moves the filter out of its param (flat_index.cc:60-62)
+      ci::VectorData v;
+      v.vector = ci::DenseVector{(const char *)queries + i * h->in_es};
+      int r = h->index->Search(v, p, &results[i]);
+      if (r != 0) return fail(r, "Index::Search");
+    }
+  }
+  for (uint32_t i = 0; i < count; ++i) {
+    const auto &docs = results[i].doc_list_;
+    const uint32_t c = (uint32_t)std::min<size_t>(docs.size(), topk);
+    out_counts[i] = c;
+    for (uint32_t j = 0; j < topk; ++j) {
+      const size_t o = (size_t)i * topk + j;
+      out_keys[o] = j < c ? docs[j].key() : ~0ull;
+      out_scores[o] = j < c ? docs[j].score() : __builtin_nanf("");
+      if (out_vectors && j < c) {
+        char *dst = (char *)out_vectors + o * h->in_es;
+        if (j < results[i].reverted_vector_list_.size())
+          std::memcpy(dst, results[i].reverted_vector_list_[j].data(),
+                      std::min(h->in_es, results[i].reverted_vector_list_[j].size()));
+        else if (docs[j].vector())
+          std::memcpy(dst, docs[j].vector(), h->in_es);
+      }
+    }
+  }
   return 0;
 }
 

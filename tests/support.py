@@ -217,6 +217,91 @@ class RefIndex:
             pass
 
 
+class CiIndex:
+    """core_interface::Index (src/core/interface) driven like tests/core/interface/index_interface_test.cc:
+    IndexFactory::CreateAndInitIndex -> Open -> Add -> (Train) -> Search.  Which streamer class answers is decided
+    by NAME inside the reference (flat_index.cc:31, ivf_index.cc:38-39): the stock one, or — after a plugin's
+    zvb200_install_overrides() — the GPU one."""
+
+    def __init__(self, kind, dim, metric, quantizer="", nlist=32, path="/tmp/zref_ci.index", dtype=DT_FP32,
+                 open_existing=False):
+        L = ref()
+        L.zref_ci_create.restype = C.c_void_p
+        L.zref_ci_create.argtypes = [C.c_char_p, C.c_int, C.c_uint32, C.c_char_p, C.c_char_p, C.c_int, C.c_char_p, C.c_int]
+        L.zref_ci_add.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_uint32]
+        L.zref_ci_train.argtypes = [C.c_void_p]
+        L.zref_ci_count.argtypes = [C.c_void_p]
+        L.zref_ci_count.restype = C.c_uint32
+        L.zref_ci_fetch.argtypes = [C.c_void_p, C.c_uint32, C.c_void_p, C.c_uint64]
+        L.zref_ci_destroy.argtypes = [C.c_void_p]
+        L.zref_ci_search.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_int, C.c_void_p, C.c_uint32,
+                                     C.c_int, C.c_float, C.c_void_p, C.c_float, C.c_int, C.c_void_p, C.c_void_p,
+                                     C.c_void_p, C.c_void_p]
+        L.zref_set_batch_fn.argtypes = [C.c_void_p]
+        self.L, self.dim, self.dtype = L, dim, dtype
+        self.in_es = dim * {DT_FP32: 4, DT_FP16: 2, DT_INT8: 1}[dtype]
+        self.h = L.zref_ci_create(kind.encode(), dtype, dim, metric.encode(), quantizer.encode(), nlist, path.encode(),
+                                  int(open_existing))
+        if not self.h:
+            raise RuntimeError("core_interface index: %s" % L.zref_last_error().decode())
+
+    def add(self, rows, first_id=0):
+        rows = np.ascontiguousarray(rows)
+        n = rows.nbytes // self.in_es
+        r = self.L.zref_ci_add(self.h, P(rows), n, first_id)
+        if r != 0:
+            raise RuntimeError("Index::Add -> %d" % r)
+
+    def train(self):
+        return self.L.zref_ci_train(self.h)
+
+    def count(self):
+        return self.L.zref_ci_count(self.h)
+
+    def fetch(self, doc_id):
+        out = np.zeros(self.in_es, np.uint8)
+        r = self.L.zref_ci_fetch(self.h, doc_id, P(out), out.nbytes)
+        assert r == self.in_es, (r, self.L.zref_last_error())
+        return out
+
+    def search(self, queries, k, batch=False, bf_pks=None, linear=False, radius=0.0, refiner=None, scale=0.0,
+               fetch_vector=False):
+        """-> (keys u64 [q,k], scores f32 [q,k] (user-facing: normalised), counts u32[q][, vectors u8 [q,k,in_es]])"""
+        queries = np.ascontiguousarray(queries)
+        q = queries.nbytes // self.in_es
+        keys = np.zeros((q, k), np.uint64); scores = np.zeros((q, k), np.float32); counts = np.zeros(q, np.uint32)
+        vec = np.zeros((q, k, self.in_es), np.uint8) if fetch_vector else None
+        pk = None if bf_pks is None else np.ascontiguousarray(bf_pks, np.uint64)
+        r = self.L.zref_ci_search(self.h, P(queries), q, k, int(batch), P(pk), 0 if pk is None else pk.size,
+                                  int(linear), float(radius), refiner.h if refiner is not None else None, float(scale),
+                                  int(fetch_vector), P(keys), P(scores), P(counts), P(vec))
+        if r != 0:
+            import zvec_b200
+            raise RuntimeError("Index::Search -> %d (%s / %s)" % (r, self.L.zref_last_error().decode(),
+                                                                  zvec_b200.lib().zvb200_last_error().decode()))
+        return (keys, scores, counts, vec) if fetch_vector else (keys, scores, counts)
+
+    def close(self):
+        if self.h:
+            self.L.zref_ci_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+def plugin_handle():
+    """ctypes handle of the loaded plugin (zvb200_install_overrides, zvb200_index_search_batch)"""
+    assert load_plugin()
+    plug = C.CDLL(PLUGIN)
+    ref().zref_set_batch_fn.argtypes = [C.c_void_p]
+    ref().zref_set_batch_fn(C.cast(plug.zvb200_index_search_batch, C.c_void_p))
+    return plug
+
+
 # ---------------------------------------------------------------------------------------
 # oracle-side helpers
 # ---------------------------------------------------------------------------------------

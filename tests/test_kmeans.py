@@ -165,3 +165,72 @@ def test_gpu_kmeans_reproduces_the_golden_vectors():
         _same_centroids(gc, ref)
         assert np.array_equal(gl, np.array(c["labels"], np.uint32)) and gf.astype(int).tolist() == c["follows"]
         assert abs(gs - c["sse"]) <= 1e-5 * abs(c["sse"])
+
+
+# ---- edge cases of KmeansCluster the device path must share -------------------------------------
+@needs_ref
+@pytest.mark.parametrize("metric,name", [("ip", "InnerProduct"), ("l2", "Euclidean")])
+def test_oracle_kmeans_other_metrics_equal_the_reference(metric, name):
+    """InnerProduct and Euclidean assignment passes pinned to the compiled reference (only SquaredEuclidean was)"""
+    x, init = _data(5000, 20, 12, 9)
+    rc, rl, rf, rs = _ref_kmeans(name, x, init, 2)
+    c = init.copy()
+    for _ in range(2):
+        dm = KO.distances(x, c, "ip" if metric == "ip" else "l2sq")
+        if metric == "l2":
+            dm = np.sqrt(dm)
+        lab = np.where(np.isnan(dm), np.inf, dm).argmin(1)
+        sums = np.zeros((len(c), x.shape[1])); np.add.at(sums, lab, x.astype(np.float64))
+        cnt = np.bincount(lab, minlength=len(c))
+        with np.errstate(invalid="ignore", divide="ignore"):
+            c = (sums / cnt[:, None]).astype(np.float32)
+    ties = _near_tie_rows(dm)
+    if not ties.any():
+        assert np.allclose(rc, c, rtol=1e-5, atol=1e-6, equal_nan=True)
+        assert np.array_equal(rf, cnt.astype(np.uint64))
+
+
+@needs_ref
+def test_reference_kmeans_puts_an_all_nan_row_into_cluster_0():
+    """LinearSeeker::seek starts at (column 0, FLT_MAX) and only moves on a strictly smaller score
+    (linear_seeker.cc:25-41): a row whose distances are all NaN follows centroid 0 and adds FLT_MAX to the cost."""
+    x, init = _data(400, 8, 4, 21)
+    x[7] = np.nan
+    rc, rl, rf, rs = _ref_kmeans("SquaredEuclidean", x, init, 1)
+    assert rl[7] == 0 or np.isnan(rc[0]).any()       # cluster 0 took the NaN row: its mean is NaN
+    assert np.isnan(rc[0]).all() and rs >= np.finfo(np.float32).max * 0.99
+
+
+@pytest.mark.gpu
+@needs_ref
+@pytest.mark.parametrize("metric,name", [(1, "Euclidean"), (2, "InnerProduct")])
+def test_gpu_kmeans_other_metrics_equal_the_reference(metric, name):
+    import zvec_b200 as z
+    x, init = _data(20000, 32, 40, 10)
+    rc, rl, rf, rs = _ref_kmeans(name, x, init, 3, threads=8)
+    gc, gl, gf, gs, it = z.kmeans(x, init, metric=metric, max_iterations=3, epsilon=0.0)
+    assert it == 3
+    if np.array_equal(gf, rf):
+        assert np.allclose(gc, rc, rtol=1e-5, atol=1e-6, equal_nan=True)
+        assert abs(gs - rs) <= 1e-4 * abs(rs)
+    assert (gl == rl).mean() > 0.999
+
+
+@pytest.mark.gpu
+@needs_ref
+def test_gpu_kmeans_nan_row_and_zero_iterations_follow_the_reference():
+    import zvec_b200 as z
+    x, init = _data(400, 8, 4, 21)
+    x[7] = np.nan
+    rc, rl, rf, rs = _ref_kmeans("SquaredEuclidean", x, init, 1)
+    gc, gl, gf, gs, it = z.kmeans(x, init, max_iterations=1, epsilon=0.0)
+    assert np.array_equal(gf, rf)                     # the NaN row was counted: cluster 0 has the reference's follows
+    assert np.isnan(gc[0]).all() and np.allclose(gc[1:], rc[1:], rtol=1e-5, atol=1e-6, equal_nan=True)
+    assert gs >= np.finfo(np.float32).max * 0.99
+    assert gl.max() < 4                               # labels never carry 0xFFFFFFFF
+    # max_iterations = 0: the loop of KmeansCluster::cluster does not run — centroids as given, nothing follows
+    y, init2 = _data(300, 8, 5, 22)
+    gc, gl, gf, gs, it = z.kmeans(y, init2, max_iterations=0)
+    assert it == 0 and np.array_equal(gc, init2) and gs == 0.0 and not gf.any()
+    ol, _, _ = KO.assign(y, init2)
+    assert (gl == ol).mean() > 0.99

@@ -412,3 +412,109 @@ def test_gpu_streamer_adds_race_with_searches(tmp_path):
         assert r.add(i + 1, x[i]) == 0
     _same(g.search(qs, k), r.search_each(qs, k), "after the race")
     g.close(); r.close()
+
+
+# ---- round 2: the rest of the IndexSearcher / IndexStreamer surface (VERDICT r1 missing 2, 5) ------------------
+def _index_keys_search(ix, queries, k, pks=None):
+    import ctypes as C
+    L = S.ref()
+    L.zref_index_search_keys.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p, C.c_uint32, C.c_uint32,
+                                         C.c_void_p, C.c_void_p, C.c_void_p]
+    queries = np.ascontiguousarray(queries)
+    q = queries.nbytes // ix.in_elem
+    keys = np.zeros((q, k), np.uint64); scores = np.zeros((q, k), np.float32); counts = np.zeros(q, np.uint32)
+    pk = None if pks is None else np.ascontiguousarray(pks, np.uint64)
+    rc = L.zref_index_search_keys(ix.h, S.P(queries), q, S.P(pk), 0 if pk is None else pk.size, k, S.P(keys),
+                                  S.P(scores), S.P(counts))
+    if rc != 0:
+        raise RuntimeError("%d %s" % (rc, L.zref_last_error().decode()))
+    return keys, scores, counts
+
+
+@needs_plugin
+@pytest.mark.gpu
+@pytest.mark.parametrize("conv,metric", [("", "SquaredEuclidean"), ("HalfFloatConverter", "InnerProduct"),
+                                         ("Int8StreamingConverter", "SquaredEuclidean")])
+def test_gpu_searcher_p_keys_group_by_and_get_vector(conv, metric):
+    """search_bf_by_p_keys_impl (flat_searcher.cc:213-237), group-by (delegated to the embedded stock searcher,
+    flat_searcher.cc:178-179), get_vector(key) / create_provider() (flat_searcher.h:111,158-160, flat_searcher.cc:26-65)
+    answered by GpuFlatSearcher as FlatSearcher answers them."""
+    import ctypes as C
+    n, d, q, k = 12000, 48, 12, 10
+    x, qs = _tie_free(n, d, 15), _tie_free(q, d, 16)
+    ref = S.RefIndex(x, S.DT_FP32, d, metric, conv, kind="Flat")
+    gpu = S.RefIndex(x, S.DT_FP32, d, metric, conv, kind="Flat:GpuFlatSearcher")
+    pks = np.concatenate([np.arange(3, n, 7), np.array([n + 5, 2 ** 41], np.int64), np.arange(100, 9000, 7)]).astype(np.uint64)
+    a, b = _index_keys_search(ref, qs, k, pks), _index_keys_search(gpu, qs, k, pks)
+    _same(b, a, "p_keys %s/%s" % (conv, metric))
+    big = np.arange(0, n, 1, dtype=np.uint64)                      # more keys than one zvb200_search_rows call takes
+    _same(_index_keys_search(gpu, qs[:3], k, big), _index_keys_search(ref, qs[:3], k, big), "p_keys, 12000 keys")
+    S.ref().zref_set_filter(5, 2)
+    try:
+        _same(_index_keys_search(gpu, qs, k, pks), _index_keys_search(ref, qs, k, pks), "p_keys + filter")
+    finally:
+        S.ref().zref_set_filter(0, 0)
+    S.ref().zref_set_group_by.argtypes = [C.c_uint64, C.c_uint32, C.c_uint32]
+    S.ref().zref_set_group_by(7, 3, 4)
+    try:
+        ga, gb = _index_keys_search(ref, qs, 12), _index_keys_search(gpu, qs, 12)
+        assert gb[2].sum() > 0
+        _same(gb, ga, "group-by")
+    finally:
+        S.ref().zref_set_group_by(0, 0, 0)
+    S.ref().zref_index_get_vector.argtypes = [C.c_void_p, C.c_uint64, C.c_void_p, C.c_uint64]
+    for key in (0, 1, 777, n - 1):
+        va, vb = np.zeros(2 * ref.elem, np.uint8), np.zeros(2 * ref.elem, np.uint8)
+        assert S.ref().zref_index_get_vector(ref.h, key, S.P(va), va.nbytes) == ref.elem
+        assert S.ref().zref_index_get_vector(gpu.h, key, S.P(vb), vb.nbytes) == ref.elem
+        assert np.array_equal(va, vb)
+    ref.close(); gpu.close()
+
+
+@needs_plugin
+@pytest.mark.gpu
+def test_gpu_streamer_p_keys_and_group_by(tmp_path):
+    """FlatStreamer::search_bf_by_p_keys_impl (flat_streamer.cc:347-389) with keys that are row numbers (add_with_id)
+    and with keys that are not (add_impl), and the group-by branch (flat_streamer.cc:321-323,365-367)."""
+    import ctypes as C
+    L = S.ref()
+    L.zref_streamer_search_keys.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p, C.c_uint32, C.c_uint32,
+                                            C.c_void_p, C.c_void_p, C.c_void_p]
+    L.zref_set_group_by.argtypes = [C.c_uint64, C.c_uint32, C.c_uint32]
+    d, k = 16, 8
+    rng = np.random.default_rng(31)
+    x = rng.standard_normal((900, d)).astype(np.float32)
+    qs = rng.standard_normal((5, d)).astype(np.float32)
+
+    def by_keys(s, queries, pks):
+        q = len(queries)
+        keys = np.zeros((q, k), np.uint64); scores = np.zeros((q, k), np.float32); counts = np.zeros(q, np.uint32)
+        pk = np.ascontiguousarray(pks, np.uint64)
+        rc = L.zref_streamer_search_keys(s.h, S.P(np.ascontiguousarray(queries)), q, S.P(pk), pk.size, k, S.P(keys),
+                                         S.P(scores), S.P(counts))
+        assert rc == 0, L.zref_last_error()
+        return keys, scores, counts
+
+    for own_keys in (False, True):
+        g = _Streamer("GpuFlatStreamer", S.DT_FP32, d, "SquaredEuclidean", str(tmp_path / ("g%d.index" % own_keys)))
+        r = _Streamer("FlatStreamer", S.DT_FP32, d, "SquaredEuclidean", str(tmp_path / ("r%d.index" % own_keys)))
+        keyof = (lambda i: 1000003 * (i + 1) % 2 ** 40) if own_keys else (lambda i: i)
+        for i in range(0, 900, 1 if own_keys else 2):           # add_with_id leaves the odd rows as holes
+            if own_keys:
+                assert g.add(keyof(i), x[i]) == r.add(keyof(i), x[i]) == 0
+            else:
+                assert g.add_with_id(i, x[i]) == r.add_with_id(i, x[i]) == 0
+        pks = [keyof(i) for i in range(0, 900, 3)] + [2 ** 45, 901]
+        for one in (True, False):
+            qq = qs[:1] if one else qs
+            got = by_keys(g, qq, pks)
+            exp = by_keys(r, qq, pks) if one else tuple(np.concatenate(p) for p in zip(*[by_keys(r, qs[i:i + 1], pks) for i in range(len(qs))]))
+            _same(got, exp, "streamer p_keys own_keys=%s one=%s" % (own_keys, one))
+        L.zref_set_group_by(5, 2, 3)
+        try:
+            a, b = g.search(qs[:1], k), r.search(qs[:1], k)
+            assert a[2].sum() > 0
+            _same(a, b, "streamer group-by")
+        finally:
+            L.zref_set_group_by(0, 0, 0)
+        g.close(); r.close()

@@ -32,6 +32,7 @@ _SIGS = {
     "zvb200_device_count": (C.c_int, []),
     "zvb200_kernel_launches": (C.c_uint64, []),
     "zvb200_store_create": (C.c_int, [C.c_int, C.c_int, C.c_int, C.c_uint32, C.POINTER(C.c_void_p)]),
+    "zvb200_store_create_sharded": (C.c_int, [C.c_void_p, C.c_uint32, C.c_int, C.c_int, C.c_uint32, C.POINTER(C.c_void_p)]),
     "zvb200_store_destroy": (C.c_int, [C.c_void_p]),
     "zvb200_store_reserve": (C.c_int, [C.c_void_p, C.c_uint64]),
     "zvb200_store_append": (C.c_int, [C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p]),
@@ -53,6 +54,15 @@ _SIGS = {
     "zvb200_ctx_last_scan_ms": (C.c_int, [C.c_void_p, C.POINTER(C.c_float)]),
     "zvb200_ctx_set_kernel": (C.c_int, [C.c_void_p, C.c_int]),
     "zvb200_ctx_last_kernel": (C.c_char_p, [C.c_void_p]),
+    "zvb200_ctx_set_row_limit": (C.c_int, [C.c_void_p, C.c_uint64]),
+    "zvb200_comm_unique_id": (C.c_int, [C.c_void_p]),
+    "zvb200_comm_init": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.POINTER(C.c_void_p)]),
+    "zvb200_comm_destroy": (C.c_int, [C.c_void_p]),
+    "zvb200_comm_set_shard_bases": (C.c_int, [C.c_void_p, C.c_void_p]),
+    "zvb200_comm_transport": (C.c_int, [C.c_void_p]),
+    "zvb200_comm_status": (C.c_int, [C.c_void_p]),
+    "zvb200_search_sharded_device": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_float,
+                                               C.c_void_p, C.c_void_p, C.c_void_p]),
     "zvb200_ctx_last_mma_kind": (C.c_int, [C.c_void_p]),
     "zvb200_distance_matrix": (C.c_int, [C.c_int, C.c_int, C.c_int, C.c_uint32, C.c_void_p, C.c_uint64,
                                          C.c_void_p, C.c_uint32, C.c_void_p]),
@@ -135,9 +145,18 @@ def metric_from_names(metric, origin=None):
 class Store:
     """Device-resident vector store on one GPU (zvb200_store_*)."""
 
-    def __init__(self, dtype, metric, dim, device=0):
+    def __init__(self, dtype, metric, dim, device=0, devices=None):
+        """devices=[0, 1, ...]: rows sharded over several GPUs of this process (zvb200_store_create_sharded);
+        reserve(total rows) is then required before the first append."""
         h = C.c_void_p()
-        _check(lib().zvb200_store_create(device, dtype, metric, dim, C.byref(h)))
+        if devices is not None and len(devices) > 1:
+            devs = np.ascontiguousarray(devices, np.int32)
+            _check(lib().zvb200_store_create_sharded(_ptr(devs), devs.size, dtype, metric, dim, C.byref(h)))
+            device = int(devs[0])
+        else:
+            if devices is not None:
+                device = int(devices[0])
+            _check(lib().zvb200_store_create(device, dtype, metric, dim, C.byref(h)))
         self.h, self.dtype, self.metric, self.dim, self.device = h, dtype, metric, dim, device
         esz = {DT_FP32: 4, DT_FP16: 2, DT_INT8: 1}[dtype]
         self.elem_bytes = dim * esz
@@ -220,6 +239,16 @@ class Context:
 
     def last_kernel(self):
         return lib().zvb200_ctx_last_kernel(self.h).decode()
+
+    def set_row_limit(self, rows):
+        """searches see rows [0, rows) only (0 = all): a snapshot next to concurrent appends"""
+        _check(lib().zvb200_ctx_set_row_limit(self.h, rows))
+
+    def search_sharded_device(self, comm, q_ptr, q, k, out_scores_ptr, out_rows_ptr, threshold=FLT_MAX, filter_ptr=None):
+        """collective over the communicator's ranks: local scan -> exchange -> merge, on this context's stream"""
+        _check(lib().zvb200_search_sharded_device(self.h, comm.h, C.c_void_p(q_ptr), q, k, threshold,
+                                                  C.c_void_p(filter_ptr) if filter_ptr else None,
+                                                  C.c_void_p(out_scores_ptr), C.c_void_p(out_rows_ptr)))
 
     def last_mma_kind(self):
         return lib().zvb200_ctx_last_mma_kind(self.h)
@@ -360,6 +389,47 @@ class Context:
     def close(self):
         if self.h:
             lib().zvb200_ctx_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+COMM_ID_BYTES = 128
+
+
+def comm_unique_id():
+    """128 opaque bytes made on one rank (ncclGetUniqueId); the caller carries them to the other ranks"""
+    buf = np.zeros(COMM_ID_BYTES, np.uint8)
+    _check(lib().zvb200_comm_unique_id(_ptr(buf)))
+    return buf
+
+
+class Comm:
+    """One rank of a multi-process row-sharded search (zvb200_comm_*), bound to a context's stream."""
+
+    def __init__(self, ctx, rank, world, unique_id, shard_bases):
+        h = C.c_void_p()
+        uid = np.ascontiguousarray(unique_id, np.uint8)
+        assert uid.size == COMM_ID_BYTES
+        _check(lib().zvb200_comm_init(ctx.h, rank, world, _ptr(uid), C.byref(h)))
+        self.h, self.rank, self.world = h, rank, world
+        bases = np.ascontiguousarray(shard_bases, np.uint64)
+        assert bases.size == world
+        _check(lib().zvb200_comm_set_shard_bases(self.h, _ptr(bases)))
+
+    def transport(self):
+        return "peer mailboxes (CUDA IPC over NVLink)" if lib().zvb200_comm_transport(self.h) == 1 else "ncclAllGather"
+
+    def status(self):
+        _check(lib().zvb200_comm_status(self.h))
+
+    def close(self):
+        if self.h:
+            lib().zvb200_comm_destroy(self.h)
             self.h = None
 
     def __del__(self):

@@ -1,16 +1,7 @@
 // C ABI of libzvec_b200.so (include/zvec_b200.h): device-resident vector store, search
 // contexts and the search / merge / distance entry points.  No CPU fallback: every
 // compute path launches the CUDA kernels in this directory or fails.
-#include <float.h>
-
-#include <algorithm>
-#include <shared_mutex>
-#include <cmath>
-#include <atomic>
-#include <cstdio>
-#include <cstring>
-
-#include "internal.h"
+#include "host.h"
 
 using namespace zvb;
 
@@ -21,111 +12,15 @@ void count_launch(int n) { g_launches.fetch_add((uint64_t)n, std::memory_order_r
 
 static thread_local std::string g_err;
 
-static int set_err(int code, const char *what, const char *detail = "") {
+int zvb_set_err(int code, const char *what, const char *detail) {
   g_err = std::string(what) + (detail && *detail ? ": " : "") + (detail ? detail : "");
   return code;
 }
-static int cuda_fail(cudaError_t e, const char *what) {
+int zvb_cuda_fail(cudaError_t e, const char *what) {
   cudaGetLastError();  // clear sticky-less error state
   return set_err(e == cudaErrorMemoryAllocation ? ZVB200_ERR_NOMEMORY : ZVB200_ERR_RUNTIME, what,
                  cudaGetErrorString(e));
 }
-#define CU(x)                                        \
-  do {                                               \
-    cudaError_t _e = (x);                            \
-    if (_e != cudaSuccess) return cuda_fail(_e, #x); \
-  } while (0)
-
-struct zvb200_store {
-  int device = 0, dtype = 0, metric = 0, sm_count = 148;
-  uint32_t dim = 0, elem_bytes = 0, d = 0, vec_bytes = 0, row_stride = 0, chunks = 0, tail_off = 0;
-  bool has_tail = false, sealed = false;
-  uint8_t *rows = nullptr;
-  float4 *tails = nullptr;
-  float *norms = nullptr;
-  uint8_t *shadow = nullptr;      // QuantizedInteger L2: bf16 operands of the tensor-core filter (built at seal)
-  uint32_t shadow_k = 0;
-  uint64_t shadowed = 0;
-  float *shadow_mmax_dev = nullptr;  // running maximum of the rows' margin shares
-  float shadow_mrow_max = 0.f;
-  uint32_t *drop = nullptr;       // device bitmap (allocated lazily)
-  uint64_t drop_words = 0;
-  uint64_t n = 0, cap = 0, normed = 0;
-  std::vector<uint64_t> keys;     // empty = identity
-  std::vector<uint32_t> drop_host;
-  bool has_drop = false, drop_dirty = false;
-  cudaStream_t stream = nullptr;
-  uint8_t *staging = nullptr;     // device staging for host appends
-  size_t staging_bytes = 0;
-  // IVF
-  zvb200_store *centroids = nullptr;
-  std::vector<uint64_t> list_offsets;
-  uint32_t *list_off_dev = nullptr;  // [nlist+1] first row of each posting list
-  uint32_t *budget_dev = nullptr;    // [nlist] list sizes in the whole index (sharded IVF), or null
-  uint64_t *gbase_dev = nullptr;     // [nlist] row of the whole index where this store's slice of each list starts
-  uint32_t nlist = 0;
-  // writers (append / seal / write / set_deleted / attach) exclusive; the host-synchronous searches shared, from the
-  // first look at the store to the stream sync that ends them: an append that re-allocates the rows (store_grow)
-  // cannot free them under a search another thread has in flight (FlatStreamer adds race with searches,
-  // tests/core/algorithm/flat/flat_streamer_test.cc:509-730)
-  std::shared_mutex mu;
-
-  RowsView view() const {
-    RowsView v;
-    v.rows = rows; v.n = n; v.row_stride = row_stride; v.chunks = chunks; v.d = d;
-    v.dtype = dtype; v.metric = metric; v.tails = tails; v.norms = norms;
-    v.drop = has_drop ? drop : nullptr;
-    if (shadow && shadowed >= n) { v.shadow = shadow; v.shadow_k = shadow_k; v.shadow_mrow_max = shadow_mrow_max; }
-    return v;
-  }
-};
-
-struct DevBuf {
-  void *p = nullptr;
-  size_t cap = 0;
-  cudaError_t ensure(size_t bytes) {
-    if (bytes <= cap) return cudaSuccess;
-    if (p) cudaFree(p);
-    p = nullptr; cap = 0;
-    size_t want = std::max(bytes, (size_t)4096);
-    cudaError_t e = cudaMalloc(&p, want);
-    if (e == cudaSuccess) cap = want;
-    return e;
-  }
-  void release() { if (p) cudaFree(p); p = nullptr; cap = 0; }
-};
-struct HostBuf {
-  void *p = nullptr;
-  size_t cap = 0;
-  cudaError_t ensure(size_t bytes) {
-    if (bytes <= cap) return cudaSuccess;
-    if (p) cudaFreeHost(p);
-    p = nullptr; cap = 0;
-    size_t want = std::max(bytes, (size_t)4096);
-    cudaError_t e = cudaMallocHost(&p, want);
-    if (e == cudaSuccess) cap = want;
-    return e;
-  }
-  void release() { if (p) cudaFreeHost(p); p = nullptr; cap = 0; }
-};
-
-struct zvb200_ctx {
-  zvb200_store *s = nullptr;
-  int device = 0;  // copy: a context may outlive its store (destruction order is the caller's)
-  cudaStream_t stream = nullptr;
-  DevBuf qshadow;
-  DevBuf qin, qf32, qraw, qtails, qnorms, part, out_scores, out_index, filter, misc, gtau;
-  DevBuf coarse_scores, coarse_index, seg_prefix, seg_row, seg_count;  // IVF
-  DevBuf qsrc, cand;  // fp32 queries before the reformer; candidate rows of the refiner
-  QueryView last_qv;
-  HostBuf h_q, h_scores, h_index;
-  int force_kernel = 0;
-  uint32_t mma_group_cap = 0;  // queries per tcgen05 launch (0: ZVB200_MMA_GROUP or 1024)
-  int last_mma_kind = -1;
-  const char *last_kernel = "none";
-  cudaEvent_t ev_scan0 = nullptr, ev_scan1 = nullptr;  // bracket the scan kernel(s) of the last search
-  bool scan_timed = false;
-};
 
 static int layout_for(int dtype, int metric, uint32_t dim, zvb200_store *s) {
   s->has_tail = false;
@@ -165,19 +60,31 @@ static int store_grow(zvb200_store *s, uint64_t want) {
   uint64_t ncap = std::max<uint64_t>(want, s->cap + s->cap / 2);
   ncap = std::max<uint64_t>(ncap, 1024);
   uint8_t *nr = nullptr;
-  CU(cudaMalloc((void **)&nr, ncap * s->row_stride));
-  if (s->n) CU(cudaMemcpyAsync(nr, s->rows, s->n * s->row_stride, cudaMemcpyDeviceToDevice, s->stream));
   float4 *nt = nullptr;
-  if (s->has_tail) {
-    CU(cudaMalloc((void **)&nt, ncap * sizeof(float4)));
-    if (s->n) CU(cudaMemcpyAsync(nt, s->tails, s->n * sizeof(float4), cudaMemcpyDeviceToDevice, s->stream));
+  cudaError_t e = cudaMalloc((void **)&nr, ncap * s->row_stride);
+  if (e == cudaSuccess && s->n) e = cudaMemcpyAsync(nr, s->rows, s->n * s->row_stride, cudaMemcpyDeviceToDevice, s->stream);
+  if (e == cudaSuccess && s->has_tail) {
+    e = cudaMalloc((void **)&nt, ncap * sizeof(float4));
+    if (e == cudaSuccess && s->n) e = cudaMemcpyAsync(nt, s->tails, s->n * sizeof(float4), cudaMemcpyDeviceToDevice, s->stream);
   }
-  CU(cudaStreamSynchronize(s->stream));
+  if (e == cudaSuccess) e = cudaStreamSynchronize(s->stream);
+  if (e != cudaSuccess) {  // the old arrays stay in charge
+    if (nr) cudaFree(nr);
+    if (nt) cudaFree(nt);
+    return cuda_fail(e, "store_grow");
+  }
   if (s->rows) cudaFree(s->rows);
   if (s->tails) cudaFree(s->tails);
   if (s->norms) { cudaFree(s->norms); s->norms = nullptr; s->normed = 0; }
   if (s->shadow) { cudaFree(s->shadow); s->shadow = nullptr; s->shadowed = 0; }
   s->rows = nr; s->tails = nt; s->cap = ncap;
+  return 0;
+}
+
+// A store addresses its rows with 32-bit indices (result rows, list offsets, the packed (score, row) keys):
+// at most 2^32 - 2 rows, checked wherever rows are added or reserved.
+int zvb_check_row_limit(uint64_t rows) {
+  if (rows >= 0xffffffffull) return set_err(ZVB200_ERR_INVALID_ARGUMENT, "a store holds at most 2^32 - 2 rows");
   return 0;
 }
 
@@ -213,6 +120,7 @@ int zvb200_store_create(int device, int dtype, int metric, uint32_t dim, zvb200_
 
 int zvb200_store_destroy(zvb200_store *s) {
   if (!s) return 0;
+  if (!s->shards.empty() || s->shard_base_dev) zvb_sharded_destroy(s);
   cudaSetDevice(s->device);
   if (s->centroids) zvb200_store_destroy(s->centroids);
   if (s->rows) cudaFree(s->rows);
@@ -233,6 +141,8 @@ int zvb200_store_destroy(zvb200_store *s) {
 int zvb200_store_reserve(zvb200_store *s, uint64_t rows) {
   if (!s) return set_err(ZVB200_ERR_INVALID_ARGUMENT, "null store");
   std::lock_guard<std::shared_mutex> g(s->mu);
+  if (int r = zvb_check_row_limit(rows)) return r;
+  if (!s->shards.empty()) return zvb_sharded_reserve(s, rows);
   CU(cudaSetDevice(s->device));
   if (rows <= s->cap) return 0;
   uint64_t keep = s->cap;
@@ -242,16 +152,18 @@ int zvb200_store_reserve(zvb200_store *s, uint64_t rows) {
   return r;
 }
 
-static int append_common(zvb200_store *s, const uint8_t *src_dev, uint64_t n) {
-  CU(launch_repack_rows(src_dev, s->elem_bytes, n, s->rows + s->n * s->row_stride, s->row_stride,
-                        s->vec_bytes, s->has_tail ? s->tails + s->n : nullptr, s->tail_off, s->stream));
+// rows [at, at + n) of the device arrays <- n elements in the reference layout (device memory)
+static int append_common(zvb200_store *s, const uint8_t *src_dev, uint64_t at, uint64_t n) {
+  CU(launch_repack_rows(src_dev, s->elem_bytes, n, s->rows + at * s->row_stride, s->row_stride,
+                        s->vec_bytes, s->has_tail ? s->tails + at : nullptr, s->tail_off, s->stream));
   return 0;
 }
 
 int zvb200_store_append(zvb200_store *s, const void *rows, uint64_t n, const uint64_t *keys) {
   if (!s || (!rows && n)) return set_err(ZVB200_ERR_INVALID_ARGUMENT, "null argument");
   std::lock_guard<std::shared_mutex> g(s->mu);
-  if (s->n + n >= 0xffffffffull) return set_err(ZVB200_ERR_INVALID_ARGUMENT, "store holds < 2^32-1 rows");
+  if (int r = zvb_check_row_limit(s->n + n)) return r;
+  if (!s->shards.empty()) return zvb_sharded_append(s, rows, n, keys, false);
   CU(cudaSetDevice(s->device));
   int r = store_grow(s, s->n + n);
   if (r != 0) return r;
@@ -260,17 +172,17 @@ int zvb200_store_append(zvb200_store *s, const void *rows, uint64_t n, const uin
     s->staging_bytes = chunk_rows * s->elem_bytes;
     CU(cudaMalloc((void **)&s->staging, s->staging_bytes));
   }
+  // the row count, the keys and the hole bits are committed together, after every chunk has arrived: a CUDA
+  // failure half way leaves the store as it was (rows beyond n are never read)
   const uint64_t n0 = s->n;
   for (uint64_t off = 0; off < n; off += chunk_rows) {
     const uint64_t m = std::min<uint64_t>(chunk_rows, n - off);
     CU(cudaMemcpyAsync(s->staging, (const uint8_t *)rows + off * s->elem_bytes, m * s->elem_bytes,
                        cudaMemcpyHostToDevice, s->stream));
-    r = append_common(s, s->staging, m);
+    r = append_common(s, s->staging, n0 + off, m);
     if (r != 0) return r;
     CU(cudaStreamSynchronize(s->stream));
-    s->n += m;
   }
-  // keys / holes
   if (keys || !s->keys.empty()) {
     if (s->keys.empty()) { s->keys.resize(n0); for (uint64_t i = 0; i < n0; ++i) s->keys[i] = i; }
     s->keys.resize(n0 + n);
@@ -278,12 +190,13 @@ int zvb200_store_append(zvb200_store *s, const void *rows, uint64_t n, const uin
       const uint64_t kv = keys ? keys[i] : n0 + i;
       s->keys[n0 + i] = kv;
       if (kv == ZVB200_INVALID_KEY) {
-        s->drop_host.resize((s->n + 31) / 32, 0u);
+        s->drop_host.resize((n0 + n + 31) / 32, 0u);
         s->drop_host[(n0 + i) >> 5] |= 1u << ((n0 + i) & 31);
         s->has_drop = true; s->drop_dirty = true;
       }
     }
   }
+  s->n = n0 + n;
   s->sealed = false;
   return 0;
 }
@@ -291,11 +204,12 @@ int zvb200_store_append(zvb200_store *s, const void *rows, uint64_t n, const uin
 int zvb200_store_append_device(zvb200_store *s, const void *rows_dev, uint64_t n) {
   if (!s || (!rows_dev && n)) return set_err(ZVB200_ERR_INVALID_ARGUMENT, "null argument");
   std::lock_guard<std::shared_mutex> g(s->mu);
-  if (s->n + n >= 0xffffffffull) return set_err(ZVB200_ERR_INVALID_ARGUMENT, "store holds < 2^32-1 rows");
+  if (int r = zvb_check_row_limit(s->n + n)) return r;
+  if (!s->shards.empty()) return zvb_sharded_append(s, rows_dev, n, nullptr, true);
   CU(cudaSetDevice(s->device));
   int r = store_grow(s, s->n + n);
   if (r != 0) return r;
-  r = append_common(s, (const uint8_t *)rows_dev, n);
+  r = append_common(s, (const uint8_t *)rows_dev, s->n, n);
   if (r != 0) return r;
   CU(cudaStreamSynchronize(s->stream));
   if (!s->keys.empty()) { uint64_t n0 = s->n; s->keys.resize(n0 + n); for (uint64_t i = 0; i < n; ++i) s->keys[n0 + i] = n0 + i; }
@@ -304,25 +218,35 @@ int zvb200_store_append_device(zvb200_store *s, const void *rows_dev, uint64_t n
   return 0;
 }
 
+// Device copy of the drop bitmap.  It must cover every row a scan can touch: rows appended after the last upload
+// grow the bitmap too (their bits are clear), not only new holes / deletions.
 static int sync_drop(zvb200_store *s) {
-  if (!s->has_drop || !s->drop_dirty) return 0;
+  if (!s->has_drop) return 0;
   const uint64_t words = (s->n + 31) / 32;
+  if (!s->drop_dirty && words <= s->drop_synced) return 0;
   s->drop_host.resize(words, 0u);
   if (words > s->drop_words) {
+    // sized for the store's capacity, so that appends within it only re-upload
+    const uint64_t want = std::max<uint64_t>(std::max<uint64_t>(words, (s->cap + 31) / 32), 64);
+    uint32_t *nd = nullptr;
+    CU(cudaMalloc((void **)&nd, want * 4));
     if (s->drop) cudaFree(s->drop);
-    s->drop = nullptr;
-    CU(cudaMalloc((void **)&s->drop, std::max<uint64_t>(words, 64) * 4));
-    s->drop_words = std::max<uint64_t>(words, 64);
+    s->drop = nd;
+    s->drop_words = want;
   }
-  CU(cudaMemcpyAsync(s->drop, s->drop_host.data(), words * 4, cudaMemcpyHostToDevice, s->stream));
+  if (words) CU(cudaMemcpyAsync(s->drop, s->drop_host.data(), words * 4, cudaMemcpyHostToDevice, s->stream));
+  if (s->drop_words > words)
+    CU(cudaMemsetAsync(s->drop + words, 0, (s->drop_words - words) * 4, s->stream));
   CU(cudaStreamSynchronize(s->stream));
   s->drop_dirty = false;
+  s->drop_synced = words;
   return 0;
 }
 
 int zvb200_store_seal(zvb200_store *s) {
   if (!s) return set_err(ZVB200_ERR_INVALID_ARGUMENT, "null store");
   std::lock_guard<std::shared_mutex> g(s->mu);
+  if (!s->shards.empty()) return zvb_sharded_seal(s);
   CU(cudaSetDevice(s->device));
   int r = sync_drop(s);
   if (r != 0) return r;
@@ -375,8 +299,10 @@ uint64_t zvb200_store_scan_bytes(const zvb200_store *s) {
 }
 
 int zvb200_store_set_deleted(zvb200_store *s, uint64_t row, int deleted) {
-  if (!s || row >= s->n) return set_err(ZVB200_ERR_INVALID_ARGUMENT, "bad row");
+  if (!s) return set_err(ZVB200_ERR_INVALID_ARGUMENT, "null store");
   std::lock_guard<std::shared_mutex> g(s->mu);
+  if (!s->shards.empty()) return zvb_sharded_set_deleted(s, row, deleted);
+  if (row >= s->n) return set_err(ZVB200_ERR_INVALID_ARGUMENT, "bad row");
   s->drop_host.resize((s->n + 31) / 32, 0u);
   if (deleted) s->drop_host[row >> 5] |= 1u << (row & 31);
   else s->drop_host[row >> 5] &= ~(1u << (row & 31));
@@ -386,8 +312,10 @@ int zvb200_store_set_deleted(zvb200_store *s, uint64_t row, int deleted) {
 }
 
 int zvb200_store_write(zvb200_store *s, uint64_t row, const void *vec, uint64_t key) {
-  if (!s || !vec || row >= s->n) return set_err(ZVB200_ERR_INVALID_ARGUMENT, "bad argument");
+  if (!s || !vec) return set_err(ZVB200_ERR_INVALID_ARGUMENT, "bad argument");
   std::lock_guard<std::shared_mutex> g(s->mu);
+  if (!s->shards.empty()) return zvb_sharded_write(s, row, vec, key);
+  if (row >= s->n) return set_err(ZVB200_ERR_INVALID_ARGUMENT, "bad row");
   CU(cudaSetDevice(s->device));
   if (!s->staging) {
     s->staging_bytes = std::max<size_t>(1, ((size_t)64 << 20) / s->elem_bytes) * s->elem_bytes;
@@ -423,6 +351,7 @@ int zvb200_store_write(zvb200_store *s, uint64_t row, const void *vec, uint64_t 
 int zvb200_store_get_vector(const zvb200_store *s, uint64_t row, void *out, size_t cap) {
   if (!s || !out || row >= s->n) return set_err(ZVB200_ERR_INVALID_ARGUMENT, "bad argument");
   if (cap < s->elem_bytes) return set_err(ZVB200_ERR_INVALID_ARGUMENT, "buffer too small");
+  if (!s->shards.empty()) return zvb_sharded_get_vector(s, row, out, cap);
   CU(cudaSetDevice(s->device));
   memset(out, 0, s->elem_bytes);
   CU(cudaMemcpy(out, s->rows + row * s->row_stride, s->vec_bytes, cudaMemcpyDeviceToHost));
@@ -441,14 +370,20 @@ int zvb200_ctx_create(zvb200_store *s, zvb200_ctx **out) {
   if (e == cudaSuccess) e = cudaEventCreate(&c->ev_scan0);
   if (e == cudaSuccess) e = cudaEventCreate(&c->ev_scan1);
   if (e != cudaSuccess) { delete c; return cuda_fail(e, "ctx_create"); }
+  if (!s->shards.empty()) {
+    const int r = zvb_sharded_ctx_create(s, c);
+    if (r != 0) { zvb200_ctx_destroy(c); return r; }
+  }
   *out = c;
   return 0;
 }
 
 int zvb200_ctx_destroy(zvb200_ctx *c) {
   if (!c) return 0;
+  zvb_sharded_ctx_destroy(c);
   cudaSetDevice(c->device);
   cudaStreamSynchronize(c->stream);
+  c->xkeys.release(); c->gather.release(); c->out_rows.release(); c->h_rows.release();
   DevBuf *d[] = {&c->qin, &c->qf32, &c->qraw, &c->qtails, &c->qnorms, &c->part, &c->out_scores,
                  &c->out_index, &c->filter, &c->misc, &c->gtau, &c->coarse_scores, &c->coarse_index,
                  &c->seg_prefix, &c->seg_row, &c->seg_count, &c->qsrc, &c->cand, &c->qshadow};
@@ -463,12 +398,26 @@ int zvb200_ctx_destroy(zvb200_ctx *c) {
 
 int zvb200_ctx_sync(zvb200_ctx *c) {
   if (!c) return set_err(ZVB200_ERR_INVALID_ARGUMENT, "null ctx");
+  CU(cudaSetDevice(c->device));
   CU(cudaStreamSynchronize(c->stream));
   return 0;
 }
 int zvb200_ctx_last_scan_ms(zvb200_ctx *c, float *ms) {
   if (!c || !ms) return set_err(ZVB200_ERR_INVALID_ARGUMENT, "null argument");
   if (!c->scan_timed) return set_err(ZVB200_ERR_NOREADY, "no search yet");
+  if (!c->sub.empty()) {  // sharded: the shards scan side by side; the longest one is the step's scan time
+    float mx = 0.f;
+    for (auto *sc : c->sub) {
+      if (!sc->scan_timed) continue;
+      float t = 0.f;
+      const int r = zvb200_ctx_last_scan_ms(sc, &t);
+      if (r != 0) return r;
+      mx = std::max(mx, t);
+    }
+    *ms = mx;
+    return 0;
+  }
+  CU(cudaSetDevice(c->device));
   CU(cudaEventSynchronize(c->ev_scan1));
   CU(cudaEventElapsedTime(ms, c->ev_scan0, c->ev_scan1));
   return 0;
@@ -480,6 +429,11 @@ int zvb200_ctx_set_kernel(zvb200_ctx *c, int which) {
   return 0;
 }
 const char *zvb200_ctx_last_kernel(const zvb200_ctx *c) { return c ? c->last_kernel : "none"; }
+int zvb200_ctx_set_row_limit(zvb200_ctx *c, uint64_t rows) {
+  if (!c) return set_err(ZVB200_ERR_INVALID_ARGUMENT, "null ctx");
+  c->row_limit = rows;
+  return 0;
+}
 int zvb200_ctx_last_mma_kind(const zvb200_ctx *c) { return c ? c->last_mma_kind : -1; }
 
 }  // extern "C"
@@ -527,9 +481,9 @@ static int prep_core(zvb200_ctx *c, zvb200_store *s, const void *queries_dev, ui
 }
 
 // Prepare queries and run scan + final merge for queries already on the device.
-static int search_core(zvb200_ctx *c, zvb200_store *s, const void *queries_dev, uint32_t q, uint32_t k,
-                       float threshold, const uint32_t *filter_dev, float *out_scores_dev,
-                       uint32_t *out_index_dev, uint64_t row_begin, uint64_t row_end) {
+int zvb_search_core(zvb200_ctx *c, zvb200_store *s, const void *queries_dev, uint32_t q, uint32_t k,
+                    float threshold, const uint32_t *filter_dev, float *out_scores_dev,
+                    uint32_t *out_index_dev, u64 *out_keys_dev, uint64_t row_begin, uint64_t row_end) {
   RowsView rv = s->view();
   const uint32_t esz = s->dtype == ZVB200_DT_FP32 ? 4 : s->dtype == ZVB200_DT_FP16 ? 2 : 1;
   QueryView qv;
@@ -602,10 +556,19 @@ static int search_core(zvb200_ctx *c, zvb200_store *s, const void *queries_dev, 
       c->last_kernel = "scan_mma";
     }
     if (q0 + group >= q) CU(cudaEventRecord(c->ev_scan1, c->stream));
-    CU(launch_merge_parts((const u64 *)c->part.p, nparts, qn, k, out_scores_dev + (size_t)q0 * k,
-                          out_index_dev + (size_t)q0 * k, c->stream));
+    CU(launch_merge_parts((const u64 *)c->part.p, nparts, qn, k, out_scores_dev ? out_scores_dev + (size_t)q0 * k : nullptr,
+                          out_index_dev ? out_index_dev + (size_t)q0 * k : nullptr,
+                          out_keys_dev ? out_keys_dev + (size_t)q0 * k : nullptr, c->stream));
   }
   return 0;
+}
+
+// the searches of this file: plain (score, row) outputs; the context's row limit (zvb200_ctx_set_row_limit) applies
+static int search_core(zvb200_ctx *c, zvb200_store *s, const void *queries_dev, uint32_t q, uint32_t k, float threshold,
+                       const uint32_t *filter_dev, float *out_scores_dev, uint32_t *out_index_dev, uint64_t row_begin,
+                       uint64_t row_end) {
+  return zvb_search_core(c, s, queries_dev, q, k, threshold, filter_dev, out_scores_dev, out_index_dev, nullptr,
+                         row_begin, row_end);
 }
 
 // device results of the context -> host outputs, document keys and per-query counts
@@ -637,9 +600,9 @@ static int finish_results(zvb200_ctx *c, zvb200_store *s, uint32_t q, uint32_t k
 
 // The refiner's second stage on the device: exact scores of each query's candidate rows, best k
 // (FlatStreamer::search_bf_by_p_keys_impl, flat_streamer.cc:347-389, with rows for keys).
-static int rows_core(zvb200_ctx *c, zvb200_store *s, const void *queries_dev, uint32_t q, const uint32_t *rows_dev,
-                     uint32_t m, uint32_t k, float threshold, const uint32_t *filter_dev, float *out_scores_dev,
-                     uint32_t *out_index_dev) {
+int zvb_rows_core(zvb200_ctx *c, zvb200_store *s, const void *queries_dev, uint32_t q, const uint32_t *rows_dev,
+                  uint32_t m, uint32_t k, float threshold, const uint32_t *filter_dev, float *out_scores_dev,
+                  uint32_t *out_index_dev, u64 *out_keys_dev) {
   QueryView qv;
   int r = prep_core(c, s, queries_dev, q, &qv);
   if (r != 0) return r;
@@ -660,8 +623,14 @@ static int rows_core(zvb200_ctx *c, zvb200_store *s, const void *queries_dev, ui
                        (const uint32_t *)c->seg_count.p, m, (u64 *)c->part.p, &nparts, s->sm_count, c->stream));
   CU(cudaEventRecord(c->ev_scan1, c->stream));
   c->last_kernel = "scan_rows";
-  CU(launch_merge_parts((const u64 *)c->part.p, nparts, q, k, out_scores_dev, out_index_dev, c->stream));
+  CU(launch_merge_parts((const u64 *)c->part.p, nparts, q, k, out_scores_dev, out_index_dev, out_keys_dev, c->stream));
   return 0;
+}
+
+static int rows_core(zvb200_ctx *c, zvb200_store *s, const void *queries_dev, uint32_t q, const uint32_t *rows_dev,
+                     uint32_t m, uint32_t k, float threshold, const uint32_t *filter_dev, float *out_scores_dev,
+                     uint32_t *out_index_dev) {
+  return zvb_rows_core(c, s, queries_dev, q, rows_dev, m, k, threshold, filter_dev, out_scores_dev, out_index_dev, nullptr);
 }
 
 // fp32 queries on the device -> the store's query layout in c->qin (the reformer the store's type implies)
@@ -676,7 +645,7 @@ static int reform_core(zvb200_ctx *c, zvb200_store *s, const float *in_dev, uint
   return 0;
 }
 
-static int check_search_args(zvb200_ctx *c, const void *queries, uint32_t q, uint32_t k) {
+int zvb_check_search_args(zvb200_ctx *c, const void *queries, uint32_t q, uint32_t k) {
   cudaGetLastError();  // a stale non-sticky error of an unrelated call must not fail this search
   if (!c || (!queries && q)) return set_err(ZVB200_ERR_INVALID_ARGUMENT, "null argument");
   if (k == 0 || k > ZVB200_MAX_TOPK) return set_err(ZVB200_ERR_INVALID_ARGUMENT, "topk must be 1..1024");
@@ -689,11 +658,14 @@ extern "C" {
 int zvb200_search_device(zvb200_ctx *c, const void *queries_dev, uint32_t q, uint32_t k,
                          float threshold, const uint32_t *filter_dev, float *out_scores_dev,
                          uint32_t *out_index_dev) {
-  int r = check_search_args(c, queries_dev, q, k);
+  int r = zvb_check_search_args(c, queries_dev, q, k);
   if (r != 0) return r;
   if (q == 0) return 0;
+  if (!c->s->shards.empty())
+    return zvb_sharded_search(c, queries_dev, false, q, k, threshold, filter_dev, nullptr, 0, out_scores_dev, out_index_dev);
   CU(cudaSetDevice(c->s->device));
-  return search_core(c, c->s, queries_dev, q, k, threshold, filter_dev, out_scores_dev, out_index_dev, 0, c->s->n);
+  const uint64_t rows = c->row_limit ? std::min<uint64_t>(c->row_limit, c->s->n) : c->s->n;
+  return search_core(c, c->s, queries_dev, q, k, threshold, filter_dev, out_scores_dev, out_index_dev, 0, rows);
 }
 
 int zvb200_search(zvb200_ctx *c, const void *queries, uint32_t q, uint32_t k, float threshold,
@@ -701,30 +673,39 @@ int zvb200_search(zvb200_ctx *c, const void *queries, uint32_t q, uint32_t k, fl
                   uint32_t *out_index, uint32_t *out_counts) {
   if (!c) return set_err(ZVB200_ERR_INVALID_ARGUMENT, "null argument");
   std::shared_lock<std::shared_mutex> rl(c->s->mu);
-  int r = check_search_args(c, queries, q, k);
+  int r = zvb_check_search_args(c, queries, q, k);
   if (r != 0) return r;
   if (!out_scores) return set_err(ZVB200_ERR_INVALID_ARGUMENT, "null out_scores");
   if (q == 0) return 0;
   zvb200_store *s = c->s;
   CU(cudaSetDevice(s->device));
   const size_t qbytes = (size_t)q * s->elem_bytes, nres = (size_t)q * k;
-  CU(c->h_q.ensure(qbytes));
-  CU(c->qin.ensure(qbytes));
   CU(c->out_scores.ensure(nres * 4));
   CU(c->out_index.ensure(nres * 4));
   CU(c->h_scores.ensure(nres * 4));
   CU(c->h_index.ensure(nres * 4));
+  if (!s->shards.empty()) {
+    r = zvb_sharded_search(c, queries, true, q, k, threshold, filter, nullptr, 0, (float *)c->out_scores.p,
+                           (uint32_t *)c->out_index.p);
+    if (r != 0) return r;
+    return finish_results(c, s, q, k, out_keys, out_scores, out_index, out_counts);
+  }
+  // rows this search sees: all of them, or the snapshot the caller took (zvb200_ctx_set_row_limit); a filter
+  // bitmap covers exactly those rows
+  const uint64_t rows = c->row_limit ? std::min<uint64_t>(c->row_limit, s->n) : s->n;
+  CU(c->h_q.ensure(qbytes));
+  CU(c->qin.ensure(qbytes));
   memcpy(c->h_q.p, queries, qbytes);
   CU(cudaMemcpyAsync(c->qin.p, c->h_q.p, qbytes, cudaMemcpyHostToDevice, c->stream));
   const uint32_t *fdev = nullptr;
   if (filter) {
-    const size_t fb = ((s->n + 31) / 32) * 4;
+    const size_t fb = ((rows + 31) / 32) * 4;
     CU(c->filter.ensure(fb));
     CU(cudaMemcpyAsync(c->filter.p, filter, fb, cudaMemcpyHostToDevice, c->stream));
     fdev = (const uint32_t *)c->filter.p;
   }
   r = search_core(c, s, c->qin.p, q, k, threshold, fdev, (float *)c->out_scores.p,
-                  (uint32_t *)c->out_index.p, 0, s->n);
+                  (uint32_t *)c->out_index.p, 0, rows);
   if (r != 0) return r;
   return finish_results(c, s, q, k, out_keys, out_scores, out_index, out_counts);
 }
@@ -834,22 +815,32 @@ int zvb200_distance_matrix(int device, int metric, int dtype, uint32_t dim, cons
 
 int zvb200_ivf_attach(zvb200_store *s, const void *centroids, uint32_t nlist, const uint64_t *list_offsets) {
   if (!s || !centroids || !list_offsets || nlist == 0) return set_err(ZVB200_ERR_INVALID_ARGUMENT, "null argument");
+  if (!s->shards.empty()) return set_err(ZVB200_ERR_UNSUPPORTED, "IVF over a sharded store: shard the lists per process (zvb200_ivf_set_budget_sizes)");
   if (!s->sealed) return set_err(ZVB200_ERR_NOREADY, "store not sealed");
   if (list_offsets[0] != 0 || list_offsets[nlist] != s->n) return set_err(ZVB200_ERR_MISMATCH, "list offsets do not cover the rows");
   for (uint32_t l = 0; l < nlist; ++l)
     if (list_offsets[l] > list_offsets[l + 1]) return set_err(ZVB200_ERR_INVALID_ARGUMENT, "list offsets not ascending");
+  // list offsets travel as u32 on the device: the store's own row limit (check_row_limit) keeps them exact
+  if (int r = zvb_check_row_limit(list_offsets[nlist])) return r;
   zvb200_store *cs = nullptr;
   int r = zvb200_store_create(s->device, s->dtype, s->metric, s->dim, &cs);
   if (r == 0) r = zvb200_store_append(cs, centroids, nlist, nullptr);
   if (r == 0) r = zvb200_store_seal(cs);
-  if (r != 0) { if (cs) zvb200_store_destroy(cs); return r; }
-  std::lock_guard<std::shared_mutex> g(s->mu);
-  CU(cudaSetDevice(s->device));
-  std::vector<uint32_t> off32(nlist + 1);
-  for (uint32_t l = 0; l <= nlist; ++l) off32[l] = (uint32_t)list_offsets[l];
   uint32_t *d = nullptr;
-  CU(cudaMalloc((void **)&d, (size_t)(nlist + 1) * 4));
-  CU(cudaMemcpy(d, off32.data(), (size_t)(nlist + 1) * 4, cudaMemcpyHostToDevice));
+  if (r == 0) {
+    std::vector<uint32_t> off32(nlist + 1);
+    for (uint32_t l = 0; l <= nlist; ++l) off32[l] = (uint32_t)list_offsets[l];
+    cudaError_t e = cudaSetDevice(s->device);
+    if (e == cudaSuccess) e = cudaMalloc((void **)&d, (size_t)(nlist + 1) * 4);
+    if (e == cudaSuccess) e = cudaMemcpy(d, off32.data(), (size_t)(nlist + 1) * 4, cudaMemcpyHostToDevice);
+    if (e != cudaSuccess) r = cuda_fail(e, "ivf_attach");
+  }
+  if (r != 0) {  // nothing attached, nothing leaked
+    if (d) cudaFree(d);
+    if (cs) zvb200_store_destroy(cs);
+    return r;
+  }
+  std::lock_guard<std::shared_mutex> g(s->mu);
   if (s->centroids) zvb200_store_destroy(s->centroids);
   if (s->list_off_dev) cudaFree(s->list_off_dev);
   if (s->budget_dev) { cudaFree(s->budget_dev); s->budget_dev = nullptr; }
@@ -872,6 +863,39 @@ int zvb200_ivf_set_budget_sizes(zvb200_store *s, const uint64_t *list_sizes) {
   return 0;
 }
 
+// top-nprobe centroids for nprobe > ZVB200_MAX_TOPK: distance matrix (the 1x1 kernels' arithmetic) + one CTA-wide
+// bitonic sort of (score, centroid) keys per query; leaves coarse_scores / coarse_index and the prepared queries
+// (c->last_qv) exactly as search_core would
+static int coarse_wide(zvb200_ctx *c, zvb200_store *cs, const void *queries_dev, uint32_t q, uint32_t nprobe) {
+  QueryView qv;
+  int r = prep_core(c, cs, queries_dev, q, &qv);
+  if (r != 0) return r;
+  RowsView rv = cs->view();
+  const uint64_t n = cs->n;
+  uint64_t p2 = 1;
+  while (p2 < n) p2 <<= 1;
+  // queries in groups so that the distance matrix + sort scratch stay below 512 MiB
+  const size_t per_query = (size_t)n * 4 + (size_t)p2 * 8;
+  const uint32_t group = (uint32_t)std::max<size_t>(1, std::min<size_t>(q, ((size_t)512 << 20) / per_query));
+  CU(c->misc.ensure((size_t)group * per_query));
+  float *dist = (float *)((uint8_t *)c->misc.p + (size_t)group * p2 * 8);
+  for (uint32_t q0 = 0; q0 < q; q0 += group) {
+    const uint32_t qn = std::min(group, q - q0);
+    QueryView g = qv;
+    g.q = qn;
+    const uint32_t esz = cs->dtype == ZVB200_DT_FP32 ? 4 : cs->dtype == ZVB200_DT_FP16 ? 2 : 1;
+    if (g.qf32) g.qf32 += (size_t)q0 * (cs->chunks * 16 / esz);
+    if (g.qraw) g.qraw += (size_t)q0 * cs->row_stride;
+    g.qtails += q0; g.qnorms += q0;
+    CU(launch_distance_matrix(rv, g, dist, c->stream));
+    CU(launch_sort_rows(dist, qn, (uint32_t)n, (uint32_t)p2, nprobe, (u64 *)c->misc.p,
+                        (float *)c->coarse_scores.p + (size_t)q0 * nprobe,
+                        (uint32_t *)c->coarse_index.p + (size_t)q0 * nprobe, c->stream));
+  }
+  c->last_kernel = "coarse_wide";
+  return 0;
+}
+
 // coarse search -> list plan -> posting-list scan -> merge, everything on the context's stream; queries, filter and
 // outputs on the device
 static int ivf_core(zvb200_ctx *c, const void *queries_dev, uint32_t q, uint32_t k, uint32_t nprobe,
@@ -886,8 +910,15 @@ static int ivf_core(zvb200_ctx *c, const void *queries_dev, uint32_t q, uint32_t
   // 1. coarse: top-nprobe centroids per query (IVFCentroidIndex::search, ivf_centroid_index.cc:273-295)
   const int keep = c->force_kernel;
   if (keep == 3 || keep == 5) c->force_kernel = 0;
-  int r = search_core(c, s->centroids, queries_dev, q, nprobe, FLT_MAX, nullptr, (float *)c->coarse_scores.p,
-                      (uint32_t *)c->coarse_index.p, 0, s->centroids->n);
+  int r;
+  if (nprobe <= ZVB200_MAX_TOPK) {
+    r = search_core(c, s->centroids, queries_dev, q, nprobe, FLT_MAX, nullptr, (float *)c->coarse_scores.p,
+                    (uint32_t *)c->coarse_index.p, 0, s->centroids->n);
+  } else {
+    // wide probing (the reference has no cap: nprobe = round(nlist * scan_ratio), ivf_searcher_context.h:61-79;
+    // nlist 16384 at the default ratio 0.1 = 1638 lists): every centroid's distance, then a full sort per query
+    r = coarse_wide(c, s->centroids, queries_dev, q, nprobe);
+  }
   c->force_kernel = keep;
   if (r != 0) return r;
   // 2. which lists each query scans under the budget (ivf_searcher.cc:216-231)
@@ -912,16 +943,16 @@ static int ivf_core(zvb200_ctx *c, const void *queries_dev, uint32_t q, uint32_t
                          (const uint32_t *)c->seg_count.p, nprobe, (u64 *)c->part.p, &nparts, s->sm_count, c->stream));
   CU(cudaEventRecord(c->ev_scan1, c->stream));
   c->last_kernel = lists_stream ? "scan_lists_stream" : "scan_lists";
-  CU(launch_merge_parts((const u64 *)c->part.p, nparts, q, k, out_scores_dev, out_index_dev, c->stream));
+  CU(launch_merge_parts((const u64 *)c->part.p, nparts, q, k, out_scores_dev, out_index_dev, nullptr, c->stream));
   return 0;
 }
 
 static int ivf_check(zvb200_ctx *c, const void *queries, uint32_t q, uint32_t k, uint32_t *nprobe) {
-  int r = check_search_args(c, queries, q, k);
+  int r = zvb_check_search_args(c, queries, q, k);
   if (r != 0) return r;
   if (!c->s->centroids) return set_err(ZVB200_ERR_NOREADY, "no IVF structure attached");
-  if (*nprobe == 0 || *nprobe > ZVB200_MAX_TOPK) return set_err(ZVB200_ERR_INVALID_ARGUMENT, "nprobe must be 1..1024");
-  *nprobe = std::min(*nprobe, c->s->nlist);
+  if (*nprobe == 0) return set_err(ZVB200_ERR_INVALID_ARGUMENT, "nprobe must be >= 1");
+  *nprobe = std::min(*nprobe, c->s->nlist);  // no upper cap, like IVFSearcherContext::update (ivf_searcher_context.h:61-79)
   return 0;
 }
 
@@ -1025,6 +1056,7 @@ int zvb200_reform_queries(zvb200_ctx *c, const float *queries_fp32, uint32_t q, 
   if (!c || (!queries_fp32 && q) || (!out && q)) return set_err(ZVB200_ERR_INVALID_ARGUMENT, "null argument");
   if (q == 0) return 0;
   zvb200_store *s = c->s;
+  if (!s->shards.empty()) return set_err(ZVB200_ERR_UNSUPPORTED, "not available on a sharded store");
   CU(cudaSetDevice(s->device));
   int r = upload_fp32_queries(c, queries_fp32, q, dim);
   if (r == 0) r = reform_core(c, s, (const float *)c->qsrc.p, q, dim);
@@ -1043,6 +1075,7 @@ int zvb200_reform_queries_device(zvb200_ctx *c, const float *queries_fp32_dev, u
   if (!c || (!queries_fp32_dev && q) || (!out_dev && q)) return set_err(ZVB200_ERR_INVALID_ARGUMENT, "null argument");
   if (q == 0) return 0;
   zvb200_store *s = c->s;
+  if (!s->shards.empty()) return set_err(ZVB200_ERR_UNSUPPORTED, "not available on a sharded store");
   CU(cudaSetDevice(s->device));
   const int kind = reform_kind(s->dtype, s->metric);
   if (kind < 0) return set_err(ZVB200_ERR_UNSUPPORTED, "no fp32 query reformer for this store type");
@@ -1059,11 +1092,12 @@ int zvb200_search_fp32(zvb200_ctx *c, const float *queries_fp32, uint32_t q, uin
                        uint32_t *out_counts) {
   if (!c) return set_err(ZVB200_ERR_INVALID_ARGUMENT, "null argument");
   std::shared_lock<std::shared_mutex> rl(c->s->mu);
-  int r = check_search_args(c, queries_fp32, q, k);
+  int r = zvb_check_search_args(c, queries_fp32, q, k);
   if (r != 0) return r;
   if (!out_scores) return set_err(ZVB200_ERR_INVALID_ARGUMENT, "null out_scores");
   if (q == 0) return 0;
   zvb200_store *s = c->s;
+  if (!s->shards.empty()) return set_err(ZVB200_ERR_UNSUPPORTED, "not available on a sharded store");
   CU(cudaSetDevice(s->device));
   const size_t nres = (size_t)q * k;
   CU(c->out_scores.ensure(nres * 4));
@@ -1083,12 +1117,22 @@ int zvb200_search_rows(zvb200_ctx *c, const void *queries, uint32_t q, const uin
                        uint32_t *out_index, uint32_t *out_counts) {
   if (!c) return set_err(ZVB200_ERR_INVALID_ARGUMENT, "null argument");
   std::shared_lock<std::shared_mutex> rl(c->s->mu);
-  int r = check_search_args(c, queries, q, k);
+  int r = zvb_check_search_args(c, queries, q, k);
   if (r != 0) return r;
   if (!out_scores || (!rows && q && m)) return set_err(ZVB200_ERR_INVALID_ARGUMENT, "null argument");
   if (m == 0 || m > ZVB200_MAX_CANDIDATES) return set_err(ZVB200_ERR_INVALID_ARGUMENT, "candidates per query must be 1..8192");
   if (q == 0) return 0;
   zvb200_store *s = c->s;
+  if (!s->shards.empty()) {
+    const size_t nr = (size_t)q * k;
+    CU(cudaSetDevice(s->device));
+    CU(c->out_scores.ensure(nr * 4));
+    CU(c->out_index.ensure(nr * 4));
+    r = zvb_sharded_search(c, queries, true, q, k, threshold, filter, rows, m, (float *)c->out_scores.p,
+                           (uint32_t *)c->out_index.p);
+    if (r != 0) return r;
+    return finish_results(c, s, q, k, out_keys, out_scores, out_index, out_counts);
+  }
   CU(cudaSetDevice(s->device));
   const size_t qbytes = (size_t)q * s->elem_bytes, nres = (size_t)q * k, rbytes = (size_t)q * m * 4;
   CU(c->h_q.ensure(std::max(qbytes, rbytes)));
@@ -1116,11 +1160,12 @@ int zvb200_search_refined(zvb200_ctx *coarse, zvb200_ctx *exact, const float *qu
   std::shared_lock<std::shared_mutex> rl1(coarse->s->mu);
   std::shared_lock<std::shared_mutex> rl2;
   if (exact->s != coarse->s) rl2 = std::shared_lock<std::shared_mutex>(exact->s->mu);
-  int r = check_search_args(coarse, queries_fp32, q, k);
-  if (r == 0) r = check_search_args(exact, queries_fp32, q, k);
+  int r = zvb_check_search_args(coarse, queries_fp32, q, k);
+  if (r == 0) r = zvb_check_search_args(exact, queries_fp32, q, k);
   if (r != 0) return r;
   if (!out_scores) return set_err(ZVB200_ERR_INVALID_ARGUMENT, "null out_scores");
   zvb200_store *sc = coarse->s, *se = exact->s;
+  if (!sc->shards.empty() || !se->shards.empty()) return set_err(ZVB200_ERR_UNSUPPORTED, "not available on a sharded store");
   if (sc->device != se->device) return set_err(ZVB200_ERR_MISMATCH, "refiner: both stores must be on one device");
   if (sc->n != se->n) return set_err(ZVB200_ERR_MISMATCH, "refiner: the stores must hold the same rows");
   // Index::_get_coarse_search_topk (src/core/interface/index.cc:794-801)
@@ -1171,7 +1216,7 @@ static void store_reset(zvb200_store *s) {
   std::lock_guard<std::shared_mutex> g(s->mu);
   s->n = 0; s->normed = 0; s->shadowed = 0;
   s->keys.clear(); s->drop_host.clear();
-  s->has_drop = false; s->drop_dirty = false; s->sealed = false;
+  s->has_drop = false; s->drop_dirty = false; s->drop_synced = 0; s->sealed = false;
 }
 
 struct KmeansScratch {
@@ -1228,8 +1273,11 @@ static int kmeans_core(int device, int metric, const float *rows_dev, const floa
       const uint32_t qn = (uint32_t)std::min<uint64_t>(chunk, n - off);
       e = search_core(c, w.cs, rows_dev + off * dim, qn, 1, FLT_MAX, nullptr, w.dist + off, w.lab + off, 0, k);
     }
+    if (e == 0) CU(launch_kmeans_fix_labels(w.lab, w.dist, n, c->stream));
     return e;
   };
+  // max_iterations == 0: nothing follows any centroid and the cost is 0 (KmeansCluster::cluster's loop does not run)
+  CU(cudaMemsetAsync(w.counts, 0, (size_t)k * sizeof(unsigned long long), c->stream));
   double cost = 0.0, new_cost = 0.0;
   uint32_t it = 0;
   for (; it < max_iterations; ++it) {

@@ -221,7 +221,7 @@ constexpr int kMergeWarps = 8;
 template <bool SLICED>
 __global__ void __launch_bounds__(kMergeWarps * 32) merge_parts_kernel(
     u64 *part, uint32_t nparts, uint32_t ninputs, uint32_t stride, uint32_t per_cta, uint32_t k, float *out_scores,
-    uint32_t *out_index) {
+    uint32_t *out_index, u64 *out_keys) {
   extern __shared__ __align__(16) uint8_t smem[];
   const int lane = lane_id(), warp = threadIdx.x >> 5;
   const uint32_t qi = blockIdx.x;
@@ -264,8 +264,9 @@ __global__ void __launch_bounds__(kMergeWarps * 32) merge_parts_kernel(
     if (SLICED) {
       if (total) src[i] = e;
     } else {
-      out_scores[(size_t)qi * k + i] = ok ? unorder_f32((uint32_t)(e >> 32)) : CUDART_NAN_F;
-      out_index[(size_t)qi * k + i] = ok ? (uint32_t)e : ZVB200_INVALID_INDEX;
+      if (out_scores) out_scores[(size_t)qi * k + i] = ok ? unorder_f32((uint32_t)(e >> 32)) : CUDART_NAN_F;
+      if (out_index) out_index[(size_t)qi * k + i] = ok ? (uint32_t)e : ZVB200_INVALID_INDEX;
+      if (out_keys) out_keys[(size_t)qi * k + i] = e;  // packed (score, row): what the multi-GPU exchange ships
     }
   }
 }
@@ -495,7 +496,7 @@ cudaError_t launch_qi8_shadow_queries(const RowsView &rv, const uint8_t *qraw, c
 }
 
 cudaError_t launch_merge_parts(const u64 *part, uint32_t nparts, uint32_t q, uint32_t k,
-                               float *out_scores, uint32_t *out_index, cudaStream_t st) {
+                               float *out_scores, uint32_t *out_index, u64 *out_keys, cudaStream_t st) {
   if (q == 0) return cudaSuccess;
   const size_t smem = sizeof(int2) * kMergeWarps + (size_t)kMergeWarps * (2 * (size_t)k + 32) * sizeof(u64);
   {  // a constant, every time: the attribute is per function AND per device, and shared by all host threads
@@ -508,13 +509,13 @@ cudaError_t launch_merge_parts(const u64 *part, uint32_t nparts, uint32_t q, uin
   // few queries, many keys each: slices of the lists first (grid.y), then one list per slice
   if ((size_t)nparts * k >= 4096 && q <= 64 && nparts >= 32) {
     const uint32_t per_cta = 16, slices = (nparts + per_cta - 1) / per_cta;
-    merge_parts_kernel<true><<<dim3(q, slices), kMergeWarps * 32, smem, st>>>(p, nparts, nparts, 1, per_cta, k, nullptr, nullptr);
+    merge_parts_kernel<true><<<dim3(q, slices), kMergeWarps * 32, smem, st>>>(p, nparts, nparts, 1, per_cta, k, nullptr, nullptr, nullptr);
     count_launch();
-    merge_parts_kernel<false><<<q, kMergeWarps * 32, smem, st>>>(p, nparts, slices, per_cta, 0, k, out_scores, out_index);
+    merge_parts_kernel<false><<<q, kMergeWarps * 32, smem, st>>>(p, nparts, slices, per_cta, 0, k, out_scores, out_index, out_keys);
     count_launch();
     return cudaGetLastError();
   }
-  merge_parts_kernel<false><<<q, kMergeWarps * 32, smem, st>>>(p, nparts, nparts, 1, 0, k, out_scores, out_index);
+  merge_parts_kernel<false><<<q, kMergeWarps * 32, smem, st>>>(p, nparts, nparts, 1, 0, k, out_scores, out_index, out_keys);
   count_launch();
   return cudaGetLastError();
 }
@@ -552,6 +553,52 @@ cudaError_t launch_distance_matrix(const RowsView &rv, const QueryView &qv, floa
   if (rv.n == 0 || qv.q == 0) return cudaSuccess;
   const uint64_t blocks = (rv.n + 7) / 8;
   distance_matrix_kernel<<<(unsigned)blocks, 256, 0, st>>>(rv, qv, out);
+  count_launch();
+  return cudaGetLastError();
+}
+
+// ---- full sort of a distance row: the coarse search of wide IVF probing (nprobe > 1024) -----------------------
+// One CTA per query: (score, row) keys of all n distances, padded to a power of two, bitonic-sorted in the CTA's
+// slice of global scratch (L2-resident: 16384 centroids = 128 KB), the first `take` written out.  NaN distances
+// sort last and are never returned (the scans' rule, index_document.h:250-261).
+namespace {
+__global__ void __launch_bounds__(1024) sort_rows_kernel(const float *dist, uint32_t n, uint32_t p2, uint32_t take,
+                                                         u64 *scratch, float *out_scores, uint32_t *out_index) {
+  const uint32_t qi = blockIdx.x;
+  u64 *keys = scratch + (size_t)qi * p2;
+  const float *d = dist + (size_t)qi * n;
+  for (uint32_t i = threadIdx.x; i < p2; i += blockDim.x) {
+    u64 kv = kMaxKey;
+    if (i < n) { const float s = d[i]; if (s == s) kv = pack_key(s, i); }
+    keys[i] = kv;
+  }
+  __syncthreads();
+  for (uint32_t size = 2; size <= p2; size <<= 1) {
+    for (uint32_t stride = size >> 1; stride > 0; stride >>= 1) {
+      for (uint32_t t = threadIdx.x; t < (p2 >> 1); t += blockDim.x) {
+        const uint32_t lo = 2 * t - (t & (stride - 1));  // index with bit `stride` clear
+        const uint32_t hi = lo + stride;
+        const bool up = (lo & size) == 0;
+        const u64 a = keys[lo], b = keys[hi];
+        if ((a > b) == up) { keys[lo] = b; keys[hi] = a; }
+      }
+      __syncthreads();
+    }
+  }
+  for (uint32_t i = threadIdx.x; i < take; i += blockDim.x) {
+    const u64 e = i < p2 ? keys[i] : kMaxKey;
+    const bool ok = e != kMaxKey;
+    out_scores[(size_t)qi * take + i] = ok ? unorder_f32((uint32_t)(e >> 32)) : CUDART_NAN_F;
+    out_index[(size_t)qi * take + i] = ok ? (uint32_t)e : ZVB200_INVALID_INDEX;
+  }
+}
+}  // namespace
+
+cudaError_t launch_sort_rows(const float *dist, uint32_t q, uint32_t n, uint32_t p2, uint32_t take, u64 *scratch,
+                             float *out_scores, uint32_t *out_index, cudaStream_t st) {
+  if (q == 0) return cudaSuccess;
+  const unsigned threads = (unsigned)std::min<uint32_t>(1024u, std::max<uint32_t>(32u, p2 >> 1));
+  sort_rows_kernel<<<q, threads, 0, st>>>(dist, n, p2, take, scratch, out_scores, out_index);
   count_launch();
   return cudaGetLastError();
 }

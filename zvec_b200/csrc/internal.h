@@ -86,7 +86,8 @@ cudaError_t launch_prep_queries(const RowsView &rv, const void *queries_dev, uin
                                 float *qnorms, cudaStream_t st);
 // part[q][nparts][k] -> final sorted (score,index) q*k, padded NaN / INVALID
 cudaError_t launch_merge_parts(const u64 *part, uint32_t nparts, uint32_t q, uint32_t k,
-                               float *out_scores, uint32_t *out_index, cudaStream_t st);
+                               float *out_scores, uint32_t *out_index, u64 *out_keys /* packed, may be null */,
+                               cudaStream_t st);
 // G sorted shard lists [g][q][k] -> q*k by (score, shard_base[g]+index)
 cudaError_t launch_merge_shards(const float *scores, const uint32_t *index, uint32_t g,
                                 const uint64_t *shard_base_dev, uint32_t q, uint32_t k,
@@ -111,6 +112,10 @@ cudaError_t launch_qi8_shadow_queries(const RowsView &rv, const uint8_t *qraw, c
                                       uint8_t *out, uint32_t shadow_k, cudaStream_t st);
 cudaError_t launch_distance_matrix(const RowsView &rv, const QueryView &qv, float *out,
                                    cudaStream_t st);
+
+// dist[q][n] -> the `take` best (score, row) per query, ascending; scratch = q * p2 keys, p2 = pow2 >= n
+cudaError_t launch_sort_rows(const float *dist, uint32_t q, uint32_t n, uint32_t p2, uint32_t take, u64 *scratch,
+                             float *out_scores, uint32_t *out_index, cudaStream_t st);
 
 // K4: IVF — list selection under the scan budget, then the posting-list scan (grid.y = query)
 cudaError_t launch_ivf_plan(const uint32_t *coarse_index, uint32_t q, uint32_t nprobe, const uint32_t *list_off,
@@ -161,6 +166,7 @@ cudaError_t launch_rows_plan(const uint32_t *rows, uint32_t q, uint32_t m, uint6
 cudaError_t launch_kmeans_accumulate(const float *rows, uint64_t n, uint32_t dim, const uint32_t *labels,
                                      const float *dist, double *sums, unsigned long long *counts, double *scores,
                                      cudaStream_t st);
+cudaError_t launch_kmeans_fix_labels(uint32_t *labels, float *dist, uint64_t n, cudaStream_t st);
 cudaError_t launch_kmeans_finalize(const double *sums, const unsigned long long *counts, const double *scores,
                                    uint32_t k, uint32_t dim, float *centroids, unsigned long long *follows,
                                    double *sse, cudaStream_t st);

@@ -16,8 +16,7 @@ __global__ void kmeans_accumulate_kernel(const float *rows, uint64_t n, uint32_t
   const uint64_t r = ((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   if (r >= n) return;
   const int lane = threadIdx.x & 31;
-  const uint32_t l = labels[r];
-  if (l == ZVB200_INVALID_INDEX) return;  // every centroid is NaN for this row: it follows no cluster
+  const uint32_t l = labels[r];  // never INVALID: kmeans_fix_labels ran
   const float *x = rows + r * dim;
   double *s = sums + (size_t)l * dim;
   for (uint32_t i = lane; i < dim; i += 32) atomicAdd(s + i, (double)x[i]);
@@ -25,6 +24,14 @@ __global__ void kmeans_accumulate_kernel(const float *rows, uint64_t n, uint32_t
     atomicAdd(counts + l, 1ull);
     atomicAdd(scores + l, (double)dist[r]);
   }
+}
+
+// A row none of whose distances compares below FLT_MAX (a NaN row, or every centroid NaN) keeps LinearSeeker::seek's
+// initial answer: column 0 with score FLT_MAX (linear_seeker.cc:25-41) -- it joins cluster 0, its count and its cost.
+__global__ void kmeans_fix_labels_kernel(uint32_t *labels, float *dist, uint64_t n) {
+  const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  if (labels[i] == ZVB200_INVALID_INDEX) { labels[i] = 0; dist[i] = 3.402823466e+38f; }
 }
 
 __global__ void kmeans_finalize_kernel(const double *sums, const unsigned long long *counts, const double *scores,
@@ -51,6 +58,13 @@ cudaError_t launch_kmeans_accumulate(const float *rows, uint64_t n, uint32_t dim
   if (n == 0) return cudaSuccess;
   const uint64_t blocks = (n + 7) / 8;
   kmeans_accumulate_kernel<<<(unsigned)blocks, 256, 0, st>>>(rows, n, dim, labels, dist, sums, counts, scores);
+  count_launch();
+  return cudaGetLastError();
+}
+
+cudaError_t launch_kmeans_fix_labels(uint32_t *labels, float *dist, uint64_t n, cudaStream_t st) {
+  if (n == 0) return cudaSuccess;
+  kmeans_fix_labels_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(labels, dist, n);
   count_launch();
   return cudaGetLastError();
 }
