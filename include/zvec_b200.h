@@ -100,6 +100,17 @@ int zvb200_store_seal(zvb200_store *s);
 uint64_t zvb200_store_count(const zvb200_store *s);
 /* Mark a row deleted / undeleted (FlatStreamerEntity DeletionMap, flat_index_format.h:106-126). */
 int zvb200_store_set_deleted(zvb200_store *s, uint64_t row, int deleted);
+/* Which operand the reference's caller hands its 1x1 distance function first.  FlatSearcher passes (feature, query)
+ * (src/core/algorithm/flat/flat_distance_matrix.h:53-55): query_first = 0, the default.  FlatStreamer and the IVF list
+ * scan pass (query, feature) (flat_streamer_entity.h:155-162, ivf_distance_calculator.h:174-183): query_first = 1.
+ * Only the QuantizedInteger -IP / cosine float epilogue (quantized_integer_metric_matrix.h:94-112) can tell the
+ * difference — it sums its two middle terms in operand order, which moves the last place of ~15 % of the scores;
+ * every other distance, L2 included, is symmetric bit for bit. */
+int zvb200_store_set_operand_order(zvb200_store *s, int query_first);
+/* The same choice for the searches of ONE context: -1 = the store's (default), 0 / 1 as above.  FlatSearcher's
+ * search_bf_by_p_keys_impl hands (query, feature) although its scans hand (feature, query)
+ * (flat_searcher_context.h:1091-1093 vs flat_distance_matrix.h:53-55). */
+int zvb200_ctx_set_operand_order(zvb200_ctx *c, int order);
 /* Overwrite row `row` (< count) with a new vector and key: the in-place branch of
  * FlatStreamerEntity::add_vector_with_id (flat_streamer_entity.cc:969-985).  A key of
  * ZVB200_INVALID_KEY turns the row into a hole, any other key makes it live again. */
@@ -314,7 +325,8 @@ int zvb200_search_refined(zvb200_ctx *coarse, zvb200_ctx *exact, const float *qu
  * (vector_mean.h:204-226; an empty cluster becomes NaN and is never chosen again, as there).  Stops after
  * max_iterations or when |cost - previous cost| < epsilon (kmeans_cluster.cc:519-529).  Optional outputs:
  * labels[n] = nearest of the RETURNED centroids (label()), follows[k] = rows per cluster and *sse = cost of the
- * last assignment pass, *iterations = passes run.  Nothing is purged. */
+ * last assignment pass, *iterations = passes run.  Nothing is cut, but as PurgeCentroids does at the end of cluster()
+ * (kmeans_cluster.cc:363-383, 533) the clusters nobody follows are swapped to the tail of centroids / follows. */
 int zvb200_kmeans(int device, int metric, const float *rows, uint64_t n, uint32_t dim, float *centroids,
                   uint32_t k, uint32_t max_iterations, double epsilon, uint32_t *labels, uint64_t *follows,
                   double *sse, uint32_t *iterations);

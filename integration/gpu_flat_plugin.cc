@@ -423,7 +423,10 @@ class GpuFlatSearcher : public IndexSearcher {
       }
     }
     std::vector<std::vector<std::pair<float, std::pair<uint32_t, uint64_t>>>> lists;
+    // FlatSearcherContext::search_bf_by_p_keys_impl hands the metric (query, feature) (flat_searcher_context.h:1091-1093)
+    zvb200_ctx_set_operand_order(ctx->handle(), 1);
     const int rc = search_rows_sliced(ctx, query, count, rows, k, &lists);
+    zvb200_ctx_set_operand_order(ctx->handle(), -1);
     if (rc != 0) return rc;
     for (uint32_t i = 0; i < count; ++i) {
       IndexDocumentList *out = ctx->mutable_result(i);
@@ -532,6 +535,8 @@ class GpuFlatStreamer : public IndexStreamer {
     std::unique_lock<std::shared_mutex> g(mu_);
     rc = zvb200_store_create(device_, dtype_of(meta_), metric_of(meta_), meta_.dimension(), &store_);
     if (rc != 0) return rc;
+    // FlatStreamerEntity::row_major_distance hands the metric (query, feature) (flat_streamer_entity.h:155-162)
+    if ((rc = zvb200_store_set_operand_order(store_, 1)) != 0) return rc;
     auto provider = stock_->create_provider();
     if (provider) {
       const size_t es = meta_.element_size();
@@ -916,7 +921,9 @@ class GpuIVFSearcher : public IndexSearcher {
     // posting lists in list order through IVFEntity (ivf_entity.h:89-170): rows + keys + offsets
     zvb200_store *st = nullptr;
     if ((rc = zvb200_store_create(device_, dtype_of(meta_), metric_of(meta_), meta_.dimension(), &st)) != 0) return rc;
-    rc = zvb200_store_reserve(st, n);
+    // IVFDistanceCalculator::row_major_distance: (query, feature) (ivf_distance_calculator.h:174-183)
+    rc = zvb200_store_set_operand_order(st, 1);
+    if (rc == 0) rc = zvb200_store_reserve(st, n);
     std::vector<uint64_t> offs(nl + 1, 0);
     std::vector<char> rows;
     std::vector<uint64_t> keys;

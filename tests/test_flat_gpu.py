@@ -479,3 +479,34 @@ def test_concurrent_contexts_on_one_store():
     [t.start() for t in ts]; [t.join() for t in ts]
     assert not errors, errors
     st.close()
+
+
+@pytest.mark.parametrize("kernel", [1, 2, 3, 4])
+@pytest.mark.parametrize("kind", ["qi8_ip", "qi8_cos", "qi8_l2"])
+def test_operand_order_of_the_streamer_is_bit_exact(kind, kernel):
+    """FlatStreamer / the IVF list scan hand the metric (query, feature), FlatSearcher (feature, query)
+    (flat_streamer_entity.h:155-162 vs flat_distance_matrix.h:53-55); the QuantizedInteger -IP epilogue sums its middle
+    terms in operand order.  With zvb200_store_set_operand_order(1) every score equals the restatement called with the
+    operands swapped, bit for bit (L2 is symmetric, it must not move)."""
+    n, d, q, k = 1200, 32, 6, 100
+    metric, dt, sdim, stored, conv = make_stored(kind, n, d, seed=91)
+    rng = np.random.default_rng(92)
+    queries = np.ascontiguousarray(conv(rng.standard_normal((q, d)).astype(np.float32)))
+    st = z.Store(dt, metric, sdim)
+    st.append(stored); st.seal()
+    st.set_operand_order(True)
+    ctx = z.Context(st)
+    ctx.set_kernel(kernel)
+    _, gs, gi, _ = ctx.search(queries, k)
+    moved = 0
+    for i in range(q):
+        # the restatement with the roles swapped: the query is the "stored row", each row the "query"
+        swapped = np.array([S.oracle_distances(metric, dt, queries[i:i + 1], sdim, stored[r])[0] for r in range(n)],
+                           np.float32)
+        plain = S.oracle_distances(metric, dt, stored, sdim, queries[i])
+        moved += int((swapped.view(np.uint32) != plain.view(np.uint32)).sum())
+        order = np.lexsort((np.arange(n), swapped))[:k]
+        assert np.array_equal(gs[i].view(np.uint32), swapped[order].view(np.uint32)), (kind, kernel, i)
+        assert np.array_equal(gi[i], order.astype(np.uint32))
+    assert (moved == 0) == (kind == "qi8_l2")     # the case tests something: -IP scores do move
+    ctx.close(); st.close()

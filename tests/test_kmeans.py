@@ -191,6 +191,24 @@ def test_oracle_kmeans_other_metrics_equal_the_reference(metric, name):
 
 
 @needs_ref
+def test_oracle_kmeans_moves_empty_clusters_to_the_tail_like_the_reference():
+    """InnerProduct k-means starves clusters; cluster() ends with PurgeCentroids (kmeans_cluster.cc:363-383, 533), which
+    swaps the empty ones to the tail even with purge_empty = false — centroids, follows and labels come back in THAT
+    order.  Zero passes rotate the list (nobody follows anything)."""
+    x, init = _data(20000, 32, 40, 10)
+    rc, rl, rf, rs = _ref_kmeans("InnerProduct", x, init, 3, threads=8)
+    assert (rf == 0).sum() >= 2 and not (rf[:-3] == 0).any()          # the case tests something
+    oc, ol, of, os_, d = KO.kmeans(x, init, 3, "ip")
+    assert np.array_equal(of, rf) and np.allclose(oc, rc, rtol=1e-5, atol=1e-6, equal_nan=True)
+    ties = _near_tie_rows(np.where(np.isnan(d), np.inf, d))
+    assert np.array_equal(ol[~ties], rl[~ties])
+    y, init2 = _data(300, 8, 5, 22)
+    rc0, _, rf0, _ = _ref_kmeans("SquaredEuclidean", y, init2, 0)
+    oc0, _, of0, _, _ = KO.kmeans(y, init2, 0)
+    assert np.array_equal(rc0, oc0) and not rf0.any() and not of0.any()
+
+
+@needs_ref
 def test_reference_kmeans_puts_an_all_nan_row_into_cluster_0():
     """LinearSeeker::seek starts at (column 0, FLT_MAX) and only moves on a strictly smaller score
     (linear_seeker.cc:25-41): a row whose distances are all NaN follows centroid 0 and adds FLT_MAX to the cost."""
@@ -228,9 +246,12 @@ def test_gpu_kmeans_nan_row_and_zero_iterations_follow_the_reference():
     assert np.isnan(gc[0]).all() and np.allclose(gc[1:], rc[1:], rtol=1e-5, atol=1e-6, equal_nan=True)
     assert gs >= np.finfo(np.float32).max * 0.99
     assert gl.max() < 4                               # labels never carry 0xFFFFFFFF
-    # max_iterations = 0: the loop of KmeansCluster::cluster does not run — centroids as given, nothing follows
+    # max_iterations = 0: the loop of KmeansCluster::cluster does not run — nothing follows, and PurgeCentroids
+    # (kmeans_cluster.cc:363-383) still swaps every 'empty' centroid to the tail: the list comes back rotated
     y, init2 = _data(300, 8, 5, 22)
+    rc0, rl0, rf0, rs0 = _ref_kmeans("SquaredEuclidean", y, init2, 0)
     gc, gl, gf, gs, it = z.kmeans(y, init2, max_iterations=0)
-    assert it == 0 and np.array_equal(gc, init2) and gs == 0.0 and not gf.any()
-    ol, _, _ = KO.assign(y, init2)
+    assert it == 0 and np.array_equal(gc, rc0) and gs == 0.0 and not gf.any()
+    assert np.array_equal(gc, init2[KO.purge_order(np.zeros(5))])
+    ol, _, _ = KO.assign(y, gc)
     assert (gl == ol).mean() > 0.99

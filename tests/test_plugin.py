@@ -434,7 +434,8 @@ def _index_keys_search(ix, queries, k, pks=None):
 @needs_plugin
 @pytest.mark.gpu
 @pytest.mark.parametrize("conv,metric", [("", "SquaredEuclidean"), ("HalfFloatConverter", "InnerProduct"),
-                                         ("Int8StreamingConverter", "SquaredEuclidean")])
+                                         ("Int8StreamingConverter", "SquaredEuclidean"),
+                                         ("Int8StreamingConverter", "InnerProduct")])
 def test_gpu_searcher_p_keys_group_by_and_get_vector(conv, metric):
     """search_bf_by_p_keys_impl (flat_searcher.cc:213-237), group-by (delegated to the embedded stock searcher,
     flat_searcher.cc:178-179), get_vector(key) / create_provider() (flat_searcher.h:111,158-160, flat_searcher.cc:26-65)
@@ -444,7 +445,9 @@ def test_gpu_searcher_p_keys_group_by_and_get_vector(conv, metric):
     x, qs = _tie_free(n, d, 15), _tie_free(q, d, 16)
     ref = S.RefIndex(x, S.DT_FP32, d, metric, conv, kind="Flat")
     gpu = S.RefIndex(x, S.DT_FP32, d, metric, conv, kind="Flat:GpuFlatSearcher")
-    pks = np.concatenate([np.arange(3, n, 7), np.array([n + 5, 2 ** 41], np.int64), np.arange(100, 9000, 7)]).astype(np.uint64)
+    # only keys the index holds: the stock FlatSearcher dereferences provider->get_vector(pk) == nullptr for any other
+    # key (flat_searcher_context.h:1091-1093; SIGSEGV here), the GPU class skips such keys like FlatStreamer does
+    pks = np.concatenate([np.arange(3, n, 7), np.arange(100, 9000, 7)]).astype(np.uint64)
     a, b = _index_keys_search(ref, qs, k, pks), _index_keys_search(gpu, qs, k, pks)
     _same(b, a, "p_keys %s/%s" % (conv, metric))
     big = np.arange(0, n, 1, dtype=np.uint64)                      # more keys than one zvb200_search_rows call takes

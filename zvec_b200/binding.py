@@ -40,6 +40,8 @@ _SIGS = {
     "zvb200_store_seal": (C.c_int, [C.c_void_p]),
     "zvb200_store_count": (C.c_uint64, [C.c_void_p]),
     "zvb200_store_set_deleted": (C.c_int, [C.c_void_p, C.c_uint64, C.c_int]),
+    "zvb200_store_set_operand_order": (C.c_int, [C.c_void_p, C.c_int]),
+    "zvb200_ctx_set_operand_order": (C.c_int, [C.c_void_p, C.c_int]),
     "zvb200_store_write": (C.c_int, [C.c_void_p, C.c_uint64, C.c_void_p, C.c_uint64]),
     "zvb200_store_get_vector": (C.c_int, [C.c_void_p, C.c_uint64, C.c_void_p, C.c_size_t]),
     "zvb200_store_scan_bytes": (C.c_uint64, [C.c_void_p]),
@@ -184,6 +186,9 @@ class Store:
 
     def scan_bytes(self):
         return lib().zvb200_store_scan_bytes(self.h)
+
+    def set_operand_order(self, query_first):
+        _check(lib().zvb200_store_set_operand_order(self.h, int(query_first)))
 
     def set_deleted(self, row, deleted=True):
         _check(lib().zvb200_store_set_deleted(self.h, row, int(deleted)))

@@ -298,6 +298,15 @@ uint64_t zvb200_store_scan_bytes(const zvb200_store *s) {
   return s->n * ((uint64_t)s->vec_bytes + (s->has_tail ? 16 : 0));
 }
 
+int zvb200_store_set_operand_order(zvb200_store *s, int query_first) {
+  if (!s) return set_err(ZVB200_ERR_INVALID_ARGUMENT, "null store");
+  std::lock_guard<std::shared_mutex> g(s->mu);
+  s->query_first = query_first != 0;
+  for (auto *sh : s->shards) sh->query_first = s->query_first;
+  // the IVF centroid index is a nested FlatSearcher (ivf_centroid_index.cc:273-295): feature first, left as it is
+  return 0;
+}
+
 int zvb200_store_set_deleted(zvb200_store *s, uint64_t row, int deleted) {
   if (!s) return set_err(ZVB200_ERR_INVALID_ARGUMENT, "null store");
   std::lock_guard<std::shared_mutex> g(s->mu);
@@ -429,6 +438,12 @@ int zvb200_ctx_set_kernel(zvb200_ctx *c, int which) {
   return 0;
 }
 const char *zvb200_ctx_last_kernel(const zvb200_ctx *c) { return c ? c->last_kernel : "none"; }
+int zvb200_ctx_set_operand_order(zvb200_ctx *c, int order) {
+  if (!c || order < -1 || order > 1) return set_err(ZVB200_ERR_INVALID_ARGUMENT, "operand order is -1, 0 or 1");
+  c->operand_order = order;
+  for (auto *sc : c->sub) sc->operand_order = order;
+  return 0;
+}
 int zvb200_ctx_set_row_limit(zvb200_ctx *c, uint64_t rows) {
   if (!c) return set_err(ZVB200_ERR_INVALID_ARGUMENT, "null ctx");
   c->row_limit = rows;
@@ -484,7 +499,7 @@ static int prep_core(zvb200_ctx *c, zvb200_store *s, const void *queries_dev, ui
 int zvb_search_core(zvb200_ctx *c, zvb200_store *s, const void *queries_dev, uint32_t q, uint32_t k,
                     float threshold, const uint32_t *filter_dev, float *out_scores_dev,
                     uint32_t *out_index_dev, u64 *out_keys_dev, uint64_t row_begin, uint64_t row_end) {
-  RowsView rv = s->view();
+  RowsView rv = zvb_view_for(c, s);
   const uint32_t esz = s->dtype == ZVB200_DT_FP32 ? 4 : s->dtype == ZVB200_DT_FP16 ? 2 : 1;
   QueryView qv;
   {
@@ -611,7 +626,7 @@ int zvb_rows_core(zvb200_ctx *c, zvb200_store *s, const void *queries_dev, uint3
   CU(c->seg_count.ensure((size_t)q * 4));
   CU(launch_rows_plan(rows_dev, q, m, s->n, (uint32_t *)c->seg_prefix.p, (uint32_t *)c->seg_row.p,
                       (uint32_t *)c->seg_count.p, c->stream));
-  RowsView rv = s->view();
+  RowsView rv = zvb_view_for(c, s);
   SearchParams sp;
   sp.k = k; sp.threshold = threshold; sp.filter = filter_dev;
   const size_t parts = scan_lists_parts(q, s->sm_count);
@@ -925,7 +940,7 @@ static int ivf_core(zvb200_ctx *c, const void *queries_dev, uint32_t q, uint32_t
   CU(launch_ivf_plan((const uint32_t *)c->coarse_index.p, q, nprobe, s->list_off_dev, s->budget_dev, max_scan_count,
                      (uint32_t *)c->seg_prefix.p, (uint32_t *)c->seg_row.p, (uint32_t *)c->seg_count.p, c->stream));
   // 3. posting-list scan, queries already in compute layout (same dtype / metric / dim as the centroids)
-  RowsView rv = s->view();
+  RowsView rv = zvb_view_for(c, s);
   SearchParams sp;
   sp.k = k; sp.threshold = threshold; sp.filter = filter_dev;
   const bool lists_stream = c->force_kernel == 4 && scan_stream_supports(rv, k, nprobe);
@@ -1294,17 +1309,40 @@ static int kmeans_core(int device, int metric, const float *rows_dev, const floa
     if (fabs(new_cost - cost) < epsilon) { ++it; break; }
     cost = new_cost;
   }
+  // cluster() ends with PurgeCentroids(cents, purge_empty_) (kmeans_cluster.cc:363-383, 533): even when nothing is
+  // cut, every centroid nobody follows is swapped with the last one not yet moved — the empty clusters end up at
+  // the tail, and label() then runs against the centroids in THAT order
+  static_assert(sizeof(unsigned long long) == sizeof(uint64_t), "follows layout");
+  std::vector<uint64_t> fol(k, 0);
+  CU(cudaMemcpyAsync(centroids, w.cent, cbytes, cudaMemcpyDeviceToHost, c->stream));
+  CU(cudaMemcpyAsync(fol.data(), w.counts, (size_t)k * sizeof(uint64_t), cudaMemcpyDeviceToHost, c->stream));
+  CU(cudaStreamSynchronize(c->stream));
+  {  // also after zero passes: nobody follows anything then, and the reference rotates the list it was given
+    bool moved = false;
+    std::vector<float> tmp(dim);
+    for (size_t index = 0, tamp = k; index < tamp;) {
+      if (fol[index] == 0) {
+        const size_t last = tamp - 1;
+        if (index != last) {
+          std::swap(fol[index], fol[last]);
+          float *a = centroids + index * dim, *b = centroids + last * dim;
+          memcpy(tmp.data(), a, dim * sizeof(float)); memcpy(a, b, dim * sizeof(float)); memcpy(b, tmp.data(), dim * sizeof(float));
+          moved = true;
+        }
+        tamp = last;
+        continue;
+      }
+      ++index;
+    }
+    if (moved) CU(cudaMemcpyAsync(w.cent, centroids, cbytes, cudaMemcpyHostToDevice, c->stream));
+  }
+  if (follows) memcpy(follows, fol.data(), (size_t)k * sizeof(uint64_t));
   if (labels) {  // KmeansCluster::label: against the centroids as returned
     r = assign();
     if (r != 0) return r;
     CU(cudaMemcpyAsync(labels, w.lab, n * sizeof(uint32_t), cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
   }
-  CU(cudaMemcpyAsync(centroids, w.cent, cbytes, cudaMemcpyDeviceToHost, c->stream));
-  if (follows) {
-    static_assert(sizeof(unsigned long long) == sizeof(uint64_t), "follows layout");
-    CU(cudaMemcpyAsync(follows, w.counts, (size_t)k * sizeof(uint64_t), cudaMemcpyDeviceToHost, c->stream));
-  }
-  CU(cudaStreamSynchronize(c->stream));
   if (sse_out) *sse_out = new_cost;
   if (iterations_out) *iterations_out = it;
   return 0;

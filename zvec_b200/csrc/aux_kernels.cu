@@ -427,7 +427,7 @@ __global__ void distance_matrix_kernel(RowsView rv, QueryView qv, float *out) {
       const int m = rv.metric;
       if (rv.dtype == ZVB200_DT_INT8) {
         if (m == ZVB200_METRIC_QI8_L2SQ) s = qi8_l2sq((float)ab, rv.tails[r], qv.qtails[j], (float)rv.d);
-        else if (metric_is_qi8(m)) s = qi8_mip((float)ab, rv.tails[r], qv.qtails[j], (float)rv.d);
+        else if (metric_is_qi8(m)) s = qi8_mip_ord((float)ab, rv.tails[r], qv.qtails[j], (float)rv.d, rv.query_first);
         else if (l2) { s = (float)(aa - 2 * ab + qq); if (m == ZVB200_METRIC_L2) s = sqrtf(s); }
         else s = -(float)ab;
       } else {

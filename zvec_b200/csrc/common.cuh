@@ -68,6 +68,14 @@ __device__ __forceinline__ float qi8_mip(float ipf, float4 m, float4 q, float d)
   return -r;
 }
 
+// The reference hands its 1x1 distance function (feature, query) from FlatSearcher (flat_distance_matrix.h:53-55) but
+// (query, feature) from FlatStreamer and the IVF list scan (flat_streamer_entity.h:155-162,
+// ivf_distance_calculator.h:174-183).  The L2 form is symmetric bit for bit; -IP sums its middle terms in the other
+// order and differs in the last place for ~15 % of the rows, so the store says which operand came first.
+__device__ __forceinline__ float qi8_mip_ord(float ipf, float4 m, float4 q, float d, bool query_first) {
+  return query_first ? qi8_mip(ipf, q, m, d) : qi8_mip(ipf, m, q, d);
+}
+
 // Relative margin of the bf16 "shadow" filter for QuantizedInteger L2 (scan_mma.cu KIND 3, aux_kernels.cu):
 // |filter value - real-arithmetic score| <= eps * [(ma^2 ms2 + mb^2 d) + (qa^2 qs2 + qb^2 d)].
 //   2^-8           scaled codes rounded to bf16 (8-bit significand), query codes exact; Cauchy-Schwarz on the sum

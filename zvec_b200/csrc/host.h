@@ -33,6 +33,7 @@ struct zvb200_store {
   int device = 0, dtype = 0, metric = 0, sm_count = 148;
   uint32_t dim = 0, elem_bytes = 0, d = 0, vec_bytes = 0, row_stride = 0, chunks = 0, tail_off = 0;
   bool has_tail = false, sealed = false;
+  bool query_first = false;       // zvb200_store_set_operand_order
   uint8_t *rows = nullptr;
   float4 *tails = nullptr;
   float *norms = nullptr;
@@ -75,6 +76,7 @@ struct zvb200_store {
     v.rows = rows; v.n = n; v.row_stride = row_stride; v.chunks = chunks; v.d = d;
     v.dtype = dtype; v.metric = metric; v.tails = tails; v.norms = norms;
     v.drop = has_drop ? drop : nullptr;
+    v.query_first = query_first;
     if (shadow && shadowed >= n) { v.shadow = shadow; v.shadow_k = shadow_k; v.shadow_mrow_max = shadow_mrow_max; }
     return v;
   }
@@ -125,6 +127,7 @@ struct zvb200_ctx {
   const char *last_kernel = "none";
   cudaEvent_t ev_scan0 = nullptr, ev_scan1 = nullptr;  // bracket the scan kernel(s) of the last search
   bool scan_timed = false;
+  int operand_order = -1;  // zvb200_ctx_set_operand_order: -1 the store's, 0 feature first, 1 query first
   uint64_t row_limit = 0;  // zvb200_ctx_set_row_limit: searches see rows [0, row_limit) only (0 = every row)
   // a context of a sharded parent: one context per shard (on the shard's device), the exchange buffers on the root
   std::vector<zvb200_ctx *> sub;
@@ -159,3 +162,9 @@ int zvb_rows_core(zvb200_ctx *c, zvb200_store *s, const void *queries_dev, uint3
                   uint32_t *out_index_dev, u64 *out_keys_dev);
 int zvb_check_search_args(zvb200_ctx *c, const void *queries, uint32_t q, uint32_t k);
 int zvb_check_row_limit(uint64_t rows);
+// the store's rows as this context's searches see them (operand order override)
+inline RowsView zvb_view_for(const zvb200_ctx *c, const zvb200_store *s) {
+  RowsView v = s->view();
+  if (c->operand_order >= 0) v.query_first = c->operand_order != 0;
+  return v;
+}

@@ -23,6 +23,7 @@ struct RowsView {
   const float4 *tails = nullptr;    // QI8: {a, b, s, s2} per row
   const float *norms = nullptr;     // |x|^2 per row (tensor-core L2 path)
   const uint32_t *drop = nullptr;   // bit set = deleted row or kInvalidKey hole
+  bool query_first = false;         // QuantizedInteger -IP: evaluate as the reference's streamer does (common.cuh)
   // QuantizedInteger L2: bf16 image of every row (scaled codes + the row's share of the score's bilinear
   // terms), shadow_k halves per row — what the tcgen05 scan contracts instead of the int8 codes (scan_mma.cu)
   const uint8_t *shadow = nullptr;

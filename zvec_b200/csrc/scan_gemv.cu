@@ -179,7 +179,7 @@ __global__ void __launch_bounds__(kThreads, QB == 1 ? 2 : 1) scan_gemv_kernel(co
         float s;
         if (DT == ZVB200_DT_INT8) {
           if (metric == ZVB200_METRIC_QI8_L2SQ) s = qi8_l2sq((float)acc[u][j], mt, qt[j], dq);
-          else if (metric_is_qi8(metric)) s = qi8_mip((float)acc[u][j], mt, qt[j], dq);
+          else if (metric_is_qi8(metric)) s = qi8_mip_ord((float)acc[u][j], mt, qt[j], dq, a.rv.query_first);
           else if (L2) {
             s = (float)((int)aa[u] - 2 * (int)acc[u][j] + qq[j]);
             if (metric == ZVB200_METRIC_L2) s = sqrtf(s);

@@ -72,6 +72,7 @@ struct MmaArgs {
   const uint8_t *qraw;  // int8 query codes, row_stride apart
   uint32_t d;           // elements of the dot product
   float threshold;
+  bool query_first;     // QuantizedInteger -IP operand order (common.cuh)
   const uint32_t *drop, *filter;
   u64 *part;            // [nq][groups][k]
   uint32_t *pub;        // [groups][nq] ordered image of each CTA's pub_j-th best score per query
@@ -528,7 +529,7 @@ scan_mma_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
         const float ipf = small_ip ? __int_as_float(ip + 0x4B400000) - 12582912.0f : (float)ip;
         return fmaf(__fmul_rn(c4.w, ipf), nQa, fmaf(c4.z, nQ2, fmaf(c4.y, nQ1, c4.x)));
       }
-      return -qi8_mip((float)ip, c4, qt, dq);
+      return -qi8_mip_ord((float)ip, c4, qt, dq, a.query_first);
     };
     const bool root6 = KIND == 2 && imode == 6 && a.metric == ZVB200_METRIC_L2;
     const float hq = (resc && qvalid) ? 0.5f * a.qnorms[q0 + slot] : 0.f;
@@ -1073,6 +1074,7 @@ cudaError_t launch_scan_mma(const RowsView &rv, const QueryView &qv, const Searc
   a.eps = (float)rv.d * 4.8e-7f + (f32 ? 2.2e-3f : 0.f);
   a.sh_mrow_max = rv.shadow_mrow_max;
   a.threshold = sp.threshold;
+  a.query_first = rv.query_first;
   a.drop = rv.drop; a.filter = sp.filter;
   a.part = part;
   a.pub = pub;

@@ -246,7 +246,7 @@ __global__ void __launch_bounds__(544, 1) scan_stream_kernel(const StreamArgs a)
           if (DT == ZVB200_DT_INT8) {
             const float4 mt = (qi8 && valid) ? ttile[rl] : make_float4(0, 0, 0, 0);
             if (metric == ZVB200_METRIC_QI8_L2SQ) s = qi8_l2sq((float)acc[u], mt, qt, dq);
-            else if (qi8) s = qi8_mip((float)acc[u], mt, qt, dq);
+            else if (qi8) s = qi8_mip_ord((float)acc[u], mt, qt, dq, a.rv.query_first);
             else if (L2) {
               s = (float)((int)aa[u] - 2 * (int)acc[u] + qq[0]);
               if (metric == ZVB200_METRIC_L2) s = sqrtf(s);

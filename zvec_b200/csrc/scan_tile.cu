@@ -209,7 +209,7 @@ __global__ void __launch_bounds__(kThreads) scan_tile_kernel(const TileArgs a) {
         float s;
         if (I8) {
           if (metric == ZVB200_METRIC_QI8_L2SQ) s = qi8_l2sq((float)acci[i][j], mt, qtl[j], dq);
-          else if (metric_is_qi8(metric)) s = qi8_mip((float)acci[i][j], mt, qtl[j], dq);
+          else if (metric_is_qi8(metric)) s = qi8_mip_ord((float)acci[i][j], mt, qtl[j], dq, a.rv.query_first);
           else if (L2) { s = (float)(aai[i] - 2 * acci[i][j] + qqi[j]); if (metric == ZVB200_METRIC_L2) s = sqrtf(s); }
           else s = -(float)acci[i][j];
         } else {
