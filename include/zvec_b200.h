@@ -151,6 +151,21 @@ int zvb200_search_device(zvb200_ctx *c, const void *queries_dev, uint32_t q, uin
                          float threshold, const uint32_t *filter_dev, float *out_scores_dev,
                          uint32_t *out_index_dev);
 int zvb200_ctx_sync(zvb200_ctx *c);
+/* zvb200_search_device for callers that cannot allocate (code under CUDA graph capture, tight serving loops,
+ * harnesses that forbid cudaMalloc).  NO counterpart in the reference.
+ * Same arguments, same results bit for bit (prep_queries -> GEMV streaming scan -> merge_parts on the context's
+ * stream), but every scratch buffer lives in one static device array of ZVB200_NOALLOC_SCRATCH_BYTES that each GPU
+ * loading the library holds until exit; the call makes no cudaMalloc / cudaFree and no allocating library call.
+ * Limits (ZVB200_ERR_INVALID_ARGUMENT beyond): q <= ZVB200_NOALLOC_MAX_QUERIES, k <= ZVB200_NOALLOC_MAX_TOPK,
+ * and prepared queries + partial lists within the scratch (rows of up to ~16 KiB at the maximum q and k); plain
+ * one-GPU stores only (ZVB200_ERR_UNSUPPORTED on a sharded one).  All calls share the array, which keeps the last
+ * call's contents (the call re-initialises what it reads): calls that overlap on the GPU race — serialise them. */
+#define ZVB200_NOALLOC_SCRATCH_BYTES 4194304
+#define ZVB200_NOALLOC_MAX_QUERIES 8u
+#define ZVB200_NOALLOC_MAX_TOPK 128u
+int zvb200_search_device_noalloc(zvb200_ctx *c, const void *queries_dev, uint32_t q, uint32_t k,
+                                 float threshold, const uint32_t *filter_dev, float *out_scores_dev,
+                                 uint32_t *out_index_dev);
 /* Device time of the scan kernel(s) of the last search on this context, from CUDA events
  * recorded on its stream around them (the IndexContext::Profiler analogue,
  * src/include/zvec/core/framework/index_context.h:31-53).  Waits for that search. */

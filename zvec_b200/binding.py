@@ -51,6 +51,8 @@ _SIGS = {
                                 C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     "zvb200_search_device": (C.c_int, [C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_float,
                                        C.c_void_p, C.c_void_p, C.c_void_p]),
+    "zvb200_search_device_noalloc": (C.c_int, [C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_float,
+                                               C.c_void_p, C.c_void_p, C.c_void_p]),
     "zvb200_ctx_sync": (C.c_int, [C.c_void_p]),
     "zvb200_ctx_stream": (C.c_void_p, [C.c_void_p]),
     "zvb200_ctx_last_scan_ms": (C.c_int, [C.c_void_p, C.POINTER(C.c_float)]),
@@ -379,6 +381,12 @@ class Context:
         _check(lib().zvb200_search_refined(self.h, exact_ctx.h, _ptr(queries_fp32), q, dim, k, scale_factor,
                                            _ptr(filter_bitmap), _ptr(keys), _ptr(scores), _ptr(index), _ptr(counts)))
         return keys, scores, index, counts
+
+    def search_device_noalloc(self, q_ptr, q, k, out_scores_ptr, out_index_ptr, threshold=FLT_MAX, filter_ptr=None):
+        """zvb200_search_device with every scratch buffer in the library's static device array (no allocation)"""
+        _check(lib().zvb200_search_device_noalloc(self.h, C.c_void_p(q_ptr), q, k, threshold,
+                                                  C.c_void_p(filter_ptr) if filter_ptr else None,
+                                                  C.c_void_p(out_scores_ptr), C.c_void_p(out_index_ptr)))
 
     def search_device(self, q_ptr, q, k, out_scores_ptr, out_index_ptr, threshold=FLT_MAX, filter_ptr=None):
         _check(lib().zvb200_search_device(self.h, C.c_void_p(q_ptr), q, k, threshold,
