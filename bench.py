@@ -473,11 +473,13 @@ def run_ours(args):
     ms_b, launches = timed(B, args.steps, args.warmup, reps_b)
     clocks = sampler.stop() if rank == 0 else None
     kernel_b = ctx.last_kernel()
-    # dominant-kernel duration, measured live with CUDA events around the scan kernel only (right after the timed
-    # region: same power state)
-    scan_ms = []
-    for _ in range(max(args.steps, 5)):
-        step_q(B)
+    # dominant-kernel duration, measured live with CUDA events around the scan kernel only, IN the power state of the
+    # timed region: the last batch of the timed region itself, then the last batch of a few more back-to-back bursts
+    # (a sync after every single batch lets the clocks recover and flatters the kernel by ~8 %)
+    scan_ms = [ctx.last_scan_ms()]
+    for _ in range(4):
+        for _ in range(max(3, reps_b)):
+            step_q(B)
         ctx.sync()
         scan_ms.append(ctx.last_scan_ms())
     scan_b = allmax(float(np.mean(scan_ms)))
@@ -486,9 +488,10 @@ def run_ours(args):
     reps_1 = calibrate(1, s1)
     ms_1, _ = timed(1, s1, max(args.warmup, 3), reps_1)
     kernel_1 = ctx.last_kernel()
-    scan_ms = []
-    for _ in range(10):
-        step_q(1)
+    scan_ms = [ctx.last_scan_ms()]
+    for _ in range(4):
+        for _ in range(max(3, reps_1)):
+            step_q(1)
         ctx.sync()
         scan_ms.append(ctx.last_scan_ms())
     scan_1 = allmax(float(np.mean(scan_ms)))

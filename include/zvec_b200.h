@@ -349,6 +349,21 @@ int zvb200_kmeans_device(int device, int metric, const float *rows_dev, uint64_t
                          float *centroids, uint32_t k, uint32_t max_iterations, double epsilon,
                          uint32_t *labels, uint64_t *follows, double *sse, uint32_t *iterations);
 
+/* ---- IVF build, after the centroids are trained (second half).
+ * zvb200_ivf_assign replaces IVFBuilder::label -> IVFCentroidIndex::search_nearest_centroid
+ * (src/core/algorithm/ivf/ivf_builder.h:243-262, ivf_centroid_index.cc:297-318: a top-1 search over the centroids per
+ * row): labels[i] = nearest of the nlist centroids to row i under `metric` (the lower centroid wins a tie; a row no
+ * centroid can score follows centroid 0).  rows / centroids: HOST, stored layout of (dtype, metric, dim).
+ * zvb200_ivf_pack replaces the list-by-list walk of IVFBuilder::dump_index (ivf_builder.cc:672-683) over labels_:
+ * order[] = row numbers posting list by posting list, ascending inside a list; list_offsets[l] = position in order[]
+ * where list l starts (InvertedListMeta::id_offset, ivf_index_format.h:41-47), list_offsets[nlist] = n.  A host
+ * adaptor hands order[] to the reference's IVFDumper (ivf_dumper.h:191-209) — integration/gpu_ivf_builder.cc — or
+ * appends the rows in that order to a store and calls zvb200_ivf_attach. */
+int zvb200_ivf_assign(int device, int dtype, int metric, uint32_t dim, const void *centroids, uint32_t nlist,
+                      const void *rows, uint64_t n, uint32_t *labels);
+int zvb200_ivf_pack(int device, const uint32_t *labels, uint64_t n, uint32_t nlist, uint32_t *order,
+                    uint64_t *list_offsets);
+
 #ifdef __cplusplus
 }
 #endif

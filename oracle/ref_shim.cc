@@ -29,6 +29,7 @@
 #include <zvec/core/framework/index_searcher.h>
 #include <zvec/core/framework/index_segment_storage.h>
 #include <zvec/core/framework/index_streamer.h>
+#include <zvec/core/framework/index_trainer.h>
 #include <zvec/core/interface/index.h>
 #include <zvec/core/interface/index_factory.h>
 #include "ivf/ivf_entity.h"
@@ -115,9 +116,43 @@ void parse_params(const char *kv, Params *p) {
 
 }  // namespace
 
+// An IndexTrainer that hands a builder centroids the caller already has (IVFBuilder::train(trainer),
+// ivf_builder.cc:272-330): the way to build a stock IVF index and a GPU-built one from the SAME centroids.
+class FixedCentroidTrainer : public IndexTrainer {
+ public:
+  FixedCentroidTrainer(const IndexMeta &meta, const void *cents, size_t count) : meta_(meta) {
+    IndexCluster::CentroidList list;
+    for (size_t i = 0; i < count; ++i)
+      list.emplace_back((const char *)cents + i * meta.element_size(), meta.element_size());
+    IndexCluster::Serialize(meta_, list, &bundle_);
+  }
+  int init(const IndexMeta &, const Params &) override { return 0; }
+  int cleanup(void) override { return 0; }
+  int train(IndexThreads::Pointer, IndexHolder::Pointer) override { return 0; }
+  int load(IndexStorage::Pointer) override { return 0; }
+  int dump(const IndexDumper::Pointer &) override { return 0; }
+  const IndexMeta &meta(void) const override { return meta_; }
+  const Stats &stats(void) const override { return stats_; }
+  IndexBundle::Pointer indexes(void) const override { return bundle_; }
+
+ private:
+  IndexMeta meta_;
+  Stats stats_;
+  IndexBundle::Pointer bundle_;
+};
+static std::string g_fixed_centroids;   // zref_set_fixed_centroids: the next zref_index_create builds from these
+static size_t g_fixed_count = 0;
+
 extern "C" {
 
 const char *zref_last_error(void) { return g_err.c_str(); }
+
+// centroids (stored layout of the index to come, `count` of `elem` bytes) for the next zref_index_create calls:
+// the builder is trained through train(trainer) instead of clustering; count = 0 clears
+void zref_set_fixed_centroids(const void *cents, uint64_t count, uint32_t elem) {
+  g_fixed_centroids.assign((const char *)cents, (size_t)count * elem);
+  g_fixed_count = count;
+}
 
 // kind: "Flat" | "IVF".  dtype: IndexMeta::DataType of the CALLER's rows.
 // converter: "" or a registered converter name (e.g. Int8StreamingConverter,
@@ -184,7 +219,18 @@ void *zref_index_create(const char *kind, const void *rows, uint64_t n, uint32_t
   int r = builder->init(ix->meta, bp);
   if (r != 0) { fail(r, "builder init"); return nullptr; }
   if (dumper->create(ix->path) != 0) { fail(-1, "dumper create"); return nullptr; }
-  r = IndexBuilder::TrainBuildAndDump(builder, holder, dumper);
+  if (g_fixed_count) {
+    IndexMeta tm = ix->meta;   // what IVFBuilder::train(trainer) compares with its converted meta
+    tm.set_reformer(std::string(), 0, Params());
+    tm.set_converter(std::string(), 0, Params());
+    if (g_fixed_centroids.size() != g_fixed_count * tm.element_size()) { fail(-1, "fixed centroids: element size"); return nullptr; }
+    auto trainer = std::make_shared<FixedCentroidTrainer>(tm, g_fixed_centroids.data(), g_fixed_count);
+    r = builder->train(trainer);
+    if (r == 0) r = builder->build(holder);
+    if (r == 0) r = builder->dump(dumper);
+  } else {
+    r = IndexBuilder::TrainBuildAndDump(builder, holder, dumper);
+  }
   if (r != 0) { fail(r, "build"); return nullptr; }
   dumper->close();
   ix->searcher = IndexFactory::CreateSearcher(searcher_name);

@@ -9,5 +9,5 @@ from .binding import (  # noqa: F401
     DT_FP16, DT_FP32, DT_INT8,
     METRIC_L2SQ, METRIC_L2, METRIC_IP, METRIC_COSINE,
     METRIC_QI8_L2SQ, METRIC_QI8_IP, METRIC_QI8_COSINE,
-    ZvecB200Error, lib, lib_path, Store, Context, Comm, comm_unique_id, distance_matrix, metric_from_names, kmeans,
+    ZvecB200Error, lib, lib_path, Store, Context, Comm, comm_unique_id, distance_matrix, metric_from_names, kmeans, ivf_assign, ivf_pack,
 )

@@ -97,6 +97,9 @@ _SIGS = {
                                         C.c_float, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     "zvb200_kmeans": (C.c_int, [C.c_int, C.c_int, C.c_void_p, C.c_uint64, C.c_uint32, C.c_void_p, C.c_uint32, C.c_uint32,
                                 C.c_double, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "zvb200_ivf_assign": (C.c_int, [C.c_int, C.c_int, C.c_int, C.c_uint32, C.c_void_p, C.c_uint32, C.c_void_p, C.c_uint64,
+                                    C.c_void_p]),
+    "zvb200_ivf_pack": (C.c_int, [C.c_int, C.c_void_p, C.c_uint64, C.c_uint32, C.c_void_p, C.c_void_p]),
     "zvb200_kmeans_device": (C.c_int, [C.c_int, C.c_int, C.c_void_p, C.c_uint64, C.c_uint32, C.c_void_p, C.c_uint32,
                                        C.c_uint32, C.c_double, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
 }
@@ -462,6 +465,26 @@ def distance_matrix(metric, dtype, dim, rows, queries, device=0):
     out = np.empty((nq, n), np.float32)
     _check(lib().zvb200_distance_matrix(device, metric, dtype, dim, _ptr(rows), n, _ptr(queries), nq, _ptr(out)))
     return out
+
+
+def ivf_assign(rows, centroids, dtype, metric, dim, device=0):
+    """nearest centroid of every row (IVFBuilder::label): rows / centroids in the stored layout -> labels u32[n]"""
+    rows, centroids = np.ascontiguousarray(rows), np.ascontiguousarray(centroids)
+    esz = dim * {DT_FP32: 4, DT_FP16: 2, DT_INT8: 1}[dtype]
+    n, k = rows.nbytes // esz, centroids.nbytes // esz
+    labels = np.zeros(n, np.uint32)
+    _check(lib().zvb200_ivf_assign(device, dtype, metric, dim, _ptr(centroids), k, _ptr(rows), n, _ptr(labels)))
+    return labels
+
+
+def ivf_pack(labels, nlist, device=0):
+    """rows grouped by posting list, ascending inside a list (IVFBuilder::dump_index's order) -> (order u32[n],
+    list_offsets u64[nlist + 1])"""
+    labels = np.ascontiguousarray(labels, np.uint32)
+    order = np.zeros(labels.size, np.uint32)
+    offs = np.zeros(nlist + 1, np.uint64)
+    _check(lib().zvb200_ivf_pack(device, _ptr(labels), labels.size, nlist, _ptr(order), _ptr(offs)))
+    return order, offs
 
 
 def kmeans(rows, centroids, metric=None, max_iterations=20, epsilon=float(np.finfo(np.float32).eps), device=0,

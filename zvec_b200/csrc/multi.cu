@@ -92,7 +92,7 @@ __global__ void merge_keys_kernel(const u64 *keys, size_t gstride, uint32_t G, c
   if (qi >= q) return;
   const int lane = threadIdx.x & 31;
   for (uint32_t i = lane; i < k; i += 32) {
-    if (out_scores) out_scores[(size_t)qi * k + i] = __int_as_float(0x7fc00000);
+    if (out_scores) out_scores[(size_t)qi * k + i] = __int_as_float(0x7fffffff);  // CUDART_NAN_F, the padding of every other merge
     if (out_rows) out_rows[(size_t)qi * k + i] = ZVB200_INVALID_KEY;
     if (out_index) out_index[(size_t)qi * k + i] = ZVB200_INVALID_INDEX;
   }
