@@ -33,6 +33,7 @@
 #include <mutex>
 #include <shared_mutex>
 #include <string>
+#include <thread>
 #include <unordered_map>
 #include <vector>
 
@@ -209,6 +210,39 @@ class GpuContext : public IndexContext {
 
 namespace {
 
+//! The host side of a filtered search: IndexFilter is an opaque std::function<bool(key)> (index_filter.h:23-62; true =
+//! drop, flat_searcher_context.h single_enqueue_filter) with no identity to key a cache by, so every filtered search
+//! evaluates it once per stored key — exactly as often as the reference calls it — into the bitmap the scan reads.
+//! Above 256k keys the evaluation is spread over host threads, whole bitmap words each: the reference itself calls
+//! one filter object from many searching threads at once (index.cc:24-45), so the callable is thread-safe by contract.
+//! 10M keys: ~50 ms on one core, ~4 ms on 16 — next to a 2.4 ms scan.  Returns the rows dropped.
+size_t build_filter_bitmap(const IndexFilter &filter, const uint64_t *keys, size_t n, bool skip_holes,
+                           std::vector<uint32_t> *bitmap) {
+  const size_t words = (n + 31) / 32;
+  bitmap->assign(words, 0u);
+  auto run = [&](size_t w0, size_t w1) -> size_t {
+    size_t dropped = 0;
+    for (size_t w = w0; w < w1; ++w) {
+      uint32_t bits = 0;
+      const size_t hi = std::min(n, (w + 1) * 32);
+      for (size_t i = w * 32; i < hi; ++i)
+        if (!(skip_holes && keys[i] == ZVB200_INVALID_KEY) && filter(keys[i])) { bits |= 1u << (i & 31); ++dropped; }
+      (*bitmap)[w] = bits;
+    }
+    return dropped;
+  };
+  const unsigned hw = std::thread::hardware_concurrency();
+  const size_t nt = n < ((size_t)1 << 18) ? 1 : std::min<size_t>({(size_t)(hw ? hw : 1), (size_t)16, words / 2048 + 1});
+  if (nt <= 1) return run(0, words);
+  std::vector<size_t> part(nt, 0);
+  std::vector<std::thread> th;
+  for (size_t t = 0; t < nt; ++t)
+    th.emplace_back([&, t] { part[t] = run(words * t / nt, words * (t + 1) / nt); });
+  size_t dropped = 0;
+  for (size_t t = 0; t < nt; ++t) { th[t].join(); dropped += part[t]; }
+  return dropped;
+}
+
 //! one search_bf_by_p_keys pass: each query's listed rows (ZVB200_INVALID_INDEX = skipped) in slices of
 //! ZVB200_MAX_CANDIDATES, the slices' best-k merged by (score, row) on the host — k entries per slice, not a scan
 int search_rows_sliced(GpuContext *ctx, const void *query, uint32_t count, const std::vector<std::vector<uint32_t>> &rows,
@@ -364,9 +398,7 @@ class GpuFlatSearcher : public IndexSearcher {
     if (ctx->filter().is_valid()) {
       // IndexFilter: true = drop (flat_searcher_context.h single_enqueue_filter); evaluated
       // once per row on the host, exactly as often as the reference calls it
-      ctx->bitmap.assign((n + 31) / 32, 0u);
-      for (size_t i = 0; i < n; ++i)
-        if (ctx->filter()(keys_[i])) { ctx->bitmap[i >> 5] |= 1u << (i & 31); ++dropped; }
+      dropped = build_filter_bitmap(ctx->filter(), keys_.data(), n, false, &ctx->bitmap);
       bitmap = ctx->bitmap.data();
     }
     const int rc = zvb200_search(ctx->handle(), query, count, k, ctx->threshold(), bitmap, ctx->keys.data(),
@@ -656,12 +688,7 @@ class GpuFlatStreamer : public IndexStreamer {
       if (n == 0) return 0;
       dropped = n - live_;
       if (ctx->filter().is_valid()) {
-        ctx->bitmap.assign((n + 31) / 32, 0u);
-        for (size_t i = 0; i < n; ++i)
-          if (all_keys_[i] != ZVB200_INVALID_KEY && ctx->filter()(all_keys_[i])) {
-            ctx->bitmap[i >> 5] |= 1u << (i & 31);
-            ++dropped;
-          }
+        dropped += build_filter_bitmap(ctx->filter(), all_keys_.data(), n, true, &ctx->bitmap);
         bitmap = ctx->bitmap.data();
       }
     }
@@ -1033,9 +1060,7 @@ class GpuIVFSearcher : public IndexSearcher {
     const uint32_t *bitmap = nullptr;
     size_t dropped = 0;
     if (ctx->filter().is_valid()) {
-      ctx->bitmap.assign((n + 31) / 32, 0u);
-      for (size_t i = 0; i < n; ++i)
-        if (ctx->filter()(keys_[i])) { ctx->bitmap[i >> 5] |= 1u << (i & 31); ++dropped; }
+      dropped = build_filter_bitmap(ctx->filter(), keys_.data(), n, false, &ctx->bitmap);
       bitmap = ctx->bitmap.data();
     }
     if (brute_force)

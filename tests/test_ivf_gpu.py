@@ -53,7 +53,7 @@ def test_ivf_search_equals_reference(metric, conv, origin, ratio, kernel):
     for batch in (1, len(qs)):
         for b0 in range(0, len(qs), batch):
             gk, gs, gi, gc = ctx.ivf_search(tq[b0:b0 + batch], k, nprobe, max_scan)
-            assert ctx.last_kernel() == ("scan_lists_stream" if kernel == 4 else "scan_lists")
+            assert ctx.last_kernel() == ("scan_lists_stream" if kernel == 4 else "scan_lists_lm" if batch >= 8 else "scan_lists")
             for j in range(gk.shape[0]):
                 i = b0 + j
                 assert gc[j] == rc[i]
@@ -81,3 +81,38 @@ def test_ivf_argument_errors():
     st.ivf_attach(np.zeros((2, 8), np.float32), [0, 4, 10])
     k_, s_, i_, c_ = ctx.ivf_search(np.zeros((1, 8), np.float32), 5, 1, 1)
     assert c_[0] == 4                                  # one list of 4 rows scanned
+
+
+@pytest.mark.parametrize("kind,d", [("fp32_l2", 48), ("fp16_ip", 200), ("qi8_l2", 96), ("fp32_cos", 1536)])
+@pytest.mark.parametrize("k", [10, 100])
+def test_list_major_scan_equals_query_major_bit_for_bit(kind, d, k):
+    """K4b (scan_lists_lm.cu) streams every probed list once for up to 8 of the batch's queries; the scores come from
+    the same arithmetic as the query-major scan, so ids AND scores are identical — with deleted rows, a filter, a tight
+    scan budget, empty lists and lists probed by more queries than one pass takes."""
+    from test_flat_gpu import make_stored
+    n, nlist, q, nprobe = 20000, 50, 200, 9
+    metric, dt, sdim, stored, conv = make_stored(kind, n, d, seed=31)
+    rng = np.random.default_rng(32)
+    cuts = np.sort(rng.choice(np.arange(1, n), nlist - 1, replace=False))
+    offs = np.concatenate([[0], cuts, [n]]).astype(np.uint64)
+    offs[7] = offs[6]                                                      # an empty list
+    cent = np.ascontiguousarray(conv(rng.standard_normal((nlist, d)).astype(np.float32)))
+    queries = np.ascontiguousarray(conv(rng.standard_normal((q, d)).astype(np.float32)))
+    st = z.Store(dt, metric, sdim)
+    st.append(stored); st.seal()
+    st.ivf_attach(cent, offs)
+    for r in (5, 77, 4000):
+        st.set_deleted(r, True)
+    fb = np.zeros((n + 31) // 32, np.uint32); fb[10:40] = 0x0f0f0f0f
+    ctx = z.Context(st)
+    for max_scan, filt in ((n, None), (2500, fb)):
+        ctx.set_kernel(1)
+        a = ctx.ivf_search(queries, k, nprobe, max_scan, filter_bitmap=filt)
+        assert ctx.last_kernel() == "scan_lists"
+        ctx.set_kernel(0)
+        b = ctx.ivf_search(queries, k, nprobe, max_scan, filter_bitmap=filt)
+        assert ctx.last_kernel() == "scan_lists_lm"
+        assert np.array_equal(a[3], b[3]) and np.array_equal(a[2], b[2]) and np.array_equal(a[0], b[0])
+        assert np.array_equal(a[1].view(np.uint32), b[1].view(np.uint32))
+        assert a[3].max() > 0
+    ctx.close(); st.close()

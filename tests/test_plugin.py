@@ -100,6 +100,27 @@ def test_gpu_searcher_filter_threshold_and_normalized_scores():
     ref.close(); gpu.close()
 
 
+@needs_plugin
+@pytest.mark.gpu
+def test_gpu_searcher_filter_over_many_keys_is_evaluated_by_several_host_threads():
+    """above 256k keys build_filter_bitmap spreads the IndexFilter calls over host threads (whole bitmap words each):
+    same rows dropped, same results as the stock searcher; n is not a multiple of 32 and not of the thread count"""
+    n, d, q, k = 300007, 16, 5, 10
+    x, qs = _tie_free(n, d, 17), _tie_free(q, d, 18)
+    ref = S.RefIndex(x, S.DT_FP32, d, "SquaredEuclidean", "", kind="Flat")
+    gpu = S.RefIndex(x, S.DT_FP32, d, "SquaredEuclidean", "", kind="Flat:GpuFlatSearcher")
+    L = S.ref()
+    try:
+        L.zref_set_filter(7, 3)
+        rk, rs, ri, rc = ref.search(qs, k)
+        gk, gs, gi, gc = gpu.search(qs, k)
+        assert np.array_equal(rc, gc) and np.array_equal(rk, gk) and (gk % 7 != 3).all()
+        assert np.allclose(rs, gs, rtol=1e-4, atol=1e-6)
+    finally:
+        L.zref_set_filter(0, 0)
+    ref.close(); gpu.close()
+
+
 # ---- GpuFlatStreamer: rows arrive between searches (flat_streamer_test.cc:180-212,731-801,1038-1117) ----
 class _Streamer:
     def __init__(self, cls, dtype, dim, metric, path):

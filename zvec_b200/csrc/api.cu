@@ -395,7 +395,7 @@ int zvb200_ctx_destroy(zvb200_ctx *c) {
   c->xkeys.release(); c->gather.release(); c->out_rows.release(); c->h_rows.release();
   DevBuf *d[] = {&c->qin, &c->qf32, &c->qraw, &c->qtails, &c->qnorms, &c->part, &c->out_scores,
                  &c->out_index, &c->filter, &c->misc, &c->gtau, &c->coarse_scores, &c->coarse_index,
-                 &c->seg_prefix, &c->seg_row, &c->seg_count, &c->qsrc, &c->cand, &c->qshadow};
+                 &c->seg_prefix, &c->seg_row, &c->seg_count, &c->seg_list, &c->lm, &c->qsrc, &c->cand, &c->qshadow};
   for (auto b : d) b->release();
   c->h_q.release(); c->h_scores.release(); c->h_index.release();
   if (c->ev_scan0) cudaEventDestroy(c->ev_scan0);
@@ -937,12 +937,33 @@ static int ivf_core(zvb200_ctx *c, const void *queries_dev, uint32_t q, uint32_t
   c->force_kernel = keep;
   if (r != 0) return r;
   // 2. which lists each query scans under the budget (ivf_searcher.cc:216-231)
-  CU(launch_ivf_plan((const uint32_t *)c->coarse_index.p, q, nprobe, s->list_off_dev, s->budget_dev, max_scan_count,
-                     (uint32_t *)c->seg_prefix.p, (uint32_t *)c->seg_row.p, (uint32_t *)c->seg_count.p, c->stream));
-  // 3. posting-list scan, queries already in compute layout (same dtype / metric / dim as the centroids)
   RowsView rv = zvb_view_for(c, s);
+  // batches scan LIST-major: a list probed by several queries of the batch is streamed once for up to 8 of them
+  // (query-major re-reads it per query: C4 at batch 1024 streamed 246 GB per batch out of a 61 GB index)
+  static const uint32_t lm_from = [] { const char *e = getenv("ZVB200_IVF_LM_FROM"); return e ? (uint32_t)atoi(e) : 8u; }();
+  const bool list_major = c->force_kernel != 1 && c->force_kernel != 4 && q >= lm_from && scan_lists_lm_qb(rv, k) > 0 &&
+                          (size_t)q * nprobe * k * sizeof(u64) <= ((size_t)1 << 30);
+  if (list_major) CU(c->seg_list.ensure((size_t)q * nprobe * 4));
+  CU(launch_ivf_plan((const uint32_t *)c->coarse_index.p, q, nprobe, s->list_off_dev, s->budget_dev, max_scan_count,
+                     (uint32_t *)c->seg_prefix.p, (uint32_t *)c->seg_row.p, (uint32_t *)c->seg_count.p, c->stream,
+                     list_major ? (uint32_t *)c->seg_list.p : nullptr));
+  // 3. posting-list scan, queries already in compute layout (same dtype / metric / dim as the centroids)
   SearchParams sp;
   sp.k = k; sp.threshold = threshold; sp.filter = filter_dev;
+  if (list_major) {
+    CU(c->lm.ensure(scan_lists_lm_scratch_words(q, nprobe, s->nlist) * 4));
+    CU(c->part.ensure((size_t)q * nprobe * k * sizeof(u64)));
+    uint32_t nparts = 0;
+    CU(cudaEventRecord(c->ev_scan0, c->stream));
+    c->scan_timed = true;
+    CU(launch_scan_lists_lm(rv, c->last_qv, sp, (const uint32_t *)c->seg_list.p, (const uint32_t *)c->seg_count.p, nprobe,
+                            s->list_off_dev, s->nlist, (uint32_t *)c->lm.p, (u64 *)c->part.p, &nparts, s->sm_count,
+                            c->stream));
+    CU(cudaEventRecord(c->ev_scan1, c->stream));
+    c->last_kernel = "scan_lists_lm";
+    CU(launch_merge_parts((const u64 *)c->part.p, nparts, q, k, out_scores_dev, out_index_dev, nullptr, c->stream));
+    return 0;
+  }
   const bool lists_stream = c->force_kernel == 4 && scan_stream_supports(rv, k, nprobe);
   const size_t parts = lists_stream ? scan_lists_stream_parts(q, s->sm_count) : scan_lists_parts(q, s->sm_count);
   CU(c->part.ensure((size_t)q * parts * k * sizeof(u64)));

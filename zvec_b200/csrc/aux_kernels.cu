@@ -610,7 +610,7 @@ cudaError_t launch_sort_rows(const float *dist, uint32_t q, uint32_t n, uint32_t
 namespace {
 __global__ void ivf_plan_kernel(const uint32_t *coarse_index, uint32_t q, uint32_t nprobe, const uint32_t *list_off,
                                 const uint32_t *budget_sizes, uint64_t max_scan_count, uint32_t *seg_prefix,
-                                uint32_t *seg_row, uint32_t *seg_count) {
+                                uint32_t *seg_row, uint32_t *seg_count, uint32_t *seg_list) {
   // one WARP per query, 32 probes at a time (a single thread walking 64 probes through two dependent global loads
   // each cost 35 us at batch 1 — half of the posting-list scan it prepares)
   const uint32_t qi = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
@@ -656,6 +656,7 @@ __global__ void ivf_plan_kernel(const uint32_t *coarse_index, uint32_t q, uint32
       const uint32_t pos = n + __popc(em & lt);
       row[pos] = b;
       pre[pos + 1] = local + linc;
+      if (seg_list) seg_list[(size_t)qi * nprobe + pos] = cid;
     }
     const uint32_t vis = __ballot_sync(0xffffffffu, visit);
     total += __shfl_sync(0xffffffffu, visit ? inc : 0, vis ? 31 - __clz(vis) : 0);
@@ -669,9 +670,9 @@ __global__ void ivf_plan_kernel(const uint32_t *coarse_index, uint32_t q, uint32
 
 cudaError_t launch_ivf_plan(const uint32_t *coarse_index, uint32_t q, uint32_t nprobe, const uint32_t *list_off,
                             const uint32_t *budget_sizes, uint64_t max_scan_count, uint32_t *seg_prefix,
-                            uint32_t *seg_row, uint32_t *seg_count, cudaStream_t st) {
+                            uint32_t *seg_row, uint32_t *seg_count, cudaStream_t st, uint32_t *seg_list) {
   ivf_plan_kernel<<<(q + 3) / 4, 128, 0, st>>>(coarse_index, q, nprobe, list_off, budget_sizes, max_scan_count,
-                                                  seg_prefix, seg_row, seg_count);
+                                                  seg_prefix, seg_row, seg_count, seg_list);
   count_launch();
   return cudaGetLastError();
 }

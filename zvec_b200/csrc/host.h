@@ -117,7 +117,7 @@ struct zvb200_ctx {
   cudaStream_t stream = nullptr;
   DevBuf qshadow;
   DevBuf qin, qf32, qraw, qtails, qnorms, part, out_scores, out_index, filter, misc, gtau;
-  DevBuf coarse_scores, coarse_index, seg_prefix, seg_row, seg_count;  // IVF
+  DevBuf coarse_scores, coarse_index, seg_prefix, seg_row, seg_count, seg_list, lm;  // IVF
   DevBuf qsrc, cand;  // fp32 queries before the reformer; candidate rows of the refiner
   QueryView last_qv;
   HostBuf h_q, h_scores, h_index;

@@ -121,7 +121,8 @@ cudaError_t launch_sort_rows(const float *dist, uint32_t q, uint32_t n, uint32_t
 // K4: IVF — list selection under the scan budget, then the posting-list scan (grid.y = query)
 cudaError_t launch_ivf_plan(const uint32_t *coarse_index, uint32_t q, uint32_t nprobe, const uint32_t *list_off,
                             const uint32_t *budget_sizes, uint64_t max_scan_count, uint32_t *seg_prefix,
-                            uint32_t *seg_row, uint32_t *seg_count, cudaStream_t st);
+                            uint32_t *seg_row, uint32_t *seg_count, cudaStream_t st,
+                            uint32_t *seg_list = nullptr /* [q][nprobe] list id of every visited segment */);
 cudaError_t launch_scan_lists(const RowsView &rv, const QueryView &qv, const SearchParams &sp,
                               const uint32_t *seg_prefix, const uint32_t *seg_row, const uint32_t *seg_count,
                               uint32_t seg_cap, u64 *part, uint32_t *nparts, int sm_count, cudaStream_t st);
@@ -130,6 +131,14 @@ cudaError_t launch_scan_lists_stream(const RowsView &rv, const QueryView &qv, co
                                      const uint32_t *seg_prefix, const uint32_t *seg_row, const uint32_t *seg_count,
                                      uint32_t seg_cap, u64 *part, uint32_t *nparts, int sm_count, cudaStream_t st);
 size_t scan_lists_stream_parts(uint32_t q, int sm_count);
+// K4b: the same scan LIST-major for query batches (scan_lists_lm.cu): every probed list is streamed once per <= QB of
+// the queries that probe it; part[q][cap][k], one partial list per (query, probe slot)
+int scan_lists_lm_qb(const RowsView &rv, uint32_t k);  // queries per list pass; 0 = unsupported shape
+size_t scan_lists_lm_scratch_words(uint32_t q, uint32_t cap, uint32_t nlist);
+cudaError_t launch_scan_lists_lm(const RowsView &rv, const QueryView &qv, const SearchParams &sp,
+                                 const uint32_t *seg_list, const uint32_t *seg_count, uint32_t cap,
+                                 const uint32_t *list_off, uint32_t nlist, uint32_t *scratch, u64 *part,
+                                 uint32_t *nparts, int sm_count, cudaStream_t st);
 
 // Lanes of a warp that share one stored row in the streaming scans (log2).  Measured on B200
 // (tools/scan_probe.py, 10M rows, batch 1): ~6 sixteen-byte chunks per lane is the sweet spot —

@@ -79,6 +79,8 @@ struct MmaArgs {
   uint32_t pub_j;       // which list entry a CTA publishes (1-based)
   uint32_t pub_m;       // pub_m * pub_j >= k: the pub_m-th smallest published score bounds the global k-th best
   float sh_mrow_max;    // KIND 3: largest row share of the filter margin in the store (bootstrap bound)
+  uint32_t sh_qcap;     // KIND 3: nominated rows a warp queues before it re-scores them together (<= 16)
+  uint32_t sh_kk_last;  // KIND 3: 32-byte K slices of the LAST k-block that hold operand columns (the rest is zero padding)
   int dbg;              // ZVB200_MMA_DEBUG probes (perf triage only): 1 no epilogue, 2 no TMA, 4 A only, 8 B only, 16 no slow path
 };
 
@@ -185,16 +187,22 @@ __device__ __forceinline__ void tmem_ld_wait_on(uint32_t (&v)[32]) {
                : "memory");
 }
 // max of 32 score words as floats, as a depth-5 tree (a running max is a 31-deep dependent chain)
+// (three-input FMNMX3: 16 instructions instead of 31)
+__device__ __forceinline__ float max3f(float a, float b, float c) {
+  float r;
+  asm("max.f32 %0, %1, %2, %3;" : "=f"(r) : "f"(a), "f"(b), "f"(c));
+  return r;
+}
 __device__ __forceinline__ float max32(const uint32_t (&v)[32]) {
-  float m[16];
+  float m[12];
 #pragma unroll
-  for (int i = 0; i < 16; ++i) m[i] = fmaxf(__uint_as_float(v[2 * i]), __uint_as_float(v[2 * i + 1]));
+  for (int i = 0; i < 10; ++i)
+    m[i] = max3f(__uint_as_float(v[3 * i]), __uint_as_float(v[3 * i + 1]), __uint_as_float(v[3 * i + 2]));
+  m[10] = __uint_as_float(v[30]);
+  m[11] = __uint_as_float(v[31]);
 #pragma unroll
-  for (int s = 8; s > 0; s >>= 1) {
-#pragma unroll
-    for (int i = 0; i < s; ++i) m[i] = fmaxf(m[i], m[i + s]);
-  }
-  return m[0];
+  for (int i = 0; i < 4; ++i) m[i] = max3f(m[3 * i], m[3 * i + 1], m[3 * i + 2]);
+  return fmaxf(max3f(m[0], m[1], m[2]), m[3]);
 }
 __device__ __forceinline__ uint32_t tmem_ld1(uint32_t taddr) {  // one column of this warp's 32 lanes, waited for
   uint32_t r;
@@ -413,6 +421,7 @@ scan_mma_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
           const uint64_t da = make_desc_sw128(sa), db = make_desc_sw128(sb);
 #pragma unroll
           for (uint32_t kk = 0; kk < 4; ++kk) {  // four 32-byte K slices per 128-byte k-block
+            if (KIND == 3 && kb + 1 == a.nkb && kk >= a.sh_kk_last) break;  // zero padding: nothing to add
             if (KIND == 0 || KIND == 3) umma_f16(d_tmem, da + 2 * kk, db + 2 * kk, idesc, (kb | kk) != 0);
             else if (KIND == 1) umma_tf32(d_tmem, da + 2 * kk, db + 2 * kk, idesc, (kb | kk) != 0);
             else umma_i8(d_tmem, da + 2 * kk, db + 2 * kk, idesc, (kb | kk) != 0);
@@ -704,6 +713,65 @@ scan_mma_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
       return b != 0xffffffffu;
     };
     uint32_t next_eval = 1;
+    // KIND 3 — nominated rows are QUEUED (row, mask of the lanes that nominated it) and re-scored together: the rows of
+    // a whole queue are staged into shared memory with all their loads in flight at once, then every nominating lane
+    // scores its own query against the staged bytes.  One HBM round trip per queue instead of one per nominated row
+    // (the exact re-score used to cost ~2000 cycles per row, 24 % of the k = 100 epilogue).
+    const uint32_t sh_rowb = a.chunks * 16 + 16;                       // staged bytes per row: the codes + the tail
+    uint8_t *sh_base = reinterpret_cast<uint8_t *>(colc) + (size_t)ew * (128 + (size_t)a.sh_qcap * sh_rowb);
+    uint32_t *sh_qrow = reinterpret_cast<uint32_t *>(sh_base), *sh_qmask = sh_qrow + 16;
+    uint8_t *sh_stage = sh_base + 128;
+    uint32_t sh_qn = 0;                                                 // warp-uniform
+    auto sh_drain = [&]() {
+      if (!SH || sh_qn == 0) return;
+      __syncwarp();
+      const uint32_t P = a.chunks + 1, total = sh_qn * P;
+      uint4 buf[4];
+#pragma unroll
+      for (int r = 0; r < 4; ++r) {
+        const uint32_t item = lane + 32 * r;
+        buf[r] = make_uint4(0, 0, 0, 0);
+        if (item < total) {
+          const uint32_t e = item / P, p = item - e * P, row = sh_qrow[e];
+          buf[r] = p < a.chunks ? __ldg(reinterpret_cast<const uint4 *>(a.rows + (size_t)row * a.row_stride) + p)
+                                : __ldg(reinterpret_cast<const uint4 *>(a.tails + row));
+        }
+      }
+#pragma unroll
+      for (int r = 0; r < 4; ++r) {
+        const uint32_t item = lane + 32 * r;
+        if (item < total) {
+          const uint32_t e = item / P, p = item - e * P;
+          *reinterpret_cast<uint4 *>(sh_stage + (size_t)e * sh_rowb + (size_t)p * 16) = buf[r];
+        }
+      }
+      __syncwarp();
+      const uint4 *qp = reinterpret_cast<const uint4 *>(a.qraw + (size_t)(q0 + slot) * a.row_stride);
+      for (uint32_t e = 0; e < sh_qn; ++e) {
+        const uint32_t row = sh_qrow[e];
+        const bool cand = (sh_qmask[e] >> lane) & 1u;
+        float s = 0.f;
+        if (cand) {
+          const uint4 *rp = reinterpret_cast<const uint4 *>(sh_stage + (size_t)e * sh_rowb);
+          int ip = 0;
+          for (uint32_t c = 0; c < a.chunks; ++c) {
+            const uint4 x = rp[c], y = __ldg(qp + c);
+            ip = __dp4a((int)x.x, (int)y.x, ip); ip = __dp4a((int)x.y, (int)y.y, ip);
+            ip = __dp4a((int)x.z, (int)y.z, ip); ip = __dp4a((int)x.w, (int)y.w, ip);
+          }
+          const float4 mt = *reinterpret_cast<const float4 *>(rp + a.chunks);
+          s = qi8_l2sq((float)ip, mt, qt, dq);
+        }
+        const u64 key = pack_key(s, row);
+        bool p = cand && key < tau_key;
+        if (p && a.drop) p = !bit_set(a.drop, row);
+        if (p && a.filter) p = !bit_set(a.filter, row);
+        if (KR > 0) { if (p) accept(key); }
+        else accept_coop(p, key);
+        __syncwarp();
+      }
+      sh_qn = 0;
+    };
     // the first-tile bootstrap needs every row of that tile to be a live row
     const bool boot = !(KIND == 2 && imode == 7) && a.groups > 1 && pubj <= 8 && !a.drop && !a.filter && ntl > 1 &&
                       a.row_begin + (t_begin + 1) * kBN <= a.row_end && !(a.dbg & (1 | 16 | 32 | 64));
@@ -807,13 +875,30 @@ scan_mma_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
 #pragma unroll
           for (int j = 0; j < 32; ++j) m |= (__uint_as_float(v[j]) >= dthr ? 1u : 0u) << j;
           uint32_t wm = __reduce_or_sync(FULL, m);
-          if (SH) {  // the int8 rows of the nominated columns: start their trips from HBM together
+          if (SH && !a.sh_qcap) {  // (ZVB200_SH_DEFER=0: re-score every nominated row at once, the round-1 path)
             for (uint32_t pm = wm; pm; pm &= pm - 1) {
               const uint32_t prow = row0 + c0 + (__ffs(pm) - 1);
               if (prow < a.row_end && (uint32_t)lane < a.chunks)
                 asm volatile("prefetch.global.L2 [%0];" ::"l"(a.rows + (size_t)prow * a.row_stride + (size_t)lane * 16));
               if (prow < a.row_end && lane == 31) asm volatile("prefetch.global.L2 [%0];" ::"l"(a.tails + prow));
             }
+          }
+          if (SH && a.sh_qcap) {
+            // queue the nominated columns (their rows start their trip from HBM now); sh_drain re-scores them together
+            for (uint32_t pm = wm; pm; pm &= pm - 1) {
+              const int j = __ffs(pm) - 1;
+              const uint32_t prow = row0 + c0 + j;
+              const uint32_t lm = __ballot_sync(FULL, (m >> j) & 1u);
+              if (prow >= a.row_end) continue;  // warp-uniform
+              if ((uint32_t)lane < a.chunks)
+                asm volatile("prefetch.global.L2 [%0];" ::"l"(a.rows + (size_t)prow * a.row_stride + (size_t)lane * 16));
+              if (lane == 31) asm volatile("prefetch.global.L2 [%0];" ::"l"(a.tails + prow));
+              if (lane == 0) { sh_qrow[sh_qn] = prow; sh_qmask[sh_qn] = lm; }
+              if (prof) ++n_ev;
+              if (++sh_qn == a.sh_qcap) sh_drain();
+            }
+            if (prof) c_slow += clock64() - c0s;
+            return;
           }
           while (wm) {
             const int j = __ffs(wm) - 1;
@@ -923,6 +1008,11 @@ scan_mma_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
       __syncwarp();
       if (lane == 0) mbar_arrive(bar_tempty + 8 * as);
       if ((resc || ic4) && lane == 0) mbar_arrive(bar_cempty + 8 * cb);  // (after the __syncwarp above)
+      if (SH && (2 * sh_qn >= a.sh_qcap || t + 1 == ntl)) {  // off the MMA's critical path, like the union bound below
+        const long long c0d = prof ? clock64() : 0;
+        sh_drain();
+        if (prof) c_ex += clock64() - c0d;
+      }
       // off the MMA's critical path: refresh the union bound at tiles 1,2,3,4,6,9,13,19,... of this CTA
       if (a.groups > 1 && t + 1 == next_eval && !(a.dbg & 32)) {
         const long long c0u = prof ? clock64() : 0;
@@ -1011,8 +1101,14 @@ static bool use_shadow(const RowsView &rv) {
   return !off && rv.dtype == ZVB200_DT_INT8 && rv.metric == ZVB200_METRIC_QI8_L2SQ && rv.shadow && rv.tails;
 }
 
+// KIND 3: nominated rows a warp queues (and stages: codes + tail) before re-scoring them together
+static uint32_t shadow_qcap(const RowsView &rv) {
+  const uint32_t rowb = rv.chunks * 16 + 16;
+  return std::max(1u, std::min(16u, 2048u / rowb));
+}
+
 static size_t colc_bytes_for(const RowsView &rv, bool shadow = false) {
-  if (shadow) return 0;
+  if (shadow) return 4 * (128 + (size_t)shadow_qcap(rv) * (rv.chunks * 16 + 16));  // per epilogue warp: queue + staged rows
   if (rv.dtype == ZVB200_DT_INT8) return 2 * kBN * sizeof(float4);
   const bool direct = rv.dtype == ZVB200_DT_FP16 && !metric_is_l2(rv.metric);
   return direct ? 0 : 4 * kBN * sizeof(float);  // ring of 4 tiles
@@ -1073,6 +1169,14 @@ cudaError_t launch_scan_mma(const RowsView &rv, const QueryView &qv, const Searc
   // (2x headroom on the accumulation term: the tensor core's internal alignment of partial sums is not IEEE)
   a.eps = (float)rv.d * 4.8e-7f + (f32 ? 2.2e-3f : 0.f);
   a.sh_mrow_max = rv.shadow_mrow_max;
+  {
+    static const bool defer = [] { const char *e = getenv("ZVB200_SH_DEFER"); return !e || atoi(e) != 0; }();
+    a.sh_qcap = defer ? shadow_qcap(rv) : 0;
+  }
+  {  // operand columns of the last k-block: d + 9 of shadow_k, in 16-half (32-byte) MMA slices
+    const uint32_t used = rv.d + 9, last = used - std::min(used, (rv.shadow_k / 64 - 1) * 64);
+    a.sh_kk_last = sh ? std::max(1u, std::min(4u, (last + 15) / 16)) : 4;
+  }
   a.threshold = sp.threshold;
   a.query_first = rv.query_first;
   a.drop = rv.drop; a.filter = sp.filter;
