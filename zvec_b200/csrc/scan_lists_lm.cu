@@ -22,10 +22,11 @@ namespace zvb {
 
 namespace {
 
-constexpr int kThreads = 256;
+// 16 warps of 4 row groups each: the same 64 rows in flight per CTA as 8 warps x 8, but twice the warps to hide the
+// LDG / LDS / FFMA latencies behind (8 warps: issue slots 28 % busy, 16.1 ms per C4 batch)
+constexpr int kThreads = 512;
 constexpr int kWarps = kThreads / 32;
-constexpr int kU = 8;
-constexpr uint32_t kPfDist = 4;  // L2 prefetch distance, in iterations of a warp's chunk loop
+constexpr int kU = 4;
 
 struct LmArgs {
   RowsView rv;
@@ -42,6 +43,7 @@ struct LmArgs {
   u64 *part;                  // [q][nslots][k]
   uint32_t nslots;
   int lpr_log2;
+  uint32_t pf_dist;           // L2 prefetch distance, in iterations of a warp's chunk loop (0 = none)
 };
 
 // One (warp, query) top-k list lives entirely in shared memory: {cnt | qn << 32, flip} then list / alt / queue of
@@ -214,8 +216,8 @@ __device__ __forceinline__ void lm_scan_item(const LmArgs &a, const LmItem &it, 
       uint4 v[kU];
 #pragma unroll
       for (int u = 0; u < kU; ++u) v[u] = ldg_stream(rp[u] + (size_t)c * 16);
-      if ((l & 7) == 0) {
-        const uint32_t pc = c + kPfDist * lpr;
+      if (a.pf_dist && (l & 7) == 0) {
+        const uint32_t pc = c + a.pf_dist * lpr;
         if (pc < C) {
 #pragma unroll
           for (int u = 0; u < kU; ++u) asm volatile("prefetch.global.L2 [%0];" ::"l"(rp[u] + (size_t)pc * 16));
@@ -515,6 +517,10 @@ cudaError_t launch_scan_lists_lm(const RowsView &rv, const QueryView &qv, const 
   a.item_list = item_list; a.item_first = item_first; a.item_n = item_n; a.n_items = n_items; a.counter = counter;
   a.part = part; a.nslots = cap; a.gtau = gtau;
   a.lpr_log2 = pick_lpr_log2(rv.chunks);
+  {
+    static const uint32_t pf = [] { const char *e = getenv("ZVB200_LM_PF"); return e ? (uint32_t)atoi(e) : 4u; }();
+    a.pf_dist = pf;
+  }
   *nparts = cap;
   const size_t smem = lm_smem(rv.dtype, rv.chunks, qb, sp.k);
   const int grid = sm_count;
