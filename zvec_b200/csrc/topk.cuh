@@ -71,10 +71,13 @@ struct WarpTopk {
       if (np < k) alt[np] = e;
     }
     if (lane < m) {
-      int lo = 0, hi = cnt;  // number of list entries < v
+      // number of list entries <= v.  Keys are unique per row, so '<=' only matters when a caller lists a row twice
+      // (zvb200_search_rows scores it twice, like FlatStreamer::search_bf_by_p_keys_impl): the list's copy goes first,
+      // the chunk's copy right behind it — with '<' both landed in one slot and the next slot kept a stale key
+      int lo = 0, hi = cnt;
       while (lo < hi) {
         int mid = (lo + hi) >> 1;
-        if (list[mid] < v) lo = mid + 1; else hi = mid;
+        if (list[mid] <= v) lo = mid + 1; else hi = mid;
       }
       int np = lane + lo;
       if (np < k) alt[np] = v;
