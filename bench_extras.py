@@ -283,7 +283,11 @@ def c4(args, z, torch, dev, pk, compare_topk, merge_candidates, log):
     vis = torch.topk(cs_all, nprobe, dim=1, largest=False).indices[:, :lists_scanned]
     uniq_lists = int(torch.unique(vis).numel())
     del cs_all, vis
-    for b, reps in ((1, 200), (1024, 5)):
+    import os as _os
+    shapes = ((1, 200), (1024, 5))
+    if _os.environ.get("ZVB200_C4_BATCHES"):       # probes: "1:20" = batch 1, 20 repetitions
+        shapes = tuple(tuple(int(v) for v in s.split(":")) for s in _os.environ["ZVB200_C4_BATCHES"].split(","))
+    for b, reps in shapes:
         f = lambda: ctx.ivf_search_device(dq.data_ptr(), b, k, nprobe, max_scan, os_.data_ptr(), oi.data_ptr())
         t = _dev_time(torch, stream, f, reps)
         sm = _scan_ms(ctx, f, 3)

@@ -976,7 +976,9 @@ static int ivf_core(zvb200_ctx *c, const void *queries_dev, uint32_t q, uint32_t
                                 c->stream));
   else
     CU(launch_scan_lists(rv, c->last_qv, sp, (const uint32_t *)c->seg_prefix.p, (const uint32_t *)c->seg_row.p,
-                         (const uint32_t *)c->seg_count.p, nprobe, (u64 *)c->part.p, &nparts, s->sm_count, c->stream));
+                         (const uint32_t *)c->seg_count.p, nprobe, (u64 *)c->part.p, &nparts, s->sm_count, c->stream,
+                         // what one query scans: the budget plus, on average, half of the list that crosses it
+                         std::min<uint64_t>(s->n, max_scan_count + s->n / std::max<uint32_t>(1, s->nlist) / 2)));
   CU(cudaEventRecord(c->ev_scan1, c->stream));
   c->last_kernel = lists_stream ? "scan_lists_stream" : "scan_lists";
   CU(launch_merge_parts((const u64 *)c->part.p, nparts, q, k, out_scores_dev, out_index_dev, nullptr, c->stream));

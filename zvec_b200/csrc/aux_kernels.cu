@@ -271,6 +271,116 @@ __global__ void __launch_bounds__(kMergeWarps * 32) merge_parts_kernel(
   }
 }
 
+// K5a', few queries with MANY partial keys (one query's IVF coarse search leaves 256 lists x 64 keys; the two-pass
+// merge above took 28 us of a 160-us call): one CTA per query finds the k-th smallest key by radix select — six
+// 11-bit digits of the u64 key, each thread's keys held in registers across the passes — compacts the keys at or
+// below it and sorts those k.  Same result as merge_parts_kernel: ascending by (score, row), padding last.
+constexpr int kSelPerThread = 16;  // keys a thread keeps in registers
+constexpr int kSelMaxThreads = 1024;  // up to 16384 keys per query
+
+template <int NT>
+__global__ void __launch_bounds__(NT) merge_select_kernel(const u64 *part, uint32_t total, uint32_t k,
+                                                          float *out_scores, uint32_t *out_index, u64 *out_keys) {
+  constexpr int BPT = 2048 / NT;  // histogram bins per thread in the scan
+  __shared__ uint32_t hist[2048];
+  __shared__ uint32_t wsum[32];
+  __shared__ uint32_t s_bin, s_need, s_all, s_cnt;
+  __shared__ u64 sel[1024];
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const u64 *keys = part + (size_t)blockIdx.x * total;
+  u64 mine[kSelPerThread];
+#pragma unroll
+  for (int i = 0; i < kSelPerThread; ++i) {
+    const uint32_t idx = tid + i * NT;
+    mine[i] = idx < total ? keys[idx] : kMaxKey;
+  }
+  // the k-th smallest key, digit by digit from the top; stops as soon as the digit's bin is needed WHOLE (with
+  // distinct scores that is after the 33 score bits at the latest: three passes, not six)
+  u64 prefix = 0;
+  uint32_t need = k;
+  int sel_shift = 0;  // the result = the keys whose bits above sel_shift are <= prefix's
+  for (int shift = 53; shift >= -2; shift -= 11) {
+    const int sh = shift < 0 ? 0 : shift;
+    const int bits = shift < 0 ? 9 : 11;  // 64 = 5 * 11 + 9
+    const u64 himask = bits + sh >= 64 ? 0ull : ~0ull << (bits + sh);
+    for (int b = tid; b < 2048; b += NT) hist[b] = 0;
+    __syncthreads();
+#pragma unroll
+    for (int i = 0; i < kSelPerThread; ++i)
+      if ((mine[i] & himask) == prefix) atomicAdd(&hist[(uint32_t)(mine[i] >> sh) & ((1u << bits) - 1u)], 1u);
+    __syncthreads();
+    uint32_t h[BPT], x = 0;
+#pragma unroll
+    for (int b = 0; b < BPT; ++b) { h[b] = hist[BPT * tid + b]; x += h[b]; }
+    const uint32_t own = x;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const uint32_t y = __shfl_up_sync(0xffffffffu, x, o);
+      if (lane >= o) x += y;
+    }
+    if (lane == 31) wsum[warp] = x;
+    __syncthreads();
+    if (warp == 0) {
+      uint32_t w = lane < NT / 32 ? wsum[lane] : 0u;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const uint32_t y = __shfl_up_sync(0xffffffffu, w, o);
+        if (lane >= o) w += y;
+      }
+      wsum[lane] = w;
+    }
+    __syncthreads();
+    uint32_t before = (warp ? wsum[warp - 1] : 0u) + x - own;  // keys in the bins below this thread's
+#pragma unroll
+    for (int b = 0; b < BPT; ++b) {
+      if (before < need && need <= before + h[b]) { s_bin = BPT * tid + b; s_need = need - before; s_all = h[b]; }
+      before += h[b];
+    }
+    __syncthreads();
+    prefix |= (u64)s_bin << sh;
+    need = s_need;
+    sel_shift = sh;
+    const bool whole = s_all == s_need;
+    __syncthreads();
+    if (whole) break;
+  }
+  // need == the bin's size now (the loop ends that way at the last digit too, where the bin is one key value)
+  if (tid == 0) s_cnt = 0;
+  __syncthreads();
+  const u64 lim = prefix >> sel_shift;
+#pragma unroll
+  for (int i = 0; i < kSelPerThread; ++i)
+    if ((mine[i] >> sel_shift) <= lim) {
+      const uint32_t pos = atomicAdd(&s_cnt, 1u);
+      if (pos < 1024) sel[pos] = mine[i];
+    }
+  __syncthreads();
+  // copies of one key beyond the k-th (a candidate row listed more than twice over): the sort drops the surplus
+  const uint32_t got = min(s_cnt, 1024u);
+  uint32_t p2 = 1;
+  while (p2 < max(got, k)) p2 <<= 1;
+  for (uint32_t i = got + tid; i < p2; i += NT) sel[i] = kMaxKey;
+  __syncthreads();
+  for (uint32_t size = 2; size <= p2; size <<= 1) {
+    for (uint32_t stride = size >> 1; stride > 0; stride >>= 1) {
+      for (uint32_t t = tid; t < (p2 >> 1); t += NT) {
+        const uint32_t lo = 2 * t - (t & (stride - 1)), hi = lo + stride;
+        const bool up = (lo & size) == 0;
+        const u64 a = sel[lo], b = sel[hi];
+        if ((a > b) == up) { sel[lo] = b; sel[hi] = a; }
+      }
+      __syncthreads();
+    }
+  }
+  for (uint32_t i = tid; i < k; i += NT) {
+    const u64 e = sel[i];
+    const bool ok = e != kMaxKey;
+    if (out_scores) out_scores[(size_t)blockIdx.x * k + i] = ok ? unorder_f32((uint32_t)(e >> 32)) : CUDART_NAN_F;
+    if (out_index) out_index[(size_t)blockIdx.x * k + i] = ok ? (uint32_t)e : ZVB200_INVALID_INDEX;
+    if (out_keys) out_keys[(size_t)blockIdx.x * k + i] = e;
+  }
+}
+
 // ---- K5b: G sorted shard lists -> one list by (score, global row) ---------------------
 // Replaces concat + std::sort + resize(topk) of CombinedVectorColumnIndexer::Search
 // (combined_vector_column_indexer.cc:167-222).  Rank-based: candidate (g,i) lands at
@@ -445,8 +555,12 @@ cudaError_t launch_prep_queries(const RowsView &rv, const void *queries_dev, uin
                                 uint32_t elem_bytes, float *qf32, uint8_t *qraw, float4 *qtails,
                                 float *qnorms, cudaStream_t st) {
   if (q == 0) return cudaSuccess;
-  prep_queries_kernel<<<q, 128, 0, st>>>(rv, (const uint8_t *)queries_dev, elem_bytes, qf32, qraw,
-                                        qtails, qnorms);
+  // one element per thread and pass: a query of 1536 floats on 128 threads was 12 dependent load round trips (7.5 us
+  // of a 140-us IVF call at batch 1)
+  const uint32_t elems = rv.dtype == ZVB200_DT_INT8 ? rv.row_stride : rv.chunks * 16 / (rv.dtype == ZVB200_DT_FP32 ? 4 : 2);
+  const unsigned threads = elems > 512 ? 1024 : elems > 128 ? 512 : 128;
+  prep_queries_kernel<<<q, threads, 0, st>>>(rv, (const uint8_t *)queries_dev, elem_bytes, qf32, qraw,
+                                            qtails, qnorms);
   count_launch();
   return cudaGetLastError();
 }
@@ -506,6 +620,21 @@ cudaError_t launch_merge_parts(const u64 *part, uint32_t nparts, uint32_t q, uin
     if (e != cudaSuccess) return e;
   }
   u64 *p = const_cast<u64 *>(part);  // the sliced pass reuses the scratch lists in place
+  // few queries, up to 16384 keys each: radix select + sort of the k survivors, one CTA per query
+  {
+    static const bool off = [] { const char *e = getenv("ZVB200_MERGE_SELECT"); return e && atoi(e) == 0; }();
+    const size_t total = (size_t)nparts * k;
+    if (!off && q <= 64 && k <= 1024 && total >= 1024 && total <= (size_t)kSelMaxThreads * kSelPerThread) {
+      if (total <= 256 * kSelPerThread)
+        merge_select_kernel<256><<<q, 256, 0, st>>>(part, (uint32_t)total, k, out_scores, out_index, out_keys);
+      else if (total <= 512 * kSelPerThread)
+        merge_select_kernel<512><<<q, 512, 0, st>>>(part, (uint32_t)total, k, out_scores, out_index, out_keys);
+      else
+        merge_select_kernel<1024><<<q, 1024, 0, st>>>(part, (uint32_t)total, k, out_scores, out_index, out_keys);
+      count_launch();
+      return cudaGetLastError();
+    }
+  }
   // few queries, many keys each: slices of the lists first (grid.y), then one list per slice
   if ((size_t)nparts * k >= 4096 && q <= 64 && nparts >= 32) {
     const uint32_t per_cta = 16, slices = (nparts + per_cta - 1) / per_cta;

@@ -125,7 +125,8 @@ cudaError_t launch_ivf_plan(const uint32_t *coarse_index, uint32_t q, uint32_t n
                             uint32_t *seg_list = nullptr /* [q][nprobe] list id of every visited segment */);
 cudaError_t launch_scan_lists(const RowsView &rv, const QueryView &qv, const SearchParams &sp,
                               const uint32_t *seg_prefix, const uint32_t *seg_row, const uint32_t *seg_count,
-                              uint32_t seg_cap, u64 *part, uint32_t *nparts, int sm_count, cudaStream_t st);
+                              uint32_t seg_cap, u64 *part, uint32_t *nparts, int sm_count, cudaStream_t st,
+                              uint64_t rows_hint = 0 /* rows one query scans, if the caller knows: picks the tile size */);
 size_t scan_lists_parts(uint32_t q, int sm_count);
 cudaError_t launch_scan_lists_stream(const RowsView &rv, const QueryView &qv, const SearchParams &sp,
                                      const uint32_t *seg_prefix, const uint32_t *seg_row, const uint32_t *seg_count,

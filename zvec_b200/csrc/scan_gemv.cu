@@ -20,7 +20,7 @@ namespace {
 
 constexpr int kThreads = 256;
 constexpr int kWarps = kThreads / 32;
-constexpr int kU = 8;  // row groups in flight per warp (memory-level parallelism)
+constexpr int kUmax = 8;  // row groups in flight per warp (memory-level parallelism); the kernels' default
 
 struct GemvArgs {
   RowsView rv;
@@ -41,7 +41,7 @@ struct GemvArgs {
 };
 
 
-template <int DT, bool L2, int QB, bool SEG>
+template <int DT, bool L2, int QB, bool SEG, int kU = kUmax>
 __global__ void __launch_bounds__(kThreads, QB == 1 ? 2 : 1) scan_gemv_kernel(const GemvArgs a) {
   typedef Chunk<DT, L2> CK;
   typedef typename CK::Acc Acc;
@@ -223,9 +223,9 @@ __global__ void __launch_bounds__(kThreads, QB == 1 ? 2 : 1) scan_gemv_kernel(co
   }
 }
 
-template <int DT, bool L2, int QB, bool SEG = false>
+template <int DT, bool L2, int QB, bool SEG = false, int KU = kUmax>
 cudaError_t launch_one(const GemvArgs &a, int grid, size_t smem, cudaStream_t st, int grid_y = 1) {
-  auto kern = scan_gemv_kernel<DT, L2, QB, SEG>;
+  auto kern = scan_gemv_kernel<DT, L2, QB, SEG, KU>;
   cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kMaxDynSmem);
   if (e == cudaSuccess && smem > (size_t)kMaxDynSmem) e = cudaErrorInvalidValue;
   if (e != cudaSuccess) return e;
@@ -262,7 +262,7 @@ cudaError_t launch_scan_gemv(const RowsView &rv, const QueryView &qv, const Sear
   a.row_begin = row_begin; a.row_end = row_end; a.part = part;
   const int lg = pick_lpr_log2(rv.chunks);
   a.lpr_log2 = lg;
-  const uint64_t rows_per_tile = (uint64_t)kU * (32 >> lg) * kWarps;
+  const uint64_t rows_per_tile = (uint64_t)kUmax * (32 >> lg) * kWarps;
   const uint64_t nrows = row_end > row_begin ? row_end - row_begin : 0;
   uint64_t ntiles = (nrows + rows_per_tile - 1) / rows_per_tile;
   int grid = (int)std::min<uint64_t>(std::max<uint64_t>(ntiles, 1), (uint64_t)sm_count * 2);
@@ -303,9 +303,35 @@ size_t scan_lists_parts(uint32_t q, int sm_count) {
   return std::max<uint32_t>(1, std::min<uint32_t>((target + q - 1) / q, (uint32_t)sm_count * 2));
 }
 
+// Row groups per warp step for a SHORT scan: the CTAs walk ceil(rows / (KU * R * 8)) tiles round-robin, so the scan
+// lasts rounds * KU row-times; 39 063 rows of C4 over 296 CTAs are 2.06 rounds of 64-row tiles (3 rounds: 24) but
+// 2.77 rounds of 48-row tiles (3 rounds: 18).
+static int pick_ku(uint64_t rows_hint, int lpr_log2, int grid) {
+  if (rows_hint == 0) return kUmax;
+  int best = kUmax;
+  uint64_t best_cost = ~0ull;
+  for (int ku : {8, 6, 4}) {
+    const uint64_t tile = (uint64_t)ku * (32 >> lpr_log2) * kWarps;
+    const uint64_t rounds = ((rows_hint + tile - 1) / tile + grid - 1) / grid;
+    const uint64_t cost = rounds * ku * 16 + (8 - ku);  // ties go to the deeper pipeline
+    if (cost < best_cost) { best_cost = cost; best = ku; }
+  }
+  return best;
+}
+
+template <int DT, bool L2>
+static cudaError_t launch_lists_ku(const GemvArgs &a, int ku, int grid, size_t smem, cudaStream_t st, int gy) {
+  switch (ku) {
+    case 4: return launch_one<DT, L2, 1, true, 4>(a, grid, smem, st, gy);
+    case 6: return launch_one<DT, L2, 1, true, 6>(a, grid, smem, st, gy);
+    default: return launch_one<DT, L2, 1, true, 8>(a, grid, smem, st, gy);
+  }
+}
+
 cudaError_t launch_scan_lists(const RowsView &rv, const QueryView &qv, const SearchParams &sp,
                               const uint32_t *seg_prefix, const uint32_t *seg_row, const uint32_t *seg_count,
-                              uint32_t seg_cap, u64 *part, uint32_t *nparts, int sm_count, cudaStream_t st) {
+                              uint32_t seg_cap, u64 *part, uint32_t *nparts, int sm_count, cudaStream_t st,
+                              uint64_t rows_hint) {
   GemvArgs a;
   a.rv = rv; a.qv = qv; a.k = sp.k; a.threshold = sp.threshold; a.filter = sp.filter;
   a.row_begin = 0; a.row_end = rv.n; a.part = part; a.q0 = 0;
@@ -314,6 +340,7 @@ cudaError_t launch_scan_lists(const RowsView &rv, const QueryView &qv, const Sea
   const int grid = (int)scan_lists_parts(qv.q, sm_count);
   a.nparts = grid;
   *nparts = grid;
+  const int ku = pick_ku(rows_hint, a.lpr_log2, grid);
   const size_t smem = gemv_smem(rv.dtype, rv.chunks, 1, sp.k, seg_cap);
   if (smem > 220 * 1024) return cudaErrorInvalidValue;
   const bool l2 = metric_is_l2(rv.metric);
@@ -323,14 +350,14 @@ cudaError_t launch_scan_lists(const RowsView &rv, const QueryView &qv, const Sea
     const int gy = (int)std::min<uint32_t>(ymax, qv.q - q0);
     cudaError_t e;
     if (rv.dtype == ZVB200_DT_FP32)
-      e = l2 ? launch_one<ZVB200_DT_FP32, true, 1, true>(a, grid, smem, st, gy)
-             : launch_one<ZVB200_DT_FP32, false, 1, true>(a, grid, smem, st, gy);
+      e = l2 ? launch_lists_ku<ZVB200_DT_FP32, true>(a, ku, grid, smem, st, gy)
+             : launch_lists_ku<ZVB200_DT_FP32, false>(a, ku, grid, smem, st, gy);
     else if (rv.dtype == ZVB200_DT_FP16)
-      e = l2 ? launch_one<ZVB200_DT_FP16, true, 1, true>(a, grid, smem, st, gy)
-             : launch_one<ZVB200_DT_FP16, false, 1, true>(a, grid, smem, st, gy);
+      e = l2 ? launch_lists_ku<ZVB200_DT_FP16, true>(a, ku, grid, smem, st, gy)
+             : launch_lists_ku<ZVB200_DT_FP16, false>(a, ku, grid, smem, st, gy);
     else
-      e = l2 ? launch_one<ZVB200_DT_INT8, true, 1, true>(a, grid, smem, st, gy)
-             : launch_one<ZVB200_DT_INT8, false, 1, true>(a, grid, smem, st, gy);
+      e = l2 ? launch_lists_ku<ZVB200_DT_INT8, true>(a, ku, grid, smem, st, gy)
+             : launch_lists_ku<ZVB200_DT_INT8, false>(a, ku, grid, smem, st, gy);
     if (e != cudaSuccess) return e;
   }
   return cudaSuccess;
