@@ -458,7 +458,8 @@ int zvb200_ctx_last_mma_kind(const zvb200_ctx *c) { return c ? c->last_mma_kind 
 // ======================================================================================
 
 // queries (stored layout, device) -> compute layout in the context's buffers
-static int prep_core(zvb200_ctx *c, zvb200_store *s, const void *queries_dev, uint32_t q, QueryView *out) {
+static int prep_core(zvb200_ctx *c, zvb200_store *s, const void *queries_dev, uint32_t q, QueryView *out,
+                     bool pad_tile = true /* zero rows up to a whole 128-query tile: only the tensor-core scan reads them */) {
   RowsView rv = s->view();
   const uint32_t esz = s->dtype == ZVB200_DT_FP32 ? 4 : s->dtype == ZVB200_DT_FP16 ? 2 : 1;
   const size_t qf32_row = (size_t)(s->chunks * 16 / esz) * 4;
@@ -471,9 +472,9 @@ static int prep_core(zvb200_ctx *c, zvb200_store *s, const void *queries_dev, ui
   CU(c->qraw.ensure(qraw_bytes));
   CU(c->qtails.ensure((size_t)q * sizeof(float4)));
   CU(c->qnorms.ensure((size_t)q * sizeof(float)));
-  if (qraw_bytes && qpad > q)
+  if (pad_tile && qraw_bytes && qpad > q)
     CU(cudaMemsetAsync((uint8_t *)c->qraw.p + (size_t)q * s->row_stride, 0, (size_t)(qpad - q) * s->row_stride, c->stream));
-  if (s->dtype == ZVB200_DT_FP32 && qpad > q)
+  if (pad_tile && s->dtype == ZVB200_DT_FP32 && qpad > q)
     CU(cudaMemsetAsync((uint8_t *)c->qf32.p + (size_t)q * qf32_row, 0, (size_t)(qpad - q) * qf32_row, c->stream));
   CU(launch_prep_queries(rv, queries_dev, q, s->elem_bytes, (float *)c->qf32.p, (uint8_t *)c->qraw.p,
                          (float4 *)c->qtails.p, (float *)c->qnorms.p, c->stream));
@@ -483,13 +484,13 @@ static int prep_core(zvb200_ctx *c, zvb200_store *s, const void *queries_dev, ui
   if (rv.shadow) {
     const size_t srow = (size_t)rv.shadow_k * 2;
     CU(c->qshadow.ensure((size_t)qpad * srow));
-    if (qpad > q) CU(cudaMemsetAsync((uint8_t *)c->qshadow.p + (size_t)q * srow, 0, (size_t)(qpad - q) * srow, c->stream));
+    if (pad_tile && qpad > q) CU(cudaMemsetAsync((uint8_t *)c->qshadow.p + (size_t)q * srow, 0, (size_t)(qpad - q) * srow, c->stream));
     CU(launch_qi8_shadow_queries(rv, (const uint8_t *)c->qraw.p, (const float4 *)c->qtails.p, q, (uint8_t *)c->qshadow.p,
                                  rv.shadow_k, c->stream));
     qv.qshadow = (const uint8_t *)c->qshadow.p;
   }
   qv.q = q;
-  qv.qpad_rows = true;
+  qv.qpad_rows = pad_tile;
   c->last_qv = qv;  // the IVF list scan reuses the prepared queries
   *out = qv;
   return 0;
@@ -501,11 +502,6 @@ int zvb_search_core(zvb200_ctx *c, zvb200_store *s, const void *queries_dev, uin
                     uint32_t *out_index_dev, u64 *out_keys_dev, uint64_t row_begin, uint64_t row_end) {
   RowsView rv = zvb_view_for(c, s);
   const uint32_t esz = s->dtype == ZVB200_DT_FP32 ? 4 : s->dtype == ZVB200_DT_FP16 ? 2 : 1;
-  QueryView qv;
-  {
-    const int r = prep_core(c, s, queries_dev, q, &qv);
-    if (r != 0) return r;
-  }
   SearchParams sp;
   sp.k = k; sp.threshold = threshold; sp.filter = filter_dev;
 
@@ -527,6 +523,11 @@ int zvb_search_core(zvb200_ctx *c, zvb200_store *s, const void *queries_dev, uin
   if (which == 4 && !stream_ok) which = 1;
   if (which == 3 && !mma_ok) return set_err(ZVB200_ERR_UNSUPPORTED, "tcgen05 scan: fp16 / fp32 stores, k <= 128 only");
   if (which == 2 && !scan_tile_supports(k)) which = 1;
+  QueryView qv;
+  {  // queries -> compute layout; only the tensor-core scan needs them padded to a whole tile
+    const int r = prep_core(c, s, queries_dev, q, &qv, which == 3);
+    if (r != 0) return r;
+  }
   const size_t maxparts = which == 1 ? scan_gemv_max_parts(s->sm_count)
                           : which == 2 ? scan_tile_max_parts(s->sm_count)
                           : which == 3 ? scan_mma_max_parts(s->sm_count) : scan_stream_max_parts(s->sm_count);
