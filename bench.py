@@ -598,7 +598,9 @@ def run_ours(args):
                                "d2h_bytes_per_step": k * (8 if world == 1 else 12)},
                        "roofline": {"bound": "hbm", "achieved": gbs1, "peak": pk["hbm_gbs"], "unit": "GB/s",
                                     "frac": gbs1 / pk["hbm_gbs"], "traffic": traffic(kernel_1, 1), "kernel": kernel_1,
-                                    "kernel_ms": scan_1, "peak_source": pk["source"],
+                                    "kernel_ms": scan_1, "peak_source": pk["source"] + (
+                                        "; above 1: that peak is a COPY measurement (read + write), a read-only stream goes faster"
+                                        if gbs1 > pk["hbm_gbs"] else ""),
                                     "algorithmic": "rows*dim*2 B per launch = %.4g" % shard_bytes}},
         }
     # ---- the other BASELINE configs, driver-measured (1 GPU): C5 reuses the C2 store as its first field

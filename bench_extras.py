@@ -51,6 +51,9 @@ def _roof(bound, achieved, peak, unit, kernel, kernel_ms, algorithmic, note=None
          "kernel": kernel, "kernel_ms": kernel_ms, "algorithmic": algorithmic}
     if note:
         r["note"] = note
+    if bound == "hbm" and achieved > peak:
+        r["note"] = (r.get("note", "") + "; " if note else "") + ("above 1: the peak is a COPY measurement (read + write, "
+                     "MEASURED_PEAKS.json how), a read-only stream goes faster")
     return r
 
 
