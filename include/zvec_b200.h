@@ -257,6 +257,25 @@ int zvb200_fuse_weighted(zvb200_ctx *c, const uint64_t *keys, const float *score
  * belong to list l.  centroids: nlist elements of the store's dtype/metric layout, HOST. */
 int zvb200_ivf_attach(zvb200_store *s, const void *centroids, uint32_t nlist,
                       const uint64_t *list_offsets);
+/* Posting lists an IVFBuilder quantised (proxima.ivf.builder.quantizer_class = Int8QuantizerConverter,
+ * ivf_builder.cc:738-800): the lists are int8 rows while the centroid index keeps its own layout (fp32 rows, for
+ * InnerProduct in the Mips-converted space of one more dimension block, ivf_centroid_index.cc:338-384).
+ * zvb200_ivf_attach_typed = zvb200_ivf_attach with the centroids' own (dtype, metric, dim).  Such a store is searched
+ * with zvb200_ivf_search_split: coarse_queries in the centroids' layout (what IVFCentroidIndex::search hands its
+ * searcher after reformer_->transform, ivf_centroid_index.cc:273-295), list_queries in the lists' layout (what
+ * IVFEntity::transform returns, ivf_searcher.cc:211-214); everything else as zvb200_ivf_search. */
+int zvb200_ivf_attach_typed(zvb200_store *s, const void *centroids, uint32_t nlist, const uint64_t *list_offsets,
+                            int c_dtype, int c_metric, uint32_t c_dim);
+int zvb200_ivf_search_split(zvb200_ctx *c, const void *coarse_queries, const void *list_queries, uint32_t q, uint32_t k,
+                            uint32_t nprobe, uint64_t max_scan_count, float threshold, const uint32_t *filter_bitmap,
+                            uint64_t *out_keys, float *out_scores, uint32_t *out_index, uint32_t *out_counts);
+/* Scores leave the scan multiplied by a constant — `distances[k] * norm_val` of IVFEntity::search
+ * (ivf_entity.cc:601,650,675,715): norm_val is the quantiser's global 1/scale (IVFEntity::load, ivf_entity.cc:541-564) or
+ * the scale of the row's posting list (quantize_by_centroid, IVFEntity::inverted_list_normalize_value, ivf_entity.h:
+ * 204-224).  list_scales: nlist values, HOST, needs an attached IVF structure (NULL: `scale` for every row; 1 = off).
+ * The product is what the threshold gates and the top-k compares, as in the reference's heap.  A scaled store is
+ * scanned by the CUDA-core kernels (GEMV scan, posting-list scans) at any batch.  zvb200_ivf_attach* drops list scales. */
+int zvb200_store_set_score_scale(zvb200_store *s, float scale, const float *list_scales);
 /* Sharded IVF (each GPU holds a slice of EVERY posting list): list_sizes[l] = rows of list l in the
  * whole index.  The scan budget of zvb200_ivf_search then counts these, so every shard visits exactly the lists
  * the unsharded index would (IVFSearcher::search_impl's loop header, ivf_searcher.cc:216-219).  NULL = unsharded. */

@@ -902,14 +902,18 @@ class GpuIVFSearcher : public IndexSearcher {
     magic_ = IndexContext::GenerateMagic();
     rc = entity_.load(cntr);
     if (rc != 0) return rc;
-    // scores of the integer-quantised variants carry per-list / global scales (IVFEntity::load,
-    // ivf_entity.cc:541-564; IVFReformerWrapper::normalize :325-353): the device store has no per-list scale
-    const std::string &rf = meta_.reformer_name();
-    accelerated_ = !cntr->get(IVF_INT8_QUANTIZED_PARAMS_SEG_ID) && !cntr->get(IVF_INT4_QUANTIZED_PARAMS_SEG_ID) &&
-                   rf != kInt8ReformerName && rf != kInt4ReformerName && metric_of(meta_) >= 0 && dtype_of(meta_) >= 0 &&
-                   entity_.vector_count() > 0;
+    // The posting lists have a meta of their own (IVFEntity::load_header, ivf_entity.cc:462-476): for an index built
+    // with proxima.ivf.builder.quantizer_class = Int8QuantizerConverter they are int8 rows under the searcher's fp32
+    // meta, and their scores carry the quantiser's global or per-list scale (IVFEntity::load, ivf_entity.cc:541-564)
+    // and a per-query one (IVFReformerWrapper::normalize :325-353).  int4 lists stay with the stock searcher.
+    lmeta_ = entity_.meta();
+    const std::string &rf = lmeta_.reformer_name();
+    int8_lists_ = rf == kInt8ReformerName && lmeta_.data_type() == IndexMeta::DataType::DT_INT8;
+    accelerated_ = !cntr->get(IVF_INT4_QUANTIZED_PARAMS_SEG_ID) && rf != kInt4ReformerName &&
+                   (int8_lists_ || (rf != kInt8ReformerName && !cntr->get(IVF_INT8_QUANTIZED_PARAMS_SEG_ID))) &&
+                   metric_of(lmeta_) >= 0 && dtype_of(lmeta_) >= 0 && entity_.vector_count() > 0;
     if (!accelerated_) {
-      why_not_ = "an index with integer-quantiser scales or an unsupported type";
+      why_not_ = "an index with int4 posting lists or an unsupported type";
       return 0;
     }
     // centroids = the nested Flat index in segment "ivf.centroid" (ivf_searcher.cc:62-86); row cid = centroid cid
@@ -920,34 +924,50 @@ class GpuIVFSearcher : public IndexSearcher {
     IndexMeta cmeta;
     if ((rc = IndexHelper::DeserializeFromStorage(nested.get(), &cmeta)) != 0) return rc;
     auto fseg = nested->get(kSegFeatures), kseg = nested->get(kSegKeys);
-    const size_t nl = entity_.inverted_list_count(), n = entity_.vector_count(), es = meta_.element_size();
-    if (!fseg || !kseg || cmeta.element_size() != es || cmeta.data_type() != meta_.data_type() ||
-        kseg->data_size() != nl * sizeof(uint64_t) || fseg->data_size() != nl * es) {
+    const size_t nl = entity_.inverted_list_count(), n = entity_.vector_count(), es = lmeta_.element_size();
+    const size_t ces = cmeta.element_size();
+    if (!fseg || !kseg || metric_of(cmeta) < 0 || dtype_of(cmeta) < 0 || kseg->data_size() != nl * sizeof(uint64_t) ||
+        fseg->data_size() != nl * ces) {
       accelerated_ = false;  // a centroid index of another shape (e.g. HNSW over centroids)
-      why_not_ = "an index whose centroid index is not a Flat index of the lists' type";
+      why_not_ = "an index whose centroid index is not a Flat index of a supported type";
       return 0;
+    }
+    // the queries of the coarse search go through the centroid index's own reformer (IVFCentroidIndex::load / search,
+    // ivf_centroid_index.cc:538-563,273-295): none for L2 lists, MipsReformer for quantised InnerProduct lists
+    creformer_.reset();
+    c_elem_ = ces;
+    if (!cmeta.reformer_name().empty()) {
+      const std::string &crf = cmeta.reformer_name();
+      if (crf == kInt8ReformerName || crf == kInt4ReformerName) {
+        accelerated_ = false;  // quantised centroids (Int8QuantizerReformer4IP and the like are private to the reference)
+        why_not_ = "an index with quantised centroids";
+        return 0;
+      }
+      creformer_ = IndexFactory::CreateReformer(crf);
+      if (!creformer_) return IndexError_NoExist;
+      if ((rc = creformer_->init(cmeta.reformer_params())) != 0) return rc;
     }
     const void *fp = nullptr;
     const uint64_t *kp = nullptr;
     if (fseg->read(0, &fp, fseg->data_size()) != fseg->data_size()) return IndexError_ReadData;
     if (kseg->read(0, reinterpret_cast<const void **>(&kp), kseg->data_size()) != kseg->data_size()) return IndexError_ReadData;
-    std::vector<char> cent(nl * es);
+    std::vector<char> cent(nl * ces);
     const bool col = cmeta.major_order() == IndexMeta::MO_COLUMN;
-    const size_t us = IndexMeta::AlignSizeof(cmeta.data_type()), units = es / us;
+    const size_t us = IndexMeta::AlignSizeof(cmeta.data_type()), units = ces / us;
     for (size_t i = 0; i < nl; ++i) {
       if (kp[i] >= nl) return IndexError_InvalidFormat;
-      char *dst = &cent[(size_t)kp[i] * es];
+      char *dst = &cent[(size_t)kp[i] * ces];
       const size_t blk = i / 32 * 32;
       if (col && blk + 32 <= nl) {
-        const char *b = static_cast<const char *>(fp) + blk * es;
+        const char *b = static_cast<const char *>(fp) + blk * ces;
         for (size_t u = 0; u < units; ++u) std::memcpy(dst + u * us, b + (u * 32 + (i - blk)) * us, us);
       } else {
-        std::memcpy(dst, static_cast<const char *>(fp) + i * es, es);
+        std::memcpy(dst, static_cast<const char *>(fp) + i * ces, ces);
       }
     }
     // posting lists in list order through IVFEntity (ivf_entity.h:89-170): rows + keys + offsets
     zvb200_store *st = nullptr;
-    if ((rc = zvb200_store_create(device_, dtype_of(meta_), metric_of(meta_), meta_.dimension(), &st)) != 0) return rc;
+    if ((rc = zvb200_store_create(device_, dtype_of(lmeta_), metric_of(lmeta_), lmeta_.dimension(), &st)) != 0) return rc;
     // IVFDistanceCalculator::row_major_distance: (query, feature) (ivf_distance_calculator.h:174-183)
     rc = zvb200_store_set_operand_order(st, 1);
     if (rc == 0) rc = zvb200_store_reserve(st, n);
@@ -981,7 +1001,19 @@ class GpuIVFSearcher : public IndexSearcher {
     offs[nl] = pos;
     if (rc == 0 && pos != n) rc = IndexError_InvalidFormat;
     if (rc == 0) rc = zvb200_store_seal(st);
-    if (rc == 0) rc = zvb200_ivf_attach(st, cent.data(), (uint32_t)nl, offs.data());
+    if (rc == 0)
+      rc = zvb200_ivf_attach_typed(st, cent.data(), (uint32_t)nl, offs.data(), dtype_of(cmeta), metric_of(cmeta),
+                                   cmeta.dimension());
+    if (rc == 0 && int8_lists_) {
+      // distances[k] * norm_val (ivf_entity.cc:601,650): one value for the index, or one per posting list
+      std::vector<float> nv(nl);
+      bool same = true;
+      for (size_t l = 0; l < nl; ++l) {
+        nv[l] = entity_.inverted_list_normalize_value(l);
+        same = same && nv[l] == nv[0];
+      }
+      rc = zvb200_store_set_score_scale(st, same ? nv[0] : 1.0f, same ? nullptr : nv.data());
+    }
     if (rc != 0) { zvb200_store_destroy(st); return rc; }
     store_ = st;
     return 0;
@@ -1046,14 +1078,24 @@ class GpuIVFSearcher : public IndexSearcher {
       log_delegated_once(&logged_group_by_, "GpuIVFSearcher", "a group-by search");
       return this->delegate(brute_force, query, qmeta, count, context);
     }
-    if (!query || !count) return IndexError_InvalidArgument;
+    if (!query || !count || qmeta.element_size() != meta_.element_size()) return IndexError_InvalidArgument;
     if (ctx->magic() != magic_) ctx->reset(this);
+    // the coarse search sees the caller's queries through the centroid index's reformer (ivf_centroid_index.cc:273-295)
+    const void *cq = query;
+    IndexQueryMeta c_qmeta = qmeta;
+    std::string cbuf;
+    int rc = 0;
+    if (creformer_ && !brute_force) {
+      if ((rc = creformer_->transform(query, qmeta, count, &cbuf, &c_qmeta)) != 0) return rc;
+      cq = cbuf.data();
+    }
+    if (!brute_force && c_qmeta.element_size() != c_elem_) return IndexError_Mismatch;
     // queries into the posting lists' format (entity->transform, ivf_searcher.cc:211-214)
     const void *tq = query;
     IndexQueryMeta iv_qmeta;
-    int rc = ctx->entity()->transform(query, qmeta, count, &tq, &iv_qmeta);
+    rc = ctx->entity()->transform(query, qmeta, count, &tq, &iv_qmeta);
     if (rc != 0) return rc;
-    if (iv_qmeta.element_size() != meta_.element_size()) return IndexError_Mismatch;
+    if (iv_qmeta.element_size() != lmeta_.element_size()) return IndexError_Mismatch;
     const uint32_t k = ctx->topk();
     ctx->begin(count);
     const size_t n = keys_.size();
@@ -1066,13 +1108,25 @@ class GpuIVFSearcher : public IndexSearcher {
     if (brute_force)
       rc = zvb200_search(ctx->handle(), tq, count, k, ctx->threshold(), bitmap, ctx->keys.data(), ctx->scores.data(),
                          ctx->index.data(), ctx->counts.data());
-    else
+    else if (cq == tq)
       rc = zvb200_ivf_search(ctx->handle(), tq, count, k, ctx->nprobe, ctx->max_scan, ctx->threshold(), bitmap,
                              ctx->keys.data(), ctx->scores.data(), ctx->index.data(), ctx->counts.data());
+    else
+      rc = zvb200_ivf_search_split(ctx->handle(), cq, tq, count, k, ctx->nprobe, ctx->max_scan, ctx->threshold(), bitmap,
+                                   ctx->keys.data(), ctx->scores.data(), ctx->index.data(), ctx->counts.data());
     if (rc != 0) return rc;
     if (brute_force) ctx->fill_stats(count, n - dropped, dropped);
     for (uint32_t i = 0; i < count; ++i) {
       IndexDocumentList *out = ctx->mutable_result(i);
+      if (int8_lists_) {
+        // entity->normalize(q, &heap) (ivf_searcher.cc:240): one float factor per query — the quantiser's 1/scale, or
+        // 1/(this query's own scale) for InnerProduct (ivf_entity.cc:325-353); 1.0f * factor is the factor itself
+        IndexDocumentHeap probe(1);
+        probe.emplace(0, 1.0f);
+        ctx->entity()->normalize(i, &probe);
+        const float factor = probe.begin()->score();
+        for (uint32_t j = 0; j < ctx->counts[i]; ++j) ctx->scores[(size_t)i * k + j] *= factor;
+      }
       for (uint32_t j = 0; j < ctx->counts[i]; ++j) {
         const size_t o = (size_t)i * k + j;
         if (ctx->fetch_vector()) {  // IVFSearcherContext::topk_to_result (ivf_searcher_context.h:190-197)
@@ -1101,7 +1155,11 @@ class GpuIVFSearcher : public IndexSearcher {
   IVFSearcher stock_{};
   IVFEntity entity_{};
   ailego::Params params_{};
-  IndexMeta meta_{};
+  IndexMeta meta_{};   // the searcher's meta: what the caller's queries look like
+  IndexMeta lmeta_{};  // the posting lists' meta (IVFEntity::meta)
+  IndexReformer::Pointer creformer_{};  // the centroid index's reformer, or null
+  size_t c_elem_{0};
+  bool int8_lists_{false};
   std::vector<uint64_t> keys_{};
   zvb200_store *store_{nullptr};
   const char *why_not_{"an index that was not loaded"};

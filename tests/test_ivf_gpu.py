@@ -8,6 +8,7 @@ import pytest
 
 import support as S
 import zvec_b200 as z
+from zvec_b200.binding import FLT_MAX
 
 pytestmark = [pytest.mark.gpu, pytest.mark.skipif(S.ref() is None, reason="oracle/_ref not available")]
 
@@ -115,4 +116,80 @@ def test_list_major_scan_equals_query_major_bit_for_bit(kind, d, k):
         assert np.array_equal(a[3], b[3]) and np.array_equal(a[2], b[2]) and np.array_equal(a[0], b[0])
         assert np.array_equal(a[1].view(np.uint32), b[1].view(np.uint32))
         assert a[3].max() > 0
+    ctx.close(); st.close()
+
+
+@pytest.mark.parametrize("metric", [z.METRIC_L2SQ, z.METRIC_IP])
+@pytest.mark.parametrize("per_list", [False, True])
+def test_typed_centroids_split_queries_and_score_scales(metric, per_list):
+    """zvb200_ivf_attach_typed + zvb200_ivf_search_split + zvb200_store_set_score_scale (the builder-quantised IVF
+    index: int8 posting lists under fp32 centroids, IVFEntity::search's distances[k] * norm_val) against numpy: the
+    int8 arithmetic is exact, the product with the scale is one fp32 multiplication, so the scores are bit for bit
+    — in both posting-list scans, in the flat scan of the same store, with a threshold on the SCALED scores."""
+    n, d, cd, nlist, q, k, nprobe, max_scan = 12000, 40, 24, 30, 24, 10, 4, 1500
+    rng = np.random.default_rng(77)
+    rows = rng.integers(-128, 128, (n, d), dtype=np.int8)
+    cuts = np.sort(rng.choice(np.arange(1, n), nlist - 1, replace=False))
+    offs = np.concatenate([[0], cuts, [n]]).astype(np.uint64)
+    cent = rng.standard_normal((nlist, cd)).astype(np.float32)
+    cq = rng.standard_normal((q, cd)).astype(np.float32)
+    lq = rng.integers(-128, 128, (q, d), dtype=np.int8)
+    scales = (0.5 + rng.random(nlist)).astype(np.float32) if per_list else None
+    gscale = np.float32(0.37)
+    st = z.Store(z.DT_INT8, metric, d)
+    st.append(rows.view(np.uint8)); st.seal()
+    st.ivf_attach_typed(cent.view(np.uint8), offs, z.DT_FP32, z.METRIC_L2SQ, cd)
+    with pytest.raises(z.ZvecB200Error) as ei:             # one query layout cannot serve both stages
+        z.Context(st).ivf_search(lq.view(np.uint8), k, nprobe, max_scan)
+    assert ei.value.code == -24
+    st.set_score_scale(1.0 if per_list else float(gscale), scales)
+    list_of = np.searchsorted(offs[1:].astype(np.int64), np.arange(n), side="right")
+    row_scale = scales[list_of] if per_list else np.full(n, gscale, np.float32)
+    r32, q32 = rows.astype(np.int64), lq.astype(np.int64)
+    if metric == z.METRIC_L2SQ:
+        dist = ((r32 ** 2).sum(1)[None, :] - 2 * (q32 @ r32.T) + (q32 ** 2).sum(1)[:, None]).astype(np.float32)
+    else:
+        dist = (-(q32 @ r32.T)).astype(np.float32)
+    scaled = dist * row_scale[None, :]                      # fp32 x fp32, rounded once
+    cd2 = ((cq[:, None, :].astype(np.float64) - cent[None, :, :]) ** 2).sum(2)
+    thr = float(np.median(scaled))
+
+    def expect(i, threshold, whole):
+        if whole:
+            cand = np.arange(n)
+        else:
+            cand, seen = [], 0
+            for l in np.argsort(cd2[i], kind="stable")[:nprobe]:
+                if seen >= max_scan:
+                    break
+                cand.append(np.arange(int(offs[l]), int(offs[l + 1]))); seen += int(offs[l + 1] - offs[l])
+            cand = np.concatenate(cand)
+        cand = cand[scaled[i][cand] <= np.float32(threshold)]
+        order = np.lexsort((cand, scaled[i][cand]))[:k]           # (score, row): the packed keys' order
+        return cand[order], scaled[i][cand[order]]
+
+    ctx = z.Context(st)
+    for threshold in (FLT_MAX, thr):
+        for kernel, batch, name in ((1, q, "scan_lists"), (0, q, "scan_lists_lm"), (0, 1, "scan_lists")):
+            ctx.set_kernel(kernel)
+            for b0 in range(0, q, batch):
+                gk, gs, gi, gc = ctx.ivf_search_split(cq[b0:b0 + batch], lq[b0:b0 + batch].view(np.uint8), k, nprobe,
+                                                      max_scan, threshold=threshold)
+                assert ctx.last_kernel() == name
+                for j in range(gk.shape[0]):
+                    ei_, es_ = expect(b0 + j, threshold, False)
+                    assert gc[j] == len(ei_)
+                    assert np.array_equal(gi[j][:len(ei_)], ei_), (name, threshold, b0 + j)
+                    assert np.array_equal(gs[j][:len(ei_)].view(np.uint32), es_.view(np.uint32))
+        ctx.set_kernel(0)
+        gk, gs, gi, gc = ctx.search(lq.view(np.uint8), k, threshold=threshold)   # search_bf_impl: every list
+        assert ctx.last_kernel() == "scan_gemv"                                 # a scaled store stays on the GEMV scan
+        for j in range(q):
+            ei_, es_ = expect(j, threshold, True)
+            assert gc[j] == len(ei_) and np.array_equal(gi[j][:len(ei_)], ei_)
+            assert np.array_equal(gs[j][:len(ei_)].view(np.uint32), es_.view(np.uint32))
+    st.ivf_attach_typed(cent.view(np.uint8), offs, z.DT_FP32, z.METRIC_L2SQ, cd)  # re-attaching drops the list scales
+    st.set_score_scale(1.0, None)
+    gk, gs, gi, gc = ctx.search(lq[:2].view(np.uint8), k)
+    assert np.array_equal(gs[0].view(np.uint32), np.sort(dist[0])[:k].view(np.uint32))
     ctx.close(); st.close()

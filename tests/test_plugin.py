@@ -282,17 +282,38 @@ def test_install_overrides_routes_stock_names_to_the_gpu_classes(tmp_path):
                                          ("SquaredEuclidean", "HalfFloatConverter"),
                                          ("SquaredEuclidean", "Int8StreamingConverter")])
 def test_gpu_ivf_searcher_equals_ivf_searcher(metric, conv):
+    _gpu_ivf_searcher_vs_stock(metric, conv, "", conv == "Int8StreamingConverter")
+
+
+# posting lists quantised by the builder itself (ivf_builder.cc:738-800): int8 rows under fp32 centroids (for
+# InnerProduct in the MipsReformer's space), scores scaled by the quantiser's global or per-list 1/scale at the heap
+# (ivf_entity.cc:601,650) and by a per-index / per-query factor afterwards (IVFReformerWrapper::normalize :325-353)
+@needs_plugin
+@pytest.mark.gpu
+@pytest.mark.parametrize("metric,extra", [
+    ("SquaredEuclidean", ""), ("Euclidean", ""), ("InnerProduct", ""),
+    ("InnerProduct", ";proxima.ivf.builder.quantize_by_centroid=true"),
+    ("SquaredEuclidean", ";proxima.ivf.searcher.brute_force_threshold=1000000"),      # search_bf_impl's path
+    ("InnerProduct", ";proxima.ivf.builder.quantize_by_centroid=true;proxima.ivf.searcher.brute_force_threshold=1000000"),
+])
+def test_gpu_ivf_searcher_int8_quantised_lists(metric, extra):
+    bp = ";proxima.ivf.builder.quantizer_class=Int8QuantizerConverter" + "".join(
+        ";" + p for p in extra.split(";") if p.startswith("proxima.ivf.builder"))
+    sp = "".join(";" + p for p in extra.split(";") if p.startswith("proxima.ivf.searcher"))
+    _gpu_ivf_searcher_vs_stock(metric, "", bp, True, sp)
+
+
+def _gpu_ivf_searcher_vs_stock(metric, conv, bp_extra, exact, sp_extra=""):
     assert S.ref().zref_has_searcher(b"GpuIVFSearcher") == 1
     n, d, nlist, k = 20000, 32, 64, 10
     rng = np.random.default_rng(8)
     centres = rng.standard_normal((nlist, d)).astype(np.float32)
     x = (centres[np.arange(n) % nlist] + 0.3 * rng.standard_normal((n, d))).astype(np.float32)
     qs = (centres[rng.integers(0, nlist, 40)] + 0.3 * rng.standard_normal((40, d))).astype(np.float32)
-    bp = "proxima.ivf.builder.centroid_count=%d" % nlist
-    sp = "proxima.ivf.searcher.scan_ratio=0.1"
+    bp = "proxima.ivf.builder.centroid_count=%d" % nlist + bp_extra
+    sp = "proxima.ivf.searcher.scan_ratio=0.1" + sp_extra
     ix = S.RefIndex(x, S.DT_FP32, d, metric, conv, kind="IVF", build_params=bp, search_params=sp)
     import zvec_b200 as z
-    exact = conv == "Int8StreamingConverter"
 
     def same(a, b, what):
         for i in range(len(a[3])):

@@ -79,6 +79,11 @@ _SIGS = {
                                        C.c_void_p]),
     "zvb200_ivf_attach": (C.c_int, [C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p]),
     "zvb200_ivf_set_budget_sizes": (C.c_int, [C.c_void_p, C.c_void_p]),
+    "zvb200_ivf_attach_typed": (C.c_int, [C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p, C.c_int, C.c_int, C.c_uint32]),
+    "zvb200_ivf_search_split": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32,
+                                          C.c_uint64, C.c_float, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
+                                          C.c_void_p]),
+    "zvb200_store_set_score_scale": (C.c_int, [C.c_void_p, C.c_float, C.c_void_p]),
     "zvb200_ivf_search": (C.c_int, [C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint64, C.c_float,
                                     C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     "zvb200_ivf_search_device": (C.c_int, [C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint64,
@@ -224,6 +229,19 @@ class Store:
         assert offs.size == nlist + 1
         _check(lib().zvb200_ivf_attach(self.h, _ptr(centroids), nlist, _ptr(offs)))
 
+    def ivf_attach_typed(self, centroids, list_offsets, c_dtype, c_metric, c_dim):
+        """centroids in a layout of their own (IVFBuilder with a quantizer_class): [nlist, c_elem_bytes] bytes"""
+        centroids = np.ascontiguousarray(centroids)
+        offs = np.ascontiguousarray(list_offsets, dtype=np.uint64)
+        nlist = offs.size - 1
+        assert centroids.nbytes % nlist == 0
+        _check(lib().zvb200_ivf_attach_typed(self.h, _ptr(centroids), nlist, _ptr(offs), c_dtype, c_metric, c_dim))
+
+    def set_score_scale(self, scale=1.0, list_scales=None):
+        """scores leave the scans multiplied by `scale`, or by list_scales[list of the row] (IVFEntity's norm_val)"""
+        ls = None if list_scales is None else np.ascontiguousarray(list_scales, np.float32)
+        _check(lib().zvb200_store_set_score_scale(self.h, scale, _ptr(ls)))
+
     def close(self):
         if self.h:
             lib().zvb200_store_destroy(self.h)
@@ -301,6 +319,23 @@ class Context:
         counts = np.empty(q, np.uint32)
         _check(lib().zvb200_ivf_search(self.h, _ptr(queries), q, k, nprobe, max_scan_count, threshold,
                                        _ptr(filter_bitmap), _ptr(keys), _ptr(scores), _ptr(index), _ptr(counts)))
+        return keys, scores, index, counts
+
+    def ivf_search_split(self, coarse_queries, list_queries, k, nprobe, max_scan_count, threshold=FLT_MAX,
+                         filter_bitmap=None):
+        """zvb200_ivf_search for a store whose centroids have a layout of their own (ivf_attach_typed)."""
+        coarse_queries = np.ascontiguousarray(coarse_queries)
+        list_queries = np.ascontiguousarray(list_queries)
+        if filter_bitmap is not None:
+            filter_bitmap = np.ascontiguousarray(filter_bitmap, np.uint32)
+        q = list_queries.nbytes // self.store.elem_bytes
+        keys = np.empty((q, k), np.uint64)
+        scores = np.empty((q, k), np.float32)
+        index = np.empty((q, k), np.uint32)
+        counts = np.empty(q, np.uint32)
+        _check(lib().zvb200_ivf_search_split(self.h, _ptr(coarse_queries), _ptr(list_queries), q, k, nprobe,
+                                             max_scan_count, threshold, _ptr(filter_bitmap), _ptr(keys), _ptr(scores),
+                                             _ptr(index), _ptr(counts)))
         return keys, scores, index, counts
 
     def ivf_search_device(self, queries_ptr, q, k, nprobe, max_scan_count, out_scores_ptr, out_index_ptr,

@@ -132,6 +132,7 @@ int zvb200_store_destroy(zvb200_store *s) {
   if (s->list_off_dev) cudaFree(s->list_off_dev);
   if (s->budget_dev) cudaFree(s->budget_dev);
   if (s->gbase_dev) cudaFree(s->gbase_dev);
+  if (s->row_scale) cudaFree(s->row_scale);
   if (s->staging) cudaFree(s->staging);
   if (s->stream) cudaStreamDestroy(s->stream);
   delete s;
@@ -393,11 +394,11 @@ int zvb200_ctx_destroy(zvb200_ctx *c) {
   cudaSetDevice(c->device);
   cudaStreamSynchronize(c->stream);
   c->xkeys.release(); c->gather.release(); c->out_rows.release(); c->h_rows.release();
-  DevBuf *d[] = {&c->qin, &c->qf32, &c->qraw, &c->qtails, &c->qnorms, &c->part, &c->out_scores,
+  DevBuf *d[] = {&c->qin, &c->qin2, &c->qf32, &c->qraw, &c->qtails, &c->qnorms, &c->part, &c->out_scores,
                  &c->out_index, &c->filter, &c->misc, &c->gtau, &c->coarse_scores, &c->coarse_index,
                  &c->seg_prefix, &c->seg_row, &c->seg_count, &c->seg_list, &c->lm, &c->qsrc, &c->cand, &c->qshadow};
   for (auto b : d) b->release();
-  c->h_q.release(); c->h_scores.release(); c->h_index.release();
+  c->h_q.release(); c->h_q2.release(); c->h_scores.release(); c->h_index.release();
   if (c->ev_scan0) cudaEventDestroy(c->ev_scan0);
   if (c->ev_scan1) cudaEventDestroy(c->ev_scan1);
   cudaStreamDestroy(c->stream);
@@ -521,6 +522,7 @@ int zvb_search_core(zvb200_ctx *c, zvb200_store *s, const void *queries_dev, uin
   const bool mma_early = mma_ok && rv.shadow && q > 2;
   if (which == 0) which = (mma_direct || (mma_ok && q > 4) || mma_early) ? 3 : (q <= 4) ? 1 : scan_tile_supports(k) ? 2 : 1;
   if (which == 4 && !stream_ok) which = 1;
+  if (rv.scaled()) which = 1;  // score scales live in the GEMV scan's epilogue (zvb200_store_set_score_scale)
   if (which == 3 && !mma_ok) return set_err(ZVB200_ERR_UNSUPPORTED, "tcgen05 scan: fp16 / fp32 stores, k <= 128 only");
   if (which == 2 && !scan_tile_supports(k)) which = 1;
   QueryView qv;
@@ -830,6 +832,12 @@ int zvb200_distance_matrix(int device, int metric, int dtype, uint32_t dim, cons
 }
 
 int zvb200_ivf_attach(zvb200_store *s, const void *centroids, uint32_t nlist, const uint64_t *list_offsets) {
+  if (!s) return set_err(ZVB200_ERR_INVALID_ARGUMENT, "null argument");
+  return zvb200_ivf_attach_typed(s, centroids, nlist, list_offsets, s->dtype, s->metric, s->dim);
+}
+
+int zvb200_ivf_attach_typed(zvb200_store *s, const void *centroids, uint32_t nlist, const uint64_t *list_offsets,
+                            int c_dtype, int c_metric, uint32_t c_dim) {
   if (!s || !centroids || !list_offsets || nlist == 0) return set_err(ZVB200_ERR_INVALID_ARGUMENT, "null argument");
   if (!s->shards.empty()) return set_err(ZVB200_ERR_UNSUPPORTED, "IVF over a sharded store: shard the lists per process (zvb200_ivf_set_budget_sizes)");
   if (!s->sealed) return set_err(ZVB200_ERR_NOREADY, "store not sealed");
@@ -839,7 +847,7 @@ int zvb200_ivf_attach(zvb200_store *s, const void *centroids, uint32_t nlist, co
   // list offsets travel as u32 on the device: the store's own row limit (check_row_limit) keeps them exact
   if (int r = zvb_check_row_limit(list_offsets[nlist])) return r;
   zvb200_store *cs = nullptr;
-  int r = zvb200_store_create(s->device, s->dtype, s->metric, s->dim, &cs);
+  int r = zvb200_store_create(s->device, c_dtype, c_metric, c_dim, &cs);
   if (r == 0) r = zvb200_store_append(cs, centroids, nlist, nullptr);
   if (r == 0) r = zvb200_store_seal(cs);
   uint32_t *d = nullptr;
@@ -861,7 +869,9 @@ int zvb200_ivf_attach(zvb200_store *s, const void *centroids, uint32_t nlist, co
   if (s->list_off_dev) cudaFree(s->list_off_dev);
   if (s->budget_dev) { cudaFree(s->budget_dev); s->budget_dev = nullptr; }
   if (s->gbase_dev) { cudaFree(s->gbase_dev); s->gbase_dev = nullptr; }
+  if (s->row_scale) { cudaFree(s->row_scale); s->row_scale = nullptr; }  // per-list scales belong to the old lists
   s->centroids = cs; s->list_off_dev = d; s->nlist = nlist;
+  s->coarse_typed = c_dtype != s->dtype || c_metric != s->metric || c_dim != s->dim;
   s->list_offsets.assign(list_offsets, list_offsets + nlist + 1);
   return 0;
 }
@@ -916,8 +926,10 @@ static int coarse_wide(zvb200_ctx *c, zvb200_store *cs, const void *queries_dev,
 // outputs on the device
 static int ivf_core(zvb200_ctx *c, const void *queries_dev, uint32_t q, uint32_t k, uint32_t nprobe,
                     uint64_t max_scan_count, float threshold, const uint32_t *filter_dev, float *out_scores_dev,
-                    uint32_t *out_index_dev) {
+                    uint32_t *out_index_dev, const void *list_queries_dev = nullptr) {
   zvb200_store *s = c->s;
+  if (s->coarse_typed && !list_queries_dev)
+    return set_err(ZVB200_ERR_MISMATCH, "centroids in a layout of their own: search with zvb200_ivf_search_split");
   CU(c->coarse_scores.ensure((size_t)q * nprobe * 4));
   CU(c->coarse_index.ensure((size_t)q * nprobe * 4));
   CU(c->seg_prefix.ensure((size_t)q * (nprobe + 1) * 4));
@@ -948,7 +960,13 @@ static int ivf_core(zvb200_ctx *c, const void *queries_dev, uint32_t q, uint32_t
   CU(launch_ivf_plan((const uint32_t *)c->coarse_index.p, q, nprobe, s->list_off_dev, s->budget_dev, max_scan_count,
                      (uint32_t *)c->seg_prefix.p, (uint32_t *)c->seg_row.p, (uint32_t *)c->seg_count.p, c->stream,
                      list_major ? (uint32_t *)c->seg_list.p : nullptr));
-  // 3. posting-list scan, queries already in compute layout (same dtype / metric / dim as the centroids)
+  // 3. posting-list scan, queries already in compute layout (same dtype / metric / dim as the centroids) — or, for
+  // split queries, prepared now in the lists' layout (the coarse search is done with the context's query buffers)
+  if (list_queries_dev) {
+    QueryView lqv;
+    const int pr = prep_core(c, s, list_queries_dev, q, &lqv, false);
+    if (pr != 0) return pr;
+  }
   SearchParams sp;
   sp.k = k; sp.threshold = threshold; sp.filter = filter_dev;
   if (list_major) {
@@ -965,7 +983,7 @@ static int ivf_core(zvb200_ctx *c, const void *queries_dev, uint32_t q, uint32_t
     CU(launch_merge_parts((const u64 *)c->part.p, nparts, q, k, out_scores_dev, out_index_dev, nullptr, c->stream));
     return 0;
   }
-  const bool lists_stream = c->force_kernel == 4 && scan_stream_supports(rv, k, nprobe);
+  const bool lists_stream = c->force_kernel == 4 && !rv.scaled() && scan_stream_supports(rv, k, nprobe);
   const size_t parts = lists_stream ? scan_lists_stream_parts(q, s->sm_count) : scan_lists_parts(q, s->sm_count);
   CU(c->part.ensure((size_t)q * parts * k * sizeof(u64)));
   uint32_t nparts = 0;
@@ -1038,6 +1056,65 @@ int zvb200_ivf_search_device(zvb200_ctx *c, const void *queries_dev, uint32_t q,
   if (q == 0) return 0;
   CU(cudaSetDevice(c->s->device));
   return ivf_core(c, queries_dev, q, k, nprobe, max_scan_count, threshold, filter_dev, out_scores_dev, out_index_dev);
+}
+
+static const uint32_t *upload_filter(zvb200_ctx *c, zvb200_store *s, const uint32_t *filter, int *err);
+
+int zvb200_ivf_search_split(zvb200_ctx *c, const void *coarse_queries, const void *list_queries, uint32_t q, uint32_t k,
+                            uint32_t nprobe, uint64_t max_scan_count, float threshold, const uint32_t *filter_bitmap,
+                            uint64_t *out_keys, float *out_scores, uint32_t *out_index, uint32_t *out_counts) {
+  if (!c) return set_err(ZVB200_ERR_INVALID_ARGUMENT, "null argument");
+  std::shared_lock<std::shared_mutex> rl(c->s->mu);
+  int r = ivf_check(c, list_queries, q, k, &nprobe);
+  if (r != 0) return r;
+  if (!out_scores || (!coarse_queries && q)) return set_err(ZVB200_ERR_INVALID_ARGUMENT, "null argument");
+  zvb200_store *s = c->s;
+  if (q == 0) return 0;
+  CU(cudaSetDevice(s->device));
+  const size_t cbytes = (size_t)q * s->centroids->elem_bytes, lbytes = (size_t)q * s->elem_bytes, nres = (size_t)q * k;
+  CU(c->h_q.ensure(cbytes));
+  CU(c->h_q2.ensure(lbytes));
+  CU(c->qin.ensure(cbytes));
+  CU(c->qin2.ensure(lbytes));
+  CU(c->out_scores.ensure(nres * 4));
+  CU(c->out_index.ensure(nres * 4));
+  memcpy(c->h_q.p, coarse_queries, cbytes);
+  memcpy(c->h_q2.p, list_queries, lbytes);
+  CU(cudaMemcpyAsync(c->qin.p, c->h_q.p, cbytes, cudaMemcpyHostToDevice, c->stream));
+  CU(cudaMemcpyAsync(c->qin2.p, c->h_q2.p, lbytes, cudaMemcpyHostToDevice, c->stream));
+  int fe = 0;
+  const uint32_t *fdev = upload_filter(c, s, filter_bitmap, &fe);
+  if (fe != 0) return fe;
+  r = ivf_core(c, c->qin.p, q, k, nprobe, max_scan_count, threshold, fdev, (float *)c->out_scores.p,
+               (uint32_t *)c->out_index.p, c->qin2.p);
+  if (r != 0) return r;
+  return finish_results(c, s, q, k, out_keys, out_scores, out_index, out_counts);
+}
+
+int zvb200_store_set_score_scale(zvb200_store *s, float scale, const float *list_scales) {
+  if (!s) return set_err(ZVB200_ERR_INVALID_ARGUMENT, "null store");
+  if (!s->shards.empty()) return set_err(ZVB200_ERR_UNSUPPORTED, "not available on a sharded store");
+  if (!(scale == scale) || (list_scales && !s->centroids))
+    return set_err(list_scales ? ZVB200_ERR_NOREADY : ZVB200_ERR_INVALID_ARGUMENT,
+                   list_scales ? "per-list scales need an attached IVF structure" : "scale is NaN");
+  std::lock_guard<std::shared_mutex> g(s->mu);
+  CU(cudaSetDevice(s->device));
+  if (s->row_scale) { cudaFree(s->row_scale); s->row_scale = nullptr; }
+  s->score_scale = scale;
+  if (!list_scales || s->n == 0) return 0;
+  float *ls = nullptr, *rs = nullptr;
+  cudaError_t e = cudaMalloc((void **)&ls, (size_t)s->nlist * 4);
+  if (e == cudaSuccess) e = cudaMalloc((void **)&rs, (size_t)s->n * 4);
+  if (e == cudaSuccess) e = cudaMemcpy(ls, list_scales, (size_t)s->nlist * 4, cudaMemcpyHostToDevice);
+  if (e == cudaSuccess) e = launch_expand_list_scale(s->list_off_dev, s->nlist, ls, s->n, rs, 0);
+  if (e == cudaSuccess) e = cudaDeviceSynchronize();
+  if (ls) cudaFree(ls);
+  if (e != cudaSuccess) {
+    if (rs) cudaFree(rs);
+    return cuda_fail(e, "set_score_scale");
+  }
+  s->row_scale = rs;
+  return 0;
 }
 
 int zvb200_ivf_set_global_bases(zvb200_store *s, const uint64_t *list_global_base) {

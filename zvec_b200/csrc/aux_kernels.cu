@@ -677,6 +677,29 @@ cudaError_t launch_ivf_global_rows(const uint32_t *index, uint64_t count, const 
   return cudaGetLastError();
 }
 
+// per-list score scales -> one scale per row (the rows of a list are contiguous): what the scans' epilogues read
+namespace {
+__global__ void expand_list_scale_kernel(const uint32_t *list_off, uint32_t nlist, const float *scales, uint64_t n,
+                                         float *row_scale) {
+  const uint64_t r = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (r >= n) return;
+  uint32_t lo = 0, hi = nlist;  // last list with list_off <= r (empty lists share an offset: the last of them wins,
+  while (hi - lo > 1) {         // and it is the one that holds the row)
+    const uint32_t mid = (lo + hi) >> 1;
+    if (list_off[mid] <= (uint32_t)r) lo = mid; else hi = mid;
+  }
+  row_scale[r] = scales[lo];
+}
+}  // namespace
+
+cudaError_t launch_expand_list_scale(const uint32_t *list_off, uint32_t nlist, const float *scales, uint64_t n,
+                                     float *row_scale, cudaStream_t st) {
+  if (n == 0) return cudaSuccess;
+  expand_list_scale_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(list_off, nlist, scales, n, row_scale);
+  count_launch();
+  return cudaGetLastError();
+}
+
 cudaError_t launch_distance_matrix(const RowsView &rv, const QueryView &qv, float *out,
                                    cudaStream_t st) {
   if (rv.n == 0 || qv.q == 0) return cudaSuccess;

@@ -59,6 +59,9 @@ struct zvb200_store {
   uint32_t *budget_dev = nullptr;    // [nlist] list sizes in the whole index (sharded IVF), or null
   uint64_t *gbase_dev = nullptr;     // [nlist] row of the whole index where this store's slice of each list starts
   uint32_t nlist = 0;
+  float *row_scale = nullptr;        // [n] zvb200_store_set_score_scale with per-list values, expanded per row
+  float score_scale = 1.f;
+  bool coarse_typed = false;         // centroids in a layout of their own (zvb200_ivf_attach_typed): split queries only
   // writers (append / seal / write / set_deleted / attach) exclusive; the host-synchronous searches shared, from the
   // first look at the store to the stream sync that ends them: an append that re-allocates the rows (store_grow)
   // cannot free them under a search another thread has in flight (FlatStreamer adds race with searches,
@@ -77,6 +80,7 @@ struct zvb200_store {
     v.dtype = dtype; v.metric = metric; v.tails = tails; v.norms = norms;
     v.drop = has_drop ? drop : nullptr;
     v.query_first = query_first;
+    v.row_scale = row_scale; v.score_scale = score_scale;
     if (shadow && shadowed >= n) { v.shadow = shadow; v.shadow_k = shadow_k; v.shadow_mrow_max = shadow_mrow_max; }
     return v;
   }
@@ -116,11 +120,11 @@ struct zvb200_ctx {
   int device = 0;  // copy: a context may outlive its store (destruction order is the caller's)
   cudaStream_t stream = nullptr;
   DevBuf qshadow;
-  DevBuf qin, qf32, qraw, qtails, qnorms, part, out_scores, out_index, filter, misc, gtau;
+  DevBuf qin, qin2, qf32, qraw, qtails, qnorms, part, out_scores, out_index, filter, misc, gtau;
   DevBuf coarse_scores, coarse_index, seg_prefix, seg_row, seg_count, seg_list, lm;  // IVF
   DevBuf qsrc, cand;  // fp32 queries before the reformer; candidate rows of the refiner
   QueryView last_qv;
-  HostBuf h_q, h_scores, h_index;
+  HostBuf h_q, h_q2, h_scores, h_index;
   int force_kernel = 0;
   uint32_t mma_group_cap = 0;  // queries per tcgen05 launch (0: ZVB200_MMA_GROUP or 1024)
   int last_mma_kind = -1;

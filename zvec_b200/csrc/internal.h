@@ -29,6 +29,12 @@ struct RowsView {
   const uint8_t *shadow = nullptr;
   uint32_t shadow_k = 0;
   float shadow_mrow_max = 0.f;      // largest row share of the shadow filter's margin (the first-tile bootstrap's bound)
+  // scores leave the scan multiplied by row_scale[row] (per posting list, expanded per row) or by score_scale: the
+  // `distances[k] * norm_val` of IVFEntity::search (ivf_entity.cc:601,650; zvb200_store_set_score_scale).  Honoured by
+  // the GEMV scan, the posting-list scans; the other kernels are not chosen for a scaled store
+  const float *row_scale = nullptr;
+  float score_scale = 1.f;
+  bool scaled() const { return row_scale || score_scale != 1.f; }
 };
 
 // Queries in "compute layout", produced by prep_queries() on the device.
@@ -97,6 +103,8 @@ cudaError_t launch_merge_shards(const float *scores, const uint32_t *index, uint
 cudaError_t launch_merge_rows(const float *scores, const uint64_t *rows, uint32_t g, uint32_t q, uint32_t k,
                               float *out_scores, uint64_t *out_rows, cudaStream_t st);
 // local rows of a list-grouped store -> rows of the whole index
+cudaError_t launch_expand_list_scale(const uint32_t *list_off, uint32_t nlist, const float *scales, uint64_t n,
+                                     float *row_scale, cudaStream_t st);
 cudaError_t launch_ivf_global_rows(const uint32_t *index, uint64_t count, const uint32_t *list_off,
                                    const uint64_t *gbase, uint32_t nlist, uint64_t *out, cudaStream_t st);
 // reference element layout (host order) -> store layout

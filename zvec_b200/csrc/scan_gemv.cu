@@ -174,6 +174,8 @@ __global__ void __launch_bounds__(kThreads, QB == 1 ? 2 : 1) scan_gemv_kernel(co
       if (valid && a.filter) valid = !bit_set(a.filter, r);
       float4 mt = make_float4(0, 0, 0, 0);
       if (metric_is_qi8(metric) && valid) mt = a.rv.tails[r];
+      // the row's score scale (IVFEntity::search: distances[k] * norm_val, ivf_entity.cc:650); 1 for a plain store
+      const float sc = a.rv.row_scale ? (valid ? a.rv.row_scale[r] : 1.f) : a.rv.score_scale;
 #pragma unroll
       for (int j = 0; j < QB; ++j) {
         float s;
@@ -190,6 +192,7 @@ __global__ void __launch_bounds__(kThreads, QB == 1 ? 2 : 1) scan_gemv_kernel(co
               : metric == ZVB200_METRIC_L2 ? sqrtf(f)
               : metric == ZVB200_METRIC_IP ? -f : 1.0f - f;
         }
+        s *= sc;
         const u64 key = pack_key(s, (uint32_t)r);
         const bool has = valid && j < nq && s <= a.threshold && key < tk[j].tau;
         tk[j].push(has, key, kMaxKey);

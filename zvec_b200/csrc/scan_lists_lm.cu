@@ -271,6 +271,8 @@ __device__ __forceinline__ void lm_scan_item(const LmArgs &a, const LmItem &it, 
       if (valid && a.filter) valid = !bit_set(a.filter, r);
       float4 mt = make_float4(0, 0, 0, 0);
       if (metric_is_qi8(metric) && valid) mt = a.rv.tails[r];
+      // the row's score scale (IVFEntity::search: distances[k] * norm_val, ivf_entity.cc:650); 1 for a plain store
+      const float sc = a.rv.row_scale ? (valid ? a.rv.row_scale[r] : 1.f) : a.rv.score_scale;
       if (spread) {
         // this lane's query: j = l (a select chain over the NQ accumulators, every lane of the group holds all of them)
         Acc mine = acc[u][0];
@@ -293,6 +295,7 @@ __device__ __forceinline__ void lm_scan_item(const LmArgs &a, const LmItem &it, 
         } else {
           s = score_of(mine, aa[u], 0, mt);
         }
+        s *= sc;
         const u64 key = pack_key(s, (uint32_t)r);
         const bool has = valid && s <= a.threshold && key < mytau;
         uint32_t any = __ballot_sync(0xffffffffu, has);
@@ -306,7 +309,7 @@ __device__ __forceinline__ void lm_scan_item(const LmArgs &a, const LmItem &it, 
       } else {
 #pragma unroll
         for (int j = 0; j < NQ; ++j) {
-          const float s = score_of(acc[u][j], aa[u], j, mt);
+          const float s = score_of(acc[u][j], aa[u], j, mt) * sc;
           const u64 key = pack_key(s, (uint32_t)r);
           const bool has = valid && s <= a.threshold && key < tau[j];
           if (__any_sync(0xffffffffu, has)) tau[j] = lm_push(it.tkwarp + (size_t)j * it.tk_u64, k, has, key, tau[j]);
