@@ -18,6 +18,12 @@ ap.add_argument("--kernel", type=int, default=0)
 ap.add_argument("--iters", type=int, default=10)
 a = ap.parse_args()
 dev = torch.device("cuda", 0)
+if os.environ.get("ZVB200_PROBE_L2_GRAN"):   # cudaLimitMaxL2FetchGranularity (0x05): 32 / 64 / 128 bytes
+    import ctypes
+    torch.zeros(1, device=dev)
+    rt = ctypes.CDLL("libcudart.so.12")
+    print("cudaDeviceSetLimit ->", rt.cudaDeviceSetLimit(5, ctypes.c_size_t(int(os.environ["ZVB200_PROBE_L2_GRAN"]))))
+    v = ctypes.c_size_t(0); rt.cudaDeviceGetLimit(ctypes.byref(v), 5); print("L2 fetch granularity now", v.value)
 g = torch.Generator(device=dev); g.manual_seed(7)
 d = a.dim
 if a.dtype == "int8q":

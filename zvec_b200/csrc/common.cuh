@@ -98,6 +98,12 @@ __device__ __forceinline__ uint4 ldg_stream(const void *p) {
   return r;
 }
 
+// a QuantizedInteger row tail {a, b, s, s2} through the same path
+__device__ __forceinline__ float4 ldg_tail(const float4 *p) {
+  const uint4 w = ldg_stream(p);
+  return make_float4(__uint_as_float(w.x), __uint_as_float(w.y), __uint_as_float(w.z), __uint_as_float(w.w));
+}
+
 __device__ __forceinline__ int lane_id() { return threadIdx.x & 31; }
 
 }  // namespace zvb

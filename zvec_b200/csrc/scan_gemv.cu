@@ -41,7 +41,11 @@ struct GemvArgs {
 };
 
 
-template <int DT, bool L2, int QB, bool SEG, int kU = kUmax>
+// PRE > 0: rows of at most PRE chunks per lane (short rows: 96-B int8 rows over 2 lanes = 3) are loaded WHOLE before
+// the first multiply — one trip to HBM per warp step instead of one per chunk iteration.  A warp step of such rows
+// is latency-bound (ncu, 40M x 96 int8: 0.41 IPC, 4.3 of 9 warp-cycles per issue on the long scoreboard, DRAM at
+// 4.8 of 6.4 TB/s): the three dependent trips were the step.
+template <int DT, bool L2, int QB, bool SEG, int kU = kUmax, int PRE = 0>
 __global__ void __launch_bounds__(kThreads, QB == 1 ? 2 : 1) scan_gemv_kernel(const GemvArgs a) {
   typedef Chunk<DT, L2> CK;
   typedef typename CK::Acc Acc;
@@ -137,11 +141,35 @@ __global__ void __launch_bounds__(kThreads, QB == 1 ? 2 : 1) scan_gemv_kernel(co
       rp[u] = a.rv.rows + sr * a.rv.row_stride;
       // QuantizedInteger: the row's tail is read only after the dot product; start its trip from HBM now (no
       // register held: the 128-register budget of 2 CTAs per SM is full) so that read finds it in L2
-      if (metric_is_qi8(metric) && l == 0) asm volatile("prefetch.global.L2 [%0];" ::"l"(a.rv.tails + sr));
+      // (one request per 64 B of tails = 4 rows; one per row measured the same)
+      if (metric_is_qi8(metric) && l == 0 && (sr & 3) == 0) asm volatile("prefetch.global.L2 [%0];" ::"l"(a.rv.tails + sr));
       aa[u] = 0;
 #pragma unroll
       for (int j = 0; j < QB; ++j) acc[u][j] = 0;
     }
+    if (PRE > 0) {
+      uint4 v[PRE > 0 ? PRE : 1][kU];
+#pragma unroll
+      for (int i = 0; i < PRE; ++i) {
+        const uint32_t c = l + i * lpr;
+#pragma unroll
+        for (int u = 0; u < kU; ++u) v[i][u] = c < C ? ldg_stream(rp[u] + (size_t)c * 16) : make_uint4(0, 0, 0, 0);
+      }
+#pragma unroll
+      for (int i = 0; i < PRE; ++i) {
+        const uint32_t c = l + i * lpr;
+        if (c < C) {
+#pragma unroll
+          for (int j = 0; j < QB; ++j) {
+#pragma unroll
+            for (int u = 0; u < kU; ++u) {
+              Acc dummy = 0;
+              CK::fma(acc[u][j], j == 0 ? aa[u] : dummy, v[i][u], qs + (size_t)j * qbytes, c);
+            }
+          }
+        }
+      }
+    } else
     for (uint32_t c = l; c < C; c += lpr) {
       uint4 v[kU];
 #pragma unroll
@@ -173,7 +201,9 @@ __global__ void __launch_bounds__(kThreads, QB == 1 ? 2 : 1) scan_gemv_kernel(co
       if (valid && a.rv.drop) valid = !bit_set(a.rv.drop, r);
       if (valid && a.filter) valid = !bit_set(a.filter, r);
       float4 mt = make_float4(0, 0, 0, 0);
-      if (metric_is_qi8(metric) && valid) mt = a.rv.tails[r];
+      // through the read-only, no-L1-allocate path like the rows: a plain ld.global of the tails costs the C3 scan
+      // 14 % (4.19 -> 4.77 TB/s at 100M x 96; ncu: 1.43x -> 1.20x the algorithmic DRAM bytes)
+      if (metric_is_qi8(metric) && valid) mt = ldg_tail(a.rv.tails + r);
       // the row's score scale (IVFEntity::search: distances[k] * norm_val, ivf_entity.cc:650); 1 for a plain store
       const float sc = a.rv.row_scale ? (valid ? a.rv.row_scale[r] : 1.f) : a.rv.score_scale;
 #pragma unroll
@@ -226,9 +256,9 @@ __global__ void __launch_bounds__(kThreads, QB == 1 ? 2 : 1) scan_gemv_kernel(co
   }
 }
 
-template <int DT, bool L2, int QB, bool SEG = false, int KU = kUmax>
+template <int DT, bool L2, int QB, bool SEG = false, int KU = kUmax, int PRE = 0>
 cudaError_t launch_one(const GemvArgs &a, int grid, size_t smem, cudaStream_t st, int grid_y = 1) {
-  auto kern = scan_gemv_kernel<DT, L2, QB, SEG, KU>;
+  auto kern = scan_gemv_kernel<DT, L2, QB, SEG, KU, PRE>;
   cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kMaxDynSmem);
   if (e == cudaSuccess && smem > (size_t)kMaxDynSmem) e = cudaErrorInvalidValue;
   if (e != cudaSuccess) return e;
@@ -237,8 +267,22 @@ cudaError_t launch_one(const GemvArgs &a, int grid, size_t smem, cudaStream_t st
   return cudaGetLastError();
 }
 
+// whole-row preload (PRE): int8 rows of at most kPre chunks per lane, kPreU row groups in flight (12 x 16 B per lane)
+constexpr int kPre = 3, kPreU = 4;
+static bool pre_applies(const RowsView &rv, int lpr_log2) {
+  static const int off = [] { const char *e = getenv("ZVB200_GEMV_PRE"); return e ? atoi(e) == 0 : 0; }();
+  return !off && rv.dtype == ZVB200_DT_INT8 && rv.chunks <= (uint32_t)(kPre << lpr_log2);
+}
+
 template <int DT, bool L2>
-cudaError_t launch_qb(const GemvArgs &a, int qb, int grid, size_t smem, cudaStream_t st) {
+cudaError_t launch_qb(const GemvArgs &a, int qb, int grid, size_t smem, cudaStream_t st, bool pre = false) {
+  if (DT == ZVB200_DT_INT8 && pre) {
+    switch (qb) {
+      case 1: return launch_one<ZVB200_DT_INT8, L2, 1, false, kPreU, kPre>(a, grid, smem, st);
+      case 2: return launch_one<ZVB200_DT_INT8, L2, 2, false, kPreU, kPre>(a, grid, smem, st);
+      default: return launch_one<ZVB200_DT_INT8, L2, 4, false, kPreU, kPre>(a, grid, smem, st);
+    }
+  }
   switch (qb) {
     case 1: return launch_one<DT, L2, 1>(a, grid, smem, st);
     case 2: return launch_one<DT, L2, 2>(a, grid, smem, st);
@@ -265,7 +309,8 @@ cudaError_t launch_scan_gemv(const RowsView &rv, const QueryView &qv, const Sear
   a.row_begin = row_begin; a.row_end = row_end; a.part = part;
   const int lg = pick_lpr_log2(rv.chunks);
   a.lpr_log2 = lg;
-  const uint64_t rows_per_tile = (uint64_t)kUmax * (32 >> lg) * kWarps;
+  const bool pre = pre_applies(rv, lg);
+  const uint64_t rows_per_tile = (uint64_t)(pre ? kPreU : kUmax) * (32 >> lg) * kWarps;
   const uint64_t nrows = row_end > row_begin ? row_end - row_begin : 0;
   uint64_t ntiles = (nrows + rows_per_tile - 1) / rows_per_tile;
   int grid = (int)std::min<uint64_t>(std::max<uint64_t>(ntiles, 1), (uint64_t)sm_count * 2);
@@ -291,8 +336,8 @@ cudaError_t launch_scan_gemv(const RowsView &rv, const QueryView &qv, const Sear
       e = l2 ? launch_qb<ZVB200_DT_FP16, true>(a, qb, grid, smem, st)
              : launch_qb<ZVB200_DT_FP16, false>(a, qb, grid, smem, st);
     else
-      e = l2 ? launch_qb<ZVB200_DT_INT8, true>(a, qb, grid, smem, st)
-             : launch_qb<ZVB200_DT_INT8, false>(a, qb, grid, smem, st);
+      e = l2 ? launch_qb<ZVB200_DT_INT8, true>(a, qb, grid, smem, st, pre)
+             : launch_qb<ZVB200_DT_INT8, false>(a, qb, grid, smem, st, pre);
     if (e != cudaSuccess) return e;
   }
   return cudaSuccess;

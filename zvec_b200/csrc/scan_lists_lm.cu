@@ -270,7 +270,7 @@ __device__ __forceinline__ void lm_scan_item(const LmArgs &a, const LmItem &it, 
       if (valid && a.rv.drop) valid = !bit_set(a.rv.drop, r);
       if (valid && a.filter) valid = !bit_set(a.filter, r);
       float4 mt = make_float4(0, 0, 0, 0);
-      if (metric_is_qi8(metric) && valid) mt = a.rv.tails[r];
+      if (metric_is_qi8(metric) && valid) mt = ldg_tail(a.rv.tails + r);  // read-only, no L1 allocation (scan_gemv.cu)
       // the row's score scale (IVFEntity::search: distances[k] * norm_val, ivf_entity.cc:650); 1 for a plain store
       const float sc = a.rv.row_scale ? (valid ? a.rv.row_scale[r] : 1.f) : a.rv.score_scale;
       if (spread) {
