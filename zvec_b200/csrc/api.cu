@@ -10,6 +10,7 @@ static std::atomic<uint64_t> g_launches{0};
 void count_launch(int n) { g_launches.fetch_add((uint64_t)n, std::memory_order_relaxed); }
 }  // namespace zvb
 
+std::atomic<uint64_t> g_buf_epoch{0};
 static thread_local std::string g_err;
 
 int zvb_set_err(int code, const char *what, const char *detail) {
@@ -141,7 +142,7 @@ int zvb200_store_destroy(zvb200_store *s) {
 
 int zvb200_store_reserve(zvb200_store *s, uint64_t rows) {
   if (!s) return set_err(ZVB200_ERR_INVALID_ARGUMENT, "null store");
-  std::lock_guard<std::shared_mutex> g(s->mu);
+  zvb200_store::Write g(s);
   if (int r = zvb_check_row_limit(rows)) return r;
   if (!s->shards.empty()) return zvb_sharded_reserve(s, rows);
   CU(cudaSetDevice(s->device));
@@ -162,7 +163,7 @@ static int append_common(zvb200_store *s, const uint8_t *src_dev, uint64_t at, u
 
 int zvb200_store_append(zvb200_store *s, const void *rows, uint64_t n, const uint64_t *keys) {
   if (!s || (!rows && n)) return set_err(ZVB200_ERR_INVALID_ARGUMENT, "null argument");
-  std::lock_guard<std::shared_mutex> g(s->mu);
+  zvb200_store::Write g(s);
   if (int r = zvb_check_row_limit(s->n + n)) return r;
   if (!s->shards.empty()) return zvb_sharded_append(s, rows, n, keys, false);
   CU(cudaSetDevice(s->device));
@@ -204,7 +205,7 @@ int zvb200_store_append(zvb200_store *s, const void *rows, uint64_t n, const uin
 
 int zvb200_store_append_device(zvb200_store *s, const void *rows_dev, uint64_t n) {
   if (!s || (!rows_dev && n)) return set_err(ZVB200_ERR_INVALID_ARGUMENT, "null argument");
-  std::lock_guard<std::shared_mutex> g(s->mu);
+  zvb200_store::Write g(s);
   if (int r = zvb_check_row_limit(s->n + n)) return r;
   if (!s->shards.empty()) return zvb_sharded_append(s, rows_dev, n, nullptr, true);
   CU(cudaSetDevice(s->device));
@@ -246,7 +247,7 @@ static int sync_drop(zvb200_store *s) {
 
 int zvb200_store_seal(zvb200_store *s) {
   if (!s) return set_err(ZVB200_ERR_INVALID_ARGUMENT, "null store");
-  std::lock_guard<std::shared_mutex> g(s->mu);
+  zvb200_store::Write g(s);
   if (!s->shards.empty()) return zvb_sharded_seal(s);
   CU(cudaSetDevice(s->device));
   int r = sync_drop(s);
@@ -301,7 +302,7 @@ uint64_t zvb200_store_scan_bytes(const zvb200_store *s) {
 
 int zvb200_store_set_operand_order(zvb200_store *s, int query_first) {
   if (!s) return set_err(ZVB200_ERR_INVALID_ARGUMENT, "null store");
-  std::lock_guard<std::shared_mutex> g(s->mu);
+  zvb200_store::Write g(s);
   s->query_first = query_first != 0;
   for (auto *sh : s->shards) sh->query_first = s->query_first;
   // the IVF centroid index is a nested FlatSearcher (ivf_centroid_index.cc:273-295): feature first, left as it is
@@ -310,7 +311,7 @@ int zvb200_store_set_operand_order(zvb200_store *s, int query_first) {
 
 int zvb200_store_set_deleted(zvb200_store *s, uint64_t row, int deleted) {
   if (!s) return set_err(ZVB200_ERR_INVALID_ARGUMENT, "null store");
-  std::lock_guard<std::shared_mutex> g(s->mu);
+  zvb200_store::Write g(s);
   if (!s->shards.empty()) return zvb_sharded_set_deleted(s, row, deleted);
   if (row >= s->n) return set_err(ZVB200_ERR_INVALID_ARGUMENT, "bad row");
   s->drop_host.resize((s->n + 31) / 32, 0u);
@@ -323,7 +324,7 @@ int zvb200_store_set_deleted(zvb200_store *s, uint64_t row, int deleted) {
 
 int zvb200_store_write(zvb200_store *s, uint64_t row, const void *vec, uint64_t key) {
   if (!s || !vec) return set_err(ZVB200_ERR_INVALID_ARGUMENT, "bad argument");
-  std::lock_guard<std::shared_mutex> g(s->mu);
+  zvb200_store::Write g(s);
   if (!s->shards.empty()) return zvb_sharded_write(s, row, vec, key);
   if (row >= s->n) return set_err(ZVB200_ERR_INVALID_ARGUMENT, "bad row");
   CU(cudaSetDevice(s->device));
@@ -393,6 +394,7 @@ int zvb200_ctx_destroy(zvb200_ctx *c) {
   zvb_sharded_ctx_destroy(c);
   cudaSetDevice(c->device);
   cudaStreamSynchronize(c->stream);
+  c->rg.reset();
   c->xkeys.release(); c->gather.release(); c->out_rows.release(); c->h_rows.release();
   DevBuf *d[] = {&c->qin, &c->qin2, &c->qf32, &c->qraw, &c->qtails, &c->qnorms, &c->part, &c->out_scores,
                  &c->out_index, &c->filter, &c->misc, &c->gtau, &c->coarse_scores, &c->coarse_index,
@@ -547,7 +549,7 @@ int zvb_search_core(zvb200_ctx *c, zvb200_store *s, const void *queries_dev, uin
   if (group >= 128) group &= ~127u; else if (group >= 64) group &= ~63u; else if (group >= 4) group &= ~3u;
   group = std::min(group, q);
   CU(c->part.ensure((size_t)group * per_query));
-  CU(cudaEventRecord(c->ev_scan0, c->stream));
+  CU(zvb_scan_event(c, c->ev_scan0));
   c->scan_timed = true;
   for (uint32_t q0 = 0; q0 < q; q0 += group) {
     const uint32_t qn = std::min(group, q - q0);
@@ -573,7 +575,7 @@ int zvb_search_core(zvb200_ctx *c, zvb200_store *s, const void *queries_dev, uin
                          s->sm_count, c->stream, &c->last_mma_kind));
       c->last_kernel = "scan_mma";
     }
-    if (q0 + group >= q) CU(cudaEventRecord(c->ev_scan1, c->stream));
+    if (q0 + group >= q) CU(zvb_scan_event(c, c->ev_scan1));
     CU(launch_merge_parts((const u64 *)c->part.p, nparts, qn, k, out_scores_dev ? out_scores_dev + (size_t)q0 * k : nullptr,
                           out_index_dev ? out_index_dev + (size_t)q0 * k : nullptr,
                           out_keys_dev ? out_keys_dev + (size_t)q0 * k : nullptr, c->stream));
@@ -589,14 +591,91 @@ static int search_core(zvb200_ctx *c, zvb200_store *s, const void *queries_dev, 
                          row_begin, row_end);
 }
 
+// ---- small searches as one CUDA graph (host.h: ReplayGraph) -------------------------------------------------
+static bool graphs_enabled() {
+  static const bool on = [] { const char *e = getenv("ZVB200_GRAPH"); return !e || atoi(e) != 0; }();
+  return on;
+}
+constexpr uint32_t kGraphMaxQueries = 8;  // beyond, the kernels are long and the launches overlap them anyway
+
+static GraphKey graph_key(const zvb200_ctx *c, int fn, uint32_t q, uint32_t k, float threshold, uint64_t rows,
+                          uint32_t nprobe = 0, uint64_t max_scan = 0) {
+  GraphKey key;
+  memset(&key, 0, sizeof key);
+  key.fn = fn; key.store = c->s; key.gen = c->s->gen; key.epoch = g_buf_epoch.load(std::memory_order_relaxed);
+  key.rows = rows; key.max_scan = max_scan; key.q = q; key.k = k; key.nprobe = nprobe;
+  memcpy(&key.thr_bits, &threshold, 4);
+  key.mma_group_cap = c->mma_group_cap; key.force_kernel = c->force_kernel; key.operand_order = c->operand_order;
+  return key;
+}
+
+// enqueue() puts the whole search on the context's stream (copies included) and returns 0; this runs it directly,
+// records it (second call with one key) or replays the recording.  The caller synchronises afterwards.
+template <class F>
+static int run_replayable(zvb200_ctx *c, const GraphKey &key, bool eligible, F &&enqueue) {
+  ReplayGraph &g = c->rg;
+  if (!eligible || !graphs_enabled() || !c->sub.empty()) return enqueue();
+  const bool same = g.seen > 0 && memcmp(&g.key, &key, sizeof key) == 0;
+  if (same && g.exec) {
+    CU(cudaGraphLaunch(g.exec, c->stream));
+    count_launch((int)g.launches);
+    c->last_kernel = g.last_kernel; c->last_mma_kind = g.last_mma_kind;
+    return 0;
+  }
+  if (!same) {  // first call with these arguments: run it, every buffer gets its size
+    g.reset();
+    g.key = key; g.seen = 1;
+    const int r = enqueue();
+    g.key.epoch = g_buf_epoch.load(std::memory_order_relaxed);  // what this very call allocated is part of the state
+    return r;
+  }
+  if (g.failed) return enqueue();
+  const uint64_t l0 = g_launches.load();
+  if (cudaStreamBeginCapture(c->stream, cudaStreamCaptureModeThreadLocal) != cudaSuccess) {
+    cudaGetLastError();
+    g.failed = true;
+    return enqueue();
+  }
+  c->capturing = true;
+  const int r = enqueue();
+  c->capturing = false;
+  cudaGraph_t graph = nullptr;
+  cudaError_t e = cudaStreamEndCapture(c->stream, &graph);
+  const uint32_t launched = (uint32_t)(g_launches.load() - l0);
+  if (r == 0 && e == cudaSuccess && graph && g_buf_epoch.load(std::memory_order_relaxed) == key.epoch)
+    e = cudaGraphInstantiate(&g.exec, graph, 0);
+  else if (e == cudaSuccess)
+    e = cudaErrorUnknown;
+  if (graph) cudaGraphDestroy(graph);
+  if (e != cudaSuccess || !g.exec) {  // nothing ran: the captured work was only recorded
+    cudaGetLastError();
+    if (g.exec) { cudaGraphExecDestroy(g.exec); g.exec = nullptr; }
+    g.failed = true;
+    if (r != 0) return r;
+    return enqueue();
+  }
+  g.launches = launched; g.last_kernel = c->last_kernel; g.last_mma_kind = c->last_mma_kind;
+  count_launch(-(int)launched);  // counted while recording, not launched yet
+  CU(cudaGraphLaunch(g.exec, c->stream));
+  count_launch((int)launched);
+  return 0;
+}
+
 // device results of the context -> host outputs, document keys and per-query counts
-static int finish_results(zvb200_ctx *c, zvb200_store *s, uint32_t q, uint32_t k, uint64_t *out_keys, float *out_scores,
-                          uint32_t *out_index, uint32_t *out_counts) {
+static int queue_result_copies(zvb200_ctx *c, uint32_t q, uint32_t k) {
   const size_t nres = (size_t)q * k;
-  CU(c->h_scores.ensure(nres * 4));
-  CU(c->h_index.ensure(nres * 4));
   CU(cudaMemcpyAsync(c->h_scores.p, c->out_scores.p, nres * 4, cudaMemcpyDeviceToHost, c->stream));
   CU(cudaMemcpyAsync(c->h_index.p, c->out_index.p, nres * 4, cudaMemcpyDeviceToHost, c->stream));
+  return 0;
+}
+static int finish_results(zvb200_ctx *c, zvb200_store *s, uint32_t q, uint32_t k, uint64_t *out_keys, float *out_scores,
+                          uint32_t *out_index, uint32_t *out_counts, bool copies_queued = false) {
+  const size_t nres = (size_t)q * k;
+  if (!copies_queued) {
+    CU(c->h_scores.ensure(nres * 4));
+    CU(c->h_index.ensure(nres * 4));
+    if (int r = queue_result_copies(c, q, k)) return r;
+  }
   CU(cudaStreamSynchronize(c->stream));
   const float *hs = (const float *)c->h_scores.p;
   const uint32_t *hi = (const uint32_t *)c->h_index.p;
@@ -635,11 +714,11 @@ int zvb_rows_core(zvb200_ctx *c, zvb200_store *s, const void *queries_dev, uint3
   const size_t parts = scan_lists_parts(q, s->sm_count);
   CU(c->part.ensure((size_t)q * parts * k * sizeof(u64)));
   uint32_t nparts = 0;
-  CU(cudaEventRecord(c->ev_scan0, c->stream));
+  CU(zvb_scan_event(c, c->ev_scan0));
   c->scan_timed = true;
   CU(launch_scan_lists(rv, qv, sp, (const uint32_t *)c->seg_prefix.p, (const uint32_t *)c->seg_row.p,
                        (const uint32_t *)c->seg_count.p, m, (u64 *)c->part.p, &nparts, s->sm_count, c->stream));
-  CU(cudaEventRecord(c->ev_scan1, c->stream));
+  CU(zvb_scan_event(c, c->ev_scan1));
   c->last_kernel = "scan_rows";
   CU(launch_merge_parts((const u64 *)c->part.p, nparts, q, k, out_scores_dev, out_index_dev, out_keys_dev, c->stream));
   return 0;
@@ -683,7 +762,11 @@ int zvb200_search_device(zvb200_ctx *c, const void *queries_dev, uint32_t q, uin
     return zvb_sharded_search(c, queries_dev, false, q, k, threshold, filter_dev, nullptr, 0, out_scores_dev, out_index_dev);
   CU(cudaSetDevice(c->s->device));
   const uint64_t rows = c->row_limit ? std::min<uint64_t>(c->row_limit, c->s->n) : c->s->n;
-  return search_core(c, c->s, queries_dev, q, k, threshold, filter_dev, out_scores_dev, out_index_dev, 0, rows);
+  GraphKey key = graph_key(c, 4, q, k, threshold, rows);
+  key.p0 = queries_dev; key.p1 = filter_dev; key.p2 = out_scores_dev; key.p3 = out_index_dev;
+  return run_replayable(c, key, q <= kGraphMaxQueries, [&]() -> int {
+    return search_core(c, c->s, queries_dev, q, k, threshold, filter_dev, out_scores_dev, out_index_dev, 0, rows);
+  });
 }
 
 int zvb200_search(zvb200_ctx *c, const void *queries, uint32_t q, uint32_t k, float threshold,
@@ -714,18 +797,21 @@ int zvb200_search(zvb200_ctx *c, const void *queries, uint32_t q, uint32_t k, fl
   CU(c->h_q.ensure(qbytes));
   CU(c->qin.ensure(qbytes));
   memcpy(c->h_q.p, queries, qbytes);
-  CU(cudaMemcpyAsync(c->qin.p, c->h_q.p, qbytes, cudaMemcpyHostToDevice, c->stream));
-  const uint32_t *fdev = nullptr;
-  if (filter) {
-    const size_t fb = ((rows + 31) / 32) * 4;
-    CU(c->filter.ensure(fb));
-    CU(cudaMemcpyAsync(c->filter.p, filter, fb, cudaMemcpyHostToDevice, c->stream));
-    fdev = (const uint32_t *)c->filter.p;
-  }
-  r = search_core(c, s, c->qin.p, q, k, threshold, fdev, (float *)c->out_scores.p,
-                  (uint32_t *)c->out_index.p, 0, rows);
+  r = run_replayable(c, graph_key(c, 1, q, k, threshold, rows), !filter && q <= kGraphMaxQueries, [&]() -> int {
+    CU(cudaMemcpyAsync(c->qin.p, c->h_q.p, qbytes, cudaMemcpyHostToDevice, c->stream));
+    const uint32_t *fdev = nullptr;
+    if (filter) {
+      const size_t fb = ((rows + 31) / 32) * 4;
+      CU(c->filter.ensure(fb));
+      CU(cudaMemcpyAsync(c->filter.p, filter, fb, cudaMemcpyHostToDevice, c->stream));
+      fdev = (const uint32_t *)c->filter.p;
+    }
+    const int rr = search_core(c, s, c->qin.p, q, k, threshold, fdev, (float *)c->out_scores.p,
+                               (uint32_t *)c->out_index.p, 0, rows);
+    return rr != 0 ? rr : queue_result_copies(c, q, k);
+  });
   if (r != 0) return r;
-  return finish_results(c, s, q, k, out_keys, out_scores, out_index, out_counts);
+  return finish_results(c, s, q, k, out_keys, out_scores, out_index, out_counts, true);
 }
 
 int zvb200_merge_topk_device(zvb200_ctx *c, const float *scores_dev, const uint32_t *index_dev,
@@ -864,7 +950,7 @@ int zvb200_ivf_attach_typed(zvb200_store *s, const void *centroids, uint32_t nli
     if (cs) zvb200_store_destroy(cs);
     return r;
   }
-  std::lock_guard<std::shared_mutex> g(s->mu);
+  zvb200_store::Write g(s);
   if (s->centroids) zvb200_store_destroy(s->centroids);
   if (s->list_off_dev) cudaFree(s->list_off_dev);
   if (s->budget_dev) { cudaFree(s->budget_dev); s->budget_dev = nullptr; }
@@ -878,7 +964,7 @@ int zvb200_ivf_attach_typed(zvb200_store *s, const void *centroids, uint32_t nli
 
 int zvb200_ivf_set_budget_sizes(zvb200_store *s, const uint64_t *list_sizes) {
   if (!s || !s->centroids) return set_err(ZVB200_ERR_NOREADY, "no IVF structure attached");
-  std::lock_guard<std::shared_mutex> g(s->mu);
+  zvb200_store::Write g(s);
   CU(cudaSetDevice(s->device));
   if (s->budget_dev) { cudaFree(s->budget_dev); s->budget_dev = nullptr; }
   if (!list_sizes) return 0;
@@ -973,12 +1059,12 @@ static int ivf_core(zvb200_ctx *c, const void *queries_dev, uint32_t q, uint32_t
     CU(c->lm.ensure(scan_lists_lm_scratch_words(q, nprobe, s->nlist) * 4));
     CU(c->part.ensure((size_t)q * nprobe * k * sizeof(u64)));
     uint32_t nparts = 0;
-    CU(cudaEventRecord(c->ev_scan0, c->stream));
+    CU(zvb_scan_event(c, c->ev_scan0));
     c->scan_timed = true;
     CU(launch_scan_lists_lm(rv, c->last_qv, sp, (const uint32_t *)c->seg_list.p, (const uint32_t *)c->seg_count.p, nprobe,
                             s->list_off_dev, s->nlist, (uint32_t *)c->lm.p, (u64 *)c->part.p, &nparts, s->sm_count,
                             c->stream));
-    CU(cudaEventRecord(c->ev_scan1, c->stream));
+    CU(zvb_scan_event(c, c->ev_scan1));
     c->last_kernel = "scan_lists_lm";
     CU(launch_merge_parts((const u64 *)c->part.p, nparts, q, k, out_scores_dev, out_index_dev, nullptr, c->stream));
     return 0;
@@ -987,7 +1073,7 @@ static int ivf_core(zvb200_ctx *c, const void *queries_dev, uint32_t q, uint32_t
   const size_t parts = lists_stream ? scan_lists_stream_parts(q, s->sm_count) : scan_lists_parts(q, s->sm_count);
   CU(c->part.ensure((size_t)q * parts * k * sizeof(u64)));
   uint32_t nparts = 0;
-  CU(cudaEventRecord(c->ev_scan0, c->stream));
+  CU(zvb_scan_event(c, c->ev_scan0));
   c->scan_timed = true;
   if (lists_stream)
     CU(launch_scan_lists_stream(rv, c->last_qv, sp, (const uint32_t *)c->seg_prefix.p, (const uint32_t *)c->seg_row.p,
@@ -998,7 +1084,7 @@ static int ivf_core(zvb200_ctx *c, const void *queries_dev, uint32_t q, uint32_t
                          (const uint32_t *)c->seg_count.p, nprobe, (u64 *)c->part.p, &nparts, s->sm_count, c->stream,
                          // what one query scans: the budget plus, on average, half of the list that crosses it
                          std::min<uint64_t>(s->n, max_scan_count + s->n / std::max<uint32_t>(1, s->nlist) / 2)));
-  CU(cudaEventRecord(c->ev_scan1, c->stream));
+  CU(zvb_scan_event(c, c->ev_scan1));
   c->last_kernel = lists_stream ? "scan_lists_stream" : "scan_lists";
   CU(launch_merge_parts((const u64 *)c->part.p, nparts, q, k, out_scores_dev, out_index_dev, nullptr, c->stream));
   return 0;
@@ -1032,18 +1118,22 @@ int zvb200_ivf_search(zvb200_ctx *c, const void *queries, uint32_t q, uint32_t k
   CU(c->h_scores.ensure(nres * 4));
   CU(c->h_index.ensure(nres * 4));
   memcpy(c->h_q.p, queries, qbytes);
-  CU(cudaMemcpyAsync(c->qin.p, c->h_q.p, qbytes, cudaMemcpyHostToDevice, c->stream));
-  const uint32_t *fdev = nullptr;
-  if (filter_bitmap) {
-    const size_t fb = (size_t)((s->n + 31) / 32) * 4;
-    CU(c->filter.ensure(fb));
-    CU(cudaMemcpyAsync(c->filter.p, filter_bitmap, fb, cudaMemcpyHostToDevice, c->stream));
-    fdev = (const uint32_t *)c->filter.p;
-  }
-  r = ivf_core(c, c->qin.p, q, k, nprobe, max_scan_count, threshold, fdev, (float *)c->out_scores.p,
-               (uint32_t *)c->out_index.p);
+  r = run_replayable(c, graph_key(c, 2, q, k, threshold, s->n, nprobe, max_scan_count),
+                     !filter_bitmap && q <= kGraphMaxQueries, [&]() -> int {
+    CU(cudaMemcpyAsync(c->qin.p, c->h_q.p, qbytes, cudaMemcpyHostToDevice, c->stream));
+    const uint32_t *fdev = nullptr;
+    if (filter_bitmap) {
+      const size_t fb = (size_t)((s->n + 31) / 32) * 4;
+      CU(c->filter.ensure(fb));
+      CU(cudaMemcpyAsync(c->filter.p, filter_bitmap, fb, cudaMemcpyHostToDevice, c->stream));
+      fdev = (const uint32_t *)c->filter.p;
+    }
+    const int rr = ivf_core(c, c->qin.p, q, k, nprobe, max_scan_count, threshold, fdev, (float *)c->out_scores.p,
+                            (uint32_t *)c->out_index.p);
+    return rr != 0 ? rr : queue_result_copies(c, q, k);
+  });
   if (r != 0) return r;
-  return finish_results(c, s, q, k, out_keys, out_scores, out_index, out_counts);
+  return finish_results(c, s, q, k, out_keys, out_scores, out_index, out_counts, true);
 }
 
 int zvb200_ivf_search_device(zvb200_ctx *c, const void *queries_dev, uint32_t q, uint32_t k, uint32_t nprobe,
@@ -1055,7 +1145,11 @@ int zvb200_ivf_search_device(zvb200_ctx *c, const void *queries_dev, uint32_t q,
   if (!out_scores_dev || !out_index_dev) return set_err(ZVB200_ERR_INVALID_ARGUMENT, "null output");
   if (q == 0) return 0;
   CU(cudaSetDevice(c->s->device));
-  return ivf_core(c, queries_dev, q, k, nprobe, max_scan_count, threshold, filter_dev, out_scores_dev, out_index_dev);
+  GraphKey key = graph_key(c, 5, q, k, threshold, c->s->n, nprobe, max_scan_count);
+  key.p0 = queries_dev; key.p1 = filter_dev; key.p2 = out_scores_dev; key.p3 = out_index_dev;
+  return run_replayable(c, key, q <= kGraphMaxQueries, [&]() -> int {
+    return ivf_core(c, queries_dev, q, k, nprobe, max_scan_count, threshold, filter_dev, out_scores_dev, out_index_dev);
+  });
 }
 
 static const uint32_t *upload_filter(zvb200_ctx *c, zvb200_store *s, const uint32_t *filter, int *err);
@@ -1078,17 +1172,23 @@ int zvb200_ivf_search_split(zvb200_ctx *c, const void *coarse_queries, const voi
   CU(c->qin2.ensure(lbytes));
   CU(c->out_scores.ensure(nres * 4));
   CU(c->out_index.ensure(nres * 4));
+  CU(c->h_scores.ensure(nres * 4));
+  CU(c->h_index.ensure(nres * 4));
   memcpy(c->h_q.p, coarse_queries, cbytes);
   memcpy(c->h_q2.p, list_queries, lbytes);
-  CU(cudaMemcpyAsync(c->qin.p, c->h_q.p, cbytes, cudaMemcpyHostToDevice, c->stream));
-  CU(cudaMemcpyAsync(c->qin2.p, c->h_q2.p, lbytes, cudaMemcpyHostToDevice, c->stream));
-  int fe = 0;
-  const uint32_t *fdev = upload_filter(c, s, filter_bitmap, &fe);
-  if (fe != 0) return fe;
-  r = ivf_core(c, c->qin.p, q, k, nprobe, max_scan_count, threshold, fdev, (float *)c->out_scores.p,
-               (uint32_t *)c->out_index.p, c->qin2.p);
+  r = run_replayable(c, graph_key(c, 3, q, k, threshold, s->n, nprobe, max_scan_count),
+                     !filter_bitmap && q <= kGraphMaxQueries, [&]() -> int {
+    CU(cudaMemcpyAsync(c->qin.p, c->h_q.p, cbytes, cudaMemcpyHostToDevice, c->stream));
+    CU(cudaMemcpyAsync(c->qin2.p, c->h_q2.p, lbytes, cudaMemcpyHostToDevice, c->stream));
+    int fe = 0;
+    const uint32_t *fdev = upload_filter(c, s, filter_bitmap, &fe);
+    if (fe != 0) return fe;
+    const int rr = ivf_core(c, c->qin.p, q, k, nprobe, max_scan_count, threshold, fdev, (float *)c->out_scores.p,
+                            (uint32_t *)c->out_index.p, c->qin2.p);
+    return rr != 0 ? rr : queue_result_copies(c, q, k);
+  });
   if (r != 0) return r;
-  return finish_results(c, s, q, k, out_keys, out_scores, out_index, out_counts);
+  return finish_results(c, s, q, k, out_keys, out_scores, out_index, out_counts, true);
 }
 
 int zvb200_store_set_score_scale(zvb200_store *s, float scale, const float *list_scales) {
@@ -1097,7 +1197,7 @@ int zvb200_store_set_score_scale(zvb200_store *s, float scale, const float *list
   if (!(scale == scale) || (list_scales && !s->centroids))
     return set_err(list_scales ? ZVB200_ERR_NOREADY : ZVB200_ERR_INVALID_ARGUMENT,
                    list_scales ? "per-list scales need an attached IVF structure" : "scale is NaN");
-  std::lock_guard<std::shared_mutex> g(s->mu);
+  zvb200_store::Write g(s);
   CU(cudaSetDevice(s->device));
   if (s->row_scale) { cudaFree(s->row_scale); s->row_scale = nullptr; }
   s->score_scale = scale;
@@ -1119,7 +1219,7 @@ int zvb200_store_set_score_scale(zvb200_store *s, float scale, const float *list
 
 int zvb200_ivf_set_global_bases(zvb200_store *s, const uint64_t *list_global_base) {
   if (!s || !s->centroids) return set_err(ZVB200_ERR_NOREADY, "no IVF structure attached");
-  std::lock_guard<std::shared_mutex> g(s->mu);
+  zvb200_store::Write g(s);
   CU(cudaSetDevice(s->device));
   if (s->gbase_dev) { cudaFree(s->gbase_dev); s->gbase_dev = nullptr; }
   if (!list_global_base) return 0;
@@ -1329,7 +1429,7 @@ int zvb200_search_refined(zvb200_ctx *coarse, zvb200_ctx *exact, const float *qu
 // over a store of the current centroids (queries = the rows, 18 944 per tcgen05 launch) + the update kernels.
 
 static void store_reset(zvb200_store *s) {
-  std::lock_guard<std::shared_mutex> g(s->mu);
+  zvb200_store::Write g(s);
   s->n = 0; s->normed = 0; s->shadowed = 0;
   s->keys.clear(); s->drop_host.clear();
   s->has_drop = false; s->drop_dirty = false; s->drop_synced = 0; s->sealed = false;

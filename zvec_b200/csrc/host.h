@@ -59,6 +59,7 @@ struct zvb200_store {
   uint32_t *budget_dev = nullptr;    // [nlist] list sizes in the whole index (sharded IVF), or null
   uint64_t *gbase_dev = nullptr;     // [nlist] row of the whole index where this store's slice of each list starts
   uint32_t nlist = 0;
+  uint64_t gen = 0;                  // bumped under the writers' lock: whatever a recorded search was built from may have changed
   float *row_scale = nullptr;        // [n] zvb200_store_set_score_scale with per-list values, expanded per row
   float score_scale = 1.f;
   bool coarse_typed = false;         // centroids in a layout of their own (zvb200_ivf_attach_typed): split queries only
@@ -67,6 +68,10 @@ struct zvb200_store {
   // cannot free them under a search another thread has in flight (FlatStreamer adds race with searches,
   // tests/core/algorithm/flat/flat_streamer_test.cc:509-730)
   std::shared_mutex mu;
+  struct Write {  // the writers' lock
+    std::lock_guard<std::shared_mutex> g;
+    explicit Write(zvb200_store *s) : g(s->mu) { ++s->gen; }
+  };
   // Sharded parent (zvb200_store_create_sharded over several devices of this process): contiguous row
   // ranges, shard g holds rows [g * shard_rows, (g + 1) * shard_rows) of the store; the parent itself holds no rows,
   // only the layout, the row count and the keys.  shard_rows is fixed by the first zvb200_store_reserve.
@@ -86,11 +91,15 @@ struct zvb200_store {
   }
 };
 
+// bumped by every re-allocation of a context buffer: a recorded search (ReplayGraph) holds the old pointers
+extern std::atomic<uint64_t> g_buf_epoch;
+
 struct DevBuf {
   void *p = nullptr;
   size_t cap = 0;
   cudaError_t ensure(size_t bytes) {
     if (bytes <= cap) return cudaSuccess;
+    g_buf_epoch.fetch_add(1, std::memory_order_relaxed);
     if (p) cudaFree(p);
     p = nullptr; cap = 0;
     size_t want = std::max(bytes, (size_t)4096);
@@ -105,6 +114,7 @@ struct HostBuf {
   size_t cap = 0;
   cudaError_t ensure(size_t bytes) {
     if (bytes <= cap) return cudaSuccess;
+    g_buf_epoch.fetch_add(1, std::memory_order_relaxed);
     if (p) cudaFreeHost(p);
     p = nullptr; cap = 0;
     size_t want = std::max(bytes, (size_t)4096);
@@ -113,6 +123,32 @@ struct HostBuf {
     return e;
   }
   void release() { if (p) cudaFreeHost(p); p = nullptr; cap = 0; }
+};
+
+// A small host-side search recorded as ONE CUDA graph (H2D of the queries, every kernel of the search, D2H of the
+// results): the second call of a context with the same arguments records it, later ones replay it with one
+// cudaGraphLaunch.  The key holds everything the launches were built from; the store's generation (bumped by every
+// writer) and the buffer epoch (bumped by every re-allocation) retire a stale recording.
+struct GraphKey {
+  int fn;                 // 1 zvb200_search, 2 zvb200_ivf_search, 3 zvb200_ivf_search_split
+  const void *store;
+  uint64_t gen, epoch, rows, max_scan;
+  uint32_t q, k, nprobe, thr_bits, mma_group_cap;
+  int force_kernel, operand_order;
+  const void *p0, *p1, *p2, *p3;  // the device-pointer forms: queries, filter, outputs
+};
+struct ReplayGraph {
+  GraphKey key;
+  int seen = 0;
+  bool failed = false;
+  cudaGraphExec_t exec = nullptr;
+  uint32_t launches = 0;
+  const char *last_kernel = "none";
+  int last_mma_kind = -1;
+  void reset() {
+    if (exec) cudaGraphExecDestroy(exec);
+    exec = nullptr; seen = 0; failed = false; launches = 0;
+  }
 };
 
 struct zvb200_ctx {
@@ -131,6 +167,8 @@ struct zvb200_ctx {
   const char *last_kernel = "none";
   cudaEvent_t ev_scan0 = nullptr, ev_scan1 = nullptr;  // bracket the scan kernel(s) of the last search
   bool scan_timed = false;
+  ReplayGraph rg;
+  bool capturing = false;  // inside cudaStreamBeginCapture: nothing may allocate
   int operand_order = -1;  // zvb200_ctx_set_operand_order: -1 the store's, 0 feature first, 1 query first
   uint64_t row_limit = 0;  // zvb200_ctx_set_row_limit: searches see rows [0, row_limit) only (0 = every row)
   // a context of a sharded parent: one context per shard (on the shard's device), the exchange buffers on the root
@@ -140,6 +178,12 @@ struct zvb200_ctx {
   DevBuf xkeys, gather, out_rows;  // packed local keys; [G][q][k] gathered keys; merged global rows
   HostBuf h_rows;
 };
+
+// the events that bracket a search's scan kernels; inside a recording they become event-record nodes of the graph
+// (cudaEventRecordExternal), so zvb200_ctx_last_scan_ms keeps working for replayed searches
+inline cudaError_t zvb_scan_event(zvb200_ctx *c, cudaEvent_t ev) {
+  return c->capturing ? cudaEventRecordWithFlags(ev, c->stream, cudaEventRecordExternal) : cudaEventRecord(ev, c->stream);
+}
 
 // ---- sharded parents (multi.cu), called by the C ABI entry points of api.cu when store->shards is not empty ----
 int zvb_sharded_destroy(zvb200_store *s);

@@ -148,23 +148,25 @@ __global__ void __launch_bounds__(kThreads, QB == 1 ? 2 : 1) scan_gemv_kernel(co
       for (int j = 0; j < QB; ++j) acc[u][j] = 0;
     }
     if (PRE > 0) {
-      uint4 v[PRE > 0 ? PRE : 1][kU];
+      for (uint32_t c0 = l; c0 < C; c0 += PRE * lpr) {
+        uint4 v[PRE > 0 ? PRE : 1][kU];
 #pragma unroll
-      for (int i = 0; i < PRE; ++i) {
-        const uint32_t c = l + i * lpr;
+        for (int i = 0; i < PRE; ++i) {
+          const uint32_t c = c0 + i * lpr;
 #pragma unroll
-        for (int u = 0; u < kU; ++u) v[i][u] = c < C ? ldg_stream(rp[u] + (size_t)c * 16) : make_uint4(0, 0, 0, 0);
-      }
+          for (int u = 0; u < kU; ++u) v[i][u] = c < C ? ldg_stream(rp[u] + (size_t)c * 16) : make_uint4(0, 0, 0, 0);
+        }
 #pragma unroll
-      for (int i = 0; i < PRE; ++i) {
-        const uint32_t c = l + i * lpr;
-        if (c < C) {
+        for (int i = 0; i < PRE; ++i) {
+          const uint32_t c = c0 + i * lpr;
+          if (c < C) {
 #pragma unroll
-          for (int j = 0; j < QB; ++j) {
+            for (int j = 0; j < QB; ++j) {
 #pragma unroll
-            for (int u = 0; u < kU; ++u) {
-              Acc dummy = 0;
-              CK::fma(acc[u][j], j == 0 ? aa[u] : dummy, v[i][u], qs + (size_t)j * qbytes, c);
+              for (int u = 0; u < kU; ++u) {
+                Acc dummy = 0;
+                CK::fma(acc[u][j], j == 0 ? aa[u] : dummy, v[i][u], qs + (size_t)j * qbytes, c);
+              }
             }
           }
         }
@@ -269,18 +271,27 @@ cudaError_t launch_one(const GemvArgs &a, int grid, size_t smem, cudaStream_t st
 
 // whole-row preload (PRE): int8 rows of at most kPre chunks per lane, kPreU row groups in flight (12 x 16 B per lane)
 constexpr int kPre = 3, kPreU = 4;
-static bool pre_applies(const RowsView &rv, int lpr_log2) {
-  static const int off = [] { const char *e = getenv("ZVB200_GEMV_PRE"); return e ? atoi(e) == 0 : 0; }();
-  return !off && rv.dtype == ZVB200_DT_INT8 && rv.chunks <= (uint32_t)(kPre << lpr_log2);
+// Where it pays (B200, batch 1 unless noted): 96-B int8 rows 5.0 -> 5.5 TB/s, QuantizedInteger 96-B rows 4.9 -> 5.1,
+// QuantizedInteger d = 768 5.6 -> 6.2, fp32 d = 1536 7.0 -> 7.3, fp16 d = 768 with 4 queries 8.9 -> 8.1 ms; where it does not:
+// 512-B fp32 rows (8 chunks per lane = trips of 3, 3, 2: 6.9 -> 6.6 TB/s) and scans of a few tiles per CTA (the 16 384
+// centroids of C4: 64-row tiles are one round of the grid, 32-row tiles two).
+static bool pre_applies(const RowsView &rv, int lpr_log2, uint64_t rows, int grid) {
+  static const int mode = [] { const char *e = getenv("ZVB200_GEMV_PRE"); return e ? atoi(e) : 1; }();
+  if (mode != 1) return mode == 2;
+  const uint32_t per_lane = (rv.chunks + (1u << lpr_log2) - 1) >> lpr_log2;
+  const bool short_int8 = rv.dtype == ZVB200_DT_INT8 && per_lane <= (uint32_t)kPre;
+  const bool long_rows = rv.row_stride >= 768 && per_lane % kPre == 0;
+  const uint64_t tile = (uint64_t)kPreU * (32 >> lpr_log2) * kWarps;
+  return (short_int8 || long_rows) && rows >= 4 * tile * (uint64_t)grid;
 }
 
 template <int DT, bool L2>
 cudaError_t launch_qb(const GemvArgs &a, int qb, int grid, size_t smem, cudaStream_t st, bool pre = false) {
-  if (DT == ZVB200_DT_INT8 && pre) {
+  if (pre) {
     switch (qb) {
-      case 1: return launch_one<ZVB200_DT_INT8, L2, 1, false, kPreU, kPre>(a, grid, smem, st);
-      case 2: return launch_one<ZVB200_DT_INT8, L2, 2, false, kPreU, kPre>(a, grid, smem, st);
-      default: return launch_one<ZVB200_DT_INT8, L2, 4, false, kPreU, kPre>(a, grid, smem, st);
+      case 1: return launch_one<DT, L2, 1, false, kPreU, kPre>(a, grid, smem, st);
+      case 2: return launch_one<DT, L2, 2, false, kPreU, kPre>(a, grid, smem, st);
+      default: return launch_one<DT, L2, 4, false, kPreU, kPre>(a, grid, smem, st);
     }
   }
   switch (qb) {
@@ -309,7 +320,8 @@ cudaError_t launch_scan_gemv(const RowsView &rv, const QueryView &qv, const Sear
   a.row_begin = row_begin; a.row_end = row_end; a.part = part;
   const int lg = pick_lpr_log2(rv.chunks);
   a.lpr_log2 = lg;
-  const bool pre = pre_applies(rv, lg);
+  const uint64_t nrows0 = row_end > row_begin ? row_end - row_begin : 0;
+  const bool pre = pre_applies(rv, lg, nrows0, sm_count * 2);
   const uint64_t rows_per_tile = (uint64_t)(pre ? kPreU : kUmax) * (32 >> lg) * kWarps;
   const uint64_t nrows = row_end > row_begin ? row_end - row_begin : 0;
   uint64_t ntiles = (nrows + rows_per_tile - 1) / rows_per_tile;
@@ -330,11 +342,11 @@ cudaError_t launch_scan_gemv(const RowsView &rv, const QueryView &qv, const Sear
     a.q0 = q0;
     cudaError_t e;
     if (rv.dtype == ZVB200_DT_FP32)
-      e = l2 ? launch_qb<ZVB200_DT_FP32, true>(a, qb, grid, smem, st)
-             : launch_qb<ZVB200_DT_FP32, false>(a, qb, grid, smem, st);
+      e = l2 ? launch_qb<ZVB200_DT_FP32, true>(a, qb, grid, smem, st, pre)
+             : launch_qb<ZVB200_DT_FP32, false>(a, qb, grid, smem, st, pre);
     else if (rv.dtype == ZVB200_DT_FP16)
-      e = l2 ? launch_qb<ZVB200_DT_FP16, true>(a, qb, grid, smem, st)
-             : launch_qb<ZVB200_DT_FP16, false>(a, qb, grid, smem, st);
+      e = l2 ? launch_qb<ZVB200_DT_FP16, true>(a, qb, grid, smem, st, pre)
+             : launch_qb<ZVB200_DT_FP16, false>(a, qb, grid, smem, st, pre);
     else
       e = l2 ? launch_qb<ZVB200_DT_INT8, true>(a, qb, grid, smem, st, pre)
              : launch_qb<ZVB200_DT_INT8, false>(a, qb, grid, smem, st, pre);
@@ -369,6 +381,7 @@ static int pick_ku(uint64_t rows_hint, int lpr_log2, int grid) {
 
 template <int DT, bool L2>
 static cudaError_t launch_lists_ku(const GemvArgs &a, int ku, int grid, size_t smem, cudaStream_t st, int gy) {
+  if (ku == -1) return launch_one<DT, L2, 1, true, kPreU, kPre>(a, grid, smem, st, gy);
   switch (ku) {
     case 4: return launch_one<DT, L2, 1, true, 4>(a, grid, smem, st, gy);
     case 6: return launch_one<DT, L2, 1, true, 6>(a, grid, smem, st, gy);
@@ -388,7 +401,8 @@ cudaError_t launch_scan_lists(const RowsView &rv, const QueryView &qv, const Sea
   const int grid = (int)scan_lists_parts(qv.q, sm_count);
   a.nparts = grid;
   *nparts = grid;
-  const int ku = pick_ku(rows_hint, a.lpr_log2, grid);
+  // a query's lists are a short scan by nature: the finer tiles of the preload form balance it better, no size rule
+  const int ku = pre_applies(rv, a.lpr_log2, ~0ull >> 8, 1) ? -1 : pick_ku(rows_hint, a.lpr_log2, grid);
   const size_t smem = gemv_smem(rv.dtype, rv.chunks, 1, sp.k, seg_cap);
   if (smem > 220 * 1024) return cudaErrorInvalidValue;
   const bool l2 = metric_is_l2(rv.metric);
