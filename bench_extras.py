@@ -90,8 +90,12 @@ def c1(args, z, torch, dev, pk, compare_topk, merge_candidates, log):
             fl = 2.0 * n * d * b
             roof = _roof("tensor", fl / (sm / 1e3) / 1e12, pk["tf_sustained"], "TFLOP/s", kern, sm,
                          "2*rows*dim*batch flop per launch = %.4g" % fl,
-                         "kind::tf32 filter + exact fp32 re-score; quoted against the measured bf16 sustained peak "
-                         "(the tf32 pipe peaks at half of it: frac_of_tf32 = 2 x frac)")
+                         "kind::tf32 filter + exact fp32 re-score; quoted against the measured bf16 sustained peak; "
+                         "this kernel's own kind::tf32 rate with the epilogue removed is 737 TFLOP/s "
+                         "(profiles/r02_mma_peaks_in_situ.txt), see frac_of_in_situ_peak; the 128 x 256 fp32 "
+                         "accumulator read-out (2048 cycles per tile) bounds d = 128 above the MMAs")
+            roof["in_situ_peak"] = 737.0
+            roof["frac_of_in_situ_peak"] = roof["achieved"] / 737.0
         out["batch%d" % b] = {"value": b / t, "unit": "queries/s", "ms_per_batch": t * 1e3, "kernel": kern,
                               "e2e": {"value": b / e2e, "unit": "queries/s", "h2d_bytes_per_step": b * d * 4,
                                       "d2h_bytes_per_step": b * k * 8}, "roofline": roof}
@@ -206,7 +210,12 @@ def c3(args, z, torch, dev, pk, compare_topk, merge_candidates, log):
             roof = _roof("tensor", fl / (sm / 1e3) / 1e12, pk["tf_sustained"], "TFLOP/s", kern, sm,
                          "2*rows*dim*batch flop per launch = %.4g" % fl,
                          "mma kind %d (3 = kind::f16 over the bf16 shadow operands, exact re-score from the int8 "
-                         "codes); quoted against the measured bf16 sustained peak" % ctx.last_mma_kind())
+                         "codes); quoted against the measured bf16 sustained peak; the TMEM read-out of "
+                         "4 B x batch x rows of accumulators (64 B per clock per SM) alone is 22.8 ms at 1.9 GHz "
+                         "for this shape = 862 TFLOP/s, see frac_of_tmem_floor" % ctx.last_mma_kind())
+            tmem_floor_s = 4.0 * b * n / (148 * 64 * 1.9e9)
+            roof["tmem_readout_floor_ms"] = tmem_floor_s * 1e3
+            roof["frac_of_tmem_floor"] = tmem_floor_s / (sm / 1e3)
         out["batch%d" % b] = {"value": b / t, "unit": "queries/s", "ms_per_batch": t * 1e3, "kernel": kern,
                               "e2e": {"value": b / e2e, "unit": "queries/s", "h2d_bytes_per_step": b * (d + 16),
                                       "d2h_bytes_per_step": b * k * 8}, "roofline": roof}
