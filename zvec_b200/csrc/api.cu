@@ -1008,6 +1008,26 @@ static int coarse_wide(zvb200_ctx *c, zvb200_store *cs, const void *queries_dev,
   return 0;
 }
 
+// top-nprobe centroids for a FEW queries: the streaming scan writes every centroid's key, one select kernel per query
+// picks and sorts the nprobe best; same arithmetic, same (score, row) order as search_core
+static int coarse_direct(zvb200_ctx *c, zvb200_store *cs, const void *queries_dev, uint32_t q, uint32_t nprobe,
+                         const IvfPlanArgs *plan) {
+  QueryView qv;
+  int r = prep_core(c, cs, queries_dev, q, &qv, false);
+  if (r != 0) return r;
+  RowsView rv = zvb_view_for(c, cs);
+  const uint32_t total = (uint32_t)cs->n;
+  CU(c->part.ensure((size_t)q * total * sizeof(u64)));
+  SearchParams sp;
+  sp.k = nprobe; sp.threshold = FLT_MAX; sp.filter = nullptr;
+  uint32_t nparts = 0;
+  CU(launch_scan_gemv(rv, qv, sp, 0, cs->n, nullptr, &nparts, cs->sm_count, c->stream, (u64 *)c->part.p, total));
+  CU(launch_select_topk((const u64 *)c->part.p, total, q, nprobe, (float *)c->coarse_scores.p,
+                        (uint32_t *)c->coarse_index.p, c->stream, plan));
+  c->last_kernel = "scan_gemv";
+  return 0;
+}
+
 // coarse search -> list plan -> posting-list scan -> merge, everything on the context's stream; queries, filter and
 // outputs on the device
 static int ivf_core(zvb200_ctx *c, const void *queries_dev, uint32_t q, uint32_t k, uint32_t nprobe,
@@ -1025,7 +1045,19 @@ static int ivf_core(zvb200_ctx *c, const void *queries_dev, uint32_t q, uint32_t
   const int keep = c->force_kernel;
   if (keep == 3 || keep == 5) c->force_kernel = 0;
   int r;
-  if (nprobe <= ZVB200_MAX_TOPK) {
+  bool planned = false;
+  static const bool direct_off = [] { const char *e = getenv("ZVB200_COARSE_DIRECT"); return e && atoi(e) == 0; }();
+  if (!direct_off && q <= 4 && keep == 0 && nprobe <= ZVB200_MAX_TOPK && s->centroids->n <= select_topk_max() &&
+      !s->centroids->has_drop) {
+    // few queries over few centroids: a CTA of the streaming scan sees ~55 rows and k = nprobe takes them all, so the
+    // in-kernel top-k is pure overhead — every centroid's key goes straight to the select kernel, which also writes
+    // the query's posting-list plan (q <= 4 is query-major: no seg_list)
+    IvfPlanArgs pa;
+    pa.list_off = s->list_off_dev; pa.budget_sizes = s->budget_dev; pa.max_scan_count = max_scan_count;
+    pa.seg_prefix = (uint32_t *)c->seg_prefix.p; pa.seg_row = (uint32_t *)c->seg_row.p; pa.seg_count = (uint32_t *)c->seg_count.p;
+    r = coarse_direct(c, s->centroids, queries_dev, q, nprobe, &pa);
+    planned = true;
+  } else if (nprobe <= ZVB200_MAX_TOPK) {
     r = search_core(c, s->centroids, queries_dev, q, nprobe, FLT_MAX, nullptr, (float *)c->coarse_scores.p,
                     (uint32_t *)c->coarse_index.p, 0, s->centroids->n);
   } else {
@@ -1043,6 +1075,7 @@ static int ivf_core(zvb200_ctx *c, const void *queries_dev, uint32_t q, uint32_t
   const bool list_major = c->force_kernel != 1 && c->force_kernel != 4 && q >= lm_from && scan_lists_lm_qb(rv, k) > 0 &&
                           (size_t)q * nprobe * k * sizeof(u64) <= ((size_t)1 << 30);
   if (list_major) CU(c->seg_list.ensure((size_t)q * nprobe * 4));
+  if (!planned || list_major)
   CU(launch_ivf_plan((const uint32_t *)c->coarse_index.p, q, nprobe, s->list_off_dev, s->budget_dev, max_scan_count,
                      (uint32_t *)c->seg_prefix.p, (uint32_t *)c->seg_row.p, (uint32_t *)c->seg_count.p, c->stream,
                      list_major ? (uint32_t *)c->seg_list.p : nullptr));

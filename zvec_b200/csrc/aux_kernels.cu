@@ -277,10 +277,16 @@ __global__ void __launch_bounds__(kMergeWarps * 32) merge_parts_kernel(
 // below it and sorts those k.  Same result as merge_parts_kernel: ascending by (score, row), padding last.
 constexpr int kSelPerThread = 16;  // keys a thread keeps in registers
 constexpr int kSelMaxThreads = 1024;  // up to 16384 keys per query
+}  // namespace
+__device__ void ivf_plan_warp(const uint32_t *ci, uint32_t qi, uint32_t nprobe, const uint32_t *list_off,
+                              const uint32_t *budget_sizes, uint64_t max_scan_count, uint32_t *seg_prefix,
+                              uint32_t *seg_row, uint32_t *seg_count, uint32_t *seg_list);
+namespace {
 
 template <int NT>
 __global__ void __launch_bounds__(NT) merge_select_kernel(const u64 *part, uint32_t total, uint32_t k,
-                                                          float *out_scores, uint32_t *out_index, u64 *out_keys) {
+                                                          float *out_scores, uint32_t *out_index, u64 *out_keys,
+                                                          const IvfPlanArgs plan = IvfPlanArgs()) {
   constexpr int BPT = 2048 / NT;  // histogram bins per thread in the scan
   __shared__ uint32_t hist[2048];
   __shared__ uint32_t wsum[32];
@@ -378,6 +384,14 @@ __global__ void __launch_bounds__(NT) merge_select_kernel(const u64 *part, uint3
     if (out_scores) out_scores[(size_t)blockIdx.x * k + i] = ok ? unorder_f32((uint32_t)(e >> 32)) : CUDART_NAN_F;
     if (out_index) out_index[(size_t)blockIdx.x * k + i] = ok ? (uint32_t)e : ZVB200_INVALID_INDEX;
     if (out_keys) out_keys[(size_t)blockIdx.x * k + i] = e;
+    if (plan.list_off) hist[i] = ok ? (uint32_t)e : ZVB200_INVALID_INDEX;  // k <= 1024 ids in the 2048-word histogram
+  }
+  // the selected keys are a query's coarse ids: its posting-list plan right here, one launch less (IVF at batch 1)
+  if (plan.list_off) {
+    __syncthreads();
+    if (warp == 0)
+      ivf_plan_warp(hist, blockIdx.x, k, plan.list_off, plan.budget_sizes, plan.max_scan_count, plan.seg_prefix, plan.seg_row,
+                    plan.seg_count, plan.seg_list);
   }
 }
 
@@ -649,6 +663,23 @@ cudaError_t launch_merge_parts(const u64 *part, uint32_t nparts, uint32_t q, uin
   return cudaGetLastError();
 }
 
+uint32_t select_topk_max() { return (uint32_t)kSelMaxThreads * kSelPerThread; }
+
+cudaError_t launch_select_topk(const u64 *keys, uint32_t total, uint32_t q, uint32_t k, float *out_scores,
+                               uint32_t *out_index, cudaStream_t st, const IvfPlanArgs *plan) {
+  if (q == 0) return cudaSuccess;
+  if (total == 0 || total > select_topk_max() || k == 0 || k > 1024) return cudaErrorInvalidValue;
+  const IvfPlanArgs pa = plan ? *plan : IvfPlanArgs();
+  if (total <= 256 * kSelPerThread)
+    merge_select_kernel<256><<<q, 256, 0, st>>>(keys, total, k, out_scores, out_index, nullptr, pa);
+  else if (total <= 512 * kSelPerThread)
+    merge_select_kernel<512><<<q, 512, 0, st>>>(keys, total, k, out_scores, out_index, nullptr, pa);
+  else
+    merge_select_kernel<1024><<<q, 1024, 0, st>>>(keys, total, k, out_scores, out_index, nullptr, pa);
+  count_launch();
+  return cudaGetLastError();
+}
+
 cudaError_t launch_merge_shards(const float *scores, const uint32_t *index, uint32_t g,
                                 const uint64_t *shard_base_dev, uint32_t q, uint32_t k,
                                 float *out_scores, uint64_t *out_rows, cudaStream_t st) {
@@ -767,9 +798,17 @@ __global__ void ivf_plan_kernel(const uint32_t *coarse_index, uint32_t q, uint32
   // each cost 35 us at batch 1 — half of the posting-list scan it prepares)
   const uint32_t qi = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   if (qi >= q) return;
+  ivf_plan_warp(coarse_index + (size_t)qi * nprobe, qi, nprobe, list_off, budget_sizes, max_scan_count, seg_prefix, seg_row,
+                seg_count, seg_list);
+}
+}  // namespace
+
+// the plan of ONE query by one warp; ci = its nprobe coarse ids in coarse order (global or shared memory)
+__device__ void ivf_plan_warp(const uint32_t *ci, uint32_t qi, uint32_t nprobe, const uint32_t *list_off,
+                              const uint32_t *budget_sizes, uint64_t max_scan_count, uint32_t *seg_prefix,
+                              uint32_t *seg_row, uint32_t *seg_count, uint32_t *seg_list) {
   const int lane = threadIdx.x & 31;
   const uint32_t lt = (1u << lane) - 1u;
-  const uint32_t *ci = coarse_index + (size_t)qi * nprobe;
   uint32_t *pre = seg_prefix + (size_t)qi * (nprobe + 1), *row = seg_row + (size_t)qi * nprobe;
   // `total` is what the budget counts: the list's size in the WHOLE index (budget_sizes, when this store holds
   // one shard of every list) — every shard then visits exactly the lists the unsharded index would
@@ -818,6 +857,7 @@ __global__ void ivf_plan_kernel(const uint32_t *coarse_index, uint32_t q, uint32
   }
   if (lane == 0) seg_count[qi] = n;
 }
+namespace {
 }  // namespace
 
 cudaError_t launch_ivf_plan(const uint32_t *coarse_index, uint32_t q, uint32_t nprobe, const uint32_t *list_off,

@@ -65,7 +65,20 @@ struct PartView {
 // K1: GEMV-style streaming scan, CUDA cores, best for q <= 4.
 cudaError_t launch_scan_gemv(const RowsView &rv, const QueryView &qv, const SearchParams &sp,
                              uint64_t row_begin, uint64_t row_end, u64 *part, uint32_t *nparts,
-                             int sm_count, cudaStream_t st);
+                             int sm_count, cudaStream_t st, u64 *all_keys = nullptr /* [q][keys_stride]: every row's key
+                             (kMaxKey = none) instead of per-CTA top-k lists */, uint32_t keys_stride = 0);
+// the k smallest of `total` packed keys per query (keys[q][total], kMaxKey = none), sorted: one CTA per query, radix
+// select in registers; total <= select_topk_max()
+// plan != null: the k selected keys are a query's coarse ids — its posting-list plan (launch_ivf_plan's outputs) is
+// written by the same kernel
+struct IvfPlanArgs {
+  const uint32_t *list_off = nullptr, *budget_sizes = nullptr;
+  uint64_t max_scan_count = 0;
+  uint32_t *seg_prefix = nullptr, *seg_row = nullptr, *seg_count = nullptr, *seg_list = nullptr;
+};
+cudaError_t launch_select_topk(const u64 *keys, uint32_t total, uint32_t q, uint32_t k, float *out_scores,
+                               uint32_t *out_index, cudaStream_t st, const IvfPlanArgs *plan = nullptr);
+uint32_t select_topk_max();
 size_t scan_gemv_max_parts(int sm_count);
 // K1s: bulk-async (cp.async.bulk + mbarrier ring) streaming scan, exact arithmetic, grid.y = query
 cudaError_t launch_scan_stream(const RowsView &rv, const QueryView &qv, const SearchParams &sp,

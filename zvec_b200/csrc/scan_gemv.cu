@@ -38,6 +38,11 @@ struct GemvArgs {
   // seg_row[i] + v - seg_prefix[i].  Arrays are [q][seg_cap(+1)].
   const uint32_t *seg_prefix, *seg_row, *seg_count;
   uint32_t seg_cap;
+  // non-null: no top-k at all — every row's key (kMaxKey for a dropped / filtered / unscorable one) goes to
+  // all_keys[query * keys_stride + row - row_begin]: a scan of FEW rows whose k takes most of them (the IVF coarse stage:
+  // 55 rows per CTA, k = 64)
+  u64 *all_keys;
+  uint32_t keys_stride;
 };
 
 
@@ -226,12 +231,18 @@ __global__ void __launch_bounds__(kThreads, QB == 1 ? 2 : 1) scan_gemv_kernel(co
         }
         s *= sc;
         const u64 key = pack_key(s, (uint32_t)r);
+        if (!SEG && a.all_keys) {  // every row of the range gets a word: its key, or "none"
+          if (l == 0 && rv_ < vend && j < nq)
+            a.all_keys[(size_t)(qbase + j) * a.keys_stride + (r - a.row_begin)] = (valid && s <= a.threshold) ? key : kMaxKey;
+          continue;
+        }
         const bool has = valid && j < nq && s <= a.threshold && key < tk[j].tau;
         tk[j].push(has, key, kMaxKey);
       }
     }
   }
 
+  if (!SEG && a.all_keys) return;
   // ---- merge the warps' lists inside the CTA, one owner warp per query ----
 #pragma unroll
   for (int j = 0; j < QB; ++j) {
@@ -313,8 +324,9 @@ size_t scan_gemv_max_parts(int sm_count) { return (size_t)sm_count * 2; }
 
 cudaError_t launch_scan_gemv(const RowsView &rv, const QueryView &qv, const SearchParams &sp,
                              uint64_t row_begin, uint64_t row_end, u64 *part, uint32_t *nparts,
-                             int sm_count, cudaStream_t st) {
+                             int sm_count, cudaStream_t st, u64 *all_keys, uint32_t keys_stride) {
   GemvArgs a;
+  a.all_keys = all_keys; a.keys_stride = keys_stride;
   a.seg_prefix = a.seg_row = a.seg_count = nullptr; a.seg_cap = 0;
   a.rv = rv; a.qv = qv; a.k = sp.k; a.threshold = sp.threshold; a.filter = sp.filter;
   a.row_begin = row_begin; a.row_end = row_end; a.part = part;
@@ -381,7 +393,9 @@ static int pick_ku(uint64_t rows_hint, int lpr_log2, int grid) {
 
 template <int DT, bool L2>
 static cudaError_t launch_lists_ku(const GemvArgs &a, int ku, int grid, size_t smem, cudaStream_t st, int gy) {
-  if (ku == -1) return launch_one<DT, L2, 1, true, kPreU, kPre>(a, grid, smem, st, gy);
+  // the preload form of a query's lists: 3 row groups x 4 chunk iterations in flight (12 loads per lane) — C4's 39 063
+  // rows: 4 x 3 64 -> 61 us, 6 x 2 60, 3 x 5 59, 3 x 4 and 2 x 6 57-58 (24-row tiles: 5.5 rounds of the grid, not 4.1)
+  if (ku == -1) return launch_one<DT, L2, 1, true, 3, 4>(a, grid, smem, st, gy);
   switch (ku) {
     case 4: return launch_one<DT, L2, 1, true, 4>(a, grid, smem, st, gy);
     case 6: return launch_one<DT, L2, 1, true, 6>(a, grid, smem, st, gy);
@@ -394,6 +408,7 @@ cudaError_t launch_scan_lists(const RowsView &rv, const QueryView &qv, const Sea
                               uint32_t seg_cap, u64 *part, uint32_t *nparts, int sm_count, cudaStream_t st,
                               uint64_t rows_hint) {
   GemvArgs a;
+  a.all_keys = nullptr; a.keys_stride = 0;
   a.rv = rv; a.qv = qv; a.k = sp.k; a.threshold = sp.threshold; a.filter = sp.filter;
   a.row_begin = 0; a.row_end = rv.n; a.part = part; a.q0 = 0;
   a.seg_prefix = seg_prefix; a.seg_row = seg_row; a.seg_count = seg_count; a.seg_cap = seg_cap;
