@@ -411,9 +411,14 @@ def c5(args, z, torch, dev, pk, st0, ctx0, data0, compare_topk, merge_candidates
                                     scan, "4 fields * rows*dim*2 B per multi-query = %.4g" % bytes_mq,
                                     "the four scans of one multi-query, summed")
         else:
+            # 64 queries are half a 128-query tile: the tensor-core scan streams every row once per batch and is
+            # HBM-bound below ~213 queries, so the bytes bound it, not the flops
             fl = 2.0 * rows * DIM * b * F
-            blk["roofline"] = _roof("tensor", fl / (scan / 1e3) / 1e12, pk["tf_sustained"], "TFLOP/s",
-                                    ctxs[1].last_kernel(), scan, "4 * 2*rows*dim*batch flop = %.4g" % fl)
+            blk["roofline"] = _roof("hbm", bytes_mq / (scan / 1e3) / 1e9, pk["hbm_gbs"], "GB/s", ctxs[1].last_kernel(),
+                                    scan, "4 fields * rows*dim*2 B per batch of multi-queries = %.4g" % bytes_mq,
+                                    "the four tensor-core scans of one batch, summed; as flops: %.1f TFLOP/s = %.3f of "
+                                    "the sustained bf16 peak" % (fl / (scan / 1e3) / 1e12,
+                                                                 fl / (scan / 1e3) / 1e12 / pk["tf_sustained"]))
         out["batch%d" % b] = blk
     # parity: per-field top-100 of 2 multi-queries vs fp32 torch over the same rows; the fused list vs the formula of
     # RrfReRanker.rerank (multi_vector_reranker.py:62-89) applied to those per-field lists
