@@ -510,3 +510,90 @@ def test_operand_order_of_the_streamer_is_bit_exact(kind, kernel):
         assert np.array_equal(gi[i], order.astype(np.uint32))
     assert (moved == 0) == (kind == "qi8_l2")     # the case tests something: -IP scores do move
     ctx.close(); st.close()
+
+
+def test_replayed_searches_follow_the_store():
+    """A small search is recorded as one CUDA graph on its second call and replayed from the third (api.cu,
+    run_replayable).  The recording must retire with everything it was built from: rows appended, a row deleted or
+    overwritten, the context's settings, a buffer that had to grow — and a replay must still count its launches."""
+    rng = np.random.default_rng(91)
+    n, d, k = 6000, 32, 5
+    x = rng.standard_normal((n, d)).astype(np.float32)
+    q = rng.standard_normal((1, d)).astype(np.float32)
+
+    def exact(rows, alive):
+        dist = ((rows - q) ** 2).sum(1).astype(np.float32)
+        dist[~alive] = np.inf
+        return np.argsort(dist, kind="stable")[:k]
+
+    st = z.Store(S.DT_FP32, S.M_L2SQ, d)
+    st.reserve(2 * n)
+    st.append(x); st.seal()
+    ctx = z.Context(st)
+    alive = np.ones(n, bool)
+    first = ctx.search(q, k)
+    assert list(first[2][0]) == list(exact(x, alive))
+    for _ in range(3):                                   # direct, recorded, replayed, replayed
+        before = z.lib().zvb200_kernel_launches()
+        again = ctx.search(q, k)
+        assert z.lib().zvb200_kernel_launches() > before
+        assert np.array_equal(again[2], first[2]) and np.array_equal(again[1].view(np.uint32), first[1].view(np.uint32))
+        assert ctx.last_kernel() == "scan_gemv" and ctx.last_scan_ms() > 0
+    best = int(first[2][0][0])
+    st.set_deleted(best, True); alive[best] = False      # a writer: the next search is direct again
+    for _ in range(3):
+        assert list(ctx.search(q, k)[2][0]) == list(exact(x, alive))
+    closer = (q + 1e-3).astype(np.float32)               # appended rows must be seen
+    st.append(closer); st.seal()
+    x2 = np.concatenate([x, closer]); alive2 = np.concatenate([alive, [True]])
+    for _ in range(3):
+        assert list(ctx.search(q, k)[2][0]) == list(exact(x2, alive2))
+    st.write(7, closer[0], 7)                            # overwritten in place
+    x2[7] = closer[0]
+    for _ in range(3):
+        assert list(ctx.search(q, k)[2][0])[:2] == [7, n]
+    for _ in range(3):                                   # other arguments: another recording
+        assert list(ctx.search(q, k, threshold=1e-3)[2][0][:2]) == [7, n]
+        assert ctx.search(q, k, threshold=1e-3)[3][0] == 2
+    big = ctx.search(rng.standard_normal((700, d)).astype(np.float32), 50)   # grows the context's buffers
+    assert big[3].min() == 50
+    for _ in range(3):
+        assert list(ctx.search(q, k)[2][0])[:2] == [7, n]
+    qd = rng.standard_normal((2, d)).astype(np.float32)  # the device-pointer form, keyed by its pointers
+    import torch
+    dq = torch.from_numpy(qd).cuda(); os_ = torch.empty((2, k), dtype=torch.float32, device="cuda")
+    oi = torch.empty((2, k), dtype=torch.int32, device="cuda")
+    want = ctx.search(qd, k)[2]
+    for _ in range(4):
+        oi.zero_()
+        ctx.search_device(dq.data_ptr(), 2, k, os_.data_ptr(), oi.data_ptr()); ctx.sync()
+        assert np.array_equal(oi.cpu().numpy().astype(np.uint32), want)
+    dq.copy_(torch.from_numpy(qd[::-1].copy()))          # same pointers, other queries: the replay reads them afresh
+    ctx.search_device(dq.data_ptr(), 2, k, os_.data_ptr(), oi.data_ptr()); ctx.sync()
+    assert np.array_equal(oi.cpu().numpy().astype(np.uint32), want[::-1])
+    ctx.close(); st.close()
+
+
+@pytest.mark.parametrize("q", [1, 6, 40])
+def test_threshold_leaves_fewer_than_k_in_many_partial_lists(q):
+    """A threshold that most rows fail leaves the per-CTA partial lists mostly padding; the select-merge
+    (merge_select_kernel, aux_kernels.cu) must still return every surviving row — its k-th smallest key is then the
+    padding value itself, thousands of copies of it (found by the 2-GPU sharded-store test: rows were lost)."""
+    rng = np.random.default_rng(101 + q)
+    n, d, k = 70001, 72, 10
+    x = rng.standard_normal((n, d)).astype(np.float32)
+    qs = rng.standard_normal((q, d)).astype(np.float32)
+    st = z.Store(S.DT_FP32, S.M_L2SQ, d)
+    st.append(x); st.seal()
+    ctx = z.Context(st)
+    full = ctx.search(qs, k)
+    th = float(np.median(full[1][:, k // 2]))
+    got = ctx.search(qs, k, threshold=th)
+    for i in range(q):
+        want = int((full[1][i] <= np.float32(th)).sum())
+        assert got[3][i] == want, (i, got[3][i], want)
+        assert np.array_equal(got[2][i][:want], full[2][i][:want])
+        assert np.array_equal(got[1][i][:want].view(np.uint32), full[1][i][:want].view(np.uint32))
+    none = ctx.search(qs, k, threshold=-1.0)
+    assert (none[3] == 0).all()
+    ctx.close(); st.close()

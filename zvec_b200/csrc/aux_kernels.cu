@@ -304,6 +304,7 @@ __global__ void __launch_bounds__(NT) merge_select_kernel(const u64 *part, uint3
   // distinct scores that is after the 33 score bits at the latest: three passes, not six)
   u64 prefix = 0;
   uint32_t need = k;
+  bool whole = false;
   int sel_shift = 0;  // the result = the keys whose bits above sel_shift are <= prefix's
   for (int shift = 53; shift >= -2; shift -= 11) {
     const int sh = shift < 0 ? 0 : shift;
@@ -346,23 +347,31 @@ __global__ void __launch_bounds__(NT) merge_select_kernel(const u64 *part, uint3
     prefix |= (u64)s_bin << sh;
     need = s_need;
     sel_shift = sh;
-    const bool whole = s_all == s_need;
+    whole = s_all == s_need;
     __syncthreads();
     if (whole) break;
   }
-  // need == the bin's size now (the loop ends that way at the last digit too, where the bin is one key value)
-  if (tid == 0) s_cnt = 0;
+  // whole: the bins below plus this bin are exactly k keys.  Otherwise the loop ran out of digits: the bin is ONE key
+  // value held more often than needed — kMaxKey padding when a query has fewer than k candidates (a tight threshold:
+  // thousands of copies), or a candidate row listed several times — and only `need` copies of it belong to the result.
+  // Padding is never selected: taking "everything <= the k-th" would push real keys out of the 1024 slots.
+  if (tid == 0) { s_cnt = 0; s_all = 0; }
   __syncthreads();
   const u64 lim = prefix >> sel_shift;
 #pragma unroll
-  for (int i = 0; i < kSelPerThread; ++i)
-    if ((mine[i] >> sel_shift) <= lim) {
+  for (int i = 0; i < kSelPerThread; ++i) {
+    if (mine[i] == kMaxKey) continue;
+    const u64 tkey = mine[i] >> sel_shift;
+    if (tkey < lim || (tkey == lim && whole)) {
       const uint32_t pos = atomicAdd(&s_cnt, 1u);
       if (pos < 1024) sel[pos] = mine[i];
+    } else if (tkey == lim) {  // a copy of the k-th key itself: at most `need` of them, behind the smaller keys
+      const uint32_t cpy = atomicAdd(&s_all, 1u);
+      if (cpy < need) sel[k - need + cpy] = mine[i];
     }
+  }
   __syncthreads();
-  // copies of one key beyond the k-th (a candidate row listed more than twice over): the sort drops the surplus
-  const uint32_t got = min(s_cnt, 1024u);
+  const uint32_t got = whole ? min(s_cnt, 1024u) : min(k, (k - need) + min(s_all, need));
   uint32_t p2 = 1;
   while (p2 < max(got, k)) p2 <<= 1;
   for (uint32_t i = got + tid; i < p2; i += NT) sel[i] = kMaxKey;
