@@ -28,8 +28,8 @@ print("# UBLKCP = cp.async.bulk, SYNCS = mbarrier ops, IDP.4A = dp4a.  HMMA / IM
 tot = collections.Counter()
 for i, fn in enumerate(order):
     name = dem[i] if i < len(dem) else fn
-    name = re.sub(r"\(.*$", "", name)
-    name = re.sub(r"zvb::|\(anonymous namespace\)::|gemv::", "", name)
+    name = re.sub(r"zvb::|\(anonymous namespace\)::|<unnamed>::|gemv::", "", name)
+    name = re.sub(r"\((?:const )?(?:CUtensorMap|GemvArgs|LmArgs|MmaArgs|[a-z]).*$", "", name)
     c = counts[fn]
     tot.update({k: v for k, v in c.items() if k != "_n"})
     print("%-70s %6d instr  %s" % (name[:70], c["_n"], " ".join("%s=%d" % (k, v) for k, v in c.items() if k != "_n")))
