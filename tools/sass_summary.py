@@ -29,7 +29,8 @@ tot = collections.Counter()
 for i, fn in enumerate(order):
     name = dem[i] if i < len(dem) else fn
     name = re.sub(r"zvb::|\(anonymous namespace\)::|<unnamed>::|gemv::", "", name)
-    name = re.sub(r"\((?:const )?(?:CUtensorMap|GemvArgs|LmArgs|MmaArgs|[a-z]).*$", "", name)
+    name = re.sub(r"\((int|bool)\)", "", name)          # <(int)2, (bool)1> -> <2, 1>
+    name = re.sub(r"\([^<>]*\)$", "", name)              # the parameter list
     c = counts[fn]
     tot.update({k: v for k, v in c.items() if k != "_n"})
     print("%-70s %6d instr  %s" % (name[:70], c["_n"], " ".join("%s=%d" % (k, v) for k, v in c.items() if k != "_n")))
