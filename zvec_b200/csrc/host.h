@@ -129,14 +129,15 @@ struct HostBuf {
 // results): the second call of a context with the same arguments records it, later ones replay it with one
 // cudaGraphLaunch.  The key holds everything the launches were built from; the store's generation (bumped by every
 // writer) and the buffer epoch (bumped by every re-allocation) retire a stale recording.
-struct GraphKey {
-  int fn;                 // 1 zvb200_search, 2 zvb200_ivf_search, 3 zvb200_ivf_search_split
+struct GraphKey {  // compared with memcmp: 8-byte members first, an even number of 4-byte ones, no padding
   const void *store;
+  const void *p0, *p1, *p2, *p3;  // the device-pointer forms: queries, filter, outputs
   uint64_t gen, epoch, rows, max_scan;
   uint32_t q, k, nprobe, thr_bits, mma_group_cap;
+  int fn;                 // 1 zvb200_search, 2 zvb200_ivf_search, 3 _split, 4 / 5 the _device forms
   int force_kernel, operand_order;
-  const void *p0, *p1, *p2, *p3;  // the device-pointer forms: queries, filter, outputs
 };
+static_assert(sizeof(GraphKey) == 5 * sizeof(void *) + 4 * 8 + 8 * 4, "GraphKey must not have padding");
 struct ReplayGraph {
   GraphKey key;
   int seen = 0;
