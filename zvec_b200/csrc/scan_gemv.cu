@@ -52,7 +52,7 @@ cudaError_t launch_scan_gemv(const RowsView &rv, const QueryView &qv, const Sear
   const int lg = pick_lpr_log2(rv.chunks);
   a.lpr_log2 = lg;
   const uint64_t nrows0 = row_end > row_begin ? row_end - row_begin : 0;
-  const bool pre = pre_applies(rv, lg, nrows0, sm_count * 2);
+  const bool pre = !all_keys && pre_applies(rv, lg, nrows0, sm_count * 2);
   const uint64_t rows_per_tile = (uint64_t)(pre ? kPreU : kUmax) * (32 >> lg) * kWarps;
   const uint64_t nrows = row_end > row_begin ? row_end - row_begin : 0;
   uint64_t ntiles = (nrows + rows_per_tile - 1) / rows_per_tile;
@@ -60,7 +60,7 @@ cudaError_t launch_scan_gemv(const RowsView &rv, const QueryView &qv, const Sear
   a.nparts = grid;
   *nparts = grid;
   // queries per pass: as many as fit 100 KB of smem (2 CTAs/SM), at most 4
-  int qb = qv.q >= 4 ? 4 : (qv.q >= 2 ? 2 : 1);
+  int qb = all_keys ? 1 : qv.q >= 4 ? 4 : (qv.q >= 2 ? 2 : 1);  // the all-keys form is built for one query per pass
   {
     static const int force = [] { const char *e = getenv("ZVB200_GEMV_QB"); return e ? atoi(e) : 0; }();
     if (force == 1 || force == 2 || force == 4) qb = std::min(force, qb);

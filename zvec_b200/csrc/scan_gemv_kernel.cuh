@@ -52,7 +52,7 @@ template <int DT>
 cudaError_t launch_lists(const GemvArgs &a, bool l2, int ku, int grid, size_t smem, cudaStream_t st, int gy);
 
 #ifdef ZVB_GEMV_DT
-template <int DT, bool L2, int QB, bool SEG, int kU = kUmax, int PRE = 0>
+template <int DT, bool L2, int QB, bool SEG, int kU = kUmax, int PRE = 0, bool TE = false, bool AK = false>
 __global__ void __launch_bounds__(kThreads, QB == 1 ? 2 : 1) scan_gemv_kernel(const GemvArgs a) {
   typedef Chunk<DT, L2> CK;
   typedef typename CK::Acc Acc;
@@ -140,6 +140,11 @@ __global__ void __launch_bounds__(kThreads, QB == 1 ? 2 : 1) scan_gemv_kernel(co
     if (base >= vend) continue;  // warp-uniform
     Acc acc[kU][QB], aa[kU];
     const uint8_t *rp[kU];
+    // short QuantizedInteger rows, one query: the tails travel WITH the rows (a register each) instead of after them
+    // (TE: its own instantiation — the four registers cost plain int8 rows 10 %, 5.5 -> 5.0 TB/s, and gain the
+    // QuantizedInteger ones 4 %, 5.12 -> 5.32)
+    constexpr bool kTailEarly = TE;
+    float4 mte[kTailEarly ? kU : 1];
 #pragma unroll
     for (int u = 0; u < kU; ++u) {
       uint64_t r = base + (uint64_t)u * R + sub;
@@ -149,7 +154,11 @@ __global__ void __launch_bounds__(kThreads, QB == 1 ? 2 : 1) scan_gemv_kernel(co
       // QuantizedInteger: the row's tail is read only after the dot product; start its trip from HBM now (no
       // register held: the 128-register budget of 2 CTAs per SM is full) so that read finds it in L2
       // (one request per 64 B of tails = 4 rows; one per row measured the same)
-      if (metric_is_qi8(metric) && l == 0 && (sr & 3) == 0) asm volatile("prefetch.global.L2 [%0];" ::"l"(a.rv.tails + sr));
+      if (kTailEarly) {
+        mte[u] = ldg_tail(a.rv.tails + sr);
+      } else if (metric_is_qi8(metric) && l == 0 && (sr & 3) == 0) {
+        asm volatile("prefetch.global.L2 [%0];" ::"l"(a.rv.tails + sr));
+      }
       aa[u] = 0;
 #pragma unroll
       for (int j = 0; j < QB; ++j) acc[u][j] = 0;
@@ -212,7 +221,8 @@ __global__ void __launch_bounds__(kThreads, QB == 1 ? 2 : 1) scan_gemv_kernel(co
       float4 mt = make_float4(0, 0, 0, 0);
       // through the read-only, no-L1-allocate path like the rows: a plain ld.global of the tails costs the C3 scan
       // 14 % (4.19 -> 4.77 TB/s at 100M x 96; ncu: 1.43x -> 1.20x the algorithmic DRAM bytes)
-      if (metric_is_qi8(metric) && valid) mt = ldg_tail(a.rv.tails + r);
+      if (kTailEarly) mt = mte[u];
+      else if (metric_is_qi8(metric) && valid) mt = ldg_tail(a.rv.tails + r);
       // the row's score scale (IVFEntity::search: distances[k] * norm_val, ivf_entity.cc:650); 1 for a plain store
       const float sc = a.rv.row_scale ? (valid ? a.rv.row_scale[r] : 1.f) : a.rv.score_scale;
 #pragma unroll
@@ -233,7 +243,8 @@ __global__ void __launch_bounds__(kThreads, QB == 1 ? 2 : 1) scan_gemv_kernel(co
         }
         s *= sc;
         const u64 key = pack_key(s, (uint32_t)r);
-        if (!SEG && a.all_keys) {  // every row of the range gets a word: its key, or "none"
+        if (AK) {  // (its own instantiation: as a run-time branch it cost the short-row scans 10 %) every row of the
+                   // range gets a word: its key, or "none"
           if (l == 0 && rv_ < vend && j < nq)
             a.all_keys[(size_t)(qbase + j) * a.keys_stride + (r - a.row_begin)] = (valid && s <= a.threshold) ? key : kMaxKey;
           continue;
@@ -244,7 +255,7 @@ __global__ void __launch_bounds__(kThreads, QB == 1 ? 2 : 1) scan_gemv_kernel(co
     }
   }
 
-  if (!SEG && a.all_keys) return;
+  if (AK) return;
   // ---- merge the warps' lists inside the CTA, one owner warp per query ----
 #pragma unroll
   for (int j = 0; j < QB; ++j) {
@@ -271,9 +282,9 @@ __global__ void __launch_bounds__(kThreads, QB == 1 ? 2 : 1) scan_gemv_kernel(co
   }
 }
 
-template <int DT, bool L2, int QB, bool SEG = false, int KU = kUmax, int PRE = 0>
+template <int DT, bool L2, int QB, bool SEG = false, int KU = kUmax, int PRE = 0, bool TE = false, bool AK = false>
 cudaError_t launch_one(const GemvArgs &a, int grid, size_t smem, cudaStream_t st, int grid_y = 1) {
-  auto kern = scan_gemv_kernel<DT, L2, QB, SEG, KU, PRE>;
+  auto kern = scan_gemv_kernel<DT, L2, QB, SEG, KU, PRE, TE, AK>;
   cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kMaxDynSmem);
   if (e == cudaSuccess && smem > (size_t)kMaxDynSmem) e = cudaErrorInvalidValue;
   if (e != cudaSuccess) return e;
@@ -285,7 +296,10 @@ cudaError_t launch_one(const GemvArgs &a, int grid, size_t smem, cudaStream_t st
 // whole-row preload (PRE): int8 rows of at most kPre chunks per lane, kPreU row groups in flight (12 x 16 B per lane)
 template <int DT, bool L2>
 cudaError_t launch_qb(const GemvArgs &a, int qb, int grid, size_t smem, cudaStream_t st, bool pre = false) {
+  if (a.all_keys) return launch_one<DT, L2, 1, false, kUmax, 0, false, true>(a, grid, smem, st);  // one query per pass
   if (pre) {
+    if (DT == ZVB200_DT_INT8 && qb == 1 && metric_is_qi8(a.rv.metric) && a.rv.chunks <= (uint32_t)(kPre << a.lpr_log2))
+      return launch_one<DT, L2, 1, false, kPreU, kPre, DT == ZVB200_DT_INT8>(a, grid, smem, st);
     switch (qb) {
       case 1: return launch_one<DT, L2, 1, false, kPreU, kPre>(a, grid, smem, st);
       case 2: return launch_one<DT, L2, 2, false, kPreU, kPre>(a, grid, smem, st);
