@@ -518,11 +518,10 @@ int zvb_search_core(zvb200_ctx *c, zvb200_store *s, const void *queries_dev, uin
   // fp32 (tf32 filter + exact re-score) from 5 queries on — below that the streaming scan is as fast and simpler
   // (one query with k > 80: the pools leave the tensor-core scan only 2 pipeline stages, 5.7 TB/s; the GEMV scan
   // streams the same rows at 6.6 TB/s — measured at 10M x 768, k = 100)
-  // (one query over a SHORT range — a shard of a store split over 8 GPUs: the tensor-core kernel's pipeline fill costs
-  // more than it saves below ~4 GB; 1.25M x 768 fp16: 0.352 ms against 0.317 ms for the GEMV scan, 5M rows: 1.149 / 1.217)
-  const uint64_t scan_bytes = (row_end > row_begin ? row_end - row_begin : 0) * (uint64_t)s->row_stride;
-  const bool mma_direct = mma_ok && s->dtype == ZVB200_DT_FP16 && !metric_is_l2(s->metric) &&
-                          !(q == 1 && (k > 80 || scan_bytes < ((uint64_t)4 << 30)));
+  // (measured and NOT done: one query over a short range — 1.25M x 768 fp16, a shard of a store split over 8 GPUs — is
+  // 0.317 ms on the GEMV scan against 0.352 ms here, but its fp32-FMA sums differ from the tensor core's in the last
+  // place: a query would score differently alone and inside a batch, on one GPU and on eight)
+  const bool mma_direct = mma_ok && s->dtype == ZVB200_DT_FP16 && !metric_is_l2(s->metric) && !(q == 1 && k > 80);
   // QuantizedInteger L2 with shadow operands: the streaming scan costs 2.5 / 8.2 ms at 1 / 4 queries (100M x 96), the
   // tensor-core scan 5.2 ms for any batch up to 128 — it takes over from 3 queries
   const bool mma_early = mma_ok && rv.shadow && q > 2;
