@@ -303,7 +303,16 @@ def test_gpu_ivf_searcher_int8_quantised_lists(metric, extra):
     _gpu_ivf_searcher_vs_stock(metric, "", bp, True, sp)
 
 
-def _gpu_ivf_searcher_vs_stock(metric, conv, bp_extra, exact, sp_extra=""):
+# int4 posting lists have no row type on the device: the GPU class must hand the index to its embedded stock searcher
+# (one log line) and answer exactly what that answers — never crash, never scan rows it cannot read
+@needs_plugin
+@pytest.mark.gpu
+def test_gpu_ivf_searcher_delegates_int4_lists():
+    _gpu_ivf_searcher_vs_stock("SquaredEuclidean", "", ";proxima.ivf.builder.quantizer_class=Int4QuantizerConverter", True,
+                               delegated=True)
+
+
+def _gpu_ivf_searcher_vs_stock(metric, conv, bp_extra, exact, sp_extra="", delegated=False):
     assert S.ref().zref_has_searcher(b"GpuIVFSearcher") == 1
     n, d, nlist, k = 20000, 32, 64, 10
     rng = np.random.default_rng(8)
@@ -339,7 +348,10 @@ def _gpu_ivf_searcher_vs_stock(metric, conv, bp_extra, exact, sp_extra=""):
     before = z.lib().zvb200_kernel_launches()
     same(ix.search(qs, k, batch=len(qs)), r_batch, "batch")
     same(ix.search(qs, k, batch=1), r_one, "one by one")
-    assert z.lib().zvb200_kernel_launches() > before              # the GPU path ran, not the delegate
+    if delegated:
+        assert z.lib().zvb200_kernel_launches() == before          # nothing on the device: the stock searcher answered
+    else:
+        assert z.lib().zvb200_kernel_launches() > before          # the GPU path ran, not the delegate
     S.ref().zref_set_filter(4, 2)
     try:
         same(ix.search(qs, k, batch=8), r_filt, "filter")
