@@ -905,15 +905,20 @@ class GpuIVFSearcher : public IndexSearcher {
     // The posting lists have a meta of their own (IVFEntity::load_header, ivf_entity.cc:462-476): for an index built
     // with proxima.ivf.builder.quantizer_class = Int8QuantizerConverter they are int8 rows under the searcher's fp32
     // meta, and their scores carry the quantiser's global or per-list scale (IVFEntity::load, ivf_entity.cc:541-564)
-    // and a per-query one (IVFReformerWrapper::normalize :325-353).  int4 lists stay with the stock searcher.
+    // and a per-query one (IVFReformerWrapper::normalize :325-353).  int4 lists (Int4QuantizerConverter: two signed
+    // nibbles per byte, low nibble first, ivf_entity.cc:420-433) go to the device as int8 rows: the reference's int4
+    // kernels sum exact integers over the sign-extended nibbles (euclidean_distance_matrix_int4.cc:35-37,
+    // inner_product_matrix_int4.cc:49-51), so the int8 kernels over the unpacked values return the same numbers.
     lmeta_ = entity_.meta();
     const std::string &rf = lmeta_.reformer_name();
     int8_lists_ = rf == kInt8ReformerName && lmeta_.data_type() == IndexMeta::DataType::DT_INT8;
-    accelerated_ = !cntr->get(IVF_INT4_QUANTIZED_PARAMS_SEG_ID) && rf != kInt4ReformerName &&
-                   (int8_lists_ || (rf != kInt8ReformerName && !cntr->get(IVF_INT8_QUANTIZED_PARAMS_SEG_ID))) &&
-                   metric_of(lmeta_) >= 0 && dtype_of(lmeta_) >= 0 && entity_.vector_count() > 0;
+    int4_lists_ = rf == kInt4ReformerName && lmeta_.data_type() == IndexMeta::DataType::DT_INT4 &&
+                  lmeta_.dimension() % 2 == 0 && lmeta_.element_size() == lmeta_.dimension() / 2;
+    const bool plain = rf != kInt8ReformerName && rf != kInt4ReformerName && !cntr->get(IVF_INT8_QUANTIZED_PARAMS_SEG_ID) &&
+                       !cntr->get(IVF_INT4_QUANTIZED_PARAMS_SEG_ID) && dtype_of(lmeta_) >= 0;
+    accelerated_ = (plain || int8_lists_ || int4_lists_) && metric_of(lmeta_) >= 0 && entity_.vector_count() > 0;
     if (!accelerated_) {
-      why_not_ = "an index with int4 posting lists or an unsupported type";
+      why_not_ = "an index with posting lists of an unsupported type";
       return 0;
     }
     // centroids = the nested Flat index in segment "ivf.centroid" (ivf_searcher.cc:62-86); row cid = centroid cid
@@ -925,6 +930,7 @@ class GpuIVFSearcher : public IndexSearcher {
     if ((rc = IndexHelper::DeserializeFromStorage(nested.get(), &cmeta)) != 0) return rc;
     auto fseg = nested->get(kSegFeatures), kseg = nested->get(kSegKeys);
     const size_t nl = entity_.inverted_list_count(), n = entity_.vector_count(), es = lmeta_.element_size();
+    const size_t des = int4_lists_ ? 2 * es : es;  // bytes of a row on the device
     const size_t ces = cmeta.element_size();
     if (!fseg || !kseg || metric_of(cmeta) < 0 || dtype_of(cmeta) < 0 || kseg->data_size() != nl * sizeof(uint64_t) ||
         fseg->data_size() != nl * ces) {
@@ -967,7 +973,9 @@ class GpuIVFSearcher : public IndexSearcher {
     }
     // posting lists in list order through IVFEntity (ivf_entity.h:89-170): rows + keys + offsets
     zvb200_store *st = nullptr;
-    if ((rc = zvb200_store_create(device_, dtype_of(lmeta_), metric_of(lmeta_), lmeta_.dimension(), &st)) != 0) return rc;
+    if ((rc = zvb200_store_create(device_, int4_lists_ ? ZVB200_DT_INT8 : dtype_of(lmeta_), metric_of(lmeta_),
+                                  lmeta_.dimension(), &st)) != 0)
+      return rc;
     // IVFDistanceCalculator::row_major_distance: (query, feature) (ivf_distance_calculator.h:174-183)
     rc = zvb200_store_set_operand_order(st, 1);
     if (rc == 0) rc = zvb200_store_reserve(st, n);
@@ -991,7 +999,12 @@ class GpuIVFSearcher : public IndexSearcher {
       for (size_t j = 0; j < lm->vector_count; ++j, ++pos) {
         const void *v = entity_.get_vector(lm->id_offset + j);
         if (!v) { rc = IndexError_ReadData; break; }
-        rows.insert(rows.end(), static_cast<const char *>(v), static_cast<const char *>(v) + es);
+        if (int4_lists_) {
+          rows.resize(rows.size() + des);
+          unpack_int4(static_cast<const uint8_t *>(v), es, reinterpret_cast<int8_t *>(&rows[rows.size() - des]));
+        } else {
+          rows.insert(rows.end(), static_cast<const char *>(v), static_cast<const char *>(v) + es);
+        }
         keys.push_back(lk[j]);
         keys_.push_back(lk[j]);
       }
@@ -1004,7 +1017,7 @@ class GpuIVFSearcher : public IndexSearcher {
     if (rc == 0)
       rc = zvb200_ivf_attach_typed(st, cent.data(), (uint32_t)nl, offs.data(), dtype_of(cmeta), metric_of(cmeta),
                                    cmeta.dimension());
-    if (rc == 0 && int8_lists_) {
+    if (rc == 0 && (int8_lists_ || int4_lists_)) {
       // distances[k] * norm_val (ivf_entity.cc:601,650): one value for the index, or one per posting list
       std::vector<float> nv(nl);
       bool same = true;
@@ -1096,6 +1109,13 @@ class GpuIVFSearcher : public IndexSearcher {
     rc = ctx->entity()->transform(query, qmeta, count, &tq, &iv_qmeta);
     if (rc != 0) return rc;
     if (iv_qmeta.element_size() != lmeta_.element_size()) return IndexError_Mismatch;
+    std::vector<int8_t> unpacked;
+    if (int4_lists_) {  // the queries as int8 too
+      const size_t es = lmeta_.element_size();
+      unpacked.resize((size_t)count * 2 * es);
+      for (uint32_t i = 0; i < count; ++i) unpack_int4(static_cast<const uint8_t *>(tq) + i * es, es, &unpacked[(size_t)i * 2 * es]);
+      tq = unpacked.data();
+    }
     const uint32_t k = ctx->topk();
     ctx->begin(count);
     const size_t n = keys_.size();
@@ -1118,7 +1138,7 @@ class GpuIVFSearcher : public IndexSearcher {
     if (brute_force) ctx->fill_stats(count, n - dropped, dropped);
     for (uint32_t i = 0; i < count; ++i) {
       IndexDocumentList *out = ctx->mutable_result(i);
-      if (int8_lists_) {
+      if (int8_lists_ || int4_lists_) {
         // entity->normalize(q, &heap) (ivf_searcher.cc:240): one float factor per query — the quantiser's 1/scale, or
         // 1/(this query's own scale) for InnerProduct (ivf_entity.cc:325-353); 1.0f * factor is the factor itself
         IndexDocumentHeap probe(1);
@@ -1159,7 +1179,14 @@ class GpuIVFSearcher : public IndexSearcher {
   IndexMeta lmeta_{};  // the posting lists' meta (IVFEntity::meta)
   IndexReformer::Pointer creformer_{};  // the centroid index's reformer, or null
   size_t c_elem_{0};
-  bool int8_lists_{false};
+  bool int8_lists_{false}, int4_lists_{false};
+  //! two signed nibbles per byte, low nibble = the even element (IVFReformerWrapper::transform, ivf_entity.cc:427-431)
+  static void unpack_int4(const uint8_t *in, size_t bytes, int8_t *out) {
+    for (size_t i = 0; i < bytes; ++i) {
+      out[2 * i] = static_cast<int8_t>(static_cast<int8_t>(in[i] << 4) >> 4);
+      out[2 * i + 1] = static_cast<int8_t>(static_cast<int8_t>(in[i]) >> 4);
+    }
+  }
   std::vector<uint64_t> keys_{};
   zvb200_store *store_{nullptr};
   const char *why_not_{"an index that was not loaded"};

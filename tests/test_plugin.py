@@ -296,20 +296,14 @@ def test_gpu_ivf_searcher_equals_ivf_searcher(metric, conv):
     ("SquaredEuclidean", ";proxima.ivf.searcher.brute_force_threshold=1000000"),      # search_bf_impl's path
     ("InnerProduct", ";proxima.ivf.builder.quantize_by_centroid=true;proxima.ivf.searcher.brute_force_threshold=1000000"),
 ])
-def test_gpu_ivf_searcher_int8_quantised_lists(metric, extra):
-    bp = ";proxima.ivf.builder.quantizer_class=Int8QuantizerConverter" + "".join(
+@pytest.mark.parametrize("quant", ["Int8QuantizerConverter", "Int4QuantizerConverter"])
+def test_gpu_ivf_searcher_int8_quantised_lists(metric, extra, quant):
+    # (int4 lists travel to the device as int8 rows: the reference's int4 kernels sum exact integers over the
+    # sign-extended nibbles, so the scores are the same numbers)
+    bp = ";proxima.ivf.builder.quantizer_class=" + quant + "".join(
         ";" + p for p in extra.split(";") if p.startswith("proxima.ivf.builder"))
     sp = "".join(";" + p for p in extra.split(";") if p.startswith("proxima.ivf.searcher"))
     _gpu_ivf_searcher_vs_stock(metric, "", bp, True, sp)
-
-
-# int4 posting lists have no row type on the device: the GPU class must hand the index to its embedded stock searcher
-# (one log line) and answer exactly what that answers — never crash, never scan rows it cannot read
-@needs_plugin
-@pytest.mark.gpu
-def test_gpu_ivf_searcher_delegates_int4_lists():
-    _gpu_ivf_searcher_vs_stock("SquaredEuclidean", "", ";proxima.ivf.builder.quantizer_class=Int4QuantizerConverter", True,
-                               delegated=True)
 
 
 def _gpu_ivf_searcher_vs_stock(metric, conv, bp_extra, exact, sp_extra="", delegated=False):
