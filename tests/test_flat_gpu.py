@@ -513,7 +513,7 @@ def test_operand_order_of_the_streamer_is_bit_exact(kind, kernel):
 
 
 def test_replayed_searches_follow_the_store():
-    """A small search is recorded as one CUDA graph on its second call and replayed from the third (api.cu,
+    """A small search is recorded as one CUDA graph on its third call and replayed from the fourth (api.cu,
     run_replayable).  The recording must retire with everything it was built from: rows appended, a row deleted or
     overwritten, the context's settings, a buffer that had to grow — and a replay must still count its launches."""
     rng = np.random.default_rng(91)
@@ -533,7 +533,7 @@ def test_replayed_searches_follow_the_store():
     alive = np.ones(n, bool)
     first = ctx.search(q, k)
     assert list(first[2][0]) == list(exact(x, alive))
-    for _ in range(3):                                   # direct, recorded, replayed, replayed
+    for _ in range(4):                                   # direct, direct, recorded, replayed
         before = z.lib().zvb200_kernel_launches()
         again = ctx.search(q, k)
         assert z.lib().zvb200_kernel_launches() > before
@@ -541,30 +541,30 @@ def test_replayed_searches_follow_the_store():
         assert ctx.last_kernel() == "scan_gemv" and ctx.last_scan_ms() > 0
     best = int(first[2][0][0])
     st.set_deleted(best, True); alive[best] = False      # a writer: the next search is direct again
-    for _ in range(3):
+    for _ in range(4):
         assert list(ctx.search(q, k)[2][0]) == list(exact(x, alive))
     closer = (q + 1e-3).astype(np.float32)               # appended rows must be seen
     st.append(closer); st.seal()
     x2 = np.concatenate([x, closer]); alive2 = np.concatenate([alive, [True]])
-    for _ in range(3):
+    for _ in range(4):
         assert list(ctx.search(q, k)[2][0]) == list(exact(x2, alive2))
     st.write(7, closer[0], 7)                            # overwritten in place
     x2[7] = closer[0]
-    for _ in range(3):
+    for _ in range(4):
         assert list(ctx.search(q, k)[2][0])[:2] == [7, n]
-    for _ in range(3):                                   # other arguments: another recording
+    for _ in range(4):                                   # other arguments: another recording
         assert list(ctx.search(q, k, threshold=1e-3)[2][0][:2]) == [7, n]
         assert ctx.search(q, k, threshold=1e-3)[3][0] == 2
     big = ctx.search(rng.standard_normal((700, d)).astype(np.float32), 50)   # grows the context's buffers
     assert big[3].min() == 50
-    for _ in range(3):
+    for _ in range(4):
         assert list(ctx.search(q, k)[2][0])[:2] == [7, n]
     qd = rng.standard_normal((2, d)).astype(np.float32)  # the device-pointer form, keyed by its pointers
     import torch
     dq = torch.from_numpy(qd).cuda(); os_ = torch.empty((2, k), dtype=torch.float32, device="cuda")
     oi = torch.empty((2, k), dtype=torch.int32, device="cuda")
     want = ctx.search(qd, k)[2]
-    for _ in range(4):
+    for _ in range(5):
         oi.zero_()
         ctx.search_device(dq.data_ptr(), 2, k, os_.data_ptr(), oi.data_ptr()); ctx.sync()
         assert np.array_equal(oi.cpu().numpy().astype(np.uint32), want)

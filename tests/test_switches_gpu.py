@@ -18,12 +18,12 @@ sys.path.insert(0, %(root)r)
 import zvec_b200 as z
 out = {}
 rng = np.random.default_rng(2024)
-# flat fp32 L2, 1 and 3 queries, third call of each (a replayed graph when replay is on)
+# flat fp32 L2, 1 and 3 queries, fourth call of each (a replayed graph when replay is on)
 x = rng.standard_normal((50000, 64)).astype(np.float32)
 q = rng.standard_normal((3, 64)).astype(np.float32)
 st = z.Store(z.DT_FP32, z.METRIC_L2SQ, 64); st.append(x); st.seal(); ctx = z.Context(st)
 for b in (1, 3):
-    for _ in range(3):
+    for _ in range(4):
         r = ctx.search(q[:b], 10)
     out["flat%%d_i" %% b], out["flat%%d_s" %% b] = r[2], r[1]
 r = ctx.search(q, 10, threshold=float(np.median(out["flat3_s"])))
@@ -36,7 +36,7 @@ tail = np.zeros((n, 4), np.float32); tail[:, 0] = 1.0 / 127
 cf = codes.astype(np.float32); tail[:, 2] = cf.sum(1); tail[:, 3] = (cf * cf).sum(1)
 rows = np.concatenate([codes.view(np.uint8), tail.view(np.uint8).reshape(n, 16)], axis=1)
 st = z.Store(z.DT_INT8, z.METRIC_QI8_L2SQ, d + 16); st.append(rows); st.seal(); ctx = z.Context(st)
-for _ in range(3):
+for _ in range(4):
     r = ctx.search(rows[5:7], 100)
 out["qi8_i"], out["qi8_s"] = r[2], r[1]
 ctx.close(); st.close()
@@ -49,7 +49,7 @@ offs = np.searchsorted(lab, np.arange(nlist + 1)).astype(np.uint64)
 qs = (cent[[3, 77, 150]] + 0.3 * rng.standard_normal((3, d))).astype(np.float32)
 st = z.Store(z.DT_FP32, z.METRIC_L2SQ, d); st.append(x); st.seal(); st.ivf_attach(cent, offs); ctx = z.Context(st)
 for b in (1, 3):
-    for _ in range(3):
+    for _ in range(4):
         r = ctx.ivf_search(qs[:b], 10, 16, 3000)
     out["ivf%%d_i" %% b], out["ivf%%d_s" %% b], out["ivf%%d_c" %% b] = r[2], r[1], r[3]
 ctx.close(); st.close()

@@ -10,7 +10,6 @@ static std::atomic<uint64_t> g_launches{0};
 void count_launch(int n) { g_launches.fetch_add((uint64_t)n, std::memory_order_relaxed); }
 }  // namespace zvb
 
-std::atomic<uint64_t> g_buf_epoch{0};
 static thread_local std::string g_err;
 
 int zvb_set_err(int code, const char *what, const char *detail) {
@@ -605,7 +604,7 @@ static GraphKey graph_key(const zvb200_ctx *c, int fn, uint32_t q, uint32_t k, f
                           uint32_t nprobe = 0, uint64_t max_scan = 0) {
   GraphKey key;
   memset(&key, 0, sizeof key);
-  key.fn = fn; key.store = c->s; key.gen = c->s->gen; key.epoch = g_buf_epoch.load(std::memory_order_relaxed);
+  key.fn = fn; key.store = c->s; key.gen = c->s->gen; key.epoch = c->buffers_signature();
   key.rows = rows; key.max_scan = max_scan; key.q = q; key.k = k; key.nprobe = nprobe;
   memcpy(&key.thr_bits, &threshold, 4);
   key.mma_group_cap = c->mma_group_cap; key.force_kernel = c->force_kernel; key.operand_order = c->operand_order;
@@ -613,7 +612,7 @@ static GraphKey graph_key(const zvb200_ctx *c, int fn, uint32_t q, uint32_t k, f
 }
 
 // enqueue() puts the whole search on the context's stream (copies included) and returns 0; this runs it directly,
-// records it (second call with one key) or replays the recording.  The caller synchronises afterwards.
+// records it (third call with one key) or replays the recording.  The caller synchronises afterwards.
 template <class F>
 static int run_replayable(zvb200_ctx *c, const GraphKey &key, bool eligible, F &&enqueue) {
   ReplayGraph &g = c->rg;
@@ -622,17 +621,22 @@ static int run_replayable(zvb200_ctx *c, const GraphKey &key, bool eligible, F &
   if (same && g.exec) {
     CU(cudaGraphLaunch(g.exec, c->stream));
     count_launch((int)g.launches);
+    ++g.replays;
     c->last_kernel = g.last_kernel; c->last_mma_kind = g.last_mma_kind;
     return 0;
   }
+  if (g.failed) return enqueue();
   if (!same) {  // first call with these arguments: run it, every buffer gets its size
     g.reset();
     g.key = key; g.seen = 1;
     const int r = enqueue();
-    g.key.epoch = g_buf_epoch.load(std::memory_order_relaxed);  // what this very call allocated is part of the state
+    g.key.epoch = c->buffers_signature();  // what this very call allocated is part of the state
     return r;
   }
-  if (g.failed) return enqueue();
+  if (g.seen < 2) {  // second call: still direct (a recording has to be replayed a few times to pay for itself)
+    ++g.seen;
+    return enqueue();
+  }
   const uint64_t l0 = g_launches.load();
   if (cudaStreamBeginCapture(c->stream, cudaStreamCaptureModeThreadLocal) != cudaSuccess) {
     cudaGetLastError();
@@ -645,7 +649,7 @@ static int run_replayable(zvb200_ctx *c, const GraphKey &key, bool eligible, F &
   cudaGraph_t graph = nullptr;
   cudaError_t e = cudaStreamEndCapture(c->stream, &graph);
   const uint32_t launched = (uint32_t)(g_launches.load() - l0);
-  if (r == 0 && e == cudaSuccess && graph && g_buf_epoch.load(std::memory_order_relaxed) == key.epoch)
+  if (r == 0 && e == cudaSuccess && graph && c->buffers_signature() == key.epoch)
     e = cudaGraphInstantiate(&g.exec, graph, 0);
   else if (e == cudaSuccess)
     e = cudaErrorUnknown;

@@ -91,15 +91,11 @@ struct zvb200_store {
   }
 };
 
-// bumped by every re-allocation of a context buffer: a recorded search (ReplayGraph) holds the old pointers
-extern std::atomic<uint64_t> g_buf_epoch;
-
 struct DevBuf {
   void *p = nullptr;
   size_t cap = 0;
   cudaError_t ensure(size_t bytes) {
     if (bytes <= cap) return cudaSuccess;
-    g_buf_epoch.fetch_add(1, std::memory_order_relaxed);
     if (p) cudaFree(p);
     p = nullptr; cap = 0;
     size_t want = std::max(bytes, (size_t)4096);
@@ -114,7 +110,6 @@ struct HostBuf {
   size_t cap = 0;
   cudaError_t ensure(size_t bytes) {
     if (bytes <= cap) return cudaSuccess;
-    g_buf_epoch.fetch_add(1, std::memory_order_relaxed);
     if (p) cudaFreeHost(p);
     p = nullptr; cap = 0;
     size_t want = std::max(bytes, (size_t)4096);
@@ -128,7 +123,10 @@ struct HostBuf {
 // A small host-side search recorded as ONE CUDA graph (H2D of the queries, every kernel of the search, D2H of the
 // results): the second call of a context with the same arguments records it, later ones replay it with one
 // cudaGraphLaunch.  The key holds everything the launches were built from; the store's generation (bumped by every
-// writer) and the buffer epoch (bumped by every re-allocation) retire a stale recording.
+// writer) and a signature of the context's own buffers (pointer and size of each: a re-allocated buffer) retire a
+// stale recording.  Recording costs a few hundred microseconds, so it waits for the THIRD call with one key, and a
+// context whose recordings keep being retired before they are replayed (searches interleaved with ingest) stops
+// recording.
 struct GraphKey {  // compared with memcmp: 8-byte members first, an even number of 4-byte ones, no padding
   const void *store;
   const void *p0, *p1, *p2, *p3;  // the device-pointer forms: queries, filter, outputs
@@ -140,15 +138,20 @@ struct GraphKey {  // compared with memcmp: 8-byte members first, an even number
 static_assert(sizeof(GraphKey) == 5 * sizeof(void *) + 4 * 8 + 8 * 4, "GraphKey must not have padding");
 struct ReplayGraph {
   GraphKey key;
-  int seen = 0;
+  int seen = 0, churn = 0;
+  uint32_t replays = 0;
   bool failed = false;
   cudaGraphExec_t exec = nullptr;
   uint32_t launches = 0;
   const char *last_kernel = "none";
   int last_mma_kind = -1;
-  void reset() {
-    if (exec) cudaGraphExecDestroy(exec);
-    exec = nullptr; seen = 0; failed = false; launches = 0;
+  void reset() {  // another key: what was recorded (if anything) is dropped
+    if (exec) {
+      cudaGraphExecDestroy(exec);
+      churn = replays >= 8 ? 0 : churn + 1;  // a recording that paid for itself does not count
+      if (churn >= 16) failed = true;        // (for good: this context's searches do not repeat)
+    }
+    exec = nullptr; seen = 0; launches = 0; replays = 0;
   }
 };
 
@@ -178,6 +181,21 @@ struct zvb200_ctx {
   cudaEvent_t ev_ready = nullptr;
   DevBuf xkeys, gather, out_rows;  // packed local keys; [G][q][k] gathered keys; merged global rows
   HostBuf h_rows;
+  //! pointer and size of every buffer a recorded search may have been built from
+  uint64_t buffers_signature() const {
+    uint64_t h = 1469598103934665603ull;
+    auto mix = [&h](const void *p, size_t cap) {
+      h = (h ^ (uint64_t)(uintptr_t)p) * 1099511628211ull;
+      h = (h ^ (uint64_t)cap) * 1099511628211ull;
+    };
+    const DevBuf *d[] = {&qshadow, &qin, &qin2, &qf32, &qraw, &qtails, &qnorms, &part, &out_scores, &out_index, &filter,
+                         &misc, &gtau, &coarse_scores, &coarse_index, &seg_prefix, &seg_row, &seg_count, &seg_list, &lm,
+                         &qsrc, &cand, &xkeys, &gather, &out_rows};
+    for (const DevBuf *b : d) mix(b->p, b->cap);
+    const HostBuf *hb[] = {&h_q, &h_q2, &h_scores, &h_index, &h_rows};
+    for (const HostBuf *b : hb) mix(b->p, b->cap);
+    return h;
+  }
 };
 
 // the events that bracket a search's scan kernels; inside a recording they become event-record nodes of the graph
