@@ -46,6 +46,19 @@ def _scan_ms(ctx, fn, reps=5):
     return float(np.mean(v))
 
 
+def _traffic(kernel, rows, dim, batch):
+    """measured DRAM bytes per launch from profiles/traffic.json (one ncu --set full capture each), else None"""
+    import json, os
+    try:
+        with open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "traffic.json")) as f:
+            for e in json.load(f)["entries"]:
+                if (e["kernel"], e["rows"], e["dim"], e["batch"]) == (kernel, rows, dim, batch):
+                    return e["bytes"]
+    except (OSError, ValueError, KeyError):
+        pass
+    return None
+
+
 def _roof(bound, achieved, peak, unit, kernel, kernel_ms, algorithmic, note=None):
     r = {"bound": bound, "achieved": achieved, "peak": peak, "unit": unit, "frac": achieved / peak, "traffic": None,
          "kernel": kernel, "kernel_ms": kernel_ms, "algorithmic": algorithmic}
@@ -205,6 +218,7 @@ def c3(args, z, torch, dev, pk, compare_topk, merge_candidates, log):
         if b == 1:
             roof = _roof("hbm", st.scan_bytes() / (sm / 1e3) / 1e9, pk["hbm_gbs"], "GB/s", kern, sm,
                          "rows*112 B per launch = %.4g" % st.scan_bytes())
+            roof["traffic"] = _traffic(kern, n, d + 16, 1)  # ncu capture of exactly this launch, when committed
         else:
             fl = 2.0 * n * d * b
             roof = _roof("tensor", fl / (sm / 1e3) / 1e12, pk["tf_sustained"], "TFLOP/s", kern, sm,
