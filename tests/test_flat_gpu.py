@@ -597,3 +597,11 @@ def test_threshold_leaves_fewer_than_k_in_many_partial_lists(q):
     none = ctx.search(qs, k, threshold=-1.0)
     assert (none[3] == 0).all()
     ctx.close(); st.close()
+
+
+@pytest.mark.parametrize("kind", ["fp16_ip", "fp32_l2", "qi8_l2"])
+@pytest.mark.parametrize("q,k", [(5, 100), (40, 50), (64, 100), (65, 100)])
+def test_shared_memory_pools_of_half_and_full_query_tiles(kind, q, k):
+    """k > 16 keeps the tensor-core scan's top-k pools in shared memory; a launch of at most 64 queries lays them out
+    for 64 query slots (one more pipeline stage), 65 queries and more for 128 — both against the oracle."""
+    assert run_case(kind, 20000, 96, q, k, seed=300 + q + k, kernel=3) == "scan_mma"

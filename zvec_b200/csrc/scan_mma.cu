@@ -54,6 +54,8 @@ struct MmaArgs {
   uint32_t ntiles;      // row tiles of kBN
   uint32_t nkb;         // k-blocks of 64 halves
   uint32_t k, nstage;
+  uint32_t pool_stride;  // query slots per pool entry row: 128, or 64 when the launch has at most 64 queries (half the
+                         // shared memory: one more pipeline stage next to 100-entry pools)
   uint32_t row_begin, row_end;  // global row numbers (tensor map B starts at row_begin)
   int mode;             // 0: s = -dot (InnerProduct), 1: s = 1 - dot (Cosine) straight from the accumulator;
                         // 2/3/4: L2 / InnerProduct / Cosine with the accumulator as a FILTER and an exact re-score
@@ -310,7 +312,7 @@ scan_mma_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
   uint8_t *sbase = smem_raw + (base - smem_u32(smem_raw));
   const uint32_t k = a.k, nstage = a.nstage;
   u64 *lists = reinterpret_cast<u64 *>(sbase + (size_t)nstage * kStage);      // [k][128]: entry i of query s at i*128+s
-  uint64_t *bars = reinterpret_cast<uint64_t *>(lists + (size_t)kQM * k);     // full[ns] empty[ns] tfull[2] tempty[2] cfull[4] cempty[4]
+  uint64_t *bars = reinterpret_cast<uint64_t *>(lists + (size_t)a.pool_stride * k);     // full[ns] empty[ns] tfull[2] tempty[2] cfull[4] cempty[4]
   uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(bars + 2 * nstage + 12);
   float *colc = reinterpret_cast<float *>((reinterpret_cast<uintptr_t>(tmem_slot + 4) + 15) & ~(uintptr_t)15);  // [2][kBN] per-column constants (float, or float4 for int8)
   constexpr int kBKe = (KIND == 0 || KIND == 3) ? 64 : KIND == 1 ? 32 : 128;   // elements per 128-byte k-block
@@ -465,7 +467,8 @@ scan_mma_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
     // 32 lanes (one query each) hit 32 different banks, and so do 32 consecutive entries of ONE query — the whole warp
     // can rescan a single query's pool (accept_coop below) as well as every lane its own
     u64 *Lw = lists + ew * 32;
-#define ZVB_POOL(i) Lw[(size_t)(i) * kQM + (lane ^ ((i) & 31))]
+    const uint32_t pstride = a.pool_stride;  // (with 64, warps 2 and 3 hold no live query: they never store, see accept_coop)
+#define ZVB_POOL(i) Lw[(size_t)(i) * pstride + (lane ^ ((i) & 31))]
     // int8: the column value is MINUS the exact score, so the rest of the epilogue runs as mode 0 (s = -value)
     constexpr bool SH = KIND == 3;
     const int K = (int)k;
@@ -638,7 +641,7 @@ scan_mma_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
         u64 mx = 0;
         int mp = 0;
         for (int i = lane; i < K; i += 32) {  // i & 31 == lane: entry i of lane src's query
-          const u64 x = Lw[(size_t)i * kQM + (src ^ lane)];
+          const u64 x = Lw[(size_t)i * pstride + (src ^ lane)];
           if (x > mx) { mx = x; mp = i; }
         }
 #pragma unroll
@@ -1083,9 +1086,9 @@ bool make_map(CUtensorMap *tm, const void *ptr, int kind, uint32_t d, uint64_t r
 constexpr size_t kSmemMax = 232448;  // 227 KB
 
 // pipeline stages that fit next to the 128 x k lists; false when not even 2 stages fit
-bool mma_config(uint32_t k, size_t colc_bytes, uint32_t *nstage, size_t *smem) {
+bool mma_config(uint32_t k, size_t colc_bytes, uint32_t *nstage, size_t *smem, uint32_t pool_stride = kQM) {
   for (uint32_t ns = 4; ns >= 2; --ns) {
-    const size_t need = 1024 + (size_t)ns * kStage + (size_t)kQM * k * 8 + (2 * ns + 12) * 8 + 32 + colc_bytes;
+    const size_t need = 1024 + (size_t)ns * kStage + (size_t)pool_stride * k * 8 + (2 * ns + 12) * 8 + 32 + colc_bytes;
     if (need <= kSmemMax) { *nstage = ns; *smem = need; return true; }
   }
   return false;
@@ -1141,9 +1144,13 @@ cudaError_t launch_scan_mma(const RowsView &rv, const QueryView &qv, const Searc
                             uint32_t *pub, int sm_count, cudaStream_t st, int *kind_out) {
   uint32_t ns; size_t smem;
   const bool sh = use_shadow(rv) && qv.qshadow && !sp.no_shadow;
-  if (!mma_config(sp.k, colc_bytes_for(rv, sh), &ns, &smem)) return cudaErrorInvalidValue;
+  // at most 64 queries: half-size pools (measured at k = 100: 2 -> 3 pipeline stages)
+  static const bool half_off = [] { const char *e = getenv("ZVB200_MMA_HALF_POOL"); return e && atoi(e) == 0; }();
+  const uint32_t pool_stride = (!half_off && qv.q <= 64) ? 64 : kQM;
+  if (!mma_config(sp.k, colc_bytes_for(rv, sh), &ns, &smem, pool_stride)) return cudaErrorInvalidValue;
   const uint64_t nrows = row_end > row_begin ? row_end - row_begin : 0;
   MmaArgs a;
+  a.pool_stride = pool_stride;
   a.nq = qv.q;
   a.qtiles = (qv.q + kQM - 1) / kQM;
   if ((int)a.qtiles > sm_count) return cudaErrorInvalidValue;  // caller splits the batch
