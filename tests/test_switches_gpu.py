@@ -1,4 +1,4 @@
-"""The round-2 fast paths (CUDA-graph replay, radix-select merge, direct coarse stage, whole-row preload) against the
+"""The round-2 fast paths (CUDA-graph replay, radix-select merge, direct coarse stage, whole-row preload, half-tile pools) against the
 forms they replaced: the library reads its switches once per process, so each form runs in a process of its own on
 the same seeded inputs and the results are compared bit for bit."""
 import os
@@ -26,6 +26,10 @@ for b in (1, 3):
     for _ in range(4):
         r = ctx.search(q[:b], 10)
     out["flat%%d_i" %% b], out["flat%%d_s" %% b] = r[2], r[1]
+q40 = rng.standard_normal((40, 64)).astype(np.float32)
+r = ctx.search(q40, 50)                      # tensor-core scan, shared-memory pools of a half query tile
+assert ctx.last_kernel() == "scan_mma"
+out["mma40_i"], out["mma40_s"] = r[2], r[1]
 r = ctx.search(q, 10, threshold=float(np.median(out["flat3_s"])))
 out["thr_i"], out["thr_s"], out["thr_c"] = r[2], r[1], r[3]
 ctx.close(); st.close()
@@ -70,7 +74,8 @@ def test_fast_paths_equal_the_forms_they_replaced(tmp_path):
     base = _run(tmp_path, "default", {})
     assert base["ivf1_c"][0] == 10 and base["thr_c"].sum() > 0 and base["thr_c"].min() < 10
     for name, env in (("no_graph", {"ZVB200_GRAPH": "0"}), ("no_select", {"ZVB200_MERGE_SELECT": "0"}),
-                      ("no_direct", {"ZVB200_COARSE_DIRECT": "0"}), ("no_pre", {"ZVB200_GEMV_PRE": "0"})):
+                      ("no_direct", {"ZVB200_COARSE_DIRECT": "0"}), ("no_pre", {"ZVB200_GEMV_PRE": "0"}),
+                      ("full_pools", {"ZVB200_MMA_HALF_POOL": "0"})):
         other = _run(tmp_path, name, env)
         for key in base.files:
             a, b = base[key], other[key]
