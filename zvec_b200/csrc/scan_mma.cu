@@ -79,6 +79,7 @@ struct MmaArgs {
   u64 *part;            // [nq][groups][k]
   uint32_t *pub;        // [groups][nq] ordered image of each CTA's pub_j-th best score per query
   uint32_t pub_j;       // which list entry a CTA publishes (1-based)
+  uint32_t pub_groups;  // groups whose published words a CTA reads for the union bound: min(groups, 64)
   uint32_t pub_m;       // pub_m * pub_j >= k: the pub_m-th smallest published score bounds the global k-th best
   float sh_mrow_max;    // KIND 3: largest row share of the filter margin in the store (bootstrap bound)
   uint32_t sh_qcap;     // KIND 3: nominated rows a warp queues before it re-scores them together (<= 16)
@@ -691,12 +692,16 @@ scan_mma_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
       uint32_t best[16];
 #pragma unroll
       for (int i = 0; i < 16; ++i) best[i] = 0xffffffffu;
-      for (uint32_t g0 = 0; g0 < a.groups; g0 += 8) {
+      // Any SUBSET of the groups gives a sound bound too (its pub_m-th smallest word still has pub_m * pub_j >= k rows at
+      // or below it), only a looser one.  A launch of one query tile has up to 148 groups: 19 dependent rounds of
+      // loads, 13 us a call, ~100 us over a short scan (1.25M x 768 at batch 1: 0.36 ms where the rows take 0.27).
+      // Such a launch looks at the first 64 groups (its own best is in tau_key already).
+      for (uint32_t g0 = 0; g0 < a.pub_groups; g0 += 8) {
         uint32_t x[8];
 #pragma unroll
         for (int u = 0; u < 8; ++u)  // the loads first, so their latencies overlap
-          x[u] = g0 + u < a.groups ? *reinterpret_cast<volatile uint32_t *>(a.pub + (size_t)(g0 + u) * a.nq + qcol)
-                                   : 0xffffffffu;
+          x[u] = g0 + u < a.pub_groups ? *reinterpret_cast<volatile uint32_t *>(a.pub + (size_t)(g0 + u) * a.nq + qcol)
+                                : 0xffffffffu;
 #pragma unroll
         for (int u = 0; u < 8; ++u) {
           uint32_t y = x[u];
@@ -1191,6 +1196,7 @@ cudaError_t launch_scan_mma(const RowsView &rv, const QueryView &qv, const Searc
   a.pub = pub;
   {
     // publish the j-th best so that the m-th smallest of the G published words covers k rows (m <= min(G,16))
+    a.pub_groups = std::min<uint32_t>(a.groups, 64u);
     const uint32_t mmax = std::min<uint32_t>(a.groups, 16u);
     a.pub_j = (sp.k + mmax - 1) / mmax;
     a.pub_m = (sp.k + a.pub_j - 1) / a.pub_j;
