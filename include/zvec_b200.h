@@ -146,7 +146,12 @@ int zvb200_search(zvb200_ctx *c, const void *queries, uint32_t q, uint32_t k, fl
                   uint32_t *out_index, uint32_t *out_counts);
 
 /* Same with DEVICE-resident queries / filter / outputs, asynchronous on the context's
- * stream; out_scores_dev and out_index_dev are q*k.  zvb200_ctx_sync() waits. */
+ * stream; out_scores_dev and out_index_dev are q*k.  zvb200_ctx_sync() waits.
+ * Searches of at most 8 queries that repeat on a context with the same arguments (for this form: the same device
+ * pointers; the bytes behind them are read afresh) are recorded as one CUDA graph on the third call and replayed from
+ * the fourth — zvb200_search, zvb200_ivf_search, zvb200_ivf_search_split and the _device forms.  Anything the store's
+ * writers change, or a context buffer that has to grow, retires the recording; results never depend on it.
+ * Environment ZVB200_GRAPH=0 turns it off. */
 int zvb200_search_device(zvb200_ctx *c, const void *queries_dev, uint32_t q, uint32_t k,
                          float threshold, const uint32_t *filter_dev, float *out_scores_dev,
                          uint32_t *out_index_dev);
