@@ -279,7 +279,8 @@ int zvb200_ivf_search_split(zvb200_ctx *c, const void *coarse_queries, const voi
  * the scale of the row's posting list (quantize_by_centroid, IVFEntity::inverted_list_normalize_value, ivf_entity.h:
  * 204-224).  list_scales: nlist values, HOST, needs an attached IVF structure (NULL: `scale` for every row; 1 = off).
  * The product is what the threshold gates and the top-k compares, as in the reference's heap.  A scaled store is
- * scanned by the CUDA-core kernels (GEMV scan, posting-list scans) at any batch.  zvb200_ivf_attach* drops list scales. */
+ * scanned by the CUDA-core kernels (GEMV scan, posting-list scans) at any batch.  zvb200_ivf_attach* drops list scales;
+ * a store that holds list scales refuses appends (ZVB200_ERR_UNSUPPORTED): they cover the rows that were attached. */
 int zvb200_store_set_score_scale(zvb200_store *s, float scale, const float *list_scales);
 /* Sharded IVF (each GPU holds a slice of EVERY posting list): list_sizes[l] = rows of list l in the
  * whole index.  The scan budget of zvb200_ivf_search then counts these, so every shard visits exactly the lists

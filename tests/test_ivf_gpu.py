@@ -188,6 +188,10 @@ def test_typed_centroids_split_queries_and_score_scales(metric, per_list):
             ei_, es_ = expect(j, threshold, True)
             assert gc[j] == len(ei_) and np.array_equal(gi[j][:len(ei_)], ei_)
             assert np.array_equal(gs[j][:len(ei_)].view(np.uint32), es_.view(np.uint32))
+    if per_list:                                           # list scales cover the attached rows only: no append
+        with pytest.raises(z.ZvecB200Error) as ei:
+            st.append(rows[:1].view(np.uint8))
+        assert ei.value.code == -12
     st.ivf_attach_typed(cent.view(np.uint8), offs, z.DT_FP32, z.METRIC_L2SQ, cd)  # re-attaching drops the list scales
     st.set_score_scale(1.0, None)
     gk, gs, gi, gc = ctx.search(lq[:2].view(np.uint8), k)

@@ -164,6 +164,7 @@ int zvb200_store_append(zvb200_store *s, const void *rows, uint64_t n, const uin
   if (!s || (!rows && n)) return set_err(ZVB200_ERR_INVALID_ARGUMENT, "null argument");
   zvb200_store::Write g(s);
   if (int r = zvb_check_row_limit(s->n + n)) return r;
+  if (s->row_scale && n) return set_err(ZVB200_ERR_UNSUPPORTED, "per-list score scales cover the rows that were attached: no append");
   if (!s->shards.empty()) return zvb_sharded_append(s, rows, n, keys, false);
   CU(cudaSetDevice(s->device));
   int r = store_grow(s, s->n + n);
@@ -206,6 +207,7 @@ int zvb200_store_append_device(zvb200_store *s, const void *rows_dev, uint64_t n
   if (!s || (!rows_dev && n)) return set_err(ZVB200_ERR_INVALID_ARGUMENT, "null argument");
   zvb200_store::Write g(s);
   if (int r = zvb_check_row_limit(s->n + n)) return r;
+  if (s->row_scale && n) return set_err(ZVB200_ERR_UNSUPPORTED, "per-list score scales cover the rows that were attached: no append");
   if (!s->shards.empty()) return zvb_sharded_append(s, rows_dev, n, nullptr, true);
   CU(cudaSetDevice(s->device));
   int r = store_grow(s, s->n + n);
